@@ -1,0 +1,110 @@
+"""ctypes loader for libbiscotti_b200.so (C-ABI declared in include/biscotti_b200.h).
+
+The library is built in-tree by ``biscotti_b200.build``; it is loaded lazily so that importing the
+package never compiles anything.  On a machine with a GPU the CUDA entry points are mandatory: ops
+raise if the library is missing instead of silently falling back to PyTorch.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+
+_LIB = None
+_PATH = Path(__file__).resolve().parent / "lib" / "libbiscotti_b200.so"
+
+
+def lib_path() -> Path:
+    return _PATH
+
+
+def load(build_if_missing: bool = True) -> ctypes.CDLL:
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not _PATH.exists():
+        if not build_if_missing or os.environ.get("BISCOTTI_NO_BUILD"):
+            raise RuntimeError(f"{_PATH} is missing; run `python -m biscotti_b200.build`")
+        from . import build as _b
+
+        _b.build()
+    _LIB = ctypes.CDLL(str(_PATH))
+    _declare(_LIB)
+    return _LIB
+
+
+def available() -> bool:
+    try:
+        load()
+        return True
+    except Exception:
+        return False
+
+
+c_i = ctypes.c_int
+c_ll = ctypes.c_longlong
+c_ull = ctypes.c_ulonglong
+c_f = ctypes.c_float
+c_d = ctypes.c_double
+c_p = ctypes.c_void_p
+c_sz = ctypes.c_size_t
+c_cp = ctypes.c_char_p
+
+
+def _declare(L: ctypes.CDLL) -> None:
+    def sig(name, res, *args):
+        f = getattr(L, name, None)
+        if f is None:
+            return
+        f.restype = res
+        f.argtypes = list(args)
+
+    sig("bsc_launch_count", c_ull)
+    sig("bsc_launch_count_reset", None)
+    # ML kernels
+    sig("bsc_local_softmax_step", c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_f, c_p)
+    sig("bsc_local_logistic_step", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_ull, c_p, c_i, c_p)
+    sig("bsc_noise_mix", c_i, c_p, c_p, c_i, c_ull, c_i, c_f, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
+    sig("bsc_noise_row", c_i, c_p, c_i, c_ull, c_i, c_i, c_f, c_p)
+    sig("bsc_noise_row_host", None, c_p, c_i, c_ull, c_i, c_i, c_f)
+    sig("bsc_gram_simt", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
+    sig("bsc_krum_select", c_i, c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_p, c_p, c_p)
+    sig("bsc_eval_softmax", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p)
+    sig("bsc_eval_logistic", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
+    # secure aggregation
+    sig("bsc_quantize", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_d, c_p)
+    sig("bsc_shares_eval", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
+    sig("bsc_share_sum", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_d, c_p, c_p)
+    sig("bsc_reconstruct_step", c_i, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_d, c_p, c_p, c_p, c_p, c_p)
+    sig("bsc_plain_sum_step", c_i, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p)
+    sig("bsc_quantize_host", None, c_p, c_p, c_i, c_i, c_i, c_i, c_d)
+    sig("bsc_shares_eval_host", None, c_p, c_p, c_i, c_i, c_i, c_i)
+    sig("bsc_shamir_recover_host", c_i, c_p, c_p, c_p, c_i, c_i, c_p)
+    # MSM
+    sig("bsc_msm_groups", c_i, c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_ll, c_p)
+    sig("bsc_g1_fixed_base_mul", c_i, c_p, c_i, c_p, c_p, c_p)
+    sig("bsc_g1_normalize", c_i, c_p, c_p, c_ll, c_p)
+    sig("bsc_g1_affine_to_bytes", c_i, c_p, c_p, c_ll, c_p)
+    sig("bsc_g1_bytes_to_affine", c_i, c_p, c_p, c_ll, c_p)
+    sig("bsc_g1_sum_rows", c_i, c_p, c_p, c_i, c_ll, c_p, c_p)
+    sig("bsc_g1_sum_cols", c_i, c_p, c_i, c_i, c_p, c_p)
+    # host crypto
+    sig("bsc_sha256", None, c_cp, c_sz, c_p)
+    sig("bsc_blake2b", None, c_cp, c_sz, c_cp, c_sz, c_p, c_sz)
+    sig("bsc_blake2xb", None, c_cp, c_sz, c_cp, c_sz, c_p, c_sz)
+    sig("bsc_shake256", None, c_cp, c_sz, c_p, c_sz)
+    sig("bsc_g1_generator", None, c_p)
+    sig("bsc_g1_on_curve", c_i, c_cp)
+    sig("bsc_g1_add", None, c_p, c_cp, c_cp)
+    sig("bsc_g1_neg", None, c_p, c_cp)
+    sig("bsc_g1_mul", None, c_p, c_cp, c_cp)
+    sig("bsc_g1_msm_i64_host", None, c_p, c_cp, c_p, c_i)
+    sig("bsc_g1_bytes_to_affine_host", None, c_cp, c_p, c_ll)
+    sig("bsc_g1_affine_to_bytes_host", None, c_p, c_p, c_ll)
+    sig("bsc_g1_jac_to_bytes_host", None, c_p, c_p, c_ll)
+    sig("bsc_g1_straus_host", None, c_p, c_p, c_p, c_i)
+    sig("bsc_srs_g1_host", None, c_cp, c_i, c_p)
+    sig("bsc_fr_powers", None, c_cp, c_i, c_p)
+    sig("bsc_schnorr_pubkey", None, c_cp, c_p)
+    sig("bsc_schnorr_sign", None, c_cp, c_sz, c_cp, c_cp, c_p)
+    sig("bsc_schnorr_verify", c_i, c_cp, c_sz, c_cp, c_cp)

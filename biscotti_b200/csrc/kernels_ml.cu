@@ -1,0 +1,486 @@
+// Batched-over-peers local training steps, DP-noise mixing, evaluation, and the SIMT Krum kernels.
+//
+// Reference behaviour reproduced (see each kernel): ML/Pytorch/client.py:38-65 (one minibatch,
+// CrossEntropyLoss, clip_grad_norm 100, flatten in named_parameters order, update = -grad),
+// ML/code/logistic_model.py:92-140 (L2-regularised logistic step, delta = -alpha*g + own noise),
+// ML/Pytorch/client_obj.py:97-98 + DistSys/main.go:1530-1537, 1653-1656 (noiser noise, averaged),
+// ML/Pytorch/client_obj.py:114-143 (Multi-Krum scores and selection),
+// ML/Pytorch/client.py:136-172 (argmax error / attack rate).
+//
+// The reference runs these once per peer process on the CPU; here one CTA handles one simulated
+// peer and the whole population of a GPU is one launch.
+#include "common.cuh"
+#include "secagg_math.cuh"
+#include <cuda_bf16.h>
+
+namespace bsc {
+
+unsigned long long g_launch_count = 0;
+
+// ------------------------------------------------------------------------------------------------
+// K1: softmax regression, one CTA per peer.
+//   w      : [C*F + C] fp32  (weight row-major [C][F], then bias[C]) — the layout of
+//            SoftmaxModel.named_parameters() (ML/Pytorch/softmax_model.py)
+//   X      : [P][Ns][F] fp32 shard (or [P][B][F] minibatch when idx == nullptr, Ns == B)
+//   y      : [P][Ns] int32 labels
+//   idx    : [P][B] int32 rows of the shard that form this block's minibatch (may be null)
+//   U      : [P][ldu] fp32 out, U = -clip(grad)
+//   loss   : [P] fp32 out (mean CE of the minibatch)
+// dynamic smem: B*F (minibatch) + B*C (logits/dlogits) + 64 floats
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) local_softmax_step_kernel(
+    const float* __restrict__ w, const float* __restrict__ X, const int* __restrict__ y,
+    const int* __restrict__ idx, float* __restrict__ U, float* __restrict__ loss, int Ns, int B, int F,
+    int C, int ldu, float clip) {
+  extern __shared__ float smem[];
+  float* sX = smem;              // [B][F]
+  float* sL = sX + B * F;        // [B][C]
+  float* red = sL + B * C;       // 40
+  __shared__ int sy[64];
+  const int p = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+
+  // stage the minibatch (vectorised when F % 4 == 0)
+  for (int b = 0; b < B; b++) {
+    const int row = idx ? idx[p * B + b] : b;
+    const float* src = X + ((size_t)p * Ns + row) * F;
+    if ((F & 3) == 0) {
+      const float4* s4 = reinterpret_cast<const float4*>(src);
+      float4* d4 = reinterpret_cast<float4*>(sX + b * F);
+      for (int k = tid; k < (F >> 2); k += blockDim.x) d4[k] = s4[k];
+    } else {
+      for (int k = tid; k < F; k += blockDim.x) sX[b * F + k] = src[k];
+    }
+    if (tid == 0) sy[b] = y[(size_t)p * Ns + row];
+  }
+  __syncthreads();
+
+  // logits[b][c] = X[b] . W[c] + bias[c]
+  for (int pair = warp; pair < B * C; pair += nwarp) {
+    const int b = pair / C, c = pair % C;
+    const float* wr = w + (size_t)c * F;
+    float acc = 0.f;
+    for (int k = lane; k < F; k += 32) acc = fmaf(sX[b * F + k], wr[k], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) sL[b * C + c] = acc + w[(size_t)C * F + c];
+  }
+  __syncthreads();
+
+  // softmax + dlogits = (softmax - onehot)/B ; mean CE loss
+  float myloss = 0.f;
+  if (tid < B) {
+    float m = -INFINITY;
+    for (int c = 0; c < C; c++) m = fmaxf(m, sL[tid * C + c]);
+    float s = 0.f;
+    for (int c = 0; c < C; c++) s += expf(sL[tid * C + c] - m);
+    const float lse = m + logf(s);
+    const int lab = sy[tid];
+    myloss = (lse - sL[tid * C + lab]) / (float)B;
+    for (int c = 0; c < C; c++) {
+      float pr = expf(sL[tid * C + c] - lse);
+      sL[tid * C + c] = (pr - (c == lab ? 1.f : 0.f)) / (float)B;
+    }
+  }
+  float tl = block_sum(myloss, red);
+  if (tid == 0 && loss) loss[p] = tl;
+
+  // pass 1: squared global norm of (gW, gb)
+  float nrm = 0.f;
+  for (int k = tid; k < F; k += blockDim.x) {
+    for (int c = 0; c < C; c++) {
+      float g = 0.f;
+      for (int b = 0; b < B; b++) g = fmaf(sL[b * C + c], sX[b * F + k], g);
+      nrm = fmaf(g, g, nrm);
+    }
+  }
+  if (tid < C) {
+    float g = 0.f;
+    for (int b = 0; b < B; b++) g += sL[b * C + tid];
+    nrm = fmaf(g, g, nrm);
+  }
+  const float total = sqrtf(block_sum(nrm, red));
+  // torch.nn.utils.clip_grad_norm: coef = max_norm / (total + 1e-6), applied when < 1
+  float coef = clip / (total + 1e-6f);
+  if (coef > 1.f) coef = 1.f;
+
+  // pass 2: write U = -coef * grad
+  float* out = U + (size_t)p * ldu;
+  for (int k = tid; k < F; k += blockDim.x) {
+    for (int c = 0; c < C; c++) {
+      float g = 0.f;
+      for (int b = 0; b < B; b++) g = fmaf(sL[b * C + c], sX[b * F + k], g);
+      out[(size_t)c * F + k] = -coef * g;
+    }
+  }
+  if (tid < C) {
+    float g = 0.f;
+    for (int b = 0; b < B; b++) g += sL[b * C + tid];
+    out[(size_t)C * F + tid] = -coef * g;
+  }
+  for (int k = C * F + C + tid; k < ldu; k += blockDim.x) out[k] = 0.f;  // zero the padding
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1b: logistic regression (creditcard path), labels in {-1,+1}.
+//   g = (1/B) X^T(-y / (1+exp(y Xw))) + lambda w ;  U = -alpha g + own_noise
+//   (ML/code/logistic_model.py:92-140; own noise = (-alpha/B) * sigma * sum_B N(0,1), :79-83,108-109)
+// One warp per peer.
+// ------------------------------------------------------------------------------------------------
+__global__ void local_logistic_step_kernel(const float* __restrict__ w, const float* __restrict__ X,
+                                           const float* __restrict__ y, const int* __restrict__ idx,
+                                           float* __restrict__ U, int P, int Ns, int B, int F, int ldu,
+                                           float alpha, float lambda, float own_noise_scale,
+                                           unsigned long long seed, const int* __restrict__ peer_ids,
+                                           int slot) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw >= P) return;
+  const int p = gw;
+  // res[b] = -y / (1 + exp(y * x.w))
+  float g_acc[4] = {0.f, 0.f, 0.f, 0.f};  // supports F <= 128
+  for (int b = 0; b < B; b++) {
+    const int row = idx ? idx[p * B + b] : b;
+    const float* xr = X + ((size_t)p * Ns + row) * F;
+    float dot = 0.f;
+    for (int k = lane; k < F; k += 32) dot = fmaf(xr[k], w[k], dot);
+    dot = warp_sum(dot);
+    const float yy = y[(size_t)p * Ns + row];
+    const float res = -yy / (1.f + expf(yy * dot));
+    for (int k = lane, j = 0; k < F; k += 32, j++) g_acc[j] = fmaf(xr[k], res, g_acc[j]);
+  }
+  const int gid = peer_ids ? peer_ids[p] : p;
+  for (int k = lane, j = 0; k < F; k += 32, j++) {
+    float g = g_acc[j] / (float)B + lambda * w[k];
+    float nz = 0.f;
+    if (own_noise_scale != 0.f) nz = own_noise_scale * gauss1(seed ^ 0x6f776e6eull, gid, slot, k);
+    U[(size_t)p * ldu + k] = -alpha * g + nz;
+  }
+  for (int k = F + lane; k < ldu; k += 32) U[(size_t)p * ldu + k] = 0.f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3/K17: noiser noise, regenerated from counters and averaged (DistSys/main.go:1592-1660), fused
+// with everything the Krum Gram kernel needs: the noised update in fp32, its split into two bf16
+// planes (hi = bf16(u), lo = bf16(u - hi); hi*hi + hi*lo + lo*hi reproduces the fp32 product to
+// ~2^-16 relative) and the fp32 squared row norm.  One CTA per peer.
+//   noisers : [P][nn] global ids of each peer's noisers (-1 = none)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) noise_mix_kernel(
+    const float* __restrict__ U, const int* __restrict__ noisers, int nn, unsigned long long seed, int slot,
+    float noise_scale, float* __restrict__ Un, __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo,
+    float* __restrict__ norms, int d, int ldu, int ldh) {
+  __shared__ float red[40];
+  __shared__ int snz[64];
+  const int p = blockIdx.x, tid = threadIdx.x;
+  int cnt = 0;
+  if (tid == 0) {
+    for (int q = 0; q < nn; q++) {
+      int id = noisers ? noisers[p * nn + q] : -1;
+      if (id >= 0) snz[cnt++] = id;
+    }
+    snz[63] = cnt;
+  }
+  __syncthreads();
+  cnt = snz[63];
+  const float inv = cnt > 0 ? noise_scale / (float)cnt : 0.f;
+  float nrm = 0.f;
+  const int d4 = (d + 3) >> 2;
+  for (int cb = tid; cb < d4; cb += blockDim.x) {
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int q = 0; q < cnt; q++) {
+      float g[4];
+      gauss4(seed, (uint32_t)snz[q], (uint32_t)slot, (uint32_t)cb, g);
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[j] += g[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int k = 4 * cb + j;
+      if (k < d) {
+        const float v = U[(size_t)p * ldu + k] + inv * acc[j];
+        if (Un) Un[(size_t)p * ldu + k] = v;
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        const float r = v - __bfloat162float(h);
+        if (hi) {
+          hi[(size_t)p * ldh + k] = h;
+          lo[(size_t)p * ldh + k] = __float2bfloat16_rn(r);
+        }
+        nrm = fmaf(v, v, nrm);
+      }
+    }
+  }
+  // zero padding columns so the Gram kernel can run over ldh without masks
+  for (int k = d + tid; k < ldh; k += blockDim.x) {
+    if (hi) {
+      hi[(size_t)p * ldh + k] = __float2bfloat16_rn(0.f);
+      lo[(size_t)p * ldh + k] = __float2bfloat16_rn(0.f);
+    }
+  }
+  for (int k = d + tid; k < ldu; k += blockDim.x)
+    if (Un) Un[(size_t)p * ldu + k] = 0.f;
+  const float t = block_sum(nrm, red);
+  if (tid == 0 && norms) norms[p] = t;
+}
+
+// raw noise table row (RequestNoise parity + tests): out[k] = scale * N(0,1)(peer, slot, k)
+__global__ void noise_row_kernel(float* __restrict__ out, int d, unsigned long long seed, int peer, int slot,
+                                 float scale) {
+  const int cb = blockIdx.x * blockDim.x + threadIdx.x;
+  if (4 * cb >= d) return;
+  float g[4];
+  gauss4(seed, peer, slot, cb, g);
+  for (int j = 0; j < 4; j++)
+    if (4 * cb + j < d) out[4 * cb + j] = scale * g[j];
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 (SIMT baseline / oracle on device): G = A A^T in fp32, 32x32 tiles, K streamed.
+// The product path is krum_gram_tc (tcgen05); this kernel is the un-fused baseline of SURVEY 8.11
+// and the on-device cross-check.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gram_simt_kernel(const float* __restrict__ A, float* __restrict__ G,
+                                                        int n, int d, int lda, int ksplit) {
+  __shared__ float sa[32][33], sb[32][33];
+  const int ti = blockIdx.x, tj = blockIdx.y, ks = blockIdx.z;
+  if (tj < ti) return;  // symmetric: upper tiles only
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int kchunk = ((d + ksplit - 1) / ksplit + 31) & ~31;
+  const int k0 = ks * kchunk, k1 = min(d, k0 + kchunk);
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int kb = k0; kb < k1; kb += 32) {
+    for (int r = ty; r < 32; r += 8) {
+      const int ri = ti * 32 + r, rj = tj * 32 + r, k = kb + tx;
+      sa[r][tx] = (ri < n && k < k1) ? A[(size_t)ri * lda + k] : 0.f;
+      sb[r][tx] = (rj < n && k < k1) ? A[(size_t)rj * lda + k] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 32; kk++) {
+      const float bv = sb[tx][kk];
+#pragma unroll
+      for (int q = 0; q < 4; q++) acc[q] = fmaf(sa[ty + 8 * q][kk], bv, acc[q]);
+    }
+    __syncthreads();
+  }
+  for (int q = 0; q < 4; q++) {
+    const int i = ti * 32 + ty + 8 * q, j = tj * 32 + tx;
+    if (i < n && j < n) {
+      float* dst = G + (size_t)ks * n * n;
+      dst[(size_t)i * n + j] = acc[q];
+      if (ti != tj) dst[(size_t)j * n + i] = acc[q];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 tail: fixed-order reduction of split-K partial Grams, distances, per-row sort, Krum scores and
+// the Multi-Krum accept set.  Single CTA (n <= 1024); one warp sorts one row at a time (bitonic in
+// shared memory).  Deterministic: partials are summed in index order and score ties break by id.
+//   Gpart  : [nsplit][ldg][ldg] fp32 partial Gram matrices (ldg >= n)
+//   scores : [n] out ; accept : [n] uint8 out ; D : optional [n][n] distances out
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) krum_select_kernel(const float* __restrict__ Gpart, int nsplit, int ldg,
+                                                          const float* __restrict__ norms, int n, int clip,
+                                                          float* __restrict__ scores,
+                                                          unsigned char* __restrict__ accept,
+                                                          float* __restrict__ Dout, int np2) {
+  extern __shared__ float srow[];  // [nwarp][np2] + [n] scores
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  float* myrow = srow + (size_t)warp * np2;
+  float* ssc = srow + (size_t)nwarp * np2;
+  const int group = n - clip;
+  for (int i = warp; i < n; i += nwarp) {
+    const float ni = norms[i];
+    for (int j = lane; j < np2; j += 32) {
+      float v = INFINITY;
+      if (j < n) {
+        float g = 0.f;
+        for (int s = 0; s < nsplit; s++) g += Gpart[((size_t)s * ldg + i) * ldg + j];
+        v = ni + norms[j] - 2.f * g;
+        if (Dout) Dout[(size_t)i * n + j] = v;
+      }
+      myrow[j] = v;
+    }
+    __syncwarp();
+    // bitonic sort ascending over np2 elements
+    for (int k = 2; k <= np2; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = lane; t < np2; t += 32) {
+          const int ixj = t ^ j;
+          if (ixj > t) {
+            const float a = myrow[t], b = myrow[ixj];
+            const bool up = ((t & k) == 0);
+            if ((a > b) == up) {
+              myrow[t] = b;
+              myrow[ixj] = a;
+            }
+          }
+        }
+        __syncwarp();
+      }
+    }
+    // score = sum(sorted[1 : group-1])
+    float s = 0.f;
+    for (int j = 1 + lane; j < group - 1; j += 32) s += myrow[j];
+    s = warp_sum(s);
+    if (lane == 0) {
+      ssc[i] = s;
+      scores[i] = s;
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += blockDim.x) {
+    const float si = ssc[i];
+    int rank = 0;
+    for (int j = 0; j < n; j++) {
+      const float sj = ssc[j];
+      rank += (sj < si) || (sj == si && j < i);
+    }
+    accept[i] = rank < (n - clip) ? 1 : 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K14/K15: argmax classification error of linear models over a held-out set, batched over
+// candidate weight vectors (RONI = error(w + delta_i) - error(w), client_obj.py:100-112).
+//   Wc : [M][ldw] candidate weights (softmax layout) ; X : [N][F]; y : [N]
+//   wrong : [M] int32 out (count of misclassified rows; caller zero-fills)
+// grid (ceil(N/8), M), 8 warps per CTA, one row per warp.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) eval_softmax_kernel(const float* __restrict__ Wc, const float* __restrict__ base,
+                                                           const float* __restrict__ X, const int* __restrict__ y,
+                                                           int* __restrict__ wrong, int N, int F, int C, int ldw) {
+  const int m = blockIdx.y;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= N) return;
+  const float* w = Wc + (size_t)m * ldw;
+  float best = -INFINITY;
+  int arg = 0;
+  for (int c = 0; c < C; c++) {
+    float acc = 0.f;
+    for (int k = lane; k < F; k += 32) {
+      float wv = w[(size_t)c * F + k];
+      if (base) wv += base[(size_t)c * F + k];
+      acc = fmaf(X[(size_t)row * F + k], wv, acc);
+    }
+    acc = warp_sum(acc);
+    float bias = w[(size_t)C * F + c];
+    if (base) bias += base[(size_t)C * F + c];
+    acc += bias;
+    if (acc > best) {
+      best = acc;
+      arg = c;
+    }
+  }
+  if (lane == 0 && arg != y[row]) atomicAdd(&wrong[m], 1);
+}
+
+// logistic (sign classifier) error: ML/code/logistic_model_test.py:13-24
+__global__ void eval_logistic_kernel(const float* __restrict__ Wc, const float* __restrict__ base,
+                                     const float* __restrict__ X, const float* __restrict__ y,
+                                     int* __restrict__ wrong, int N, int F, int ldw) {
+  const int m = blockIdx.y;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= N) return;
+  float acc = 0.f;
+  for (int k = lane; k < F; k += 32) {
+    float wv = Wc[(size_t)m * ldw + k];
+    if (base) wv += base[k];
+    acc = fmaf(X[(size_t)row * F + k], wv, acc);
+  }
+  acc = warp_sum(acc);
+  const float pred = acc >= 0.f ? 1.f : -1.f;
+  if (lane == 0 && pred != y[row]) atomicAdd(&wrong[m], 1);
+}
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+unsigned long long bsc_launch_count() { return g_launch_count; }
+void bsc_launch_count_reset() { g_launch_count = 0; }
+
+int bsc_local_softmax_step(const float* w, const float* X, const int* y, const int* idx, float* U, float* loss,
+                           int P, int Ns, int B, int F, int C, int ldu, float clip, void* stream) {
+  if (B > 64 || C > 32) return -1;
+  const size_t smem = ((size_t)B * F + (size_t)B * C + 64) * sizeof(float);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    BSC_CHECK(cudaFuncSetAttribute(local_softmax_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  local_softmax_step_kernel<<<P, 256, smem, (cudaStream_t)stream>>>(w, X, y, idx, U, loss, Ns, B, F, C, ldu, clip);
+  return finish_launch("local_softmax_step");
+}
+
+int bsc_local_logistic_step(const float* w, const float* X, const float* y, const int* idx, float* U, int P, int Ns,
+                            int B, int F, int ldu, float alpha, float lambda, float own_noise_scale,
+                            unsigned long long seed, const int* peer_ids, int slot, void* stream) {
+  if (F > 128) return -1;
+  const int threads = 128, wpb = threads / 32;
+  local_logistic_step_kernel<<<(P + wpb - 1) / wpb, threads, 0, (cudaStream_t)stream>>>(
+      w, X, y, idx, U, P, Ns, B, F, ldu, alpha, lambda, own_noise_scale, seed, peer_ids, slot);
+  return finish_launch("local_logistic_step");
+}
+
+int bsc_noise_mix(const float* U, const int* noisers, int nn, unsigned long long seed, int slot, float noise_scale,
+                  float* Un, void* hi, void* lo, float* norms, int P, int d, int ldu, int ldh, void* stream) {
+  if (nn > 62) return -1;
+  noise_mix_kernel<<<P, 256, 0, (cudaStream_t)stream>>>(U, noisers, nn, seed, slot, noise_scale, Un,
+                                                         (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, norms, d, ldu, ldh);
+  return finish_launch("noise_mix");
+}
+
+int bsc_noise_row(float* out, int d, unsigned long long seed, int peer, int slot, float scale, void* stream) {
+  const int n4 = (d + 3) / 4;
+  noise_row_kernel<<<(n4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(out, d, seed, peer, slot, scale);
+  return finish_launch("noise_row");
+}
+
+// host restatement of the same generator (CPU path + oracle)
+void bsc_noise_row_host(float* out, int d, unsigned long long seed, int peer, int slot, float scale) {
+  for (int cb = 0; 4 * cb < d; cb++) {
+    float g[4];
+    gauss4(seed, peer, slot, cb, g);
+    for (int j = 0; j < 4 && 4 * cb + j < d; j++) out[4 * cb + j] = scale * g[j];
+  }
+}
+
+int bsc_gram_simt(const float* A, float* Gpart, int n, int d, int lda, int ksplit, void* stream) {
+  const int nt = (n + 31) / 32;
+  dim3 grid(nt, nt, ksplit);
+  gram_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A, Gpart, n, d, lda, ksplit);
+  return finish_launch("gram_simt");
+}
+
+int bsc_krum_select(const float* Gpart, int nsplit, int ldg, const float* norms, int n, int clip, float* scores,
+                    unsigned char* accept, float* Dout, void* stream) {
+  if (n > 1024 || n < 3) return -1;
+  int np2 = 32;
+  while (np2 < n) np2 <<= 1;
+  const size_t smem = ((size_t)8 * np2 + n) * sizeof(float);
+  krum_select_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(Gpart, nsplit, ldg, norms, n, clip, scores, accept, Dout,
+                                                              np2);
+  return finish_launch("krum_select");
+}
+
+int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F,
+                     int C, int ldw, void* stream) {
+  dim3 grid((N + 7) / 8, M);
+  eval_softmax_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(Wc, base, X, y, wrong, N, F, C, ldw);
+  return finish_launch("eval_softmax");
+}
+
+int bsc_eval_logistic(const float* Wc, const float* base, const float* X, const float* y, int* wrong, int M, int N,
+                      int F, int ldw, void* stream) {
+  dim3 grid((N + 7) / 8, M);
+  eval_logistic_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(Wc, base, X, y, wrong, N, F, ldw);
+  return finish_launch("eval_logistic");
+}
+
+}  // extern "C"

@@ -1,0 +1,184 @@
+// BN256 G1 multi-scalar multiplication for polynomial commitments and KZG witnesses, batched over
+// peers x chunks x shares.
+//
+// Reference work replaced (all double-and-add per term on the CPU, amd64 asm field):
+//   createCommitment            DistSys/kyber.go:533-562   sum_i coeff_i * PKG1_i
+//   fillPolynomialMap           DistSys/kyber.go:172-202   per-chunk commitment with SRS slice [10c,10c+10)
+//   createShareAndWitness       DistSys/kyber.go:579-646   witness = commit(quotient (p(X)-p(x))/(X-x))
+//   aggregateSecret             DistSys/kyber.go:244-287   G1 adds of commitments / witnesses
+//
+// B200 design: witnesses are rewritten as 9-term MSMs with the *update coefficients themselves* as
+// scalars over a precomputed per-(chunk, share) base table
+//     W_{c,s} = sum_{j=1..9} a_j * T_{c,s,j},   T_{c,s,j} = sum_{k<j} x_s^{j-1-k} * PKG1[10c+k]
+// (identical group element to committing to the quotient polynomial), so every scalar is a small
+// signed fixed-point integer (|a| <~ 2^20) instead of a ~2^50 quotient coefficient.  One thread
+// computes one output with an interleaved (Straus) doubling chain; consecutive threads share the
+// bases of a group so base loads are warp-broadcast.  Results are normalised with Montgomery's
+// batched-inversion trick.
+#include "common.cuh"
+#include "g1.cuh"
+
+namespace bsc {
+
+constexpr int MSM_TMAX = 16;
+
+//   Q      : [rows][ldq] int64 scalars ; sel[p] (optional) maps output peer p to a row of Q
+//   sidx[g]: offset of group g's first scalar within a row ; bidx[g]: index of its first base
+//   og[g]  : output offset of group g (optional, default g) ; out[p*ostride_p + og[g]]
+__global__ void __launch_bounds__(128) msm_groups_kernel(const long long* __restrict__ Q, int ldq,
+                                                         const int* __restrict__ sel, int P,
+                                                         const int* __restrict__ sidx, const int* __restrict__ bidx,
+                                                         const int* __restrict__ og, int G, int T,
+                                                         const G1Affine* __restrict__ bases, G1Jac* __restrict__ out,
+                                                         long long ostride_p) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < (long long)G * P;
+  const int g = live ? (int)(i / P) : 0, p = live ? (int)(i % P) : 0;
+  const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
+  int64_t s[MSM_TMAX];
+  uint64_t maxmag = 0;
+  for (int t = 0; t < T; t++) {
+    s[t] = live ? row[t] : 0;
+    const uint64_t m = s[t] < 0 ? (uint64_t)0 - (uint64_t)s[t] : (uint64_t)s[t];
+    maxmag |= m;
+  }
+  int nbits = 64 - __clzll((long long)maxmag);
+  if (maxmag == 0) nbits = 0;
+  // keep the warp in lock-step on the shared doubling chain
+  nbits = __reduce_max_sync(0xffffffffu, nbits);
+  const G1Jac acc = g1_straus_i64<MSM_TMAX>(bases + bidx[g], s, T, nbits);
+  if (live) out[(size_t)p * ostride_p + (og ? og[g] : g)] = acc;
+}
+
+// k_i * B for full 256-bit scalars (SRS generation: PKG1[i] = tau^i * G, DistSys/publicKey.go:28-66)
+__global__ void g1_fixed_base_mul_kernel(const U256* __restrict__ k, int N, G1Affine base, G1Jac* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  out[i] = g1_mul_u256(base, k[i]);
+}
+
+// Jacobian -> affine (Montgomery form), BATCH points per thread share one field inversion.
+constexpr int NORM_BATCH = 8;
+__global__ void __launch_bounds__(128) g1_normalize_kernel(const G1Jac* __restrict__ in, G1Affine* __restrict__ out,
+                                                           long long N) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long base = t * NORM_BATCH;
+  if (base >= N) return;
+  Fp z[NORM_BATCH], pre[NORM_BATCH];
+  const int cnt = (int)min((long long)NORM_BATCH, N - base);
+  Fp run = fe_one<BnP>();
+  for (int i = 0; i < NORM_BATCH; i++) {
+    z[i] = (i < cnt) ? in[base + i].z : fe_one<BnP>();
+    if (fe_is_zero(z[i])) z[i] = fe_one<BnP>();  // infinity: handled by the flag below
+    run = fe_mul(run, z[i]);
+    pre[i] = run;
+  }
+  Fp inv = fe_inv(run);
+  for (int i = NORM_BATCH - 1; i >= 0; i--) {
+    const Fp zi = (i > 0) ? fe_mul(inv, pre[i - 1]) : inv;
+    inv = fe_mul(inv, z[i]);
+    if (i < cnt) {
+      const G1Jac pt = in[base + i];
+      out[base + i] = g1j_to_affine_with_inv(pt, zi);
+    }
+  }
+}
+
+__global__ void g1_affine_to_bytes_kernel(const G1Affine* __restrict__ in, unsigned char* __restrict__ out, long long N) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  g1a_to_bytes(out + 64 * i, in[i]);
+}
+__global__ void g1_bytes_to_affine_kernel(const unsigned char* __restrict__ in, G1Affine* __restrict__ out, long long N) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  out[i] = g1a_from_bytes(in + 64 * i);
+}
+
+// Miner aggregation (kyber.go:244-287): out[g] = sum_{q<nsel} pts[sel[q]*G + g], affine inputs.
+__global__ void __launch_bounds__(128) g1_sum_rows_kernel(const G1Affine* __restrict__ pts, const int* __restrict__ sel,
+                                                          int nsel, long long G, G1Jac* __restrict__ out) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  G1Jac acc = g1j_inf();
+  for (int q = 0; q < nsel; q++) acc = g1j_add_affine(acc, pts[(size_t)sel[q] * G + g]);
+  out[g] = acc;
+}
+
+// Full-vector commitment = sum of the chunk commitments: one CTA per row,
+// strided partial sums then a shared-memory Jacobian tree.  out[p] = sum_{g<G} pts[p*G + g].
+__global__ void __launch_bounds__(128) g1_sum_cols_kernel(const G1Affine* __restrict__ pts, int G,
+                                                          G1Jac* __restrict__ out) {
+  __shared__ G1Jac sh[128];
+  const int p = blockIdx.x, tid = threadIdx.x;
+  G1Jac acc = g1j_inf();
+  for (int g = tid; g < G; g += blockDim.x) acc = g1j_add_affine(acc, pts[(size_t)p * G + g]);
+  sh[tid] = acc;
+  __syncthreads();
+  for (int s = blockDim.x >> 1; s > 0; s >>= 1) {
+    if (tid < s) sh[tid] = g1j_add(sh[tid], sh[tid + s]);
+    __syncthreads();
+  }
+  if (tid == 0) out[p] = sh[0];
+}
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+int bsc_msm_groups(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og,
+                   int G, int T, const void* bases_affine, void* out_jac, long long ostride_p, void* stream) {
+  if (T > MSM_TMAX) return -1;
+  const long long n = (long long)G * P;
+  if (n == 0) return 0;
+  msm_groups_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)bases_affine, (G1Jac*)out_jac, ostride_p);
+  return finish_launch("msm_groups");
+}
+
+int bsc_g1_fixed_base_mul(const void* scalars_u256, int N, const void* base_affine, void* out_jac, void* stream) {
+  G1Affine b;
+  BSC_CHECK(cudaMemcpy(&b, base_affine, sizeof(b), cudaMemcpyDefault));
+  g1_fixed_base_mul_kernel<<<(N + 63) / 64, 64, 0, (cudaStream_t)stream>>>((const U256*)scalars_u256, N, b,
+                                                                            (G1Jac*)out_jac);
+  return finish_launch("g1_fixed_base_mul");
+}
+
+int bsc_g1_normalize(const void* in_jac, void* out_affine, long long N, void* stream) {
+  const long long nt = (N + NORM_BATCH - 1) / NORM_BATCH;
+  if (nt == 0) return 0;
+  g1_normalize_kernel<<<(unsigned)((nt + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Jac*)in_jac,
+                                                                                       (G1Affine*)out_affine, N);
+  return finish_launch("g1_normalize");
+}
+
+int bsc_g1_affine_to_bytes(const void* in_affine, unsigned char* out, long long N, void* stream) {
+  if (N == 0) return 0;
+  g1_affine_to_bytes_kernel<<<(unsigned)((N + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)in_affine,
+                                                                                          out, N);
+  return finish_launch("g1_affine_to_bytes");
+}
+
+int bsc_g1_bytes_to_affine(const unsigned char* in, void* out_affine, long long N, void* stream) {
+  if (N == 0) return 0;
+  g1_bytes_to_affine_kernel<<<(unsigned)((N + 127) / 128), 128, 0, (cudaStream_t)stream>>>(in, (G1Affine*)out_affine,
+                                                                                          N);
+  return finish_launch("g1_bytes_to_affine");
+}
+
+int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
+  if (G == 0) return 0;
+  g1_sum_rows_kernel<<<(unsigned)((G + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)pts_affine, sel,
+                                                                                   nsel, G, (G1Jac*)out_jac);
+  return finish_launch("g1_sum_rows");
+}
+
+int bsc_g1_sum_cols(const void* pts_affine, int P, int G, void* out_jac, void* stream) {
+  if (P == 0) return 0;
+  g1_sum_cols_kernel<<<P, 128, 0, (cudaStream_t)stream>>>((const G1Affine*)pts_affine, G, (G1Jac*)out_jac);
+  return finish_launch("g1_sum_cols");
+}
+
+}  // extern "C"
