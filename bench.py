@@ -1,0 +1,249 @@
+#!/usr/bin/env python
+"""Headline benchmark: block iterations/sec at 100 peers, MNIST softmax (BASELINE.json).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework
+    python bench.py --impl reference ...                     # the unmodified reference, if installable
+
+One "step" is one complete Biscotti block iteration with everything on (local SGD step of every
+worker, KZG commitments, VRF noiser lottery + DP noise, Multi-Krum, Shamir shares + witnesses for
+every approved worker, miner aggregation, reconstruction, SGD step, block hash + ledger append,
+test-error / attack-rate evaluation) — the same work the reference's 39.5 s/block covers.
+Total work is fixed at 100 peers, so scaling over N GPUs is strong scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+BASELINE_BLOCKS_PER_S = 1.0 / 39.5          # BASELINE.md headline: 39.5 s/block, 100 peers, MNIST
+REF_UNAVAILABLE = ("reference is a Go 1.10 + CPython 2.7 program (go-python, net/rpc); no go/python2 toolchain in "
+                   "this image and it has no setup.py/pyproject, so pip cannot build or install it")
+
+
+def reference_arm(args):
+    print(json.dumps({"impl": "reference", "unavailable": REF_UNAVAILABLE}))
+    return 0
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period: float = 0.2):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.ok:
+            self.join(timeout=2)
+        return {"sm_mhz": (statistics.median(self.samples) if self.samples else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--peers", type=int, default=100)
+    ap.add_argument("--dataset", default="mnist")
+    ap.add_argument("--comm", default=None, help="fused | nccl (default: fused when available)")
+    ap.add_argument("--gram", default="auto")
+    ap.add_argument("--profile-phases", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from biscotti_b200 import _native
+    from biscotti_b200.config import BiscottiConfig
+    from biscotti_b200.parallel.comm import init_distributed, NcclComm
+    from biscotti_b200.protocol.engine import BiscottiEngine
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device; bench.py measures the B200 path"}))
+        return 1
+    rank, local, world = init_distributed("cuda")
+    if world == 1:
+        torch.cuda.set_device(0)
+        local = 0
+    dev = torch.device("cuda", local)
+    L = _native.load()
+    cfg = BiscottiConfig(num_nodes=args.peers, dataset=args.dataset, max_iterations=args.steps + args.warmup + 8,
+                         gram_impl=args.gram)
+    comm = None
+    comm_name = "single"
+    if world > 1:
+        comm_name = args.comm or "fused"
+        comm = None
+        if comm_name == "fused":
+            try:
+                from biscotti_b200.parallel.fused import FusedComm
+
+                comm = FusedComm(rank, world, dev, cfg)
+            except Exception as e:  # fused path unavailable: say so and use the library baseline
+                if rank == 0:
+                    print(f"[bench] fused comm unavailable ({e}); using nccl baseline", file=sys.stderr)
+                comm_name = "nccl"
+        if comm is None:
+            comm = NcclComm(rank, world, dev)
+    eng = BiscottiEngine(cfg, device=dev, rank=rank, world=world, comm=comm)
+
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---------------- device-timed arm: resident shards, CUDA events per step --------------------
+    for _ in range(args.warmup):
+        eng.step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    L.bsc_launch_count_reset()
+    evs = []
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()                                   # L2 flush between timed iterations (not timed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.step()
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = int(L.bsc_launch_count())
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    dev_ms = float(t.item())
+    ms_per_step = dev_ms / args.steps
+
+    # ---------------- end-to-end arm: public API, minibatches from pinned host memory ------------
+    P, B, F = eng.P, cfg.batch_size, cfg.spec.n_features
+    hostX = torch.randn(max(1, P), B, F).pin_memory()
+    hosty = torch.randint(0, cfg.spec.n_classes, (max(1, P), B), dtype=torch.int32).pin_memory()
+    # draw host minibatches from the same synthetic distribution as the shards
+    hostX.copy_(eng.data.X[:, :B].cpu()) if P else None
+    hosty.copy_(eng.data.y[:, :B].cpu()) if P else None
+    dX = torch.empty_like(hostX, device=dev)
+    dy = torch.empty_like(hosty, device=dev)
+    res_host = torch.empty(2, dtype=torch.float32).pin_memory()
+    for _ in range(2):
+        dX.copy_(hostX, non_blocking=True)
+        dy.copy_(hosty, non_blocking=True)
+        eng.step((dX, dy))
+    barrier()
+    e2e_t0 = time.perf_counter()
+    for _ in range(args.steps):
+        dX.copy_(hostX, non_blocking=True)               # H2D of this step's inputs
+        dy.copy_(hosty, non_blocking=True)
+        rep = eng.step((dX, dy))
+        res = torch.tensor([rep.test_error or 0.0, rep.attack_rate or 0.0], device=dev)
+        res_host.copy_(res, non_blocking=False)          # D2H of the step's result
+    barrier()
+    e2e_s = time.perf_counter() - e2e_t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(te, op=torch.distributed.ReduceOp.MAX)
+    e2e_s = float(te.item())
+    clocks = sampler.stop()
+
+    # chain equality across ranks (the reference's correctness oracle)
+    chain_ok = True
+    if world > 1:
+        hs = comm.all_gather_bytes(eng.chain.latest_hash()) if hasattr(comm, "all_gather_bytes") else [eng.chain.latest_hash()]
+        chain_ok = all(h == hs[0] for h in hs)
+
+    if rank == 0:
+        value = 1000.0 / ms_per_step
+        last = eng.reports[-1]
+        out = {
+            "metric": "block iterations/sec at 100 peers MNIST",
+            "value": value,
+            "unit": "blocks/s",
+            "n_gpus": world,
+            "steps": args.steps,
+            "warmup": args.warmup,
+            "ms_per_step": ms_per_step,
+            "higher_is_better": True,
+            "scaling": "strong",
+            "vs_baseline": value / BASELINE_BLOCKS_PER_S,
+            "dtype": "fp32 (Krum Gram on tcgen05 as bf16x3 split, fp32 accumulate); int64 shares; BN256 256-bit",
+            "data": "synthetic (Gaussian-blob MNIST-shaped shards, random-init/zero genesis weights)",
+            "impl": "ours",
+            "config": {"model": "mnist softmax d=7850", "peers": cfg.num_nodes, "global_batch": cfg.num_nodes * B,
+                       "seq_len": None, "parallelism": f"peers sharded over {world} GPU(s), comm={comm_name}",
+                       "committees": {"noisers": cfg.num_noisers, "verifiers": cfg.num_verifiers, "miners": cfg.num_miners},
+                       "perc_samples": cfg.perc_samples, "epsilon": cfg.epsilon, "secure_agg": cfg.secure_agg,
+                       "commitments": cfg.commitments, "l2": "256 MiB flush between timed iterations",
+                       "timing": "CUDA events per step, max over ranks"},
+            "clocks": clocks,
+            "e2e": {"value": args.steps / e2e_s, "unit": "blocks/s",
+                    "h2d_bytes_per_step": int(hostX.numel() * 4 + hosty.numel() * 4) * world,
+                    "d2h_bytes_per_step": int(res_host.numel() * 4 + eng.d * 8 + 64 * max(1, last.n_contributors)),
+                    "timing": "wall clock between barrier+synchronize, max over ranks"},
+            "gpu_launches": launches,
+            "wall_ms_per_step": wall * 1e3 / args.steps,
+            "chain_equal_across_ranks": chain_ok,
+            "last_block": {"contributors": last.n_contributors, "accepted": last.n_accepted, "krum_set": last.n_krum,
+                           "test_error": last.test_error, "empty": last.empty},
+        }
+        if args.profile_phases:
+            eng._timing = True
+            eng.step()
+            out["phase_ms"] = eng.reports[-1].phase_ms
+        print(json.dumps(out))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -88,6 +88,24 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_g1_bytes_to_affine", c_i, c_p, c_p, c_ll, c_p)
     sig("bsc_g1_sum_rows", c_i, c_p, c_p, c_i, c_ll, c_p, c_p)
     sig("bsc_g1_sum_cols", c_i, c_p, c_i, c_i, c_p, c_p)
+    sig("bsc_msm_groups_host", None, c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_ll)
+    sig("bsc_g1_normalize_host", None, c_p, c_p, c_ll)
+    sig("bsc_g1_sum_rows_host", None, c_p, c_p, c_i, c_ll, c_p)
+    sig("bsc_g1_sum_cols_host", None, c_p, c_i, c_i, c_p)
+    sig("bsc_g1_fixed_base_mul_host", None, c_p, c_i, c_p, c_p)
+    # VRF / hashing
+    sig("bsc_sha512", None, c_cp, c_sz, c_p)
+    sig("bsc_vrf_pubkey", None, c_cp, c_p)
+    sig("bsc_vrf_secret_scalar", None, c_cp, c_p)
+    sig("bsc_vrf_hash_to_curve", None, c_cp, c_sz, c_p, c_p)
+    sig("bsc_vrf_output_from_gamma", None, c_cp, c_cp, c_sz, c_p)
+    sig("bsc_vrf_prove", None, c_cp, c_cp, c_sz, c_p, c_p)
+    sig("bsc_vrf_verify", c_i, c_cp, c_cp, c_sz, c_cp, c_cp)
+    sig("bsc_ed25519_scalarmult_batch", c_i, c_p, c_p, c_i, c_i, c_p, c_p)
+    sig("bsc_ed25519_scalarmult_batch_host", None, c_p, c_p, c_i, c_i, c_p)
+    sig("bsc_sha256_batch", c_i, c_p, c_i, c_ll, c_i, c_p, c_p)
+    sig("bsc_lottery_roles", c_i, c_cp, c_i, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p)
+    sig("bsc_lottery_noisers", c_i, c_cp, c_i, c_p, c_i, c_i, c_i, c_p)
     # host crypto
     sig("bsc_sha256", None, c_cp, c_sz, c_p)
     sig("bsc_blake2b", None, c_cp, c_sz, c_cp, c_sz, c_p, c_sz)

@@ -1,0 +1,165 @@
+"""Command line: the reference's entrypoints re-expressed for one-process-per-GPU execution.
+
+    python -m biscotti_b200 localtest <numNodes> <dataset> [flags]     # DistSys/localTest.sh parity
+    python -m biscotti_b200 fedsys    <numNodes> <dataset> [flags]     # FedSys/localTest.sh parity
+    python -m biscotti_b200 keygen -n <nodesPerHost> -d <dims> [-h hosts] # keyGeneration parity
+    python -m biscotti_b200 vrf-demo                                    # vrf_main.go parity
+
+Flags keep the reference's names (DistSys/main.go:613-647): -na -nv -nn -sa -np -vp -ep -po -ns -rs -c.
+`localtest` ends like localTest.sh:61-89: each rank dumps its chain (PrintChain) and the dumps are
+compared pairwise; "SUCCESS! Nodes have same blockchain" is printed when they are identical.
+Under torchrun the N simulated peers are sharded over the ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import hashlib
+import sys
+
+
+def _bool(s: str) -> bool:
+    return str(s).lower() in ("1", "true", "t", "yes")
+
+
+def add_protocol_flags(ap: argparse.ArgumentParser):
+    ap.add_argument("-na", type=int, default=3, help="number of aggregators/miners")
+    ap.add_argument("-nv", type=int, default=3, help="number of verifiers")
+    ap.add_argument("-nn", type=int, default=2, help="number of noisers")
+    ap.add_argument("-sa", type=_bool, default=True, help="secure aggregation")
+    ap.add_argument("-np", type=_bool, default=True, help="noising")
+    ap.add_argument("-vp", type=_bool, default=True, help="verification")
+    ap.add_argument("-ep", type=float, default=2.0, help="epsilon")
+    ap.add_argument("-po", type=float, default=0.0, help="fraction of poisoners")
+    ap.add_argument("-ns", type=int, default=None, help="percent of updates to collect (default 70; fedsys 35)")
+    ap.add_argument("-rs", type=_bool, default=False, help="random sampling of updates before Krum")
+    ap.add_argument("-c", type=int, default=0, help="number of colluders")
+    ap.add_argument("--defense", default="KRUM", choices=["KRUM", "RONI"])
+    ap.add_argument("--iterations", type=int, default=100, help="MAX_ITERATIONS")
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--device", default="auto")
+    ap.add_argument("--shard-size", type=int, default=None)
+    ap.add_argument("--fail-prob", type=float, default=-0.005)
+    ap.add_argument("--tau", type=int, default=2, help="SRS trapdoor (2 = reference compat, 0 = random)")
+    ap.add_argument("--comm", default="nccl", choices=["nccl", "fused"])
+    ap.add_argument("--gram", default="auto")
+    ap.add_argument("--print-hash", action="store_true")
+    ap.add_argument("--no-dump", action="store_true")
+    ap.add_argument("--log", action="store_true", help="emit [peer] log lines on stderr")
+    ap.add_argument("--save-chain", default=None)
+
+
+def config_from_args(a, mode: str):
+    from .config import BiscottiConfig
+
+    ns = a.ns if a.ns is not None else (35 if mode == "fedsys" else 70)
+    kw = dict(num_nodes=a.num_nodes, dataset=a.dataset, num_miners=a.na, num_verifiers=a.nv, num_noisers=a.nn,
+              secure_agg=a.sa, noising=a.np, verification=a.vp, epsilon=a.ep, poison_fraction=a.po, perc_samples=ns,
+              random_sampling=a.rs, colluders=a.c, defense=a.defense, max_iterations=a.iterations, seed=a.seed,
+              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm)
+    if a.shard_size:
+        kw["shard_size"] = a.shard_size
+    return BiscottiConfig(**kw)
+
+
+def run_localtest(a, mode: str) -> int:
+    import torch
+
+    from .parallel.comm import init_distributed, NcclComm
+    from .protocol.engine import BiscottiEngine
+
+    dev_type = a.device
+    if dev_type == "auto":
+        dev_type = "cuda" if torch.cuda.is_available() else "cpu"
+    rank, local, world = init_distributed("cuda" if dev_type.startswith("cuda") else "cpu")
+    device = torch.device("cuda", local) if dev_type.startswith("cuda") else torch.device("cpu")
+    cfg = config_from_args(a, mode)
+    comm = None
+    if world > 1:
+        if cfg.comm_impl == "fused" and device.type == "cuda":
+            from .parallel.fused import FusedComm
+
+            comm = FusedComm(rank, world, device, cfg)
+        else:
+            comm = NcclComm(rank, world, device)
+    eng = BiscottiEngine(cfg, device=device, rank=rank, world=world, comm=comm, log_stream=sys.stderr if a.log else None)
+    eng.run()
+    dump = eng.print_chain()
+    ok = True
+    if world > 1:
+        digests = comm.all_gather_bytes(hashlib.sha256(dump.encode()).digest())
+        ok = all(d == digests[0] for d in digests)
+    if rank == 0:
+        if not a.no_dump:
+            sys.stdout.write(dump)
+        if a.print_hash:
+            print("chain-hash", hashlib.sha256(dump.encode()).hexdigest())
+        if a.save_chain:
+            eng.chain.save(a.save_chain)
+        last = eng.reports[-1]
+        print(f"blocks={len(eng.chain)} final_test_error={last.test_error} attack_rate={last.attack_rate}")
+        # localTest.sh:70-89
+        print("SUCCESS! Nodes have same blockchain" if ok else "FAILURE! Nodes have different blockchains")
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0 if ok else 1
+
+
+def run_keygen(a) -> int:
+    from .crypto.primitives import write_bootstrap_files
+
+    hosts = None
+    if a.hosts:
+        with open(a.hosts) as f:
+            hosts = [l.strip() for l in f if l.strip()]
+    total = a.n * (len(hosts) if hosts else 1)
+    write_bootstrap_files(a.out, total, a.d, hosts, seed=a.seed, tau=a.tau, nodes_per_host=a.n)
+    print(f"wrote peersfile.txt commitKey.json pKeyG1.json for {total} peers, d={a.d} into {a.out}")
+    return 0
+
+
+def run_vrf_demo(a) -> int:
+    """vrf_main.go:75-153: prove / verify and a stake lottery over 100 nodes."""
+    from .crypto import primitives as cp
+
+    key = cp.VRFKey(hashlib.sha256(b"vrf-demo").digest())
+    msg = hashlib.sha256(b"block-hash").digest()
+    vrf, proof = key.prove(msg)
+    print("VRF output:", vrf.hex())
+    print("Proof verifies:", cp.vrf_verify(key.public, msg, vrf, proof))
+    v, m = cp.lottery_roles(msg, [10] * 100, 3, 3)
+    nz = cp.lottery_noisers(vrf, [10] * 100, 0, 2)
+    print("verifiers", v, "miners", m, "noisers", nz)
+    return 0
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="biscotti_b200", add_help=True)
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    for name in ("localtest", "fedsys"):
+        sp = sub.add_parser(name)
+        sp.add_argument("num_nodes", type=int)
+        sp.add_argument("dataset")
+        add_protocol_flags(sp)
+    kg = sub.add_parser("keygen", add_help=False)
+    kg.add_argument("-n", type=int, default=10)
+    kg.add_argument("-d", type=int, default=25)
+    kg.add_argument("-h", dest="hosts", default=None)
+    kg.add_argument("--out", default="keys")
+    kg.add_argument("--seed", type=int, default=1)
+    kg.add_argument("--tau", type=int, default=2)
+    sub.add_parser("vrf-demo")
+    a = ap.parse_args(argv)
+    if a.cmd == "localtest":
+        return run_localtest(a, "biscotti")
+    if a.cmd == "fedsys":
+        return run_localtest(a, "fedsys")
+    if a.cmd == "keygen":
+        return run_keygen(a)
+    return run_vrf_demo(a)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

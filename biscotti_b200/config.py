@@ -1,0 +1,143 @@
+"""Run configuration: every flag and compile-time constant of the reference peer, in one place.
+
+Flag parity: DistSys/main.go:613-647 (``-t -i -d -f -a -pa -p -c -na -nv -nn -sa -np -vp -ep -po -ns
+-rs``), constants DistSys/main.go:28-60 and DistSys/honest.go:44-57, dataset table
+ML/Pytorch/datasets.py:18-52 and DistSys/localTest.sh:16-20.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field, asdict
+
+BASE_PORT = 8000           # main.go:29 (kept for the peers-file format only; no sockets are opened)
+DEFAULT_STAKE = 10         # main.go:39
+STAKE_UNIT = 5             # honest.go:46
+VERIFIER_PRIME, MINER_PRIME, NOISER_PRIME = 2, 3, 5   # main.go:41-43
+PRECISION = 4              # main.go:45
+POLY_SIZE = 10             # main.go:46
+MAX_ITERATIONS = 100       # main.go:48
+FAIL_PROB = -0.005         # main.go:55 (fault injection off)
+CONV_THRESHOLD = 0.0       # honest.go:51
+NOISE_TABLE_ITERS = 100    # client_obj.py:17, logistic_model.py:21
+# timeouts in seconds, scaled by N/100 (main.go:31-36, 786-821); here they order simulated events
+TIMEOUTS = dict(roni=120, krum=60, krum_r=60, update=90, block=300, peer=5)
+
+
+@dataclass(frozen=True)
+class DatasetSpec:
+    name: str
+    model: str          # softmax | logistic | mnist_cnn | cifar_cnn | lfw_cnn | svm
+    n_features: int     # flattened input size
+    n_classes: int
+    n_params: int
+    image_shape: tuple = ()
+
+
+# ML/Pytorch/datasets.py + model files (param counts: SURVEY §2.5)
+DATASETS = {
+    "mnist": DatasetSpec("mnist", "softmax", 784, 10, 7850, (1, 28, 28)),
+    "creditcard": DatasetSpec("creditcard", "logistic", 25, 2, 25),
+    "cifar": DatasetSpec("cifar", "cifar_cnn", 3072, 10, 259770, (3, 32, 32)),
+    "mnist_cnn": DatasetSpec("mnist_cnn", "mnist_cnn", 784, 10, 164266, (1, 28, 28)),
+    "lfw": DatasetSpec("lfw", "lfw_cnn", 8742, 2, 18254, (3, 62, 47)),
+    "lfw_softmax": DatasetSpec("lfw_softmax", "softmax", 8742, 2, 17486, (3, 62, 47)),
+}
+
+
+@dataclass
+class BiscottiConfig:
+    # ---- reference flags --------------------------------------------------------------------
+    num_nodes: int = 10               # -t
+    dataset: str = "creditcard"       # -d
+    num_miners: int = 3               # -na
+    num_verifiers: int = 3            # -nv
+    num_noisers: int = 2              # -nn
+    secure_agg: bool = True           # -sa
+    noising: bool = True              # -np
+    verification: bool = True         # -vp
+    epsilon: float = 2.0              # -ep
+    poison_fraction: float = 0.0      # -po
+    perc_samples: int = 70            # -ns (percent of peers whose updates Krum waits for)
+    random_sampling: bool = False     # -rs
+    colluders: int = 0                # -c
+    defense: str = "KRUM"             # POISON_DEFENSE: KRUM | RONI
+    # ---- constants exposed as knobs -----------------------------------------------------------
+    max_iterations: int = MAX_ITERATIONS
+    batch_size: int = 10              # honest.go:47
+    precision: int = PRECISION
+    fail_prob: float = FAIL_PROB
+    krum_adversary_frac: float = 0.5  # main.go:780-783
+    clip_norm: float = 100.0          # client.py:53
+    dp_delta: float = 1e-5            # client_obj.py:61
+    logistic_alpha: float = 1e-2      # logistic_model.py
+    logistic_lambda: float = 1e-2
+    dp_in_model: bool = False         # main.go:155 DP_IN_MODEL
+    roni_threshold: float = 0.02      # honest.go:598-629
+    # ---- framework knobs (no reference counterpart) -------------------------------------------
+    mode: str = "biscotti"            # biscotti | fedsys
+    seed: int = 1
+    srs_tau: int = 2                  # publicKey.go:36 compat; 0 => random tau
+    commitments: bool = True          # compute KZG commitments + witnesses (reference always does)
+    share_trigger: str = "half"       # "half": miners act on NUM_SAMPLES/2 shares (main.go:360); "all"
+    deterministic_time: bool = True   # inject block timestamps so chains are reproducible
+    shard_size: int = 600             # rows per peer shard (mnist 60000/100)
+    test_size: int = 2000
+    eval_every: int = 1               # reference evaluates every block (honest.go:141-162)
+    gram_impl: str = "auto"           # auto | tcgen05 | simt
+    comm_impl: str = "fused"          # fused (in-kernel P2P) | nccl (baseline)
+    extra: dict = field(default_factory=dict)
+
+    # ---- derived quantities (main.go:672-684, 825) ---------------------------------------------
+    @property
+    def spec(self) -> DatasetSpec:
+        return DATASETS[self.dataset]
+
+    @property
+    def dim(self) -> int:
+        return self.spec.n_params
+
+    @property
+    def num_samples(self) -> int:
+        n = int(self.num_nodes * self.perc_samples / 100.0)
+        cap = self.num_nodes - self.num_verifiers - self.num_miners
+        return max(1, min(n, cap))
+
+    @property
+    def krum_thresh(self) -> int:
+        if self.random_sampling:
+            return max(1, self.num_nodes - self.num_verifiers - self.num_miners)
+        return self.num_samples
+
+    @property
+    def total_shares(self) -> int:
+        return int(math.ceil(2.0 * POLY_SIZE / self.num_miners)) * self.num_miners
+
+    @property
+    def shares_per_miner(self) -> int:
+        return self.total_shares // self.num_miners
+
+    @property
+    def nchunk(self) -> int:
+        return (self.dim + POLY_SIZE - 1) // POLY_SIZE
+
+    @property
+    def noise_sigma(self) -> float:
+        if self.epsilon <= 0:
+            return 0.0
+        if self.spec.model == "logistic":
+            return math.sqrt(2.0 * math.log(1.25)) / self.epsilon           # logistic_model.py:81
+        return math.sqrt(2.0 * math.log(1.25 / self.dp_delta)) / self.epsilon  # client_obj.py:61-63
+
+    @property
+    def noise_scale(self) -> float:
+        """getNoise scale incl. the sum over `batch` presampled normals (std sqrt(batch)*sigma)."""
+        s = self.noise_sigma * math.sqrt(self.batch_size)
+        if self.spec.model == "logistic":
+            return -self.logistic_alpha / self.batch_size * s                # logistic_model.py:108-109
+        return -1.0 / self.batch_size * s                                     # client_obj.py:97-98
+
+    def timeout(self, name: str) -> float:
+        return TIMEOUTS[name] * max(1.0, self.num_nodes / 100.0)
+
+    def to_dict(self) -> dict:
+        return asdict(self)

@@ -181,4 +181,50 @@ int bsc_g1_sum_cols(const void* pts_affine, int P, int G, void* out_jac, void* s
   return finish_launch("g1_sum_cols");
 }
 
+
+// ---- host mirrors (CPU plumbing path + oracles; same templates as the kernels) --------------------
+void bsc_msm_groups_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx,
+                         const int* og, int G, int T, const void* bases_affine, void* out_jac, long long ostride_p) {
+  const G1Affine* bases = (const G1Affine*)bases_affine;
+  G1Jac* out = (G1Jac*)out_jac;
+  for (int g = 0; g < G; g++)
+    for (int p = 0; p < P; p++) {
+      const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
+      uint64_t maxmag = 0;
+      for (int t = 0; t < T; t++) maxmag |= row[t] < 0 ? (uint64_t)0 - (uint64_t)row[t] : (uint64_t)row[t];
+      int nbits = 0;
+      while (nbits < 64 && (maxmag >> nbits)) nbits++;
+      out[(size_t)p * ostride_p + (og ? og[g] : g)] =
+          g1_straus_i64<MSM_TMAX>(bases + bidx[g], (const int64_t*)row, T, nbits);
+    }
+}
+void bsc_g1_normalize_host(const void* in_jac, void* out_affine, long long N) {
+  const G1Jac* in = (const G1Jac*)in_jac;
+  G1Affine* out = (G1Affine*)out_affine;
+  for (long long i = 0; i < N; i++) out[i] = g1j_to_affine(in[i]);
+}
+void bsc_g1_sum_rows_host(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac) {
+  const G1Affine* pts = (const G1Affine*)pts_affine;
+  G1Jac* out = (G1Jac*)out_jac;
+  for (long long g = 0; g < G; g++) {
+    G1Jac acc = g1j_inf();
+    for (int q = 0; q < nsel; q++) acc = g1j_add_affine(acc, pts[(size_t)sel[q] * G + g]);
+    out[g] = acc;
+  }
+}
+void bsc_g1_sum_cols_host(const void* pts_affine, int P, int G, void* out_jac) {
+  const G1Affine* pts = (const G1Affine*)pts_affine;
+  G1Jac* out = (G1Jac*)out_jac;
+  for (int p = 0; p < P; p++) {
+    G1Jac acc = g1j_inf();
+    for (int g = 0; g < G; g++) acc = g1j_add_affine(acc, pts[(size_t)p * G + g]);
+    out[p] = acc;
+  }
+}
+void bsc_g1_fixed_base_mul_host(const void* scalars_u256, int N, const void* base_affine, void* out_jac) {
+  const U256* k = (const U256*)scalars_u256;
+  G1Jac* out = (G1Jac*)out_jac;
+  for (int i = 0; i < N; i++) out[i] = g1_mul_u256(*(const G1Affine*)base_affine, k[i]);
+}
+
 }  // extern "C"

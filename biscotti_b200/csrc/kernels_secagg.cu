@@ -67,7 +67,7 @@ __global__ void share_sum_kernel(const float* __restrict__ U, const int* __restr
 //   bad    : int[2] -> {inexact divisions, shares inconsistent with the recovered polynomial}
 __global__ void reconstruct_step_kernel(const long long* __restrict__ Ysum, const int* __restrict__ xs,
                                         const unsigned char* __restrict__ avail, int S, int c0, int nc, int d,
-                                        double inv_scale, double* __restrict__ w64, float* __restrict__ w32,
+                                        double scale, double* __restrict__ w64, float* __restrict__ w32,
                                         double* __restrict__ dsum, int* __restrict__ bad) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nc) return;
@@ -92,7 +92,7 @@ __global__ void reconstruct_step_kernel(const long long* __restrict__ Ysum, cons
   for (int j = 0; j < POLY_SIZE; j++) {
     const int k = c * POLY_SIZE + j;
     if (k < d) {
-      const double delta = (double)coef[j] * inv_scale;
+      const double delta = (double)coef[j] / scale;  // updateIntToFloat, kyber.go:745-757
       const double nw = w64[k] + delta;
       w64[k] = nw;
       if (w32) w32[k] = (float)nw;
@@ -143,8 +143,8 @@ int bsc_share_sum(const float* U, const int* sel, int nsel, int d, int ldu, int 
 }
 
 int bsc_reconstruct_step(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d,
-                         double inv_scale, double* w64, float* w32, double* dsum, int* bad, void* stream) {
-  reconstruct_step_kernel<<<(nc + 127) / 128, 128, 0, (cudaStream_t)stream>>>(Ysum, xs, avail, S, c0, nc, d, inv_scale,
+                         double scale, double* w64, float* w32, double* dsum, int* bad, void* stream) {
+  reconstruct_step_kernel<<<(nc + 127) / 128, 128, 0, (cudaStream_t)stream>>>(Ysum, xs, avail, S, c0, nc, d, scale,
                                                                                w64, w32, dsum, bad);
   return finish_launch("reconstruct_step");
 }

@@ -1,0 +1,583 @@
+// Host ledger runtime: blocks, chain, canonical serialisation, hashing, PrintChain-style dump,
+// longest-chain adoption / fork repair helpers, and the stake lottery.
+//
+// Behavioural parity with the reference:
+//   Block / BlockData / Update fields        DistSys/block.go:14-20, blockData.go:10-14, update.go:13-22
+//   Hash = SHA256(prev || decimal(ts) || enc) DistSys/block.go:23-28  (enc: see encode_block_data —
+//                                             a documented canonical encoding instead of Go gob)
+//   empty blocks carry Timestamp 0            DistSys/block.go:32-38
+//   genesis = iteration -1, zero weights      DistSys/block.go:46-53
+//   getBlock(it) = Blocks[it+1] + check       DistSys/blockchain.go:77-96
+//   PrintChain dump                           DistSys/blockchain.go:43-53, blockData.go:24-27, update.go:24-37
+//   better-block replacement rule             DistSys/honest.go:631-653
+//   lottery                                   DistSys/vrf.go:54-182 (bit-exact: it is the consensus rule)
+#include <stdint.h>
+#include <string.h>
+#include <stdio.h>
+#include <math.h>
+#include <time.h>
+#include <string>
+#include <vector>
+#include <map>
+#include <charconv>
+#include "sha256.cuh"
+
+using namespace bsc;
+
+namespace {
+
+struct Update {
+  int32_t source = 0;
+  int32_t iteration = 0;
+  uint8_t accepted = 0;
+  std::string commitment;               // 64-byte G1 wire bytes (may be empty)
+  std::vector<double> delta;            // only in the plain (-sa=false) path
+  std::vector<double> noise;            // optional
+  std::vector<double> noised;           // optional
+  std::vector<std::string> signatures;  // Schnorr c||r blobs
+};
+
+struct Block {
+  int64_t timestamp = 0;
+  int64_t iteration = -1;
+  std::vector<double> w;
+  std::vector<Update> updates;
+  std::string prev_hash;
+  std::string hash;
+  std::map<int, int> stake;
+};
+
+struct Chain {
+  std::vector<Block> blocks;
+};
+
+void put_u32(std::string& o, uint32_t v) {
+  for (int i = 0; i < 4; i++) o.push_back((char)(v >> (8 * i)));
+}
+void put_u64(std::string& o, uint64_t v) {
+  for (int i = 0; i < 8; i++) o.push_back((char)(v >> (8 * i)));
+}
+void put_f64s(std::string& o, const std::vector<double>& v) {
+  put_u64(o, v.size());
+  const size_t off = o.size();
+  o.resize(off + 8 * v.size());
+  memcpy(&o[off], v.data(), 8 * v.size());  // little-endian hosts only (x86-64 / aarch64)
+}
+void put_bytes(std::string& o, const std::string& b) {
+  put_u32(o, (uint32_t)b.size());
+  o += b;
+}
+
+// Canonical BlockData encoding ("BSCD1"): the hash preimage component that stands in for
+// gob(BlockData) (blockData.go:31-41).  Field order follows the Go struct order.
+std::string encode_block_data(const Block& b) {
+  std::string o = "BSCD1";
+  put_u64(o, (uint64_t)b.iteration);
+  put_f64s(o, b.w);
+  put_u32(o, (uint32_t)b.updates.size());
+  for (const Update& u : b.updates) {
+    put_u32(o, (uint32_t)u.source);
+    put_u32(o, (uint32_t)u.iteration);
+    put_f64s(o, u.delta);
+    put_bytes(o, u.commitment);
+    put_f64s(o, u.noise);
+    put_f64s(o, u.noised);
+    o.push_back((char)u.accepted);
+    put_u32(o, (uint32_t)u.signatures.size());
+    for (const std::string& s : u.signatures) put_bytes(o, s);
+  }
+  return o;
+}
+
+void set_hash(Block& b) {
+  std::string pre = b.prev_hash;
+  pre += std::to_string((long long)b.timestamp);
+  pre += encode_block_data(b);
+  uint8_t h[32];
+  sha256_oneshot((const uint8_t*)pre.data(), pre.size(), h);
+  b.hash.assign((const char*)h, 32);
+}
+
+// full block wire encoding (chain transfer / checkpoint)
+std::string encode_block(const Block& b) {
+  std::string o = "BSCB1";
+  put_u64(o, (uint64_t)b.timestamp);
+  put_bytes(o, b.prev_hash);
+  put_bytes(o, b.hash);
+  put_u32(o, (uint32_t)b.stake.size());
+  for (auto& kv : b.stake) {
+    put_u32(o, (uint32_t)kv.first);
+    put_u32(o, (uint32_t)kv.second);
+  }
+  put_bytes(o, encode_block_data(b));
+  return o;
+}
+
+struct Reader {
+  const uint8_t* p;
+  size_t n, off = 0;
+  bool ok = true;
+  bool need(size_t k) {
+    if (off + k > n) ok = false;
+    return ok;
+  }
+  uint32_t u32() {
+    if (!need(4)) return 0;
+    uint32_t v = 0;
+    for (int i = 0; i < 4; i++) v |= (uint32_t)p[off + i] << (8 * i);
+    off += 4;
+    return v;
+  }
+  uint64_t u64() {
+    if (!need(8)) return 0;
+    uint64_t v = 0;
+    for (int i = 0; i < 8; i++) v |= (uint64_t)p[off + i] << (8 * i);
+    off += 8;
+    return v;
+  }
+  std::string bytes() {
+    uint32_t k = u32();
+    if (!need(k)) return std::string();
+    std::string s((const char*)p + off, k);
+    off += k;
+    return s;
+  }
+  std::vector<double> f64s() {
+    uint64_t k = u64();
+    std::vector<double> v;
+    if (k > (n - off) / 8) {
+      ok = false;
+      return v;
+    }
+    v.resize(k);
+    memcpy(v.data(), p + off, 8 * k);
+    off += 8 * k;
+    return v;
+  }
+  bool tag(const char* t) {
+    size_t k = strlen(t);
+    if (!need(k) || memcmp(p + off, t, k) != 0) {
+      ok = false;
+      return false;
+    }
+    off += k;
+    return true;
+  }
+};
+
+bool decode_block_data(Reader& r, Block& b) {
+  if (!r.tag("BSCD1")) return false;
+  b.iteration = (int64_t)r.u64();
+  b.w = r.f64s();
+  uint32_t nu = r.u32();
+  for (uint32_t i = 0; i < nu && r.ok; i++) {
+    Update u;
+    u.source = (int32_t)r.u32();
+    u.iteration = (int32_t)r.u32();
+    u.delta = r.f64s();
+    u.commitment = r.bytes();
+    u.noise = r.f64s();
+    u.noised = r.f64s();
+    if (r.need(1)) u.accepted = r.p[r.off++];
+    uint32_t ns = r.u32();
+    for (uint32_t j = 0; j < ns && r.ok; j++) u.signatures.push_back(r.bytes());
+    b.updates.push_back(std::move(u));
+  }
+  return r.ok;
+}
+
+bool decode_block(Reader& r, Block& b) {
+  if (!r.tag("BSCB1")) return false;
+  b.timestamp = (int64_t)r.u64();
+  b.prev_hash = r.bytes();
+  b.hash = r.bytes();
+  uint32_t ns = r.u32();
+  for (uint32_t i = 0; i < ns && r.ok; i++) {
+    int k = (int)r.u32();
+    int v = (int)r.u32();
+    b.stake[k] = v;
+  }
+  std::string bd = r.bytes();
+  Reader r2{(const uint8_t*)bd.data(), bd.size()};
+  return r.ok && decode_block_data(r2, b);
+}
+
+// Go fmt %v for float64 = strconv 'g' with the shortest round-trip digits; the %e form is used when
+// exp < -4 || exp >= 6 (shortest mode fixes the decision precision at 6), e.g. 1e+06, 1.5e-05.
+std::string go_float(double v) {
+  if (v != v) return "NaN";
+  if (isinf(v)) return v > 0 ? "+Inf" : "-Inf";
+  if (v == 0) return signbit(v) ? "-0" : "0";
+  char buf[64];
+  auto res = std::to_chars(buf, buf + sizeof(buf), v, std::chars_format::scientific);
+  std::string s(buf, res.ptr);  // d.ddddde[+-]XX shortest
+  std::string sign;
+  if (s[0] == '-') {
+    sign = "-";
+    s = s.substr(1);
+  }
+  size_t epos = s.find('e');
+  std::string mant = s.substr(0, epos);
+  int exp = atoi(s.c_str() + epos + 1);
+  std::string digits;
+  for (char c : mant)
+    if (c != '.') digits.push_back(c);
+  if (exp < -4 || exp >= 6) {
+    std::string o = sign + digits.substr(0, 1);
+    if (digits.size() > 1) o += "." + digits.substr(1);
+    char eb[16];
+    snprintf(eb, sizeof(eb), "e%c%02d", exp < 0 ? '-' : '+', abs(exp));
+    return o + eb;
+  }
+  std::string o = sign;
+  if (exp < 0) {
+    o += "0.";
+    o.append((size_t)(-exp - 1), '0');
+    o += digits;
+  } else if ((int)digits.size() <= exp + 1) {
+    o += digits;
+    o.append((size_t)(exp + 1 - (int)digits.size()), '0');
+  } else {
+    o += digits.substr(0, (size_t)exp + 1) + "." + digits.substr((size_t)exp + 1);
+  }
+  return o;
+}
+
+std::string hex(const std::string& b) {
+  static const char* d = "0123456789abcdef";
+  std::string o;
+  for (unsigned char c : b) {
+    o.push_back(d[c >> 4]);
+    o.push_back(d[c & 15]);
+  }
+  return o;
+}
+
+std::string array_to_string(const std::vector<double>& a) {
+  std::string o = "[";
+  for (size_t i = 0; i < a.size(); i++) {
+    if (i) o += ",";
+    o += go_float(a[i]);
+  }
+  return o + "]";
+}
+
+// bn256.G1 point String(): "bn256.G1:(x, y)" with 64-hex-digit coordinates; the point at infinity
+// prints as (0, 1) after MakeAffine (curve.go:202-224, gfp.go:19-21).
+std::string point_string(const std::string& c) {
+  std::string x(32, '\0'), y(32, '\0');
+  bool inf = true;
+  if (c.size() == 64) {
+    for (unsigned char ch : c) inf = inf && ch == 0;
+    if (!inf) {
+      x = c.substr(0, 32);
+      y = c.substr(32, 32);
+    }
+  }
+  if (inf) y[31] = 1;
+  return "bn256.G1:(" + hex(x) + ", " + hex(y) + ")";
+}
+
+std::string dump_chain(const Chain& c) {
+  std::string o;
+  for (const Block& b : c.blocks) {
+    o += "Prev. hash: " + hex(b.prev_hash) + "\n";
+    o += "Data: Iteration: " + std::to_string((long long)b.iteration) + ", GlobalW: " + array_to_string(b.w) +
+         ", deltas: [";
+    for (size_t i = 0; i < b.updates.size(); i++) {
+      const Update& u = b.updates[i];
+      o += "{Iteration:" + std::to_string(u.iteration) + ", Commitment:" + point_string(u.commitment) +
+           ", Deltas:" + array_to_string(u.delta) + "}";
+      if (i + 1 != b.updates.size()) o += " ,";
+    }
+    o += "]\n";
+    o += "Hash: " + hex(b.hash) + "\n\n";
+  }
+  return o;
+}
+
+Block genesis(int d) {
+  Block b;
+  b.timestamp = 0;
+  b.iteration = -1;
+  b.w.assign((size_t)d, 0.0);
+  set_hash(b);
+  return b;
+}
+
+thread_local std::string g_scratch;
+
+}  // namespace
+
+extern "C" {
+
+void* bsc_chain_new(int d) {
+  Chain* c = new Chain();
+  c->blocks.push_back(genesis(d));
+  return c;
+}
+void bsc_chain_free(void* c) { delete (Chain*)c; }
+int bsc_chain_len(void* c) { return (int)((Chain*)c)->blocks.size(); }
+int bsc_chain_dim(void* c) { return (int)((Chain*)c)->blocks.back().w.size(); }
+long long bsc_chain_latest_iteration(void* c) { return ((Chain*)c)->blocks.back().iteration; }
+
+// ---- block builder -------------------------------------------------------------------------------
+void* bsc_block_new(long long iteration, const double* w, int d) {
+  Block* b = new Block();
+  b->iteration = iteration;
+  b->w.assign(w, w + d);
+  return b;
+}
+void bsc_block_free(void* b) { delete (Block*)b; }
+void bsc_block_add_update(void* bp, int source, int iteration, int accepted, const uint8_t* commitment, int clen,
+                          const double* delta, int dlen, const double* noise, int nlen, const double* noised,
+                          int ndlen, const uint8_t* sigs, int nsigs, int siglen) {
+  Block* b = (Block*)bp;
+  Update u;
+  u.source = source;
+  u.iteration = iteration;
+  u.accepted = (uint8_t)accepted;
+  if (commitment && clen > 0) u.commitment.assign((const char*)commitment, (size_t)clen);
+  if (delta && dlen > 0) u.delta.assign(delta, delta + dlen);
+  if (noise && nlen > 0) u.noise.assign(noise, noise + nlen);
+  if (noised && ndlen > 0) u.noised.assign(noised, noised + ndlen);
+  for (int i = 0; i < nsigs; i++) u.signatures.emplace_back((const char*)sigs + (size_t)i * siglen, (size_t)siglen);
+  b->updates.push_back(std::move(u));
+}
+void bsc_block_set_stake(void* bp, const int* ids, const int* vals, int n) {
+  Block* b = (Block*)bp;
+  b->stake.clear();
+  for (int i = 0; i < n; i++) b->stake[ids[i]] = vals[i];
+}
+// Seal against the chain tip and append (NewBlock + AddBlock, block.go:30-44, blockchain.go:12-16).
+// timestamp < 0 => reference rule: 0 for an empty block, wall-clock seconds otherwise.
+// Consumes the builder.  Returns the new chain length.
+int bsc_chain_append(void* cp, void* bp, long long timestamp) {
+  Chain* c = (Chain*)cp;
+  Block* b = (Block*)bp;
+  if (timestamp < 0) timestamp = b->updates.empty() ? 0 : (long long)time(nullptr);
+  b->timestamp = timestamp;
+  b->prev_hash = c->blocks.back().hash;
+  set_hash(*b);
+  c->blocks.push_back(std::move(*b));
+  delete b;
+  return (int)c->blocks.size();
+}
+
+// getBlock(it) = Blocks[it+1] with the consistency check (blockchain.go:77-96): index or -1/-2
+int bsc_chain_block_index(void* cp, long long iteration) {
+  Chain* c = (Chain*)cp;
+  if ((long long)c->blocks.size() >= iteration + 2 && iteration + 1 >= 0) {
+    if (c->blocks[(size_t)(iteration + 1)].iteration != iteration) return -2;
+    return (int)(iteration + 1);
+  }
+  return -1;
+}
+void bsc_chain_hash(void* cp, int index, uint8_t out[32]) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  memcpy(out, b.hash.data(), 32);
+}
+void bsc_chain_prev_hash(void* cp, int index, uint8_t out[32], int* len) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  *len = (int)b.prev_hash.size();
+  memcpy(out, b.prev_hash.data(), b.prev_hash.size());
+}
+void bsc_chain_weights(void* cp, int index, double* out) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  memcpy(out, b.w.data(), 8 * b.w.size());
+}
+long long bsc_chain_block_info(void* cp, int index, long long* iteration, int* nupdates, int* nstake) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  *iteration = b.iteration;
+  *nupdates = (int)b.updates.size();
+  *nstake = (int)b.stake.size();
+  return b.timestamp;
+}
+void bsc_chain_block_stake(void* cp, int index, int* ids, int* vals) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  int i = 0;
+  for (auto& kv : b.stake) {
+    ids[i] = kv.first;
+    vals[i] = kv.second;
+    i++;
+  }
+}
+int bsc_chain_update_info(void* cp, int index, int u, int* source, int* accepted, uint8_t commitment[64], int* nsigs) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  if (u < 0 || u >= (int)b.updates.size()) return -1;
+  const Update& up = b.updates[(size_t)u];
+  *source = up.source;
+  *accepted = up.accepted;
+  *nsigs = (int)up.signatures.size();
+  memset(commitment, 0, 64);
+  memcpy(commitment, up.commitment.data(), up.commitment.size() < 64 ? up.commitment.size() : 64);
+  return (int)up.delta.size();
+}
+
+// recompute every hash and the prev-hash links; 1 = consistent
+int bsc_chain_verify(void* cp) {
+  Chain* c = (Chain*)cp;
+  for (size_t i = 0; i < c->blocks.size(); i++) {
+    Block t = c->blocks[i];
+    set_hash(t);
+    if (t.hash != c->blocks[i].hash) return 0;
+    if (i > 0 && c->blocks[i].prev_hash != c->blocks[i - 1].hash) return 0;
+  }
+  return 1;
+}
+
+// serialisation (RegisterPeer chain transfer main.go:420-436; doubles as checkpoint format)
+size_t bsc_chain_serialize(void* cp, uint8_t* out, size_t cap) {
+  Chain* c = (Chain*)cp;
+  std::string o = "BSCC1";
+  put_u32(o, (uint32_t)c->blocks.size());
+  for (const Block& b : c->blocks) put_bytes(o, encode_block(b));
+  if (out && cap >= o.size()) memcpy(out, o.data(), o.size());
+  return o.size();
+}
+void* bsc_chain_deserialize(const uint8_t* in, size_t n) {
+  Reader r{in, n};
+  if (!r.tag("BSCC1")) return nullptr;
+  uint32_t nb = r.u32();
+  Chain* c = new Chain();
+  for (uint32_t i = 0; i < nb && r.ok; i++) {
+    std::string bb = r.bytes();
+    Reader rb{(const uint8_t*)bb.data(), bb.size()};
+    Block b;
+    if (!decode_block(rb, b)) r.ok = false;
+    c->blocks.push_back(std::move(b));
+  }
+  if (!r.ok || c->blocks.empty()) {
+    delete c;
+    return nullptr;
+  }
+  return c;
+}
+// single-block wire form (RegisterBlock gossip, main.go:398-409)
+size_t bsc_chain_block_serialize(void* cp, int index, uint8_t* out, size_t cap) {
+  Chain* c = (Chain*)cp;
+  const Block& b = index < 0 ? c->blocks.back() : c->blocks[(size_t)index];
+  std::string o = encode_block(b);
+  if (out && cap >= o.size()) memcpy(out, o.data(), o.size());
+  return o.size();
+}
+// Append or replace from a received block.  Return codes:
+//   1 appended, 2 replaced an empty block by a non-empty one (honest.go:631-653), 0 duplicate/ignored,
+//  -1 malformed, -2 does not link to our chain, -3 hash mismatch
+int bsc_chain_accept_block(void* cp, const uint8_t* in, size_t n) {
+  Chain* c = (Chain*)cp;
+  Reader r{in, n};
+  Block b;
+  if (!decode_block(r, b)) return -1;
+  Block t = b;
+  set_hash(t);
+  if (t.hash != b.hash) return -3;
+  const long long idx = b.iteration + 1;
+  if (idx == (long long)c->blocks.size()) {
+    if (b.prev_hash != c->blocks.back().hash) return -2;
+    c->blocks.push_back(std::move(b));
+    return 1;
+  }
+  if (idx > 0 && idx < (long long)c->blocks.size()) {
+    Block& mine = c->blocks[(size_t)idx];
+    if (mine.hash == b.hash) return 0;
+    const bool better = b.prev_hash == mine.prev_hash && mine.updates.empty() && !b.updates.empty();
+    if (better && idx + 1 == (long long)c->blocks.size()) {
+      mine = std::move(b);
+      return 2;
+    }
+    return 0;
+  }
+  return -2;
+}
+
+const char* bsc_chain_dump(void* cp, size_t* len) {
+  g_scratch = dump_chain(*(Chain*)cp);
+  *len = g_scratch.size();
+  return g_scratch.data();
+}
+int bsc_chain_equal(void* a, void* b) {
+  Chain* x = (Chain*)a;
+  Chain* y = (Chain*)b;
+  if (x->blocks.size() != y->blocks.size()) return 0;
+  for (size_t i = 0; i < x->blocks.size(); i++)
+    if (x->blocks[i].hash != y->blocks[i].hash) return 0;
+  return 1;
+}
+const char* bsc_go_float(double v) {
+  g_scratch = go_float(v);
+  return g_scratch.c_str();
+}
+
+// ---- stake lottery (DistSys/vrf.go:54-182) ---------------------------------------------------------
+// tickets: node id repeated stake[id] times, ids 0..n-1.  Draw = big-endian 2 bytes at cursor i mod
+// #tickets, cursor advances by one byte, SHA-256 re-hash of the current buffer when i >= len-1,
+// duplicates (and `exclude`) skipped.  `cursor_io`/`buf` carry the state from the verifier draw into
+// the miner draw exactly like getVRFRoles does.
+static int lottery_draw(std::vector<uint8_t>& buf, size_t& i, const std::vector<int>& tickets, int want, int exclude,
+                        int* out) {
+  std::vector<char> seen;
+  int got = 0;
+  int maxid = 0;
+  for (int t : tickets) maxid = t > maxid ? t : maxid;
+  seen.assign((size_t)maxid + 1, 0);
+  // the reference loops forever if `want` exceeds the distinct eligible ids; bound it instead
+  int distinct = 0;
+  {
+    std::vector<char> has((size_t)maxid + 1, 0);
+    for (int t : tickets)
+      if (!has[(size_t)t] && t != exclude) {
+        has[(size_t)t] = 1;
+        distinct++;
+      }
+  }
+  if (want > distinct) want = distinct;
+  while (got < want) {
+    if (i + 1 >= buf.size()) {
+      uint8_t h[32];
+      sha256_oneshot(buf.data(), buf.size(), h);
+      buf.assign(h, h + 32);
+      i = 0;
+    }
+    const size_t idx = ((size_t)buf[i] * 256 + buf[i + 1]) % tickets.size();
+    const int winner = tickets[idx];
+    if (!seen[(size_t)winner] && winner != exclude) {
+      seen[(size_t)winner] = 1;
+      out[got++] = winner;
+    }
+    i++;
+  }
+  return got;
+}
+
+// roles: verifiers first, then miners continue from the same byte cursor (vrf.go:103-182)
+int bsc_lottery_roles(const uint8_t* input, int inlen, const int* stake, int n, int nverifiers, int nminers,
+                      int* verifiers, int* miners, int* nv_out, int* nm_out) {
+  std::vector<int> tickets;
+  for (int id = 0; id < n; id++)
+    for (int k = 0; k < stake[id]; k++) tickets.push_back(id);
+  if (tickets.empty()) return -1;
+  std::vector<uint8_t> buf(input, input + inlen);
+  size_t i = 0;
+  *nv_out = lottery_draw(buf, i, tickets, nverifiers, -1, verifiers);
+  *nm_out = lottery_draw(buf, i, tickets, nminers, -1, miners);
+  return 0;
+}
+// noisers from a peer's private VRF output, excluding itself (vrf.go:54-100)
+int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n, int source, int want, int* noisers) {
+  std::vector<int> tickets;
+  for (int id = 0; id < n; id++)
+    for (int k = 0; k < stake[id]; k++) tickets.push_back(id);
+  if (tickets.empty()) return 0;
+  std::vector<uint8_t> buf(vrf_out, vrf_out + len);
+  size_t i = 0;
+  return lottery_draw(buf, i, tickets, want, source, noisers);
+}
+
+}  // extern "C"

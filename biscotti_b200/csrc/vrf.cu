@@ -1,0 +1,261 @@
+// ECVRF (Ed25519 / Elligator2 / SHAKE256) — host prove/verify plus the batched device kernels that
+// evaluate every simulated peer's VRF in one launch, and a batched SHA-256 kernel.
+//
+// Reference: DistSys/vrf.go:16-52 (two coniks VRF keypairs per peer, Prove on the latest block
+// hash, 32-byte output + 96-byte proof).  coniks-go itself is not in the reference tree; the
+// construction implemented here is  H = 8*Elligator2(SHAKE256(m)),  Gamma = x*H,
+// r = SHAKE256(skhr || pk || m) mod l,  s = SHAKE256(G || H || pk || Gamma || rG || rH || m) mod l,
+// t = r - s*x,  proof = s || t || Gamma,  output = SHAKE256(Gamma || m)[:32].
+#include "common.cuh"
+#include "ed25519.cuh"
+#include "sha256.cuh"
+#include <string.h>
+
+// SHAKE256 lives in host_crypto.cpp
+struct Shake256 {
+  uint64_t st[25];
+  size_t pos;
+  bool squeezing;
+};
+void shake256_init(Shake256& s);
+void shake256_absorb(Shake256& s, const uint8_t* in, size_t n);
+void shake256_squeeze(Shake256& s, uint8_t* out, size_t n);
+
+namespace bsc {
+
+// ---- SHA-512 (host only; Ed25519 secret expansion) ------------------------------------------------
+static const uint64_t K512[80] = {
+    0x428a2f98d728ae22ULL, 0x7137449123ef65cdULL, 0xb5c0fbcfec4d3b2fULL, 0xe9b5dba58189dbbcULL, 0x3956c25bf348b538ULL,
+    0x59f111f1b605d019ULL, 0x923f82a4af194f9bULL, 0xab1c5ed5da6d8118ULL, 0xd807aa98a3030242ULL, 0x12835b0145706fbeULL,
+    0x243185be4ee4b28cULL, 0x550c7dc3d5ffb4e2ULL, 0x72be5d74f27b896fULL, 0x80deb1fe3b1696b1ULL, 0x9bdc06a725c71235ULL,
+    0xc19bf174cf692694ULL, 0xe49b69c19ef14ad2ULL, 0xefbe4786384f25e3ULL, 0x0fc19dc68b8cd5b5ULL, 0x240ca1cc77ac9c65ULL,
+    0x2de92c6f592b0275ULL, 0x4a7484aa6ea6e483ULL, 0x5cb0a9dcbd41fbd4ULL, 0x76f988da831153b5ULL, 0x983e5152ee66dfabULL,
+    0xa831c66d2db43210ULL, 0xb00327c898fb213fULL, 0xbf597fc7beef0ee4ULL, 0xc6e00bf33da88fc2ULL, 0xd5a79147930aa725ULL,
+    0x06ca6351e003826fULL, 0x142929670a0e6e70ULL, 0x27b70a8546d22ffcULL, 0x2e1b21385c26c926ULL, 0x4d2c6dfc5ac42aedULL,
+    0x53380d139d95b3dfULL, 0x650a73548baf63deULL, 0x766a0abb3c77b2a8ULL, 0x81c2c92e47edaee6ULL, 0x92722c851482353bULL,
+    0xa2bfe8a14cf10364ULL, 0xa81a664bbc423001ULL, 0xc24b8b70d0f89791ULL, 0xc76c51a30654be30ULL, 0xd192e819d6ef5218ULL,
+    0xd69906245565a910ULL, 0xf40e35855771202aULL, 0x106aa07032bbd1b8ULL, 0x19a4c116b8d2d0c8ULL, 0x1e376c085141ab53ULL,
+    0x2748774cdf8eeb99ULL, 0x34b0bcb5e19b48a8ULL, 0x391c0cb3c5c95a63ULL, 0x4ed8aa4ae3418acbULL, 0x5b9cca4f7763e373ULL,
+    0x682e6ff3d6b2b8a3ULL, 0x748f82ee5defb2fcULL, 0x78a5636f43172f60ULL, 0x84c87814a1f0ab72ULL, 0x8cc702081a6439ecULL,
+    0x90befffa23631e28ULL, 0xa4506cebde82bde9ULL, 0xbef9a3f7b2c67915ULL, 0xc67178f2e372532bULL, 0xca273eceea26619cULL,
+    0xd186b8c721c0c207ULL, 0xeada7dd6cde0eb1eULL, 0xf57d4f7fee6ed178ULL, 0x06f067aa72176fbaULL, 0x0a637dc5a2c898a6ULL,
+    0x113f9804bef90daeULL, 0x1b710b35131c471bULL, 0x28db77f523047d84ULL, 0x32caab7b40c72493ULL, 0x3c9ebe0a15c9bebcULL,
+    0x431d67c49c100d4cULL, 0x4cc5d4becb3e42b6ULL, 0x597f299cfc657e2aULL, 0x5fcb6fab3ad6faecULL, 0x6c44198c4a475817ULL};
+static inline uint64_t r64(uint64_t x, int n) { return (x >> n) | (x << (64 - n)); }
+static void sha512(const uint8_t* data, size_t n, uint8_t out[64]) {
+  uint64_t h[8] = {0x6a09e667f3bcc908ULL, 0xbb67ae8584caa73bULL, 0x3c6ef372fe94f82bULL, 0xa54ff53a5f1d36f1ULL,
+                   0x510e527fade682d1ULL, 0x9b05688c2b3e6c1fULL, 0x1f83d9abfb41bd6bULL, 0x5be0cd19137e2179ULL};
+  size_t total = n + 1 + 16;
+  size_t padded = (total + 127) / 128 * 128;
+  uint8_t* buf = new uint8_t[padded];
+  memset(buf, 0, padded);
+  memcpy(buf, data, n);
+  buf[n] = 0x80;
+  uint64_t bits = (uint64_t)n * 8;
+  for (int i = 0; i < 8; i++) buf[padded - 1 - i] = (uint8_t)(bits >> (8 * i));
+  for (size_t off = 0; off < padded; off += 128) {
+    uint64_t w[80];
+    for (int i = 0; i < 16; i++) {
+      uint64_t v = 0;
+      for (int j = 0; j < 8; j++) v = (v << 8) | buf[off + 8 * i + j];
+      w[i] = v;
+    }
+    for (int i = 16; i < 80; i++) {
+      uint64_t s0 = r64(w[i - 15], 1) ^ r64(w[i - 15], 8) ^ (w[i - 15] >> 7);
+      uint64_t s1 = r64(w[i - 2], 19) ^ r64(w[i - 2], 61) ^ (w[i - 2] >> 6);
+      w[i] = w[i - 16] + s0 + w[i - 7] + s1;
+    }
+    uint64_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+    for (int i = 0; i < 80; i++) {
+      uint64_t S1 = r64(e, 14) ^ r64(e, 18) ^ r64(e, 41);
+      uint64_t ch = (e & f) ^ (~e & g);
+      uint64_t t1 = hh + S1 + ch + K512[i] + w[i];
+      uint64_t S0 = r64(a, 28) ^ r64(a, 34) ^ r64(a, 39);
+      uint64_t mj = (a & b) ^ (a & c) ^ (b & c);
+      uint64_t t2 = S0 + mj;
+      hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
+  }
+  delete[] buf;
+  for (int i = 0; i < 8; i++)
+    for (int j = 0; j < 8; j++) out[8 * i + j] = (uint8_t)(h[i] >> (56 - 8 * j));
+}
+
+// 64 little-endian bytes mod l -> Montgomery scalar
+static Fs sc_reduce64(const uint8_t b[64]) {
+  Fs lo = fe_from_u256<EdL>(u256_from_le(b));
+  Fs hi = fe_from_u256<EdL>(u256_from_le(b + 32));
+  Fs r2;
+  for (int i = 0; i < 8; i++) r2.x.v[i] = EdL::r2(i);  // Montgomery form of 2^256 mod l
+  return fe_add(lo, fe_mul(hi, r2));
+}
+
+static void expand_secret(const uint8_t seed[32], U256& x, uint8_t skhr[32]) {
+  uint8_t h[64];
+  sha512(seed, 32, h);
+  h[0] &= 248;
+  h[31] &= 127;
+  h[31] |= 64;
+  x = u256_from_le(h);
+  memcpy(skhr, h + 32, 32);
+}
+
+static EdPoint hash_to_curve(const uint8_t* m, size_t n) {
+  uint8_t hm[32];
+  Shake256 s;
+  shake256_init(s);
+  shake256_absorb(s, m, n);
+  shake256_squeeze(s, hm, 32);
+  return ed_elligator2_x8(hm);
+}
+
+// ---- device kernels ------------------------------------------------------------------------------
+// out[i] = compress(k[i] * base[b(i)]) for 256-bit scalars; base index = i % nbase (nbase = 1: the
+// shared H of a block; nbase = N: per-element bases)
+__global__ void ed25519_scalarmult_kernel(const U256* __restrict__ k, const EdPoint* __restrict__ bases, int nbase,
+                                          int N, unsigned char* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  EdPoint r = ed_mul(bases[i % nbase], k[i]);
+  ed_compress(out + 32 * (size_t)i, r);
+}
+
+// batched SHA-256: digest of msgs[i] (each `len` bytes, `stride` apart) -> out[i][32]
+__global__ void sha256_batch_kernel(const unsigned char* __restrict__ msgs, int len, long long stride, int N,
+                                    unsigned char* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  sha256_oneshot(msgs + (size_t)i * stride, (size_t)len, out + 32 * (size_t)i);
+}
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+void bsc_sha512(const uint8_t* data, size_t n, uint8_t out[64]) { sha512(data, n, out); }
+
+// public key (32 bytes) from a 32-byte seed
+void bsc_vrf_pubkey(const uint8_t seed[32], uint8_t pk[32]) {
+  U256 x;
+  uint8_t skhr[32];
+  expand_secret(seed, x, skhr);
+  ed_compress(pk, ed_mul(ed_basepoint(), x));
+}
+// expanded secret scalar (little-endian words) for the device kernel
+void bsc_vrf_secret_scalar(const uint8_t seed[32], uint32_t out_words[8]) {
+  U256 x;
+  uint8_t skhr[32];
+  expand_secret(seed, x, skhr);
+  memcpy(out_words, x.v, 32);
+}
+// H = hashToCurve(m) in the device struct layout (4 x 8 words, Montgomery form)
+void bsc_vrf_hash_to_curve(const uint8_t* m, size_t n, void* out_point, uint8_t out_bytes[32]) {
+  EdPoint h = hash_to_curve(m, n);
+  if (out_point) memcpy(out_point, &h, sizeof(h));
+  if (out_bytes) ed_compress(out_bytes, h);
+}
+// output = SHAKE256(Gamma || m)[:32]
+void bsc_vrf_output_from_gamma(const uint8_t gamma[32], const uint8_t* m, size_t n, uint8_t out[32]) {
+  Shake256 s;
+  shake256_init(s);
+  shake256_absorb(s, gamma, 32);
+  shake256_absorb(s, m, n);
+  shake256_squeeze(s, out, 32);
+}
+
+void bsc_vrf_prove(const uint8_t seed[32], const uint8_t* m, size_t n, uint8_t vrf[32], uint8_t proof[96]) {
+  U256 x;
+  uint8_t skhr[32], pk[32];
+  expand_secret(seed, x, skhr);
+  const EdPoint B = ed_basepoint();
+  ed_compress(pk, ed_mul(B, x));
+  const EdPoint H = hash_to_curve(m, n);
+  uint8_t hB[32], gammaB[32], gB[32], grB[32], hrB[32];
+  ed_compress(hB, H);
+  ed_compress(gammaB, ed_mul(H, x));
+  ed_compress(gB, B);
+  uint8_t rH[64], sH[64];
+  Shake256 s;
+  shake256_init(s);
+  shake256_absorb(s, skhr, 32);
+  shake256_absorb(s, pk, 32);
+  shake256_absorb(s, m, n);
+  shake256_squeeze(s, rH, 64);
+  const Fs r = sc_reduce64(rH);
+  const U256 rp = fe_to_u256(r);
+  ed_compress(grB, ed_mul(B, rp));
+  ed_compress(hrB, ed_mul(H, rp));
+  shake256_init(s);
+  shake256_absorb(s, gB, 32);
+  shake256_absorb(s, hB, 32);
+  shake256_absorb(s, pk, 32);
+  shake256_absorb(s, gammaB, 32);
+  shake256_absorb(s, grB, 32);
+  shake256_absorb(s, hrB, 32);
+  shake256_absorb(s, m, n);
+  shake256_squeeze(s, sH, 64);
+  const Fs sc = sc_reduce64(sH);
+  const Fs xs = fe_from_u256<EdL>(x);
+  const Fs t = fe_sub(r, fe_mul(sc, xs));
+  u256_to_le(proof, fe_to_u256(sc));
+  u256_to_le(proof + 32, fe_to_u256(t));
+  memcpy(proof + 64, gammaB, 32);
+  bsc_vrf_output_from_gamma(gammaB, m, n, vrf);
+}
+
+int bsc_vrf_verify(const uint8_t pk[32], const uint8_t* m, size_t n, const uint8_t vrf[32], const uint8_t proof[96]) {
+  EdPoint P, Gamma;
+  if (!ed_decompress(P, pk) || !ed_decompress(Gamma, proof + 64)) return 0;
+  const U256 sc = u256_from_le(proof), t = u256_from_le(proof + 32);
+  const EdPoint B = ed_basepoint();
+  const EdPoint H = hash_to_curve(m, n);
+  const Fq d2 = ed_const_2d();
+  // rG = tG + sP ; rH = tH + s*Gamma
+  const EdPoint rG = ed_add(ed_mul(B, t), ed_mul(P, sc), d2);
+  const EdPoint rHp = ed_add(ed_mul(H, t), ed_mul(Gamma, sc), d2);
+  uint8_t gB[32], hB[32], grB[32], hrB[32], sH[64];
+  ed_compress(gB, B);
+  ed_compress(hB, H);
+  ed_compress(grB, rG);
+  ed_compress(hrB, rHp);
+  Shake256 s;
+  shake256_init(s);
+  shake256_absorb(s, gB, 32);
+  shake256_absorb(s, hB, 32);
+  shake256_absorb(s, pk, 32);
+  shake256_absorb(s, proof + 64, 32);
+  shake256_absorb(s, grB, 32);
+  shake256_absorb(s, hrB, 32);
+  shake256_absorb(s, m, n);
+  shake256_squeeze(s, sH, 64);
+  const U256 s2 = fe_to_u256(sc_reduce64(sH));
+  if (!u256_eq(s2, sc)) return 0;
+  uint8_t out[32];
+  bsc_vrf_output_from_gamma(proof + 64, m, n, out);
+  return memcmp(out, vrf, 32) == 0 ? 1 : 0;
+}
+
+// device: gamma[i] = compress(x[i] * H) for all peers
+int bsc_ed25519_scalarmult_batch(const void* scalars_u256, const void* bases, int nbase, int N, unsigned char* out,
+                                 void* stream) {
+  if (N == 0) return 0;
+  ed25519_scalarmult_kernel<<<(N + 63) / 64, 64, 0, (cudaStream_t)stream>>>((const U256*)scalars_u256,
+                                                                            (const EdPoint*)bases, nbase, N, out);
+  return finish_launch("ed25519_scalarmult_batch");
+}
+void bsc_ed25519_scalarmult_batch_host(const void* scalars_u256, const void* bases, int nbase, int N,
+                                       unsigned char* out) {
+  const U256* k = (const U256*)scalars_u256;
+  const EdPoint* b = (const EdPoint*)bases;
+  for (int i = 0; i < N; i++) ed_compress(out + 32 * (size_t)i, ed_mul(b[i % nbase], k[i]));
+}
+int bsc_sha256_batch(const unsigned char* msgs, int len, long long stride, int N, unsigned char* out, void* stream) {
+  if (N == 0) return 0;
+  sha256_batch_kernel<<<(N + 63) / 64, 64, 0, (cudaStream_t)stream>>>(msgs, len, stride, N, out);
+  return finish_launch("sha256_batch");
+}
+
+}  // extern "C"

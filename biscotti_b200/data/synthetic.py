@@ -1,0 +1,93 @@
+"""Synthetic datasets of the reference's shapes, sharded per peer.
+
+The real blobs are absent (.MISSING_LARGE_BLOBS) and BASELINE.json prescribes synthetic data.  The
+generators keep what the protocol depends on:
+  * per-peer shards (`mnist{i}.npy`, ML/Pytorch/data/mnist/parse_mnist.py:111-163: uniform slices),
+  * a held-out test set (`mnist_test`) and the attack set (`mnist_digit1`, client.py:13-23),
+  * the poisoned shard (`mnist_bad`: every 1 relabelled 7, parse_mnist.py:295-301; creditcard:
+    flipped labels) used by peers with id > idx (DistSys/main.go:836-844),
+  * creditcard rows standardised with a bias column (ML/code/utils.py:88-121), labels in {-1,+1}.
+Classes are Gaussian blobs around random prototypes so that training converges like the real task.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+from ..config import BiscottiConfig, DATASETS
+
+
+@dataclass
+class PeerData:
+    X: torch.Tensor          # [P_local, Ns, F]
+    y: torch.Tensor          # [P_local, Ns]  int32 (softmax/cnn) or float32 +-1 (logistic)
+    X_test: torch.Tensor     # [Nt, F]
+    y_test: torch.Tensor
+    X_attack: torch.Tensor   # rows of the attack source class (digit 1)
+    y_attack: torch.Tensor
+    peer_ids: torch.Tensor   # global ids of the local peers
+    poisoned: torch.Tensor   # bool [P_local]
+
+
+def _prototypes(n_classes: int, n_features: int, gen: torch.Generator, sep: float):
+    protos = torch.randn(n_classes, n_features, generator=gen)
+    return protos / protos.norm(dim=1, keepdim=True) * sep
+
+
+def poisoner_ids(cfg: BiscottiConfig) -> set[int]:
+    """DistSys rule: ids strictly greater than N*(1-po) poison (main.go:836-844)."""
+    if cfg.poison_fraction <= 0:
+        return set()
+    idx = int(cfg.num_nodes * (1.0 - cfg.poison_fraction))
+    return {i for i in range(cfg.num_nodes) if i > idx}
+
+
+def make_data(cfg: BiscottiConfig, peer_ids: list[int], device="cpu", noise: float = 1.0, sep: float = 6.0) -> PeerData:
+    spec = DATASETS[cfg.dataset]
+    F, C = spec.n_features, spec.n_classes
+    logistic = spec.model == "logistic"
+    g0 = torch.Generator().manual_seed(cfg.seed * 7919 + 13)
+    if logistic:
+        Fr = F - 1  # last column is the bias (utils.py:88-121)
+        wtrue = torch.randn(Fr, generator=g0)
+
+        def sample(n, gen):
+            X = torch.randn(n, Fr, generator=gen)
+            y = torch.sign(X @ wtrue + 0.3 * torch.randn(n, generator=gen))
+            y[y == 0] = 1.0
+            return torch.cat([X, torch.ones(n, 1)], dim=1), y.float()
+    else:
+        protos = _prototypes(C, F, g0, sep)
+
+        def sample(n, gen):
+            y = torch.randint(0, C, (n,), generator=gen)
+            X = protos[y] + noise * torch.randn(n, F, generator=gen)
+            return X, y.int()
+
+    bad = poisoner_ids(cfg)
+    Xs, ys, pz = [], [], []
+    for pid in peer_ids:
+        gen = torch.Generator().manual_seed(cfg.seed * 1000003 + pid)
+        X, y = sample(cfg.shard_size, gen)
+        if pid in bad:
+            if logistic:
+                y = -y
+            else:
+                y = torch.where(y == 1, torch.full_like(y, 7 % C), y)
+        Xs.append(X)
+        ys.append(y)
+        pz.append(pid in bad)
+    gt = torch.Generator().manual_seed(cfg.seed * 104729 + 1)
+    Xt, yt = sample(cfg.test_size, gt)
+    if logistic:
+        Xa, ya = Xt[yt > 0], yt[yt > 0]
+    else:
+        Xa, ya = Xt[yt == 1], yt[yt == 1]
+    if Xa.shape[0] == 0:
+        Xa, ya = Xt[:1], yt[:1]
+    dev = torch.device(device)
+    return PeerData(torch.stack(Xs).to(dev) if Xs else torch.empty(0, cfg.shard_size, F, device=dev),
+                    torch.stack(ys).to(dev) if ys else torch.empty(0, cfg.shard_size, device=dev),
+                    Xt.to(dev), yt.to(dev), Xa.contiguous().to(dev), ya.contiguous().to(dev),
+                    torch.tensor(peer_ids, dtype=torch.int32, device=dev), torch.tensor(pz, dtype=torch.bool))

@@ -1,0 +1,178 @@
+"""Polynomial commitments and KZG witnesses on BN256 G1, batched over peers.
+
+Reference: DistSys/kyber.go:172-202 (per-chunk commitments with SRS slice [10c, 10c+10)), :533-562
+(createCommitment), :579-646 (createShareAndWitness), :244-287 (aggregateSecret), :456-482
+(generateMinerSecretShares); DistSys/publicKey.go:28-66 (SRS = powers of tau, tau = 2).
+
+Points live on the device as ``uint32[..., 16]`` (affine, Montgomery form) or ``uint32[..., 24]``
+(Jacobian); the 64-byte big-endian wire form (point.go:109-167) is produced only for what enters
+the ledger.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from ._call import lib, ptr, stream, check
+from .secagg import POLY_SIZE, nchunks
+
+AFF = 16  # uint32 words per affine point
+JAC = 24  # uint32 words per Jacobian point
+
+
+def _i32(x, device):
+    return torch.tensor(x, dtype=torch.int32, device=device)
+
+
+class CommitmentEngine:
+    """Holds the SRS and the witness base table for one model dimension and runs the MSM kernels."""
+
+    def __init__(self, d: int, total_shares: int, tau: int = 2, device="cpu", srs_bytes: bytes | None = None):
+        self.d, self.S, self.device = d, total_shares, torch.device(device)
+        self.nchunk = nchunks(d)
+        self.dpad = self.nchunk * POLY_SIZE
+        self.tau = tau
+        L = lib()
+        # ---- SRS (PKG1[i] = tau^i * G), padded with the generator (padding scalars are always 0)
+        if srs_bytes is None:
+            srs_bytes = self._generate_srs(tau)
+        self.srs_bytes = srs_bytes
+        gen = ctypes.create_string_buffer(64)
+        L.bsc_g1_generator(gen)
+        full = srs_bytes + gen.raw * (self.dpad - d)
+        host_aff = torch.empty(self.dpad, AFF, dtype=torch.int32)
+        L.bsc_g1_bytes_to_affine_host(full, ptr(host_aff), self.dpad)
+        self.bases = host_aff.to(self.device)
+        # ---- index tables
+        c = torch.arange(self.nchunk, dtype=torch.int32)
+        self.c_sidx = (c * POLY_SIZE).to(self.device)
+        self.c_bidx = (c * POLY_SIZE).to(self.device)
+        S = self.S
+        cs = torch.arange(self.nchunk * S, dtype=torch.int32)
+        self.w_sidx = ((cs // S) * POLY_SIZE + 1).to(self.device)          # a_1..a_9 of the chunk
+        self.w_bidx = (cs * (POLY_SIZE - 1)).to(self.device)               # T[c, s, 0..8]
+        self.wtable = self._build_witness_table()
+
+    # -- SRS ------------------------------------------------------------------------------------
+    def _generate_srs(self, tau: int) -> bytes:
+        L = lib()
+        d = self.d
+        tb = int(tau).to_bytes(32, "big")
+        if tau == 2 or d <= 4096 or self.device.type != "cuda":
+            out = ctypes.create_string_buffer(64 * d)
+            L.bsc_srs_g1_host(tb, d, out)
+            return out.raw
+        words = torch.empty(d, 8, dtype=torch.int32)
+        L.bsc_fr_powers(tb, d, ptr(words))
+        gen = ctypes.create_string_buffer(64)
+        L.bsc_g1_generator(gen)
+        g_aff = torch.empty(AFF, dtype=torch.int32)
+        L.bsc_g1_bytes_to_affine_host(gen.raw, ptr(g_aff), 1)
+        k = words.to(self.device)
+        jac = torch.empty(d, JAC, dtype=torch.int32, device=self.device)
+        check(L.bsc_g1_fixed_base_mul(ptr(k), d, ptr(g_aff), ptr(jac), stream(self.device)), "g1_fixed_base_mul")
+        return self.to_bytes(self.normalize(jac))
+
+    # -- witness base table T[c, s, j-1] = sum_{k<j} x_s^{j-1-k} * PKG1[10c+k], j = 1..9 ------------
+    def _build_witness_table(self):
+        S, T = self.S, POLY_SIZE - 1
+        # "peers" of this MSM are the share indices s; scalars depend only on (s, j, k)
+        Q = torch.zeros(S, T * T, dtype=torch.int64)
+        for s in range(S):
+            x = s - 10
+            for j in range(1, POLY_SIZE):
+                for k in range(j):
+                    Q[s, (j - 1) * T + k] = x ** (j - 1 - k)
+        G = self.nchunk * T
+        g = torch.arange(G, dtype=torch.int32)
+        cc, jj = g // T, g % T
+        sidx = (jj * T)
+        bidx = (cc * POLY_SIZE)
+        og = (cc * (S * T) + jj)
+        out = self._msm(Q.to(self.device), None, S, sidx.to(self.device), bidx.to(self.device), og.to(self.device), G, T,
+                        self.bases, ostride=T, nout=self.nchunk * S * T)
+        return self.normalize(out)
+
+    # -- raw kernels -----------------------------------------------------------------------------
+    def _msm(self, Q, sel, P, sidx, bidx, og, G, T, bases, ostride, nout):
+        out = torch.empty(nout, JAC, dtype=torch.int32, device=self.device)
+        L = lib()
+        if self.device.type == "cuda":
+            check(L.bsc_msm_groups(ptr(Q), Q.stride(0), ptr(sel), P, ptr(sidx), ptr(bidx), ptr(og), G, T, ptr(bases),
+                                   ptr(out), ostride, stream(self.device)), "msm_groups")
+        else:
+            L.bsc_msm_groups_host(ptr(Q), Q.stride(0), ptr(sel), P, ptr(sidx), ptr(bidx), ptr(og), G, T, ptr(bases),
+                                  ptr(out), ostride)
+        return out
+
+    def normalize(self, jac: torch.Tensor) -> torch.Tensor:
+        shape = jac.shape[:-1]
+        N = jac.numel() // JAC
+        out = torch.empty(*shape, AFF, dtype=torch.int32, device=jac.device)
+        if jac.is_cuda:
+            check(lib().bsc_g1_normalize(ptr(jac), ptr(out), N, stream(jac.device)), "g1_normalize")
+        else:
+            lib().bsc_g1_normalize_host(ptr(jac), ptr(out), N)
+        return out
+
+    def to_bytes(self, aff: torch.Tensor) -> bytes:
+        N = aff.numel() // AFF
+        if aff.is_cuda:
+            out = torch.empty(N, 64, dtype=torch.uint8, device=aff.device)
+            check(lib().bsc_g1_affine_to_bytes(ptr(aff), ptr(out), N, stream(aff.device)), "g1_affine_to_bytes")
+            return out.cpu().numpy().tobytes()
+        buf = ctypes.create_string_buffer(64 * N)
+        lib().bsc_g1_affine_to_bytes_host(ptr(aff.contiguous()), buf, N)
+        return buf.raw
+
+    def to_bytes_tensor(self, aff: torch.Tensor) -> torch.Tensor:
+        """Device-resident wire bytes [N, 64] (no host sync)."""
+        N = aff.numel() // AFF
+        out = torch.empty(N, 64, dtype=torch.uint8, device=aff.device)
+        if aff.is_cuda:
+            check(lib().bsc_g1_affine_to_bytes(ptr(aff), ptr(out), N, stream(aff.device)), "g1_affine_to_bytes")
+        else:
+            buf = ctypes.create_string_buffer(64 * N)
+            lib().bsc_g1_affine_to_bytes_host(ptr(aff.contiguous()), buf, N)
+            out = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).view(N, 64)
+        return out
+
+    # -- protocol-level operations -----------------------------------------------------------------
+    def chunk_commitments(self, Q: torch.Tensor, sel: torch.Tensor | None = None) -> torch.Tensor:
+        """C[p, c] = sum_j Q[p, 10c+j] * PKG1[10c+j]  -> affine [P, nchunk, 16]."""
+        P = Q.shape[0] if sel is None else sel.numel()
+        jac = self._msm(Q, sel, P, self.c_sidx, self.c_bidx, None, self.nchunk, POLY_SIZE, self.bases,
+                        ostride=self.nchunk, nout=P * self.nchunk)
+        return self.normalize(jac).view(P, self.nchunk, AFF)
+
+    def full_commitments(self, chunk_aff: torch.Tensor) -> torch.Tensor:
+        """Full-vector commitment = sum of the chunk commitments -> affine [P, 16]."""
+        P, G = chunk_aff.shape[0], chunk_aff.shape[1]
+        jac = torch.empty(P, JAC, dtype=torch.int32, device=chunk_aff.device)
+        if chunk_aff.is_cuda:
+            check(lib().bsc_g1_sum_cols(ptr(chunk_aff), P, G, ptr(jac), stream(chunk_aff.device)), "g1_sum_cols")
+        else:
+            lib().bsc_g1_sum_cols_host(ptr(chunk_aff), P, G, ptr(jac))
+        return self.normalize(jac)
+
+    def witnesses(self, Q: torch.Tensor, sel: torch.Tensor | None = None) -> torch.Tensor:
+        """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> affine [P, nchunk, S, 16]."""
+        P = Q.shape[0] if sel is None else sel.numel()
+        G = self.nchunk * self.S
+        jac = self._msm(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.wtable, ostride=G,
+                        nout=P * G)
+        return self.normalize(jac).view(P, self.nchunk, self.S, AFF)
+
+    def aggregate(self, pts_aff: torch.Tensor, sel: torch.Tensor) -> torch.Tensor:
+        """Miner-side homomorphic add over contributing peers: pts [P, G..., 16] -> affine [G..., 16]."""
+        P = pts_aff.shape[0]
+        inner = pts_aff.shape[1:-1]
+        G = pts_aff.numel() // (P * AFF)
+        jac = torch.empty(G, JAC, dtype=torch.int32, device=pts_aff.device)
+        if pts_aff.is_cuda:
+            check(lib().bsc_g1_sum_rows(ptr(pts_aff), ptr(sel), sel.numel(), G, ptr(jac), stream(pts_aff.device)),
+                  "g1_sum_rows")
+        else:
+            lib().bsc_g1_sum_rows_host(ptr(pts_aff), ptr(sel), sel.numel(), G, ptr(jac))
+        return self.normalize(jac).view(*inner, AFF)

@@ -1,0 +1,435 @@
+"""The Biscotti protocol engine: one object per rank simulating its share of the peers.
+
+What one `step()` does is the reference's block iteration (call stacks §3.3-3.6):
+  1. role lottery on the latest block hash            DistSys/main.go:486-565, vrf.go:103-182
+  2. local SGD step of every worker                   honest.go:165-200, client_obj.py:73-77
+  3. commitment to the quantised update               kyber.go:533-562 (one MSM per chunk, summed)
+  4. noiser lottery + DP noise                        vrf.go:54-100, main.go:1592-1660, 1530-1537
+  5. Multi-Krum over the first KRUM_UPDATETHRESH      krum.go:227-365, client_obj.py:114-143
+  6. Schnorr approvals, >= nv/2 needed                kyber.go:873-896, main.go:1686
+  7. Shamir shares + KZG witnesses to the miners      kyber.go:456-482, main.go:1847-1952
+  8. miners aggregate, leader reconstructs the sum    kyber.go:244-287, 809-857; honest.go:391-502
+  9. w_{t+1} = w_t + sum, stake update, block append  honest.go:391-440, block.go:23-44
+ 10. flood + test error / attack rate                 main.go:1403-1444, honest.go:141-162
+
+There are no per-peer processes, sockets or wall-clock timeouts: peers are rows of device tensors,
+message arrival order is an explicit seeded permutation (so "first NUM_SAMPLES/2 shares win" and
+Krum's "first KRUM_UPDATETHRESH updates" are reproducible), and every rank replays the same control
+flow from the same block hash, so the ledger is replicated without gossip.
+"""
+from __future__ import annotations
+
+import hashlib
+import math
+import time
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from ..config import BiscottiConfig, DEFAULT_STAKE, STAKE_UNIT, POLY_SIZE, NOISE_TABLE_ITERS
+from ..crypto import primitives as cp
+from ..data.synthetic import make_data, poisoner_ids
+from ..ledger.chain import Blockchain, UpdateRecord
+from ..models.registry import Model
+from ..ops import ml, krum as krum_ops, secagg
+from ..ops.msm import CommitmentEngine
+from ..utils.log import PeerLogger
+
+
+@dataclass
+class BlockReport:
+    iteration: int
+    block_hash: bytes
+    empty: bool
+    verifiers: list
+    miners: list
+    n_workers: int
+    n_krum: int
+    n_accepted: int
+    n_contributors: int
+    test_error: float | None = None
+    attack_rate: float | None = None
+    loss: float | None = None
+    bad_shares: int = 0
+    phase_ms: dict = field(default_factory=dict)
+    unmasked_updates: int = 0
+
+
+class BiscottiEngine:
+    def __init__(self, cfg: BiscottiConfig, device="cpu", rank: int = 0, world: int = 1, comm=None, log_stream=None,
+                 external_inputs: bool = False):
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.rank, self.world, self.comm = rank, world, comm
+        n = cfg.num_nodes
+        per = (n + world - 1) // world
+        self.local_ids = list(range(rank * per, min(n, (rank + 1) * per)))
+        self.owner = [p // per for p in range(n)]
+        self.P = len(self.local_ids)
+        self.local_index = {p: i for i, p in enumerate(self.local_ids)}
+        self.model = Model(cfg)
+        self.d = cfg.dim
+        self.ldu = ml.pad_to(self.d, 4)
+        self.ldh = ml.pad_to(self.d, 64)
+        self.S = cfg.total_shares
+        self.log = PeerLogger(rank, stream=log_stream)
+        self.external_inputs = external_inputs
+        # ---- state
+        self.chain = Blockchain(self.d)
+        self.stake = [DEFAULT_STAKE] * n
+        self.alive = [True] * n
+        self.iteration = 0
+        self.keys = cp.derive_peer_keys(n, cfg.seed)
+        self.poisoners = poisoner_ids(cfg)
+        self.colluder_ids = set(range(n - cfg.colluders, n)) if cfg.colluders > 0 else set()
+        self.data = None if external_inputs else make_data(cfg, self.local_ids, self.device)
+        if external_inputs:
+            self.data = make_data(cfg, [], self.device)   # test / attack sets only
+        w0 = self.model.init_weights()
+        if w0.abs().sum() != 0:
+            # non-zero genesis (CNNs): record it as the genesis block's GlobalW
+            self.chain = Blockchain(self.d)
+            self.chain.add_block(-1, w0.numpy(), [], None, timestamp=0)
+        self.w64 = w0.to(self.device)
+        self.w32 = self.w64.float()
+        self.U = torch.zeros(max(1, self.P), self.ldu, dtype=torch.float32, device=self.device)
+        self.commit = None
+        if cfg.commitments and cfg.secure_agg and cfg.mode == "biscotti":
+            self.commit = CommitmentEngine(self.d, self.S, tau=cfg.srs_tau or self._random_tau(), device=self.device)
+        self.vrf = cp.BatchedVRF([k.vrf_noise for k in self.keys], self.device)
+        self.reports: list[BlockReport] = []
+        self._rng = np.random.RandomState(cfg.seed * 65537 % (2**31))
+        self._timing = False
+
+    # ------------------------------------------------------------------------------------------
+    def _random_tau(self) -> int:
+        h = hashlib.sha256(f"bsc-tau-{self.cfg.seed}".encode()).digest()
+        return int.from_bytes(h, "big") % cp_order()
+
+    def _arrival_order(self, ids: list[int], tag: str) -> list[int]:
+        """Deterministic stand-in for network arrival order, identical on every rank."""
+        h = hashlib.sha256(f"{self.cfg.seed}-{self.iteration}-{tag}".encode()).digest()
+        rs = np.random.RandomState(int.from_bytes(h[:4], "little"))
+        perm = rs.permutation(len(ids))
+        return [ids[i] for i in perm]
+
+    def _phase(self, name: str):
+        return _Phase(self, name)
+
+    # ------------------------------------------------------------------------------------------
+    def select_roles(self):
+        cfg = self.cfg
+        h = self.chain.latest_hash()
+        stake = [s if a else 0 for s, a in zip(self.stake, self.alive)]
+        if sum(stake) == 0:
+            return [], [], h
+        verifiers, miners = cp.lottery_roles(h, stake, cfg.num_verifiers, cfg.num_miners)
+        verifiers = sorted(verifiers)  # getRoleNames sorts verifiers (main.go:529-565)
+        return verifiers, miners, h
+
+    def sample_minibatch(self, n_local: int):
+        """Random minibatch without replacement per peer (logistic_model.py:121-125, DataLoader shuffle)."""
+        Ns, B = self.cfg.shard_size, self.cfg.batch_size
+        rows = []
+        for p in (self.local_ids or [0]):
+            # seeded per (seed, iteration, peer) so the draw does not depend on how peers are sharded
+            rs = np.random.RandomState((self.cfg.seed * 1000003 + self.iteration * 7919 + p * 104729) % (2**31))
+            rows.append(rs.choice(Ns, size=B, replace=False))
+        return torch.from_numpy(np.stack(rows).astype(np.int32))
+
+    # ------------------------------------------------------------------------------------------
+    def step(self, inputs=None) -> BlockReport:
+        """Run one block iteration.  `inputs` = (X [P,B,F], y [P,B]) device tensors when the caller feeds
+        minibatches (bench end-to-end path); otherwise minibatches are drawn from the resident shards."""
+        cfg = self.cfg
+        if cfg.mode == "fedsys":
+            from .fedsys import fedsys_step
+
+            return fedsys_step(self, inputs)
+        t0 = time.perf_counter()
+        it = self.iteration
+        n = cfg.num_nodes
+        dev = self.device
+        phases = {}
+        self._phases = phases
+        # ---- fault injection (main.go:1117-1120): a failing peer sits this block out and rejoins
+        if cfg.fail_prob > 0:
+            for p in range(1, n):
+                self.alive[p] = self._rng.rand() >= cfg.fail_prob
+        # ---- 1. roles
+        verifiers, miners, prev_hash = self.select_roles()
+        committee = set(verifiers) | set(miners)
+        workers = [p for p in range(n) if p not in committee and self.alive[p]]
+        slot = it % NOISE_TABLE_ITERS
+        rep = BlockReport(it, b"", True, verifiers, miners, len(workers), 0, 0, 0)
+        if not verifiers or not miners or not workers:
+            return self._finish_block(rep, [], None, phases, t0)   # main.go:1696-1707, 1934-1944
+
+        # ---- 2. local step for my workers (all local rows are computed; non-workers are ignored)
+        with self._phase("local_step"):
+            if inputs is not None:
+                X, y = inputs
+                idx = None
+            else:
+                X, y = self.data.X, self.data.y
+                idx = self.sample_minibatch(self.P).to(dev)
+            if self.P:
+                pid = self.data.peer_ids if not self.external_inputs else torch.tensor(self.local_ids, dtype=torch.int32, device=dev)
+                self.model.local_step(self.w32, X, y, idx, self.U, peer_ids=pid, slot=slot)
+
+        # ---- 3. commitments (local peers)
+        Q = None
+        chunkC = None
+        fullC_bytes = {}
+        if self.commit is not None and self.P:
+            with self._phase("commit"):
+                Q = secagg.quantize(self.U, self.d, cfg.precision)
+                chunkC = self.commit.chunk_commitments(Q)                      # [P, nchunk, 16]
+                fullC = self.commit.full_commitments(chunkC)                   # [P, 16]
+                fullC_dev = self.commit.to_bytes_tensor(fullC)                 # [P, 64] on device
+
+        # ---- 4. noisers + noise
+        with self._phase("noise"):
+            noiser_tab = torch.full((max(1, self.P), max(1, cfg.num_noisers)), -1, dtype=torch.int32)
+            noisers_of = {}
+            if cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
+                outs = self.vrf.outputs(prev_hash)
+                stake = [s if a else 0 for s, a in zip(self.stake, self.alive)]
+                for p in workers:
+                    nz = cp.lottery_noisers(outs[p], stake, p, cfg.num_noisers)
+                    noisers_of[p] = nz
+                    if p in self.local_index:
+                        for j, q in enumerate(nz):
+                            noiser_tab[self.local_index[p], j] = q
+            scale = cfg.noise_scale if (cfg.noising and cfg.epsilon > 0) else 0.0
+            Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab.to(dev), cfg.seed, slot, scale, self.d, ldh=self.ldh)
+
+        # ---- 5. verification
+        arrival = self._arrival_order(workers, "verify")
+        krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh, sorted by id
+        rep.n_krum = len(krum_set)
+        accepted: list[int] = []
+        with self._phase("verify"):
+            if not cfg.verification:
+                accepted = list(krum_set)
+            elif cfg.defense == "RONI":
+                accepted = self._roni(krum_set, Un)
+            else:
+                accepted = self._krum(krum_set, Un, hi, lo, norms)
+        rep.n_accepted = len(accepted)
+        # collusion accounting (main.go:1026-1057, 1138-1144)
+        if self.colluder_ids:
+            vcol = any(v in self.colluder_ids for v in verifiers)
+            rep.unmasked_updates = sum(1 for p in krum_set if vcol and noisers_of.get(p) and
+                                       all(q in self.colluder_ids for q in noisers_of[p]))
+
+        # ---- 6. approvals: every verifier signs the commitment of each accepted update
+        approved = accepted if len(verifiers) >= max(1, len(verifiers) // 2) else []
+
+        # ---- 7/8. shares, witnesses, aggregation, reconstruction, SGD step
+        share_order = [p for p in self._arrival_order(approved, "shares")]
+        trigger = max(1, cfg.num_samples // 2) if cfg.share_trigger == "half" else len(share_order)
+        contributors = sorted(share_order[:trigger])            # main.go:360 + leader intersection
+        alive_miners = [m for m in miners if self.alive[m]]
+        shares_avail = self._available_shares(miners, alive_miners)
+        enough = len(contributors) >= 2 and sum(shares_avail) >= POLY_SIZE and len(alive_miners) > 0
+        if not enough:
+            return self._finish_block(rep, [], None, phases, t0)   # main.go:2099-2117
+        rep.n_contributors = len(contributors)
+        local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
+        sel = torch.tensor(local_contrib, dtype=torch.int32, device=dev)
+        agg_commit = None
+        if cfg.secure_agg:
+            if self.commit is not None and self.P:
+                with self._phase("witness"):
+                    # every approved worker generates shares + witnesses for the miners (kyber.go:456-482)
+                    appr_local = torch.tensor([self.local_index[p] for p in approved if p in self.local_index],
+                                              dtype=torch.int32, device=dev)
+                    W = self.commit.witnesses(Q, appr_local) if appr_local.numel() else None
+                with self._phase("miner_aggregate"):
+                    if W is not None and sel.numel():
+                        # positions of contributors inside the approved-local list
+                        pos = {int(r): i for i, r in enumerate(appr_local.tolist())}
+                        csel = torch.tensor([pos[r] for r in local_contrib], dtype=torch.int32, device=dev)
+                        aggW = self.commit.aggregate(W, csel)               # [nchunk, S, 16]
+                        aggC = self.commit.aggregate(chunkC, sel)           # [nchunk, 16]
+                        agg_commit = (aggC, aggW)
+            with self._phase("secagg"):
+                Ysum = secagg.share_sum(self.U, sel, self.d, self.S, cfg.precision) if sel.numel() else \
+                    torch.zeros(cfg.nchunk, self.S, dtype=torch.int64, device=dev)
+                if self.comm is not None:
+                    Ysum = self.comm.all_reduce_i64(Ysum)
+                xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
+                xs_t = torch.tensor(xs, dtype=torch.int32, device=dev)
+                av_t = torch.tensor(shares_avail, dtype=torch.uint8, device=dev)
+                _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
+        else:
+            with self._phase("secagg"):
+                if self.comm is not None and self.world > 1:
+                    rows = self.comm.gather_rows(contributors, self.U, self.local_index, self.owner)
+                    rsel = torch.arange(len(contributors), dtype=torch.int32, device=dev)
+                    secagg.plain_sum_step(rows, rsel, self.d, self.w64, self.w32)
+                else:
+                    secagg.plain_sum_step(self.U, sel, self.d, self.w64, self.w32)
+                bad = torch.zeros(2, dtype=torch.int32, device=dev)
+
+        # ---- 9. block assembly (host)
+        with self._phase("block"):
+            updates = []
+            commits = {}
+            if self.commit is not None and self.P:
+                cb = fullC_dev.cpu().numpy()
+                for p in contributors:
+                    if p in self.local_index:
+                        commits[p] = cb[self.local_index[p]].tobytes()
+            if self.comm is not None:
+                commits = self.comm.merge_dicts(commits)
+            for p in contributors:
+                c = commits.get(p, b"")
+                sigs = []
+                if cfg.verification and c:
+                    sigs = [cp.schnorr_sign(c, self.keys[v].schnorr_secret) for v in verifiers] if cfg.extra.get("sign", False) else []
+                rec = UpdateRecord(source=p, iteration=it, commitment=c, accepted=True, signatures=sigs)
+                if not cfg.secure_agg and p in self.local_index and self.world == 1:
+                    rec.delta = self.U[self.local_index[p], : self.d].double().cpu().numpy()
+                updates.append(rec)
+                self.stake[p] += STAKE_UNIT
+            if not cfg.secure_agg:
+                for p in krum_set:
+                    if p not in accepted:
+                        self.stake[p] -= STAKE_UNIT                      # honest.go:362-370 (plain path only)
+            rep.bad_shares = int(bad.sum().item())
+        return self._finish_block(rep, updates, agg_commit, phases, t0)
+
+    # ------------------------------------------------------------------------------------------
+    def _available_shares(self, miners, alive_miners):
+        spm = self.cfg.shares_per_miner
+        avail = [0] * self.S
+        for j, m in enumerate(miners):
+            if m in alive_miners:
+                for s in range(j * spm, min(self.S, (j + 1) * spm)):
+                    avail[s] = 1
+        return avail
+
+    def _gather_rows(self, ids: list[int], local: torch.Tensor) -> torch.Tensor:
+        """Rows of `local` (indexed by local peer position) for global peer ids, in order."""
+        if self.comm is None:
+            ix = torch.tensor([self.local_index[p] for p in ids], dtype=torch.long, device=local.device)
+            return local.index_select(0, ix).contiguous()
+        return self.comm.gather_rows(ids, local, self.local_index, self.owner)
+
+    def _krum(self, krum_set, Un, hi, lo, norms):
+        cfg = self.cfg
+        nk = len(krum_set)
+        if nk < 3:
+            return list(krum_set)
+        clip = int(math.floor(cfg.krum_adversary_frac * nk))
+        if self.comm is not None and hasattr(self.comm, "krum_fused"):
+            acc = self.comm.krum_fused(krum_set, hi, lo, norms, clip, self.local_index, self.owner)
+        else:
+            Uk = self._gather_rows(krum_set, Un)
+            hik = self._gather_rows(krum_set, hi) if hi is not None else None
+            lok = self._gather_rows(krum_set, lo) if lo is not None else None
+            nrm = self._gather_rows(krum_set, norms.unsqueeze(1)).squeeze(1) if norms is not None else None
+            _, acc, _ = krum_ops.krum(Uk, self.d, clip, hik, lok, nrm, impl=cfg.gram_impl)
+        mask = acc.cpu().tolist()
+        return [p for p, a in zip(krum_set, mask) if a]
+
+    def _roni(self, krum_set, Un):
+        """RONI (main.go:191-233, honest.go:598-629): reject when validation error rises by > threshold."""
+        Uk = self._gather_rows(krum_set, Un)
+        base_err = self.model.eval_errors(self.w32.unsqueeze(0), None, self.data.X_test, self.data.y_test)[0]
+        errs = self.model.eval_errors(Uk, self.w32, self.data.X_test, self.data.y_test)
+        ok = ((errs - base_err) <= self.cfg.roni_threshold).cpu().tolist()
+        return [p for p, a in zip(krum_set, ok) if a]
+
+    def evaluate(self):
+        w = self.w32.unsqueeze(0)
+        te = self.model.eval_errors(w, None, self.data.X_test, self.data.y_test)
+        ar = self.model.eval_errors(w, None, self.data.X_attack, self.data.y_attack)
+        return te, ar
+
+    def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0) -> BlockReport:
+        cfg = self.cfg
+        it = self.iteration
+        with self._phase("block"):
+            w_host = self.w64.cpu().numpy()
+            ts = (0 if not updates else 1 + it) if cfg.deterministic_time else -1
+            stake_map = {i: s for i, s in enumerate(self.stake)}
+            rep.block_hash = self.chain.add_block(it, w_host, updates, stake_map, timestamp=ts)
+            rep.empty = not updates
+        if cfg.eval_every and (it % cfg.eval_every == 0):
+            with self._phase("eval"):
+                te, ar = self.evaluate()
+                rep.test_error, rep.attack_rate = float(te[0]), float(ar[0])
+                self.log.train_error(it, rep.test_error)
+                self.log.attack_rate(it, rep.attack_rate)
+        rep.phase_ms = dict(phases)
+        rep.phase_ms["total_host"] = (time.perf_counter() - t0) * 1e3
+        self.last_aggregate = agg_commit
+        self.reports.append(rep)
+        self.iteration += 1
+        return rep
+
+    # ------------------------------------------------------------------------------------------
+    def run(self, iterations: int | None = None):
+        """Main loop (main.go:1059-1187): runs until iterationCount > MAX_ITERATIONS, i.e. max+1 blocks
+        after genesis (102 logged blocks with the genesis one)."""
+        total = (self.cfg.max_iterations + 1) if iterations is None else iterations
+        for _ in range(total):
+            self.step()
+        return self.reports
+
+    def print_chain(self) -> str:
+        return self.chain.dump()
+
+    # rejoin: a restarted peer adopts the longest chain it is offered (main.go:1000-1013)
+    def adopt_chain(self, serialized: bytes) -> bool:
+        other = Blockchain.deserialize(serialized)
+        if len(other) > len(self.chain) and other.verify():
+            self.chain = other
+            self.iteration = other.latest_iteration + 1
+            w = torch.from_numpy(other.weights()).to(self.device)
+            self.w64.copy_(w)
+            self.w32.copy_(w.float())
+            info = other.block_info(-1)
+            if info["stake"]:
+                for k, v in info["stake"].items():
+                    self.stake[k] = v
+            return True
+        return False
+
+
+def cp_order() -> int:
+    from ..oracle.bn256 import ORDER
+
+    return ORDER
+
+
+class _Phase:
+    """Phase timer: CUDA events when timing is enabled on a GPU engine, wall clock otherwise."""
+
+    def __init__(self, eng: BiscottiEngine, name: str):
+        self.eng, self.name = eng, name
+
+    def __enter__(self):
+        e = self.eng
+        if e._timing and e.device.type == "cuda":
+            self.ev0 = torch.cuda.Event(enable_timing=True)
+            self.ev1 = torch.cuda.Event(enable_timing=True)
+            self.ev0.record()
+        else:
+            self.t0 = time.perf_counter()
+        return self
+
+    def __exit__(self, *a):
+        e = self.eng
+        if e._timing and e.device.type == "cuda":
+            self.ev1.record()
+            self.ev1.synchronize()
+            ms = self.ev0.elapsed_time(self.ev1)
+        else:
+            ms = (time.perf_counter() - self.t0) * 1e3
+        e._phases[self.name] = e._phases.get(self.name, 0.0) + ms
+        return False

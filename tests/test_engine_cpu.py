@@ -1,0 +1,132 @@
+"""End-to-end protocol on the CPU plumbing config (creditcard logistic, 10 peers — BASELINE.json
+config 1) and the ledger-equality oracle of DistSys/localTest.sh:39-89."""
+import math
+import os
+import subprocess
+import sys
+
+import numpy as np
+import torch
+
+from biscotti_b200.config import BiscottiConfig
+from biscotti_b200.ops import krum as krum_ops, ml
+from biscotti_b200.protocol.engine import BiscottiEngine
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _cfg(**kw):
+    base = dict(num_nodes=10, dataset="creditcard", max_iterations=3, shard_size=100, test_size=300)
+    base.update(kw)
+    return BiscottiConfig(**base)
+
+
+def test_derived_constants_match_reference_defaults():
+    c = BiscottiConfig(num_nodes=100, dataset="mnist")
+    assert c.dim == 7850 and c.total_shares == 21 and c.shares_per_miner == 7 and c.nchunk == 785
+    assert c.num_samples == 70 and c.krum_thresh == 70
+    c2 = BiscottiConfig(num_nodes=10)
+    assert c2.num_samples == 4                   # capped at N - nv - na (main.go:672-678)
+    assert abs(c.noise_sigma - math.sqrt(2 * math.log(1.25 / 1e-5)) / 2.0) < 1e-12
+
+
+def test_krum_cpu_matches_numpy_restatement():
+    torch.manual_seed(0)
+    X = torch.randn(12, 40)
+    X[3] += 8.0                                  # an outlier must be rejected
+    scores, acc, D = krum_ops.krum_reference(X, clip=6)
+    s2, a2, _ = krum_ops.krum(X, 40, 6)
+    assert torch.allclose(scores.float(), s2, rtol=1e-4, atol=1e-3)
+    assert a2.bool().tolist() == acc.tolist()
+    assert not acc[3] and int(acc.sum()) == 6
+
+
+def test_softmax_step_reference_matches_autograd():
+    torch.manual_seed(1)
+    P, B, F, C = 3, 10, 20, 4
+    w = torch.randn(C * F + C) * 0.1
+    X = torch.randn(P, B, F)
+    y = torch.randint(0, C, (P, B), dtype=torch.int32)
+    U, loss = ml.softmax_step_reference(w, X, y, C, clip=100.0)
+    for p in range(P):
+        wp = w.clone().requires_grad_(True)
+        logits = X[p] @ wp[:C * F].view(C, F).t() + wp[C * F:]
+        l = torch.nn.functional.cross_entropy(logits, y[p].long())
+        l.backward()
+        assert torch.allclose(U[p], -wp.grad, atol=1e-6)
+        assert abs(float(loss[p]) - float(l)) < 1e-5
+
+
+def test_ten_peer_creditcard_chain_runs_and_learns():
+    e = BiscottiEngine(_cfg(max_iterations=12))
+    reps = e.run()
+    assert len(reps) == 13 and len(e.chain) == 14        # genesis + (max_iterations + 1) blocks
+    assert e.chain.verify()
+    non_empty = [r for r in reps if not r.empty]
+    assert len(non_empty) >= 10
+    assert all(r.bad_shares == 0 for r in reps)
+    assert reps[-1].test_error < reps[0].test_error + 0.05
+    # stake: +5 per accepted contribution (honest.go:418-419)
+    assert sum(e.stake) == 10 * 10 + 5 * sum(r.n_contributors for r in reps)
+    assert "Iteration: 12, GlobalW: [" in e.print_chain()
+
+
+def test_same_seed_same_chain_different_seed_different_chain():
+    a = BiscottiEngine(_cfg())
+    b = BiscottiEngine(_cfg())
+    c = BiscottiEngine(_cfg(seed=2))
+    for e in (a, b, c):
+        e.run()
+    assert a.print_chain() == b.print_chain()
+    assert a.chain == b.chain and not (a.chain == c.chain)
+
+
+def test_options_plain_aggregation_no_noise_no_verification_roni():
+    for kw in (dict(secure_agg=False), dict(noising=False), dict(verification=False), dict(defense="RONI"),
+               dict(commitments=False), dict(random_sampling=True, perc_samples=40)):
+        e = BiscottiEngine(_cfg(max_iterations=2, **kw))
+        reps = e.run()
+        assert e.chain.verify() and len(reps) == 3
+        assert any(not r.empty for r in reps), kw
+
+
+def test_no_committee_or_dead_miners_mint_empty_blocks():
+    e = BiscottiEngine(_cfg(max_iterations=1))
+    e.alive = [False] * 10
+    e.alive[0] = True
+    r = e.step()
+    assert r.empty and len(e.chain) == 2
+    h_empty = e.chain.latest_hash()
+    f = BiscottiEngine(_cfg(max_iterations=1))
+    f.alive = [False] * 10
+    f.alive[0] = True
+    assert f.step().block_hash == h_empty          # empty blocks are byte-identical across peers
+
+
+def test_rejoin_adopts_longest_chain():
+    a = BiscottiEngine(_cfg(max_iterations=4))
+    a.run()
+    late = BiscottiEngine(_cfg(max_iterations=4))
+    assert late.adopt_chain(a.chain.serialize())
+    assert late.iteration == a.iteration and late.chain == a.chain
+    assert np.allclose(late.w64.numpy(), a.w64.numpy())
+    assert not late.adopt_chain(a.chain.serialize())   # not longer any more
+
+
+def test_localtest_cli_two_ranks_gloo_chain_equality():
+    """localTest.sh parity: N peers sharded over 2 processes (gloo); every rank must print the same chain,
+    and it must equal the single-process chain."""
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    single = subprocess.run([sys.executable, "-m", "biscotti_b200", "localtest", "10", "creditcard", "--iterations", "3",
+                             "--device", "cpu", "--shard-size", "100", "--print-hash"], capture_output=True, text=True,
+                            env=env, cwd=ROOT, timeout=600)
+    assert single.returncode == 0, single.stderr[-2000:]
+    multi = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                            "--master-addr", "127.0.0.1", "--master-port", "29631", "-m", "biscotti_b200", "localtest",
+                            "10", "creditcard", "--iterations", "3", "--device", "cpu", "--shard-size", "100",
+                            "--print-hash"], capture_output=True, text=True, env=env, cwd=ROOT, timeout=900)
+    assert multi.returncode == 0, multi.stderr[-3000:]
+    assert "SUCCESS! Nodes have same blockchain" in multi.stdout
+    h1 = [l for l in single.stdout.splitlines() if l.startswith("chain-hash")][0]
+    h2 = [l for l in multi.stdout.splitlines() if l.startswith("chain-hash")][0]
+    assert h1 == h2

@@ -1,0 +1,67 @@
+"""Ledger rules (DistSys/block.go, blockData.go, blockchain.go, honest.go:631-653)."""
+import numpy as np
+import pytest
+
+from biscotti_b200.ledger.chain import Blockchain, UpdateRecord, go_float
+
+
+def test_genesis_and_empty_blocks_are_identical_across_peers():
+    a, b = Blockchain(5), Blockchain(5)
+    assert len(a) == 1 and a.latest_iteration == -1
+    assert a.latest_hash() == b.latest_hash()
+    assert np.all(a.weights() == 0)
+    # empty blocks carry Timestamp 0 => every peer mints the same one (block.go:32-38)
+    ha = a.add_block(0, np.zeros(5), [], {0: 10})
+    hb = b.add_block(0, np.zeros(5), [], {0: 10})
+    assert ha == hb and a == b
+
+
+def test_hash_links_and_verify_and_tamper():
+    c = Blockchain(3)
+    u = UpdateRecord(source=2, iteration=0, commitment=bytes(range(64)), signatures=[b"s" * 64])
+    c.add_block(0, [0.1, -0.2, 0.3], [u], {0: 10, 2: 15}, timestamp=7)
+    c.add_block(1, [0.2, -0.1, 0.3], [], None)
+    assert c.verify()
+    assert c.prev_hash(2) == c.block_hash(1)
+    info = c.block_info(1)
+    assert info["iteration"] == 0 and info["timestamp"] == 7 and info["stake"] == {0: 10, 2: 15}
+    assert info["updates"][0]["source"] == 2 and info["updates"][0]["nsigs"] == 1
+    assert c.get_block_index(0) == 1 and c.get_block_index(5) == -1
+
+
+def test_serialize_round_trip_and_longest_chain():
+    c = Blockchain(4)
+    for it in range(3):
+        c.add_block(it, np.arange(4) * 0.5 + it, [UpdateRecord(1, it, b"\x01" * 64, delta=np.ones(4))], {1: 10 + 5 * it},
+                    timestamp=it + 1)
+    d = Blockchain.deserialize(c.serialize())
+    assert d == c and d.verify() and d.dump() == c.dump()
+    with pytest.raises(ValueError):
+        Blockchain.deserialize(b"garbage")
+
+
+def test_block_gossip_accept_and_better_block_replacement():
+    a, b = Blockchain(2), Blockchain(2)
+    a.add_block(0, [1.0, 2.0], [UpdateRecord(3, 0, b"\x02" * 64)], {3: 15}, timestamp=9)
+    assert b.accept_block(a.serialize_block(-1)) == 1          # appended
+    assert b.accept_block(a.serialize_block(-1)) == 0          # duplicate
+    assert a == b
+    # c minted an empty block for the same height; a non-empty one replaces it (honest.go:631-653)
+    c = Blockchain(2)
+    c.add_block(0, [0.0, 0.0], [], None)
+    assert c.accept_block(a.serialize_block(-1)) == 2
+    assert c == a
+    blk = bytearray(a.serialize_block(-1))
+    blk[-3] ^= 1
+    assert Blockchain(2).accept_block(bytes(blk)) < 0          # tampered payload: hash mismatch
+
+
+def test_print_chain_format_and_go_floats():
+    c = Blockchain(2)
+    c.add_block(0, [0.5, 1e6], [UpdateRecord(1, 0, b"\x00" * 64)], None, timestamp=1)
+    text = c.dump()
+    assert text.startswith("Prev. hash: \nData: Iteration: -1, GlobalW: [0,0], deltas: []\nHash: ")
+    assert "Iteration: 0, GlobalW: [0.5,1e+06]" in text
+    assert "Commitment:bn256.G1:(" in text
+    assert go_float(0.1) == "0.1" and go_float(123456789.0) == "1.23456789e+08"
+    assert go_float(1e-5) == "1e-05" and go_float(-2.5) == "-2.5" and go_float(100000.0) == "100000"
