@@ -1,0 +1,45 @@
+"""Protocol engine on the GPU: MNIST-shaped softmax peers, determinism, learning, poisoning defence."""
+import pytest
+import torch
+
+from biscotti_b200.config import BiscottiConfig
+from biscotti_b200.protocol.engine import BiscottiEngine
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(**kw):
+    base = dict(num_nodes=30, dataset="mnist", max_iterations=4, shard_size=100, test_size=500)
+    base.update(kw)
+    return BiscottiConfig(**base)
+
+
+def test_mnist_chain_on_gpu_is_deterministic_and_consistent(lib):
+    lib.bsc_launch_count_reset()
+    a = BiscottiEngine(_cfg(), device="cuda:0")
+    b = BiscottiEngine(_cfg(), device="cuda:0")
+    ra, rb = a.run(), b.run()
+    assert lib.bsc_launch_count() > 50
+    assert a.chain == b.chain and a.chain.verify()
+    assert all(r.bad_shares == 0 for r in ra)
+    assert any(not r.empty for r in ra)
+    assert a.print_chain() == b.print_chain()
+
+
+def test_mnist_learns_and_krum_rejects_poisoners():
+    cfg = _cfg(num_nodes=40, max_iterations=14, poison_fraction=0.3, epsilon=2.0)
+    e = BiscottiEngine(cfg, device="cuda:0")
+    reps = e.run()
+    assert reps[-1].test_error < 0.5 * reps[0].test_error + 0.05
+    assert reps[-1].attack_rate is not None
+    # poisoners' stake should lag honest peers' stake (they are rejected by Multi-Krum)
+    bad = sorted(e.poisoners)
+    good = [p for p in range(cfg.num_nodes) if p not in e.poisoners]
+    assert sum(e.stake[p] for p in bad) / len(bad) <= sum(e.stake[p] for p in good) / len(good)
+
+
+def test_fedsys_mode_on_gpu():
+    cfg = _cfg(mode="fedsys", perc_samples=35, max_iterations=6)
+    e = BiscottiEngine(cfg, device="cuda:0")
+    reps = e.run()
+    assert reps[-1].test_error < reps[0].test_error

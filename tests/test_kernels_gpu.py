@@ -1,0 +1,181 @@
+"""CUDA kernels vs plain PyTorch fp32 references / the bit-exact host mirrors.  Run on the B200 box."""
+import ctypes
+
+import pytest
+import torch
+
+from biscotti_b200.ops import ml, krum as krum_ops, secagg
+from biscotti_b200.ops.msm import CommitmentEngine
+from biscotti_b200.crypto import primitives as cp
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def test_native_library_is_loaded_and_counts_launches(lib):
+    lib.bsc_launch_count_reset()
+    ml.noise_row(64, 1, 2, 3, 1.0, device=DEV)
+    torch.cuda.synchronize()
+    assert lib.bsc_launch_count() == 1
+
+
+@pytest.mark.parametrize("P,B,F,C", [(7, 10, 784, 10), (3, 10, 20, 4), (2, 5, 8742, 2)])
+def test_softmax_step_matches_fp32_reference(P, B, F, C):
+    torch.manual_seed(0)
+    w = (torch.randn(C * F + C) * 0.05)
+    X = torch.randn(P, 32, F)
+    y = torch.randint(0, C, (P, 32), dtype=torch.int32)
+    idx = torch.stack([torch.randperm(32)[:B] for _ in range(P)]).int()
+    Xb = torch.gather(X, 1, idx.long().unsqueeze(-1).expand(P, B, F))
+    yb = torch.gather(y, 1, idx.long())
+    Uref, lref = ml.softmax_step_reference(w, Xb, yb, C, 100.0)
+    U, loss = ml.softmax_step(w.to(DEV), X.to(DEV), y.to(DEV), idx.to(DEV), C, 100.0)
+    assert torch.allclose(U.cpu(), Uref, rtol=1e-4, atol=1e-6)
+    assert torch.allclose(loss.cpu(), lref, rtol=1e-4, atol=1e-5)
+    # clipping active: scale gradients up through tiny clip
+    Uref2, _ = ml.softmax_step_reference(w, Xb, yb, C, 0.01)
+    U2, _ = ml.softmax_step(w.to(DEV), X.to(DEV), y.to(DEV), idx.to(DEV), C, 0.01)
+    assert torch.allclose(U2.cpu(), Uref2, rtol=1e-4, atol=1e-7)
+    assert abs(float(U2[0].norm()) - 0.01) < 1e-4
+
+
+def test_logistic_step_matches_reference():
+    torch.manual_seed(1)
+    P, B, F = 9, 10, 25
+    w = torch.randn(F) * 0.1
+    X = torch.randn(P, B, F)
+    y = torch.sign(torch.randn(P, B))
+    ref = ml.logistic_step_reference(w, X, y, 1e-2, 1e-2)
+    out = ml.logistic_step(w.to(DEV), X.to(DEV), y.to(DEV), None, 1e-2, 1e-2)
+    assert torch.allclose(out.cpu()[:, :F], ref, rtol=1e-4, atol=1e-7)
+
+
+def test_noise_rows_match_host_generator_and_are_gaussian():
+    d = 7850
+    g = ml.noise_row(d, 42, 5, 17, 1.0, device=DEV).cpu()
+    h = ml.noise_row(d, 42, 5, 17, 1.0, device="cpu")
+    assert torch.allclose(g, h, rtol=1e-4, atol=1e-4)
+    big = torch.cat([ml.noise_row(d, 42, p, 0, 1.0, device=DEV) for p in range(20)]).cpu()
+    assert abs(float(big.mean())) < 0.02 and abs(float(big.std()) - 1.0) < 0.02
+    assert not torch.equal(ml.noise_row(d, 42, 5, 18, 1.0, device=DEV).cpu(), g)
+
+
+def test_noise_mix_planes_and_norms():
+    torch.manual_seed(2)
+    P, d = 6, 1000
+    ldu = 1000
+    U = torch.randn(P, ldu) * 0.1
+    noisers = torch.tensor([[1, 2], [0, -1], [-1, -1], [3, 4], [5, 0], [2, 2]], dtype=torch.int32)
+    ref = ml.noise_mix(U, noisers, 9, 3, -0.5, d)
+    out = ml.noise_mix(U.to(DEV), noisers.to(DEV), 9, 3, -0.5, d)
+    assert torch.allclose(out[0].cpu(), ref[0], rtol=1e-4, atol=1e-5)
+    assert torch.allclose(out[3].cpu(), ref[3], rtol=1e-4, atol=1e-4)
+    rec = out[1].float() + out[2].float()
+    assert torch.allclose(rec[:, :d].cpu(), ref[0][:, :d], rtol=2e-5, atol=1e-6)     # bf16 hi+lo ~ 16 mantissa bits
+    assert float(out[1][:, d:].float().abs().sum()) == 0.0
+    assert torch.equal(out[0][2].cpu(), U[2])                                      # no noisers => untouched
+
+
+@pytest.mark.parametrize("n,d,ksplit", [(70, 7850, 8), (33, 257, 1), (140, 1000, 3)])
+def test_gram_simt_and_krum_select_match_reference(n, d, ksplit):
+    torch.manual_seed(3)
+    X = torch.randn(n, d) * 0.1
+    X[: n // 5] += 0.5                      # a poisoned cluster
+    Xd = X.to(DEV)
+    G = krum_ops.gram_simt(Xd, d, ksplit).sum(0).cpu()
+    assert torch.allclose(G, X @ X.t(), rtol=1e-4, atol=1e-3)
+    clip = n // 2
+    sref, aref, Dref = krum_ops.krum_reference(X, clip)
+    s, a, D = krum_ops.krum_select(krum_ops.gram_simt(Xd, d, ksplit), (Xd * Xd).sum(1), n, clip, want_D=True)
+    assert torch.allclose(D.cpu().double(), Dref, rtol=1e-3, atol=1e-2)
+    assert torch.allclose(s.cpu().double(), sref, rtol=1e-3, atol=1e-1)
+    assert a.cpu().bool().tolist() == aref.tolist()
+    assert int(a.sum()) == n - clip
+
+
+def test_secagg_kernels_match_host_mirrors():
+    torch.manual_seed(4)
+    P, d, S = 12, 7850, 21
+    U = torch.randn(P, 7852) * 0.05
+    Ud = U.to(DEV)
+    Q = secagg.quantize(Ud, d)
+    assert torch.equal(Q.cpu(), secagg.quantize(U, d))
+    Y = secagg.shares_eval(Q, S)
+    assert torch.equal(Y.cpu(), secagg.shares_eval(Q.cpu(), S))
+    sel = torch.tensor([0, 3, 4, 9, 11], dtype=torch.int32)
+    Ysum = secagg.share_sum(Ud, sel.to(DEV), d, S)
+    assert torch.equal(Ysum.cpu(), Y.cpu()[sel.long()].sum(0))
+    # reconstruct from non-contiguous shares (miner 1 of 3 missing) and apply the step
+    xs = torch.tensor([0, 1, 2, 3, 4, 5, 6, 14, 15, 16], dtype=torch.int32, device=DEV)
+    avail = torch.tensor([1] * 7 + [0] * 7 + [1] * 7, dtype=torch.uint8, device=DEV)
+    w64 = torch.zeros(d, dtype=torch.float64, device=DEV)
+    w32 = torch.zeros(d, device=DEV)
+    dsum, bad = secagg.reconstruct_step(Ysum, xs, avail, d, w64, w32, want_dsum=True)
+    assert int(bad.sum()) == 0
+    exp = Q.cpu()[sel.long()][:, :d].sum(0).double() / 1e4
+    assert torch.equal(w64.cpu(), exp) and torch.equal(dsum.cpu(), exp)
+    assert torch.equal(w32.cpu(), exp.float())
+    Ybad = Ysum.clone()
+    Ybad[5, 20] += 3
+    _, bad = secagg.reconstruct_step(Ybad, xs, avail, d, torch.zeros_like(w64), None)
+    assert int(bad[1]) == 1
+    # plain aggregation
+    w = torch.zeros(d, dtype=torch.float64, device=DEV)
+    secagg.plain_sum_step(Ud, sel.to(DEV), d, w, None)
+    assert torch.allclose(w.cpu(), U[sel.long()][:, :d].double().sum(0))
+
+
+def test_msm_kernels_match_host_mirror_bit_for_bit():
+    d, S = 57, 21
+    cpu = CommitmentEngine(d, S, tau=2, device="cpu")
+    gpu = CommitmentEngine(d, S, tau=2, device=DEV)
+    assert gpu.to_bytes(gpu.wtable) == cpu.to_bytes(cpu.wtable)
+    g = torch.Generator().manual_seed(5)
+    Q = torch.zeros(5, 60, dtype=torch.int64)
+    Q[:, :d] = torch.randint(-10**6, 10**6, (5, d), generator=g)
+    Q[1] = 0                                              # all-zero update -> infinity everywhere
+    Q[2, 3] = -(2**40)                                    # a large negative scalar
+    Cc, Cg = cpu.chunk_commitments(Q), gpu.chunk_commitments(Q.to(DEV))
+    assert gpu.to_bytes(Cg) == cpu.to_bytes(Cc)
+    assert gpu.to_bytes(gpu.full_commitments(Cg)) == cpu.to_bytes(cpu.full_commitments(Cc))
+    Wc, Wg = cpu.witnesses(Q), gpu.witnesses(Q.to(DEV))
+    assert gpu.to_bytes(Wg) == cpu.to_bytes(Wc)
+    sel = torch.tensor([0, 2, 4], dtype=torch.int32)
+    assert gpu.to_bytes(gpu.aggregate(Wg, sel.to(DEV))) == cpu.to_bytes(cpu.aggregate(Wc, sel))
+    # random-tau SRS generated on the device equals the host one
+    cpu_r = CommitmentEngine(20, S, tau=987654321, device="cpu")
+    gpu_r = CommitmentEngine(20, S, tau=987654321, device=DEV)
+    assert cpu_r.srs_bytes == gpu_r.srs_bytes
+
+
+def test_batched_vrf_and_sha256_on_device(lib):
+    import hashlib
+
+    keys = [cp.VRFKey(hashlib.sha256(bytes([i])).digest()) for i in range(9)]
+    msg = hashlib.sha256(b"blk").digest()
+    assert cp.BatchedVRF(keys, DEV).outputs(msg) == [k.prove(msg)[0] for k in keys]
+    msgs = torch.randint(0, 256, (50, 100), dtype=torch.uint8)
+    out = torch.empty(50, 32, dtype=torch.uint8, device=DEV)
+    md = msgs.to(DEV)
+    rc = lib.bsc_sha256_batch(ctypes.c_void_p(md.data_ptr()), 100, 100, 50, ctypes.c_void_p(out.data_ptr()),
+                              ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    for i in (0, 17, 49):
+        assert bytes(out[i].cpu().tolist()) == hashlib.sha256(bytes(msgs[i].tolist())).digest()
+
+
+def test_eval_kernels():
+    torch.manual_seed(6)
+    N, F, C, M = 300, 784, 10, 4
+    X = torch.randn(N, F)
+    y = torch.randint(0, C, (N,), dtype=torch.int32)
+    Wc = torch.randn(M, C * F + C) * 0.1
+    base = torch.randn(C * F + C) * 0.1
+    ref = ml.eval_softmax_errors(Wc, base, X, y, C)
+    out = ml.eval_softmax_errors(Wc.to(DEV), base.to(DEV), X.to(DEV), y.to(DEV), C)
+    assert torch.allclose(out.cpu(), ref, atol=2.0 / N)
+    Xl = torch.randn(N, 25)
+    yl = torch.sign(torch.randn(N))
+    Wl = torch.randn(M, 25)
+    assert torch.allclose(ml.eval_logistic_errors(Wl.to(DEV), None, Xl.to(DEV), yl.to(DEV)).cpu(),
+                          ml.eval_logistic_errors(Wl, None, Xl, yl), atol=2.0 / N)
