@@ -136,6 +136,52 @@ class BatchedVRF:
             return gam
         return self.finish(gam, msg)
 
+    # ---- asynchronous form used by the engine: launch on a side stream at the top of a block, collect
+    # the noiser committees (one native call) when the noise phase needs them.
+    def launch(self, msg: bytes):
+        L = _L()
+        n = len(self.keys)
+        hpt = torch.empty(32, dtype=torch.int32)
+        L.bsc_vrf_hash_to_curve(msg, len(msg), ctypes.c_void_p(hpt.data_ptr()), None)
+        if self.device.type != "cuda":
+            gam = torch.empty(n, 32, dtype=torch.uint8)
+            L.bsc_ed25519_scalarmult_batch_host(ctypes.c_void_p(self.scalars.data_ptr()),
+                                                ctypes.c_void_p(hpt.data_ptr()), 1, n, ctypes.c_void_p(gam.data_ptr()))
+            return (gam, None, msg)
+        if not hasattr(self, "_side"):
+            self._side = torch.cuda.Stream(self.device)
+            self._host_gam = torch.empty(n, 32, dtype=torch.uint8).pin_memory()
+            self._hpt_pinned = torch.empty(32, dtype=torch.int32).pin_memory()
+            self._hd = torch.empty(32, dtype=torch.int32, device=self.device)
+            self._gam = torch.empty(n, 32, dtype=torch.uint8, device=self.device)
+        self._hpt_pinned.copy_(hpt)
+        self._side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self._side):
+            self._hd.copy_(self._hpt_pinned, non_blocking=True)
+            rc = L.bsc_ed25519_scalarmult_batch(ctypes.c_void_p(self.scalars.data_ptr()),
+                                                ctypes.c_void_p(self._hd.data_ptr()), 1, n,
+                                                ctypes.c_void_p(self._gam.data_ptr()),
+                                                ctypes.c_void_p(self._side.cuda_stream))
+            if rc:
+                raise RuntimeError("ed25519_scalarmult_batch failed")
+            self._host_gam.copy_(self._gam, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+        return (self._host_gam, ev, msg)
+
+    def noiser_table(self, handle, stake: list[int], is_worker: np.ndarray, want: int) -> np.ndarray:
+        """[n, want] int32 table of noiser ids (-1 = none) for every worker (vrf.go:54-100)."""
+        gam, ev, msg = handle
+        if ev is not None:
+            ev.synchronize()
+        n = len(self.keys)
+        out = np.full((n, max(1, want)), -1, dtype=np.int32)
+        st = np.asarray(stake, dtype=np.int32)
+        iw = np.ascontiguousarray(is_worker, dtype=np.uint8)
+        _L().bsc_noisers_batch(ctypes.c_void_p(gam.data_ptr()), msg, len(msg), st.ctypes.data_as(ctypes.c_void_p), n,
+                               iw.ctypes.data_as(ctypes.c_void_p), want, out.ctypes.data_as(ctypes.c_void_p), None)
+        return out
+
     def finish(self, gam: torch.Tensor, msg: bytes):
         L = _L()
         raw = gam.cpu().numpy().tobytes()

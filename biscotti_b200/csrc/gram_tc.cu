@@ -1,0 +1,295 @@
+// Krum Gram matrix on the 5th-generation tensor cores: tcgen05.mma with TMEM accumulators, operands
+// staged by TMA (cp.async.bulk.tensor) into 128B-swizzled shared memory, warp-specialised
+// producer / MMA-issuer / epilogue roles, split-K over CTAs with a deterministic fixed-order
+// reduction in krum_select_kernel.
+//
+// What it computes (ML/Pytorch/client_obj.py:132-143, the np.dot(X, X.T) inside get_krum_scores):
+//   G = U U^T for the noised updates U [n, d].  U arrives as two bf16 planes (hi = bf16(u),
+//   lo = bf16(u - hi), written by noise_mix_kernel) and the product is formed as
+//   hi*hi^T + hi*lo^T + lo*hi^T with fp32 accumulation in TMEM ("bf16x3"), which keeps ~16 mantissa
+//   bits per factor: Krum ranks peers by small differences of ||a||^2 + ||b||^2 - 2 a.b, plain bf16
+//   would not survive the cancellation.
+//
+// Tiling: 128x128 output tile per CTA (UMMA M=128, N=128, K=16), BLOCK_K = 64 bf16 = one 128-byte
+// swizzle atom, 3-stage mbarrier ring.  Only tiles with ti <= tj are computed; the epilogue also
+// writes the mirrored tile.  Diagonal tiles reuse the A operand tiles as B (half the traffic — the
+// whole problem for n <= 128, i.e. the 100-peer headline configuration).
+#include "common.cuh"
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+namespace bsc {
+
+constexpr int GT_BM = 128;
+constexpr int GT_BK = 64;
+constexpr int GT_STAGES = 3;
+constexpr int GT_TILE_BYTES = GT_BM * GT_BK * 2;  // 16 KiB: 128 rows x 128 B
+constexpr int GT_STAGE_BYTES = 4 * GT_TILE_BYTES;
+constexpr int GT_THREADS = 192;                   // warp0 TMA, warp1 MMA+TMEM, warps 2-5 epilogue
+constexpr int GT_TMEM_COLS = 128;
+constexpr size_t GT_SMEM = (size_t)GT_STAGES * GT_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  for (uint32_t spin = 0; !mbar_try_wait(bar, parity); spin++) {
+    if (spin > (1u << 24)) {
+      printf("[biscotti_b200] gram_tc: mbarrier wait timed out (block %d,%d thread %d)\n", blockIdx.x, blockIdx.y,
+             threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"((uint64_t)map), "r"(x), "r"(y), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// K-major operand, 128-byte swizzle, rows of 128 B, 8-row groups 1024 B apart (SBO).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);        // start address
+  d |= (uint64_t)1 << 16;                            // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset
+  d |= (uint64_t)1 << 46;                            // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                            // layout: SWIZZLE_128B
+  return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, N=128, M=128
+__device__ __forceinline__ uint32_t umma_idesc_bf16_128x128() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+//   tm_hi / tm_lo : 2-D tensor maps over the bf16 planes, dims (ldh, rows), box (64, 128), SWIZZLE_128B
+//   Gpart         : [gridDim.y][ldg][ldg] fp32, ldg = ntile*128
+//   kb_total      : number of 64-wide k-blocks ; kb_per : k-blocks per split (gridDim.y * kb_per >= kb_total)
+__global__ void __launch_bounds__(GT_THREADS, 1)
+    gram_tc_kernel(const __grid_constant__ CUtensorMap tm_hi, const __grid_constant__ CUtensorMap tm_lo,
+                   float* __restrict__ Gpart, int ldg, int ntile, int kb_total, int kb_per) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;              // SWIZZLE_128B needs 1024-B alignment
+  const uint32_t bars = tiles + GT_STAGES * GT_STAGE_BYTES;   // full[3], empty[3], tmem_full, tmem slot
+  const uint32_t bar_full = bars, bar_empty = bars + 8 * GT_STAGES, bar_tmem = bars + 16 * GT_STAGES;
+  const uint32_t tmem_slot = bar_tmem + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // decode the upper-triangular tile pair
+  int ti = 0, tj = 0;
+  {
+    int p = blockIdx.x;
+    for (ti = 0; ti < ntile; ti++) {
+      const int rowlen = ntile - ti;
+      if (p < rowlen) {
+        tj = ti + p;
+        break;
+      }
+      p -= rowlen;
+    }
+  }
+  const bool diag = (ti == tj);
+  const int split = blockIdx.y;
+  const int kb0 = split * kb_per;
+  const int nkb = min(kb_total, kb0 + kb_per) - kb0;   // host guarantees nkb >= 1
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < GT_STAGES; s++) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    mbar_init(bar_tmem, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(GT_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int kb = 0; kb < nkb; kb++) {
+        const int s = kb % GT_STAGES;
+        const uint32_t ph = (uint32_t)(kb / GT_STAGES) & 1u;
+        mbar_wait(bar_empty + 8 * s, ph ^ 1u);
+        const uint32_t st = tiles + s * GT_STAGE_BYTES;
+        mbar_expect_tx(bar_full + 8 * s, diag ? 2 * GT_TILE_BYTES : 4 * GT_TILE_BYTES);
+        const int kx = (kb0 + kb) * GT_BK;
+        tma_load_2d(st, &tm_hi, kx, ti * GT_BM, bar_full + 8 * s);
+        tma_load_2d(st + GT_TILE_BYTES, &tm_lo, kx, ti * GT_BM, bar_full + 8 * s);
+        if (!diag) {
+          tma_load_2d(st + 2 * GT_TILE_BYTES, &tm_hi, kx, tj * GT_BM, bar_full + 8 * s);
+          tma_load_2d(st + 3 * GT_TILE_BYTES, &tm_lo, kx, tj * GT_BM, bar_full + 8 * s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16_128x128();
+      for (int kb = 0; kb < nkb; kb++) {
+        const int s = kb % GT_STAGES;
+        const uint32_t ph = (uint32_t)(kb / GT_STAGES) & 1u;
+        mbar_wait(bar_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t st = tiles + s * GT_STAGE_BYTES;
+        const uint64_t a_hi = umma_desc_sw128(st), a_lo = umma_desc_sw128(st + GT_TILE_BYTES);
+        const uint64_t b_hi = diag ? a_hi : umma_desc_sw128(st + 2 * GT_TILE_BYTES);
+        const uint64_t b_lo = diag ? a_lo : umma_desc_sw128(st + 3 * GT_TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < GT_BK / 16; k++) {
+          const uint64_t off = (uint64_t)((k * 16 * 2) >> 4);   // advance 32 B inside the swizzle atom
+          umma_bf16(tmem_base, a_hi + off, b_hi + off, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_bf16(tmem_base, a_hi + off, b_lo + off, idesc, 1u);
+          umma_bf16(tmem_base, a_lo + off, b_hi + off, idesc, 1u);
+        }
+        umma_commit(bar_empty + 8 * s);   // frees the smem stage once these MMAs have read it
+      }
+      umma_commit(bar_tmem);              // accumulator complete
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> global (direct + mirrored tile) =====
+    const int q = warp & 3;               // TMEM lane quarter this warp may touch
+    mbar_wait(bar_tmem, 0);
+    tc_fence_after();
+    float* G = Gpart + (size_t)split * ldg * ldg;
+    const int row = ti * GT_BM + q * 32 + lane;
+#pragma unroll 1
+    for (int cc = 0; cc < GT_BM / 32; cc++) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(cc * 32), v);
+      const int col0 = tj * GT_BM + cc * 32;
+      float4* dst = reinterpret_cast<float4*>(G + (size_t)row * ldg + col0);
+#pragma unroll
+      for (int c = 0; c < 8; c++)
+        dst[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
+                             __uint_as_float(v[4 * c + 3]));
+      if (!diag) {
+#pragma unroll
+        for (int c = 0; c < 32; c++) G[(size_t)(col0 + c) * ldg + row] = __uint_as_float(v[c]);   // coalesced over lanes
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(GT_TMEM_COLS) : "memory");
+  }
+}
+
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_tmapEncodeTiled get_encode() {
+  static PFN_tmapEncodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = (PFN_tmapEncodeTiled)p;
+  }
+  return fn;
+}
+
+// bf16 [rows][ld] row-major plane -> tensor map with a (64 x box_rows) box, 128-byte swizzle, zero OOB fill
+int make_plane_map(CUtensorMap* map, const void* base, int rows, int ld, int box_rows) {
+  PFN_tmapEncodeTiled enc = get_encode();
+  if (!enc) return -2;
+  cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)GT_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+// G partials of hi/lo planes [rows][ldh] (ldh % 64 == 0, 16-byte aligned base), first n rows valid.
+// Gpart: [ksplit][ldg][ldg] with ldg = ceil(n/128)*128; every split must own >= 1 k-block.
+int bsc_gram_tc(const void* hi, const void* lo, int n, int rows, int ldh, int ksplit, float* Gpart, int ldg,
+                void* stream) {
+  if (ldh % GT_BK != 0 || n < 1 || ksplit < 1) return -1;
+  const int ntile = (n + GT_BM - 1) / GT_BM;
+  if (ldg != ntile * GT_BM) return -1;
+  const int kb_total = ldh / GT_BK;
+  const int kb_per = (kb_total + ksplit - 1) / ksplit;
+  if ((ksplit - 1) * kb_per >= kb_total) return -4;   // an empty split would leave its partial unwritten
+  CUtensorMap mh, ml;
+  int rc = make_plane_map(&mh, hi, rows, ldh, GT_BM);
+  if (rc) return rc;
+  rc = make_plane_map(&ml, lo, rows, ldh, GT_BM);
+  if (rc) return rc;
+  static bool configured = false;
+  if (!configured) {
+    BSC_CHECK(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GT_SMEM));
+    configured = true;
+  }
+  dim3 grid(ntile * (ntile + 1) / 2, ksplit);
+  gram_tc_kernel<<<grid, GT_THREADS, GT_SMEM, (cudaStream_t)stream>>>(mh, ml, Gpart, ldg, ntile, kb_total, kb_per);
+  return finish_launch("gram_tc");
+}
+
+}  // extern "C"

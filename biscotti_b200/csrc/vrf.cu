@@ -238,6 +238,22 @@ int bsc_vrf_verify(const uint8_t pk[32], const uint8_t* m, size_t n, const uint8
   return memcmp(out, vrf, 32) == 0 ? 1 : 0;
 }
 
+int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n, int source, int want, int* noisers);
+
+// All workers' noiser committees in one call: output_p = SHAKE256(Gamma_p || m)[:32], then the stake
+// lottery of vrf.go:54-100 seeded by output_p with p itself excluded.  out[p*want + j] = noiser id or -1.
+void bsc_noisers_batch(const uint8_t* gammas, const uint8_t* m, size_t mlen, const int* stake, int n,
+                       const uint8_t* is_worker, int want, int* out, uint8_t* vrf_out) {
+  for (int p = 0; p < n; p++) {
+    for (int j = 0; j < want; j++) out[(size_t)p * want + j] = -1;
+    uint8_t o[32];
+    bsc_vrf_output_from_gamma(gammas + 32 * (size_t)p, m, mlen, o);
+    if (vrf_out) memcpy(vrf_out + 32 * (size_t)p, o, 32);
+    if (is_worker && !is_worker[p]) continue;
+    bsc_lottery_noisers(o, 32, stake, n, p, want, out + (size_t)p * want);
+  }
+}
+
 // device: gamma[i] = compress(x[i] * H) for all peers
 int bsc_ed25519_scalarmult_batch(const void* scalars_u256, const void* bases, int nbase, int N, unsigned char* out,
                                  void* stream) {

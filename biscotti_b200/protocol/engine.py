@@ -131,12 +131,16 @@ class BiscottiEngine:
     def sample_minibatch(self, n_local: int):
         """Random minibatch without replacement per peer (logistic_model.py:121-125, DataLoader shuffle)."""
         Ns, B = self.cfg.shard_size, self.cfg.batch_size
-        rows = []
-        for p in (self.local_ids or [0]):
-            # seeded per (seed, iteration, peer) so the draw does not depend on how peers are sharded
-            rs = np.random.RandomState((self.cfg.seed * 1000003 + self.iteration * 7919 + p * 104729) % (2**31))
-            rows.append(rs.choice(Ns, size=B, replace=False))
-        return torch.from_numpy(np.stack(rows).astype(np.int32))
+        n = self.cfg.num_nodes
+        # One seeded draw for ALL n peers (so the result does not depend on how peers are sharded over
+        # ranks), generated on the engine's device; each rank keeps the rows of its own peers.
+        if not hasattr(self, "_mb_gen"):
+            self._mb_gen = torch.Generator(device=self.device)
+        self._mb_gen.manual_seed((self.cfg.seed * 1000003 + self.iteration * 7919) % (2**62))
+        keys = torch.rand(n, Ns, generator=self._mb_gen, device=self.device)
+        idx = keys.topk(B, dim=1, largest=False).indices.int()
+        lo = self.local_ids[0] if self.local_ids else 0
+        return idx[lo: lo + max(1, self.P)].contiguous()
 
     # ------------------------------------------------------------------------------------------
     def step(self, inputs=None) -> BlockReport:
@@ -166,6 +170,11 @@ class BiscottiEngine:
         if not verifiers or not miners or not workers:
             return self._finish_block(rep, [], None, phases, t0)   # main.go:1696-1707, 1934-1944
 
+        # VRF evaluation of every peer on the previous block hash runs on a side stream, overlapped with
+        # the local step and the commitment MSM; the noise phase collects it.
+        use_noise = cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0
+        vrf_handle = self.vrf.launch(prev_hash) if use_noise else None
+
         # ---- 2. local step for my workers (all local rows are computed; non-workers are ignored)
         with self._phase("local_step"):
             if inputs is not None:
@@ -193,17 +202,19 @@ class BiscottiEngine:
         with self._phase("noise"):
             noiser_tab = torch.full((max(1, self.P), max(1, cfg.num_noisers)), -1, dtype=torch.int32)
             noisers_of = {}
-            if cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
-                outs = self.vrf.outputs(prev_hash)
+            if use_noise:
                 stake = [s if a else 0 for s, a in zip(self.stake, self.alive)]
-                for p in workers:
-                    nz = cp.lottery_noisers(outs[p], stake, p, cfg.num_noisers)
-                    noisers_of[p] = nz
-                    if p in self.local_index:
-                        for j, q in enumerate(nz):
-                            noiser_tab[self.local_index[p], j] = q
-            scale = cfg.noise_scale if (cfg.noising and cfg.epsilon > 0) else 0.0
-            Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab.to(dev), cfg.seed, slot, scale, self.d, ldh=self.ldh)
+                is_worker = np.zeros(n, dtype=np.uint8)
+                is_worker[workers] = 1
+                full_tab = self.vrf.noiser_table(vrf_handle, stake, is_worker, cfg.num_noisers)   # [n, nn]
+                if self.P:
+                    lo_id = self.local_ids[0]
+                    noiser_tab = torch.from_numpy(full_tab[lo_id: lo_id + self.P].copy())
+                if self.colluder_ids:
+                    noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
+            scale = cfg.noise_scale if use_noise else 0.0
+            Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab.to(dev, non_blocking=True), cfg.seed, slot, scale, self.d,
+                                             ldh=self.ldh)
 
         # ---- 5. verification
         arrival = self._arrival_order(workers, "verify")

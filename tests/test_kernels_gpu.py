@@ -179,3 +179,31 @@ def test_eval_kernels():
     Wl = torch.randn(M, 25)
     assert torch.allclose(ml.eval_logistic_errors(Wl.to(DEV), None, Xl.to(DEV), yl.to(DEV)).cpu(),
                           ml.eval_logistic_errors(Wl, None, Xl, yl), atol=2.0 / N)
+
+
+@pytest.mark.parametrize("n,d,ksplit", [(100, 7850, 16), (70, 7850, None), (128, 64, 1), (200, 1000, 4), (300, 2500, 5)])
+def test_gram_tcgen05_matches_fp32_reference(n, d, ksplit):
+    """tcgen05/TMA Gram kernel (bf16x3 split, fp32 TMEM accumulation) vs an fp64 reference of the same
+    product; the dropped lo*lo term bounds the relative error by ~2^-16."""
+    from biscotti_b200.ops import gram_tc
+
+    torch.manual_seed(7)
+    U = torch.randn(n, ml.pad_to(d, 4)) * 0.1
+    U[:, d:] = 0
+    noisers = torch.full((n, 1), -1, dtype=torch.int32)
+    Un, hi, lo, norms = ml.noise_mix(U.to(DEV), noisers.to(DEV), 1, 0, 0.0, d)
+    if ksplit is None:
+        ksplit = gram_tc.ksplit_for(n, hi.shape[1])
+    Gp = gram_tc.gram_tc(hi, lo, n, ksplit)
+    torch.cuda.synchronize()
+    G = Gp.sum(0)[:n, :n].double().cpu()
+    X = U[:, :d].double()
+    ref = X @ X.t()
+    scale = float(ref.diagonal().mean())
+    assert torch.allclose(G, ref, rtol=0, atol=3e-5 * scale), float((G - ref).abs().max() / scale)
+    assert torch.equal(G, G.t())                               # mirrored tiles are exact copies
+    # end to end through krum(): same accept set as the fp64 restatement
+    clip = n // 2
+    _, aref, _ = krum_ops.krum_reference(U[:, :d], clip)
+    _, a, _ = krum_ops.krum(Un, d, clip, hi, lo, norms, impl="tcgen05")
+    assert a.cpu().bool().tolist() == aref.tolist()
