@@ -50,6 +50,96 @@ __global__ void __launch_bounds__(128) msm_groups_kernel(const long long* __rest
   if (live) out[(size_t)p * ostride_p + (og ? og[g] : g)] = acc;
 }
 
+// ---- fixed-base window tables ----------------------------------------------------------------------
+// Every base of the commitment / witness MSMs is fixed for the life of a run (SRS points and the
+// witness base table), so the doubling chain can be paid once: table[b][i][k-1] = k * 2^(w*i) * B_b for
+// k = 1..2^(w-1).  A scalar is recoded into NW signed w-bit digits and each term costs NW mixed
+// additions and no doublings.  With w = 7, NW = 3 (|scalar| < 2^20, the clipped fixed-point range)
+// a 9-term witness drops from ~20 doublings + ~90 additions to 27 additions.
+HD int64_t table_max_mag(int w, int nw) { return (int64_t)1 << (w * nw - 1); }
+
+// one thread per (base, window): emits the 2^(w-1) multiples as Jacobian points (normalised afterwards)
+__global__ void __launch_bounds__(128) msm_table_build_kernel(const G1Affine* __restrict__ bases, long long nb, int w,
+                                                              int nw, G1Jac* __restrict__ out) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nb * nw) return;
+  const long long b = t / nw;
+  const int i = (int)(t % nw);
+  const int H = 1 << (w - 1);
+  G1Jac J = g1j_from_affine(bases[b]);
+  for (int k = 0; k < w * i; k++) J = g1j_dbl(J);
+  G1Jac acc = J;
+  G1Jac* dst = out + (size_t)t * H;
+  dst[0] = acc;
+  for (int k = 1; k < H; k++) {
+    acc = g1j_add(acc, J);
+    dst[k] = acc;
+  }
+}
+
+template <int TMAX>
+HDN inline G1Jac g1_table_msm(const G1Affine* __restrict__ table, long long first_base, const int64_t* s, int T, int w,
+                              int nw) {
+  const int H = 1 << (w - 1);
+  const uint64_t mask = ((uint64_t)1 << w) - 1;
+  const uint64_t lim = (uint64_t)table_max_mag(w, nw);
+  bool overflow = false;
+  for (int t = 0; t < T; t++) {
+    const uint64_t m = s[t] < 0 ? (uint64_t)0 - (uint64_t)s[t] : (uint64_t)s[t];
+    overflow = overflow || (m >= lim);
+  }
+  if (overflow) {
+    // rare: a scalar outside the table range -> interleaved double-and-add over the k=1 entries
+    G1Affine b[TMAX];
+    uint64_t maxmag = 0;
+    for (int t = 0; t < T; t++) {
+      b[t] = table[((size_t)(first_base + t) * nw) * H];
+      maxmag |= s[t] < 0 ? (uint64_t)0 - (uint64_t)s[t] : (uint64_t)s[t];
+    }
+    int nbits = 0;
+    while (nbits < 64 && (maxmag >> nbits)) nbits++;
+    return g1_straus_i64<TMAX>(b, s, T, nbits);
+  }
+  G1Jac acc = g1j_inf();
+  for (int t = 0; t < T; t++) {
+    const bool neg = s[t] < 0;
+    uint64_t m = neg ? (uint64_t)0 - (uint64_t)s[t] : (uint64_t)s[t];
+    const G1Affine* tb = table + ((size_t)(first_base + t) * nw) * H;
+    for (int i = 0; i < nw && m != 0; i++) {
+      uint64_t dgt = m & mask;
+      m >>= w;
+      bool dneg = neg;
+      if (dgt > (uint64_t)H) {
+        dgt = ((uint64_t)1 << w) - dgt;
+        dneg = !neg;
+        m += 1;
+      }
+      if (dgt) {
+        G1Affine pt = tb[(size_t)i * H + (dgt - 1)];
+        if (dneg) pt.y = fe_neg(pt.y);
+        acc = g1j_add_affine(acc, pt);
+      }
+    }
+  }
+  return acc;
+}
+
+// same indexing contract as msm_groups_kernel, bases replaced by their window tables
+__global__ void __launch_bounds__(128) msm_table_kernel(const long long* __restrict__ Q, int ldq,
+                                                        const int* __restrict__ sel, int P,
+                                                        const int* __restrict__ sidx, const int* __restrict__ bidx,
+                                                        const int* __restrict__ og, int G, int T,
+                                                        const G1Affine* __restrict__ table, int w, int nw,
+                                                        G1Jac* __restrict__ out, long long ostride_p) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)G * P) return;
+  const int g = (int)(i / P), p = (int)(i % P);
+  const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
+  int64_t s[MSM_TMAX];
+  for (int t = 0; t < T; t++) s[t] = row[t];
+  out[(size_t)p * ostride_p + (og ? og[g] : g)] = g1_table_msm<MSM_TMAX>(table, bidx[g], s, T, w, nw);
+}
+
 // k_i * B for full 256-bit scalars (SRS generation: PKG1[i] = tau^i * G, DistSys/publicKey.go:28-66)
 __global__ void g1_fixed_base_mul_kernel(const U256* __restrict__ k, int N, G1Affine base, G1Jac* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -136,6 +226,51 @@ int bsc_msm_groups(const long long* Q, int ldq, const int* sel, int P, const int
   msm_groups_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
       Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)bases_affine, (G1Jac*)out_jac, ostride_p);
   return finish_launch("msm_groups");
+}
+
+int bsc_msm_table_build(const void* bases_affine, long long nb, int w, int nw, void* out_jac, void* stream) {
+  if (w < 2 || w > 12 || nw < 1) return -1;
+  const long long n = nb * nw;
+  if (n == 0) return 0;
+  msm_table_build_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)bases_affine,
+                                                                                       nb, w, nw, (G1Jac*)out_jac);
+  return finish_launch("msm_table_build");
+}
+void bsc_msm_table_build_host(const void* bases_affine, long long nb, int w, int nw, void* out_jac) {
+  const G1Affine* bases = (const G1Affine*)bases_affine;
+  G1Jac* out = (G1Jac*)out_jac;
+  const int H = 1 << (w - 1);
+  for (long long t = 0; t < nb * nw; t++) {
+    G1Jac J = g1j_from_affine(bases[t / nw]);
+    for (int k = 0; k < w * (int)(t % nw); k++) J = g1j_dbl(J);
+    G1Jac acc = J;
+    out[(size_t)t * H] = acc;
+    for (int k = 1; k < H; k++) {
+      acc = g1j_add(acc, J);
+      out[(size_t)t * H + k] = acc;
+    }
+  }
+}
+int bsc_msm_table(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og,
+                  int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p,
+                  void* stream) {
+  if (T > MSM_TMAX) return -1;
+  const long long n = (long long)G * P;
+  if (n == 0) return 0;
+  msm_table_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+  return finish_launch("msm_table");
+}
+void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx,
+                        const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac,
+                        long long ostride_p) {
+  G1Jac* out = (G1Jac*)out_jac;
+  for (int g = 0; g < G; g++)
+    for (int p = 0; p < P; p++) {
+      const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
+      out[(size_t)p * ostride_p + (og ? og[g] : g)] =
+          g1_table_msm<MSM_TMAX>((const G1Affine*)table_affine, bidx[g], (const int64_t*)row, T, w, nw);
+    }
 }
 
 int bsc_g1_fixed_base_mul(const void* scalars_u256, int N, const void* base_affine, void* out_jac, void* stream) {

@@ -28,7 +28,8 @@ def _i32(x, device):
 class CommitmentEngine:
     """Holds the SRS and the witness base table for one model dimension and runs the MSM kernels."""
 
-    def __init__(self, d: int, total_shares: int, tau: int = 2, device="cpu", srs_bytes: bytes | None = None):
+    def __init__(self, d: int, total_shares: int, tau: int = 2, device="cpu", srs_bytes: bytes | None = None,
+                 window: int | None = None, max_scalar_bits: int = 20, table_budget_bytes: int = 48 << 30):
         self.d, self.S, self.device = d, total_shares, torch.device(device)
         self.nchunk = nchunks(d)
         self.dpad = self.nchunk * POLY_SIZE
@@ -53,6 +54,21 @@ class CommitmentEngine:
         self.w_sidx = ((cs // S) * POLY_SIZE + 1).to(self.device)          # a_1..a_9 of the chunk
         self.w_bidx = (cs * (POLY_SIZE - 1)).to(self.device)               # T[c, s, 0..8]
         self.wtable = self._build_witness_table()
+        # ---- fixed-base window tables (device path; window=0 disables them)
+        self.w = self.nw = 0
+        self.c_table = self.w_table = None
+        if window is None:
+            window = 7 if self.device.type == "cuda" else 0
+        if window:
+            nbases = self.dpad + self.wtable.shape[0]
+            while window > 2:
+                nw = -(-(max_scalar_bits + 1) // window)
+                if nbases * nw * (1 << (window - 1)) * 64 <= table_budget_bytes:
+                    break
+                window -= 1
+            self.w, self.nw = window, -(-(max_scalar_bits + 1) // window)
+            self.c_table = self._build_window_table(self.bases)
+            self.w_table = self._build_window_table(self.wtable)
 
     # -- SRS ------------------------------------------------------------------------------------
     def _generate_srs(self, tau: int) -> bytes:
@@ -94,7 +110,38 @@ class CommitmentEngine:
                         self.bases, ostride=T, nout=self.nchunk * S * T)
         return self.normalize(out)
 
+    def _build_window_table(self, bases_aff: torch.Tensor) -> torch.Tensor:
+        """table[b][i][k-1] = k * 2^(w*i) * B_b (affine), built in chunks to bound the Jacobian scratch."""
+        L = lib()
+        nb = bases_aff.shape[0]
+        H = 1 << (self.w - 1)
+        per = self.nw * H
+        table = torch.empty(nb * per, AFF, dtype=torch.int32, device=self.device)
+        chunk = max(1, (1 << 22) // per)
+        for b0 in range(0, nb, chunk):
+            b1 = min(nb, b0 + chunk)
+            jac = torch.empty((b1 - b0) * per, JAC, dtype=torch.int32, device=self.device)
+            src = bases_aff[b0:b1].contiguous()
+            if self.device.type == "cuda":
+                check(L.bsc_msm_table_build(ptr(src), b1 - b0, self.w, self.nw, ptr(jac), stream(self.device)),
+                      "msm_table_build")
+            else:
+                L.bsc_msm_table_build_host(ptr(src), b1 - b0, self.w, self.nw, ptr(jac))
+            table[b0 * per: b1 * per] = self.normalize(jac)
+        return table
+
     # -- raw kernels -----------------------------------------------------------------------------
+    def _msm_table(self, Q, sel, P, sidx, bidx, og, G, T, table, ostride, nout):
+        out = torch.empty(nout, JAC, dtype=torch.int32, device=self.device)
+        L = lib()
+        if self.device.type == "cuda":
+            check(L.bsc_msm_table(ptr(Q), Q.stride(0), ptr(sel), P, ptr(sidx), ptr(bidx), ptr(og), G, T, ptr(table),
+                                  self.w, self.nw, ptr(out), ostride, stream(self.device)), "msm_table")
+        else:
+            L.bsc_msm_table_host(ptr(Q), Q.stride(0), ptr(sel), P, ptr(sidx), ptr(bidx), ptr(og), G, T, ptr(table),
+                                 self.w, self.nw, ptr(out), ostride)
+        return out
+
     def _msm(self, Q, sel, P, sidx, bidx, og, G, T, bases, ostride, nout):
         out = torch.empty(nout, JAC, dtype=torch.int32, device=self.device)
         L = lib()
@@ -142,8 +189,12 @@ class CommitmentEngine:
     def chunk_commitments(self, Q: torch.Tensor, sel: torch.Tensor | None = None) -> torch.Tensor:
         """C[p, c] = sum_j Q[p, 10c+j] * PKG1[10c+j]  -> affine [P, nchunk, 16]."""
         P = Q.shape[0] if sel is None else sel.numel()
-        jac = self._msm(Q, sel, P, self.c_sidx, self.c_bidx, None, self.nchunk, POLY_SIZE, self.bases,
-                        ostride=self.nchunk, nout=P * self.nchunk)
+        if self.c_table is not None:
+            jac = self._msm_table(Q, sel, P, self.c_sidx, self.c_bidx, None, self.nchunk, POLY_SIZE, self.c_table,
+                                  ostride=self.nchunk, nout=P * self.nchunk)
+        else:
+            jac = self._msm(Q, sel, P, self.c_sidx, self.c_bidx, None, self.nchunk, POLY_SIZE, self.bases,
+                            ostride=self.nchunk, nout=P * self.nchunk)
         return self.normalize(jac).view(P, self.nchunk, AFF)
 
     def full_commitments(self, chunk_aff: torch.Tensor) -> torch.Tensor:
@@ -160,8 +211,12 @@ class CommitmentEngine:
         """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> affine [P, nchunk, S, 16]."""
         P = Q.shape[0] if sel is None else sel.numel()
         G = self.nchunk * self.S
-        jac = self._msm(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.wtable, ostride=G,
-                        nout=P * G)
+        if self.w_table is not None:
+            jac = self._msm_table(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.w_table, ostride=G,
+                                  nout=P * G)
+        else:
+            jac = self._msm(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.wtable, ostride=G,
+                            nout=P * G)
         return self.normalize(jac).view(P, self.nchunk, self.S, AFF)
 
     def aggregate(self, pts_aff: torch.Tensor, sel: torch.Tensor) -> torch.Tensor:
