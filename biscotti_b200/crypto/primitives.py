@@ -141,29 +141,29 @@ class BatchedVRF:
     def launch(self, msg: bytes):
         L = _L()
         n = len(self.keys)
-        hpt = torch.empty(32, dtype=torch.int32)
-        L.bsc_vrf_hash_to_curve(msg, len(msg), ctypes.c_void_p(hpt.data_ptr()), None)
+        hxy = torch.empty(64, dtype=torch.uint8)
+        L.bsc_vrf_hash_to_curve_xy(msg, len(msg), ctypes.c_void_p(hxy.data_ptr()))
         if self.device.type != "cuda":
             gam = torch.empty(n, 32, dtype=torch.uint8)
-            L.bsc_ed25519_scalarmult_batch_host(ctypes.c_void_p(self.scalars.data_ptr()),
-                                                ctypes.c_void_p(hpt.data_ptr()), 1, n, ctypes.c_void_p(gam.data_ptr()))
+            L.bsc_ed25519_scalarmult_r25_host(ctypes.c_void_p(self.scalars.data_ptr()), ctypes.c_void_p(hxy.data_ptr()),
+                                              n, ctypes.c_void_p(gam.data_ptr()))
             return (gam, None, msg)
         if not hasattr(self, "_side"):
             self._side = torch.cuda.Stream(self.device)
             self._host_gam = torch.empty(n, 32, dtype=torch.uint8).pin_memory()
-            self._hpt_pinned = torch.empty(32, dtype=torch.int32).pin_memory()
-            self._hd = torch.empty(32, dtype=torch.int32, device=self.device)
+            self._hpt_pinned = torch.empty(64, dtype=torch.uint8).pin_memory()
+            self._hd = torch.empty(64, dtype=torch.uint8, device=self.device)
             self._gam = torch.empty(n, 32, dtype=torch.uint8, device=self.device)
-        self._hpt_pinned.copy_(hpt)
+        self._hpt_pinned.copy_(hxy)
         self._side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(self._side):
             self._hd.copy_(self._hpt_pinned, non_blocking=True)
-            rc = L.bsc_ed25519_scalarmult_batch(ctypes.c_void_p(self.scalars.data_ptr()),
-                                                ctypes.c_void_p(self._hd.data_ptr()), 1, n,
-                                                ctypes.c_void_p(self._gam.data_ptr()),
-                                                ctypes.c_void_p(self._side.cuda_stream))
+            rc = L.bsc_ed25519_scalarmult_r25(ctypes.c_void_p(self.scalars.data_ptr()),
+                                              ctypes.c_void_p(self._hd.data_ptr()), n,
+                                              ctypes.c_void_p(self._gam.data_ptr()),
+                                              ctypes.c_void_p(self._side.cuda_stream))
             if rc:
-                raise RuntimeError("ed25519_scalarmult_batch failed")
+                raise RuntimeError("ed25519_scalarmult_r25 failed")
             self._host_gam.copy_(self._gam, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self._side)

@@ -1,0 +1,324 @@
+// Latency-oriented Ed25519 scalar multiplication for the per-block VRF evaluation (host+device).
+//
+// The VRF of every peer is evaluated on the previous block hash (DistSys/vrf.go:54-100), so one
+// ~253-bit scalar multiplication per peer sits on the critical path of every block and only ~100
+// threads exist to hide latency behind.  The generic 8x32 Montgomery field (field.cuh) is a serial
+// carry chain; here the field is 2^255-19 in radix 2^25.5 (ten signed limbs, 64-bit products, lazy
+// carries) whose 100 partial products are independent, which is what a lone warp needs to keep the
+// integer pipe busy.  Scalar recoding is signed radix-16 (64 digits in [-8, 8]) over a shared table of
+// 1H..8H: 252 doublings + <= 64 additions.  Results are canonical compressed points, so they are
+// bit-identical to the generic-field implementation in ed25519.cuh (tests compare the two).
+#pragma once
+#include <stdint.h>
+#include "field.cuh"
+
+namespace bsc {
+
+struct F25 {
+  int32_t v[10];
+};
+
+HD F25 f25_zero() {
+  F25 r;
+#pragma unroll
+  for (int i = 0; i < 10; i++) r.v[i] = 0;
+  return r;
+}
+HD F25 f25_one() {
+  F25 r = f25_zero();
+  r.v[0] = 1;
+  return r;
+}
+HD F25 f25_add(const F25& a, const F25& b) {
+  F25 r;
+#pragma unroll
+  for (int i = 0; i < 10; i++) r.v[i] = a.v[i] + b.v[i];
+  return r;
+}
+HD F25 f25_sub(const F25& a, const F25& b) {
+  F25 r;
+#pragma unroll
+  for (int i = 0; i < 10; i++) r.v[i] = a.v[i] - b.v[i];
+  return r;
+}
+HD F25 f25_neg(const F25& a) {
+  F25 r;
+#pragma unroll
+  for (int i = 0; i < 10; i++) r.v[i] = -a.v[i];
+  return r;
+}
+
+// interleaved carry chain; even limbs hold 26 bits, odd limbs 25 bits
+HD F25 f25_carry(int64_t h[10]) {
+  int64_t c;
+  c = (h[0] + ((int64_t)1 << 25)) >> 26; h[1] += c; h[0] -= c << 26;
+  c = (h[4] + ((int64_t)1 << 25)) >> 26; h[5] += c; h[4] -= c << 26;
+  c = (h[1] + ((int64_t)1 << 24)) >> 25; h[2] += c; h[1] -= c << 25;
+  c = (h[5] + ((int64_t)1 << 24)) >> 25; h[6] += c; h[5] -= c << 25;
+  c = (h[2] + ((int64_t)1 << 25)) >> 26; h[3] += c; h[2] -= c << 26;
+  c = (h[6] + ((int64_t)1 << 25)) >> 26; h[7] += c; h[6] -= c << 26;
+  c = (h[3] + ((int64_t)1 << 24)) >> 25; h[4] += c; h[3] -= c << 25;
+  c = (h[7] + ((int64_t)1 << 24)) >> 25; h[8] += c; h[7] -= c << 25;
+  c = (h[4] + ((int64_t)1 << 25)) >> 26; h[5] += c; h[4] -= c << 26;
+  c = (h[8] + ((int64_t)1 << 25)) >> 26; h[9] += c; h[8] -= c << 26;
+  c = (h[9] + ((int64_t)1 << 24)) >> 25; h[0] += c * 19; h[9] -= c << 25;
+  c = (h[0] + ((int64_t)1 << 25)) >> 26; h[1] += c; h[0] -= c << 26;
+  F25 r;
+#pragma unroll
+  for (int i = 0; i < 10; i++) r.v[i] = (int32_t)h[i];
+  return r;
+}
+
+// h = f*g (dbl = false) or 2*f*g (dbl = true); inputs bounded by 1.65*2^26, output by 1.01*2^25/2^26
+template <bool DBL>
+HD F25 f25_mul_t(const F25& f, const F25& g) {
+  int32_t g19[10], f2[10];
+#pragma unroll
+  for (int i = 0; i < 10; i++) {
+    g19[i] = 19 * g.v[i];
+    f2[i] = 2 * f.v[i];
+  }
+  int64_t h[10];
+#pragma unroll
+  for (int k = 0; k < 10; k++) h[k] = 0;
+#pragma unroll
+  for (int i = 0; i < 10; i++) {
+#pragma unroll
+    for (int j = 0; j < 10; j++) {
+      const int32_t fi = ((i & 1) && (j & 1)) ? f2[i] : f.v[i];
+      const bool wrap = (i + j) >= 10;
+      const int32_t gj = wrap ? g19[j] : g.v[j];
+      h[wrap ? i + j - 10 : i + j] += (int64_t)fi * gj;
+    }
+  }
+  if (DBL) {
+#pragma unroll
+    for (int k = 0; k < 10; k++) h[k] += h[k];
+  }
+  return f25_carry(h);
+}
+HD F25 f25_mul(const F25& f, const F25& g) { return f25_mul_t<false>(f, g); }
+HD F25 f25_sq(const F25& f) { return f25_mul_t<false>(f, f); }
+HD F25 f25_sq2(const F25& f) { return f25_mul_t<true>(f, f); }
+
+HD int64_t ld3(const uint8_t* p) { return (int64_t)p[0] | ((int64_t)p[1] << 8) | ((int64_t)p[2] << 16); }
+HD int64_t ld4(const uint8_t* p) { return ld3(p) | ((int64_t)p[3] << 24); }
+
+HD F25 f25_frombytes(const uint8_t s[32]) {
+  int64_t h[10];
+  h[0] = ld4(s);
+  h[1] = ld3(s + 4) << 6;
+  h[2] = ld3(s + 7) << 5;
+  h[3] = ld3(s + 10) << 3;
+  h[4] = ld3(s + 13) << 2;
+  h[5] = ld4(s + 16);
+  h[6] = ld3(s + 20) << 7;
+  h[7] = ld3(s + 23) << 5;
+  h[8] = ld3(s + 26) << 4;
+  h[9] = (ld3(s + 29) & 8388607) << 2;
+  int64_t c;
+  c = (h[9] + ((int64_t)1 << 24)) >> 25; h[0] += c * 19; h[9] -= c << 25;
+  c = (h[1] + ((int64_t)1 << 24)) >> 25; h[2] += c; h[1] -= c << 25;
+  c = (h[3] + ((int64_t)1 << 24)) >> 25; h[4] += c; h[3] -= c << 25;
+  c = (h[5] + ((int64_t)1 << 24)) >> 25; h[6] += c; h[5] -= c << 25;
+  c = (h[7] + ((int64_t)1 << 24)) >> 25; h[8] += c; h[7] -= c << 25;
+  c = (h[0] + ((int64_t)1 << 25)) >> 26; h[1] += c; h[0] -= c << 26;
+  c = (h[2] + ((int64_t)1 << 25)) >> 26; h[3] += c; h[2] -= c << 26;
+  c = (h[4] + ((int64_t)1 << 25)) >> 26; h[5] += c; h[4] -= c << 26;
+  c = (h[6] + ((int64_t)1 << 25)) >> 26; h[7] += c; h[6] -= c << 26;
+  c = (h[8] + ((int64_t)1 << 25)) >> 26; h[9] += c; h[8] -= c << 26;
+  F25 r;
+#pragma unroll
+  for (int i = 0; i < 10; i++) r.v[i] = (int32_t)h[i];
+  return r;
+}
+
+// canonical little-endian encoding (full reduction mod 2^255-19)
+HD void f25_tobytes(uint8_t s[32], const F25& f) {
+  int32_t h[10];
+#pragma unroll
+  for (int i = 0; i < 10; i++) h[i] = f.v[i];
+  int32_t q = (19 * h[9] + ((int32_t)1 << 24)) >> 25;
+  q = (h[0] + q) >> 26; q = (h[1] + q) >> 25; q = (h[2] + q) >> 26; q = (h[3] + q) >> 25; q = (h[4] + q) >> 26;
+  q = (h[5] + q) >> 25; q = (h[6] + q) >> 26; q = (h[7] + q) >> 25; q = (h[8] + q) >> 26; q = (h[9] + q) >> 25;
+  h[0] += 19 * q;
+  int32_t c;
+  c = h[0] >> 26; h[1] += c; h[0] -= c << 26;
+  c = h[1] >> 25; h[2] += c; h[1] -= c << 25;
+  c = h[2] >> 26; h[3] += c; h[2] -= c << 26;
+  c = h[3] >> 25; h[4] += c; h[3] -= c << 25;
+  c = h[4] >> 26; h[5] += c; h[4] -= c << 26;
+  c = h[5] >> 25; h[6] += c; h[5] -= c << 25;
+  c = h[6] >> 26; h[7] += c; h[6] -= c << 26;
+  c = h[7] >> 25; h[8] += c; h[7] -= c << 25;
+  c = h[8] >> 26; h[9] += c; h[8] -= c << 26;
+  c = h[9] >> 25; h[9] -= c << 25;
+  s[0] = (uint8_t)(h[0] >> 0); s[1] = (uint8_t)(h[0] >> 8); s[2] = (uint8_t)(h[0] >> 16);
+  s[3] = (uint8_t)((h[0] >> 24) | (h[1] << 2));
+  s[4] = (uint8_t)(h[1] >> 6); s[5] = (uint8_t)(h[1] >> 14);
+  s[6] = (uint8_t)((h[1] >> 22) | (h[2] << 3));
+  s[7] = (uint8_t)(h[2] >> 5); s[8] = (uint8_t)(h[2] >> 13);
+  s[9] = (uint8_t)((h[2] >> 21) | (h[3] << 5));
+  s[10] = (uint8_t)(h[3] >> 3); s[11] = (uint8_t)(h[3] >> 11);
+  s[12] = (uint8_t)((h[3] >> 19) | (h[4] << 6));
+  s[13] = (uint8_t)(h[4] >> 2); s[14] = (uint8_t)(h[4] >> 10); s[15] = (uint8_t)(h[4] >> 18);
+  s[16] = (uint8_t)(h[5] >> 0); s[17] = (uint8_t)(h[5] >> 8); s[18] = (uint8_t)(h[5] >> 16);
+  s[19] = (uint8_t)((h[5] >> 24) | (h[6] << 1));
+  s[20] = (uint8_t)(h[6] >> 7); s[21] = (uint8_t)(h[6] >> 15);
+  s[22] = (uint8_t)((h[6] >> 23) | (h[7] << 3));
+  s[23] = (uint8_t)(h[7] >> 5); s[24] = (uint8_t)(h[7] >> 13);
+  s[25] = (uint8_t)((h[7] >> 21) | (h[8] << 4));
+  s[26] = (uint8_t)(h[8] >> 4); s[27] = (uint8_t)(h[8] >> 12);
+  s[28] = (uint8_t)((h[8] >> 20) | (h[9] << 6));
+  s[29] = (uint8_t)(h[9] >> 2); s[30] = (uint8_t)(h[9] >> 10); s[31] = (uint8_t)(h[9] >> 18);
+}
+
+HDN inline F25 f25_sqn(F25 t, int n) {
+  for (int i = 0; i < n; i++) t = f25_sq(t);
+  return t;
+}
+// z^(p-2) with the standard 254-squaring / 11-multiplication chain
+HDN inline F25 f25_invert(const F25& z) {
+  F25 z2 = f25_sq(z);
+  F25 t = f25_sqn(z2, 2);
+  F25 z9 = f25_mul(t, z);
+  F25 z11 = f25_mul(z9, z2);
+  t = f25_sq(z11);
+  F25 z2_5_0 = f25_mul(t, z9);
+  t = f25_sqn(z2_5_0, 5);
+  F25 z2_10_0 = f25_mul(t, z2_5_0);
+  t = f25_sqn(z2_10_0, 10);
+  F25 z2_20_0 = f25_mul(t, z2_10_0);
+  t = f25_sqn(z2_20_0, 20);
+  t = f25_mul(t, z2_20_0);
+  t = f25_sqn(t, 10);
+  F25 z2_50_0 = f25_mul(t, z2_10_0);
+  t = f25_sqn(z2_50_0, 50);
+  F25 z2_100_0 = f25_mul(t, z2_50_0);
+  t = f25_sqn(z2_100_0, 100);
+  t = f25_mul(t, z2_100_0);
+  t = f25_sqn(t, 50);
+  t = f25_mul(t, z2_50_0);
+  t = f25_sqn(t, 5);
+  return f25_mul(t, z11);
+}
+
+struct EdP3 { F25 X, Y, Z, T; };        // extended
+struct EdP1 { F25 X, Y, Z, T; };        // completed ((X:Z), (Y:T))
+struct EdCached { F25 YpX, YmX, Z, T2d; };
+
+HD F25 f25_const_2d() {
+  // 2d mod p as little-endian bytes of the canonical value
+  const uint8_t b[32] = {0x59, 0xf1, 0xb2, 0x26, 0x94, 0x9b, 0xd6, 0xeb, 0x56, 0xb1, 0x83, 0x82, 0x9a, 0x14, 0xe0, 0x00,
+                         0x30, 0xd1, 0xf3, 0xee, 0xf2, 0x80, 0x8e, 0x19, 0xe7, 0xfc, 0xdf, 0x56, 0xdc, 0xd9, 0x06, 0x24};
+  return f25_frombytes(b);
+}
+
+HD EdP3 edr_identity() {
+  EdP3 r;
+  r.X = f25_zero(); r.Y = f25_one(); r.Z = f25_one(); r.T = f25_zero();
+  return r;
+}
+HD EdP3 edr_p1_to_p3(const EdP1& p) {
+  EdP3 r;
+  r.X = f25_mul(p.X, p.T); r.Y = f25_mul(p.Y, p.Z); r.Z = f25_mul(p.Z, p.T); r.T = f25_mul(p.X, p.Y);
+  return r;
+}
+// doubling of the projective part (X:Y:Z) of p
+HD EdP1 edr_dbl(const F25& X, const F25& Y, const F25& Z) {
+  EdP1 r;
+  F25 XX = f25_sq(X), YY = f25_sq(Y), B = f25_sq2(Z);
+  F25 A = f25_sq(f25_add(X, Y));
+  r.Y = f25_add(YY, XX);
+  r.Z = f25_sub(YY, XX);
+  r.X = f25_sub(A, r.Y);
+  r.T = f25_sub(B, r.Z);
+  return r;
+}
+HD EdCached edr_to_cached(const EdP3& p, const F25& d2) {
+  EdCached c;
+  c.YpX = f25_add(p.Y, p.X); c.YmX = f25_sub(p.Y, p.X); c.Z = p.Z; c.T2d = f25_mul(p.T, d2);
+  return c;
+}
+// p + q (neg = false) or p - q (neg = true)
+HD EdP1 edr_add(const EdP3& p, const EdCached& q, bool neg) {
+  EdP1 r;
+  F25 a = f25_add(p.Y, p.X), b = f25_sub(p.Y, p.X);
+  F25 A = f25_mul(a, neg ? q.YmX : q.YpX);
+  F25 Bm = f25_mul(b, neg ? q.YpX : q.YmX);
+  F25 C = f25_mul(q.T2d, p.T);
+  F25 ZZ = f25_mul(p.Z, q.Z);
+  F25 D = f25_add(ZZ, ZZ);
+  r.X = f25_sub(A, Bm);
+  r.Y = f25_add(A, Bm);
+  if (neg) {
+    r.Z = f25_sub(D, C);
+    r.T = f25_add(D, C);
+  } else {
+    r.Z = f25_add(D, C);
+    r.T = f25_sub(D, C);
+  }
+  return r;
+}
+HDN inline void edr_compress(uint8_t out[32], const EdP3& p) {
+  F25 zi = f25_invert(p.Z);
+  F25 x = f25_mul(p.X, zi), y = f25_mul(p.Y, zi);
+  uint8_t xb[32];
+  f25_tobytes(out, y);
+  f25_tobytes(xb, x);
+  out[31] ^= (uint8_t)((xb[0] & 1) << 7);
+}
+// affine (x, y) as 64 canonical little-endian bytes -> extended
+HD EdP3 edr_from_affine_bytes(const uint8_t xy[64]) {
+  EdP3 r;
+  r.X = f25_frombytes(xy);
+  r.Y = f25_frombytes(xy + 32);
+  r.Z = f25_one();
+  r.T = f25_mul(r.X, r.Y);
+  return r;
+}
+
+// table[k] = (k+1) * H in cached form, k = 0..7
+HDN inline void edr_build_table(EdCached table[8], const EdP3& H, const F25& d2) {
+  table[0] = edr_to_cached(H, d2);
+  EdP3 acc = H;
+  for (int k = 1; k < 8; k++) {
+    acc = edr_p1_to_p3(edr_add(acc, table[0], false));
+    table[k] = edr_to_cached(acc, d2);
+  }
+}
+
+// scalar (32 little-endian bytes, < 2^255) times the table's base point
+HDN inline EdP3 edr_scalarmult(const uint8_t a[32], const EdCached* table) {
+  signed char e[64];
+  for (int i = 0; i < 32; i++) {
+    e[2 * i] = (signed char)(a[i] & 15);
+    e[2 * i + 1] = (signed char)((a[i] >> 4) & 15);
+  }
+  int carry = 0;
+  for (int i = 0; i < 63; i++) {
+    e[i] = (signed char)(e[i] + carry);
+    carry = (e[i] + 8) >> 4;
+    e[i] = (signed char)(e[i] - (carry << 4));
+  }
+  e[63] = (signed char)(e[63] + carry);
+  EdP3 r = edr_identity();
+  for (int i = 63; i >= 0; i--) {
+    // r = 16 r : three projective doublings and a final one back to extended coordinates
+    EdP1 t = edr_dbl(r.X, r.Y, r.Z);
+#pragma unroll 1
+    for (int k = 0; k < 3; k++) {
+      F25 X = f25_mul(t.X, t.T), Y = f25_mul(t.Y, t.Z), Z = f25_mul(t.Z, t.T);
+      t = edr_dbl(X, Y, Z);
+    }
+    r = edr_p1_to_p3(t);
+    const int dgt = e[i];
+    if (dgt != 0) {
+      const int m = dgt < 0 ? -dgt : dgt;
+      r = edr_p1_to_p3(edr_add(r, table[m - 1], dgt < 0));
+    }
+  }
+  return r;
+}
+
+}  // namespace bsc

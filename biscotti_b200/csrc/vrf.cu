@@ -8,6 +8,7 @@
 // t = r - s*x,  proof = s || t || Gamma,  output = SHAKE256(Gamma || m)[:32].
 #include "common.cuh"
 #include "ed25519.cuh"
+#include "ed25519_r25.cuh"
 #include "sha256.cuh"
 #include <string.h>
 
@@ -121,6 +122,25 @@ __global__ void ed25519_scalarmult_kernel(const U256* __restrict__ k, const EdPo
   ed_compress(out + 32 * (size_t)i, r);
 }
 
+// Latency-optimised form: radix-2^25.5 field, signed radix-16 windows over a shared table of 1H..8H
+// built once per CTA.  scalars: N x 32 little-endian bytes; hxy: affine H as 64 little-endian bytes.
+__global__ void __launch_bounds__(32) ed25519_scalarmult_r25_kernel(const unsigned char* __restrict__ scalars,
+                                                                    const unsigned char* __restrict__ hxy, int N,
+                                                                    unsigned char* __restrict__ out) {
+  __shared__ EdCached table[8];
+  if (threadIdx.x == 0) {
+    uint8_t b[64];
+    for (int i = 0; i < 64; i++) b[i] = hxy[i];
+    edr_build_table(table, edr_from_affine_bytes(b), f25_const_2d());
+  }
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  uint8_t a[32];
+  for (int k = 0; k < 32; k++) a[k] = scalars[32 * (size_t)i + k];
+  edr_compress(out + 32 * (size_t)i, edr_scalarmult(a, table));
+}
+
 // batched SHA-256: digest of msgs[i] (each `len` bytes, `stride` apart) -> out[i][32]
 __global__ void sha256_batch_kernel(const unsigned char* __restrict__ msgs, int len, long long stride, int N,
                                     unsigned char* __restrict__ out) {
@@ -156,6 +176,13 @@ void bsc_vrf_hash_to_curve(const uint8_t* m, size_t n, void* out_point, uint8_t 
   EdPoint h = hash_to_curve(m, n);
   if (out_point) memcpy(out_point, &h, sizeof(h));
   if (out_bytes) ed_compress(out_bytes, h);
+}
+// affine H = hashToCurve(m) as x || y, 32 canonical little-endian bytes each (input of the r25 kernel)
+void bsc_vrf_hash_to_curve_xy(const uint8_t* m, size_t n, uint8_t out[64]) {
+  EdPoint h = hash_to_curve(m, n);
+  Fq zi = fe_inv(h.Z);
+  u256_to_le(out, fe_to_u256(fe_mul(h.X, zi)));
+  u256_to_le(out + 32, fe_to_u256(fe_mul(h.Y, zi)));
 }
 // output = SHAKE256(Gamma || m)[:32]
 void bsc_vrf_output_from_gamma(const uint8_t gamma[32], const uint8_t* m, size_t n, uint8_t out[32]) {
@@ -261,6 +288,18 @@ int bsc_ed25519_scalarmult_batch(const void* scalars_u256, const void* bases, in
   ed25519_scalarmult_kernel<<<(N + 63) / 64, 64, 0, (cudaStream_t)stream>>>((const U256*)scalars_u256,
                                                                             (const EdPoint*)bases, nbase, N, out);
   return finish_launch("ed25519_scalarmult_batch");
+}
+int bsc_ed25519_scalarmult_r25(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out,
+                               void* stream) {
+  if (N == 0) return 0;
+  ed25519_scalarmult_r25_kernel<<<(N + 31) / 32, 32, 0, (cudaStream_t)stream>>>(scalars, hxy, N, out);
+  return finish_launch("ed25519_scalarmult_r25");
+}
+void bsc_ed25519_scalarmult_r25_host(const unsigned char* scalars, const unsigned char* hxy, int N,
+                                     unsigned char* out) {
+  EdCached table[8];
+  edr_build_table(table, edr_from_affine_bytes(hxy), f25_const_2d());
+  for (int i = 0; i < N; i++) edr_compress(out + 32 * (size_t)i, edr_scalarmult(scalars + 32 * (size_t)i, table));
 }
 void bsc_ed25519_scalarmult_batch_host(const void* scalars_u256, const void* bases, int nbase, int N,
                                        unsigned char* out) {

@@ -207,3 +207,26 @@ def test_gram_tcgen05_matches_fp32_reference(n, d, ksplit):
     _, aref, _ = krum_ops.krum_reference(U[:, :d], clip)
     _, a, _ = krum_ops.krum(Un, d, clip, hi, lo, norms, impl="tcgen05")
     assert a.cpu().bool().tolist() == aref.tolist()
+
+
+def test_vrf_side_stream_path_matches_generic_lottery():
+    """Engine path: radix-2^25.5 Ed25519 kernel on a side stream + one native noiser-lottery call, against
+    the generic-field prove() outputs and the per-peer Python-driven lottery."""
+    import hashlib
+
+    import numpy as np
+
+    n = 40
+    keys = [cp.VRFKey(hashlib.sha256(b"k%d" % i).digest()) for i in range(n)]
+    msg = hashlib.sha256(b"prev-block").digest()
+    stake = [10 + 5 * (i % 4) for i in range(n)]
+    bv = cp.BatchedVRF(keys, DEV)
+    is_worker = np.ones(n, dtype=np.uint8)
+    is_worker[[3, 7]] = 0
+    tab = bv.noiser_table(bv.launch(msg), stake, is_worker, 2)
+    for p in range(n):
+        if not is_worker[p]:
+            assert tab[p].tolist() == [-1, -1]
+            continue
+        out = keys[p].prove(msg)[0]
+        assert tab[p].tolist() == cp.lottery_noisers(out, stake, p, 2)
