@@ -1,0 +1,273 @@
+/* biscotti_b200 C ABI - every extern "C" entry point of libbiscotti_b200.so.
+ *
+ * Conventions: device pointers are plain pointers into CUDA global memory; `stream` is a cudaStream_t
+ * passed as void*; functions returning int return 0 on success, a cudaError_t on a launch failure, or a
+ * negative value for an argument error.  `*_host` functions are CPU mirrors built from the same
+ * host/device headers as the kernels (bit-exact oracles and the CPU plumbing path).  Point layouts:
+ * affine = 16 x uint32 (x, y in Montgomery form), Jacobian = 24 x uint32, wire = 64 big-endian bytes.
+ * Generated from the sources by tools/gen_header.py; comments are the ones beside each definition.
+ */
+#ifndef BISCOTTI_B200_H
+#define BISCOTTI_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* --------------------------------------------------------------------------------------------
+ * kernels_ml.cu - Local steps, DP noise, Krum tail, evaluation.  Reference: ML/Pytorch/client.py:38-65, 136-172; ML/code/logistic_model.py:92-140; ML/Pytorch/client_obj.py:97-143; DistSys/main.go:1592-1660; DistSys/krum.go:77-166.
+ * -------------------------------------------------------------------------------------------- */
+unsigned long long bsc_launch_count();
+
+void bsc_launch_count_reset();
+
+int bsc_local_softmax_step(const float* w, const float* X, const int* y, const int* idx, float* U, float* loss, int P, int Ns, int B, int F, int C, int ldu, float clip, void* stream);
+
+int bsc_local_logistic_step(const float* w, const float* X, const float* y, const int* idx, float* U, int P, int Ns, int B, int F, int ldu, float alpha, float lambda, float own_noise_scale, unsigned long long seed, const int* peer_ids, int slot, void* stream);
+
+int bsc_noise_mix(const float* U, const int* noisers, int nn, unsigned long long seed, int slot, float noise_scale, float* Un, void* hi, void* lo, float* norms, int P, int d, int ldu, int ldh, void* stream);
+
+int bsc_noise_row(float* out, int d, unsigned long long seed, int peer, int slot, float scale, void* stream);
+
+// host restatement of the same generator (CPU path + oracle)
+void bsc_noise_row_host(float* out, int d, unsigned long long seed, int peer, int slot, float scale);
+
+int bsc_gram_simt(const float* A, float* Gpart, int n, int d, int lda, int ksplit, void* stream);
+
+int bsc_krum_select(const float* Gpart, int nsplit, int ldg, const float* norms, int n, int clip, float* scores, unsigned char* accept, float* Dout, void* stream);
+
+int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F, int C, int ldw, void* stream);
+
+int bsc_eval_logistic(const float* Wc, const float* base, const float* X, const float* y, int* wrong, int M, int N, int F, int ldw, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * gram_tc.cu - tcgen05/TMA Gram kernel for Multi-Krum.  Reference: ML/Pytorch/client_obj.py:132-143.
+ * -------------------------------------------------------------------------------------------- */
+// G partials of hi/lo planes [rows][ldh] (ldh % 64 == 0, 16-byte aligned base), first n rows valid.
+// Gpart: [ksplit][ldg][ldg] with ldg = ceil(n/128)*128; every split must own >= 1 k-block.
+int bsc_gram_tc(const void* hi, const void* lo, int n, int rows, int ldh, int ksplit, float* Gpart, int ldg, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * kernels_secagg.cu - Fixed-point, Shamir shares, aggregation, reconstruction + SGD step.  Reference: DistSys/kyber.go:244-287, 579-609, 698-757, 809-857; DistSys/honest.go:346-502.
+ * -------------------------------------------------------------------------------------------- */
+int bsc_quantize(const float* U, long long* Q, int P, int d, int ldu, int dpad, double scale, void* stream);
+
+int bsc_shares_eval(const long long* Q, long long* Y, int P, int nchunk, int dpad, int S, void* stream);
+
+int bsc_share_sum(const float* U, const int* sel, int nsel, int d, int ldu, int c0, int nc, int S, double scale, long long* Ysum, void* stream);
+
+int bsc_reconstruct_step(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d, double scale, double* w64, float* w32, double* dsum, int* bad, void* stream);
+
+int bsc_plain_sum_step(const float* U, const int* sel, int nsel, int d, int ldu, double* w64, float* w32, double* dsum, void* stream);
+
+// ---- host restatements (CPU plumbing path and oracles; same arithmetic, same header) -------------
+void bsc_quantize_host(const float* U, long long* Q, int P, int d, int ldu, int dpad, double scale);
+
+void bsc_shares_eval_host(const long long* Q, long long* Y, int P, int nchunk, int dpad, int S);
+
+// returns number of chunks whose recovery was inexact or inconsistent
+int bsc_shamir_recover_host(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int nc, long long* coef_out);
+
+/* --------------------------------------------------------------------------------------------
+ * kernels_msm.cu - BN256 G1 MSM for commitments and witnesses.  Reference: DistSys/kyber.go:172-202, 456-482, 533-562, 579-646; DistSys/publicKey.go:28-66.
+ * -------------------------------------------------------------------------------------------- */
+int bsc_msm_groups(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* bases_affine, void* out_jac, long long ostride_p, void* stream);
+
+int bsc_msm_table_build(const void* bases_affine, long long nb, int w, int nw, void* out_jac, void* stream);
+
+void bsc_msm_table_build_host(const void* bases_affine, long long nb, int w, int nw, void* out_jac);
+
+int bsc_msm_table(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p, void* stream);
+
+void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p);
+
+int bsc_g1_fixed_base_mul(const void* scalars_u256, int N, const void* base_affine, void* out_jac, void* stream);
+
+int bsc_g1_normalize(const void* in_jac, void* out_affine, long long N, void* stream);
+
+int bsc_g1_affine_to_bytes(const void* in_affine, unsigned char* out, long long N, void* stream);
+
+int bsc_g1_bytes_to_affine(const unsigned char* in, void* out_affine, long long N, void* stream);
+
+int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac, void* stream);
+
+int bsc_g1_sum_cols(const void* pts_affine, int P, int G, void* out_jac, void* stream);
+
+// ---- host mirrors (CPU plumbing path + oracles; same templates as the kernels) --------------------
+void bsc_msm_groups_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* bases_affine, void* out_jac, long long ostride_p);
+
+void bsc_g1_normalize_host(const void* in_jac, void* out_affine, long long N);
+
+void bsc_g1_sum_rows_host(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac);
+
+void bsc_g1_sum_cols_host(const void* pts_affine, int P, int G, void* out_jac);
+
+void bsc_g1_fixed_base_mul_host(const void* scalars_u256, int N, const void* base_affine, void* out_jac);
+
+/* --------------------------------------------------------------------------------------------
+ * vrf.cu - ECVRF, batched Ed25519 scalar multiplication, batched SHA-256, noiser lottery.  Reference: DistSys/vrf.go:16-100.
+ * -------------------------------------------------------------------------------------------- */
+void bsc_sha512(const uint8_t* data, size_t n, uint8_t out[64]);
+
+// public key (32 bytes) from a 32-byte seed
+void bsc_vrf_pubkey(const uint8_t seed[32], uint8_t pk[32]);
+
+// expanded secret scalar (little-endian words) for the device kernel
+void bsc_vrf_secret_scalar(const uint8_t seed[32], uint32_t out_words[8]);
+
+// H = hashToCurve(m) in the device struct layout (4 x 8 words, Montgomery form)
+void bsc_vrf_hash_to_curve(const uint8_t* m, size_t n, void* out_point, uint8_t out_bytes[32]);
+
+// affine H = hashToCurve(m) as x || y, 32 canonical little-endian bytes each (input of the r25 kernel)
+void bsc_vrf_hash_to_curve_xy(const uint8_t* m, size_t n, uint8_t out[64]);
+
+// output = SHAKE256(Gamma || m)[:32]
+void bsc_vrf_output_from_gamma(const uint8_t gamma[32], const uint8_t* m, size_t n, uint8_t out[32]);
+
+void bsc_vrf_prove(const uint8_t seed[32], const uint8_t* m, size_t n, uint8_t vrf[32], uint8_t proof[96]);
+
+int bsc_vrf_verify(const uint8_t pk[32], const uint8_t* m, size_t n, const uint8_t vrf[32], const uint8_t proof[96]);
+
+// All workers' noiser committees in one call: output_p = SHAKE256(Gamma_p || m)[:32], then the stake
+// lottery of vrf.go:54-100 seeded by output_p with p itself excluded.  out[p*want + j] = noiser id or -1.
+void bsc_noisers_batch(const uint8_t* gammas, const uint8_t* m, size_t mlen, const int* stake, int n, const uint8_t* is_worker, int want, int* out, uint8_t* vrf_out);
+
+// device: gamma[i] = compress(x[i] * H) for all peers
+int bsc_ed25519_scalarmult_batch(const void* scalars_u256, const void* bases, int nbase, int N, unsigned char* out, void* stream);
+
+int bsc_ed25519_scalarmult_r25(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out, void* stream);
+
+void bsc_ed25519_scalarmult_r25_host(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out);
+
+void bsc_ed25519_scalarmult_batch_host(const void* scalars_u256, const void* bases, int nbase, int N, unsigned char* out);
+
+int bsc_sha256_batch(const unsigned char* msgs, int len, long long stride, int N, unsigned char* out, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * host_crypto.cpp - Host crypto runtime (G1 byte API, SRS, hashes, Schnorr).  Reference: DistSys/kyber.go:873-933; DistSys/publicKey.go; lib/dedis/kyber/pairing/bn256/point.go:109-167; lib/dedis/kyber/xof/blake2xb/blake.go.
+ * -------------------------------------------------------------------------------------------- */
+void bsc_sha256(const uint8_t* data, size_t n, uint8_t out[32]);
+
+void bsc_blake2b(const uint8_t* data, size_t n, const uint8_t* key, size_t keylen, uint8_t* out, size_t outlen);
+
+void bsc_blake2xb(const uint8_t* seed, size_t seedlen, const uint8_t* msg, size_t n, uint8_t* out, size_t outlen);
+
+void bsc_shake256(const uint8_t* data, size_t n, uint8_t* out, size_t outlen);
+
+// ---- G1 byte API ---------------------------------------------------------------------------------
+void bsc_g1_generator(uint8_t out[64]);
+
+int bsc_g1_on_curve(const uint8_t in[64]);
+
+void bsc_g1_add(uint8_t out[64], const uint8_t a[64], const uint8_t b[64]);
+
+void bsc_g1_neg(uint8_t out[64], const uint8_t a[64]);
+
+// scalar: 32-byte big-endian, reduced mod the group order first (mod.Int semantics)
+void bsc_g1_mul(uint8_t out[64], const uint8_t in[64], const uint8_t k_be[32]);
+
+// naive signed-int64 MSM oracle, one double-and-add per term like createCommitment (kyber.go:533-562)
+void bsc_g1_msm_i64_host(uint8_t out[64], const uint8_t* bases64, const long long* scalars, int n);
+
+// wire bytes <-> device layout (Montgomery affine, 16 x uint32)
+void bsc_g1_bytes_to_affine_host(const uint8_t* in, void* out_affine, long long N);
+
+void bsc_g1_affine_to_bytes_host(const void* in_affine, uint8_t* out, long long N);
+
+void bsc_g1_jac_to_bytes_host(const void* in_jac, uint8_t* out, long long N);
+
+// host mirror of the device Straus kernel (same template) for CPU-side unit tests
+void bsc_g1_straus_host(uint8_t out[64], const void* bases_affine, const long long* s, int T);
+
+// SRS: PKG1[i] = tau^i * G for i < d (DistSys/publicKey.go:28-66).  tau = 2 reproduces the reference's
+// hard-coded trapdoor (:36); any other 32-byte big-endian tau gives a proper setup.
+void bsc_srs_g1_host(const uint8_t tau_be[32], int d, uint8_t* out);
+
+// tau^i as plain little-endian 8x32 words, for the device fixed-base kernel
+void bsc_fr_powers(const uint8_t tau_be[32], int d, uint32_t* out_words);
+
+// ---- Schnorr (kyber.go:873-933) ------------------------------------------------------------------
+// pub = x*G
+void bsc_schnorr_pubkey(const uint8_t x_be[32], uint8_t pub[64]);
+
+// sig = c || r, c = H(T || msg), r = v - x*c ; v supplied by the caller (32 random bytes)
+void bsc_schnorr_sign(const uint8_t* msg, size_t n, const uint8_t x_be[32], const uint8_t v_be[32], uint8_t sig[64]);
+
+int bsc_schnorr_verify(const uint8_t* msg, size_t n, const uint8_t pub[64], const uint8_t sig[64]);
+
+/* --------------------------------------------------------------------------------------------
+ * ledger.cpp - Ledger and stake lottery.  Reference: DistSys/block.go, blockData.go, update.go, blockchain.go, honest.go:631-653, vrf.go:54-182.
+ * -------------------------------------------------------------------------------------------- */
+void* bsc_chain_new(int d);
+
+void bsc_chain_free(void* c);
+
+int bsc_chain_len(void* c);
+
+int bsc_chain_dim(void* c);
+
+long long bsc_chain_latest_iteration(void* c);
+
+// ---- block builder -------------------------------------------------------------------------------
+void* bsc_block_new(long long iteration, const double* w, int d);
+
+void bsc_block_free(void* b);
+
+void bsc_block_add_update(void* bp, int source, int iteration, int accepted, const uint8_t* commitment, int clen, const double* delta, int dlen, const double* noise, int nlen, const double* noised, int ndlen, const uint8_t* sigs, int nsigs, int siglen);
+
+void bsc_block_set_stake(void* bp, const int* ids, const int* vals, int n);
+
+// Seal against the chain tip and append (NewBlock + AddBlock, block.go:30-44, blockchain.go:12-16).
+// timestamp < 0 => reference rule: 0 for an empty block, wall-clock seconds otherwise.
+// Consumes the builder.  Returns the new chain length.
+int bsc_chain_append(void* cp, void* bp, long long timestamp);
+
+// getBlock(it) = Blocks[it+1] with the consistency check (blockchain.go:77-96): index or -1/-2
+int bsc_chain_block_index(void* cp, long long iteration);
+
+void bsc_chain_hash(void* cp, int index, uint8_t out[32]);
+
+void bsc_chain_prev_hash(void* cp, int index, uint8_t out[32], int* len);
+
+void bsc_chain_weights(void* cp, int index, double* out);
+
+long long bsc_chain_block_info(void* cp, int index, long long* iteration, int* nupdates, int* nstake);
+
+void bsc_chain_block_stake(void* cp, int index, int* ids, int* vals);
+
+int bsc_chain_update_info(void* cp, int index, int u, int* source, int* accepted, uint8_t commitment[64], int* nsigs);
+
+// recompute every hash and the prev-hash links; 1 = consistent
+int bsc_chain_verify(void* cp);
+
+// serialisation (RegisterPeer chain transfer main.go:420-436; doubles as checkpoint format)
+size_t bsc_chain_serialize(void* cp, uint8_t* out, size_t cap);
+
+void* bsc_chain_deserialize(const uint8_t* in, size_t n);
+
+// single-block wire form (RegisterBlock gossip, main.go:398-409)
+size_t bsc_chain_block_serialize(void* cp, int index, uint8_t* out, size_t cap);
+
+// Append or replace from a received block.  Return codes:
+//   1 appended, 2 replaced an empty block by a non-empty one (honest.go:631-653), 0 duplicate/ignored,
+//  -1 malformed, -2 does not link to our chain, -3 hash mismatch
+int bsc_chain_accept_block(void* cp, const uint8_t* in, size_t n);
+
+const char* bsc_chain_dump(void* cp, size_t* len);
+
+int bsc_chain_equal(void* a, void* b);
+
+const char* bsc_go_float(double v);
+
+// roles: verifiers first, then miners continue from the same byte cursor (vrf.go:103-182)
+int bsc_lottery_roles(const uint8_t* input, int inlen, const int* stake, int n, int nverifiers, int nminers, int* verifiers, int* miners, int* nv_out, int* nm_out);
+
+// noisers from a peer's private VRF output, excluding itself (vrf.go:54-100)
+int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n, int source, int want, int* noisers);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BISCOTTI_B200_H */
