@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "secagg_math.cuh"
 #include <cuda_bf16.h>
+#include <mutex>
 
 namespace bsc {
 
@@ -467,6 +468,79 @@ int bsc_krum_select(const float* Gpart, int nsplit, int ldg, const float* norms,
   krum_select_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(Gpart, nsplit, ldg, norms, n, clip, scores, accept, Dout,
                                                               np2);
   return finish_launch("krum_select");
+}
+
+// ---- allocation-free Multi-Krum ----------------------------------------------------------------------
+// Split-K partial Gram matrices normally live in a buffer the caller allocates (bsc_gram_simt ->
+// bsc_krum_select).  Some callers cannot allocate device memory at the point where they need a Krum
+// verdict: code running inside a region where cudaMalloc is forbidden or would serialise the device
+// (a verifier loop that must not touch the allocator between blocks, a host that embeds this library
+// under a fixed memory budget handed out at start-up, a plug-in called from a framework that owns the
+// caching allocator).  For them the partials go into the fixed array below, which belongs to the
+// library image: every GPU that loads libbiscotti_b200.so holds these 512 KiB until the process exits.
+#define BSC_KRUM_STATIC_MAX_PEERS 128
+#define BSC_KRUM_STATIC_MAX_SPLITS 8
+static __device__ __align__(256) float g_krum_static_scratch[BSC_KRUM_STATIC_MAX_SPLITS * BSC_KRUM_STATIC_MAX_PEERS *
+                                                             BSC_KRUM_STATIC_MAX_PEERS];
+static float* g_krum_static_ptr[64] = {nullptr};   // device address of the array, per device ordinal
+static std::mutex g_krum_static_mu;
+
+// split count used by bsc_krum_scores_static for a given dimension (so a caller can reproduce the same
+// reduction order with the allocating entry points)
+int bsc_krum_static_splits(int d) {
+  int ks = d / 512;
+  if (ks < 1) ks = 1;
+  if (ks > BSC_KRUM_STATIC_MAX_SPLITS) ks = BSC_KRUM_STATIC_MAX_SPLITS;
+  return ks;
+}
+
+// No counterpart in the reference (its Krum runs in NumPy on the host, client_obj.py:114-143); this is
+// the allocation-free variant of bsc_gram_simt + bsc_krum_select for callers that cannot call
+// cudaMalloc.  Inputs: A [n][lda] fp32 updates (first d columns used), norms [n] squared row norms.
+// Outputs: scores [n], accept [n] (1 = in the Multi-Krum accept set).  Limits: 3 <= n <= 128 peers, any
+// d >= 1; larger n is rejected with -1 and a message on stderr.  Nothing is allocated or freed, here or
+// in any library it calls.  The first call on each device looks up the device address of the scratch
+// array (cudaGetSymbolAddress, which may load the CUDA module), so make that first call before starting
+// any stream capture.  All calls on a device share the one scratch array: a call rewrites every word it
+// later reads (nothing has to start at zero, and contents left by the previous call are never
+// consumed), but two calls whose kernels overlap on the GPU — different streams, or different host
+// threads — race on it; serialise them on one stream.
+int bsc_krum_scores_static(const float* A, const float* norms, int n, int d, int lda, int clip, float* scores,
+                           unsigned char* accept, void* stream) {
+  if (n > BSC_KRUM_STATIC_MAX_PEERS || n < 3 || d < 1 || clip < 0 || clip >= n) {
+    fprintf(stderr,
+            "[biscotti_b200] bsc_krum_scores_static: n=%d d=%d clip=%d outside the static scratch limits "
+            "(3 <= n <= %d peers, d >= 1, 0 <= clip < n); use bsc_gram_simt + bsc_krum_select with your own buffer\n",
+            n, d, clip, BSC_KRUM_STATIC_MAX_PEERS);
+    return -1;
+  }
+  int dev = 0;
+  BSC_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return -2;
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_krum_static_mu);
+    if (!g_krum_static_ptr[dev]) {
+      // the symbol's name is only a host-side handle; kernels need its address on the current device
+      float* p = nullptr;
+      BSC_CHECK(cudaGetSymbolAddress((void**)&p, g_krum_static_scratch));
+      g_krum_static_ptr[dev] = p;
+    }
+    scratch = g_krum_static_ptr[dev];
+  }
+  const int ksplit = bsc_krum_static_splits(d);
+  const int nt = (n + 31) / 32;
+  dim3 grid(nt, nt, ksplit);
+  // partials are stored [ksplit][n][n]; every (i, j) of every split is written by this launch
+  gram_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A, scratch, n, d, lda, ksplit);
+  int rc = finish_launch("krum_scores_static/gram");
+  if (rc) return rc;
+  int np2 = 32;
+  while (np2 < n) np2 <<= 1;
+  const size_t smem = ((size_t)8 * np2 + n) * sizeof(float);
+  krum_select_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(scratch, ksplit, n, norms, n, clip, scores, accept,
+                                                              nullptr, np2);
+  return finish_launch("krum_scores_static/select");
 }
 
 int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F,

@@ -38,6 +38,23 @@ int bsc_gram_simt(const float* A, float* Gpart, int n, int d, int lda, int kspli
 
 int bsc_krum_select(const float* Gpart, int nsplit, int ldg, const float* norms, int n, int clip, float* scores, unsigned char* accept, float* Dout, void* stream);
 
+// split count used by bsc_krum_scores_static for a given dimension (so a caller can reproduce the same
+// reduction order with the allocating entry points)
+int bsc_krum_static_splits(int d);
+
+// No counterpart in the reference (its Krum runs in NumPy on the host, client_obj.py:114-143); this is
+// the allocation-free variant of bsc_gram_simt + bsc_krum_select for callers that cannot call
+// cudaMalloc.  Inputs: A [n][lda] fp32 updates (first d columns used), norms [n] squared row norms.
+// Outputs: scores [n], accept [n] (1 = in the Multi-Krum accept set).  Limits: 3 <= n <= 128 peers, any
+// d >= 1; larger n is rejected with -1 and a message on stderr.  Nothing is allocated or freed, here or
+// in any library it calls.  The first call on each device looks up the device address of the scratch
+// array (cudaGetSymbolAddress, which may load the CUDA module), so make that first call before starting
+// any stream capture.  All calls on a device share the one scratch array: a call rewrites every word it
+// later reads (nothing has to start at zero, and contents left by the previous call are never
+// consumed), but two calls whose kernels overlap on the GPU — different streams, or different host
+// threads — race on it; serialise them on one stream.
+int bsc_krum_scores_static(const float* A, const float* norms, int n, int d, int lda, int clip, float* scores, unsigned char* accept, void* stream);
+
 int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F, int C, int ldw, void* stream);
 
 int bsc_eval_logistic(const float* Wc, const float* base, const float* X, const float* y, int* wrong, int M, int N, int F, int ldw, void* stream);
