@@ -70,8 +70,10 @@ HD F25 f25_carry(int64_t h[10]) {
 }
 
 // h = f*g (dbl = false) or 2*f*g (dbl = true); inputs bounded by 1.65*2^26, output by 1.01*2^25/2^26
+// A real function on the device (see HDNI in field.cuh): one warp per SM runs this kernel, so every
+// instruction-cache miss is fully exposed; inlined, one window step is ~7k instructions (118 KB).
 template <bool DBL>
-HD F25 f25_mul_t(const F25& f, const F25& g) {
+HDNI F25 f25_mul_t(const F25& f, const F25& g) {
   int32_t g19[10], f2[10];
 #pragma unroll
   for (int i = 0; i < 10; i++) {

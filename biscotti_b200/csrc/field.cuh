@@ -11,9 +11,14 @@
 #if defined(__CUDACC__)
 #define HD __host__ __device__ __forceinline__
 #define HDN __host__ __device__
+// fe_mul is deliberately a real function on the device: fully inlined, a mixed point addition is ~5k
+// SASS instructions (80 KB) and the MSM kernels stall on instruction fetch (ncu: stall_no_instruction is
+// the top reason); as a call the hot loop fits the instruction cache.
+#define HDNI __host__ __device__ __noinline__
 #else
 #define HD inline
 #define HDN
+#define HDNI
 #endif
 
 namespace bsc {
@@ -201,7 +206,7 @@ HD Fe<M> fe_dbl(const Fe<M>& a) { return fe_add(a, a); }
 
 // Montgomery product a*b*R^-1 mod m (CIOS, 32-bit limbs, 64-bit partial products).
 template <class M>
-HD Fe<M> fe_mul(const Fe<M>& a, const Fe<M>& b) {
+HDNI Fe<M> fe_mul(const Fe<M>& a, const Fe<M>& b) {
   uint32_t t[10];
 #pragma unroll
   for (int i = 0; i < 10; i++) t[i] = 0;

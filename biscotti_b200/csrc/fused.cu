@@ -1,0 +1,482 @@
+// Fused compute + collective kernels over NVLink peer memory (the two communication-bound paths).
+//
+// 1. krum_gram_fused_kernel — the reference's workers->verifiers fan-out (every noised update sent to
+//    every verifier, DistSys/main.go:1666-1775, krum.go:227-365) fused with the Gram GEMM of
+//    get_krum_scores (ML/Pytorch/client_obj.py:132-143).  Instead of all-gathering the n x d updates,
+//    the K (= d) dimension is sharded over the GPUs: GPU r computes the partial Gram over its slice of
+//    d for ALL peers, pulling the other GPUs' rows of that slice tile by tile with TMA straight from
+//    their memory into the tcgen05 pipeline (1/8 of the all-gather bytes cross NVLink), and pushes its
+//    128x128 fp32 partial into every GPU's reduction buffer with peer stores.  krum_select_fused_kernel
+//    then reduces the partials in fixed order (bit-identical on every GPU), forms distances, sorts,
+//    scores and selects.
+// 2. secagg_fused_kernel — the workers->miners share scatter, the miners' fold and the leader's gather
+//    (main.go:1847-1952, 2157-2235; kyber.go:244-287, 809-857; honest.go:391-502) as one
+//    reduce-scatter + reconstruct + SGD step + all-gather: the GPU that owns a chunk range pulls every
+//    GPU's partial share sums with peer loads, adds them, recovers the polynomial exactly, verifies the
+//    redundant shares, de-quantises, steps the weights and stores the new slice into every GPU's copy.
+//
+// Cross-GPU ordering uses the epoch flags of symm.cuh; all waits are bounded.
+#include "common.cuh"
+#include "symm.cuh"
+#include "tc_ptx.cuh"
+#include "secagg_math.cuh"
+#include <cuda_bf16.h>
+#include <string.h>
+
+namespace bsc {
+
+constexpr int FG_BM = 128;
+constexpr int FG_BK = 64;
+constexpr int FG_STAGES = 3;
+constexpr int FG_TILE_BYTES = FG_BM * FG_BK * 2;
+constexpr int FG_STAGE_BYTES = 4 * FG_TILE_BYTES;
+constexpr int FG_THREADS = 192;
+constexpr int FG_TMEM_COLS = 128;
+constexpr size_t FG_SMEM = (size_t)FG_STAGES * FG_STAGE_BYTES + 1024 + 256;
+
+struct GramFusedParams {
+  CUtensorMap hi[SYMM_MAX_WORLD];   // rank q's bf16 hi plane [Sr][ldh], box (64 x Sr), SWIZZLE_128B
+  CUtensorMap lo[SYMM_MAX_WORLD];
+  PeerTable gpart;                  // rank q's reduction buffer [world*ksplit][ldg][ldg] fp32
+  PeerTable flags;                  // rank q's flag array
+  unsigned int* done_counter;       // local, zero between launches
+  unsigned long long epoch;
+  int world, rank, Sr, ntile, ldg;
+  int kb_lo, kb_cnt, kb_per, ksplit;
+};
+
+__global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __grid_constant__ GramFusedParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  const uint32_t bars = tiles + FG_STAGES * FG_STAGE_BYTES;
+  const uint32_t bar_full = bars, bar_empty = bars + 8 * FG_STAGES, bar_tmem = bars + 16 * FG_STAGES;
+  const uint32_t tmem_slot = bar_tmem + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int ti = 0, tj = 0;
+  {
+    int p = blockIdx.x;
+    for (ti = 0; ti < P.ntile; ti++) {
+      const int rowlen = P.ntile - ti;
+      if (p < rowlen) {
+        tj = ti + p;
+        break;
+      }
+      p -= rowlen;
+    }
+  }
+  const bool diag = (ti == tj);
+  const int split = blockIdx.y;
+  const int kb0 = P.kb_lo + split * P.kb_per;
+  int nkb = min(P.kb_lo + P.kb_cnt, kb0 + P.kb_per) - kb0;
+  if (nkb < 0) nkb = 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < FG_STAGES; s++) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    mbar_init(bar_tmem, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(FG_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  const int sub = FG_BM / P.Sr;   // TMA boxes (= owning ranks) per 128-row tile
+
+  if (warp == 0) {
+    if (lane == 0 && nkb > 0) {
+      // every rank must have finished writing this block's planes before its rows are pulled
+      symm_wait_all(reinterpret_cast<const unsigned long long*>(P.flags.ptr[P.rank]), P.world, SLOT_PLANES, P.epoch);
+      asm volatile("fence.proxy.async;" ::: "memory");
+      for (int kb = 0; kb < nkb; kb++) {
+        const int s = kb % FG_STAGES;
+        const uint32_t ph = (uint32_t)(kb / FG_STAGES) & 1u;
+        mbar_wait(bar_empty + 8 * s, ph ^ 1u);
+        const uint32_t st = tiles + s * FG_STAGE_BYTES;
+        mbar_expect_tx(bar_full + 8 * s, diag ? 2 * FG_TILE_BYTES : 4 * FG_TILE_BYTES);
+        const int kx = (kb0 + kb) * FG_BK;
+        for (int j = 0; j < sub; j++) {
+          const int owner = ti * sub + j;
+          const uint32_t off = (uint32_t)j * P.Sr * 128u;   // Sr % 8 == 0 keeps every box on a 1024-B swizzle atom
+          tma_load_2d(st + off, &P.hi[owner], kx, 0, bar_full + 8 * s);
+          tma_load_2d(st + FG_TILE_BYTES + off, &P.lo[owner], kx, 0, bar_full + 8 * s);
+        }
+        if (!diag) {
+          for (int j = 0; j < sub; j++) {
+            const int owner = tj * sub + j;
+            const uint32_t off = (uint32_t)j * P.Sr * 128u;
+            tma_load_2d(st + 2 * FG_TILE_BYTES + off, &P.hi[owner], kx, 0, bar_full + 8 * s);
+            tma_load_2d(st + 3 * FG_TILE_BYTES + off, &P.lo[owner], kx, 0, bar_full + 8 * s);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && nkb > 0) {
+      const uint32_t idesc = umma_idesc_bf16_128x128();
+      for (int kb = 0; kb < nkb; kb++) {
+        const int s = kb % FG_STAGES;
+        const uint32_t ph = (uint32_t)(kb / FG_STAGES) & 1u;
+        mbar_wait(bar_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t st = tiles + s * FG_STAGE_BYTES;
+        const uint64_t a_hi = umma_desc_sw128(st), a_lo = umma_desc_sw128(st + FG_TILE_BYTES);
+        const uint64_t b_hi = diag ? a_hi : umma_desc_sw128(st + 2 * FG_TILE_BYTES);
+        const uint64_t b_lo = diag ? a_lo : umma_desc_sw128(st + 3 * FG_TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < FG_BK / 16; k++) {
+          const uint64_t off = (uint64_t)((k * 16 * 2) >> 4);
+          umma_bf16(tmem_base, a_hi + off, b_hi + off, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_bf16(tmem_base, a_hi + off, b_lo + off, idesc, 1u);
+          umma_bf16(tmem_base, a_lo + off, b_hi + off, idesc, 1u);
+        }
+        umma_commit(bar_empty + 8 * s);
+      }
+      umma_commit(bar_tmem);
+    }
+  } else {
+    // epilogue: TMEM -> registers -> every rank's reduction buffer (peer stores over NVLink)
+    const int q4 = warp & 3;
+    if (nkb > 0) {
+      mbar_wait(bar_tmem, 0);
+      tc_fence_after();
+    }
+    const size_t part = ((size_t)P.rank * P.ksplit + split) * P.ldg * P.ldg;
+    const int row = ti * FG_BM + q4 * 32 + lane;
+#pragma unroll 1
+    for (int cc = 0; cc < FG_BM / 32; cc++) {
+      uint32_t v[32];
+      if (nkb > 0) {
+        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cc * 32), v);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++) v[c] = 0u;
+      }
+      const int col0 = tj * FG_BM + cc * 32;
+      for (int dst_rank = 0; dst_rank < P.world; dst_rank++) {
+        float* G = reinterpret_cast<float*>(P.gpart.ptr[dst_rank]) + part;
+        float4* dst = reinterpret_cast<float4*>(G + (size_t)row * P.ldg + col0);
+#pragma unroll
+        for (int c = 0; c < 8; c++)
+          dst[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
+                               __uint_as_float(v[4 * c + 3]));
+        if (!diag) {
+#pragma unroll
+          for (int c = 0; c < 32; c++) G[(size_t)(col0 + c) * P.ldg + row] = __uint_as_float(v[c]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(FG_TMEM_COLS) : "memory");
+  }
+  // last CTA of this rank publishes "my partials are in everybody's buffer"
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned int total = gridDim.x * gridDim.y;
+    const unsigned int old = atomicAdd(P.done_counter, 1u);
+    if (old == total - 1) {
+      *P.done_counter = 0;
+      symm_signal_all(P.flags, P.world, P.rank, SLOT_GRAM, P.epoch);
+    }
+  }
+}
+
+// Tail of the fused Krum path.  Identical on every rank: waits until all ranks' partials have landed
+// in the local reduction buffer, reduces them in (rank, split) order, takes squared norms from the
+// diagonal of the reduced Gram (no norm exchange needed), and runs the Multi-Krum scoring/selection
+// over the participating slots rows[0..n).
+__global__ void __launch_bounds__(256) krum_select_fused_kernel(const float* __restrict__ Gpart, int nsplit, int ldg,
+                                                                const int* __restrict__ rows, int n, int clip,
+                                                                const unsigned long long* __restrict__ my_flags,
+                                                                int world, unsigned long long epoch,
+                                                                float* __restrict__ scores,
+                                                                unsigned char* __restrict__ accept, int np2) {
+  extern __shared__ float srow[];   // [nwarp][np2] rows, [n] scores, [n] diag
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  float* myrow = srow + (size_t)warp * np2;
+  float* ssc = srow + (size_t)nwarp * np2;
+  float* sdiag = ssc + n;
+  __shared__ int srows[1024];
+  if (tid == 0) symm_wait_all(my_flags, world, SLOT_GRAM, epoch);
+  __syncthreads();
+  for (int i = tid; i < n; i += blockDim.x) {
+    const int r = rows[i];
+    srows[i] = r;
+    float g = 0.f;
+    for (int s = 0; s < nsplit; s++) g += Gpart[((size_t)s * ldg + r) * ldg + r];
+    sdiag[i] = g;
+  }
+  __syncthreads();
+  const int group = n - clip;
+  for (int i = warp; i < n; i += nwarp) {
+    const float ni = sdiag[i];
+    const int ri = srows[i];
+    for (int j = lane; j < np2; j += 32) {
+      float v = INFINITY;
+      if (j < n) {
+        const int rj = srows[j];
+        float g = 0.f;
+        for (int s = 0; s < nsplit; s++) g += Gpart[((size_t)s * ldg + ri) * ldg + rj];
+        v = ni + sdiag[j] - 2.f * g;
+      }
+      myrow[j] = v;
+    }
+    __syncwarp();
+    for (int k = 2; k <= np2; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = lane; t < np2; t += 32) {
+          const int ixj = t ^ j;
+          if (ixj > t) {
+            const float a = myrow[t], b = myrow[ixj];
+            const bool up = ((t & k) == 0);
+            if ((a > b) == up) {
+              myrow[t] = b;
+              myrow[ixj] = a;
+            }
+          }
+        }
+        __syncwarp();
+      }
+    }
+    float s = 0.f;
+    for (int j = 1 + lane; j < group - 1; j += 32) s += myrow[j];
+    s = warp_sum(s);
+    if (lane == 0) {
+      ssc[i] = s;
+      scores[i] = s;
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += blockDim.x) {
+    const float si = ssc[i];
+    int rank = 0;
+    for (int j = 0; j < n; j++) {
+      const float sj = ssc[j];
+      rank += (sj < si) || (sj == si && j < i);
+    }
+    accept[i] = rank < (n - clip) ? 1 : 0;
+  }
+}
+
+// ---- secure aggregation -------------------------------------------------------------------------------
+struct SecaggFusedParams {
+  PeerTable ypart;   // rank q's partial share sums [nchunk][S] int64 over its local contributors
+  PeerTable w64;     // rank q's fp64 master weights [d]
+  PeerTable w32;     // rank q's fp32 working copy [d]
+  PeerTable flags;
+  unsigned int* done_counter;
+  int* bad;          // local int[2]
+  unsigned long long epoch;
+  double scale;
+  int world, rank, S, d, c0, nc;
+  int xs[POLY_SIZE];
+  unsigned char avail[MAX_SHARES];
+};
+
+__global__ void __launch_bounds__(128) secagg_fused_kernel(const __grid_constant__ SecaggFusedParams P) {
+  if (threadIdx.x == 0)
+    symm_wait_all(reinterpret_cast<const unsigned long long*>(P.flags.ptr[P.rank]), P.world, SLOT_SHARES, P.epoch);
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < P.nc) {
+    const int c = P.c0 + i;
+    // reduce-scatter: pull this chunk's share sums from every rank (int64 adds: order-independent)
+    int64_t ysum[MAX_SHARES];
+    for (int s = 0; s < P.S; s++) {
+      uint64_t acc = 0;
+      for (int q = 0; q < P.world; q++)
+        acc += (uint64_t) reinterpret_cast<const long long*>(P.ypart.ptr[q])[(size_t)c * P.S + s];
+      ysum[s] = (int64_t)acc;
+    }
+    int lx[POLY_SIZE];
+    int64_t ly[POLY_SIZE], coef[POLY_SIZE];
+#pragma unroll
+    for (int j = 0; j < POLY_SIZE; j++) {
+      lx[j] = P.xs[j];
+      ly[j] = ysum[lx[j]];
+    }
+    const bool exact = shamir_recover(lx, ly, coef);
+    if (!exact) atomicAdd(&P.bad[0], 1);
+    int mism = 0;
+    for (int s = 0; s < P.S; s++)
+      if (P.avail[s]) mism += (shamir_eval(coef, s) != ysum[s]);
+    if (mism) atomicAdd(&P.bad[1], mism);
+    const double* wl = reinterpret_cast<const double*>(P.w64.ptr[P.rank]);
+#pragma unroll
+    for (int j = 0; j < POLY_SIZE; j++) {
+      const int k = c * POLY_SIZE + j;
+      if (k < P.d) {
+        const double nw = wl[k] + (double)coef[j] / P.scale;
+        // all-gather: the owner stores the new coordinate into every rank's copy
+        for (int q = 0; q < P.world; q++) {
+          reinterpret_cast<double*>(P.w64.ptr[q])[k] = nw;
+          reinterpret_cast<float*>(P.w32.ptr[q])[k] = (float)nw;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned int old = atomicAdd(P.done_counter, 1u);
+    if (old == gridDim.x - 1) {
+      *P.done_counter = 0;
+      symm_signal_all(P.flags, P.world, P.rank, SLOT_WEIGHTS, P.epoch);
+    }
+  }
+}
+
+__global__ void symm_signal_kernel(PeerTable flags, int world, int rank, int slot, unsigned long long epoch) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) symm_signal_all(flags, world, rank, slot, epoch);
+}
+__global__ void symm_wait_kernel(const unsigned long long* my_flags, int world, int slot, unsigned long long epoch) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) symm_wait_all(my_flags, world, slot, epoch);
+}
+
+int make_plane_map(CUtensorMap* map, const void* base, int rows, int ld, int box_rows);   // gram_tc.cu
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+// ---- symmetric memory plumbing (cudaMalloc + CUDA IPC; handles travel over torch.distributed) ----------
+int bsc_symm_alloc(size_t bytes, void** out) {
+  BSC_CHECK(cudaMalloc(out, bytes));
+  BSC_CHECK(cudaMemset(*out, 0, bytes));
+  return 0;
+}
+int bsc_symm_free(void* p) {
+  BSC_CHECK(cudaFree(p));
+  return 0;
+}
+int bsc_ipc_get_handle(void* p, unsigned char out[64]) {
+  cudaIpcMemHandle_t h;
+  BSC_CHECK(cudaIpcGetMemHandle(&h, p));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(out, &h, 64);
+  return 0;
+}
+int bsc_ipc_open_handle(const unsigned char in[64], void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, in, 64);
+  BSC_CHECK(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int bsc_ipc_close_handle(void* p) {
+  BSC_CHECK(cudaIpcCloseMemHandle(p));
+  return 0;
+}
+int bsc_symm_signal(void* const* flag_ptrs, int world, int rank, int slot, unsigned long long epoch, void* stream) {
+  PeerTable t;
+  for (int q = 0; q < SYMM_MAX_WORLD; q++) t.ptr[q] = q < world ? flag_ptrs[q] : nullptr;
+  symm_signal_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(t, world, rank, slot, epoch);
+  return finish_launch("symm_signal");
+}
+int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long epoch, void* stream) {
+  symm_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const unsigned long long*)my_flags, world, slot, epoch);
+  return finish_launch("symm_wait");
+}
+
+// Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
+// [world*ksplit][ldg][ldg] fp32 reduction buffer, flags[q]: rank q's flag array.  world*Sr must be a
+// multiple of 128 and Sr a multiple of 8.
+int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world,
+                        int rank, int Sr, int ldh, int ksplit, int ldg, unsigned int* done_counter,
+                        unsigned long long epoch, void* stream) {
+  if (world < 1 || world > SYMM_MAX_WORLD || Sr % 8 != 0 || FG_BM % Sr != 0 || (world * Sr) % FG_BM != 0 ||
+      ldh % FG_BK != 0)
+    return -1;
+  GramFusedParams P;
+  memset(&P, 0, sizeof(P));
+  for (int q = 0; q < world; q++) {
+    int rc = make_plane_map(&P.hi[q], plane_hi[q], Sr, ldh, Sr);
+    if (rc) return rc;
+    rc = make_plane_map(&P.lo[q], plane_lo[q], Sr, ldh, Sr);
+    if (rc) return rc;
+    P.gpart.ptr[q] = gpart[q];
+    P.flags.ptr[q] = flags[q];
+  }
+  P.done_counter = done_counter;
+  P.epoch = epoch;
+  P.world = world;
+  P.rank = rank;
+  P.Sr = Sr;
+  P.ntile = world * Sr / FG_BM;
+  P.ldg = ldg;
+  if (ldg != P.ntile * FG_BM) return -1;
+  const int kb_total = ldh / FG_BK;
+  const int per_rank = (kb_total + world - 1) / world;     // this rank's slice of the K dimension
+  P.kb_lo = min(kb_total, rank * per_rank);
+  P.kb_cnt = min(kb_total, P.kb_lo + per_rank) - P.kb_lo;
+  P.ksplit = ksplit;
+  P.kb_per = (max(P.kb_cnt, 1) + ksplit - 1) / ksplit;
+  static bool configured = false;
+  if (!configured) {
+    BSC_CHECK(cudaFuncSetAttribute(krum_gram_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FG_SMEM));
+    configured = true;
+  }
+  dim3 grid(P.ntile * (P.ntile + 1) / 2, ksplit);
+  krum_gram_fused_kernel<<<grid, FG_THREADS, FG_SMEM, (cudaStream_t)stream>>>(P);
+  return finish_launch("krum_gram_fused");
+}
+
+int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const int* rows, int n, int clip,
+                          const void* my_flags, int world, unsigned long long epoch, float* scores,
+                          unsigned char* accept, void* stream) {
+  if (n > 1024 || n < 3) return -1;
+  int np2 = 32;
+  while (np2 < n) np2 <<= 1;
+  const size_t smem = ((size_t)8 * np2 + 2 * n) * sizeof(float);
+  krum_select_fused_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(gpart_local, nsplit, ldg, rows, n, clip,
+                                                                    (const unsigned long long*)my_flags, world, epoch,
+                                                                    scores, accept, np2);
+  return finish_launch("krum_select_fused");
+}
+
+// Fused reduce-scatter + reconstruct + SGD step + all-gather for this rank's chunk range [c0, c0+nc).
+int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank,
+                     int S, int d, int c0, int nc, const int* xs_host, const unsigned char* avail_host, double scale,
+                     unsigned int* done_counter, int* bad, unsigned long long epoch, void* stream) {
+  if (world < 1 || world > SYMM_MAX_WORLD || S > MAX_SHARES) return -1;
+  SecaggFusedParams P;
+  memset(&P, 0, sizeof(P));
+  for (int q = 0; q < world; q++) {
+    P.ypart.ptr[q] = ypart[q];
+    P.w64.ptr[q] = w64[q];
+    P.w32.ptr[q] = w32[q];
+    P.flags.ptr[q] = flags[q];
+  }
+  P.done_counter = done_counter;
+  P.bad = bad;
+  P.epoch = epoch;
+  P.scale = scale;
+  P.world = world;
+  P.rank = rank;
+  P.S = S;
+  P.d = d;
+  P.c0 = c0;
+  P.nc = nc;
+  for (int j = 0; j < POLY_SIZE; j++) P.xs[j] = xs_host[j];
+  for (int s = 0; s < S; s++) P.avail[s] = avail_host ? avail_host[s] : 1;
+  const int blocks = max(1, (nc + 127) / 128);
+  secagg_fused_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(P);
+  return finish_launch("secagg_fused");
+}
+
+}  // extern "C"

@@ -115,7 +115,8 @@ def noise_row(d: int, seed: int, peer: int, slot: int, scale: float, device="cpu
     return out
 
 
-def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_planes: bool = True, ldh=None):
+def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_planes: bool = True, ldh=None,
+              out_hi=None, out_lo=None):
     """Un = U + mean_q noise(q); returns (Un fp32 [P,ldu], hi bf16 [P,ldh], lo bf16 [P,ldh], norms [P]).
     noisers: int32 [P, nn] global ids (-1 = unused slot)."""
     P, ldu = U.shape
@@ -137,8 +138,12 @@ def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_plane
             lo = torch.nn.functional.pad(lo, (0, pad))
         return Un, hi.contiguous(), lo.contiguous(), (Un[:, :d] ** 2).sum(dim=1)
     Un = torch.empty_like(U)
-    hi = torch.empty(P, ldh, dtype=torch.bfloat16, device=U.device) if want_planes else None
-    lo = torch.empty(P, ldh, dtype=torch.bfloat16, device=U.device) if want_planes else None
+    if out_hi is not None:      # caller-provided planes (rows >= P), e.g. views into symmetric peer memory
+        hi, lo = out_hi, out_lo
+        ldh = hi.stride(0)
+    else:
+        hi = torch.empty(P, ldh, dtype=torch.bfloat16, device=U.device) if want_planes else None
+        lo = torch.empty(P, ldh, dtype=torch.bfloat16, device=U.device) if want_planes else None
     norms = torch.empty(P, dtype=torch.float32, device=U.device)
     check(lib().bsc_noise_mix(ptr(U), ptr(noisers), nn, ctypes.c_ulonglong(seed & (2**64 - 1)), slot,
                               ctypes.c_float(scale), ptr(Un), ptr(hi), ptr(lo), ptr(norms), P, d, ldu, ldh,

@@ -44,12 +44,13 @@ def shares_eval(Q: torch.Tensor, S: int):
     return Y
 
 
-def share_sum(U: torch.Tensor, sel: torch.Tensor, d: int, S: int, precision: int = 4, c0: int = 0, nc: int | None = None):
+def share_sum(U: torch.Tensor, sel: torch.Tensor, d: int, S: int, precision: int = 4, c0: int = 0, nc: int | None = None,
+              out: torch.Tensor | None = None):
     """Aggregated shares of the selected rows for chunk range [c0, c0+nc): Ysum [nc, S] int64."""
     nc = nchunks(d) - c0 if nc is None else nc
     scale = float(10 ** precision)
     if U.is_cuda:
-        Ysum = torch.empty(nc, S, dtype=torch.int64, device=U.device)
+        Ysum = out if out is not None else torch.empty(nc, S, dtype=torch.int64, device=U.device)
         check(lib().bsc_share_sum(ptr(U), ptr(sel), sel.numel(), d, U.stride(0), c0, nc, S, ctypes.c_double(scale),
                                   ptr(Ysum), stream(U.device)), "share_sum")
         return Ysum

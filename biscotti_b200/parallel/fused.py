@@ -1,0 +1,211 @@
+"""Symmetric peer memory + the fused compute/collective kernels (csrc/fused.cu).
+
+Each rank cudaMalloc's one region with a fixed layout (flags, bf16 planes, Gram reduction buffer, share
+sums, weights), exports it with CUDA IPC, and maps every other rank's region (handles are exchanged with
+`torch.distributed.all_gather_object`; that is all NCCL/torch.distributed is used for on this path
+besides tiny metadata).  Kernels then address remote data directly over NVLink:
+
+  * `krum_fused`   : TMA pulls of remote update tiles inside the tcgen05 Gram kernel + peer stores of the
+                     partial Gram (all-gather fused into the GEMM, K sharded over GPUs)
+  * `secagg_fused` : peer loads of partial share sums (reduce-scatter), exact reconstruction, SGD step,
+                     peer stores of the new weights (all-gather)
+
+Reference exchanges replaced: DistSys/main.go:1666-1775 (updates -> verifiers), :1847-1952 + :2157-2235
+(shares -> miners -> leader), :1403-1444 (block flood of the new weights).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from ..config import BiscottiConfig
+from ..ops.ml import pad_to
+from .comm import NcclComm
+
+SLOT_PLANES, SLOT_GRAM, SLOT_SHARES, SLOT_WEIGHTS, SLOT_POINTS = 0, 1, 2, 3, 4
+SYMM_MAX_WORLD = 8
+
+c_i, c_p, c_ull, c_d, c_sz = ctypes.c_int, ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_double, ctypes.c_size_t
+
+
+class _RawCuda:
+    """Minimal __cuda_array_interface__ carrier so torch can view a raw device pointer without copying."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
+def tensor_from_ptr(ptr: int, shape, dtype: torch.dtype, device) -> torch.Tensor:
+    ts = {torch.float32: "<f4", torch.float64: "<f8", torch.int64: "<i8", torch.int32: "<i4", torch.uint8: "|u1",
+          torch.bfloat16: "<i2"}[dtype]
+    t = torch.as_tensor(_RawCuda(ptr, shape, ts), device=device)
+    return t.view(torch.bfloat16) if dtype == torch.bfloat16 else t
+
+
+def _declare(L):
+    L.bsc_symm_alloc.argtypes = [c_sz, ctypes.POINTER(c_p)]
+    L.bsc_symm_free.argtypes = [c_p]
+    L.bsc_ipc_get_handle.argtypes = [c_p, c_p]
+    L.bsc_ipc_open_handle.argtypes = [ctypes.c_char_p, ctypes.POINTER(c_p)]
+    L.bsc_ipc_close_handle.argtypes = [c_p]
+    L.bsc_symm_signal.argtypes = [c_p, c_i, c_i, c_i, c_ull, c_p]
+    L.bsc_symm_wait.argtypes = [c_p, c_i, c_i, c_ull, c_p]
+    L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_ull, c_p]
+    L.bsc_krum_select_fused.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
+    L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_d, c_p, c_p, c_ull, c_p]
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed with code {rc}")
+
+
+class FusedComm(NcclComm):
+    def __init__(self, rank: int, world: int, device, cfg: BiscottiConfig, ksplit: int | None = None):
+        super().__init__(rank, world, device)
+        if world > SYMM_MAX_WORLD or 128 % world != 0:
+            raise ValueError("fused path supports 1, 2, 4 or 8 ranks")
+        self.L = _native.load()
+        _declare(self.L)
+        self.cfg = cfg
+        n, d = cfg.num_nodes, cfg.dim
+        self.per = (n + world - 1) // world
+        # slots per rank: >= local peers, multiple of 128/world (so world*Sr is a whole number of 128-row tiles)
+        self.Sr = max(8, 128 // world)
+        while self.Sr < self.per:
+            self.Sr *= 2
+        if self.Sr > 128:
+            raise ValueError("fused Gram path supports at most 128 peers per rank")
+        self.ldh = pad_to(d, 64)
+        self.ntile = world * self.Sr // 128
+        self.ldg = self.ntile * 128
+        kb_total = self.ldh // 64
+        per_rank_kb = (kb_total + world - 1) // world
+        self.ksplit = ksplit or max(1, min(per_rank_kb // 4 if per_rank_kb >= 8 else 1,
+                                           148 // max(1, self.ntile * (self.ntile + 1) // 2)))
+        self.S = cfg.total_shares
+        self.nchunk = cfg.nchunk
+        self.d = d
+        # ---- layout of the symmetric region
+        off = 0
+
+        def take(nbytes):
+            nonlocal off
+            o = off
+            off = (off + nbytes + 1023) // 1024 * 1024
+            return o
+
+        self.o_flags = take(8 * 8 * SYMM_MAX_WORLD)
+        self.o_cnt = take(64)
+        self.o_bad = take(64)
+        self.o_hi = take(self.Sr * self.ldh * 2)
+        self.o_lo = take(self.Sr * self.ldh * 2)
+        self.o_gpart = take(world * self.ksplit * self.ldg * self.ldg * 4)
+        self.o_ypart = take(self.nchunk * self.S * 8)
+        self.o_w64 = take(d * 8)
+        self.o_w32 = take(d * 4)
+        self.nbytes = off
+        base = c_p()
+        _check(self.L.bsc_symm_alloc(self.nbytes, ctypes.byref(base)), "symm_alloc")
+        self.base = base.value
+        handle = ctypes.create_string_buffer(64)
+        _check(self.L.bsc_ipc_get_handle(c_p(self.base), handle), "ipc_get_handle")
+        handles = [None] * world
+        if world > 1:
+            dist.all_gather_object(handles, handle.raw)
+        else:
+            handles = [handle.raw]
+        self.bases = []
+        for q in range(world):
+            if q == rank:
+                self.bases.append(self.base)
+            else:
+                p = c_p()
+                _check(self.L.bsc_ipc_open_handle(handles[q], ctypes.byref(p)), "ipc_open_handle")
+                self.bases.append(p.value)
+        dev = self.device
+        self.hi = tensor_from_ptr(self.base + self.o_hi, (self.Sr, self.ldh), torch.bfloat16, dev)
+        self.lo = tensor_from_ptr(self.base + self.o_lo, (self.Sr, self.ldh), torch.bfloat16, dev)
+        self.ypart = tensor_from_ptr(self.base + self.o_ypart, (self.nchunk, self.S), torch.int64, dev)
+        self.w64 = tensor_from_ptr(self.base + self.o_w64, (d,), torch.float64, dev)
+        self.w32 = tensor_from_ptr(self.base + self.o_w32, (d,), torch.float32, dev)
+        self.bad = tensor_from_ptr(self.base + self.o_bad, (2,), torch.int32, dev)
+        self.gpart = tensor_from_ptr(self.base + self.o_gpart, (world * self.ksplit, self.ldg, self.ldg), torch.float32, dev)
+        self._tables = {name: self._table(o) for name, o in (("flags", self.o_flags), ("hi", self.o_hi), ("lo", self.o_lo),
+                                                             ("gpart", self.o_gpart), ("ypart", self.o_ypart),
+                                                             ("w64", self.o_w64), ("w32", self.o_w32))}
+        if world > 1:
+            dist.barrier()
+
+    def _table(self, offset: int):
+        arr = (c_p * SYMM_MAX_WORLD)()
+        for q in range(self.world):
+            arr[q] = self.bases[q] + offset
+        return arr
+
+    def _stream(self):
+        return c_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ---- flags ----------------------------------------------------------------------------------
+    def signal(self, slot: int, epoch: int):
+        _check(self.L.bsc_symm_signal(self._tables["flags"], self.world, self.rank, slot, epoch, self._stream()), "signal")
+
+    def wait(self, slot: int, epoch: int):
+        _check(self.L.bsc_symm_wait(c_p(self.base + self.o_flags), self.world, slot, epoch, self._stream()), "wait")
+
+    def slot_of(self, peer: int) -> int:
+        return (peer // self.per) * self.Sr + (peer % self.per)
+
+    # ---- fused Krum -------------------------------------------------------------------------------
+    def krum_fused(self, krum_set, clip: int, epoch: int):
+        """Planes of this block must already be in self.hi / self.lo.  Returns accept (uint8, device)."""
+        n = len(krum_set)
+        dev = self.device
+        self.signal(SLOT_PLANES, epoch)
+        _check(self.L.bsc_krum_gram_fused(self._tables["hi"], self._tables["lo"], self._tables["gpart"],
+                                          self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
+                                          self.ldg, c_p(self.base + self.o_cnt), epoch, self._stream()), "krum_gram_fused")
+        rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32, device=dev)
+        scores = torch.empty(n, dtype=torch.float32, device=dev)
+        accept = torch.empty(n, dtype=torch.uint8, device=dev)
+        _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg,
+                                            c_p(rows.data_ptr()), n, clip, c_p(self.base + self.o_flags), self.world,
+                                            epoch, c_p(scores.data_ptr()), c_p(accept.data_ptr()), self._stream()),
+               "krum_select_fused")
+        return scores, accept
+
+    # ---- fused secure aggregation ---------------------------------------------------------------------
+    def chunk_range(self):
+        per = (self.nchunk + self.world - 1) // self.world
+        c0 = min(self.nchunk, self.rank * per)
+        return c0, min(self.nchunk, c0 + per) - c0
+
+    def secagg_fused(self, xs, avail, precision: int, epoch: int):
+        """self.ypart must hold this rank's partial share sums.  Updates self.w64 / self.w32 on every rank."""
+        self.signal(SLOT_SHARES, epoch)
+        c0, nc = self.chunk_range()
+        xs_a = (c_i * 10)(*xs)
+        av = (ctypes.c_ubyte * 64)(*(list(avail) + [0] * (64 - len(avail))))
+        self.bad.zero_()
+        _check(self.L.bsc_secagg_fused(self._tables["ypart"], self._tables["w64"], self._tables["w32"], self._tables["flags"],
+                                       self.world, self.rank, self.S, self.d, c0, nc, xs_a, av, float(10 ** precision),
+                                       c_p(self.base + self.o_cnt + 16), c_p(self.base + self.o_bad), epoch, self._stream()),
+               "secagg_fused")
+        self.wait(SLOT_WEIGHTS, epoch)
+        return self.bad
+
+    def all_gather_rows_u8(self, local: torch.Tensor) -> torch.Tensor:
+        """[per, k] uint8 blocks from every rank -> [world*per, k] (commitment bytes for the block)."""
+        per = self.per
+        pad = torch.zeros(per, local.shape[1], dtype=local.dtype, device=local.device)
+        pad[: local.shape[0]] = local[:per]
+        if self.world == 1:
+            return pad
+        out = torch.empty(self.world * per, local.shape[1], dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, pad)
+        return out

@@ -91,8 +91,16 @@ class BiscottiEngine:
             # non-zero genesis (CNNs): record it as the genesis block's GlobalW
             self.chain = Blockchain(self.d)
             self.chain.add_block(-1, w0.numpy(), [], None, timestamp=0)
-        self.w64 = w0.to(self.device)
-        self.w32 = self.w64.float()
+        self.fused = comm is not None and hasattr(comm, "krum_fused")
+        if self.fused:
+            # weights live in symmetric peer memory: the owner of a chunk range stores its new slice
+            # straight into every rank's copy (secagg_fused_kernel)
+            comm.w64.copy_(w0.to(self.device))
+            comm.w32.copy_(w0.float().to(self.device))
+            self.w64, self.w32 = comm.w64, comm.w32
+        else:
+            self.w64 = w0.to(self.device)
+            self.w32 = self.w64.float()
         self.U = torch.zeros(max(1, self.P), self.ldu, dtype=torch.float32, device=self.device)
         self.commit = None
         if cfg.commitments and cfg.secure_agg and cfg.mode == "biscotti":
@@ -214,7 +222,8 @@ class BiscottiEngine:
                     noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
             scale = cfg.noise_scale if use_noise else 0.0
             Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab.to(dev, non_blocking=True), cfg.seed, slot, scale, self.d,
-                                             ldh=self.ldh)
+                                             ldh=self.ldh, out_hi=self.comm.hi if self.fused else None,
+                                             out_lo=self.comm.lo if self.fused else None)
 
         # ---- 5. verification
         arrival = self._arrival_order(workers, "verify")
@@ -267,14 +276,22 @@ class BiscottiEngine:
                         aggC = self.commit.aggregate(chunkC, sel)           # [nchunk, 16]
                         agg_commit = (aggC, aggW)
             with self._phase("secagg"):
-                Ysum = secagg.share_sum(self.U, sel, self.d, self.S, cfg.precision) if sel.numel() else \
-                    torch.zeros(cfg.nchunk, self.S, dtype=torch.int64, device=dev)
-                if self.comm is not None:
-                    Ysum = self.comm.all_reduce_i64(Ysum)
                 xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
-                xs_t = torch.tensor(xs, dtype=torch.int32, device=dev)
-                av_t = torch.tensor(shares_avail, dtype=torch.uint8, device=dev)
-                _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
+                if self.fused:
+                    # reduce-scatter + reconstruct + SGD step + all-gather in one kernel over peer memory
+                    if sel.numel():
+                        secagg.share_sum(self.U, sel, self.d, self.S, cfg.precision, out=self.comm.ypart)
+                    else:
+                        self.comm.ypart.zero_()
+                    bad = self.comm.secagg_fused(xs, shares_avail, cfg.precision, it + 1)
+                else:
+                    Ysum = secagg.share_sum(self.U, sel, self.d, self.S, cfg.precision) if sel.numel() else \
+                        torch.zeros(cfg.nchunk, self.S, dtype=torch.int64, device=dev)
+                    if self.comm is not None:
+                        Ysum = self.comm.all_reduce_i64(Ysum)
+                    xs_t = torch.tensor(xs, dtype=torch.int32, device=dev)
+                    av_t = torch.tensor(shares_avail, dtype=torch.uint8, device=dev)
+                    _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
         else:
             with self._phase("secagg"):
                 if self.comm is not None and self.world > 1:
@@ -290,12 +307,17 @@ class BiscottiEngine:
             updates = []
             commits = {}
             if self.commit is not None and self.P:
-                cb = fullC_dev.cpu().numpy()
-                for p in contributors:
-                    if p in self.local_index:
-                        commits[p] = cb[self.local_index[p]].tobytes()
-            if self.comm is not None:
-                commits = self.comm.merge_dicts(commits)
+                if self.comm is not None and hasattr(self.comm, "all_gather_rows_u8"):
+                    cb = self.comm.all_gather_rows_u8(fullC_dev).cpu().numpy()      # [world*per, 64], row = peer id
+                    for p in contributors:
+                        commits[p] = cb[p].tobytes()
+                else:
+                    cb = fullC_dev.cpu().numpy()
+                    for p in contributors:
+                        if p in self.local_index:
+                            commits[p] = cb[self.local_index[p]].tobytes()
+                    if self.comm is not None:
+                        commits = self.comm.merge_dicts(commits)
             for p in contributors:
                 c = commits.get(p, b"")
                 sigs = []
@@ -336,8 +358,8 @@ class BiscottiEngine:
         if nk < 3:
             return list(krum_set)
         clip = int(math.floor(cfg.krum_adversary_frac * nk))
-        if self.comm is not None and hasattr(self.comm, "krum_fused"):
-            acc = self.comm.krum_fused(krum_set, hi, lo, norms, clip, self.local_index, self.owner)
+        if self.fused:
+            _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1)
         else:
             Uk = self._gather_rows(krum_set, Un)
             hik = self._gather_rows(krum_set, hi) if hi is not None else None

@@ -284,6 +284,34 @@ int bsc_lottery_roles(const uint8_t* input, int inlen, const int* stake, int n, 
 // noisers from a peer's private VRF output, excluding itself (vrf.go:54-100)
 int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n, int source, int want, int* noisers);
 
+/* --------------------------------------------------------------------------------------------
+ * fused.cu - 
+ * -------------------------------------------------------------------------------------------- */
+// ---- symmetric memory plumbing (cudaMalloc + CUDA IPC; handles travel over torch.distributed) ----------
+int bsc_symm_alloc(size_t bytes, void** out);
+
+int bsc_symm_free(void* p);
+
+int bsc_ipc_get_handle(void* p, unsigned char out[64]);
+
+int bsc_ipc_open_handle(const unsigned char in[64], void** out);
+
+int bsc_ipc_close_handle(void* p);
+
+int bsc_symm_signal(void* const* flag_ptrs, int world, int rank, int slot, unsigned long long epoch, void* stream);
+
+int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long epoch, void* stream);
+
+// Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
+// [world*ksplit][ldg][ldg] fp32 reduction buffer, flags[q]: rank q's flag array.  world*Sr must be a
+// multiple of 128 and Sr a multiple of 8.
+int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world, int rank, int Sr, int ldh, int ksplit, int ldg, unsigned int* done_counter, unsigned long long epoch, void* stream);
+
+int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const int* rows, int n, int clip, const void* my_flags, int world, unsigned long long epoch, float* scores, unsigned char* accept, void* stream);
+
+// Fused reduce-scatter + reconstruct + SGD step + all-gather for this rank's chunk range [c0, c0+nc).
+int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank, int S, int d, int c0, int nc, const int* xs_host, const unsigned char* avail_host, double scale, unsigned int* done_counter, int* bad, unsigned long long epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
