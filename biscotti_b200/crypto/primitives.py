@@ -109,8 +109,9 @@ class BatchedVRF:
     """All peers' VRF outputs on one block hash in one launch: Gamma_p = x_p * H(m) on the device
     (ed25519_scalarmult_kernel), output_p = SHAKE256(Gamma_p || m) on the host."""
 
-    def __init__(self, keys: list[VRFKey], device="cpu"):
+    def __init__(self, keys: list[VRFKey], device="cpu", kernel: str = "quad"):
         self.keys = keys
+        self.kernel = kernel   # "quad": four lanes per scalar multiplication; "r25": one thread each
         self.device = torch.device(device)
         words = np.stack([k.secret_scalar_words() for k in keys]).astype(np.uint32)
         self.scalars = torch.from_numpy(words.view(np.int32)).to(self.device)
@@ -158,7 +159,8 @@ class BatchedVRF:
         self._side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(self._side):
             self._hd.copy_(self._hpt_pinned, non_blocking=True)
-            rc = L.bsc_ed25519_scalarmult_r25(ctypes.c_void_p(self.scalars.data_ptr()),
+            kern = L.bsc_ed25519_scalarmult_quad if self.kernel == "quad" else L.bsc_ed25519_scalarmult_r25
+            rc = kern(ctypes.c_void_p(self.scalars.data_ptr()),
                                               ctypes.c_void_p(self._hd.data_ptr()), n,
                                               ctypes.c_void_p(self._gam.data_ptr()),
                                               ctypes.c_void_p(self._side.cuda_stream))

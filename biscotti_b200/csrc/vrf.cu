@@ -141,6 +141,111 @@ __global__ void __launch_bounds__(32) ed25519_scalarmult_r25_kernel(const unsign
   edr_compress(out + 32 * (size_t)i, edr_scalarmult(a, table));
 }
 
+// Quad-parallel form: four lanes cooperate on one scalar multiplication.  Every point operation of the
+// window method is two rounds of four independent field multiplications (doubling: XX, YY, 2ZZ, (X+Y)^2
+// then the four completed->extended products; addition: A, B, C, ZZ then the same four products), so a
+// quad runs each round in the time of one multiplication and exchanges the results with width-4
+// shuffles.  The sequential depth drops from ~2400 multiplications to ~630 rounds — this is what the
+// per-block critical path sees, because the VRF of block t+1 cannot start before block t is hashed.
+__device__ __forceinline__ F25 quad_pick(const F25& r, int src) {
+  F25 o;
+#pragma unroll
+  for (int i = 0; i < 10; i++) o.v[i] = __shfl_sync(0xffffffffu, r.v[i], src, 4);
+  return o;
+}
+__device__ __forceinline__ F25 f25_sel4(int j, const F25& a, const F25& b, const F25& c, const F25& d) {
+  F25 o;
+#pragma unroll
+  for (int i = 0; i < 10; i++) o.v[i] = j == 0 ? a.v[i] : (j == 1 ? b.v[i] : (j == 2 ? c.v[i] : d.v[i]));
+  return o;
+}
+
+__global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsigned char* __restrict__ scalars,
+                                                                      const unsigned char* __restrict__ hxy, int N,
+                                                                      unsigned char* __restrict__ out) {
+  __shared__ EdCached table[8];
+  if (threadIdx.x == 0) {
+    uint8_t b[64];
+    for (int i = 0; i < 64; i++) b[i] = hxy[i];
+    edr_build_table(table, edr_from_affine_bytes(b), f25_const_2d());
+  }
+  __syncthreads();
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int peer = gid >> 2, j = gid & 3;
+  const int pi = peer < N ? peer : N - 1;      // idle quads mirror the last peer so shuffles stay full-warp
+  // signed radix-16 recoding (every lane of the quad computes the same digits)
+  signed char e[64];
+  for (int i = 0; i < 32; i++) {
+    const unsigned char a = scalars[32 * (size_t)pi + i];
+    e[2 * i] = (signed char)(a & 15);
+    e[2 * i + 1] = (signed char)((a >> 4) & 15);
+  }
+  int carry = 0;
+  for (int i = 0; i < 63; i++) {
+    e[i] = (signed char)(e[i] + carry);
+    carry = (e[i] + 8) >> 4;
+    e[i] = (signed char)(e[i] - (carry << 4));
+  }
+  e[63] = (signed char)(e[63] + carry);
+
+  F25 X = f25_zero(), Y = f25_one(), Z = f25_one(), T = f25_zero();   // identity, replicated in the quad
+#pragma unroll 1
+  for (int i = 63; i >= 0; i--) {
+    const int dgt = e[i];
+    // steps 0..3 are doublings, step 4 (if the digit is non-zero) is the table addition
+    const int nsteps = dgt != 0 ? 5 : 4;
+#pragma unroll 1
+    for (int step = 0; step < nsteps; step++) {
+      F25 a, b;
+      const bool is_add = (step == 4);
+      bool neg = false;
+      if (!is_add) {
+        // lane 2 forms 2*Z*Z directly (operand Z+Z) so that every input of the second round stays inside
+        // the radix-2^25.5 multiplication bounds, exactly like the reference formulas' sq2
+        const F25 xy = f25_add(X, Y);
+        a = f25_sel4(j, X, Y, Z, xy);
+        b = f25_sel4(j, X, Y, f25_add(Z, Z), xy);
+      } else {
+        neg = dgt < 0;
+        const EdCached& q = table[(neg ? -dgt : dgt) - 1];
+        const F25 ypx = f25_add(Y, X), ymx = f25_sub(Y, X);
+        a = f25_sel4(j, ypx, ymx, q.T2d, Z);
+        b = f25_sel4(j, neg ? q.YmX : q.YpX, neg ? q.YpX : q.YmX, T, q.Z);
+      }
+      const F25 r = f25_mul(a, b);
+      const F25 r0 = quad_pick(r, 0), r1 = quad_pick(r, 1), r2 = quad_pick(r, 2), r3 = quad_pick(r, 3);
+      F25 cX, cY, cZ, cT;   // completed point ((cX:cZ), (cY:cT))
+      if (!is_add) {
+        // r0 = XX, r1 = YY, r2 = 2ZZ, r3 = (X+Y)^2
+        cY = f25_add(r1, r0);
+        cZ = f25_sub(r1, r0);
+        cX = f25_sub(r3, cY);
+        cT = f25_sub(r2, cZ);
+      } else {
+        // r0 = A, r1 = B, r2 = C, r3 = ZZ
+        const F25 D = f25_add(r3, r3);
+        cX = f25_sub(r0, r1);
+        cY = f25_add(r0, r1);
+        cZ = neg ? f25_sub(D, r2) : f25_add(D, r2);
+        cT = neg ? f25_add(D, r2) : f25_sub(D, r2);
+      }
+      // second round: X3 = cX*cT, Y3 = cY*cZ, Z3 = cZ*cT, T3 = cX*cY
+      const F25 a2 = f25_sel4(j, cX, cY, cZ, cX);
+      const F25 b2 = f25_sel4(j, cT, cZ, cT, cY);
+      const F25 s = f25_mul(a2, b2);
+      X = quad_pick(s, 0);
+      Y = quad_pick(s, 1);
+      Z = quad_pick(s, 2);
+      T = quad_pick(s, 3);
+    }
+  }
+  if (peer < N && j == 0) {
+    EdP3 p;
+    p.X = X; p.Y = Y; p.Z = Z; p.T = T;
+    edr_compress(out + 32 * (size_t)peer, p);
+  }
+}
+
 // batched SHA-256: digest of msgs[i] (each `len` bytes, `stride` apart) -> out[i][32]
 __global__ void sha256_batch_kernel(const unsigned char* __restrict__ msgs, int len, long long stride, int N,
                                     unsigned char* __restrict__ out) {
@@ -294,6 +399,13 @@ int bsc_ed25519_scalarmult_r25(const unsigned char* scalars, const unsigned char
   if (N == 0) return 0;
   ed25519_scalarmult_r25_kernel<<<(N + 31) / 32, 32, 0, (cudaStream_t)stream>>>(scalars, hxy, N, out);
   return finish_launch("ed25519_scalarmult_r25");
+}
+int bsc_ed25519_scalarmult_quad(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out,
+                                void* stream) {
+  if (N == 0) return 0;
+  const int threads = 4 * N;
+  ed25519_scalarmult_quad_kernel<<<(threads + 127) / 128, 128, 0, (cudaStream_t)stream>>>(scalars, hxy, N, out);
+  return finish_launch("ed25519_scalarmult_quad");
 }
 void bsc_ed25519_scalarmult_r25_host(const unsigned char* scalars, const unsigned char* hxy, int N,
                                      unsigned char* out) {

@@ -156,6 +156,8 @@ int bsc_ed25519_scalarmult_batch(const void* scalars_u256, const void* bases, in
 
 int bsc_ed25519_scalarmult_r25(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out, void* stream);
 
+int bsc_ed25519_scalarmult_quad(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out, void* stream);
+
 void bsc_ed25519_scalarmult_r25_host(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out);
 
 void bsc_ed25519_scalarmult_batch_host(const void* scalars_u256, const void* bases, int nbase, int N, unsigned char* out);

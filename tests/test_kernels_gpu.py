@@ -230,3 +230,23 @@ def test_vrf_side_stream_path_matches_generic_lottery():
             continue
         out = keys[p].prove(msg)[0]
         assert tab[p].tolist() == cp.lottery_noisers(out, stake, p, 2)
+
+
+def test_vrf_quad_and_single_thread_kernels_agree():
+    import hashlib
+
+    import numpy as np
+
+    n = 37
+    keys = [cp.VRFKey(hashlib.sha256(b"q%d" % i).digest()) for i in range(n)]
+    msg = hashlib.sha256(b"another-block").digest()
+    stake = [10] * n
+    w = np.ones(n, dtype=np.uint8)
+    quad = cp.BatchedVRF(keys, DEV, kernel="quad")
+    one = cp.BatchedVRF(keys, DEV, kernel="r25")
+    hq, ho = quad.launch(msg), one.launch(msg)
+    tq = quad.noiser_table(hq, stake, w, 3)
+    to = one.noiser_table(ho, stake, w, 3)
+    assert bytes(hq[0].numpy().tobytes()) == bytes(ho[0].numpy().tobytes())     # Gamma_p = x_p * H, all peers
+    assert bytes(hq[0][5].tolist()) == keys[5].prove(msg)[1][64:]
+    assert (tq == to).all()
