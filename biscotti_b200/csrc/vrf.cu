@@ -163,11 +163,15 @@ __device__ __forceinline__ F25 f25_sel4(int j, const F25& a, const F25& b, const
 __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsigned char* __restrict__ scalars,
                                                                       const unsigned char* __restrict__ hxy, int N,
                                                                       unsigned char* __restrict__ out) {
-  __shared__ EdCached table[8];
+  __shared__ EdCached table[9];   // 1H..8H, then the identity (digit 0) so every quad runs the same steps
   if (threadIdx.x == 0) {
     uint8_t b[64];
     for (int i = 0; i < 64; i++) b[i] = hxy[i];
     edr_build_table(table, edr_from_affine_bytes(b), f25_const_2d());
+    table[8].YpX = f25_one();
+    table[8].YmX = f25_one();
+    table[8].Z = f25_one();
+    table[8].T2d = f25_zero();
   }
   __syncthreads();
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -192,8 +196,9 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
 #pragma unroll 1
   for (int i = 63; i >= 0; i--) {
     const int dgt = e[i];
-    // steps 0..3 are doublings, step 4 (if the digit is non-zero) is the table addition
-    const int nsteps = dgt != 0 ? 5 : 4;
+    // steps 0..3 are doublings, step 4 is the table addition.  A zero digit adds the identity instead of
+    // skipping the step: control flow must stay warp-uniform because the shuffles below are full-warp.
+    const int nsteps = 5;
 #pragma unroll 1
     for (int step = 0; step < nsteps; step++) {
       F25 a, b;
@@ -207,7 +212,7 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
         b = f25_sel4(j, X, Y, f25_add(Z, Z), xy);
       } else {
         neg = dgt < 0;
-        const EdCached& q = table[(neg ? -dgt : dgt) - 1];
+        const EdCached& q = table[dgt == 0 ? 8 : (neg ? -dgt : dgt) - 1];
         const F25 ypx = f25_add(Y, X), ymx = f25_sub(Y, X);
         a = f25_sel4(j, ypx, ymx, q.T2d, Z);
         b = f25_sel4(j, neg ? q.YmX : q.YpX, neg ? q.YpX : q.YmX, T, q.Z);
