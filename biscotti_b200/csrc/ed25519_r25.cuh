@@ -205,6 +205,46 @@ HDN inline F25 f25_invert(const F25& z) {
   return f25_mul(t, z11);
 }
 
+// z^((p-5)/8) = z^(2^252 - 3)
+HDN inline F25 f25_pow22523(const F25& z) {
+  F25 t0 = f25_sq(z);
+  F25 t1 = f25_sqn(t0, 2);
+  t1 = f25_mul(z, t1);
+  t0 = f25_mul(t0, t1);
+  t0 = f25_sq(t0);
+  t0 = f25_mul(t1, t0);
+  t1 = f25_sqn(t0, 5);
+  t0 = f25_mul(t1, t0);
+  t1 = f25_sqn(t0, 10);
+  t1 = f25_mul(t1, t0);
+  F25 t2 = f25_sqn(t1, 20);
+  t1 = f25_mul(t2, t1);
+  t1 = f25_sqn(t1, 10);
+  t0 = f25_mul(t1, t0);
+  t1 = f25_sqn(t0, 50);
+  t1 = f25_mul(t1, t0);
+  t2 = f25_sqn(t1, 100);
+  t1 = f25_mul(t2, t1);
+  t1 = f25_sqn(t1, 50);
+  t0 = f25_mul(t1, t0);
+  t0 = f25_sqn(t0, 2);
+  return f25_mul(t0, z);
+}
+HD bool f25_is_zero(const F25& a) {
+  uint8_t s[32];
+  f25_tobytes(s, a);
+  uint8_t o = 0;
+  for (int i = 0; i < 32; i++) o |= s[i];
+  return o == 0;
+}
+HD bool f25_eq(const F25& a, const F25& b) { return f25_is_zero(f25_sub(a, b)); }
+HD F25 f25_from_u32(uint32_t x) {
+  F25 r = f25_zero();
+  r.v[0] = (int32_t)(x & 0x3ffffff);
+  r.v[1] = (int32_t)(x >> 26);
+  return r;
+}
+
 struct EdP3 { F25 X, Y, Z, T; };        // extended
 struct EdP1 { F25 X, Y, Z, T; };        // completed ((X:Z), (Y:T))
 struct EdCached { F25 YpX, YmX, Z, T2d; };
@@ -278,6 +318,74 @@ HD EdP3 edr_from_affine_bytes(const uint8_t xy[64]) {
   r.Z = f25_one();
   r.T = f25_mul(r.X, r.Y);
   return r;
+}
+
+HD F25 f25_const_d() {
+  const uint8_t b[32] = {0xa3, 0x78, 0x59, 0x13, 0xca, 0x4d, 0xeb, 0x75, 0xab, 0xd8, 0x41, 0x41, 0x4d, 0x0a, 0x70, 0x00,
+                         0x98, 0xe8, 0x79, 0x77, 0x79, 0x40, 0xc7, 0x8c, 0x73, 0xfe, 0x6f, 0x2b, 0xee, 0x6c, 0x03, 0x52};
+  return f25_frombytes(b);
+}
+HD F25 f25_const_sqrtm1() {
+  const uint8_t b[32] = {0xb0, 0xa0, 0x0e, 0x4a, 0x27, 0x1b, 0xee, 0xc4, 0x78, 0xe4, 0x2f, 0xad, 0x06, 0x18, 0x43, 0x2f,
+                         0xa7, 0xd7, 0xfb, 0x3d, 0x99, 0x00, 0x4d, 0x2b, 0x0b, 0xdf, 0xc1, 0x4f, 0x80, 0x24, 0x83, 0x2b};
+  return f25_frombytes(b);
+}
+// x from y and a sign bit (same contract as ed_from_parity_and_y in ed25519.cuh)
+HDN inline bool edr_from_parity_and_y(EdP3& r, uint32_t sign, const F25& y) {
+  const F25 one = f25_one();
+  F25 y2 = f25_sq(y);
+  F25 u = f25_sub(y2, one);
+  F25 v = f25_add(f25_mul(y2, f25_const_d()), one);
+  F25 v3 = f25_mul(f25_sq(v), v);
+  F25 v7 = f25_mul(f25_sq(v3), v);
+  F25 x = f25_mul(f25_mul(u, v3), f25_pow22523(f25_mul(u, v7)));
+  F25 vx2 = f25_mul(v, f25_sq(x));
+  if (!f25_eq(vx2, u)) {
+    if (!f25_is_zero(f25_add(vx2, u))) return false;
+    x = f25_mul(x, f25_const_sqrtm1());
+  }
+  uint8_t xb[32];
+  f25_tobytes(xb, x);
+  if ((uint32_t)(xb[0] & 1) != sign) x = f25_mul(f25_neg(x), one);   // negate, then re-carry the limbs
+  r.X = x;
+  r.Y = y;
+  r.Z = one;
+  r.T = f25_mul(x, y);
+  return true;
+}
+// Elligator2 + cofactor clearing in the fast field (same map as ed_elligator2_x8 in ed25519.cuh)
+HDN inline EdP3 edr_elligator2_x8(const uint8_t h[32]) {
+  uint8_t t[32];
+  for (int i = 0; i < 32; i++) t[i] = h[i];
+  const uint32_t bit = t[31] >> 7;
+  t[31] &= 127;
+  const F25 one = f25_one();
+  const F25 A = f25_from_u32(486662);
+  F25 r = f25_frombytes(t);
+  F25 den = f25_add(f25_sq2(r), one);
+  F25 v = f25_mul(f25_neg(A), f25_invert(den));
+  F25 v2 = f25_sq(v);
+  F25 e = f25_add(f25_add(f25_mul(v2, v), v), f25_mul(v2, A));
+  e = f25_mul(e, one);   // re-carry the three-term sum before it is used as a multiplication input
+  // Legendre symbol e^((p-1)/2) = (e^((p-5)/8))^4 * e^2
+  F25 chi = f25_mul(f25_sqn(f25_pow22523(e), 2), f25_sq(e));
+  const bool minus1 = !f25_eq(chi, one) && !f25_is_zero(chi);
+  if (minus1) v = f25_mul(f25_sub(f25_neg(v), A), one);
+  F25 y = f25_mul(f25_sub(v, one), f25_invert(f25_add(v, one)));
+  EdP3 p;
+  if (!edr_from_parity_and_y(p, bit, y)) p = edr_identity();
+  EdP1 c = edr_dbl(p.X, p.Y, p.Z);
+  for (int k = 0; k < 2; k++) {
+    F25 X = f25_mul(c.X, c.T), Y = f25_mul(c.Y, c.Z), Z = f25_mul(c.Z, c.T);
+    c = edr_dbl(X, Y, Z);
+  }
+  return edr_p1_to_p3(c);
+}
+// affine x || y (canonical little-endian) of an extended point
+HDN inline void edr_to_affine_bytes(uint8_t out[64], const EdP3& p) {
+  F25 zi = f25_invert(p.Z);
+  f25_tobytes(out, f25_mul(p.X, zi));
+  f25_tobytes(out + 32, f25_mul(p.Y, zi));
 }
 
 // table[k] = (k+1) * H in cached form, k = 0..7

@@ -11,6 +11,7 @@
 #include "ed25519_r25.cuh"
 #include "sha256.cuh"
 #include <string.h>
+#include <vector>
 
 // SHAKE256 lives in host_crypto.cpp
 struct Shake256 {
@@ -289,6 +290,17 @@ void bsc_vrf_hash_to_curve(const uint8_t* m, size_t n, void* out_point, uint8_t 
 }
 // affine H = hashToCurve(m) as x || y, 32 canonical little-endian bytes each (input of the r25 kernel)
 void bsc_vrf_hash_to_curve_xy(const uint8_t* m, size_t n, uint8_t out[64]) {
+  // fast-field Elligator2 (bit-identical to the generic-field hash_to_curve; checked in the tests): this
+  // runs on the host at the top of every block, ahead of the VRF kernel
+  uint8_t hm[32];
+  Shake256 s;
+  shake256_init(s);
+  shake256_absorb(s, m, n);
+  shake256_squeeze(s, hm, 32);
+  edr_to_affine_bytes(out, edr_elligator2_x8(hm));
+}
+// generic-field version of the same (oracle for the fast one)
+void bsc_vrf_hash_to_curve_xy_generic(const uint8_t* m, size_t n, uint8_t out[64]) {
   EdPoint h = hash_to_curve(m, n);
   Fq zi = fe_inv(h.Z);
   u256_to_le(out, fe_to_u256(fe_mul(h.X, zi)));
@@ -381,13 +393,42 @@ int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n
 // lottery of vrf.go:54-100 seeded by output_p with p itself excluded.  out[p*want + j] = noiser id or -1.
 void bsc_noisers_batch(const uint8_t* gammas, const uint8_t* m, size_t mlen, const int* stake, int n,
                        const uint8_t* is_worker, int want, int* out, uint8_t* vrf_out) {
+  // ticket list and eligibility are shared by every peer of the block: build them once
+  std::vector<int> tickets;
+  int distinct = 0;
+  for (int id = 0; id < n; id++) {
+    for (int k = 0; k < stake[id]; k++) tickets.push_back(id);
+    distinct += stake[id] > 0;
+  }
+  std::vector<int> stamp((size_t)n, -1);
   for (int p = 0; p < n; p++) {
     for (int j = 0; j < want; j++) out[(size_t)p * want + j] = -1;
     uint8_t o[32];
     bsc_vrf_output_from_gamma(gammas + 32 * (size_t)p, m, mlen, o);
     if (vrf_out) memcpy(vrf_out + 32 * (size_t)p, o, 32);
-    if (is_worker && !is_worker[p]) continue;
-    bsc_lottery_noisers(o, 32, stake, n, p, want, out + (size_t)p * want);
+    if ((is_worker && !is_worker[p]) || tickets.empty()) continue;
+    // vrf.go:54-100: 2-byte big-endian draws at a byte cursor, SHA-256 re-hash when the bytes run out,
+    // duplicates and the peer itself skipped
+    const int eligible = distinct - (stake[p] > 0 ? 1 : 0);
+    const int need = want < eligible ? want : eligible;
+    uint8_t buf[32];
+    memcpy(buf, o, 32);
+    size_t i = 0;
+    int got = 0;
+    while (got < need) {
+      if (i + 1 >= 32) {
+        uint8_t h[32];
+        sha256_oneshot(buf, 32, h);
+        memcpy(buf, h, 32);
+        i = 0;
+      }
+      const int winner = tickets[((size_t)buf[i] * 256 + buf[i + 1]) % tickets.size()];
+      if (winner != p && stamp[(size_t)winner] != p) {
+        stamp[(size_t)winner] = p;
+        out[(size_t)p * want + got++] = winner;
+      }
+      i++;
+    }
   }
 }
 

@@ -1,0 +1,26 @@
+#!/usr/bin/env python
+"""Host-side hot spots of a block iteration (cProfile over a few steady-state steps)."""
+import cProfile
+import os
+import pstats
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from biscotti_b200.config import BiscottiConfig  # noqa: E402
+from biscotti_b200.protocol.engine import BiscottiEngine  # noqa: E402
+
+cfg = BiscottiConfig(num_nodes=100, dataset="mnist", max_iterations=60)
+eng = BiscottiEngine(cfg, device="cuda:0")
+for _ in range(4):
+    eng.step()
+torch.cuda.synchronize()
+pr = cProfile.Profile()
+pr.enable()
+for _ in range(20):
+    eng.step()
+torch.cuda.synchronize()
+pr.disable()
+st = pstats.Stats(pr)
+st.sort_stats("cumulative").print_stats(45)
