@@ -170,7 +170,7 @@ class FusedComm(NcclComm):
         _check(self.L.bsc_krum_gram_fused(self._tables["hi"], self._tables["lo"], self._tables["gpart"],
                                           self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
                                           self.ldg, c_p(self.base + self.o_cnt), epoch, self._stream()), "krum_gram_fused")
-        rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32, device=dev)
+        rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)
         _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg,

@@ -125,6 +125,21 @@ class BiscottiEngine:
     def _phase(self, name: str):
         return _Phase(self, name)
 
+    def _idx(self, values, dtype=torch.int32) -> torch.Tensor:
+        """Small host list -> device tensor through a pinned staging ring (asynchronous H2D, no host sync)."""
+        n = len(values)
+        if self.device.type != "cuda":
+            return torch.tensor(values, dtype=dtype)
+        if not hasattr(self, "_stage"):
+            self._stage = [torch.empty(4096, dtype=torch.int64).pin_memory() for _ in range(32)]
+            self._stage_i = 0
+        buf = self._stage[self._stage_i % len(self._stage)]
+        self._stage_i += 1
+        view = buf.view(dtype)[:n] if n <= buf.view(dtype).numel() else torch.empty(n, dtype=dtype).pin_memory()
+        if n:
+            view.copy_(torch.as_tensor(values, dtype=dtype))
+        return view.to(self.device, non_blocking=True)
+
     # ------------------------------------------------------------------------------------------
     def select_roles(self):
         cfg = self.cfg
@@ -218,6 +233,8 @@ class BiscottiEngine:
                 if self.P:
                     lo_id = self.local_ids[0]
                     noiser_tab = torch.from_numpy(full_tab[lo_id: lo_id + self.P].copy())
+                    if dev.type == "cuda":
+                        noiser_tab = noiser_tab.pin_memory()
                 if self.colluder_ids:
                     noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
             scale = cfg.noise_scale if use_noise else 0.0
@@ -258,20 +275,20 @@ class BiscottiEngine:
             return self._finish_block(rep, [], None, phases, t0)   # main.go:2099-2117
         rep.n_contributors = len(contributors)
         local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
-        sel = torch.tensor(local_contrib, dtype=torch.int32, device=dev)
+        sel = self._idx(local_contrib)
         agg_commit = None
         if cfg.secure_agg:
             if self.commit is not None and self.P:
                 with self._phase("witness"):
                     # every approved worker generates shares + witnesses for the miners (kyber.go:456-482)
-                    appr_local = torch.tensor([self.local_index[p] for p in approved if p in self.local_index],
-                                              dtype=torch.int32, device=dev)
-                    W = self.commit.witnesses(Q, appr_local) if appr_local.numel() else None
+                    appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
+                    appr_local = self._idx(appr_rows)
+                    W = self.commit.witnesses(Q, appr_local) if appr_rows else None
                 with self._phase("miner_aggregate"):
-                    if W is not None and sel.numel():
+                    if W is not None and local_contrib:
                         # positions of contributors inside the approved-local list
-                        pos = {int(r): i for i, r in enumerate(appr_local.tolist())}
-                        csel = torch.tensor([pos[r] for r in local_contrib], dtype=torch.int32, device=dev)
+                        pos = {r: i for i, r in enumerate(appr_rows)}
+                        csel = self._idx([pos[r] for r in local_contrib])
                         aggW = self.commit.aggregate(W, csel)               # [nchunk, S, 16]
                         aggC = self.commit.aggregate(chunkC, sel)           # [nchunk, 16]
                         agg_commit = (aggC, aggW)
@@ -289,8 +306,8 @@ class BiscottiEngine:
                         torch.zeros(cfg.nchunk, self.S, dtype=torch.int64, device=dev)
                     if self.comm is not None:
                         Ysum = self.comm.all_reduce_i64(Ysum)
-                    xs_t = torch.tensor(xs, dtype=torch.int32, device=dev)
-                    av_t = torch.tensor(shares_avail, dtype=torch.uint8, device=dev)
+                    xs_t = self._idx(xs)
+                    av_t = self._idx(shares_avail, torch.uint8)
                     _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
         else:
             with self._phase("secagg"):
@@ -345,10 +362,11 @@ class BiscottiEngine:
                     avail[s] = 1
         return avail
 
-    def _gather_rows(self, ids: list[int], local: torch.Tensor) -> torch.Tensor:
+    def _gather_rows(self, ids: list[int], local: torch.Tensor, ix=None) -> torch.Tensor:
         """Rows of `local` (indexed by local peer position) for global peer ids, in order."""
         if self.comm is None:
-            ix = torch.tensor([self.local_index[p] for p in ids], dtype=torch.long, device=local.device)
+            if ix is None:
+                ix = self._idx([self.local_index[p] for p in ids], torch.int64)
             return local.index_select(0, ix).contiguous()
         return self.comm.gather_rows(ids, local, self.local_index, self.owner)
 
@@ -361,10 +379,11 @@ class BiscottiEngine:
         if self.fused:
             _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1)
         else:
-            Uk = self._gather_rows(krum_set, Un)
-            hik = self._gather_rows(krum_set, hi) if hi is not None else None
-            lok = self._gather_rows(krum_set, lo) if lo is not None else None
-            nrm = self._gather_rows(krum_set, norms.unsqueeze(1)).squeeze(1) if norms is not None else None
+            ix = self._idx([self.local_index[p] for p in krum_set], torch.int64) if self.comm is None else None
+            Uk = self._gather_rows(krum_set, Un, ix)
+            hik = self._gather_rows(krum_set, hi, ix) if hi is not None else None
+            lok = self._gather_rows(krum_set, lo, ix) if lo is not None else None
+            nrm = self._gather_rows(krum_set, norms.unsqueeze(1), ix).squeeze(1) if norms is not None else None
             _, acc, _ = krum_ops.krum(Uk, self.d, clip, hik, lok, nrm, impl=cfg.gram_impl)
         mask = acc.cpu().tolist()
         return [p for p, a in zip(krum_set, mask) if a]
