@@ -200,6 +200,13 @@ def main():
         hs = comm.all_gather_bytes(eng.chain.latest_hash()) if hasattr(comm, "all_gather_bytes") else [eng.chain.latest_hash()]
         chain_ok = all(h == hs[0] for h in hs)
 
+    phase_ms = None
+    if args.profile_phases:          # every rank takes the extra instrumented step (collective kernels inside)
+        eng._timing = True
+        eng.step()
+        phase_ms = eng.reports[-1].phase_ms
+        eng._timing = False
+
     if rank == 0:
         value = 1000.0 / ms_per_step
         last = eng.reports[-1]
@@ -234,10 +241,8 @@ def main():
             "last_block": {"contributors": last.n_contributors, "accepted": last.n_accepted, "krum_set": last.n_krum,
                            "test_error": last.test_error, "empty": last.empty},
         }
-        if args.profile_phases:
-            eng._timing = True
-            eng.step()
-            out["phase_ms"] = eng.reports[-1].phase_ms
+        if phase_ms is not None:
+            out["phase_ms"] = phase_ms
         print(json.dumps(out))
     if world > 1:
         torch.distributed.barrier()

@@ -88,6 +88,10 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_g1_bytes_to_affine", c_i, c_p, c_p, c_ll, c_p)
     sig("bsc_g1_sum_rows", c_i, c_p, c_p, c_i, c_ll, c_p, c_p)
     sig("bsc_g1_sum_cols", c_i, c_p, c_i, c_i, c_p, c_p)
+    sig("bsc_g1_sum_rows_jac", c_i, c_p, c_p, c_i, c_ll, c_p, c_p)
+    sig("bsc_g1_sum_cols_jac", c_i, c_p, c_i, c_i, c_p, c_p)
+    sig("bsc_g1_sum_rows_jac_host", None, c_p, c_p, c_i, c_ll, c_p)
+    sig("bsc_g1_sum_cols_jac_host", None, c_p, c_i, c_i, c_p)
     sig("bsc_msm_table_build", c_i, c_p, c_ll, c_i, c_i, c_p, c_p)
     sig("bsc_msm_table_build_host", None, c_p, c_ll, c_i, c_i, c_p)
     sig("bsc_msm_table", c_i, c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_ll, c_p)

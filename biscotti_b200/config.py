@@ -83,6 +83,8 @@ class BiscottiConfig:
     shard_size: int = 600             # rows per peer shard (mnist 60000/100)
     test_size: int = 2000
     eval_every: int = 1               # reference evaluates every block (honest.go:141-162)
+    affine_wire: bool = False         # True: normalise every chunk commitment / witness to the 64-byte affine
+                                      # wire form (kyber.go:88-168) even though no wire exists between GPUs
     gram_impl: str = "auto"           # auto | tcgen05 | simt
     comm_impl: str = "fused"          # fused (in-kernel P2P) | nccl (baseline)
     extra: dict = field(default_factory=dict)

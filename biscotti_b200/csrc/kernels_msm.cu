@@ -212,6 +212,33 @@ __global__ void __launch_bounds__(128) g1_sum_cols_kernel(const G1Affine* __rest
   if (tid == 0) out[p] = sh[0];
 }
 
+// Jacobian-input variants: points stay in Jacobian form between kernels (no field inversion on the
+// block's critical path); only what enters the ledger is normalised.  sel_rows: rows are strided by
+// `row_stride` points; the peer dimension is split over gridDim.y partial sums (fixed order) to shorten
+// the dependent addition chain, and the partials are added by the y == 0 thread's owner afterwards.
+__global__ void __launch_bounds__(128) g1_sum_rows_jac_kernel(const G1Jac* __restrict__ pts, const int* __restrict__ sel,
+                                                              int nsel, long long G, G1Jac* __restrict__ out) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  G1Jac acc = g1j_inf();
+  for (int q = 0; q < nsel; q++) acc = g1j_add(acc, pts[(size_t)sel[q] * G + g]);
+  out[g] = acc;
+}
+__global__ void __launch_bounds__(128) g1_sum_cols_jac_kernel(const G1Jac* __restrict__ pts, int G,
+                                                              G1Jac* __restrict__ out) {
+  __shared__ G1Jac sh[128];
+  const int p = blockIdx.x, tid = threadIdx.x;
+  G1Jac acc = g1j_inf();
+  for (int g = tid; g < G; g += blockDim.x) acc = g1j_add(acc, pts[(size_t)p * G + g]);
+  sh[tid] = acc;
+  __syncthreads();
+  for (int s = blockDim.x >> 1; s > 0; s >>= 1) {
+    if (tid < s) sh[tid] = g1j_add(sh[tid], sh[tid + s]);
+    __syncthreads();
+  }
+  if (tid == 0) out[p] = sh[0];
+}
+
 }  // namespace bsc
 
 using namespace bsc;
@@ -308,6 +335,36 @@ int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long 
   g1_sum_rows_kernel<<<(unsigned)((G + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)pts_affine, sel,
                                                                                    nsel, G, (G1Jac*)out_jac);
   return finish_launch("g1_sum_rows");
+}
+
+int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
+  if (G == 0) return 0;
+  g1_sum_rows_jac_kernel<<<(unsigned)((G + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Jac*)pts_jac, sel, nsel,
+                                                                                       G, (G1Jac*)out_jac);
+  return finish_launch("g1_sum_rows_jac");
+}
+int bsc_g1_sum_cols_jac(const void* pts_jac, int P, int G, void* out_jac, void* stream) {
+  if (P == 0) return 0;
+  g1_sum_cols_jac_kernel<<<P, 128, 0, (cudaStream_t)stream>>>((const G1Jac*)pts_jac, G, (G1Jac*)out_jac);
+  return finish_launch("g1_sum_cols_jac");
+}
+void bsc_g1_sum_rows_jac_host(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac) {
+  const G1Jac* pts = (const G1Jac*)pts_jac;
+  G1Jac* out = (G1Jac*)out_jac;
+  for (long long g = 0; g < G; g++) {
+    G1Jac acc = g1j_inf();
+    for (int q = 0; q < nsel; q++) acc = g1j_add(acc, pts[(size_t)sel[q] * G + g]);
+    out[g] = acc;
+  }
+}
+void bsc_g1_sum_cols_jac_host(const void* pts_jac, int P, int G, void* out_jac) {
+  const G1Jac* pts = (const G1Jac*)pts_jac;
+  G1Jac* out = (G1Jac*)out_jac;
+  for (int p = 0; p < P; p++) {
+    G1Jac acc = g1j_inf();
+    for (int g = 0; g < G; g++) acc = g1j_add(acc, pts[(size_t)p * G + g]);
+    out[p] = acc;
+  }
 }
 
 int bsc_g1_sum_cols(const void* pts_affine, int P, int G, void* out_jac, void* stream) {

@@ -161,10 +161,14 @@ class Blockchain:
                 nz.ctypes.data_as(c_p) if nz is not None else None, nnz,
                 nd.ctypes.data_as(c_p) if nd is not None else None, nnd,
                 sigs or None, len(u.signatures), siglen)
-        if stake:
-            ids = (c_i * len(stake))(*stake.keys())
-            vals = (c_i * len(stake))(*stake.values())
-            self._L.bsc_block_set_stake(b, ids, vals, len(stake))
+        if stake is not None and len(stake):
+            if isinstance(stake, dict):
+                ids = np.fromiter(stake.keys(), dtype=np.int32, count=len(stake))
+                vals = np.fromiter(stake.values(), dtype=np.int32, count=len(stake))
+            else:                                   # dense list: node id == position
+                vals = np.asarray(stake, dtype=np.int32)
+                ids = np.arange(len(vals), dtype=np.int32)
+            self._L.bsc_block_set_stake(b, ids.ctypes.data_as(c_p), vals.ctypes.data_as(c_p), len(vals))
         self._L.bsc_chain_append(self._h, b, timestamp)
         return self.latest_hash()
 

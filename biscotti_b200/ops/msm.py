@@ -186,8 +186,12 @@ class CommitmentEngine:
         return out
 
     # -- protocol-level operations -----------------------------------------------------------------
-    def chunk_commitments(self, Q: torch.Tensor, sel: torch.Tensor | None = None) -> torch.Tensor:
-        """C[p, c] = sum_j Q[p, 10c+j] * PKG1[10c+j]  -> affine [P, nchunk, 16]."""
+    # Point tensors are recognised by their last dimension: 16 words = affine, 24 words = Jacobian.  With
+    # affine=False the kernels hand Jacobian points to each other and no field inversion is paid until
+    # something is serialised (workers and miners share device memory here, so the 64-byte wire form of
+    # kyber.go:88-168 is only needed for what enters the ledger).
+    def chunk_commitments(self, Q: torch.Tensor, sel: torch.Tensor | None = None, affine: bool = True) -> torch.Tensor:
+        """C[p, c] = sum_j Q[p, 10c+j] * PKG1[10c+j]  -> [P, nchunk, 16 | 24]."""
         P = Q.shape[0] if sel is None else sel.numel()
         if self.c_table is not None:
             jac = self._msm_table(Q, sel, P, self.c_sidx, self.c_bidx, None, self.nchunk, POLY_SIZE, self.c_table,
@@ -195,20 +199,25 @@ class CommitmentEngine:
         else:
             jac = self._msm(Q, sel, P, self.c_sidx, self.c_bidx, None, self.nchunk, POLY_SIZE, self.bases,
                             ostride=self.nchunk, nout=P * self.nchunk)
+        if not affine:
+            return jac.view(P, self.nchunk, JAC)
         return self.normalize(jac).view(P, self.nchunk, AFF)
 
-    def full_commitments(self, chunk_aff: torch.Tensor) -> torch.Tensor:
+    def full_commitments(self, chunk_pts: torch.Tensor) -> torch.Tensor:
         """Full-vector commitment = sum of the chunk commitments -> affine [P, 16]."""
-        P, G = chunk_aff.shape[0], chunk_aff.shape[1]
-        jac = torch.empty(P, JAC, dtype=torch.int32, device=chunk_aff.device)
-        if chunk_aff.is_cuda:
-            check(lib().bsc_g1_sum_cols(ptr(chunk_aff), P, G, ptr(jac), stream(chunk_aff.device)), "g1_sum_cols")
+        P, G = chunk_pts.shape[0], chunk_pts.shape[1]
+        isj = chunk_pts.shape[-1] == JAC
+        jac = torch.empty(P, JAC, dtype=torch.int32, device=chunk_pts.device)
+        L = lib()
+        if chunk_pts.is_cuda:
+            fn = L.bsc_g1_sum_cols_jac if isj else L.bsc_g1_sum_cols
+            check(fn(ptr(chunk_pts), P, G, ptr(jac), stream(chunk_pts.device)), "g1_sum_cols")
         else:
-            lib().bsc_g1_sum_cols_host(ptr(chunk_aff), P, G, ptr(jac))
+            (L.bsc_g1_sum_cols_jac_host if isj else L.bsc_g1_sum_cols_host)(ptr(chunk_pts), P, G, ptr(jac))
         return self.normalize(jac)
 
-    def witnesses(self, Q: torch.Tensor, sel: torch.Tensor | None = None) -> torch.Tensor:
-        """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> affine [P, nchunk, S, 16]."""
+    def witnesses(self, Q: torch.Tensor, sel: torch.Tensor | None = None, affine: bool = True) -> torch.Tensor:
+        """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> [P, nchunk, S, 16 | 24]."""
         P = Q.shape[0] if sel is None else sel.numel()
         G = self.nchunk * self.S
         if self.w_table is not None:
@@ -217,17 +226,24 @@ class CommitmentEngine:
         else:
             jac = self._msm(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.wtable, ostride=G,
                             nout=P * G)
+        if not affine:
+            return jac.view(P, self.nchunk, self.S, JAC)
         return self.normalize(jac).view(P, self.nchunk, self.S, AFF)
 
-    def aggregate(self, pts_aff: torch.Tensor, sel: torch.Tensor) -> torch.Tensor:
-        """Miner-side homomorphic add over contributing peers: pts [P, G..., 16] -> affine [G..., 16]."""
-        P = pts_aff.shape[0]
-        inner = pts_aff.shape[1:-1]
-        G = pts_aff.numel() // (P * AFF)
-        jac = torch.empty(G, JAC, dtype=torch.int32, device=pts_aff.device)
-        if pts_aff.is_cuda:
-            check(lib().bsc_g1_sum_rows(ptr(pts_aff), ptr(sel), sel.numel(), G, ptr(jac), stream(pts_aff.device)),
-                  "g1_sum_rows")
+    def aggregate(self, pts: torch.Tensor, sel: torch.Tensor, affine: bool = True) -> torch.Tensor:
+        """Miner-side homomorphic add over contributing peers: pts [P, G..., 16|24] -> [G..., 16|24]."""
+        P = pts.shape[0]
+        inner = pts.shape[1:-1]
+        words = pts.shape[-1]
+        G = pts.numel() // (P * words)
+        jac = torch.empty(G, JAC, dtype=torch.int32, device=pts.device)
+        L = lib()
+        if pts.is_cuda:
+            fn = L.bsc_g1_sum_rows_jac if words == JAC else L.bsc_g1_sum_rows
+            check(fn(ptr(pts), ptr(sel), sel.numel(), G, ptr(jac), stream(pts.device)), "g1_sum_rows")
         else:
-            lib().bsc_g1_sum_rows_host(ptr(pts_aff), ptr(sel), sel.numel(), G, ptr(jac))
+            (L.bsc_g1_sum_rows_jac_host if words == JAC else L.bsc_g1_sum_rows_host)(ptr(pts), ptr(sel), sel.numel(), G,
+                                                                                   ptr(jac))
+        if not affine:
+            return jac.view(*inner, JAC)
         return self.normalize(jac).view(*inner, AFF)

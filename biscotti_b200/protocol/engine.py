@@ -217,7 +217,7 @@ class BiscottiEngine:
         if self.commit is not None and self.P:
             with self._phase("commit"):
                 Q = secagg.quantize(self.U, self.d, cfg.precision)
-                chunkC = self.commit.chunk_commitments(Q)                      # [P, nchunk, 16]
+                chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
                 fullC = self.commit.full_commitments(chunkC)                   # [P, 16]
                 fullC_dev = self.commit.to_bytes_tensor(fullC)                 # [P, 64] on device
 
@@ -283,14 +283,14 @@ class BiscottiEngine:
                     # every approved worker generates shares + witnesses for the miners (kyber.go:456-482)
                     appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
                     appr_local = self._idx(appr_rows)
-                    W = self.commit.witnesses(Q, appr_local) if appr_rows else None
+                    W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire) if appr_rows else None
                 with self._phase("miner_aggregate"):
                     if W is not None and local_contrib:
                         # positions of contributors inside the approved-local list
                         pos = {r: i for i, r in enumerate(appr_rows)}
                         csel = self._idx([pos[r] for r in local_contrib])
-                        aggW = self.commit.aggregate(W, csel)               # [nchunk, S, 16]
-                        aggC = self.commit.aggregate(chunkC, sel)           # [nchunk, 16]
+                        aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)        # [nchunk, S, 16|24]
+                        aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)    # [nchunk, 16|24]
                         agg_commit = (aggC, aggW)
             with self._phase("secagg"):
                 xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
@@ -319,17 +319,30 @@ class BiscottiEngine:
                     secagg.plain_sum_step(self.U, sel, self.d, self.w64, self.w32)
                 bad = torch.zeros(2, dtype=torch.int32, device=dev)
 
-        # ---- 9. block assembly (host)
+        # ---- 9. block assembly (host).  Evaluation of the new weights is launched first so that one
+        # device->host collection (weights, commitments, share-check counters, error rates) and one stream
+        # synchronisation serve the whole tail of the block.
         with self._phase("block"):
             updates = []
             commits = {}
+            want = {"w": self.w64, "bad": bad}
+            if cfg.eval_every and (it % cfg.eval_every == 0):
+                te, ar = self.evaluate()
+                want["te"], want["ar"] = te, ar
+            gathered = False
             if self.commit is not None and self.P:
                 if self.comm is not None and hasattr(self.comm, "all_gather_rows_u8"):
-                    cb = self.comm.all_gather_rows_u8(fullC_dev).cpu().numpy()      # [world*per, 64], row = peer id
+                    want["cb"] = self.comm.all_gather_rows_u8(fullC_dev)             # [world*per, 64], row = peer id
+                    gathered = True
+                else:
+                    want["cb"] = fullC_dev
+            host = self._collect(want)
+            if "cb" in host:
+                cb = host["cb"]
+                if gathered:
                     for p in contributors:
                         commits[p] = cb[p].tobytes()
                 else:
-                    cb = fullC_dev.cpu().numpy()
                     for p in contributors:
                         if p in self.local_index:
                             commits[p] = cb[self.local_index[p]].tobytes()
@@ -349,8 +362,8 @@ class BiscottiEngine:
                 for p in krum_set:
                     if p not in accepted:
                         self.stake[p] -= STAKE_UNIT                      # honest.go:362-370 (plain path only)
-            rep.bad_shares = int(bad.sum().item())
-        return self._finish_block(rep, updates, agg_commit, phases, t0)
+            rep.bad_shares = int(host["bad"].sum())
+        return self._finish_block(rep, updates, agg_commit, phases, t0, host)
 
     # ------------------------------------------------------------------------------------------
     def _available_shares(self, miners, alive_miners):
@@ -402,21 +415,40 @@ class BiscottiEngine:
         ar = self.model.eval_errors(w, None, self.data.X_attack, self.data.y_attack)
         return te, ar
 
-    def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0) -> BlockReport:
+    def _collect(self, tensors: dict) -> dict:
+        """Device tensors -> numpy, through persistent pinned buffers, with a single stream synchronisation."""
+        if self.device.type != "cuda":
+            return {k: v.detach().cpu().numpy() for k, v in tensors.items()}
+        if not hasattr(self, "_pinned"):
+            self._pinned = {}
+        out = {}
+        for k, v in tensors.items():
+            key = (k, tuple(v.shape), v.dtype)
+            buf = self._pinned.get(key)
+            if buf is None:
+                buf = torch.empty(v.shape, dtype=v.dtype).pin_memory()
+                self._pinned[key] = buf
+            buf.copy_(v, non_blocking=True)
+            out[k] = buf
+        torch.cuda.current_stream(self.device).synchronize()
+        return {k: b.numpy() for k, b in out.items()}
+
+    def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0, host=None) -> BlockReport:
         cfg = self.cfg
         it = self.iteration
         with self._phase("block"):
-            w_host = self.w64.cpu().numpy()
+            if host is None:
+                want = {"w": self.w64}
+                if cfg.eval_every and (it % cfg.eval_every == 0):
+                    want["te"], want["ar"] = self.evaluate()
+                host = self._collect(want)
             ts = (0 if not updates else 1 + it) if cfg.deterministic_time else -1
-            stake_map = {i: s for i, s in enumerate(self.stake)}
-            rep.block_hash = self.chain.add_block(it, w_host, updates, stake_map, timestamp=ts)
+            rep.block_hash = self.chain.add_block(it, host["w"], updates, self.stake, timestamp=ts)
             rep.empty = not updates
-        if cfg.eval_every and (it % cfg.eval_every == 0):
-            with self._phase("eval"):
-                te, ar = self.evaluate()
-                rep.test_error, rep.attack_rate = float(te[0]), float(ar[0])
-                self.log.train_error(it, rep.test_error)
-                self.log.attack_rate(it, rep.attack_rate)
+        if "te" in host:
+            rep.test_error, rep.attack_rate = float(host["te"][0]), float(host["ar"][0])
+            self.log.train_error(it, rep.test_error)
+            self.log.attack_rate(it, rep.attack_rate)
         rep.phase_ms = dict(phases)
         rep.phase_ms["total_host"] = (time.perf_counter() - t0) * 1e3
         self.last_aggregate = agg_commit
