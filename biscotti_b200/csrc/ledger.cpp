@@ -24,6 +24,10 @@
 
 using namespace bsc;
 
+namespace bsc {
+void sha256_fast(const uint8_t* data, size_t n, uint8_t out[32]);   // sha256_ni.cpp (SHA-NI when available)
+}
+
 namespace {
 
 struct Update {
@@ -94,7 +98,7 @@ void set_hash(Block& b) {
   pre += std::to_string((long long)b.timestamp);
   pre += encode_block_data(b);
   uint8_t h[32];
-  sha256_oneshot((const uint8_t*)pre.data(), pre.size(), h);
+  sha256_fast((const uint8_t*)pre.data(), pre.size(), h);
   b.hash.assign((const char*)h, 32);
 }
 
@@ -343,6 +347,23 @@ void bsc_block_add_update(void* bp, int source, int iteration, int accepted, con
   if (noised && ndlen > 0) u.noised.assign(noised, noised + ndlen);
   for (int i = 0; i < nsigs; i++) u.signatures.emplace_back((const char*)sigs + (size_t)i * siglen, (size_t)siglen);
   b->updates.push_back(std::move(u));
+}
+// Batch form for secure-aggregation blocks: n accepted updates that carry only (source, commitment,
+// signatures) — honest.go:391-440 appends exactly such commitment-only updates.  sigs may be null.
+void bsc_block_add_commit_updates(void* bp, int n, const int* sources, int iteration, const uint8_t* commitments,
+                                  int clen, const uint8_t* sigs, int nsigs_each, int siglen) {
+  Block* b = (Block*)bp;
+  b->updates.reserve(b->updates.size() + (size_t)n);
+  for (int i = 0; i < n; i++) {
+    Update u;
+    u.source = sources[i];
+    u.iteration = iteration;
+    u.accepted = 1;
+    if (commitments && clen > 0) u.commitment.assign((const char*)commitments + (size_t)i * clen, (size_t)clen);
+    for (int k = 0; k < nsigs_each; k++)
+      u.signatures.emplace_back((const char*)sigs + ((size_t)i * nsigs_each + k) * siglen, (size_t)siglen);
+    b->updates.push_back(std::move(u));
+  }
 }
 void bsc_block_set_stake(void* bp, const int* ids, const int* vals, int n) {
   Block* b = (Block*)bp;

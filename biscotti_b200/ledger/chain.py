@@ -29,6 +29,7 @@ def _lib():
         L.bsc_block_free.argtypes = [c_p]
         L.bsc_block_add_update.argtypes = [c_p, c_i, c_i, c_i, c_p, c_i, c_p, c_i, c_p, c_i, c_p, c_i, c_p, c_i, c_i]
         L.bsc_block_set_stake.argtypes = [c_p, c_p, c_p, c_i]
+        L.bsc_block_add_commit_updates.argtypes = [c_p, c_i, c_p, c_i, c_p, c_i, c_p, c_i, c_i]
         L.bsc_chain_append.argtypes = [c_p, c_p, c_ll]
         L.bsc_chain_block_index.argtypes = [c_p, c_ll]
         L.bsc_chain_hash.argtypes = [c_p, c_i, c_p]
@@ -149,6 +150,19 @@ class Blockchain:
         peer mints the same empty block.  Returns the new block's hash."""
         w, d = _f64(weights)
         b = self._L.bsc_block_new(iteration, w.ctypes.data_as(c_p), d)
+        simple = len(updates) > 0 and all(u.delta is None and u.noise is None and u.noised is None and u.accepted
+                                          and len(u.commitment) == len(updates[0].commitment)
+                                          and len(u.signatures) == len(updates[0].signatures) for u in updates)
+        if simple:
+            # commitment-only updates of a secure-aggregation block: one native call for all of them
+            src = np.fromiter((u.source for u in updates), dtype=np.int32, count=len(updates))
+            cm = b"".join(u.commitment for u in updates)
+            ns = len(updates[0].signatures)
+            sg = b"".join(s_ for u in updates for s_ in u.signatures)
+            sl = len(updates[0].signatures[0]) if ns else 0
+            self._L.bsc_block_add_commit_updates(b, len(updates), src.ctypes.data_as(c_p), updates[0].iteration,
+                                                 cm or None, len(updates[0].commitment), sg or None, ns, sl)
+            updates = ()
         for u in updates:
             dl, ndl = _f64(u.delta)
             nz, nnz = _f64(u.noise)

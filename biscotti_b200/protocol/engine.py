@@ -234,7 +234,10 @@ class BiscottiEngine:
                     lo_id = self.local_ids[0]
                     noiser_tab = torch.from_numpy(full_tab[lo_id: lo_id + self.P].copy())
                     if dev.type == "cuda":
-                        noiser_tab = noiser_tab.pin_memory()
+                        if not hasattr(self, "_nz_pinned"):
+                            self._nz_pinned = torch.empty_like(noiser_tab).pin_memory()
+                        self._nz_pinned.copy_(noiser_tab)
+                        noiser_tab = self._nz_pinned
                 if self.colluder_ids:
                     noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
             scale = cfg.noise_scale if use_noise else 0.0

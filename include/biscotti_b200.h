@@ -110,6 +110,14 @@ int bsc_g1_bytes_to_affine(const unsigned char* in, void* out_affine, long long 
 
 int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac, void* stream);
 
+int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream);
+
+int bsc_g1_sum_cols_jac(const void* pts_jac, int P, int G, void* out_jac, void* stream);
+
+void bsc_g1_sum_rows_jac_host(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac);
+
+void bsc_g1_sum_cols_jac_host(const void* pts_jac, int P, int G, void* out_jac);
+
 int bsc_g1_sum_cols(const void* pts_affine, int P, int G, void* out_jac, void* stream);
 
 // ---- host mirrors (CPU plumbing path + oracles; same templates as the kernels) --------------------
@@ -139,6 +147,9 @@ void bsc_vrf_hash_to_curve(const uint8_t* m, size_t n, void* out_point, uint8_t 
 
 // affine H = hashToCurve(m) as x || y, 32 canonical little-endian bytes each (input of the r25 kernel)
 void bsc_vrf_hash_to_curve_xy(const uint8_t* m, size_t n, uint8_t out[64]);
+
+// generic-field version of the same (oracle for the fast one)
+void bsc_vrf_hash_to_curve_xy_generic(const uint8_t* m, size_t n, uint8_t out[64]);
 
 // output = SHAKE256(Gamma || m)[:32]
 void bsc_vrf_output_from_gamma(const uint8_t gamma[32], const uint8_t* m, size_t n, uint8_t out[32]);
@@ -235,6 +246,10 @@ void* bsc_block_new(long long iteration, const double* w, int d);
 void bsc_block_free(void* b);
 
 void bsc_block_add_update(void* bp, int source, int iteration, int accepted, const uint8_t* commitment, int clen, const double* delta, int dlen, const double* noise, int nlen, const double* noised, int ndlen, const uint8_t* sigs, int nsigs, int siglen);
+
+// Batch form for secure-aggregation blocks: n accepted updates that carry only (source, commitment,
+// signatures) — honest.go:391-440 appends exactly such commitment-only updates.  sigs may be null.
+void bsc_block_add_commit_updates(void* bp, int n, const int* sources, int iteration, const uint8_t* commitments, int clen, const uint8_t* sigs, int nsigs_each, int siglen);
 
 void bsc_block_set_stake(void* bp, const int* ids, const int* vals, int n);
 
