@@ -139,4 +139,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_fr_powers", None, c_cp, c_i, c_p)
     sig("bsc_schnorr_pubkey", None, c_cp, c_p)
     sig("bsc_schnorr_sign", None, c_cp, c_sz, c_cp, c_cp, c_p)
+    sig("bsc_schnorr_nonces", None, c_i, c_p, c_i, c_p, c_p, c_p)
+    sig("bsc_schnorr_finish_batch", None, c_i, c_p, c_i, c_p, c_p, c_p, c_p)
+    sig("bsc_g1_comb_mul", c_i, c_p, c_i, c_p, c_i, c_i, c_p, c_p)
     sig("bsc_schnorr_verify", c_i, c_cp, c_sz, c_cp, c_cp)

@@ -78,6 +78,7 @@ class BiscottiConfig:
     seed: int = 1
     srs_tau: int = 2                  # publicKey.go:36 compat; 0 => random tau
     commitments: bool = True          # compute KZG commitments + witnesses (reference always does)
+    sign_approvals: bool = True       # verifiers Schnorr-sign accepted commitments (kyber.go:873-896)
     share_trigger: str = "half"       # "half": miners act on NUM_SAMPLES/2 shares (main.go:360); "all"
     deterministic_time: bool = True   # inject block timestamps so chains are reproducible
     shard_size: int = 600             # rows per peer shard (mnist 60000/100)

@@ -1,0 +1,103 @@
+"""Batched Schnorr approvals: every verifier signs the commitment of every update Multi-Krum accepted
+(DistSys/krum.go:338-358 -> SchnorrSign, kyber.go:873-896).
+
+The expensive part of a signature is the commitment T = v*G.  All (verifier, update) pairs of a block
+are done in one launch of the fixed-base comb kernel (g1_comb_mul_kernel: 33 mixed additions per
+scalar over a table of the generator's window multiples); hashing c = H(T || msg) with BLAKE2Xb and the
+scalar arithmetic r = v - x*c stay on the host (microseconds).  The launch is asynchronous, so it
+overlaps with the witness MSM; `finish()` is called when the block is assembled.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from .. import _native
+from ..ops.msm import AFF, JAC
+
+W_BITS, N_WIN = 8, 33          # 33 * 8 = 264 >= 257: the recoding carry of a 256-bit scalar has a window
+
+
+class SchnorrBatchSigner:
+    def __init__(self, device="cpu"):
+        self.device = torch.device(device)
+        self.L = _native.load()
+        self._table = None
+
+    def _ensure_table(self):
+        if self._table is not None or self.device.type != "cuda":
+            return
+        L = self.L
+        gen = ctypes.create_string_buffer(64)
+        L.bsc_g1_generator(gen)
+        g_aff = torch.empty(1, AFF, dtype=torch.int32)
+        L.bsc_g1_bytes_to_affine_host(gen.raw, ctypes.c_void_p(g_aff.data_ptr()), 1)
+        H = 1 << (W_BITS - 1)
+        jac = torch.empty(N_WIN * H, JAC, dtype=torch.int32, device=self.device)
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        g_dev = g_aff.to(self.device)
+        rc = L.bsc_msm_table_build(ctypes.c_void_p(g_dev.data_ptr()), 1, W_BITS, N_WIN, ctypes.c_void_p(jac.data_ptr()), stream)
+        assert rc == 0
+        self._table = torch.empty(N_WIN * H, AFF, dtype=torch.int32, device=self.device)
+        rc = L.bsc_g1_normalize(ctypes.c_void_p(jac.data_ptr()), ctypes.c_void_p(self._table.data_ptr()), N_WIN * H, stream)
+        assert rc == 0
+
+    def launch(self, secrets: list[bytes], tags: list[bytes]):
+        """Start signing: one (secret key, unique tag) pair per signature.  Returns a handle for finish()."""
+        n = len(secrets)
+        L = self.L
+        x = np.frombuffer(b"".join(secrets), dtype=np.uint8).copy()
+        tg = np.frombuffer(b"".join(tags), dtype=np.uint8).copy()
+        taglen = len(tags[0]) if n else 0
+        vw = np.empty((max(1, n), 8), dtype=np.uint32)
+        vbe = np.empty(max(1, n) * 32, dtype=np.uint8)
+        if n:
+            L.bsc_schnorr_nonces(n, tg.ctypes.data_as(ctypes.c_void_p), taglen, x.ctypes.data_as(ctypes.c_void_p),
+                                 vw.ctypes.data_as(ctypes.c_void_p), vbe.ctypes.data_as(ctypes.c_void_p))
+        T_dev = None
+        if self.device.type == "cuda" and n:
+            self._ensure_table()
+            k = torch.from_numpy(vw.view(np.int32)).pin_memory().to(self.device, non_blocking=True)
+            stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            jac = torch.empty(n, JAC, dtype=torch.int32, device=self.device)
+            rc = L.bsc_g1_comb_mul(ctypes.c_void_p(k.data_ptr()), n, ctypes.c_void_p(self._table.data_ptr()), W_BITS, N_WIN,
+                                   ctypes.c_void_p(jac.data_ptr()), stream)
+            assert rc == 0, rc
+            aff = torch.empty(n, AFF, dtype=torch.int32, device=self.device)
+            assert L.bsc_g1_normalize(ctypes.c_void_p(jac.data_ptr()), ctypes.c_void_p(aff.data_ptr()), n, stream) == 0
+            T_dev = torch.empty(n, 64, dtype=torch.uint8, device=self.device)
+            assert L.bsc_g1_affine_to_bytes(ctypes.c_void_p(aff.data_ptr()), ctypes.c_void_p(T_dev.data_ptr()), n, stream) == 0
+            self._keep = (k, jac, aff)
+        return dict(n=n, x=x, vw=vw, vbe=vbe, T_dev=T_dev)
+
+    def finish(self, handle, msgs: list[bytes], T_host: np.ndarray | None = None) -> list[bytes]:
+        """Complete the signatures over `msgs` (all the same length).  T_host: the [n, 64] commitment bytes if
+        the caller already copied handle['T_dev'] to the host; otherwise they are fetched (or computed on the
+        CPU when there is no GPU)."""
+        n = handle["n"]
+        if n == 0:
+            return []
+        L = self.L
+        if T_host is None:
+            if handle["T_dev"] is not None:
+                T_host = handle["T_dev"].cpu().numpy()
+            else:
+                gen = ctypes.create_string_buffer(64)
+                L.bsc_g1_generator(gen)
+                g_aff = np.empty(AFF, dtype=np.int32)
+                L.bsc_g1_bytes_to_affine_host(gen.raw, g_aff.ctypes.data_as(ctypes.c_void_p), 1)
+                jac = np.empty((n, JAC), dtype=np.int32)
+                L.bsc_g1_fixed_base_mul_host(handle["vw"].ctypes.data_as(ctypes.c_void_p), n,
+                                             g_aff.ctypes.data_as(ctypes.c_void_p), jac.ctypes.data_as(ctypes.c_void_p))
+                T_host = np.empty((n, 64), dtype=np.uint8)
+                L.bsc_g1_jac_to_bytes_host(jac.ctypes.data_as(ctypes.c_void_p), T_host.ctypes.data_as(ctypes.c_void_p), n)
+        T_host = np.ascontiguousarray(T_host, dtype=np.uint8)
+        m = np.frombuffer(b"".join(msgs), dtype=np.uint8).copy()
+        sigs = np.empty(n * 64, dtype=np.uint8)
+        L.bsc_schnorr_finish_batch(n, m.ctypes.data_as(ctypes.c_void_p), len(msgs[0]), handle["x"].ctypes.data_as(ctypes.c_void_p),
+                                   handle["vbe"].ctypes.data_as(ctypes.c_void_p), T_host.ctypes.data_as(ctypes.c_void_p),
+                                   sigs.ctypes.data_as(ctypes.c_void_p))
+        raw = sigs.tobytes()
+        return [raw[64 * i: 64 * i + 64] for i in range(n)]

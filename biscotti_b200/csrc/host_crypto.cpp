@@ -407,6 +407,35 @@ void bsc_schnorr_sign(const uint8_t* msg, size_t n, const uint8_t x_be[32], cons
   u256_to_be(sig, fe_to_u256(c));
   u256_to_be(sig + 32, fe_to_u256(r));
 }
+// Batched signing split in two so that the scalar multiplications T_i = v_i*G can run on the GPU
+// (g1_comb_mul_kernel): (1) derive nonces, (2) given the T_i, finish c_i = H(T_i || msg_i), r_i = v_i - x_i*c_i.
+// Nonce: v = SHA-256("bsc-schnorr-nonce" || x || tag) mod order, tag = caller-chosen unique bytes.
+void bsc_schnorr_nonces(int n, const uint8_t* tags, int taglen, const uint8_t* x_be, uint32_t* v_words_le,
+                        uint8_t* v_be) {
+  for (int i = 0; i < n; i++) {
+    Sha256 s;
+    sha256_init(s);
+    sha256_update(s, (const uint8_t*)"bsc-schnorr-nonce", 17);
+    sha256_update(s, x_be + 32 * (size_t)i, 32);
+    sha256_update(s, tags + (size_t)taglen * i, (size_t)taglen);
+    uint8_t h[32];
+    sha256_final(s, h);
+    const U256 v = fe_to_u256(fe_from_u256<BnN>(u256_from_be(h)));
+    memcpy(v_words_le + 8 * (size_t)i, v.v, 32);
+    u256_to_be(v_be + 32 * (size_t)i, v);
+  }
+}
+void bsc_schnorr_finish_batch(int n, const uint8_t* msgs, int msglen, const uint8_t* x_be, const uint8_t* v_be,
+                              const uint8_t* T, uint8_t* sigs) {
+  for (int i = 0; i < n; i++) {
+    const Fr x = fe_from_u256<BnN>(u256_from_be(x_be + 32 * (size_t)i));
+    const Fr v = fe_from_u256<BnN>(u256_from_be(v_be + 32 * (size_t)i));
+    const Fr c = hash_schnorr(msgs + (size_t)msglen * i, (size_t)msglen, T + 64 * (size_t)i);
+    const Fr r = fe_sub(v, fe_mul(x, c));
+    u256_to_be(sigs + 64 * (size_t)i, fe_to_u256(c));
+    u256_to_be(sigs + 64 * (size_t)i + 32, fe_to_u256(r));
+  }
+}
 int bsc_schnorr_verify(const uint8_t* msg, size_t n, const uint8_t pub[64], const uint8_t sig[64]) {
   const U256 order = mod_of<BnN>();
   U256 cu = u256_from_be(sig), ru = u256_from_be(sig + 32);

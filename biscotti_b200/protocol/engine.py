@@ -29,6 +29,7 @@ import torch
 
 from ..config import BiscottiConfig, DEFAULT_STAKE, STAKE_UNIT, POLY_SIZE, NOISE_TABLE_ITERS
 from ..crypto import primitives as cp
+from ..crypto.schnorr_batch import SchnorrBatchSigner
 from ..data.synthetic import make_data, poisoner_ids
 from ..ledger.chain import Blockchain, UpdateRecord
 from ..models.registry import Model
@@ -106,6 +107,7 @@ class BiscottiEngine:
         if cfg.commitments and cfg.secure_agg and cfg.mode == "biscotti":
             self.commit = CommitmentEngine(self.d, self.S, tau=cfg.srs_tau or self._random_tau(), device=self.device)
         self.vrf = cp.BatchedVRF([k.vrf_noise for k in self.keys], self.device)
+        self.signer = SchnorrBatchSigner(self.device) if (cfg.verification and cfg.sign_approvals) else None
         self.reports: list[BlockReport] = []
         self._rng = np.random.RandomState(cfg.seed * 65537 % (2**31))
         self._timing = False
@@ -277,6 +279,16 @@ class BiscottiEngine:
         if not enough:
             return self._finish_block(rep, [], None, phases, t0)   # main.go:2099-2117
         rep.n_contributors = len(contributors)
+        # approvals: every verifier signs the commitment of each update it accepted (krum.go:338-358).  The
+        # T = v*G halves of the signatures run on the GPU now, overlapped with the witness MSM; they are
+        # completed on the host when the block is assembled.  Signatures are produced for the updates that
+        # end up in the block (the contributors).
+        sig_handle = None
+        if self.signer is not None and self.commit is not None:
+            import struct
+
+            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in contributors for v in verifiers],
+                                            [struct.pack("<qii", it, p, v) for p in contributors for v in verifiers])
         local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
         sel = self._idx(local_contrib)
         agg_commit = None
@@ -339,6 +351,8 @@ class BiscottiEngine:
                     gathered = True
                 else:
                     want["cb"] = fullC_dev
+            if sig_handle is not None and sig_handle["T_dev"] is not None:
+                want["sigT"] = sig_handle["T_dev"]
             host = self._collect(want)
             if "cb" in host:
                 cb = host["cb"]
@@ -351,11 +365,14 @@ class BiscottiEngine:
                             commits[p] = cb[self.local_index[p]].tobytes()
                     if self.comm is not None:
                         commits = self.comm.merge_dicts(commits)
-            for p in contributors:
+            all_sigs = None
+            if sig_handle is not None and all(len(commits.get(p, b"")) == 64 for p in contributors):
+                msgs = [commits[p] for p in contributors for _ in verifiers]
+                all_sigs = self.signer.finish(sig_handle, msgs, host.get("sigT"))
+            nv = len(verifiers)
+            for ci, p in enumerate(contributors):
                 c = commits.get(p, b"")
-                sigs = []
-                if cfg.verification and c:
-                    sigs = [cp.schnorr_sign(c, self.keys[v].schnorr_secret) for v in verifiers] if cfg.extra.get("sign", False) else []
+                sigs = all_sigs[ci * nv: (ci + 1) * nv] if all_sigs is not None else []
                 rec = UpdateRecord(source=p, iteration=it, commitment=c, accepted=True, signatures=sigs)
                 if not cfg.secure_agg and p in self.local_index and self.world == 1:
                     rec.delta = self.U[self.local_index[p], : self.d].double().cpu().numpy()

@@ -100,6 +100,8 @@ int bsc_msm_table(const long long* Q, int ldq, const int* sel, int P, const int*
 
 void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p);
 
+int bsc_g1_comb_mul(const void* scalars_u256, int N, const void* table_affine, int w, int nw, void* out_jac, void* stream);
+
 int bsc_g1_fixed_base_mul(const void* scalars_u256, int N, const void* base_affine, void* out_jac, void* stream);
 
 int bsc_g1_normalize(const void* in_jac, void* out_affine, long long N, void* stream);
@@ -225,6 +227,13 @@ void bsc_schnorr_pubkey(const uint8_t x_be[32], uint8_t pub[64]);
 // sig = c || r, c = H(T || msg), r = v - x*c ; v supplied by the caller (32 random bytes)
 void bsc_schnorr_sign(const uint8_t* msg, size_t n, const uint8_t x_be[32], const uint8_t v_be[32], uint8_t sig[64]);
 
+// Batched signing split in two so that the scalar multiplications T_i = v_i*G can run on the GPU
+// (g1_comb_mul_kernel): (1) derive nonces, (2) given the T_i, finish c_i = H(T_i || msg_i), r_i = v_i - x_i*c_i.
+// Nonce: v = SHA-256("bsc-schnorr-nonce" || x || tag) mod order, tag = caller-chosen unique bytes.
+void bsc_schnorr_nonces(int n, const uint8_t* tags, int taglen, const uint8_t* x_be, uint32_t* v_words_le, uint8_t* v_be);
+
+void bsc_schnorr_finish_batch(int n, const uint8_t* msgs, int msglen, const uint8_t* x_be, const uint8_t* v_be, const uint8_t* T, uint8_t* sigs);
+
 int bsc_schnorr_verify(const uint8_t* msg, size_t n, const uint8_t pub[64], const uint8_t sig[64]);
 
 /* --------------------------------------------------------------------------------------------
@@ -328,6 +337,13 @@ int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const i
 
 // Fused reduce-scatter + reconstruct + SGD step + all-gather for this rank's chunk range [c0, c0+nc).
 int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank, int S, int d, int c0, int nc, const int* xs_host, const unsigned char* avail_host, double scale, unsigned int* done_counter, int* bad, unsigned long long epoch, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * sha256_ni.cpp - 
+ * -------------------------------------------------------------------------------------------- */
+void bsc_sha256_fast(const uint8_t* data, size_t n, uint8_t out[32]);
+
+int bsc_sha256_has_ni();
 
 #ifdef __cplusplus
 }

@@ -250,3 +250,20 @@ def test_vrf_quad_and_single_thread_kernels_agree():
     assert bytes(hq[0].numpy().tobytes()) == bytes(ho[0].numpy().tobytes())     # Gamma_p = x_p * H, all peers
     assert bytes(hq[0][5].tolist()) == keys[5].prove(msg)[1][64:]
     assert (tq == to).all()
+
+
+def test_batched_schnorr_on_device_matches_host_and_verifies():
+    import hashlib
+    import struct
+
+    from biscotti_b200.crypto.schnorr_batch import SchnorrBatchSigner
+
+    secrets = [hashlib.sha256(b"sk%d" % i).digest() for i in range(7)]
+    tags = [struct.pack("<qii", 3, i, 2 * i) for i in range(7)]
+    msgs = [bytes([i]) * 64 for i in range(7)]
+    gpu, cpu = SchnorrBatchSigner(DEV), SchnorrBatchSigner("cpu")
+    sg = gpu.finish(gpu.launch(secrets, tags), msgs)
+    sc = cpu.finish(cpu.launch(secrets, tags), msgs)
+    assert sg == sc                                           # comb kernel T = v*G equals the host double-and-add
+    for sk, m, s in zip(secrets, msgs, sg):
+        assert cp.schnorr_verify(m, cp.schnorr_pubkey(sk), s)
