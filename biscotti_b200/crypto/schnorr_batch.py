@@ -56,21 +56,35 @@ class SchnorrBatchSigner:
         if n:
             L.bsc_schnorr_nonces(n, tg.ctypes.data_as(ctypes.c_void_p), taglen, x.ctypes.data_as(ctypes.c_void_p),
                                  vw.ctypes.data_as(ctypes.c_void_p), vbe.ctypes.data_as(ctypes.c_void_p))
-        T_dev = None
+        T_dev, event = None, None
         if self.device.type == "cuda" and n:
             self._ensure_table()
-            k = torch.from_numpy(vw.view(np.int32)).pin_memory().to(self.device, non_blocking=True)
-            stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-            jac = torch.empty(n, JAC, dtype=torch.int32, device=self.device)
-            rc = L.bsc_g1_comb_mul(ctypes.c_void_p(k.data_ptr()), n, ctypes.c_void_p(self._table.data_ptr()), W_BITS, N_WIN,
-                                   ctypes.c_void_p(jac.data_ptr()), stream)
-            assert rc == 0, rc
-            aff = torch.empty(n, AFF, dtype=torch.int32, device=self.device)
-            assert L.bsc_g1_normalize(ctypes.c_void_p(jac.data_ptr()), ctypes.c_void_p(aff.data_ptr()), n, stream) == 0
-            T_dev = torch.empty(n, 64, dtype=torch.uint8, device=self.device)
-            assert L.bsc_g1_affine_to_bytes(ctypes.c_void_p(aff.data_ptr()), ctypes.c_void_p(T_dev.data_ptr()), n, stream) == 0
+            if not hasattr(self, "_side"):
+                self._side = torch.cuda.Stream(self.device)
+                self._k_pinned = torch.empty(4096, 8, dtype=torch.int32).pin_memory()
+            main = torch.cuda.current_stream(self.device)
+            kp = self._k_pinned[:n] if n <= self._k_pinned.shape[0] else torch.empty(n, 8, dtype=torch.int32).pin_memory()
+            kp.copy_(torch.from_numpy(vw.view(np.int32)[:n]))
+            # side stream: the comb kernel is a single small CTA-wave and runs under the witness MSM
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                stream = ctypes.c_void_p(self._side.cuda_stream)
+                k = kp.to(self.device, non_blocking=True)
+                jac = torch.empty(n, JAC, dtype=torch.int32, device=self.device)
+                rc = L.bsc_g1_comb_mul(ctypes.c_void_p(k.data_ptr()), n, ctypes.c_void_p(self._table.data_ptr()), W_BITS,
+                                       N_WIN, ctypes.c_void_p(jac.data_ptr()), stream)
+                assert rc == 0, rc
+                aff = torch.empty(n, AFF, dtype=torch.int32, device=self.device)
+                assert L.bsc_g1_normalize(ctypes.c_void_p(jac.data_ptr()), ctypes.c_void_p(aff.data_ptr()), n, stream) == 0
+                T_dev = torch.empty(n, 64, dtype=torch.uint8, device=self.device)
+                assert L.bsc_g1_affine_to_bytes(ctypes.c_void_p(aff.data_ptr()), ctypes.c_void_p(T_dev.data_ptr()), n,
+                                                stream) == 0
+                event = torch.cuda.Event()
+                event.record(self._side)
+            for t in (k, jac, aff, T_dev):
+                t.record_stream(self._side)
             self._keep = (k, jac, aff)
-        return dict(n=n, x=x, vw=vw, vbe=vbe, T_dev=T_dev)
+        return dict(n=n, x=x, vw=vw, vbe=vbe, T_dev=T_dev, event=event)
 
     def finish(self, handle, msgs: list[bytes], T_host: np.ndarray | None = None) -> list[bytes]:
         """Complete the signatures over `msgs` (all the same length).  T_host: the [n, 64] commitment bytes if
@@ -82,6 +96,8 @@ class SchnorrBatchSigner:
         L = self.L
         if T_host is None:
             if handle["T_dev"] is not None:
+                if handle.get("event") is not None:
+                    torch.cuda.current_stream(self.device).wait_event(handle["event"])
                 T_host = handle["T_dev"].cpu().numpy()
             else:
                 gen = ctypes.create_string_buffer(64)

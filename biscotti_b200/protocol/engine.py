@@ -352,6 +352,7 @@ class BiscottiEngine:
                 else:
                     want["cb"] = fullC_dev
             if sig_handle is not None and sig_handle["T_dev"] is not None:
+                torch.cuda.current_stream(dev).wait_event(sig_handle["event"])
                 want["sigT"] = sig_handle["T_dev"]
             host = self._collect(want)
             if "cb" in host:
