@@ -1,0 +1,248 @@
+// K2: batched-over-peers local step of the reference's one-convolution CNNs.
+//
+//   mnist_cnn : Conv2d(1,16,5,1,pad 4) + ReLU + MaxPool(1) + Linear(16*32*32, 10)   ML/Pytorch/mnist_cnn_model.py:12-39
+//   cifar_cnn : Conv2d(3,20,3,1,pad 3) + ReLU + MaxPool(1) + Linear(25920, 10)      ML/Pytorch/cifar_cnn_model.py:11-29
+//   step      : one minibatch, CrossEntropyLoss, clip_grad_norm 100, flatten in named_parameters order
+//               (conv.weight, conv.bias, fc.weight, fc.bias), update = -grad    ML/Pytorch/client.py:38-65
+//
+// Every peer starts from the same global weights, so the forward convolution is one launch over all
+// P*B images; the backward pass is per-peer (each peer needs its own weight gradient).  Five kernels:
+//   cnn1_conv_fwd     activations act[p][b][oc][oy][ox] = relu(conv)
+//   cnn1_fc_fwd_loss  logits, softmax, dlogits, loss, fc.bias gradient (one CTA per peer)
+//   cnn1_fc_bwd       fc.weight gradient (the bulk of the update: C*J floats per peer), d(act) masked by
+//                     ReLU written over act, partial squared norms
+//   cnn1_conv_wgrad   conv.weight / conv.bias gradients (one CTA per (peer, out-channel)), partial norms
+//   cnn1_clip_scale   fixed-order sum of the partial norms, U = -coef * grad
+// Partial norms are written to per-CTA slots and summed in index order: the clip coefficient (and with it
+// the ledger) is bit-reproducible.
+#include "common.cuh"
+
+namespace bsc {
+
+struct Cnn1Shape {
+  int IC, OC, K, pad, H, W;   // input channels, output channels, kernel, padding, input height/width
+  int OH, OW, J, C, B;        // output height/width, J = OC*OH*OW, classes, batch
+  int off_cw, off_cb, off_fw, off_fb, d;   // offsets of the four parameter tensors in the flat vector
+};
+
+__global__ void __launch_bounds__(256) cnn1_conv_fwd_kernel(const float* __restrict__ w, const float* __restrict__ X,
+                                                            float* __restrict__ act, Cnn1Shape s, int PB) {
+  extern __shared__ float sw[];   // conv weights + bias
+  const int nw = s.OC * s.IC * s.K * s.K;
+  for (int i = threadIdx.x; i < nw + s.OC; i += blockDim.x) sw[i] = i < nw ? w[s.off_cw + i] : w[s.off_cb + i - nw];
+  __syncthreads();
+  const long long total = (long long)PB * s.J;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int ox = (int)(t % s.OW);
+    const int oy = (int)((t / s.OW) % s.OH);
+    const int oc = (int)((t / ((long long)s.OW * s.OH)) % s.OC);
+    const long long img = t / s.J;
+    const float* x = X + img * s.IC * s.H * s.W;
+    float acc = sw[nw + oc];
+    for (int ic = 0; ic < s.IC; ic++)
+      for (int ky = 0; ky < s.K; ky++) {
+        const int iy = oy + ky - s.pad;
+        if (iy < 0 || iy >= s.H) continue;
+        for (int kx = 0; kx < s.K; kx++) {
+          const int ix = ox + kx - s.pad;
+          if (ix < 0 || ix >= s.W) continue;
+          acc = fmaf(sw[((oc * s.IC + ic) * s.K + ky) * s.K + kx], x[(ic * s.H + iy) * s.W + ix], acc);
+        }
+      }
+    act[t] = acc > 0.f ? acc : 0.f;
+  }
+}
+
+// one CTA per peer: logits[b][c], softmax, dl = (softmax - onehot)/B, loss, fc.bias gradient
+__global__ void __launch_bounds__(256) cnn1_fc_fwd_loss_kernel(const float* __restrict__ w, const float* __restrict__ act,
+                                                               const int* __restrict__ y, float* __restrict__ dl,
+                                                               float* __restrict__ loss, float* __restrict__ U, int ldu,
+                                                               Cnn1Shape s) {
+  __shared__ float sl[32 * 16];
+  __shared__ float red[40];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  const float* a = act + (size_t)p * s.B * s.J;
+  for (int pair = warp; pair < s.B * s.C; pair += nwarp) {
+    const int b = pair / s.C, c = pair % s.C;
+    const float* wr = w + s.off_fw + (size_t)c * s.J;
+    const float* ar = a + (size_t)b * s.J;
+    float acc = 0.f;
+    for (int j = lane; j < s.J; j += 32) acc = fmaf(ar[j], wr[j], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) sl[b * s.C + c] = acc + w[s.off_fb + c];
+  }
+  __syncthreads();
+  float myloss = 0.f;
+  if (tid < s.B) {
+    float m = -INFINITY;
+    for (int c = 0; c < s.C; c++) m = fmaxf(m, sl[tid * s.C + c]);
+    float sum = 0.f;
+    for (int c = 0; c < s.C; c++) sum += expf(sl[tid * s.C + c] - m);
+    const float lse = m + logf(sum);
+    const int lab = y[p * s.B + tid];
+    myloss = (lse - sl[tid * s.C + lab]) / (float)s.B;
+    for (int c = 0; c < s.C; c++) {
+      const float pr = expf(sl[tid * s.C + c] - lse);
+      sl[tid * s.C + c] = (pr - (c == lab ? 1.f : 0.f)) / (float)s.B;
+    }
+  }
+  const float tl = block_sum(myloss, red);
+  if (tid == 0 && loss) loss[p] = tl;
+  for (int i = tid; i < s.B * s.C; i += blockDim.x) dl[(size_t)p * s.B * s.C + i] = sl[i];
+  if (tid < s.C) {
+    float g = 0.f;
+    for (int b = 0; b < s.B; b++) g += sl[b * s.C + tid];
+    U[(size_t)p * ldu + s.off_fb + tid] = g;   // unscaled gradient; cnn1_clip_scale finishes it
+  }
+}
+
+// grid (ceil(J/256), P): thread j -> fc.weight gradient column j, masked d(act) written over act
+__global__ void __launch_bounds__(256) cnn1_fc_bwd_kernel(const float* __restrict__ w, float* __restrict__ act,
+                                                          const float* __restrict__ dl, float* __restrict__ U, int ldu,
+                                                          float* __restrict__ partial, int nslots, Cnn1Shape s) {
+  __shared__ float sdl[32 * 16];
+  __shared__ float red[40];
+  const int p = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int i = threadIdx.x; i < s.B * s.C; i += blockDim.x) sdl[i] = dl[(size_t)p * s.B * s.C + i];
+  __syncthreads();
+  float nrm = 0.f;
+  if (j < s.J) {
+    float wc[16];
+    for (int c = 0; c < s.C; c++) wc[c] = w[s.off_fw + (size_t)c * s.J + j];
+    float g[16];
+    for (int c = 0; c < s.C; c++) g[c] = 0.f;
+    float* a = act + (size_t)p * s.B * s.J + j;
+    for (int b = 0; b < s.B; b++) {
+      const float av = a[(size_t)b * s.J];
+      float da = 0.f;
+      for (int c = 0; c < s.C; c++) {
+        const float d = sdl[b * s.C + c];
+        g[c] = fmaf(d, av, g[c]);
+        da = fmaf(d, wc[c], da);
+      }
+      a[(size_t)b * s.J] = av > 0.f ? da : 0.f;   // d(pre-activation)
+    }
+    for (int c = 0; c < s.C; c++) {
+      U[(size_t)p * ldu + s.off_fw + (size_t)c * s.J + j] = g[c];
+      nrm = fmaf(g[c], g[c], nrm);
+    }
+  }
+  const float t = block_sum(nrm, red);
+  if (threadIdx.x == 0) partial[(size_t)p * nslots + blockIdx.x] = t;
+}
+
+// grid (OC, P): conv.weight[oc][*] and conv.bias[oc] gradients of one peer
+__global__ void __launch_bounds__(256) cnn1_conv_wgrad_kernel(const float* __restrict__ X, const float* __restrict__ dpre,
+                                                              float* __restrict__ U, int ldu,
+                                                              float* __restrict__ partial, int nslots, int slot0,
+                                                              Cnn1Shape s) {
+  __shared__ float red[40];
+  const int oc = blockIdx.x, p = blockIdx.y, tid = threadIdx.x;
+  const int taps = s.IC * s.K * s.K;   // <= 75 for the reference models
+  float acc[80];
+  for (int t = 0; t < taps; t++) acc[t] = 0.f;
+  float accb = 0.f;
+  const int npos = s.B * s.OH * s.OW;
+  for (int pos = tid; pos < npos; pos += blockDim.x) {
+    const int ox = pos % s.OW, oy = (pos / s.OW) % s.OH, b = pos / (s.OW * s.OH);
+    const float d = dpre[((size_t)(p * s.B + b) * s.OC + oc) * s.OH * s.OW + oy * s.OW + ox];
+    if (d == 0.f) continue;
+    accb += d;
+    const float* x = X + (size_t)(p * s.B + b) * s.IC * s.H * s.W;
+    int t = 0;
+    for (int ic = 0; ic < s.IC; ic++)
+      for (int ky = 0; ky < s.K; ky++) {
+        const int iy = oy + ky - s.pad;
+        for (int kx = 0; kx < s.K; kx++, t++) {
+          const int ix = ox + kx - s.pad;
+          if (iy >= 0 && iy < s.H && ix >= 0 && ix < s.W) acc[t] = fmaf(d, x[(ic * s.H + iy) * s.W + ix], acc[t]);
+        }
+      }
+  }
+  float nrm = 0.f;
+  for (int t = 0; t < taps; t++) {
+    const float g = block_sum(acc[t], red);
+    if (tid == 0) {
+      U[(size_t)p * ldu + s.off_cw + oc * taps + t] = g;
+      nrm = fmaf(g, g, nrm);
+    }
+  }
+  const float gb = block_sum(accb, red);
+  if (tid == 0) {
+    U[(size_t)p * ldu + s.off_cb + oc] = gb;
+    nrm = fmaf(gb, gb, nrm);
+    partial[(size_t)p * nslots + slot0 + oc] = nrm;
+  }
+}
+
+// one CTA per peer: total norm from the partial slots (+ fc.bias), then U = -coef * grad
+__global__ void __launch_bounds__(256) cnn1_clip_scale_kernel(float* __restrict__ U, int ldu, const float* __restrict__ partial,
+                                                              int nslots, float clip, Cnn1Shape s) {
+  __shared__ float coef_s;
+  const int p = blockIdx.x;
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int i = 0; i < nslots; i++) tot += partial[(size_t)p * nslots + i];   // fixed order
+    for (int c = 0; c < s.C; c++) {
+      const float g = U[(size_t)p * ldu + s.off_fb + c];
+      tot = fmaf(g, g, tot);
+    }
+    float coef = clip / (sqrtf(tot) + 1e-6f);
+    coef_s = coef > 1.f ? 1.f : coef;
+  }
+  __syncthreads();
+  const float m = -coef_s;
+  float* row = U + (size_t)p * ldu;
+  for (int k = threadIdx.x; k < s.d; k += blockDim.x) row[k] *= m;
+  for (int k = s.d + threadIdx.x; k < ldu; k += blockDim.x) row[k] = 0.f;
+}
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC
+long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, int H, int W, int C) {
+  const int OH = H + 2 * pad - K + 1, OW = W + 2 * pad - K + 1;
+  const long long J = (long long)OC * OH * OW;
+  const long long nslots = (J + 255) / 256 + OC;
+  return (long long)P * B * J + (long long)P * B * C + (long long)P * nslots;
+}
+
+// One-conv-layer CNN local step for P peers.  w: flat global weights; X: [P][B][IC][H][W]; y: [P][B];
+// U: [P][ldu] out (= -clip(grad)); loss: [P] (may be null); scratch: see bsc_cnn1_scratch_floats.
+int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B,
+                        int IC, int OC, int K, int pad, int H, int W, int C, int ldu, float clip, void* stream) {
+  Cnn1Shape s;
+  s.IC = IC; s.OC = OC; s.K = K; s.pad = pad; s.H = H; s.W = W;
+  s.OH = H + 2 * pad - K + 1;
+  s.OW = W + 2 * pad - K + 1;
+  s.J = OC * s.OH * s.OW;
+  s.C = C;
+  s.B = B;
+  s.off_cw = 0;
+  s.off_cb = OC * IC * K * K;
+  s.off_fw = s.off_cb + OC;
+  s.off_fb = s.off_fw + C * s.J;
+  s.d = s.off_fb + C;
+  if (C > 16 || B > 32 || IC * K * K > 80 || ldu < s.d) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nfc = (s.J + 255) / 256;
+  const int nslots = nfc + OC;
+  float* act = scratch;
+  float* dl = act + (size_t)P * B * s.J;
+  float* partial = dl + (size_t)P * B * C;
+  const long long total = (long long)P * B * s.J;
+  const int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  const size_t smem = (size_t)(OC * IC * K * K + OC) * sizeof(float);
+  cnn1_conv_fwd_kernel<<<grid, 256, smem, st>>>(w, X, act, s, P * B);
+  cnn1_fc_fwd_loss_kernel<<<P, 256, 0, st>>>(w, act, y, dl, loss, U, ldu, s);
+  cnn1_fc_bwd_kernel<<<dim3(nfc, P), 256, 0, st>>>(w, act, dl, U, ldu, partial, nslots, s);
+  cnn1_conv_wgrad_kernel<<<dim3(OC, P), 256, 0, st>>>(X, act, U, ldu, partial, nslots, nfc, s);
+  cnn1_clip_scale_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, s);
+  return finish_launch("cnn1_local_step", 5);
+}
+
+}  // extern "C"

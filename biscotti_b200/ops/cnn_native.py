@@ -1,0 +1,36 @@
+"""ctypes wrapper of the one-conv-layer CNN local-step kernels (csrc/kernels_cnn.cu)."""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from .. import _native
+from ._call import ptr, stream, check
+
+_scratch = {}
+
+
+def local_step(kind: str, w32: torch.Tensor, Xb: torch.Tensor, yb: torch.Tensor, clip: float, out: torch.Tensor):
+    """Xb: [P, B, IC*H*W] minibatch, yb: [P, B] int32, out: [P, ldu] <- -clip(grad)."""
+    from ..models.registry import CNN_ARCH
+
+    arch = CNN_ARCH[kind]
+    c = arch["convs"][0]
+    IC, H, W = arch["image"]
+    P, B = Xb.shape[0], Xb.shape[1]
+    L = _native.load()
+    L.bsc_cnn1_scratch_floats.restype = ctypes.c_longlong
+    n = L.bsc_cnn1_scratch_floats(P, B, IC, c.cout, c.k, c.pad, H, W, arch["n_classes"])
+    key = (Xb.device, n)
+    buf = _scratch.get(key)
+    if buf is None:
+        _scratch.clear()
+        buf = torch.empty(n, dtype=torch.float32, device=Xb.device)
+        _scratch[key] = buf
+    Xc = Xb.contiguous().float()
+    yc = yb.contiguous().int()
+    check(L.bsc_cnn1_local_step(ptr(w32), ptr(Xc), ptr(yc), ptr(out), None, ptr(buf), P, B, IC, c.cout, c.k, c.pad, H, W,
+                                arch["n_classes"], out.stride(0), ctypes.c_float(clip), stream(Xb.device)),
+          "cnn1_local_step")
+    return out

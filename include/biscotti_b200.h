@@ -339,6 +339,16 @@ int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const i
 int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank, int S, int d, int c0, int nc, const int* xs_host, const unsigned char* avail_host, double scale, unsigned int* done_counter, int* bad, unsigned long long epoch, void* stream);
 
 /* --------------------------------------------------------------------------------------------
+ * kernels_cnn.cu - 
+ * -------------------------------------------------------------------------------------------- */
+// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC
+long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, int H, int W, int C);
+
+// One-conv-layer CNN local step for P peers.  w: flat global weights; X: [P][B][IC][H][W]; y: [P][B];
+// U: [P][ldu] out (= -clip(grad)); loss: [P] (may be null); scratch: see bsc_cnn1_scratch_floats.
+int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B, int IC, int OC, int K, int pad, int H, int W, int C, int ldu, float clip, void* stream);
+
+/* --------------------------------------------------------------------------------------------
  * sha256_ni.cpp - 
  * -------------------------------------------------------------------------------------------- */
 void bsc_sha256_fast(const uint8_t* data, size_t n, uint8_t out[32]);

@@ -267,3 +267,30 @@ def test_batched_schnorr_on_device_matches_host_and_verifies():
     assert sg == sc                                           # comb kernel T = v*G equals the host double-and-add
     for sk, m, s in zip(secrets, msgs, sg):
         assert cp.schnorr_verify(m, cp.schnorr_pubkey(sk), s)
+
+
+@pytest.mark.parametrize("kind", ["mnist_cnn", "cifar_cnn"])
+def test_cnn_local_step_kernels_match_autograd(kind):
+    """Hand-written conv/fc forward+backward (kernels_cnn.cu) vs per-peer torch autograd on the CPU."""
+    from biscotti_b200.models.registry import CNN_ARCH, cnn_local_step, cnn_param_slices
+    from biscotti_b200.ops import cnn_native
+
+    arch = CNN_ARCH[kind]
+    _, d = cnn_param_slices(arch)
+    torch.manual_seed(8)
+    P, B = 3, 10
+    F = arch["image"][0] * arch["image"][1] * arch["image"][2]
+    w = torch.randn(d) * 0.02
+    Xb = torch.randn(P, B, F)
+    yb = torch.randint(0, arch["n_classes"], (P, B), dtype=torch.int32)
+    ref = cnn_local_step(arch, w, Xb, yb, 100.0, torch.zeros(P, d))
+    out = torch.zeros(P, d + 2, device=DEV)
+    cnn_native.local_step(kind, w.to(DEV), Xb.to(DEV), yb.to(DEV), 100.0, out)
+    got = out.cpu()[:, :d]
+    scale = float(ref.abs().max())
+    assert torch.allclose(got, ref, rtol=1e-3, atol=2e-5 * max(1.0, scale)), float((got - ref).abs().max())
+    # clipping path
+    ref2 = cnn_local_step(arch, w, Xb, yb, 0.05, torch.zeros(P, d))
+    cnn_native.local_step(kind, w.to(DEV), Xb.to(DEV), yb.to(DEV), 0.05, out)
+    assert torch.allclose(out.cpu()[:, :d], ref2, rtol=1e-3, atol=1e-6)
+    assert abs(float(out[0, :d].norm()) - 0.05) < 1e-3
