@@ -69,6 +69,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_noise_row_host", None, c_p, c_i, c_ull, c_i, c_i, c_f)
     sig("bsc_gram_simt", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
     sig("bsc_krum_select", c_i, c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_p, c_p, c_p)
+    sig("bsc_krum_select_mc", c_i, c_p, c_i, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_p)
     sig("bsc_eval_softmax", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p)
     sig("bsc_eval_logistic", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
     sig("bsc_cnn1_scratch_floats", c_ll, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i)

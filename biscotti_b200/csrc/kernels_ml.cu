@@ -342,6 +342,84 @@ __global__ void __launch_bounds__(256) krum_select_kernel(const float* __restric
   }
 }
 
+// Multi-CTA form of the Krum tail: one warp per row, 8 rows per CTA (scores), then a single small CTA
+// ranks the scores (accept).  Same arithmetic and the same fixed reduction order as krum_select_kernel,
+// so both produce identical bits; this one removes the single-CTA serialisation over rows.
+//   rows (optional): participant i lives at row/column rows[i] of the partial Grams
+//   norms == nullptr: squared norms are taken from the reduced Gram's diagonal
+__global__ void __launch_bounds__(256) krum_scores_kernel(const float* __restrict__ Gpart, int nsplit, int ldg,
+                                                          const float* __restrict__ norms, const int* __restrict__ rows,
+                                                          int n, int clip, float* __restrict__ scores,
+                                                          float* __restrict__ Dout, int np2) {
+  extern __shared__ float srow[];  // [nwarp][np2] + [n] norms
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  float* myrow = srow + (size_t)warp * np2;
+  float* snorm = srow + (size_t)nwarp * np2;
+  for (int i = tid; i < n; i += blockDim.x) {
+    if (norms) {
+      snorm[i] = norms[i];
+    } else {
+      const int r = rows ? rows[i] : i;
+      float g = 0.f;
+      for (int s = 0; s < nsplit; s++) g += Gpart[((size_t)s * ldg + r) * ldg + r];
+      snorm[i] = g;
+    }
+  }
+  __syncthreads();
+  const int i = blockIdx.x * nwarp + warp;
+  if (i >= n) return;
+  const int group = n - clip;
+  const int ri = rows ? rows[i] : i;
+  const float ni = snorm[i];
+  for (int j = lane; j < np2; j += 32) {
+    float v = INFINITY;
+    if (j < n) {
+      const int rj = rows ? rows[j] : j;
+      float g = 0.f;
+      for (int s = 0; s < nsplit; s++) g += Gpart[((size_t)s * ldg + ri) * ldg + rj];
+      v = ni + snorm[j] - 2.f * g;
+      if (Dout) Dout[(size_t)i * n + j] = v;
+    }
+    myrow[j] = v;
+  }
+  __syncwarp();
+  for (int k = 2; k <= np2; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = lane; t < np2; t += 32) {
+        const int ixj = t ^ j;
+        if (ixj > t) {
+          const float a = myrow[t], b = myrow[ixj];
+          const bool up = ((t & k) == 0);
+          if ((a > b) == up) {
+            myrow[t] = b;
+            myrow[ixj] = a;
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+  float s = 0.f;
+  for (int j = 1 + lane; j < group - 1; j += 32) s += myrow[j];
+  s = warp_sum(s);
+  if (lane == 0) scores[i] = s;
+}
+__global__ void __launch_bounds__(256) krum_accept_kernel(const float* __restrict__ scores, int n, int clip,
+                                                          unsigned char* __restrict__ accept) {
+  extern __shared__ float ssc[];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) ssc[i] = scores[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float si = ssc[i];
+    int rank = 0;
+    for (int j = 0; j < n; j++) {
+      const float sj = ssc[j];
+      rank += (sj < si) || (sj == si && j < i);
+    }
+    accept[i] = rank < (n - clip) ? 1 : 0;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K14/K15: argmax classification error of linear models over a held-out set, batched over
 // candidate weight vectors (RONI = error(w + delta_i) - error(w), client_obj.py:100-112).
@@ -541,6 +619,20 @@ int bsc_krum_scores_static(const float* A, const float* norms, int n, int d, int
   krum_select_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(scratch, ksplit, n, norms, n, clip, scores, accept,
                                                               nullptr, np2);
   return finish_launch("krum_scores_static/select");
+}
+
+// Multi-CTA Krum tail (scores over a grid of row-groups, then the ranking).  rows / norms may be null
+// (identity mapping / norms from the Gram diagonal).  Bit-identical to bsc_krum_select.
+int bsc_krum_select_mc(const float* Gpart, int nsplit, int ldg, const float* norms, const int* rows, int n, int clip,
+                       float* scores, unsigned char* accept, float* Dout, void* stream) {
+  if (n > 1024 || n < 3) return -1;
+  int np2 = 32;
+  while (np2 < n) np2 <<= 1;
+  const size_t smem = ((size_t)8 * np2 + n) * sizeof(float);
+  krum_scores_kernel<<<(n + 7) / 8, 256, smem, (cudaStream_t)stream>>>(Gpart, nsplit, ldg, norms, rows, n, clip, scores,
+                                                                        Dout, np2);
+  krum_accept_kernel<<<1, 256, (size_t)n * sizeof(float), (cudaStream_t)stream>>>(scores, n, clip, accept);
+  return finish_launch("krum_select_mc", 2);
 }
 
 int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F,

@@ -50,7 +50,12 @@ def krum_select(Gpart: torch.Tensor, norms: torch.Tensor, n: int, clip: int, wan
     scores = torch.empty(n, dtype=torch.float32, device=Gpart.device)
     accept = torch.empty(n, dtype=torch.uint8, device=Gpart.device)
     D = torch.empty(n, n, dtype=torch.float32, device=Gpart.device) if want_D else None
-    check(lib().bsc_krum_select(ptr(Gpart), nsplit, ldg, ptr(norms), n, clip, ptr(scores), ptr(accept), ptr(D),
+    L = lib()
+    if hasattr(L, "bsc_krum_select_mc"):
+        check(L.bsc_krum_select_mc(ptr(Gpart), nsplit, ldg, ptr(norms), None, n, clip, ptr(scores), ptr(accept), ptr(D),
+                                   stream(Gpart.device)), "krum_select_mc")
+    else:
+        check(L.bsc_krum_select(ptr(Gpart), nsplit, ldg, ptr(norms), n, clip, ptr(scores), ptr(accept), ptr(D),
                                 stream(Gpart.device)), "krum_select")
     return scores, accept, D
 

@@ -55,6 +55,10 @@ int bsc_krum_static_splits(int d);
 // threads — race on it; serialise them on one stream.
 int bsc_krum_scores_static(const float* A, const float* norms, int n, int d, int lda, int clip, float* scores, unsigned char* accept, void* stream);
 
+// Multi-CTA Krum tail (scores over a grid of row-groups, then the ranking).  rows / norms may be null
+// (identity mapping / norms from the Gram diagonal).  Bit-identical to bsc_krum_select.
+int bsc_krum_select_mc(const float* Gpart, int nsplit, int ldg, const float* norms, const int* rows, int n, int clip, float* scores, unsigned char* accept, float* Dout, void* stream);
+
 int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F, int C, int ldw, void* stream);
 
 int bsc_eval_logistic(const float* Wc, const float* base, const float* X, const float* y, int* wrong, int M, int N, int F, int ldw, void* stream);
