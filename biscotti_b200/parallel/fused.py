@@ -173,10 +173,18 @@ class FusedComm(NcclComm):
         rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)
-        _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg,
-                                            c_p(rows.data_ptr()), n, clip, c_p(self.base + self.o_flags), self.world,
-                                            epoch, c_p(scores.data_ptr()), c_p(accept.data_ptr()), self._stream()),
-               "krum_select_fused")
+        if hasattr(self.L, "bsc_krum_select_mc"):
+            # wait until every rank's partials have landed here, then the multi-CTA tail (norms from the
+            # reduced Gram's diagonal, participants addressed through their slots)
+            self.wait(SLOT_GRAM, epoch)
+            _check(self.L.bsc_krum_select_mc(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg, None,
+                                             c_p(rows.data_ptr()), n, clip, c_p(scores.data_ptr()),
+                                             c_p(accept.data_ptr()), None, self._stream()), "krum_select_mc")
+        else:
+            _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg,
+                                                c_p(rows.data_ptr()), n, clip, c_p(self.base + self.o_flags), self.world,
+                                                epoch, c_p(scores.data_ptr()), c_p(accept.data_ptr()), self._stream()),
+                   "krum_select_fused")
         return scores, accept
 
     # ---- fused secure aggregation ---------------------------------------------------------------------
