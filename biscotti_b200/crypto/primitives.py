@@ -155,18 +155,27 @@ class BatchedVRF:
             self._hpt_pinned = torch.empty(64, dtype=torch.uint8).pin_memory()
             self._hd = torch.empty(64, dtype=torch.uint8, device=self.device)
             self._gam = torch.empty(n, 32, dtype=torch.uint8, device=self.device)
+            self._xyz = torch.empty(n, 30, dtype=torch.int32, device=self.device)
+            self._host_xyz = torch.empty(n, 30, dtype=torch.int32).pin_memory()
         self._hpt_pinned.copy_(hxy)
         self._side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(self._side):
             self._hd.copy_(self._hpt_pinned, non_blocking=True)
-            kern = L.bsc_ed25519_scalarmult_quad if self.kernel == "quad" else L.bsc_ed25519_scalarmult_r25
-            rc = kern(ctypes.c_void_p(self.scalars.data_ptr()),
-                                              ctypes.c_void_p(self._hd.data_ptr()), n,
-                                              ctypes.c_void_p(self._gam.data_ptr()),
-                                              ctypes.c_void_p(self._side.cuda_stream))
+            if self.kernel == "quad":
+                # projective results; the single shared inversion + compression happens on the host
+                rc = L.bsc_ed25519_scalarmult_quad_xyz(ctypes.c_void_p(self.scalars.data_ptr()),
+                                                       ctypes.c_void_p(self._hd.data_ptr()), n,
+                                                       ctypes.c_void_p(self._xyz.data_ptr()),
+                                                       ctypes.c_void_p(self._side.cuda_stream))
+                self._host_xyz.copy_(self._xyz, non_blocking=True)
+            else:
+                rc = L.bsc_ed25519_scalarmult_r25(ctypes.c_void_p(self.scalars.data_ptr()),
+                                                  ctypes.c_void_p(self._hd.data_ptr()), n,
+                                                  ctypes.c_void_p(self._gam.data_ptr()),
+                                                  ctypes.c_void_p(self._side.cuda_stream))
+                self._host_gam.copy_(self._gam, non_blocking=True)
             if rc:
-                raise RuntimeError("ed25519_scalarmult_r25 failed")
-            self._host_gam.copy_(self._gam, non_blocking=True)
+                raise RuntimeError("ed25519 scalar multiplication kernel failed")
             ev = torch.cuda.Event()
             ev.record(self._side)
         return (self._host_gam, ev, msg)
@@ -174,9 +183,12 @@ class BatchedVRF:
     def noiser_table(self, handle, stake: list[int], is_worker: np.ndarray, want: int) -> np.ndarray:
         """[n, want] int32 table of noiser ids (-1 = none) for every worker (vrf.go:54-100)."""
         gam, ev, msg = handle
+        n = len(self.keys)
         if ev is not None:
             ev.synchronize()
-        n = len(self.keys)
+            if self.kernel == "quad":
+                _L().bsc_ed25519_compress_batch(ctypes.c_void_p(self._host_xyz.data_ptr()), n,
+                                                ctypes.c_void_p(gam.data_ptr()))
         out = np.full((n, max(1, want)), -1, dtype=np.int32)
         st = np.asarray(stake, dtype=np.int32)
         iw = np.ascontiguousarray(is_worker, dtype=np.uint8)

@@ -73,7 +73,7 @@ HD F25 f25_carry(int64_t h[10]) {
 // A real function on the device (see HDNI in field.cuh): one warp per SM runs this kernel, so every
 // instruction-cache miss is fully exposed; inlined, one window step is ~7k instructions (118 KB).
 template <bool DBL>
-HDNI F25 f25_mul_t(const F25& f, const F25& g) {
+HD F25 f25_mul_inl(const F25& f, const F25& g) {
   int32_t g19[10], f2[10];
 #pragma unroll
   for (int i = 0; i < 10; i++) {
@@ -98,6 +98,11 @@ HDNI F25 f25_mul_t(const F25& f, const F25& g) {
     for (int k = 0; k < 10; k++) h[k] += h[k];
   }
   return f25_carry(h);
+}
+// out-of-line instance for code with many call sites (point formulas, inversion chains)
+template <bool DBL>
+HDNI F25 f25_mul_t(const F25& f, const F25& g) {
+  return f25_mul_inl<DBL>(f, g);
 }
 HD F25 f25_mul(const F25& f, const F25& g) { return f25_mul_t<false>(f, g); }
 HD F25 f25_sq(const F25& f) { return f25_mul_t<false>(f, f); }

@@ -163,7 +163,8 @@ __device__ __forceinline__ F25 f25_sel4(int j, const F25& a, const F25& b, const
 
 __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsigned char* __restrict__ scalars,
                                                                       const unsigned char* __restrict__ hxy, int N,
-                                                                      unsigned char* __restrict__ out) {
+                                                                      unsigned char* __restrict__ out,
+                                                                      int32_t* __restrict__ xyz_out) {
   __shared__ EdCached table[9];   // 1H..8H, then the identity (digit 0) so every quad runs the same steps
   if (threadIdx.x == 0) {
     uint8_t b[64];
@@ -218,7 +219,7 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
         a = f25_sel4(j, ypx, ymx, q.T2d, Z);
         b = f25_sel4(j, neg ? q.YmX : q.YpX, neg ? q.YpX : q.YmX, T, q.Z);
       }
-      const F25 r = f25_mul(a, b);
+      const F25 r = f25_mul_inl<false>(a, b);   // two call sites only: inlined, no call / stack traffic
       const F25 r0 = quad_pick(r, 0), r1 = quad_pick(r, 1), r2 = quad_pick(r, 2), r3 = quad_pick(r, 3);
       F25 cX, cY, cZ, cT;   // completed point ((cX:cZ), (cY:cT))
       if (!is_add) {
@@ -238,7 +239,7 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
       // second round: X3 = cX*cT, Y3 = cY*cZ, Z3 = cZ*cT, T3 = cX*cY
       const F25 a2 = f25_sel4(j, cX, cY, cZ, cX);
       const F25 b2 = f25_sel4(j, cT, cZ, cT, cY);
-      const F25 s = f25_mul(a2, b2);
+      const F25 s = f25_mul_inl<false>(a2, b2);
       X = quad_pick(s, 0);
       Y = quad_pick(s, 1);
       Z = quad_pick(s, 2);
@@ -246,9 +247,20 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
     }
   }
   if (peer < N && j == 0) {
-    EdP3 p;
-    p.X = X; p.Y = Y; p.Z = Z; p.T = T;
-    edr_compress(out + 32 * (size_t)peer, p);
+    if (xyz_out) {
+      // projective result; the host normalises all peers with one shared inversion (Montgomery's trick):
+      // the ~265 sequential squarings of an in-kernel inversion would be a fifth of this kernel
+      int32_t* o = xyz_out + 30 * (size_t)peer;
+      for (int i = 0; i < 10; i++) {
+        o[i] = X.v[i];
+        o[10 + i] = Y.v[i];
+        o[20 + i] = Z.v[i];
+      }
+    } else {
+      EdP3 p;
+      p.X = X; p.Y = Y; p.Z = Z; p.T = T;
+      edr_compress(out + 32 * (size_t)peer, p);
+    }
   }
 }
 
@@ -450,8 +462,43 @@ int bsc_ed25519_scalarmult_quad(const unsigned char* scalars, const unsigned cha
                                 void* stream) {
   if (N == 0) return 0;
   const int threads = 4 * N;
-  ed25519_scalarmult_quad_kernel<<<(threads + 127) / 128, 128, 0, (cudaStream_t)stream>>>(scalars, hxy, N, out);
+  ed25519_scalarmult_quad_kernel<<<(threads + 127) / 128, 128, 0, (cudaStream_t)stream>>>(scalars, hxy, N, out, nullptr);
   return finish_launch("ed25519_scalarmult_quad");
+}
+// same, but leaves the results projective: xyz_out[i] = X, Y, Z as 3 x 10 radix-2^25.5 limbs
+int bsc_ed25519_scalarmult_quad_xyz(const unsigned char* scalars, const unsigned char* hxy, int N, int* xyz_out,
+                                    void* stream) {
+  if (N == 0) return 0;
+  const int threads = 4 * N;
+  ed25519_scalarmult_quad_kernel<<<(threads + 127) / 128, 128, 0, (cudaStream_t)stream>>>(scalars, hxy, N, nullptr,
+                                                                                          xyz_out);
+  return finish_launch("ed25519_scalarmult_quad_xyz");
+}
+// host: compress N projective points with a single field inversion (prefix products)
+void bsc_ed25519_compress_batch(const int* xyz, int N, unsigned char* out) {
+  std::vector<F25> pre((size_t)N);
+  F25 run = f25_one();
+  for (int i = 0; i < N; i++) {
+    F25 z;
+    for (int k = 0; k < 10; k++) z.v[k] = xyz[30 * (size_t)i + 20 + k];
+    run = f25_mul(run, z);
+    pre[(size_t)i] = run;
+  }
+  F25 inv = f25_invert(run);
+  for (int i = N - 1; i >= 0; i--) {
+    F25 x, y, z;
+    for (int k = 0; k < 10; k++) {
+      x.v[k] = xyz[30 * (size_t)i + k];
+      y.v[k] = xyz[30 * (size_t)i + 10 + k];
+      z.v[k] = xyz[30 * (size_t)i + 20 + k];
+    }
+    const F25 zi = i > 0 ? f25_mul(inv, pre[(size_t)i - 1]) : inv;
+    inv = f25_mul(inv, z);
+    uint8_t xb[32];
+    f25_tobytes(out + 32 * (size_t)i, f25_mul(y, zi));
+    f25_tobytes(xb, f25_mul(x, zi));
+    out[32 * (size_t)i + 31] ^= (uint8_t)((xb[0] & 1) << 7);
+  }
 }
 void bsc_ed25519_scalarmult_r25_host(const unsigned char* scalars, const unsigned char* hxy, int N,
                                      unsigned char* out) {
