@@ -230,6 +230,24 @@ class CommitmentEngine:
             return jac.view(P, self.nchunk, self.S, JAC)
         return self.normalize(jac).view(P, self.nchunk, self.S, AFF)
 
+    def verify_commitment(self, Q_row: torch.Tensor, commitment: bytes) -> bool:
+        """verifyCommitment (kyber.go:564-577): recompute the full-vector commitment and compare bytes."""
+        C = self.chunk_commitments(Q_row.view(1, -1), affine=False)
+        return self.to_bytes(self.full_commitments(C)) == commitment
+
+    def verify_share_trapdoor(self, chunk_commit: bytes, witness: bytes, chunk: int, s: int, y: int) -> bool:
+        """Opening check C - y*tau^(10c)*G == (tau - x_s)*W.  verifySecret (kyber.go:650-673) does this with a
+        pairing because tau is secret; with the reference's public tau = 2 (publicKey.go:36) — or any tau this
+        engine was built with — the same relation can be checked in G1 directly.  Used by tests and the
+        peer-scale 'Shamir verify' sweep; an unknown-tau deployment needs the pairing (not implemented)."""
+        from ..oracle import bn256 as O
+
+        x = s - 10
+        tau = self.tau % O.ORDER
+        lhs = O.add(O.from_bytes(chunk_commit), O.neg(O.mul(O.GEN, (y * pow(tau, 10 * chunk, O.ORDER)) % O.ORDER)))
+        rhs = O.mul(O.from_bytes(witness), (tau - x) % O.ORDER)
+        return lhs == rhs
+
     def aggregate(self, pts: torch.Tensor, sel: torch.Tensor, affine: bool = True) -> torch.Tensor:
         """Miner-side homomorphic add over contributing peers: pts [P, G..., 16|24] -> [G..., 16|24]."""
         P = pts.shape[0]

@@ -266,8 +266,11 @@ class BiscottiEngine:
             rep.unmasked_updates = sum(1 for p in krum_set if vcol and noisers_of.get(p) and
                                        all(q in self.colluder_ids for q in noisers_of[p]))
 
-        # ---- 6. approvals: every verifier signs the commitment of each accepted update
-        approved = accepted if len(verifiers) >= max(1, len(verifiers) // 2) else []
+        # ---- 6. approvals: every reachable verifier signs the commitment of each accepted update; a worker
+        # proceeds when it holds >= floor(nv/2) signatures (main.go:1686).  All verifiers run the same Krum on
+        # the same set here, so the signature count is the number of live verifiers.
+        signers = [v for v in verifiers if self.alive[v]]
+        approved = accepted if (signers and len(signers) >= len(verifiers) // 2) else []
 
         # ---- 7/8. shares, witnesses, aggregation, reconstruction, SGD step
         share_order = [p for p in self._arrival_order(approved, "shares")]
@@ -287,8 +290,8 @@ class BiscottiEngine:
         if self.signer is not None and self.commit is not None:
             import struct
 
-            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in contributors for v in verifiers],
-                                            [struct.pack("<qii", it, p, v) for p in contributors for v in verifiers])
+            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in contributors for v in signers],
+                                            [struct.pack("<qii", it, p, v) for p in contributors for v in signers])
         local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
         sel = self._idx(local_contrib)
         agg_commit = None
@@ -368,9 +371,9 @@ class BiscottiEngine:
                         commits = self.comm.merge_dicts(commits)
             all_sigs = None
             if sig_handle is not None and all(len(commits.get(p, b"")) == 64 for p in contributors):
-                msgs = [commits[p] for p in contributors for _ in verifiers]
+                msgs = [commits[p] for p in contributors for _ in signers]
                 all_sigs = self.signer.finish(sig_handle, msgs, host.get("sigT"))
-            nv = len(verifiers)
+            nv = len(signers)
             for ci, p in enumerate(contributors):
                 c = commits.get(p, b"")
                 sigs = all_sigs[ci * nv: (ci + 1) * nv] if all_sigs is not None else []

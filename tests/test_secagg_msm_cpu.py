@@ -132,3 +132,21 @@ def test_miner_aggregation_is_homomorphic():
     agg = eng.to_bytes(eng.aggregate(C, sel))
     Csum = eng.to_bytes(eng.chunk_commitments((Q[0] + Q[2]).unsqueeze(0)))
     assert agg == Csum      # aggregateSecret (kyber.go:244-287): sum of commitments commits to the sum
+
+
+def test_verify_commitment_and_share_opening_helpers():
+    d, S = 20, 21
+    eng = CommitmentEngine(d, S, tau=2, device="cpu")
+    g = torch.Generator().manual_seed(9)
+    Q = torch.randint(-10**5, 10**5, (1, 20), generator=g, dtype=torch.int64)
+    C = eng.chunk_commitments(Q)
+    full = eng.to_bytes(eng.full_commitments(C))
+    assert eng.verify_commitment(Q[0], full)
+    assert not eng.verify_commitment(Q[0] + 1, full)
+    W = eng.witnesses(Q)
+    Y = secagg.shares_eval(Q, S)
+    Cb, Wb = eng.to_bytes(C), eng.to_bytes(W)
+    for c, s in ((0, 3), (1, 10), (1, 20)):
+        off = 64 * (c * S + s)
+        assert eng.verify_share_trapdoor(Cb[64 * c:64 * c + 64], Wb[off:off + 64], c, s, int(Y[0, c, s]))
+        assert not eng.verify_share_trapdoor(Cb[64 * c:64 * c + 64], Wb[off:off + 64], c, s, int(Y[0, c, s]) + 1)
