@@ -135,6 +135,57 @@ def run_vrf_demo(a) -> int:
     return 0
 
 
+def run_kzg_demo(a) -> int:
+    """kyber-demo/kyber.go + DistSys/kyber.go:289-454 (commented main): share two copies of one vector to three
+    miners, aggregate homomorphically, recover the sum, and check a KZG opening."""
+    import torch
+
+    from .ops import secagg
+    from .ops.msm import CommitmentEngine
+
+    d, S = 25, 21
+    eng = CommitmentEngine(d, S, tau=2, device="cpu")
+    delta = torch.tensor([[-0.0105, -0.0166, 0.0049] + [0.001 * i for i in range(22)] + [0.0] * 3])
+    Q = secagg.quantize(torch.cat([delta, delta]), d, 4)
+    print("quantised head:", Q[0, :6].tolist())
+    C = eng.chunk_commitments(Q)
+    W = eng.witnesses(Q)
+    Y = secagg.shares_eval(Q, S)
+    per = S // 3
+    for m in range(3):
+        print(f"miner {m} holds shares {m * per}..{(m + 1) * per - 1} of {Q.shape[1] // 10} chunks")
+    Ysum = Y.sum(0).contiguous()
+    w = torch.zeros(d, dtype=torch.float64)
+    _, bad = secagg.reconstruct_step(Ysum, torch.arange(10, dtype=torch.int32), None, d, w, None)
+    print("recovered sum head:", [round(float(v), 4) for v in w[:4]], "inconsistent shares:", int(bad.sum()))
+    ok = eng.verify_share_trapdoor(eng.to_bytes(C)[:64], eng.to_bytes(W)[:64], 0, 0, int(Y[0, 0, 0]))
+    print("KZG opening of chunk 0 at x=-10 verifies:", ok)
+    return 0 if ok and int(bad.sum()) == 0 else 1
+
+
+def run_experiment(a) -> int:
+    import json
+
+    import torch
+
+    from .eval import experiments as ex
+
+    dev = a.device
+    if dev == "auto":
+        dev = "cuda:0" if torch.cuda.is_available() else "cpu"
+    fn = getattr(ex, a.name)
+    kw = {}
+    if a.name not in ("committee_capture", "unmasked_probability"):
+        kw["device"] = dev
+        if a.blocks:
+            kw["blocks"] = a.blocks
+    rows = fn(**kw)
+    if a.csv:
+        ex.write_csv(rows, a.csv)
+    print(json.dumps(rows, indent=1))
+    return 0
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="biscotti_b200", add_help=True)
     sub = ap.add_subparsers(dest="cmd", required=True)
@@ -151,7 +202,18 @@ def main(argv=None) -> int:
     kg.add_argument("--seed", type=int, default=1)
     kg.add_argument("--tau", type=int, default=2)
     sub.add_parser("vrf-demo")
+    sub.add_parser("kzg-demo")
+    exp = sub.add_parser("experiment")
+    exp.add_argument("name", choices=["cost_breakdown", "fedsys_scale", "committee_scale", "noise_krum", "poison_heatmap",
+                                      "privacy_utility", "churn", "committee_capture", "unmasked_probability"])
+    exp.add_argument("--device", default="auto")
+    exp.add_argument("--blocks", type=int, default=None)
+    exp.add_argument("--csv", default=None)
     a = ap.parse_args(argv)
+    if a.cmd == "kzg-demo":
+        return run_kzg_demo(a)
+    if a.cmd == "experiment":
+        return run_experiment(a)
     if a.cmd == "localtest":
         return run_localtest(a, "biscotti")
     if a.cmd == "fedsys":

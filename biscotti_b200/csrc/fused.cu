@@ -37,9 +37,10 @@ constexpr size_t FG_SMEM = (size_t)FG_STAGES * FG_STAGE_BYTES + 1024 + 256;
 struct GramFusedParams {
   CUtensorMap hi[SYMM_MAX_WORLD];   // rank q's bf16 hi plane [Sr][ldh], box (64 x Sr), SWIZZLE_128B
   CUtensorMap lo[SYMM_MAX_WORLD];
-  PeerTable gpart;                  // rank q's reduction buffer [world*ksplit][ldg][ldg] fp32
+  PeerTable gpart;                  // rank q's reduction buffer [world][ldg][ldg] fp32 (one partial per source rank)
   PeerTable flags;                  // rank q's flag array
-  unsigned int* done_counter;       // local, zero between launches
+  float* lpart;                     // local split-K scratch [ksplit][npairs][128][128] fp32
+  unsigned int* done_counter;       // local: [0] = finished tile pairs, [1 + pair] = finished splits of a pair
   unsigned long long epoch;
   int world, rank, Sr, ntile, ldg;
   int kb_lo, kb_cnt, kb_per, ksplit;
@@ -144,14 +145,14 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
       umma_commit(bar_tmem);
     }
   } else {
-    // epilogue: TMEM -> registers -> every rank's reduction buffer (peer stores over NVLink)
+    // epilogue, stage 1: TMEM -> registers -> this rank's local split-K scratch
     const int q4 = warp & 3;
     if (nkb > 0) {
       mbar_wait(bar_tmem, 0);
       tc_fence_after();
     }
-    const size_t part = ((size_t)P.rank * P.ksplit + split) * P.ldg * P.ldg;
-    const int row = ti * FG_BM + q4 * 32 + lane;
+    float* L = P.lpart + ((size_t)split * gridDim.x + blockIdx.x) * (FG_BM * FG_BM);
+    const int lrow = q4 * 32 + lane;
 #pragma unroll 1
     for (int cc = 0; cc < FG_BM / 32; cc++) {
       uint32_t v[32];
@@ -161,19 +162,11 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
 #pragma unroll
         for (int c = 0; c < 32; c++) v[c] = 0u;
       }
-      const int col0 = tj * FG_BM + cc * 32;
-      for (int dst_rank = 0; dst_rank < P.world; dst_rank++) {
-        float* G = reinterpret_cast<float*>(P.gpart.ptr[dst_rank]) + part;
-        float4* dst = reinterpret_cast<float4*>(G + (size_t)row * P.ldg + col0);
+      float4* dst = reinterpret_cast<float4*>(L + (size_t)lrow * FG_BM + cc * 32);
 #pragma unroll
-        for (int c = 0; c < 8; c++)
-          dst[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
-                               __uint_as_float(v[4 * c + 3]));
-        if (!diag) {
-#pragma unroll
-          for (int c = 0; c < 32; c++) G[(size_t)(col0 + c) * P.ldg + row] = __uint_as_float(v[c]);
-        }
-      }
+      for (int c = 0; c < 8; c++)
+        dst[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
+                             __uint_as_float(v[4 * c + 3]));
     }
   }
   tc_fence_before();
@@ -182,14 +175,38 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(FG_TMEM_COLS) : "memory");
   }
-  // last CTA of this rank publishes "my partials are in everybody's buffer"
+  // epilogue, stage 2: the CTA that finishes a tile pair last reduces that pair's split-K partials in split
+  // order (they are L2-resident) and stores the reduced 128x128 tile, and its mirror, into every rank's
+  // reduction buffer over NVLink: one tile per (source rank, pair) crosses the links instead of one per CTA.
+  __shared__ unsigned int s_last;
   if (threadIdx.x == 0) {
-    __threadfence_system();
-    const unsigned int total = gridDim.x * gridDim.y;
-    const unsigned int old = atomicAdd(P.done_counter, 1u);
-    if (old == total - 1) {
-      *P.done_counter = 0;
-      symm_signal_all(P.flags, P.world, P.rank, SLOT_GRAM, P.epoch);
+    __threadfence();
+    s_last = (atomicAdd(P.done_counter + 1 + blockIdx.x, 1u) == gridDim.y - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    const float* Lp = P.lpart + (size_t)blockIdx.x * (FG_BM * FG_BM);
+    const size_t split_stride = (size_t)gridDim.x * (FG_BM * FG_BM);
+    const size_t part = (size_t)P.rank * P.ldg * P.ldg;
+    for (int e = threadIdx.x; e < FG_BM * FG_BM; e += blockDim.x) {
+      float acc = 0.f;
+      for (unsigned int sp = 0; sp < gridDim.y; sp++) acc += __ldcg(Lp + sp * split_stride + e);
+      const int r = ti * FG_BM + e / FG_BM, c = tj * FG_BM + e % FG_BM;
+      for (int q = 0; q < P.world; q++) {
+        float* G = reinterpret_cast<float*>(P.gpart.ptr[q]) + part;
+        G[(size_t)r * P.ldg + c] = acc;
+        if (!diag) G[(size_t)c * P.ldg + r] = acc;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      P.done_counter[1 + blockIdx.x] = 0;
+      if (atomicAdd(P.done_counter, 1u) == gridDim.x - 1) {
+        P.done_counter[0] = 0;
+        symm_signal_all(P.flags, P.world, P.rank, SLOT_GRAM, P.epoch);
+      }
     }
   }
 }
@@ -394,10 +411,11 @@ int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long 
 }
 
 // Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
-// [world*ksplit][ldg][ldg] fp32 reduction buffer, flags[q]: rank q's flag array.  world*Sr must be a
-// multiple of 128 and Sr a multiple of 8.
+// [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
+// array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed).
+// world*Sr must be a multiple of 128 and Sr a multiple of 8.
 int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world,
-                        int rank, int Sr, int ldh, int ksplit, int ldg, unsigned int* done_counter,
+                        int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter,
                         unsigned long long epoch, void* stream) {
   if (world < 1 || world > SYMM_MAX_WORLD || Sr % 8 != 0 || FG_BM % Sr != 0 || (world * Sr) % FG_BM != 0 ||
       ldh % FG_BK != 0)
@@ -412,6 +430,7 @@ int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* cons
     P.gpart.ptr[q] = gpart[q];
     P.flags.ptr[q] = flags[q];
   }
+  P.lpart = lpart;
   P.done_counter = done_counter;
   P.epoch = epoch;
   P.world = world;

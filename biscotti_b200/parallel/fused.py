@@ -55,7 +55,7 @@ def _declare(L):
     L.bsc_ipc_close_handle.argtypes = [c_p]
     L.bsc_symm_signal.argtypes = [c_p, c_i, c_i, c_i, c_ull, c_p]
     L.bsc_symm_wait.argtypes = [c_p, c_i, c_i, c_ull, c_p]
-    L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_ull, c_p]
+    L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_ull, c_p]
     L.bsc_krum_select_fused.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
     L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_d, c_p, c_p, c_ull, c_p]
 
@@ -101,11 +101,13 @@ class FusedComm(NcclComm):
             return o
 
         self.o_flags = take(8 * 8 * SYMM_MAX_WORLD)
-        self.o_cnt = take(64)
+        self.o_cnt = take(1024)
         self.o_bad = take(64)
         self.o_hi = take(self.Sr * self.ldh * 2)
         self.o_lo = take(self.Sr * self.ldh * 2)
-        self.o_gpart = take(world * self.ksplit * self.ldg * self.ldg * 4)
+        self.o_gpart = take(world * self.ldg * self.ldg * 4)
+        self.npairs = self.ntile * (self.ntile + 1) // 2
+        self.o_lpart = take(self.ksplit * self.npairs * 128 * 128 * 4)
         self.o_ypart = take(self.nchunk * self.S * 8)
         self.o_w64 = take(d * 8)
         self.o_w32 = take(d * 4)
@@ -135,7 +137,7 @@ class FusedComm(NcclComm):
         self.w64 = tensor_from_ptr(self.base + self.o_w64, (d,), torch.float64, dev)
         self.w32 = tensor_from_ptr(self.base + self.o_w32, (d,), torch.float32, dev)
         self.bad = tensor_from_ptr(self.base + self.o_bad, (2,), torch.int32, dev)
-        self.gpart = tensor_from_ptr(self.base + self.o_gpart, (world * self.ksplit, self.ldg, self.ldg), torch.float32, dev)
+        self.gpart = tensor_from_ptr(self.base + self.o_gpart, (world, self.ldg, self.ldg), torch.float32, dev)
         self._tables = {name: self._table(o) for name, o in (("flags", self.o_flags), ("hi", self.o_hi), ("lo", self.o_lo),
                                                              ("gpart", self.o_gpart), ("ypart", self.o_ypart),
                                                              ("w64", self.o_w64), ("w32", self.o_w32))}
@@ -169,7 +171,8 @@ class FusedComm(NcclComm):
         self.signal(SLOT_PLANES, epoch)
         _check(self.L.bsc_krum_gram_fused(self._tables["hi"], self._tables["lo"], self._tables["gpart"],
                                           self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
-                                          self.ldg, c_p(self.base + self.o_cnt), epoch, self._stream()), "krum_gram_fused")
+                                          self.ldg, c_p(self.base + self.o_lpart), c_p(self.base + self.o_cnt), epoch,
+                                          self._stream()), "krum_gram_fused")
         rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)
@@ -177,11 +180,11 @@ class FusedComm(NcclComm):
             # wait until every rank's partials have landed here, then the multi-CTA tail (norms from the
             # reduced Gram's diagonal, participants addressed through their slots)
             self.wait(SLOT_GRAM, epoch)
-            _check(self.L.bsc_krum_select_mc(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg, None,
+            _check(self.L.bsc_krum_select_mc(c_p(self.base + self.o_gpart), self.world, self.ldg, None,
                                              c_p(rows.data_ptr()), n, clip, c_p(scores.data_ptr()),
                                              c_p(accept.data_ptr()), None, self._stream()), "krum_select_mc")
         else:
-            _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world * self.ksplit, self.ldg,
+            _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world, self.ldg,
                                                 c_p(rows.data_ptr()), n, clip, c_p(self.base + self.o_flags), self.world,
                                                 epoch, c_p(scores.data_ptr()), c_p(accept.data_ptr()), self._stream()),
                    "krum_select_fused")
@@ -202,7 +205,7 @@ class FusedComm(NcclComm):
         self.bad.zero_()
         _check(self.L.bsc_secagg_fused(self._tables["ypart"], self._tables["w64"], self._tables["w32"], self._tables["flags"],
                                        self.world, self.rank, self.S, self.d, c0, nc, xs_a, av, float(10 ** precision),
-                                       c_p(self.base + self.o_cnt + 16), c_p(self.base + self.o_bad), epoch, self._stream()),
+                                       c_p(self.base + self.o_cnt + 512), c_p(self.base + self.o_bad), epoch, self._stream()),
                "secagg_fused")
         self.wait(SLOT_WEIGHTS, epoch)
         return self.bad

@@ -175,6 +175,12 @@ int bsc_ed25519_scalarmult_r25(const unsigned char* scalars, const unsigned char
 
 int bsc_ed25519_scalarmult_quad(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out, void* stream);
 
+// same, but leaves the results projective: xyz_out[i] = X, Y, Z as 3 x 10 radix-2^25.5 limbs
+int bsc_ed25519_scalarmult_quad_xyz(const unsigned char* scalars, const unsigned char* hxy, int N, int* xyz_out, void* stream);
+
+// host: compress N projective points with a single field inversion (prefix products)
+void bsc_ed25519_compress_batch(const int* xyz, int N, unsigned char* out);
+
 void bsc_ed25519_scalarmult_r25_host(const unsigned char* scalars, const unsigned char* hxy, int N, unsigned char* out);
 
 void bsc_ed25519_scalarmult_batch_host(const void* scalars_u256, const void* bases, int nbase, int N, unsigned char* out);
@@ -333,9 +339,10 @@ int bsc_symm_signal(void* const* flag_ptrs, int world, int rank, int slot, unsig
 int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long epoch, void* stream);
 
 // Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
-// [world*ksplit][ldg][ldg] fp32 reduction buffer, flags[q]: rank q's flag array.  world*Sr must be a
-// multiple of 128 and Sr a multiple of 8.
-int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world, int rank, int Sr, int ldh, int ksplit, int ldg, unsigned int* done_counter, unsigned long long epoch, void* stream);
+// [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
+// array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed).
+// world*Sr must be a multiple of 128 and Sr a multiple of 8.
+int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world, int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter, unsigned long long epoch, void* stream);
 
 int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const int* rows, int n, int clip, const void* my_flags, int world, unsigned long long epoch, float* scores, unsigned char* accept, void* stream);
 
