@@ -40,7 +40,8 @@ struct GramFusedParams {
   PeerTable gpart;                  // rank q's reduction buffer [world][ldg][ldg] fp32 (one partial per source rank)
   PeerTable flags;                  // rank q's flag array
   float* lpart;                     // local split-K scratch [ksplit][npairs][128][128] fp32
-  unsigned int* done_counter;       // local: [0] = finished tile pairs, [1 + pair] = finished splits of a pair
+  unsigned int* done_counter;       // local, monotonic: [0] = CTAs finished, [1 + pair] = splits of a pair written
+  unsigned int seq;                 // 1-based launch sequence number of this kernel on this rank
   unsigned long long epoch;
   int world, rank, Sr, ntile, ldg;
   int kb_lo, kb_cnt, kb_per, ksplit;
@@ -175,21 +176,35 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(FG_TMEM_COLS) : "memory");
   }
-  // epilogue, stage 2: the CTA that finishes a tile pair last reduces that pair's split-K partials in split
-  // order (they are L2-resident) and stores the reduced 128x128 tile, and its mirror, into every rank's
-  // reduction buffer over NVLink: one tile per (source rank, pair) crosses the links instead of one per CTA.
-  __shared__ unsigned int s_last;
+  // epilogue, stage 2: all CTAs of a tile pair meet at a counter barrier (every CTA of this grid is resident:
+  // grid <= #SMs at one CTA per SM), then each reduces its 1/ksplit slice of the pair's tile over the split-K
+  // partials in split order (L2-resident) and stores the slice, and its mirror, into every rank's reduction
+  // buffer over NVLink.  One reduced tile per (source rank, pair) crosses the links, and the reduction
+  // itself is spread over all of the pair's CTAs.  Counters only grow (target = launch sequence * count).
   if (threadIdx.x == 0) {
     __threadfence();
-    s_last = (atomicAdd(P.done_counter + 1 + blockIdx.x, 1u) == gridDim.y - 1) ? 1u : 0u;
+    atomicAdd(P.done_counter + 1 + blockIdx.x, 1u);
+    const unsigned int target = P.seq * gridDim.y;
+    unsigned long long spins = 0;
+    for (;;) {
+      unsigned int v;
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(P.done_counter + 1 + blockIdx.x) : "memory");
+      if (v >= target) break;
+      __nanosleep(32);
+      if (++spins > (1ull << 24)) {
+        printf("[biscotti_b200] krum_gram_fused: split barrier timed out (pair %d split %d)\n", blockIdx.x, blockIdx.y);
+        __trap();
+      }
+    }
   }
   __syncthreads();
-  if (s_last) {
-    __threadfence();
+  {
     const float* Lp = P.lpart + (size_t)blockIdx.x * (FG_BM * FG_BM);
     const size_t split_stride = (size_t)gridDim.x * (FG_BM * FG_BM);
     const size_t part = (size_t)P.rank * P.ldg * P.ldg;
-    for (int e = threadIdx.x; e < FG_BM * FG_BM; e += blockDim.x) {
+    const int chunk = (FG_BM * FG_BM + gridDim.y - 1) / gridDim.y;
+    const int e0 = split * chunk, e1 = min(FG_BM * FG_BM, e0 + chunk);
+    for (int e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
       float acc = 0.f;
       for (unsigned int sp = 0; sp < gridDim.y; sp++) acc += __ldcg(Lp + sp * split_stride + e);
       const int r = ti * FG_BM + e / FG_BM, c = tj * FG_BM + e % FG_BM;
@@ -199,15 +214,12 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
         if (!diag) G[(size_t)c * P.ldg + r] = acc;
       }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      P.done_counter[1 + blockIdx.x] = 0;
-      if (atomicAdd(P.done_counter, 1u) == gridDim.x - 1) {
-        P.done_counter[0] = 0;
-        symm_signal_all(P.flags, P.world, P.rank, SLOT_GRAM, P.epoch);
-      }
-    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned int total = gridDim.x * gridDim.y;
+    if (atomicAdd(P.done_counter, 1u) + 1u == P.seq * total) symm_signal_all(P.flags, P.world, P.rank, SLOT_GRAM, P.epoch);
   }
 }
 
@@ -412,11 +424,12 @@ int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long 
 
 // Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
 // [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
-// array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed).
+// array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed once;
+// the counters only grow), seq: 1-based count of launches of this kernel on this rank.
 // world*Sr must be a multiple of 128 and Sr a multiple of 8.
 int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world,
                         int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter,
-                        unsigned long long epoch, void* stream) {
+                        unsigned int seq, unsigned long long epoch, void* stream) {
   if (world < 1 || world > SYMM_MAX_WORLD || Sr % 8 != 0 || FG_BM % Sr != 0 || (world * Sr) % FG_BM != 0 ||
       ldh % FG_BK != 0)
     return -1;
@@ -432,6 +445,7 @@ int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* cons
   }
   P.lpart = lpart;
   P.done_counter = done_counter;
+  P.seq = seq;
   P.epoch = epoch;
   P.world = world;
   P.rank = rank;
@@ -451,6 +465,7 @@ int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* cons
     configured = true;
   }
   dim3 grid(P.ntile * (P.ntile + 1) / 2, ksplit);
+  if (grid.x * grid.y > 148) return -5;   // the in-kernel split barrier needs every CTA resident (1 CTA per SM)
   krum_gram_fused_kernel<<<grid, FG_THREADS, FG_SMEM, (cudaStream_t)stream>>>(P);
   return finish_launch("krum_gram_fused");
 }

@@ -8,11 +8,12 @@
 // Every peer starts from the same global weights, so the forward convolution is one launch over all
 // P*B images; the backward pass is per-peer (each peer needs its own weight gradient).  Five kernels:
 //   cnn1_conv_fwd     activations act[p][b][oc][oy][ox] = relu(conv)
-//   cnn1_fc_fwd_loss  logits, softmax, dlogits, loss, fc.bias gradient (one CTA per peer)
+//   cnn1_fc_fwd       logits (one CTA per image)
+//   cnn1_loss         softmax, dlogits, loss, fc.bias gradient (one warp per peer)
 //   cnn1_fc_bwd       fc.weight gradient (the bulk of the update: C*J floats per peer), d(act) masked by
 //                     ReLU written over act, partial squared norms
 //   cnn1_conv_wgrad   conv.weight / conv.bias gradients (one CTA per (peer, out-channel)), partial norms
-//   cnn1_clip_scale   fixed-order sum of the partial norms, U = -coef * grad
+//   cnn1_coef/scale   fixed-shape reduction of the partial norms -> clip coefficient, U = -coef * grad
 // Partial norms are written to per-CTA slots and summed in index order: the clip coefficient (and with it
 // the ledger) is bit-reproducible.
 #include "common.cuh"
@@ -53,46 +54,46 @@ __global__ void __launch_bounds__(256) cnn1_conv_fwd_kernel(const float* __restr
   }
 }
 
-// one CTA per peer: logits[b][c], softmax, dl = (softmax - onehot)/B, loss, fc.bias gradient
-__global__ void __launch_bounds__(256) cnn1_fc_fwd_loss_kernel(const float* __restrict__ w, const float* __restrict__ act,
-                                                               const int* __restrict__ y, float* __restrict__ dl,
-                                                               float* __restrict__ loss, float* __restrict__ U, int ldu,
-                                                               Cnn1Shape s) {
-  __shared__ float sl[32 * 16];
-  __shared__ float red[40];
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-  const float* a = act + (size_t)p * s.B * s.J;
-  for (int pair = warp; pair < s.B * s.C; pair += nwarp) {
-    const int b = pair / s.C, c = pair % s.C;
+// grid (B, P): the C logits of one image (one warp per class, strided), written to logits[p][b][c]
+__global__ void __launch_bounds__(256) cnn1_fc_fwd_kernel(const float* __restrict__ w, const float* __restrict__ act,
+                                                          float* __restrict__ logits, Cnn1Shape s) {
+  const int b = blockIdx.x, p = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const float* ar = act + ((size_t)p * s.B + b) * s.J;
+  for (int c = warp; c < s.C; c += nwarp) {
     const float* wr = w + s.off_fw + (size_t)c * s.J;
-    const float* ar = a + (size_t)b * s.J;
     float acc = 0.f;
     for (int j = lane; j < s.J; j += 32) acc = fmaf(ar[j], wr[j], acc);
     acc = warp_sum(acc);
-    if (lane == 0) sl[b * s.C + c] = acc + w[s.off_fb + c];
+    if (lane == 0) logits[((size_t)p * s.B + b) * s.C + c] = acc + w[s.off_fb + c];
   }
-  __syncthreads();
+}
+// one warp per peer: softmax, dl = (softmax - onehot)/B (written over logits), loss, fc.bias gradient
+__global__ void cnn1_loss_kernel(float* __restrict__ dl, const int* __restrict__ y, float* __restrict__ loss,
+                                 float* __restrict__ U, int ldu, int P, Cnn1Shape s) {
+  const int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (p >= P) return;
+  float* sl = dl + (size_t)p * s.B * s.C;
   float myloss = 0.f;
-  if (tid < s.B) {
+  if (lane < s.B) {
     float m = -INFINITY;
-    for (int c = 0; c < s.C; c++) m = fmaxf(m, sl[tid * s.C + c]);
+    for (int c = 0; c < s.C; c++) m = fmaxf(m, sl[lane * s.C + c]);
     float sum = 0.f;
-    for (int c = 0; c < s.C; c++) sum += expf(sl[tid * s.C + c] - m);
+    for (int c = 0; c < s.C; c++) sum += expf(sl[lane * s.C + c] - m);
     const float lse = m + logf(sum);
-    const int lab = y[p * s.B + tid];
-    myloss = (lse - sl[tid * s.C + lab]) / (float)s.B;
+    const int lab = y[p * s.B + lane];
+    myloss = (lse - sl[lane * s.C + lab]) / (float)s.B;
     for (int c = 0; c < s.C; c++) {
-      const float pr = expf(sl[tid * s.C + c] - lse);
-      sl[tid * s.C + c] = (pr - (c == lab ? 1.f : 0.f)) / (float)s.B;
+      const float pr = expf(sl[lane * s.C + c] - lse);
+      sl[lane * s.C + c] = (pr - (c == lab ? 1.f : 0.f)) / (float)s.B;
     }
   }
-  const float tl = block_sum(myloss, red);
-  if (tid == 0 && loss) loss[p] = tl;
-  for (int i = tid; i < s.B * s.C; i += blockDim.x) dl[(size_t)p * s.B * s.C + i] = sl[i];
-  if (tid < s.C) {
+  myloss = warp_sum(myloss);
+  if (lane == 0 && loss) loss[p] = myloss;
+  __syncwarp();
+  if (lane < s.C) {
     float g = 0.f;
-    for (int b = 0; b < s.B; b++) g += sl[b * s.C + tid];
-    U[(size_t)p * ldu + s.off_fb + tid] = g;   // unscaled gradient; cnn1_clip_scale finishes it
+    for (int b = 0; b < s.B; b++) g += sl[b * s.C + lane];
+    U[(size_t)p * ldu + s.off_fb + lane] = g;   // unscaled gradient; cnn1_scale finishes it
   }
 }
 
@@ -175,26 +176,32 @@ __global__ void __launch_bounds__(256) cnn1_conv_wgrad_kernel(const float* __res
   }
 }
 
-// one CTA per peer: total norm from the partial slots (+ fc.bias), then U = -coef * grad
-__global__ void __launch_bounds__(256) cnn1_clip_scale_kernel(float* __restrict__ U, int ldu, const float* __restrict__ partial,
-                                                              int nslots, float clip, Cnn1Shape s) {
-  __shared__ float coef_s;
+// one CTA per peer: clip coefficient from the partial squared norms (+ fc.bias), fixed-shape tree reduction
+// (deterministic: the same slots are combined in the same order on every run and every rank)
+__global__ void __launch_bounds__(256) cnn1_coef_kernel(const float* __restrict__ U, int ldu, const float* __restrict__ partial,
+                                                        int nslots, float clip, float* __restrict__ coef, Cnn1Shape s) {
+  __shared__ float red[40];
   const int p = blockIdx.x;
-  if (threadIdx.x == 0) {
-    float tot = 0.f;
-    for (int i = 0; i < nslots; i++) tot += partial[(size_t)p * nslots + i];   // fixed order
-    for (int c = 0; c < s.C; c++) {
-      const float g = U[(size_t)p * ldu + s.off_fb + c];
-      tot = fmaf(g, g, tot);
-    }
-    float coef = clip / (sqrtf(tot) + 1e-6f);
-    coef_s = coef > 1.f ? 1.f : coef;
+  float t = 0.f;
+  for (int i = threadIdx.x; i < nslots; i += blockDim.x) t += partial[(size_t)p * nslots + i];
+  if (threadIdx.x < s.C) {
+    const float g = U[(size_t)p * ldu + s.off_fb + threadIdx.x];
+    t = fmaf(g, g, t);
   }
-  __syncthreads();
-  const float m = -coef_s;
+  const float tot = block_sum(t, red);
+  if (threadIdx.x == 0) {
+    const float c = clip / (sqrtf(tot) + 1e-6f);
+    coef[p] = c > 1.f ? 1.f : c;
+  }
+}
+// grid (ceil(ldu/4096), P): U = -coef * grad, padding zeroed
+__global__ void __launch_bounds__(256) cnn1_scale_kernel(float* __restrict__ U, int ldu, const float* __restrict__ coef,
+                                                         Cnn1Shape s) {
+  const int p = blockIdx.y;
+  const float m = -coef[p];
   float* row = U + (size_t)p * ldu;
-  for (int k = threadIdx.x; k < s.d; k += blockDim.x) row[k] *= m;
-  for (int k = s.d + threadIdx.x; k < ldu; k += blockDim.x) row[k] = 0.f;
+  const int k0 = blockIdx.x * 4096;
+  for (int k = k0 + threadIdx.x; k < min(ldu, k0 + 4096); k += blockDim.x) row[k] = k < s.d ? row[k] * m : 0.f;
 }
 
 }  // namespace bsc
@@ -203,12 +210,12 @@ using namespace bsc;
 
 extern "C" {
 
-// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC
+// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P]
 long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, int H, int W, int C) {
   const int OH = H + 2 * pad - K + 1, OW = W + 2 * pad - K + 1;
   const long long J = (long long)OC * OH * OW;
   const long long nslots = (J + 255) / 256 + OC;
-  return (long long)P * B * J + (long long)P * B * C + (long long)P * nslots;
+  return (long long)P * B * J + (long long)P * B * C + (long long)P * nslots + P;
 }
 
 // One-conv-layer CNN local step for P peers.  w: flat global weights; X: [P][B][IC][H][W]; y: [P][B];
@@ -234,15 +241,18 @@ int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, 
   float* act = scratch;
   float* dl = act + (size_t)P * B * s.J;
   float* partial = dl + (size_t)P * B * C;
+  float* coef = partial + (size_t)P * nslots;
   const long long total = (long long)P * B * s.J;
   const int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
   const size_t smem = (size_t)(OC * IC * K * K + OC) * sizeof(float);
   cnn1_conv_fwd_kernel<<<grid, 256, smem, st>>>(w, X, act, s, P * B);
-  cnn1_fc_fwd_loss_kernel<<<P, 256, 0, st>>>(w, act, y, dl, loss, U, ldu, s);
+  cnn1_fc_fwd_kernel<<<dim3(B, P), 256, 0, st>>>(w, act, dl, s);
+  cnn1_loss_kernel<<<(P + 3) / 4, 128, 0, st>>>(dl, y, loss, U, ldu, P, s);
   cnn1_fc_bwd_kernel<<<dim3(nfc, P), 256, 0, st>>>(w, act, dl, U, ldu, partial, nslots, s);
   cnn1_conv_wgrad_kernel<<<dim3(OC, P), 256, 0, st>>>(X, act, U, ldu, partial, nslots, nfc, s);
-  cnn1_clip_scale_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, s);
-  return finish_launch("cnn1_local_step", 5);
+  cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
+  cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s);
+  return finish_launch("cnn1_local_step", 7);
 }
 
 }  // extern "C"

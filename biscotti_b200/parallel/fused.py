@@ -55,7 +55,7 @@ def _declare(L):
     L.bsc_ipc_close_handle.argtypes = [c_p]
     L.bsc_symm_signal.argtypes = [c_p, c_i, c_i, c_i, c_ull, c_p]
     L.bsc_symm_wait.argtypes = [c_p, c_i, c_i, c_ull, c_p]
-    L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_ull, c_p]
+    L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, ctypes.c_uint, c_ull, c_p]
     L.bsc_krum_select_fused.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
     L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_d, c_p, c_p, c_ull, c_p]
 
@@ -168,11 +168,12 @@ class FusedComm(NcclComm):
         """Planes of this block must already be in self.hi / self.lo.  Returns accept (uint8, device)."""
         n = len(krum_set)
         dev = self.device
+        self._gram_seq = getattr(self, "_gram_seq", 0) + 1
         self.signal(SLOT_PLANES, epoch)
         _check(self.L.bsc_krum_gram_fused(self._tables["hi"], self._tables["lo"], self._tables["gpart"],
                                           self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
-                                          self.ldg, c_p(self.base + self.o_lpart), c_p(self.base + self.o_cnt), epoch,
-                                          self._stream()), "krum_gram_fused")
+                                          self.ldg, c_p(self.base + self.o_lpart), c_p(self.base + self.o_cnt), self._gram_seq,
+                                          epoch, self._stream()), "krum_gram_fused")
         rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)

@@ -340,9 +340,10 @@ int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long 
 
 // Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
 // [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
-// array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed).
+// array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed once;
+// the counters only grow), seq: 1-based count of launches of this kernel on this rank.
 // world*Sr must be a multiple of 128 and Sr a multiple of 8.
-int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world, int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter, unsigned long long epoch, void* stream);
+int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world, int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter, unsigned int seq, unsigned long long epoch, void* stream);
 
 int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const int* rows, int n, int clip, const void* my_flags, int world, unsigned long long epoch, float* scores, unsigned char* accept, void* stream);
 
