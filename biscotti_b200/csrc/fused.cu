@@ -71,6 +71,9 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
   }
   const bool diag = (ti == tj);
   const int split = blockIdx.y;
+  // The planes of this block were written by the previous kernel on this stream, so they are complete when
+  // this kernel starts: publish them to every rank before anything else (no separate signal launch).
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) symm_signal_all(P.flags, P.world, P.rank, SLOT_PLANES, P.epoch);
   const int kb0 = P.kb_lo + split * P.kb_per;
   int nkb = min(P.kb_lo + P.kb_cnt, kb0 + P.kb_per) - kb0;
   if (nkb < 0) nkb = 0;
@@ -317,6 +320,8 @@ struct SecaggFusedParams {
 };
 
 __global__ void __launch_bounds__(128) secagg_fused_kernel(const __grid_constant__ SecaggFusedParams P) {
+  // this rank's partial share sums were produced by the previous kernel on this stream: publish, then wait
+  if (blockIdx.x == 0 && threadIdx.x == 0) symm_signal_all(P.flags, P.world, P.rank, SLOT_SHARES, P.epoch);
   if (threadIdx.x == 0)
     symm_wait_all(reinterpret_cast<const unsigned long long*>(P.flags.ptr[P.rank]), P.world, SLOT_SHARES, P.epoch);
   __syncthreads();

@@ -11,6 +11,7 @@
 // peer and the whole population of a GPU is one launch.
 #include "common.cuh"
 #include "secagg_math.cuh"
+#include "symm.cuh"
 #include <cuda_bf16.h>
 #include <mutex>
 
@@ -350,9 +351,15 @@ __global__ void __launch_bounds__(256) krum_select_kernel(const float* __restric
 __global__ void __launch_bounds__(256) krum_scores_kernel(const float* __restrict__ Gpart, int nsplit, int ldg,
                                                           const float* __restrict__ norms, const int* __restrict__ rows,
                                                           int n, int clip, float* __restrict__ scores,
-                                                          float* __restrict__ Dout, int np2) {
+                                                          float* __restrict__ Dout, int np2,
+                                                          const unsigned long long* __restrict__ wait_flags, int world,
+                                                          unsigned long long epoch) {
   extern __shared__ float srow[];  // [nwarp][np2] + [n] norms
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  if (wait_flags) {   // fused multi-GPU path: every rank's partial Gram must have landed in Gpart first
+    if (tid == 0) symm_wait_all(wait_flags, world, SLOT_GRAM, epoch);
+    __syncthreads();
+  }
   float* myrow = srow + (size_t)warp * np2;
   float* snorm = srow + (size_t)nwarp * np2;
   for (int i = tid; i < n; i += blockDim.x) {
@@ -630,9 +637,25 @@ int bsc_krum_select_mc(const float* Gpart, int nsplit, int ldg, const float* nor
   while (np2 < n) np2 <<= 1;
   const size_t smem = ((size_t)8 * np2 + n) * sizeof(float);
   krum_scores_kernel<<<(n + 7) / 8, 256, smem, (cudaStream_t)stream>>>(Gpart, nsplit, ldg, norms, rows, n, clip, scores,
-                                                                        Dout, np2);
+                                                                        Dout, np2, nullptr, 0, 0ull);
   krum_accept_kernel<<<1, 256, (size_t)n * sizeof(float), (cudaStream_t)stream>>>(scores, n, clip, accept);
   return finish_launch("krum_select_mc", 2);
+}
+// Same tail for the fused multi-GPU path: the scores kernel first waits (bounded) until every rank has
+// published SLOT_GRAM for `epoch` in my_flags, i.e. all partial Grams have landed in Gpart.
+int bsc_krum_select_mc_wait(const float* Gpart, int nsplit, int ldg, const int* rows, int n, int clip,
+                            const void* my_flags, int world, unsigned long long epoch, float* scores,
+                            unsigned char* accept, void* stream) {
+  if (n > 1024 || n < 3) return -1;
+  int np2 = 32;
+  while (np2 < n) np2 <<= 1;
+  const size_t smem = ((size_t)8 * np2 + n) * sizeof(float);
+  krum_scores_kernel<<<(n + 7) / 8, 256, smem, (cudaStream_t)stream>>>(Gpart, nsplit, ldg, nullptr, rows, n, clip,
+                                                                        scores, nullptr, np2,
+                                                                        (const unsigned long long*)my_flags, world,
+                                                                        epoch);
+  krum_accept_kernel<<<1, 256, (size_t)n * sizeof(float), (cudaStream_t)stream>>>(scores, n, clip, accept);
+  return finish_launch("krum_select_mc_wait", 2);
 }
 
 int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F,

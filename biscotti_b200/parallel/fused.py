@@ -57,6 +57,7 @@ def _declare(L):
     L.bsc_symm_wait.argtypes = [c_p, c_i, c_i, c_ull, c_p]
     L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, ctypes.c_uint, c_ull, c_p]
     L.bsc_krum_select_fused.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
+    L.bsc_krum_select_mc_wait.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
     L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_d, c_p, c_p, c_ull, c_p]
 
 
@@ -168,8 +169,7 @@ class FusedComm(NcclComm):
         """Planes of this block must already be in self.hi / self.lo.  Returns accept (uint8, device)."""
         n = len(krum_set)
         dev = self.device
-        self._gram_seq = getattr(self, "_gram_seq", 0) + 1
-        self.signal(SLOT_PLANES, epoch)
+        self._gram_seq = getattr(self, "_gram_seq", 0) + 1   # the Gram kernel publishes SLOT_PLANES itself
         _check(self.L.bsc_krum_gram_fused(self._tables["hi"], self._tables["lo"], self._tables["gpart"],
                                           self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
                                           self.ldg, c_p(self.base + self.o_lpart), c_p(self.base + self.o_cnt), self._gram_seq,
@@ -177,13 +177,13 @@ class FusedComm(NcclComm):
         rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)
-        if hasattr(self.L, "bsc_krum_select_mc"):
-            # wait until every rank's partials have landed here, then the multi-CTA tail (norms from the
-            # reduced Gram's diagonal, participants addressed through their slots)
-            self.wait(SLOT_GRAM, epoch)
-            _check(self.L.bsc_krum_select_mc(c_p(self.base + self.o_gpart), self.world, self.ldg, None,
-                                             c_p(rows.data_ptr()), n, clip, c_p(scores.data_ptr()),
-                                             c_p(accept.data_ptr()), None, self._stream()), "krum_select_mc")
+        if hasattr(self.L, "bsc_krum_select_mc_wait"):
+            # multi-CTA tail; its first kernel waits until every rank's partials have landed here (norms from
+            # the reduced Gram's diagonal, participants addressed through their slots)
+            _check(self.L.bsc_krum_select_mc_wait(c_p(self.base + self.o_gpart), self.world, self.ldg,
+                                                  c_p(rows.data_ptr()), n, clip, c_p(self.base + self.o_flags),
+                                                  self.world, epoch, c_p(scores.data_ptr()), c_p(accept.data_ptr()),
+                                                  self._stream()), "krum_select_mc_wait")
         else:
             _check(self.L.bsc_krum_select_fused(c_p(self.base + self.o_gpart), self.world, self.ldg,
                                                 c_p(rows.data_ptr()), n, clip, c_p(self.base + self.o_flags), self.world,
@@ -199,17 +199,19 @@ class FusedComm(NcclComm):
 
     def secagg_fused(self, xs, avail, precision: int, epoch: int):
         """self.ypart must hold this rank's partial share sums.  Updates self.w64 / self.w32 on every rank."""
-        self.signal(SLOT_SHARES, epoch)
-        c0, nc = self.chunk_range()
+        c0, nc = self.chunk_range()   # the kernel publishes SLOT_SHARES itself
         xs_a = (c_i * 10)(*xs)
         av = (ctypes.c_ubyte * 64)(*(list(avail) + [0] * (64 - len(avail))))
-        self.bad.zero_()
         _check(self.L.bsc_secagg_fused(self._tables["ypart"], self._tables["w64"], self._tables["w32"], self._tables["flags"],
                                        self.world, self.rank, self.S, self.d, c0, nc, xs_a, av, float(10 ** precision),
                                        c_p(self.base + self.o_cnt + 512), c_p(self.base + self.o_bad), epoch, self._stream()),
                "secagg_fused")
         self.wait(SLOT_WEIGHTS, epoch)
-        return self.bad
+        # `bad` accumulates over the run (no zeroing launch per block); report this block's increment lazily
+        prev = getattr(self, "_bad_prev", None)
+        cur = self.bad.clone()
+        self._bad_prev = cur
+        return cur if prev is None else cur - prev
 
     def all_gather_rows_u8(self, local: torch.Tensor) -> torch.Tensor:
         """[per, k] uint8 blocks from every rank -> [world*per, k] (commitment bytes for the block)."""

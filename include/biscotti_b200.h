@@ -59,6 +59,10 @@ int bsc_krum_scores_static(const float* A, const float* norms, int n, int d, int
 // (identity mapping / norms from the Gram diagonal).  Bit-identical to bsc_krum_select.
 int bsc_krum_select_mc(const float* Gpart, int nsplit, int ldg, const float* norms, const int* rows, int n, int clip, float* scores, unsigned char* accept, float* Dout, void* stream);
 
+// Same tail for the fused multi-GPU path: the scores kernel first waits (bounded) until every rank has
+// published SLOT_GRAM for `epoch` in my_flags, i.e. all partial Grams have landed in Gpart.
+int bsc_krum_select_mc_wait(const float* Gpart, int nsplit, int ldg, const int* rows, int n, int clip, const void* my_flags, int world, unsigned long long epoch, float* scores, unsigned char* accept, void* stream);
+
 int bsc_eval_softmax(const float* Wc, const float* base, const float* X, const int* y, int* wrong, int M, int N, int F, int C, int ldw, void* stream);
 
 int bsc_eval_logistic(const float* Wc, const float* base, const float* X, const float* y, int* wrong, int M, int N, int F, int ldw, void* stream);
@@ -353,7 +357,7 @@ int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, voi
 /* --------------------------------------------------------------------------------------------
  * kernels_cnn.cu - 
  * -------------------------------------------------------------------------------------------- */
-// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC
+// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P]
 long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, int H, int W, int C);
 
 // One-conv-layer CNN local step for P peers.  w: flat global weights; X: [P][B][IC][H][W]; y: [P][B];
