@@ -155,9 +155,11 @@ __device__ __forceinline__ F25 quad_pick(const F25& r, int src) {
   return o;
 }
 __device__ __forceinline__ F25 f25_sel4(int j, const F25& a, const F25& b, const F25& c, const F25& d) {
+  // branch-free: lanes of one quad take different operands, and a branchy select diverges inside every warp
+  const int32_t m0 = -(int32_t)(j == 0), m1 = -(int32_t)(j == 1), m2 = -(int32_t)(j == 2), m3 = -(int32_t)(j == 3);
   F25 o;
 #pragma unroll
-  for (int i = 0; i < 10; i++) o.v[i] = j == 0 ? a.v[i] : (j == 1 ? b.v[i] : (j == 2 ? c.v[i] : d.v[i]));
+  for (int i = 0; i < 10; i++) o.v[i] = (a.v[i] & m0) | (b.v[i] & m1) | (c.v[i] & m2) | (d.v[i] & m3);
   return o;
 }
 
@@ -205,7 +207,6 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
     for (int step = 0; step < nsteps; step++) {
       F25 a, b;
       const bool is_add = (step == 4);
-      bool neg = false;
       if (!is_add) {
         // lane 2 forms 2*Z*Z directly (operand Z+Z) so that every input of the second round stays inside
         // the radix-2^25.5 multiplication bounds, exactly like the reference formulas' sq2
@@ -213,11 +214,21 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
         a = f25_sel4(j, X, Y, Z, xy);
         b = f25_sel4(j, X, Y, f25_add(Z, Z), xy);
       } else {
-        neg = dgt < 0;
-        const EdCached& q = table[dgt == 0 ? 8 : (neg ? -dgt : dgt) - 1];
+        // Subtracting a table entry = adding its negation (swap Y+X / Y-X, negate 2dT); the choice is made
+        // with masks, not branches: digits differ between the quads of a warp.
+        const int32_t nm = -(int32_t)(dgt < 0);
+        const int mag = (dgt ^ nm) - nm;
+        const EdCached& q = table[mag == 0 ? 8 : mag - 1];
+        F25 qp, qm, qt;
+#pragma unroll
+        for (int i = 0; i < 10; i++) {
+          qp.v[i] = (q.YpX.v[i] & ~nm) | (q.YmX.v[i] & nm);
+          qm.v[i] = (q.YmX.v[i] & ~nm) | (q.YpX.v[i] & nm);
+          qt.v[i] = (q.T2d.v[i] ^ nm) - nm;
+        }
         const F25 ypx = f25_add(Y, X), ymx = f25_sub(Y, X);
-        a = f25_sel4(j, ypx, ymx, q.T2d, Z);
-        b = f25_sel4(j, neg ? q.YmX : q.YpX, neg ? q.YpX : q.YmX, T, q.Z);
+        a = f25_sel4(j, ypx, ymx, qt, Z);
+        b = f25_sel4(j, qp, qm, T, q.Z);
       }
       const F25 r = f25_mul_inl<false>(a, b);   // two call sites only: inlined, no call / stack traffic
       const F25 r0 = quad_pick(r, 0), r1 = quad_pick(r, 1), r2 = quad_pick(r, 2), r3 = quad_pick(r, 3);
@@ -233,8 +244,8 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
         const F25 D = f25_add(r3, r3);
         cX = f25_sub(r0, r1);
         cY = f25_add(r0, r1);
-        cZ = neg ? f25_sub(D, r2) : f25_add(D, r2);
-        cT = neg ? f25_add(D, r2) : f25_sub(D, r2);
+        cZ = f25_add(D, r2);
+        cT = f25_sub(D, r2);
       }
       // second round: X3 = cX*cT, Y3 = cY*cZ, Z3 = cZ*cT, T3 = cX*cY
       const F25 a2 = f25_sel4(j, cX, cY, cZ, cX);
