@@ -78,6 +78,31 @@ HD int64_t shamir_eval(const int64_t a[POLY_SIZE], int s) {
   return (int64_t)acc;
 }
 
+// num / den for a small non-zero den, assuming the division is exact (the caller verifies q*den == num).
+// Device code has no 128-bit divide instruction — a software __int128 division is hundreds of
+// instructions, and share recovery does 45 of them per chunk — so the quotient is formed as
+// (num >> tz) * inverse(odd part of den) mod 2^128: the 64-bit inverse comes from five Newton steps and one
+// more step widens it to 128 bits.
+HD __int128 exact_div_small(__int128 num, int64_t den) {
+  const bool neg = den < 0;
+  uint64_t d = neg ? (uint64_t)0 - (uint64_t)den : (uint64_t)den;
+  if (d == 0) return 0;   // duplicate share indices: the caller's q*den == num check reports it
+  int tz = 0;
+  while ((d & 1) == 0) {
+    d >>= 1;
+    tz++;
+  }
+  uint64_t inv = d;                       // d*d = 1 (mod 8): three correct bits
+#pragma unroll
+  for (int it = 0; it < 5; it++) inv *= 2 - d * inv;   // 6, 12, 24, 48, 96 bits (mod 2^64)
+  const unsigned __int128 d128 = d;
+  unsigned __int128 inv128 = inv;
+  inv128 *= (unsigned __int128)2 - d128 * inv128;       // 128 bits
+  const __int128 shifted = num >> tz;                   // arithmetic shift; exact when 2^tz divides num
+  const __int128 q = (__int128)((unsigned __int128)shifted * inv128);
+  return neg ? -q : q;
+}
+
 // Recover the POLY_SIZE integer coefficients from POLY_SIZE shares (xs[i] = share index s_i,
 // ys[i] = aggregated share).  Exact: Newton divided differences of an integer polynomial at
 // integer nodes are integers, so every division below is exact.  Returns false if a division
@@ -90,7 +115,7 @@ HDN inline bool shamir_recover(const int* xs, const int64_t* ys, int64_t out[POL
     for (int i = POLY_SIZE - 1; i >= k; i--) {
       __int128 num = dd[i] - dd[i - 1];
       int64_t den = (int64_t)(xs[i] - xs[i - k]);
-      __int128 q = num / den;
+      const __int128 q = exact_div_small(num, den);
       if (q * den != num) exact = false;
       dd[i] = q;
     }
