@@ -84,6 +84,7 @@ class BiscottiConfig:
     shard_size: int = 600             # rows per peer shard (mnist 60000/100)
     test_size: int = 2000
     eval_every: int = 1               # reference evaluates every block (honest.go:141-162)
+    msm_window: int | None = None     # fixed-base window bits for the MSM tables (None = largest that fits HBM budget)
     affine_wire: bool = False         # True: normalise every chunk commitment / witness to the 64-byte affine
                                       # wire form (kyber.go:88-168) even though no wire exists between GPUs
     gram_impl: str = "auto"           # auto | tcgen05 | simt

@@ -57,14 +57,20 @@ class CommitmentEngine:
         # ---- fixed-base window tables (device path; window=0 disables them)
         self.w = self.nw = 0
         self.c_table = self.w_table = None
+        nbases = self.dpad + self.wtable.shape[0]
+
+        def table_bytes(w):
+            return nbases * (-(-(max_scalar_bits + 1) // w)) * (1 << (w - 1)) * 64
+
         if window is None:
-            window = 7 if self.device.type == "cuda" else 0
+            # fewest windows (= additions per term) whose tables fit the budget: 11 bits -> 2 windows,
+            # 7 -> 3, 6 -> 4, ...  (MNIST-sized models take w = 11: ~20 GB of HBM buys 18 instead of 27
+            # additions per witness; the CIFAR CNN lands on w = 6)
+            window = 0
+            if self.device.type == "cuda":
+                window = next((w for w in (11, 7, 6, 5, 4, 3) if table_bytes(w) <= table_budget_bytes), 3)
         if window:
-            nbases = self.dpad + self.wtable.shape[0]
-            while window > 2:
-                nw = -(-(max_scalar_bits + 1) // window)
-                if nbases * nw * (1 << (window - 1)) * 64 <= table_budget_bytes:
-                    break
+            while window > 2 and table_bytes(window) > table_budget_bytes:
                 window -= 1
             self.w, self.nw = window, -(-(max_scalar_bits + 1) // window)
             self.c_table = self._build_window_table(self.bases)
@@ -117,7 +123,7 @@ class CommitmentEngine:
         H = 1 << (self.w - 1)
         per = self.nw * H
         table = torch.empty(nb * per, AFF, dtype=torch.int32, device=self.device)
-        chunk = max(1, (1 << 22) // per)
+        chunk = max(1, (1 << 23) // per)
         for b0 in range(0, nb, chunk):
             b1 = min(nb, b0 + chunk)
             jac = torch.empty((b1 - b0) * per, JAC, dtype=torch.int32, device=self.device)

@@ -105,7 +105,8 @@ class BiscottiEngine:
         self.U = torch.zeros(max(1, self.P), self.ldu, dtype=torch.float32, device=self.device)
         self.commit = None
         if cfg.commitments and cfg.secure_agg and cfg.mode == "biscotti":
-            self.commit = CommitmentEngine(self.d, self.S, tau=cfg.srs_tau or self._random_tau(), device=self.device)
+            self.commit = CommitmentEngine(self.d, self.S, tau=cfg.srs_tau or self._random_tau(), device=self.device,
+                                           window=cfg.msm_window)
         self.vrf = cp.BatchedVRF([k.vrf_noise for k in self.keys], self.device)
         self.signer = SchnorrBatchSigner(self.device) if (cfg.verification and cfg.sign_approvals) else None
         self.reports: list[BlockReport] = []
