@@ -139,6 +139,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_g1_bytes_to_affine_host", None, c_cp, c_p, c_ll)
     sig("bsc_g1_affine_to_bytes_host", None, c_p, c_p, c_ll)
     sig("bsc_g1_jac_to_bytes_host", None, c_p, c_p, c_ll)
+    sig("bsc_g1_jac_to_bytes_batch_host", None, c_p, c_p, c_i, c_p)
     sig("bsc_g1_straus_host", None, c_p, c_p, c_p, c_i)
     sig("bsc_srs_g1_host", None, c_cp, c_i, c_p)
     sig("bsc_fr_powers", None, c_cp, c_i, c_p)

@@ -350,6 +350,30 @@ void bsc_g1_jac_to_bytes_host(const void* in_jac, uint8_t* out, long long N) {
   const G1Jac* a = (const G1Jac*)in_jac;
   for (long long i = 0; i < N; i++) g1a_to_bytes(out + 64 * i, g1j_to_affine(a[i]));
 }
+// Jacobian -> 64-byte wire form for the selected rows, with one shared field inversion (Montgomery's trick).
+// Used at block assembly: the device hands over the contributors' full commitments in Jacobian form and
+// no inversion kernel sits on the block's critical path.  idx may be null (rows 0..n-1).
+void bsc_g1_jac_to_bytes_batch_host(const void* in_jac, const int* idx, int n, uint8_t* out) {
+  const G1Jac* a = (const G1Jac*)in_jac;
+  std::vector<Fp> pre((size_t)n);
+  Fp run = fe_one<BnP>();
+  for (int i = 0; i < n; i++) {
+    const G1Jac& p = a[idx ? idx[i] : i];
+    if (!g1j_is_inf(p)) run = fe_mul(run, p.z);
+    pre[(size_t)i] = run;
+  }
+  Fp inv = fe_inv(run);
+  for (int i = n - 1; i >= 0; i--) {
+    const G1Jac& p = a[idx ? idx[i] : i];
+    if (g1j_is_inf(p)) {
+      memset(out + 64 * (size_t)i, 0, 64);
+      continue;
+    }
+    const Fp zi = i > 0 ? fe_mul(inv, pre[(size_t)i - 1]) : inv;
+    inv = fe_mul(inv, p.z);
+    g1a_to_bytes(out + 64 * (size_t)i, g1j_to_affine_with_inv(p, zi));
+  }
+}
 // host mirror of the device Straus kernel (same template) for CPU-side unit tests
 void bsc_g1_straus_host(uint8_t out[64], const void* bases_affine, const long long* s, int T) {
   uint64_t maxmag = 0;

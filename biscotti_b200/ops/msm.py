@@ -209,8 +209,9 @@ class CommitmentEngine:
             return jac.view(P, self.nchunk, JAC)
         return self.normalize(jac).view(P, self.nchunk, AFF)
 
-    def full_commitments(self, chunk_pts: torch.Tensor) -> torch.Tensor:
-        """Full-vector commitment = sum of the chunk commitments -> affine [P, 16]."""
+    def full_commitments(self, chunk_pts: torch.Tensor, jacobian: bool = False) -> torch.Tensor:
+        """Full-vector commitment = sum of the chunk commitments -> affine [P, 16]
+        (or Jacobian [P, 24] when `jacobian`, to be normalised on the host for the rows that enter a block)."""
         P, G = chunk_pts.shape[0], chunk_pts.shape[1]
         isj = chunk_pts.shape[-1] == JAC
         jac = torch.empty(P, JAC, dtype=torch.int32, device=chunk_pts.device)
@@ -220,7 +221,19 @@ class CommitmentEngine:
             check(fn(ptr(chunk_pts), P, G, ptr(jac), stream(chunk_pts.device)), "g1_sum_cols")
         else:
             (L.bsc_g1_sum_cols_jac_host if isj else L.bsc_g1_sum_cols_host)(ptr(chunk_pts), P, G, ptr(jac))
-        return self.normalize(jac)
+        return jac if jacobian else self.normalize(jac)
+
+    @staticmethod
+    def jac_rows_to_bytes(jac_host, rows) -> list:
+        """Wire bytes of the selected rows of a host [N, 24] int32 Jacobian array, one shared inversion."""
+        import numpy as np
+
+        jac_host = np.ascontiguousarray(jac_host, dtype=np.int32)
+        idx = np.asarray(rows, dtype=np.int32)
+        out = np.empty((len(rows), 64), dtype=np.uint8)
+        lib().bsc_g1_jac_to_bytes_batch_host(jac_host.ctypes.data_as(ctypes.c_void_p), idx.ctypes.data_as(ctypes.c_void_p),
+                                             len(rows), out.ctypes.data_as(ctypes.c_void_p))
+        return [out[i].tobytes() for i in range(len(rows))]
 
     def witnesses(self, Q: torch.Tensor, sel: torch.Tensor | None = None, affine: bool = True) -> torch.Tensor:
         """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> [P, nchunk, S, 16 | 24]."""

@@ -221,8 +221,9 @@ class BiscottiEngine:
             with self._phase("commit"):
                 Q = secagg.quantize(self.U, self.d, cfg.precision)
                 chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
-                fullC = self.commit.full_commitments(chunkC)                   # [P, 16]
-                fullC_dev = self.commit.to_bytes_tensor(fullC)                 # [P, 64] on device
+                # full-vector commitments stay Jacobian on the device; the rows that enter the block are
+                # normalised on the host with one shared inversion when the block is assembled
+                fullC_dev = self.commit.full_commitments(chunkC, jacobian=True).view(torch.uint8)   # [P, 96]
 
         # ---- 4. noisers + noise
         with self._phase("noise"):
@@ -351,7 +352,7 @@ class BiscottiEngine:
             gathered = False
             if self.commit is not None and self.P:
                 if self.comm is not None and hasattr(self.comm, "all_gather_rows_u8"):
-                    want["cb"] = self.comm.all_gather_rows_u8(fullC_dev)             # [world*per, 64], row = peer id
+                    want["cb"] = self.comm.all_gather_rows_u8(fullC_dev)             # [world*per, 96], row = peer id
                     gathered = True
                 else:
                     want["cb"] = fullC_dev
@@ -361,13 +362,14 @@ class BiscottiEngine:
             host = self._collect(want)
             if "cb" in host:
                 cb = host["cb"]
+                cbj = cb.view(np.int32).reshape(cb.shape[0], 24)
                 if gathered:
-                    for p in contributors:
-                        commits[p] = cb[p].tobytes()
+                    for p, b in zip(contributors, CommitmentEngine.jac_rows_to_bytes(cbj, list(contributors))):
+                        commits[p] = b
                 else:
-                    for p in contributors:
-                        if p in self.local_index:
-                            commits[p] = cb[self.local_index[p]].tobytes()
+                    mine = [p for p in contributors if p in self.local_index]
+                    for p, b in zip(mine, CommitmentEngine.jac_rows_to_bytes(cbj, [self.local_index[p] for p in mine])):
+                        commits[p] = b
                     if self.comm is not None:
                         commits = self.comm.merge_dicts(commits)
             all_sigs = None

@@ -224,6 +224,11 @@ void bsc_g1_affine_to_bytes_host(const void* in_affine, uint8_t* out, long long 
 
 void bsc_g1_jac_to_bytes_host(const void* in_jac, uint8_t* out, long long N);
 
+// Jacobian -> 64-byte wire form for the selected rows, with one shared field inversion (Montgomery's trick).
+// Used at block assembly: the device hands over the contributors' full commitments in Jacobian form and
+// no inversion kernel sits on the block's critical path.  idx may be null (rows 0..n-1).
+void bsc_g1_jac_to_bytes_batch_host(const void* in_jac, const int* idx, int n, uint8_t* out);
+
 // host mirror of the device Straus kernel (same template) for CPU-side unit tests
 void bsc_g1_straus_host(uint8_t out[64], const void* bases_affine, const long long* s, int T);
 
