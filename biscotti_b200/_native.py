@@ -141,6 +141,18 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_g1_jac_to_bytes_host", None, c_p, c_p, c_ll)
     sig("bsc_g1_jac_to_bytes_batch_host", None, c_p, c_p, c_i, c_p)
     sig("bsc_g1_straus_host", None, c_p, c_p, c_p, c_i)
+    # G2 / GT / pairing (host)
+    sig("bsc_g2_generator", None, c_p)
+    sig("bsc_g2_on_curve", c_i, c_cp)
+    sig("bsc_g2_add", None, c_p, c_cp, c_cp)
+    sig("bsc_g2_neg", None, c_p, c_cp)
+    sig("bsc_g2_mul", None, c_p, c_cp, c_cp)
+    sig("bsc_srs_g2_host", None, c_cp, c_i, c_p)
+    sig("bsc_pairing", None, c_cp, c_cp, c_p)
+    sig("bsc_pairing_check", c_i, c_cp, c_cp, c_i)
+    sig("bsc_gt_mul", None, c_p, c_cp, c_cp)
+    sig("bsc_gt_pow", None, c_p, c_cp, c_cp)
+    sig("bsc_kzg_verify_share", c_i, c_cp, c_cp, c_cp, c_cp, c_cp, c_i, c_ll)
     sig("bsc_srs_g1_host", None, c_cp, c_i, c_p)
     sig("bsc_fr_powers", None, c_cp, c_i, c_p)
     sig("bsc_schnorr_pubkey", None, c_cp, c_p)

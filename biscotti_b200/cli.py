@@ -160,7 +160,9 @@ def run_kzg_demo(a) -> int:
     print("recovered sum head:", [round(float(v), 4) for v in w[:4]], "inconsistent shares:", int(bad.sum()))
     ok = eng.verify_share_trapdoor(eng.to_bytes(C)[:64], eng.to_bytes(W)[:64], 0, 0, int(Y[0, 0, 0]))
     print("KZG opening of chunk 0 at x=-10 verifies:", ok)
-    return 0 if ok and int(bad.sum()) == 0 else 1
+    okp = eng.verify_share_pairing(eng.to_bytes(C)[:64], eng.to_bytes(W)[:64], 0, 0, int(Y[0, 0, 0]))
+    print("same opening through the pairing (verifySecret, kyber.go:650-673):", okp)
+    return 0 if ok and okp and int(bad.sum()) == 0 else 1
 
 
 def run_experiment(a) -> int:

@@ -260,15 +260,17 @@ def generate_srs_bytes(d: int, tau: int = 2) -> bytes:
 def write_bootstrap_files(outdir: str, n_nodes: int, dims: int, hosts: list[str] | None = None, seed: int = 1,
                           tau: int = 2, nodes_per_host: int | None = None):
     """Write peersfile.txt, commitKey.json, pKeyG1.json in the reference's JSON-lines layout
-    (one {Id,Pkey,Skey} object per line, base64 byte fields like Go's encoding/json).  G2 halves of the
-    SRS are only needed for pairing checks the live path never runs; Skey carries the G1 point again so
-    the file keeps its shape (documented deviation)."""
+    (one {Id,Pkey,Skey} object per line, base64 byte fields like Go's encoding/json): commitKey.json carries
+    PKG1[i] (64-byte G1) as Pkey and PKG2[i] (129-byte G2) as Skey, generateBootstrapFile.go:102-133."""
+    from . import pairing
+
     os.makedirs(outdir, exist_ok=True)
     srs = generate_srs_bytes(dims, tau)
+    srs2 = pairing.srs_g2(tau, dims)
     with open(os.path.join(outdir, "commitKey.json"), "w") as f:
         for i in range(dims):
             pt = base64.b64encode(srs[64 * i: 64 * i + 64]).decode()
-            f.write(json.dumps({"Id": i, "Pkey": pt, "Skey": pt}) + "\n")
+            f.write(json.dumps({"Id": i, "Pkey": pt, "Skey": base64.b64encode(srs2[i]).decode()}) + "\n")
     keys = derive_peer_keys(n_nodes, seed)
     with open(os.path.join(outdir, "pKeyG1.json"), "w") as f:
         for i, k in enumerate(keys):
@@ -294,3 +296,19 @@ def load_commit_key(path: str) -> bytes:
             if line.strip():
                 pts.append(base64.b64decode(json.loads(line)["Pkey"]))
     return b"".join(pts)
+
+
+def load_commit_key_g2(path: str) -> list[bytes]:
+    """The G2 half of commitKey.json (PKG2[i] = tau^i * G2, honest.go:848-864)."""
+    pts = []
+    with open(path) as f:
+        for line in f:
+            if line.strip():
+                pts.append(base64.b64decode(json.loads(line)["Skey"]))
+    return pts
+
+
+def g1_generator() -> bytes:
+    out = _buf(64)
+    _L().bsc_g1_generator(out)
+    return out.raw

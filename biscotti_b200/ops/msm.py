@@ -258,7 +258,7 @@ class CommitmentEngine:
         """Opening check C - y*tau^(10c)*G == (tau - x_s)*W.  verifySecret (kyber.go:650-673) does this with a
         pairing because tau is secret; with the reference's public tau = 2 (publicKey.go:36) — or any tau this
         engine was built with — the same relation can be checked in G1 directly.  Used by tests and the
-        peer-scale 'Shamir verify' sweep; an unknown-tau deployment needs the pairing (not implemented)."""
+        peer-scale 'Shamir verify' sweep; an unknown-tau deployment uses `verify_share_pairing`."""
         from ..oracle import bn256 as O
 
         x = s - 10
@@ -266,6 +266,17 @@ class CommitmentEngine:
         lhs = O.add(O.from_bytes(chunk_commit), O.neg(O.mul(O.GEN, (y * pow(tau, 10 * chunk, O.ORDER)) % O.ORDER)))
         rhs = O.mul(O.from_bytes(witness), (tau - x) % O.ORDER)
         return lhs == rhs
+
+    def verify_share_pairing(self, chunk_commit: bytes, witness: bytes, chunk: int, s: int, y: int) -> bool:
+        """verifySecret (kyber.go:650-673) proper: e(C, g2) == e(W, tau*g2 - x_s*g2) * e(PKG1[10c], g2)^y, using only
+        public SRS points (g2 and tau*g2), so it also holds for a secret tau.  Host pairing, ~10 ms per check."""
+        from ..crypto import pairing
+
+        if not hasattr(self, "_g2_srs"):
+            g2 = pairing.g2_generator()
+            self._g2_srs = (g2, pairing.g2_mul(g2, self.tau))
+        base = self.srs_bytes[64 * POLY_SIZE * chunk: 64 * POLY_SIZE * chunk + 64]
+        return pairing.verify_secret(chunk_commit, witness, s - 10, y, self._g2_srs[0], self._g2_srs[1], base=base)
 
     def aggregate(self, pts: torch.Tensor, sel: torch.Tensor, affine: bool = True) -> torch.Tensor:
         """Miner-side homomorphic add over contributing peers: pts [P, G..., 16|24] -> [G..., 16|24]."""

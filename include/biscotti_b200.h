@@ -370,6 +370,39 @@ long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, 
 int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B, int IC, int OC, int K, int pad, int H, int W, int C, int ldu, float clip, void* stream);
 
 /* --------------------------------------------------------------------------------------------
+ * pairing.cpp - 
+ * -------------------------------------------------------------------------------------------- */
+// ---- G2 (129-byte wire form; a first byte of 0x00 is the point at infinity) ---------------------------
+void bsc_g2_generator(uint8_t* out129);
+
+int bsc_g2_on_curve(const uint8_t* in129);
+
+void bsc_g2_add(uint8_t* out129, const uint8_t* a129, const uint8_t* b129);
+
+void bsc_g2_neg(uint8_t* out129, const uint8_t* a129);
+
+// scalar: 32-byte big-endian, taken as is (callers reduce mod the group order)
+void bsc_g2_mul(uint8_t* out129, const uint8_t* pt129, const uint8_t* k32);
+
+// PKG2[i] = tau^i * G2, i < d (DistSys/publicKey.go:42-57) -> d * 129 bytes
+void bsc_srs_g2_host(const uint8_t* tau32, int d, uint8_t* out);
+
+// ---- GT / pairing --------------------------------------------------------------------------------------
+void bsc_pairing(const uint8_t* g1_64, const uint8_t* g2_129, uint8_t* out384);
+
+// 1 iff prod_i e(P_i, Q_i) == 1; one final exponentiation for the whole product
+int bsc_pairing_check(const uint8_t* g1s, const uint8_t* g2s, int n);
+
+void bsc_gt_mul(uint8_t* out384, const uint8_t* a384, const uint8_t* b384);
+
+void bsc_gt_pow(uint8_t* out384, const uint8_t* a384, const uint8_t* k32);
+
+// verifySecret (DistSys/kyber.go:650-673): e(C, g2) == e(W, tau*g2 - x*g2) * e(B, g2)^y, checked as
+// e(C - y*B, g2) * e(-W, tau*g2 - x*g2) == 1.  B is the first SRS point of the chunk's slice (g1 for chunk 0,
+// which is the only case the reference's formula covers; chunk c is committed against PKG1[10c..], kyber.go:172-202).
+int bsc_kzg_verify_share(const uint8_t* commit64, const uint8_t* witness64, const uint8_t* base64, const uint8_t* g2_129, const uint8_t* tau_g2_129, int x, long long y);
+
+/* --------------------------------------------------------------------------------------------
  * sha256_ni.cpp - 
  * -------------------------------------------------------------------------------------------- */
 void bsc_sha256_fast(const uint8_t* data, size_t n, uint8_t out[32]);
