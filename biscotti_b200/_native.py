@@ -74,6 +74,9 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_eval_logistic", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
     sig("bsc_cnn1_scratch_floats", c_ll, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i)
     sig("bsc_cnn1_local_step", c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_f, c_p)
+    sig("bsc_cnn2_scratch_floats", c_ll, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i)
+    sig("bsc_cnn2_local_step", c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
+        c_i, c_f, c_p)
     # secure aggregation
     sig("bsc_quantize", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_d, c_p)
     sig("bsc_shares_eval", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_p)

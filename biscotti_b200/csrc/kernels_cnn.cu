@@ -16,6 +16,7 @@
 //   cnn1_coef/scale   fixed-shape reduction of the partial norms -> clip coefficient, U = -coef * grad
 // Partial norms are written to per-CTA slots and summed in index order: the clip coefficient (and with it
 // the ledger) is bit-reproducible.
+#include <string.h>
 #include "common.cuh"
 
 namespace bsc {
@@ -204,6 +205,167 @@ __global__ void __launch_bounds__(256) cnn1_scale_kernel(float* __restrict__ U, 
   for (int k = k0 + threadIdx.x; k < min(ldu, k0 + 4096); k += blockDim.x) row[k] = k < s.d ? row[k] * m : 0.f;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Two-convolution model with 2x2 max-pooling after each ReLU:
+//   lfw_cnn : Conv2d(3,18,3,1,1)+ReLU+MaxPool2 + Conv2d(18,36,3,1,1)+ReLU+MaxPool2 + Linear(5940, 2)
+//             ML/Pytorch/lfw_cnn_model.py:11-29 (18 254 parameters)
+// The pooled activation and a 2-bit arg-max are all the forward pass keeps per 2x2 window: relu(max) ==
+// max(relu), and the backward pass routes a gradient to the arg-max position only where the pooled value is
+// positive.  The classifier head reuses the cnn1_fc_* / loss / coef / scale kernels above (J = pooled size).
+
+// thread -> one pooled output (img, oc, py, px): the four conv outputs of its window from one (K+1)^2 patch per channel
+template <int K>
+__global__ void __launch_bounds__(256) cnn2_conv_pool_fwd_kernel(const float* __restrict__ wt, const float* __restrict__ bias,
+                                                                 const float* __restrict__ in, float* __restrict__ out,
+                                                                 uint8_t* __restrict__ arg, int IC, int H, int W, int OC,
+                                                                 int pad, int PH, int PW, long long total) {
+  extern __shared__ float sw[];
+  const int nw = OC * IC * K * K;
+  for (int i = threadIdx.x; i < nw + OC; i += blockDim.x) sw[i] = i < nw ? wt[i] : bias[i - nw];
+  __syncthreads();
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int px = (int)(t % PW);
+    const int py = (int)((t / PW) % PH);
+    const int oc = (int)((t / ((long long)PW * PH)) % OC);
+    const long long img = t / ((long long)PW * PH * OC);
+    const float* x = in + img * IC * H * W;
+    const float b = sw[nw + oc];
+    float a00 = b, a01 = b, a10 = b, a11 = b;
+    const int iy0 = 2 * py - pad, ix0 = 2 * px - pad;
+    for (int ic = 0; ic < IC; ic++) {
+      float patch[K + 1][K + 1];
+#pragma unroll
+      for (int r = 0; r <= K; r++)
+#pragma unroll
+        for (int c = 0; c <= K; c++) {
+          const int iy = iy0 + r, ix = ix0 + c;
+          patch[r][c] = (iy >= 0 && iy < H && ix >= 0 && ix < W) ? x[(ic * H + iy) * W + ix] : 0.f;
+        }
+      const float* wk = sw + (oc * IC + ic) * K * K;
+#pragma unroll
+      for (int ky = 0; ky < K; ky++)
+#pragma unroll
+        for (int kx = 0; kx < K; kx++) {
+          const float wv = wk[ky * K + kx];
+          a00 = fmaf(wv, patch[ky][kx], a00);
+          a01 = fmaf(wv, patch[ky][kx + 1], a01);
+          a10 = fmaf(wv, patch[ky + 1][kx], a10);
+          a11 = fmaf(wv, patch[ky + 1][kx + 1], a11);
+        }
+    }
+    float best = a00;
+    int q = 0;
+    if (a01 > best) { best = a01; q = 1; }
+    if (a10 > best) { best = a10; q = 2; }
+    if (a11 > best) { best = a11; q = 3; }
+    out[t] = best > 0.f ? best : 0.f;
+    arg[t] = (uint8_t)q;
+  }
+}
+
+// grid (OC, P): weight / bias gradients of one output channel of one peer from the pooled gradient dp (already
+// masked by the ReLU) and the arg-max map; input channels are processed ICB at a time to bound registers.
+template <int K, int ICB>
+__global__ void __launch_bounds__(256) cnn2_conv_wgrad_kernel(const float* __restrict__ in, const float* __restrict__ dp,
+                                                              const uint8_t* __restrict__ arg, float* __restrict__ U, int ldu,
+                                                              int off_w, int off_b, float* __restrict__ partial, int nslots,
+                                                              int slot0, int B, int IC, int H, int W, int OC, int pad, int PH,
+                                                              int PW) {
+  __shared__ float red[40];
+  const int oc = blockIdx.x, p = blockIdx.y, tid = threadIdx.x;
+  const int npos = B * PH * PW;
+  float nrm = 0.f;
+  for (int ic0 = 0; ic0 < IC; ic0 += ICB) {
+    float acc[ICB * K * K];
+#pragma unroll
+    for (int t = 0; t < ICB * K * K; t++) acc[t] = 0.f;
+    float accb = 0.f;
+    for (int pos = tid; pos < npos; pos += blockDim.x) {
+      const int px = pos % PW, py = (pos / PW) % PH, b = pos / (PW * PH);
+      const size_t idx = ((size_t)(p * B + b) * OC + oc) * PH * PW + py * PW + px;
+      const float d = dp[idx];
+      if (d == 0.f) continue;
+      const int a = arg[idx];
+      const int oy = 2 * py + (a >> 1), ox = 2 * px + (a & 1);
+      accb += d;
+      const float* x = in + (size_t)(p * B + b) * IC * H * W;
+#pragma unroll
+      for (int i = 0; i < ICB; i++) {
+        const int ic = ic0 + i;
+        if (ic >= IC) break;
+#pragma unroll
+        for (int ky = 0; ky < K; ky++) {
+          const int iy = oy + ky - pad;
+#pragma unroll
+          for (int kx = 0; kx < K; kx++) {
+            const int ix = ox + kx - pad;
+            if (iy >= 0 && iy < H && ix >= 0 && ix < W)
+              acc[(i * K + ky) * K + kx] = fmaf(d, x[(ic * H + iy) * W + ix], acc[(i * K + ky) * K + kx]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < ICB * K * K; t++) {
+      const float g = block_sum(acc[t], red);
+      if (tid == 0 && ic0 + t / (K * K) < IC) {
+        U[(size_t)p * ldu + off_w + (oc * IC + ic0) * K * K + t] = g;
+        nrm = fmaf(g, g, nrm);
+      }
+    }
+    if (ic0 == 0) {
+      const float gb = block_sum(accb, red);
+      if (tid == 0) {
+        U[(size_t)p * ldu + off_b + oc] = gb;
+        nrm = fmaf(gb, gb, nrm);
+      }
+    }
+  }
+  if (tid == 0) partial[(size_t)p * nslots + slot0 + oc] = nrm;
+}
+
+// thread -> one input position (img, ic, y, x) of the second convolution: gathers the sparse gradient of the
+// conv output (non-zero only at arg-max positions) through the transposed filter, masked by the first
+// layer's ReLU (a1 = pooled activation of layer 1 = this layer's input)
+template <int K>
+__global__ void __launch_bounds__(256) cnn2_dgrad_kernel(const float* __restrict__ wt, const float* __restrict__ dp2,
+                                                         const uint8_t* __restrict__ arg2, const float* __restrict__ a1,
+                                                         float* __restrict__ dp1, int IC, int H, int W, int OC, int pad,
+                                                         int PH, int PW, long long total) {
+  extern __shared__ float sw[];
+  const int nw = OC * IC * K * K;
+  for (int i = threadIdx.x; i < nw; i += blockDim.x) sw[i] = wt[i];
+  __syncthreads();
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    if (!(a1[t] > 0.f)) {
+      dp1[t] = 0.f;
+      continue;
+    }
+    const int x = (int)(t % W);
+    const int y = (int)((t / W) % H);
+    const int ic = (int)((t / ((long long)W * H)) % IC);
+    const long long img = t / ((long long)W * H * IC);
+    float g = 0.f;
+    for (int oc = 0; oc < OC; oc++) {
+      const size_t base = ((size_t)img * OC + oc) * PH * PW;
+      const float* wk = sw + (oc * IC + ic) * K * K;
+#pragma unroll
+      for (int ky = 0; ky < K; ky++) {
+        const int oy = y - ky + pad;
+        if (oy < 0 || (oy >> 1) >= PH) continue;
+#pragma unroll
+        for (int kx = 0; kx < K; kx++) {
+          const int ox = x - kx + pad;
+          if (ox < 0 || (ox >> 1) >= PW) continue;
+          const size_t idx = base + (oy >> 1) * PW + (ox >> 1);
+          if (arg2[idx] == (((oy & 1) << 1) | (ox & 1))) g = fmaf(dp2[idx], wk[ky * K + kx], g);
+        }
+      }
+    }
+    dp1[t] = g;
+  }
+}
+
 }  // namespace bsc
 
 using namespace bsc;
@@ -253,6 +415,110 @@ int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, 
   cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
   cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s);
   return finish_launch("cnn1_local_step", 7);
+}
+
+// ---- two-convolution model (conv+ReLU+MaxPool2 twice, then a linear head) ------------------------------------
+struct Cnn2Dims {
+  int OH1, OW1, PH1, PW1, OH2, OW2, PH2, PW2;
+  long long n1, J, nfc, nslots;   // n1 = OC1*PH1*PW1 floats per image after layer 1, J = OC2*PH2*PW2
+};
+static Cnn2Dims cnn2_dims(int H, int W, int OC1, int K1, int pad1, int OC2, int K2, int pad2) {
+  Cnn2Dims m;
+  m.OH1 = H + 2 * pad1 - K1 + 1; m.OW1 = W + 2 * pad1 - K1 + 1;
+  m.PH1 = m.OH1 / 2; m.PW1 = m.OW1 / 2;
+  m.OH2 = m.PH1 + 2 * pad2 - K2 + 1; m.OW2 = m.PW1 + 2 * pad2 - K2 + 1;
+  m.PH2 = m.OH2 / 2; m.PW2 = m.OW2 / 2;
+  m.n1 = (long long)OC1 * m.PH1 * m.PW1;
+  m.J = (long long)OC2 * m.PH2 * m.PW2;
+  m.nfc = (m.J + 255) / 256;
+  m.nslots = m.nfc + OC2 + OC1;
+  return m;
+}
+// scratch (floats): pool1 [PB*n1], dp1 [PB*n1], act [PB*J], dl [PB*C], partial [P*nslots], coef [P],
+// arg1 bytes [PB*n1], arg2 bytes [PB*J] (each rounded up to whole floats)
+long long bsc_cnn2_scratch_floats(int P, int B, int IC, int H, int W, int OC1, int K1, int pad1, int OC2, int K2, int pad2,
+                                  int C) {
+  const Cnn2Dims m = cnn2_dims(H, W, OC1, K1, pad1, OC2, K2, pad2);
+  const long long PB = (long long)P * B;
+  return 2 * PB * m.n1 + PB * m.J + PB * C + (long long)P * m.nslots + P + (PB * m.n1 + 3) / 4 + (PB * m.J + 3) / 4 + 8;
+}
+
+extern "C++" {
+template <int K>
+static void cnn2_launch_fwd(const float* wt, const float* bias, const float* in, float* out, uint8_t* arg, int IC, int H,
+                            int W, int OC, int pad, int PH, int PW, long long total, cudaStream_t st) {
+  const long long blocks = (total + 255) / 256;
+  const int grid = (int)(blocks < 148 * 16 ? blocks : 148 * 16);
+  const size_t smem = (size_t)(OC * IC * K * K + OC) * sizeof(float);
+  cnn2_conv_pool_fwd_kernel<K><<<grid, 256, smem, st>>>(wt, bias, in, out, arg, IC, H, W, OC, pad, PH, PW, total);
+}
+template <int K>
+static void cnn2_launch_wgrad(const float* in, const float* dp, const uint8_t* arg, float* U, int ldu, int off_w, int off_b,
+                              float* partial, int nslots, int slot0, int P, int B, int IC, int H, int W, int OC, int pad,
+                              int PH, int PW, cudaStream_t st) {
+  cnn2_conv_wgrad_kernel<K, 3><<<dim3(OC, P), 256, 0, st>>>(in, dp, arg, U, ldu, off_w, off_b, partial, nslots, slot0, B, IC,
+                                                            H, W, OC, pad, PH, PW);
+}
+template <int K>
+static void cnn2_launch_dgrad(const float* wt, const float* dp2, const uint8_t* arg2, const float* a1, float* dp1, int IC,
+                              int H, int W, int OC, int pad, int PH, int PW, long long total, cudaStream_t st) {
+  const long long blocks = (total + 255) / 256;
+  const int grid = (int)(blocks < 148 * 16 ? blocks : 148 * 16);
+  const size_t smem = (size_t)OC * IC * K * K * sizeof(float);
+  cnn2_dgrad_kernel<K><<<grid, 256, smem, st>>>(wt, dp2, arg2, a1, dp1, IC, H, W, OC, pad, PH, PW, total);
+}
+}  // extern "C++"
+#define CNN2_BY_K(K, call3, call5) \
+  do {                             \
+    if ((K) == 3) { call3; } else { call5; } \
+  } while (0)
+
+// Local step of the two-convolution model for P peers.  w: flat global weights in named_parameters order
+// (conv0.weight, conv0.bias, conv1.weight, conv1.bias, fc.weight, fc.bias); X: [P][B][IC][H][W]; y: [P][B];
+// U: [P][ldu] out (= -clip(grad)); loss: [P] or null; scratch: bsc_cnn2_scratch_floats floats.
+int bsc_cnn2_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B,
+                        int IC, int H, int W, int OC1, int K1, int pad1, int OC2, int K2, int pad2, int C, int ldu,
+                        float clip, void* stream) {
+  if ((K1 != 3 && K1 != 5) || (K2 != 3 && K2 != 5) || C > 16 || B > 32) return -1;
+  const Cnn2Dims m = cnn2_dims(H, W, OC1, K1, pad1, OC2, K2, pad2);
+  if (m.PH2 <= 0 || m.PW2 <= 0) return -1;
+  const int off_w1 = 0, off_b1 = OC1 * IC * K1 * K1, off_w2 = off_b1 + OC1, off_b2 = off_w2 + OC2 * OC1 * K2 * K2;
+  Cnn1Shape s;   // the head kernels only read J, C, B, off_fw, off_fb, d
+  memset(&s, 0, sizeof(s));
+  s.J = (int)m.J; s.C = C; s.B = B;
+  s.off_fw = off_b2 + OC2;
+  s.off_fb = s.off_fw + C * (int)m.J;
+  s.d = s.off_fb + C;
+  if (ldu < s.d || (size_t)(OC2 * OC1 * K2 * K2 + OC2) * sizeof(float) > 48 * 1024) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long PB = (long long)P * B;
+  const int nslots = (int)m.nslots, nfc = (int)m.nfc;
+  float* pool1 = scratch;
+  float* dp1 = pool1 + PB * m.n1;
+  float* act = dp1 + PB * m.n1;
+  float* dl = act + PB * m.J;
+  float* partial = dl + PB * C;
+  float* coef = partial + (long long)P * nslots;
+  uint8_t* arg1 = (uint8_t*)(coef + P);
+  uint8_t* arg2 = arg1 + ((PB * m.n1 + 3) / 4) * 4;
+  // forward
+  CNN2_BY_K(K1, cnn2_launch_fwd<3>(w + off_w1, w + off_b1, X, pool1, arg1, IC, H, W, OC1, pad1, m.PH1, m.PW1, PB * m.n1, st),
+            cnn2_launch_fwd<5>(w + off_w1, w + off_b1, X, pool1, arg1, IC, H, W, OC1, pad1, m.PH1, m.PW1, PB * m.n1, st));
+  CNN2_BY_K(K2, cnn2_launch_fwd<3>(w + off_w2, w + off_b2, pool1, act, arg2, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, PB * m.J, st),
+            cnn2_launch_fwd<5>(w + off_w2, w + off_b2, pool1, act, arg2, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, PB * m.J, st));
+  cnn1_fc_fwd_kernel<<<dim3(B, P), 256, 0, st>>>(w, act, dl, s);
+  cnn1_loss_kernel<<<(P + 3) / 4, 128, 0, st>>>(dl, y, loss, U, ldu, P, s);
+  // backward: head (act <- masked gradient of the pooled layer-2 output), then the two convolutions
+  cnn1_fc_bwd_kernel<<<dim3(nfc, P), 256, 0, st>>>(w, act, dl, U, ldu, partial, nslots, s);
+  CNN2_BY_K(K2, cnn2_launch_wgrad<3>(pool1, act, arg2, U, ldu, off_w2, off_b2, partial, nslots, nfc, P, B, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, st),
+            cnn2_launch_wgrad<5>(pool1, act, arg2, U, ldu, off_w2, off_b2, partial, nslots, nfc, P, B, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, st));
+  CNN2_BY_K(K2, cnn2_launch_dgrad<3>(w + off_w2, act, arg2, pool1, dp1, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, PB * m.n1, st),
+            cnn2_launch_dgrad<5>(w + off_w2, act, arg2, pool1, dp1, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, PB * m.n1, st));
+  CNN2_BY_K(K1, cnn2_launch_wgrad<3>(X, dp1, arg1, U, ldu, off_w1, off_b1, partial, nslots, nfc + OC2, P, B, IC, H, W, OC1, pad1, m.PH1, m.PW1, st),
+            cnn2_launch_wgrad<5>(X, dp1, arg1, U, ldu, off_w1, off_b1, partial, nslots, nfc + OC2, P, B, IC, H, W, OC1, pad1, m.PH1, m.PW1, st));
+  cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
+  cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s);
+  return finish_launch("cnn2_local_step", 10);
 }
 
 }  // extern "C"

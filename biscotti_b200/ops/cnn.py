@@ -6,10 +6,10 @@ from .. import _native
 
 
 def supports(kind: str) -> bool:
-    if kind not in ("mnist_cnn", "cifar_cnn"):
+    if kind not in ("mnist_cnn", "cifar_cnn", "lfw_cnn"):
         return False
     try:
-        return hasattr(_native.load(), "bsc_cnn1_local_step")
+        return hasattr(_native.load(), "bsc_cnn2_local_step" if kind == "lfw_cnn" else "bsc_cnn1_local_step")
     except Exception:
         return False
 

@@ -1,4 +1,5 @@
-"""ctypes wrapper of the one-conv-layer CNN local-step kernels (csrc/kernels_cnn.cu)."""
+"""ctypes wrapper of the CNN local-step kernels (csrc/kernels_cnn.cu): one-convolution models (mnist_cnn,
+cifar_cnn) and the two-convolution + max-pool model (lfw_cnn)."""
 from __future__ import annotations
 
 import ctypes
@@ -16,6 +17,8 @@ def local_step(kind: str, w32: torch.Tensor, Xb: torch.Tensor, yb: torch.Tensor,
     from ..models.registry import CNN_ARCH
 
     arch = CNN_ARCH[kind]
+    if len(arch["convs"]) == 2:
+        return _local_step2(arch, w32, Xb, yb, clip, out)
     c = arch["convs"][0]
     IC, H, W = arch["image"]
     P, B = Xb.shape[0], Xb.shape[1]
@@ -33,4 +36,31 @@ def local_step(kind: str, w32: torch.Tensor, Xb: torch.Tensor, yb: torch.Tensor,
     check(L.bsc_cnn1_local_step(ptr(w32), ptr(Xc), ptr(yc), ptr(out), None, ptr(buf), P, B, IC, c.cout, c.k, c.pad, H, W,
                                 arch["n_classes"], out.stride(0), ctypes.c_float(clip), stream(Xb.device)),
           "cnn1_local_step")
+    return out
+
+
+def _scratch_buf(device, n):
+    key = (device, n)
+    buf = _scratch.get(key)
+    if buf is None:
+        _scratch.clear()
+        buf = torch.empty(n, dtype=torch.float32, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def _local_step2(arch, w32, Xb, yb, clip, out):
+    """conv+ReLU+MaxPool2 twice, then the linear head (lfw_cnn_model.py:11-29)."""
+    c1, c2 = arch["convs"]
+    assert c1.pool == 2 and c2.pool == 2
+    IC, H, W = arch["image"]
+    P, B = Xb.shape[0], Xb.shape[1]
+    L = _native.load()
+    n = L.bsc_cnn2_scratch_floats(P, B, IC, H, W, c1.cout, c1.k, c1.pad, c2.cout, c2.k, c2.pad, arch["n_classes"])
+    buf = _scratch_buf(Xb.device, n)
+    Xc = Xb.contiguous().float()
+    yc = yb.contiguous().int()
+    check(L.bsc_cnn2_local_step(ptr(w32), ptr(Xc), ptr(yc), ptr(out), None, ptr(buf), P, B, IC, H, W, c1.cout, c1.k, c1.pad,
+                                c2.cout, c2.k, c2.pad, arch["n_classes"], out.stride(0), ctypes.c_float(clip),
+                                stream(Xb.device)), "cnn2_local_step")
     return out

@@ -369,6 +369,15 @@ long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, 
 // U: [P][ldu] out (= -clip(grad)); loss: [P] (may be null); scratch: see bsc_cnn1_scratch_floats.
 int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B, int IC, int OC, int K, int pad, int H, int W, int C, int ldu, float clip, void* stream);
 
+// scratch (floats): pool1 [PB*n1], dp1 [PB*n1], act [PB*J], dl [PB*C], partial [P*nslots], coef [P],
+// arg1 bytes [PB*n1], arg2 bytes [PB*J] (each rounded up to whole floats)
+long long bsc_cnn2_scratch_floats(int P, int B, int IC, int H, int W, int OC1, int K1, int pad1, int OC2, int K2, int pad2, int C);
+
+// Local step of the two-convolution model for P peers.  w: flat global weights in named_parameters order
+// (conv0.weight, conv0.bias, conv1.weight, conv1.bias, fc.weight, fc.bias); X: [P][B][IC][H][W]; y: [P][B];
+// U: [P][ldu] out (= -clip(grad)); loss: [P] or null; scratch: bsc_cnn2_scratch_floats floats.
+int bsc_cnn2_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B, int IC, int H, int W, int OC1, int K1, int pad1, int OC2, int K2, int pad2, int C, int ldu, float clip, void* stream);
+
 /* --------------------------------------------------------------------------------------------
  * pairing.cpp - 
  * -------------------------------------------------------------------------------------------- */

@@ -269,7 +269,7 @@ def test_batched_schnorr_on_device_matches_host_and_verifies():
         assert cp.schnorr_verify(m, cp.schnorr_pubkey(sk), s)
 
 
-@pytest.mark.parametrize("kind", ["mnist_cnn", "cifar_cnn"])
+@pytest.mark.parametrize("kind", ["mnist_cnn", "cifar_cnn", "lfw_cnn"])
 def test_cnn_local_step_kernels_match_autograd(kind):
     """Hand-written conv/fc forward+backward (kernels_cnn.cu) vs per-peer torch autograd on the CPU."""
     from biscotti_b200.models.registry import CNN_ARCH, cnn_local_step, cnn_param_slices
