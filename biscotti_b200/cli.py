@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import argparse
 import hashlib
+import os
 import sys
 
 
@@ -46,6 +47,7 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--no-dump", action="store_true")
     ap.add_argument("--log", action="store_true", help="emit [peer] log lines on stderr")
     ap.add_argument("--save-chain", default=None)
+    ap.add_argument("--resume", default=None, help="chain file to adopt before running (restart / rejoin, main.go:1000-1013)")
 
 
 def config_from_args(a, mode: str):
@@ -82,8 +84,18 @@ def run_localtest(a, mode: str) -> int:
         else:
             comm = NcclComm(rank, world, device)
     eng = BiscottiEngine(cfg, device=device, rank=rank, world=world, comm=comm, log_stream=sys.stderr if a.log else None)
-    eng.run()
+    if a.resume:
+        # a restarted deployment adopts the saved chain (the ledger is the checkpoint) and continues from its height
+        with open(a.resume, "rb") as f:
+            adopted = eng.adopt_chain(f.read())
+        if rank == 0:
+            print(f"resume: adopted={adopted} height={len(eng.chain)} next_iteration={eng.iteration}", file=sys.stderr)
+    eng.run(max(0, cfg.max_iterations + 1 - eng.iteration))
     dump = eng.print_chain()
+    dump_dir = os.environ.get("BISCOTTI_DUMP_DIR")
+    if dump_dir:   # one PrintChain file per rank, for the reference-style pairwise `cmp` (deploy/local_test.sh)
+        with open(os.path.join(dump_dir, f"chain_rank{rank}.txt"), "w") as f:
+            f.write(dump)
     ok = True
     if world > 1:
         digests = comm.all_gather_bytes(hashlib.sha256(dump.encode()).digest())

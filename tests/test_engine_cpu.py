@@ -113,6 +113,23 @@ def test_rejoin_adopts_longest_chain():
     assert not late.adopt_chain(a.chain.serialize())   # not longer any more
 
 
+def test_restart_from_saved_ledger_reproduces_uninterrupted_run(tmp_path):
+    """The ledger is the checkpoint: a process killed after block k and restarted from the saved
+    chain continues to exactly the chain an uninterrupted run produces (deploy/fail_and_restart.sh)."""
+    straight = BiscottiEngine(_cfg(max_iterations=7))
+    straight.run()
+    first = BiscottiEngine(_cfg(max_iterations=7))
+    first.run(4)
+    first.chain.save(str(tmp_path / "chain.bin"))
+    second = BiscottiEngine(_cfg(max_iterations=7))
+    with open(tmp_path / "chain.bin", "rb") as f:
+        assert second.adopt_chain(f.read())
+    assert second.iteration == 4
+    second.run(8 - second.iteration)
+    assert second.chain == straight.chain
+    assert second.stake == straight.stake
+
+
 def test_localtest_cli_two_ranks_gloo_chain_equality():
     """localTest.sh parity: N peers sharded over 2 processes (gloo); every rank must print the same chain,
     and it must equal the single-process chain."""
