@@ -15,6 +15,7 @@
 // computes one output with an interleaved (Straus) doubling chain; consecutive threads share the
 // bases of a group so base loads are warp-broadcast.  Results are normalised with Montgomery's
 // batched-inversion trick.
+#include <stdlib.h>
 #include "common.cuh"
 #include "g1.cuh"
 
@@ -125,7 +126,8 @@ HDN inline G1Jac g1_table_msm(const G1Affine* __restrict__ table, long long firs
 }
 
 // same indexing contract as msm_groups_kernel, bases replaced by their window tables
-__global__ void __launch_bounds__(128) msm_table_kernel(const long long* __restrict__ Q, int ldq,
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) msm_table_kernel(const long long* __restrict__ Q, int ldq,
                                                         const int* __restrict__ sel, int P,
                                                         const int* __restrict__ sidx, const int* __restrict__ bidx,
                                                         const int* __restrict__ og, int G, int T,
@@ -135,9 +137,8 @@ __global__ void __launch_bounds__(128) msm_table_kernel(const long long* __restr
   if (i >= (long long)G * P) return;
   const int g = (int)(i / P), p = (int)(i % P);
   const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
-  int64_t s[MSM_TMAX];
-  for (int t = 0; t < T; t++) s[t] = row[t];
-  out[(size_t)p * ostride_p + (og ? og[g] : g)] = g1_table_msm<MSM_TMAX>(table, bidx[g], s, T, w, nw);
+  // scalars are read in place (twice: range check, then digits) rather than staged in registers
+  out[(size_t)p * ostride_p + (og ? og[g] : g)] = g1_table_msm<MSM_TMAX>(table, bidx[g], (const int64_t*)row, T, w, nw);
 }
 
 // Fixed-base comb for full-width scalars: out[i] = k_i * B with B's window table (w bits, nw windows,
@@ -294,7 +295,7 @@ int bsc_msm_groups(const long long* Q, int ldq, const int* sel, int P, const int
 }
 
 int bsc_msm_table_build(const void* bases_affine, long long nb, int w, int nw, void* out_jac, void* stream) {
-  if (w < 2 || w > 12 || nw < 1) return -1;
+  if (w < 2 || w > 14 || nw < 1) return -1;
   const long long n = nb * nw;
   if (n == 0) return 0;
   msm_table_build_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)bases_affine,
@@ -322,8 +323,14 @@ int bsc_msm_table(const long long* Q, int ldq, const int* sel, int P, const int*
   if (T > MSM_TMAX) return -1;
   const long long n = (long long)G * P;
   if (n == 0) return 0;
-  msm_table_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-      Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+  static const int minb = getenv("BSC_MSM_MINB") ? atoi(getenv("BSC_MSM_MINB")) : 4;
+  const unsigned grid = (unsigned)((n + 127) / 128);
+  if (minb >= 8)
+    msm_table_kernel<8><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+  else if (minb >= 6)
+    msm_table_kernel<6><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+  else
+    msm_table_kernel<4><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
   return finish_launch("msm_table");
 }
 void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx,

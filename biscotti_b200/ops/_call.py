@@ -19,7 +19,18 @@ def ptr(t):
     return ctypes.c_void_p(t.data_ptr())
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream(device=None):
+    """Raw handle of the current CUDA stream of `device` (the C entry points take it as void*)."""
+    if _raw_stream is not None:
+        if isinstance(device, str):
+            device = torch.device(device)
+        idx = device.index if isinstance(device, torch.device) else device
+        if idx is None:
+            idx = torch.cuda.current_device()
+        return ctypes.c_void_p(_raw_stream(idx))     # one C call, no Stream object
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 

@@ -11,6 +11,7 @@ the ledger.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -62,6 +63,12 @@ class CommitmentEngine:
         def table_bytes(w):
             return nbases * (-(-(max_scalar_bits + 1) // w)) * (1 << (w - 1)) * 64
 
+        env_gb = os.environ.get("BISCOTTI_MSM_TABLE_GB")
+        if env_gb:
+            table_budget_bytes = int(float(env_gb) * (1 << 30))
+        env_w = os.environ.get("BISCOTTI_MSM_WINDOW")
+        if env_w and window is None:
+            window = int(env_w)
         if window is None:
             # fewest windows (= additions per term) whose tables fit the budget: 11 bits -> 2 windows,
             # 7 -> 3, 6 -> 4, ...  (MNIST-sized models take w = 11: ~20 GB of HBM buys 18 instead of 27

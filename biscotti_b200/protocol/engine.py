@@ -19,8 +19,10 @@ flow from the same block hash, so the ledger is replicated without gossip.
 """
 from __future__ import annotations
 
+import contextlib
 import hashlib
 import math
+import random
 import time
 from dataclasses import dataclass, field
 
@@ -81,6 +83,8 @@ class BiscottiEngine:
         self.stake = [DEFAULT_STAKE] * n
         self.alive = [True] * n
         self.iteration = 0
+        self._pre = None          # prefetched (Q, chunkC, fullC) of the next iteration, see _prefetch_next
+        self._next_inputs, self._fed_inputs = None, False
         self.keys = cp.derive_peer_keys(n, cfg.seed)
         self.poisoners = poisoner_ids(cfg)
         self.colluder_ids = set(range(n - cfg.colluders, n)) if cfg.colluders > 0 else set()
@@ -121,9 +125,9 @@ class BiscottiEngine:
     def _arrival_order(self, ids: list[int], tag: str) -> list[int]:
         """Deterministic stand-in for network arrival order, identical on every rank."""
         h = hashlib.sha256(f"{self.cfg.seed}-{self.iteration}-{tag}".encode()).digest()
-        rs = np.random.RandomState(int.from_bytes(h[:4], "little"))
-        perm = rs.permutation(len(ids))
-        return [ids[i] for i in perm]
+        out = list(ids)
+        random.Random(int.from_bytes(h[:8], "little")).shuffle(out)   # Mersenne twister: same order on every rank
+        return out
 
     def _phase(self, name: str):
         return _Phase(self, name)
@@ -154,25 +158,74 @@ class BiscottiEngine:
         verifiers = sorted(verifiers)  # getRoleNames sorts verifiers (main.go:529-565)
         return verifiers, miners, h
 
-    def sample_minibatch(self, n_local: int):
+    def sample_minibatch(self, n_local: int, it: int | None = None):
         """Random minibatch without replacement per peer (logistic_model.py:121-125, DataLoader shuffle)."""
         Ns, B = self.cfg.shard_size, self.cfg.batch_size
         n = self.cfg.num_nodes
+        it = self.iteration if it is None else it
         # One seeded draw for ALL n peers (so the result does not depend on how peers are sharded over
         # ranks), generated on the engine's device; each rank keeps the rows of its own peers.
         if not hasattr(self, "_mb_gen"):
             self._mb_gen = torch.Generator(device=self.device)
-        self._mb_gen.manual_seed((self.cfg.seed * 1000003 + self.iteration * 7919) % (2**62))
+        self._mb_gen.manual_seed((self.cfg.seed * 1000003 + it * 7919) % (2**62))
         keys = torch.rand(n, Ns, generator=self._mb_gen, device=self.device)
         idx = keys.topk(B, dim=1, largest=False).indices.int()
         lo = self.local_ids[0] if self.local_ids else 0
         return idx[lo: lo + max(1, self.P)].contiguous()
 
     # ------------------------------------------------------------------------------------------
-    def step(self, inputs=None) -> BlockReport:
-        """Run one block iteration.  `inputs` = (X [P,B,F], y [P,B]) device tensors when the caller feeds
-        minibatches (bench end-to-end path); otherwise minibatches are drawn from the resident shards."""
+    def _local_and_commit(self, inputs, it: int, timed: bool):
+        """Local SGD step of every local peer from the current global weights, then quantisation and the
+        polynomial commitments of the update (phases 2 and 3 of an iteration).  Returns (Q, chunkC, fullC)."""
+        cfg, dev = self.cfg, self.device
+        slot = it % NOISE_TABLE_ITERS
+        phase = self._phase if timed else (lambda name: contextlib.nullcontext())
+        with phase("local_step"):
+            if inputs is not None:
+                X, y = inputs
+                idx = None
+            else:
+                X, y = self.data.X, self.data.y
+                idx = self.sample_minibatch(self.P, it).to(dev)
+            if self.P:
+                pid = self.data.peer_ids if not self.external_inputs else torch.tensor(self.local_ids, dtype=torch.int32, device=dev)
+                self.model.local_step(self.w32, X, y, idx, self.U, peer_ids=pid, slot=slot)
+        Q = chunkC = fullC_dev = None
+        if self.commit is not None and self.P:
+            with phase("commit"):
+                Q = secagg.quantize(self.U, self.d, cfg.precision)
+                chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
+                # full-vector commitments stay Jacobian on the device; the rows that enter the block are
+                # normalised on the host with one shared inversion when the block is assembled
+                fullC_dev = self.commit.full_commitments(chunkC, jacobian=True).view(torch.uint8)   # [P, 96]
+        return Q, chunkC, fullC_dev
+
+    def _prefetch_next(self, it_next: int):
+        """Queue the next iteration's local step and commitment MSM behind this iteration's aggregation kernel.
+        They read only the new global weights (already updated in stream order) and the resident shards, so the
+        device works on them while the host assembles, signs and hashes the current block.  The reference has no
+        such overlap (phases are strictly sequential); the values are identical either way."""
         cfg = self.cfg
+        if not cfg.prefetch or not cfg.secure_agg or cfg.mode == "fedsys":
+            return   # the plain path still reads U when the block is assembled
+        nxt = self._next_inputs
+        if nxt is None and (self._fed_inputs or self.external_inputs):
+            return   # minibatches come from the caller and the next one has not been handed over
+        if nxt is not None and len(nxt) == 3:      # (X, y, event): the H2D copy was issued on another stream
+            torch.cuda.current_stream(self.device).wait_event(nxt[2])
+            nxt = (nxt[0], nxt[1])
+        Q, chunkC, fullC = self._local_and_commit(nxt, it_next, timed=False)
+        self._pre = {"it": it_next, "Q": Q, "chunkC": chunkC, "fullC": fullC,
+                     "src": None if nxt is None else nxt[0].data_ptr()}
+
+    def step(self, inputs=None, next_inputs=None) -> BlockReport:
+        """Run one block iteration.  `inputs` = (X [P,B,F], y [P,B]) device tensors when the caller feeds
+        minibatches (bench end-to-end path); otherwise minibatches are drawn from the resident shards.
+        `next_inputs` = the following call's `inputs` (optionally with a CUDA event that marks their H2D copy
+        complete), if the caller already has them: a double-buffered input pipeline lets the engine start the
+        next local step while this block is being assembled."""
+        cfg = self.cfg
+        self._next_inputs, self._fed_inputs = next_inputs, inputs is not None
         if cfg.mode == "fedsys":
             from .fedsys import fedsys_step
 
@@ -201,30 +254,18 @@ class BiscottiEngine:
         use_noise = cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0
         vrf_handle = self.vrf.launch(prev_hash) if use_noise else None
 
-        # ---- 2. local step for my workers (all local rows are computed; non-workers are ignored)
-        with self._phase("local_step"):
-            if inputs is not None:
-                X, y = inputs
-                idx = None
-            else:
-                X, y = self.data.X, self.data.y
-                idx = self.sample_minibatch(self.P).to(dev)
-            if self.P:
-                pid = self.data.peer_ids if not self.external_inputs else torch.tensor(self.local_ids, dtype=torch.int32, device=dev)
-                self.model.local_step(self.w32, X, y, idx, self.U, peer_ids=pid, slot=slot)
+        # ---- 2/3. local step + commitments of my peers.  Neither depends on the roles or on the block hash, so
+        # the previous step may already have queued them behind its aggregation kernel (see _prefetch_next).
+        pre, self._pre = self._pre, None
+        if pre is not None and pre["it"] == it and pre["src"] == (None if inputs is None else inputs[0].data_ptr()):
+            Q, chunkC, fullC_dev = pre["Q"], pre["chunkC"], pre["fullC"]
+        else:
+            Q, chunkC, fullC_dev = self._local_and_commit(inputs, it, timed=True)
 
-        # ---- 3. commitments (local peers)
-        Q = None
-        chunkC = None
-        fullC_bytes = {}
-        if self.commit is not None and self.P:
-            with self._phase("commit"):
-                Q = secagg.quantize(self.U, self.d, cfg.precision)
-                chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
-                # full-vector commitments stay Jacobian on the device; the rows that enter the block are
-                # normalised on the host with one shared inversion when the block is assembled
-                fullC_dev = self.commit.full_commitments(chunkC, jacobian=True).view(torch.uint8)   # [P, 96]
-
+        # host-side bookkeeping that does not need the VRF outputs goes first: the noise phase below waits for them
+        arrival = self._arrival_order(workers, "verify")
+        krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh, sorted by id
+        rep.n_krum = len(krum_set)
         # ---- 4. noisers + noise
         with self._phase("noise"):
             noiser_tab = torch.full((max(1, self.P), max(1, cfg.num_noisers)), -1, dtype=torch.int32)
@@ -250,9 +291,6 @@ class BiscottiEngine:
                                              out_lo=self.comm.lo if self.fused else None)
 
         # ---- 5. verification
-        arrival = self._arrival_order(workers, "verify")
-        krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh, sorted by id
-        rep.n_krum = len(krum_set)
         accepted: list[int] = []
         with self._phase("verify"):
             if not cfg.verification:
@@ -284,16 +322,6 @@ class BiscottiEngine:
         if not enough:
             return self._finish_block(rep, [], None, phases, t0)   # main.go:2099-2117
         rep.n_contributors = len(contributors)
-        # approvals: every verifier signs the commitment of each update it accepted (krum.go:338-358).  The
-        # T = v*G halves of the signatures run on the GPU now, overlapped with the witness MSM; they are
-        # completed on the host when the block is assembled.  Signatures are produced for the updates that
-        # end up in the block (the contributors).
-        sig_handle = None
-        if self.signer is not None and self.commit is not None:
-            import struct
-
-            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in contributors for v in signers],
-                                            [struct.pack("<qii", it, p, v) for p in contributors for v in signers])
         local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
         sel = self._idx(local_contrib)
         agg_commit = None
@@ -339,6 +367,17 @@ class BiscottiEngine:
                     secagg.plain_sum_step(self.U, sel, self.d, self.w64, self.w32)
                 bad = torch.zeros(2, dtype=torch.int32, device=dev)
 
+        # approvals: every verifier signs the commitment of each update it accepted (krum.go:338-358).  The
+        # T = v*G halves of the signatures run on the GPU (side stream); their host-side preparation happens here,
+        # after the witness / aggregation kernels have been queued, so it overlaps them.  The signatures are
+        # completed on the host when the block is assembled, for the updates that end up in the block.
+        sig_handle = None
+        if self.signer is not None and self.commit is not None:
+            import struct
+
+            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in contributors for v in signers],
+                                            [struct.pack("<qii", it, p, v) for p in contributors for v in signers])
+
         # ---- 9. block assembly (host).  Evaluation of the new weights is launched first so that one
         # device->host collection (weights, commitments, share-check counters, error rates) and one stream
         # synchronisation serve the whole tail of the block.
@@ -359,7 +398,7 @@ class BiscottiEngine:
             if sig_handle is not None and sig_handle["T_dev"] is not None:
                 torch.cuda.current_stream(dev).wait_event(sig_handle["event"])
                 want["sigT"] = sig_handle["T_dev"]
-            host = self._collect(want)
+            host = self._collect(want, before_sync=lambda: self._prefetch_next(it + 1))
             if "cb" in host:
                 cb = host["cb"]
                 cbj = cb.view(np.int32).reshape(cb.shape[0], 24)
@@ -442,10 +481,15 @@ class BiscottiEngine:
         ar = self.model.eval_errors(w, None, self.data.X_attack, self.data.y_attack)
         return te, ar
 
-    def _collect(self, tensors: dict) -> dict:
-        """Device tensors -> numpy, through persistent pinned buffers, with a single stream synchronisation."""
+    def _collect(self, tensors: dict, before_sync=None) -> dict:
+        """Device tensors -> numpy, through persistent pinned buffers, with a single synchronisation.  `before_sync`
+        runs after the copies are queued and before the host waits for them: work it launches sits behind the
+        copies in the stream and is not waited for."""
         if self.device.type != "cuda":
-            return {k: v.detach().cpu().numpy() for k, v in tensors.items()}
+            out = {k: v.detach().cpu().numpy().copy() for k, v in tensors.items()}
+            if before_sync is not None:
+                before_sync()
+            return out
         if not hasattr(self, "_pinned"):
             self._pinned = {}
         out = {}
@@ -457,7 +501,14 @@ class BiscottiEngine:
                 self._pinned[key] = buf
             buf.copy_(v, non_blocking=True)
             out[k] = buf
-        torch.cuda.current_stream(self.device).synchronize()
+        if before_sync is None:
+            torch.cuda.current_stream(self.device).synchronize()
+        else:
+            if not hasattr(self, "_collect_ev"):
+                self._collect_ev = torch.cuda.Event()
+            self._collect_ev.record()
+            before_sync()
+            self._collect_ev.synchronize()
         return {k: b.numpy() for k, b in out.items()}
 
     def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0, host=None) -> BlockReport:
@@ -499,6 +550,7 @@ class BiscottiEngine:
     def adopt_chain(self, serialized: bytes) -> bool:
         other = Blockchain.deserialize(serialized)
         if len(other) > len(self.chain) and other.verify():
+            self._pre = None
             self.chain = other
             self.iteration = other.latest_iteration + 1
             w = torch.from_numpy(other.weights()).to(self.device)

@@ -130,6 +130,25 @@ def test_restart_from_saved_ledger_reproduces_uninterrupted_run(tmp_path):
     assert second.stake == straight.stake
 
 
+def test_prefetched_local_step_gives_the_same_chain():
+    """Queuing iteration t+1's local step + commitments behind iteration t's aggregation (engine._prefetch_next)
+    is a scheduling change only: the ledger is identical with and without it, also when minibatches are fed by the
+    caller through `inputs` / `next_inputs`."""
+    a = BiscottiEngine(_cfg(max_iterations=6, prefetch=True))
+    b = BiscottiEngine(_cfg(max_iterations=6, prefetch=False))
+    a.run()
+    b.run()
+    assert a.chain == b.chain
+    c = BiscottiEngine(_cfg(max_iterations=6, prefetch=True))
+    d = BiscottiEngine(_cfg(max_iterations=6, prefetch=False))
+    B = c.cfg.batch_size
+    feeds = [(c.data.X[:, i:i + B].contiguous(), c.data.y[:, i:i + B].contiguous()) for i in range(8)]
+    for i in range(7):
+        c.step(feeds[i], next_inputs=feeds[i + 1])
+        d.step(feeds[i])
+    assert c.chain == d.chain and c._pre is not None
+
+
 def test_localtest_cli_two_ranks_gloo_chain_equality():
     """localTest.sh parity: N peers sharded over 2 processes (gloo); every rank must print the same chain,
     and it must equal the single-process chain."""
