@@ -150,6 +150,7 @@ class BatchedVRF:
                                               n, ctypes.c_void_p(gam.data_ptr()))
             return (gam, None, msg)
         if not hasattr(self, "_side"):
+            torch.cuda.current_stream(self.device).synchronize()   # once: the scalars' upload has landed
             self._side = torch.cuda.Stream(self.device)
             self._host_gam = torch.empty(n, 32, dtype=torch.uint8).pin_memory()
             self._hpt_pinned = torch.empty(64, dtype=torch.uint8).pin_memory()
@@ -158,7 +159,8 @@ class BatchedVRF:
             self._xyz = torch.empty(n, 30, dtype=torch.int32, device=self.device)
             self._host_xyz = torch.empty(n, 30, dtype=torch.int32).pin_memory()
         self._hpt_pinned.copy_(hxy)
-        self._side.wait_stream(torch.cuda.current_stream(self.device))
+        # No wait on the compute stream: the kernel reads only the static secret scalars and the point copied here,
+        # so it may run beside whatever the main stream still has queued (the prefetched local step / commitment MSM).
         with torch.cuda.stream(self._side):
             self._hd.copy_(self._hpt_pinned, non_blocking=True)
             if self.kernel == "quad":

@@ -60,13 +60,15 @@ class SchnorrBatchSigner:
         if self.device.type == "cuda" and n:
             self._ensure_table()
             if not hasattr(self, "_side"):
+                torch.cuda.current_stream(self.device).synchronize()   # once: the comb table build has finished
                 self._side = torch.cuda.Stream(self.device)
                 self._k_pinned = torch.empty(4096, 8, dtype=torch.int32).pin_memory()
             main = torch.cuda.current_stream(self.device)
             kp = self._k_pinned[:n] if n <= self._k_pinned.shape[0] else torch.empty(n, 8, dtype=torch.int32).pin_memory()
             kp.copy_(torch.from_numpy(vw.view(np.int32)[:n]))
-            # side stream: the comb kernel is a single small CTA-wave and runs under the witness MSM
-            self._side.wait_stream(main)
+            # side stream: the comb kernel is a single small CTA-wave and runs under the witness MSM.  It does not
+            # wait for the compute stream (its inputs are the nonces uploaded here and the static comb table), so
+            # it starts at once even though the witness / aggregation kernels were queued first.
             with torch.cuda.stream(self._side):
                 stream = ctypes.c_void_p(self._side.cuda_stream)
                 k = kp.to(self.device, non_blocking=True)
