@@ -90,6 +90,8 @@ def main():
     ap.add_argument("--comm", default=None, help="fused | nccl (default: fused when available)")
     ap.add_argument("--gram", default="auto")
     ap.add_argument("--profile-phases", action="store_true")
+    ap.add_argument("--e2e-pipeline", type=int, default=0,
+                    help="1: double-buffered H2D + next_inputs; 0: copy then step (default: measured 388 vs 381 blocks/s)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -171,19 +173,40 @@ def main():
     # draw host minibatches from the same synthetic distribution as the shards
     hostX.copy_(eng.data.X[:, :B].cpu()) if P else None
     hosty.copy_(eng.data.y[:, :B].cpu()) if P else None
-    # Inputs are copied from pinned host memory at the start of every step.  (The engine also accepts the next step's
-    # minibatch as `next_inputs` for a double-buffered pipeline; measured here it did not pay: 365 vs 378 blocks/s.)
-    dX = torch.empty_like(hostX, device=dev)
-    dy = torch.empty_like(hosty, device=dev)
+    # Optional double-buffered input pipeline (--e2e-pipeline 1): while step i runs, step i+1's minibatch is copied from pinned
+    # host memory on a copy stream and handed to the engine as `next_inputs`, which lets it queue that step's local
+    # pass behind this step's aggregation.  Every step's H2D copy is inside the timed region either way.
+    bufs = [(torch.empty_like(hostX, device=dev), torch.empty_like(hosty, device=dev)) for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device=dev)
     res_host = torch.empty(2, dtype=torch.float32).pin_memory()
 
+    def h2d(slot):
+        ev = torch.cuda.Event()
+        with torch.cuda.stream(copy_stream):             # slot's previous reader finished a full step ago
+            bufs[slot][0].copy_(hostX, non_blocking=True)
+            bufs[slot][1].copy_(hosty, non_blocking=True)
+            ev.record()
+        return (bufs[slot][0], bufs[slot][1], ev)
+
     def run_e2e(nsteps):
-        for _ in range(nsteps):
-            dX.copy_(hostX, non_blocking=True)               # H2D of this step's inputs
-            dy.copy_(hosty, non_blocking=True)
-            rep = eng.step((dX, dy))
+        if not args.e2e_pipeline:
+            dX, dy = bufs[0]
+            for _ in range(nsteps):
+                dX.copy_(hostX, non_blocking=True)               # H2D of this step's inputs
+                dy.copy_(hosty, non_blocking=True)
+                rep = eng.step((dX, dy))
+                res = torch.tensor([rep.test_error or 0.0, rep.attack_rate or 0.0], device=dev)
+                res_host.copy_(res, non_blocking=False)          # D2H of the step's result
+            return
+        torch.cuda.current_stream(dev).synchronize()
+        cur = h2d(0)
+        torch.cuda.current_stream(dev).wait_event(cur[2])
+        for i in range(nsteps):
+            nxt = h2d((i + 1) % 2)                               # H2D of the next step's inputs (one copy per step)
+            rep = eng.step((cur[0], cur[1]), next_inputs=nxt)
             res = torch.tensor([rep.test_error or 0.0, rep.attack_rate or 0.0], device=dev)
-            res_host.copy_(res, non_blocking=False)          # D2H of the step's result
+            res_host.copy_(res, non_blocking=False)              # D2H of the step's result
+            cur = nxt
 
     run_e2e(2)
     barrier()
