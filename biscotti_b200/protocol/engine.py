@@ -85,6 +85,7 @@ class BiscottiEngine:
         self.iteration = 0
         self._pre = None          # prefetched (Q, chunkC, fullC) of the next iteration, see _prefetch_next
         self._next_inputs, self._fed_inputs = None, False
+        self._eval_pending = None
         self.keys = cp.derive_peer_keys(n, cfg.seed)
         self.poisoners = poisoner_ids(cfg)
         self.colluder_ids = set(range(n - cfg.colluders, n)) if cfg.colluders > 0 else set()
@@ -385,9 +386,7 @@ class BiscottiEngine:
             updates = []
             commits = {}
             want = {"w": self.w64, "bad": bad}
-            if cfg.eval_every and (it % cfg.eval_every == 0):
-                te, ar = self.evaluate()
-                want["te"], want["ar"] = te, ar
+            do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
             gathered = False
             if self.commit is not None and self.P:
                 if self.comm is not None and hasattr(self.comm, "all_gather_rows_u8"):
@@ -398,7 +397,14 @@ class BiscottiEngine:
             if sig_handle is not None and sig_handle["T_dev"] is not None:
                 torch.cuda.current_stream(dev).wait_event(sig_handle["event"])
                 want["sigT"] = sig_handle["T_dev"]
-            host = self._collect(want, before_sync=lambda: self._prefetch_next(it + 1))
+            # Evaluation of the new weights is not part of the block: it is queued behind the collection (with the
+            # next iteration's prefetch) and read back after the block has been assembled and hashed.
+            def after_copies():
+                if do_eval:
+                    self._launch_eval()
+                self._prefetch_next(it + 1)
+
+            host = self._collect(want, before_sync=after_copies)
             if "cb" in host:
                 cb = host["cb"]
                 cbj = cb.view(np.int32).reshape(cb.shape[0], 24)
@@ -481,6 +487,20 @@ class BiscottiEngine:
         ar = self.model.eval_errors(w, None, self.data.X_attack, self.data.y_attack)
         return te, ar
 
+    def _launch_eval(self):
+        """Queue the error-rate kernels and their read-back; _finish_block picks the numbers up."""
+        te, ar = self.evaluate()
+        if self.device.type != "cuda":
+            self._eval_pending = (te.detach().cpu(), ar.detach().cpu(), None)
+            return
+        if not hasattr(self, "_eval_pinned"):
+            self._eval_pinned = (torch.empty_like(te, device="cpu").pin_memory(), torch.empty_like(ar, device="cpu").pin_memory())
+            self._eval_ev = torch.cuda.Event()
+        self._eval_pinned[0].copy_(te, non_blocking=True)
+        self._eval_pinned[1].copy_(ar, non_blocking=True)
+        self._eval_ev.record()
+        self._eval_pending = (self._eval_pinned[0], self._eval_pinned[1], self._eval_ev)
+
     def _collect(self, tensors: dict, before_sync=None) -> dict:
         """Device tensors -> numpy, through persistent pinned buffers, with a single synchronisation.  `before_sync`
         runs after the copies are queued and before the host waits for them: work it launches sits behind the
@@ -523,6 +543,11 @@ class BiscottiEngine:
             ts = (0 if not updates else 1 + it) if cfg.deterministic_time else -1
             rep.block_hash = self.chain.add_block(it, host["w"], updates, self.stake, timestamp=ts)
             rep.empty = not updates
+        pend, self._eval_pending = self._eval_pending, None
+        if pend is not None:
+            if pend[2] is not None:
+                pend[2].synchronize()
+            host = dict(host, te=pend[0].numpy(), ar=pend[1].numpy())
         if "te" in host:
             rep.test_error, rep.attack_rate = float(host["te"][0]), float(host["ar"][0])
             self.log.train_error(it, rep.test_error)
