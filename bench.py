@@ -33,7 +33,7 @@ def reference_arm(args):
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
-    def __init__(self, index: int, period: float = 0.2):
+    def __init__(self, index: int, period: float = 0.025):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
