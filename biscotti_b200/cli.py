@@ -47,6 +47,7 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--no-dump", action="store_true")
     ap.add_argument("--log", action="store_true", help="emit [peer] log lines on stderr")
     ap.add_argument("--save-chain", default=None)
+    ap.add_argument("--data-dir", default=None, help="directory of <dataset><i>.npy shard files (default: synthetic data)")
     ap.add_argument("--resume", default=None, help="chain file to adopt before running (restart / rejoin, main.go:1000-1013)")
 
 
@@ -57,7 +58,7 @@ def config_from_args(a, mode: str):
     kw = dict(num_nodes=a.num_nodes, dataset=a.dataset, num_miners=a.na, num_verifiers=a.nv, num_noisers=a.nn,
               secure_agg=a.sa, noising=a.np, verification=a.vp, epsilon=a.ep, poison_fraction=a.po, perc_samples=ns,
               random_sampling=a.rs, colluders=a.c, defense=a.defense, max_iterations=a.iterations, seed=a.seed,
-              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm)
+              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm, data_dir=a.data_dir)
     if a.shard_size:
         kw["shard_size"] = a.shard_size
     return BiscottiConfig(**kw)
@@ -200,6 +201,33 @@ def run_experiment(a) -> int:
     return 0
 
 
+def run_make_shards(a) -> int:
+    """parse_mnist.py / parse_cifar.py / lfw parsers: [n, F+1] row files -> per-peer shards, test, attack and poisoned
+    sets in the layout data/files.py reads.  Without --train the rows are drawn from the synthetic generator, which
+    gives a self-contained way to exercise the file-backed path."""
+    import numpy as np
+
+    from .config import BiscottiConfig, DATASETS
+    from .data.files import write_shards
+
+    spec = DATASETS[a.dataset]
+    if a.train:
+        tr, te = np.load(a.train), np.load(a.test or a.train)
+        X, y, Xt, yt = tr[:, :-1], tr[:, -1], te[:, :-1], te[:, -1]
+    else:
+        from .data.synthetic import make_data
+
+        cfg = BiscottiConfig(num_nodes=a.n, dataset=a.dataset, seed=a.seed)
+        d = make_data(cfg, list(range(a.n)), "cpu")
+        X = d.X.reshape(-1, spec.n_features).numpy()
+        y = d.y.reshape(-1).numpy().astype(np.float64)
+        Xt, yt = d.X_test.numpy(), d.y_test.numpy().astype(np.float64)
+    files = write_shards(a.out, a.dataset, X, y, Xt, yt, a.n, source=a.source, target=a.target,
+                         standardize=not a.no_standardize, seed=a.seed)
+    print(f"wrote {len(files)} files to {a.out} ({a.n} shards of {a.dataset})")
+    return 0
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="biscotti_b200", add_help=True)
     sub = ap.add_subparsers(dest="cmd", required=True)
@@ -215,6 +243,16 @@ def main(argv=None) -> int:
     kg.add_argument("--out", default="keys")
     kg.add_argument("--seed", type=int, default=1)
     kg.add_argument("--tau", type=int, default=2)
+    ms = sub.add_parser("make-shards")
+    ms.add_argument("dataset")
+    ms.add_argument("-n", type=int, default=100, help="number of peer shards")
+    ms.add_argument("--train", default=None, help=".npy with rows features||label (default: synthetic rows)")
+    ms.add_argument("--test", default=None)
+    ms.add_argument("--out", default="data")
+    ms.add_argument("--source", type=int, default=1)
+    ms.add_argument("--target", type=int, default=7)
+    ms.add_argument("--no-standardize", action="store_true")
+    ms.add_argument("--seed", type=int, default=1)
     sub.add_parser("vrf-demo")
     sub.add_parser("kzg-demo")
     exp = sub.add_parser("experiment")
@@ -234,6 +272,8 @@ def main(argv=None) -> int:
         return run_localtest(a, "fedsys")
     if a.cmd == "keygen":
         return run_keygen(a)
+    if a.cmd == "make-shards":
+        return run_make_shards(a)
     return run_vrf_demo(a)
 
 

@@ -44,6 +44,10 @@ def poisoner_ids(cfg: BiscottiConfig) -> set[int]:
 
 
 def make_data(cfg: BiscottiConfig, peer_ids: list[int], device="cpu", noise: float = 1.0, sep: float = 6.0) -> PeerData:
+    if getattr(cfg, "data_dir", None):
+        from .files import load_peer_data      # real shard files in the reference's layout
+
+        return load_peer_data(cfg, peer_ids, cfg.data_dir, device)
     spec = DATASETS[cfg.dataset]
     F, C = spec.n_features, spec.n_classes
     logistic = spec.model == "logistic"

@@ -51,3 +51,36 @@ def train_test_split(rows, train_cut: float = 0.8):
     """*_dataset.py: first 80 % of each shard file trains, the rest validates."""
     cut = int(rows.shape[0] * train_cut)
     return rows[:cut], rows[cut:]
+
+
+def laplace_noise(shape, scale: float, seed: int = 0):
+    """utils.py lap_noise: Laplace(0, scale) samples (the reference's alternative DP mechanism)."""
+    return np.random.RandomState(seed).laplace(0.0, scale, size=shape)
+
+
+def exp_noise(shape, scale: float, seed: int = 0):
+    """utils.py exp_noise: Exponential(scale) samples."""
+    return np.random.RandomState(seed).exponential(scale, size=shape)
+
+
+def approx_fprime(w, f, eps: float = 1e-7):
+    """utils.py:273-311 — numerical gradient for checking a model's funObj.  The reference perturbs along the
+    imaginary axis (complex step); objectives here are real-valued torch/numpy code, so central differences are
+    used instead: g_i = (f(w + eps e_i) - f(w - eps e_i)) / (2 eps)."""
+    w = np.asarray(w, dtype=np.float64)
+    g = np.zeros_like(w)
+    for i in range(w.size):
+        e = np.zeros_like(w)
+        e.flat[i] = eps
+        g.flat[i] = (f(w + e) - f(w - e)) / (2 * eps)
+    return g
+
+
+def check_gradient(f_and_g, w, tol: float = 1e-5) -> float:
+    """utils.py check_gradient: max abs difference between the analytic and the numerical gradient."""
+    _, g = f_and_g(w)
+    num = approx_fprime(w, lambda v: f_and_g(v)[0])
+    err = float(np.max(np.abs(np.asarray(g) - num)))
+    if err > tol:
+        raise AssertionError(f"gradient check failed: max abs error {err:.3e}")
+    return err

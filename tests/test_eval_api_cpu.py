@@ -69,3 +69,71 @@ def test_churn_rejoin_and_data_utils_and_extras():
     assert int((d != 0).sum()) == 2
     g = extras.svm_step(torch.zeros(4 * 6 + 4), torch.randn(10, 6), torch.randint(0, 4, (10,)), 4)
     assert g.shape == (28,)
+
+
+def test_file_backed_shards_round_trip(tmp_path):
+    """make-shards layout (parse_mnist.py) -> load_peer_data -> an engine run from files."""
+    import numpy as np
+
+    from biscotti_b200.config import BiscottiConfig
+    from biscotti_b200.data.files import load_peer_data, load_rows, write_shards
+    from biscotti_b200.protocol.engine import BiscottiEngine
+
+    rs = np.random.RandomState(0)
+    n, F = 400, 784
+    y = rs.randint(0, 10, size=n).astype(np.float64)
+    X = rs.randn(n, F) + y[:, None] * 0.3
+    files = write_shards(str(tmp_path), "mnist", X, y, X[:100], y[:100], n_shards=4)
+    names = {f.split("/")[-1] for f in files}
+    assert {"mnist0.npy", "mnist3.npy", "mnist_train.npy", "mnist_test.npy", "mnist_digit1.npy", "mnist_bad.npy"} <= names
+    Xb, yb = load_rows(str(tmp_path / "mnist_bad"), is_train=False, train_cut=0.0)
+    assert not (yb == 1).any() and (yb == 7).sum() >= (y == 7).sum()          # every 1 relabelled 7
+    Xtr, ytr = load_rows(str(tmp_path / "mnist0"))
+    assert Xtr.shape == (80, F)                                               # first 80 % of a 100-row shard
+    cfg = BiscottiConfig(num_nodes=4, dataset="mnist", shard_size=80, poison_fraction=0.3, data_dir=str(tmp_path),
+                         max_iterations=2, commitments=False, num_verifiers=1, num_miners=1, num_noisers=1)
+    d = load_peer_data(cfg, [0, 1, 2, 3], str(tmp_path))
+    assert d.X.shape == (4, 80, F) and bool(d.poisoned[3]) and not bool(d.poisoned[0])
+    assert not (d.y[3] == 1).any()                                            # the poisoner reads mnist_bad
+    eng = BiscottiEngine(cfg)
+    eng.run()
+    assert len(eng.chain) == 4 and eng.chain.verify()
+
+
+def test_ml_sandboxes_and_lsh_sieve():
+    import torch
+
+    from biscotti_b200.sim import ml_main
+
+    rows = ml_main.run_clients("creditcard", honest=6, poisoners=0, rounds=12, defense="none", log_every=11)
+    assert rows[-1]["test_error"] < rows[0]["test_error"] + 0.05 and rows[-1]["accepted"] == 6
+    kr = ml_main.run_clients("mnist", honest=6, poisoners=4, rounds=3, defense="krum", log_every=1)
+    assert all(r["accepted"] == 6 for r in kr)                                # n - clip survive Multi-Krum
+    leak = ml_main.gradient_leak("mnist", batches=(1, 10), epsilons=(0.0,))
+    assert leak[0]["leak_cosine"] > 0.999 and leak[1]["leak_cosine"] < leak[0]["leak_cosine"]
+    g = torch.Generator().manual_seed(0)
+    base = torch.randn(1, 64, generator=g)
+    deltas = torch.cat([base + 0.05 * torch.randn(8, 64, generator=g), -base + 0.05 * torch.randn(2, 64, generator=g)])
+    keep = ml_main.lsh_sieve(deltas, keep_fraction=0.8)
+    assert set(keep.tolist()) == set(range(8))                                # the two outliers are sieved out
+
+
+def test_gradient_check_and_noise_utils():
+    import numpy as np
+
+    from biscotti_b200.data.utils import check_gradient, exp_noise, laplace_noise
+
+    A = np.random.RandomState(1).randn(5, 5)
+    A = A @ A.T
+
+    def quad(w):
+        return 0.5 * float(w @ A @ w), A @ w
+
+    assert check_gradient(quad, np.arange(5.0)) < 1e-5
+    try:
+        check_gradient(lambda w: (float(w @ A @ w), A @ w), np.arange(5.0))   # wrong by a factor 2
+        raise RuntimeError("should have failed")
+    except AssertionError:
+        pass
+    assert abs(np.mean(np.abs(laplace_noise(20000, 2.0))) - 2.0) < 0.1
+    assert abs(np.mean(exp_noise(20000, 3.0)) - 3.0) < 0.15
