@@ -143,3 +143,27 @@ def test_lottery_matches_reference_rule():
 def test_role_ids_are_prime_products():
     r = cp.role_ids(6, [1, 2], [2, 3], [5])
     assert r == [1, 2, 6, 3, 1, 5]
+
+
+def test_p256_vrf_reading_copy_and_hmac_commitments():
+    """vrf-reference/: P-256 VRF evaluate / proof_to_hash round trip, rejection of tampering, HMAC commitments."""
+    from biscotti_b200.crypto import p256_vrf as V
+
+    assert V._mul(V.G, V.N) is None and (V.G[1] ** 2 - (V.G[0] ** 3 + V.A * V.G[0] + V.B)) % V.P == 0
+    key = V.P256VRFKey(b"\x07" * 32)
+    index, proof = key.evaluate(b"block-hash")
+    assert len(index) == 32 and len(proof) == 129
+    assert V.proof_to_hash(key.public, b"block-hash", proof) == index
+    assert key.evaluate(b"block-hash")[0] == index                       # a VRF is a function
+    assert V.proof_to_hash(key.public, b"other", proof) is None
+    other = V.P256VRFKey(b"\x08" * 32)
+    assert V.proof_to_hash(other.public, b"block-hash", proof) is None
+    bad = bytearray(proof)
+    bad[40] ^= 1
+    assert V.proof_to_hash(key.public, b"block-hash", bytes(bad)) is None
+    assert other.evaluate(b"block-hash")[0] != index
+    nonce = bytes(range(16))
+    c = V.commit("alice", "app", b"profile", nonce)
+    assert len(c) == 32 and V.verify_commitment("alice", "app", c, b"profile", nonce)
+    assert not V.verify_commitment("alice", "app", c, b"profile2", nonce)
+    assert not V.verify_commitment("alic", "eapp", c, b"profile", nonce)  # length-prefixed fields do not collide
