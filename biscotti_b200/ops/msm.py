@@ -30,7 +30,7 @@ class CommitmentEngine:
     """Holds the SRS and the witness base table for one model dimension and runs the MSM kernels."""
 
     def __init__(self, d: int, total_shares: int, tau: int = 2, device="cpu", srs_bytes: bytes | None = None,
-                 window: int | None = None, max_scalar_bits: int = 20, table_budget_bytes: int = 48 << 30):
+                 window: int | None = None, max_scalar_bits: int = 20, table_budget_bytes: int | None = None):
         self.d, self.S, self.device = d, total_shares, torch.device(device)
         self.nchunk = nchunks(d)
         self.dpad = self.nchunk * POLY_SIZE
@@ -63,6 +63,11 @@ class CommitmentEngine:
         def table_bytes(w):
             return nbases * (-(-(max_scalar_bits + 1) // w)) * (1 << (w - 1)) * 64
 
+        # HBM budget of the window tables: half of the device (90 GB of a B200's 180 GB) unless told otherwise
+        if table_budget_bytes is None:
+            table_budget_bytes = 48 << 30
+            if self.device.type == "cuda":
+                table_budget_bytes = torch.cuda.get_device_properties(self.device).total_memory // 2
         env_gb = os.environ.get("BISCOTTI_MSM_TABLE_GB")
         if env_gb:
             table_budget_bytes = int(float(env_gb) * (1 << 30))
@@ -70,12 +75,12 @@ class CommitmentEngine:
         if env_w and window is None:
             window = int(env_w)
         if window is None:
-            # fewest windows (= additions per term) whose tables fit the budget: 11 bits -> 2 windows,
-            # 7 -> 3, 6 -> 4, ...  (MNIST-sized models take w = 11: ~20 GB of HBM buys 18 instead of 27
-            # additions per witness; the CIFAR CNN lands on w = 6)
+            # fewest windows (= additions per term), then the widest such window, whose tables fit the budget:
+            # 12 or 11 bits -> 2 windows, 7 -> 3, 6 -> 4, ...  (MNIST-sized models take w = 12: 41 GB of HBM, 18
+            # instead of 27 additions per witness and mostly-zero high digits; the CIFAR CNN lands on w = 7, 64 GB)
             window = 0
             if self.device.type == "cuda":
-                window = next((w for w in (11, 7, 6, 5, 4, 3) if table_bytes(w) <= table_budget_bytes), 3)
+                window = next((w for w in (12, 11, 7, 6, 5, 4, 3) if table_bytes(w) <= table_budget_bytes), 3)
         if window:
             while window > 2 and table_bytes(window) > table_budget_bytes:
                 window -= 1

@@ -11,14 +11,17 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from biscotti_b200.config import BiscottiConfig  # noqa: E402
 from biscotti_b200.protocol.engine import BiscottiEngine  # noqa: E402
 
-cfg = BiscottiConfig(num_nodes=100, dataset="mnist", max_iterations=60)
+DATASET = os.environ.get("HP_DATASET", "mnist")
+PEERS = int(os.environ.get("HP_PEERS", "100"))
+STEPS = int(os.environ.get("HP_STEPS", "20"))
+cfg = BiscottiConfig(num_nodes=PEERS, dataset=DATASET, max_iterations=STEPS + 40)
 eng = BiscottiEngine(cfg, device="cuda:0")
 for _ in range(4):
     eng.step()
 torch.cuda.synchronize()
 pr = cProfile.Profile()
 pr.enable()
-for _ in range(20):
+for _ in range(STEPS):
     eng.step()
 torch.cuda.synchronize()
 pr.disable()
