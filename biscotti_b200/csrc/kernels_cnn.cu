@@ -345,22 +345,23 @@ __global__ void __launch_bounds__(256) cnn2_dgrad_kernel(const float* __restrict
     const int y = (int)((t / W) % H);
     const int ic = (int)((t / ((long long)W * H)) % IC);
     const long long img = t / ((long long)W * H * IC);
+    // conv outputs that read this input: oy in [y+pad-(K-1), y+pad]; they live in at most (K+1)/2+1 pooled rows.
+    // Each pooled cell carries one gradient at its arg-max position, so a cell costs one byte + one float load.
+    const int py0 = max(0, (y + pad - (K - 1)) >> 1), py1 = min(PH - 1, (y + pad) >> 1);
+    const int px0 = max(0, (x + pad - (K - 1)) >> 1), px1 = min(PW - 1, (x + pad) >> 1);
     float g = 0.f;
     for (int oc = 0; oc < OC; oc++) {
       const size_t base = ((size_t)img * OC + oc) * PH * PW;
       const float* wk = sw + (oc * IC + ic) * K * K;
-#pragma unroll
-      for (int ky = 0; ky < K; ky++) {
-        const int oy = y - ky + pad;
-        if (oy < 0 || (oy >> 1) >= PH) continue;
-#pragma unroll
-        for (int kx = 0; kx < K; kx++) {
-          const int ox = x - kx + pad;
-          if (ox < 0 || (ox >> 1) >= PW) continue;
-          const size_t idx = base + (oy >> 1) * PW + (ox >> 1);
-          if (arg2[idx] == (((oy & 1) << 1) | (ox & 1))) g = fmaf(dp2[idx], wk[ky * K + kx], g);
+      for (int py = py0; py <= py1; py++)
+        for (int px = px0; px <= px1; px++) {
+          const size_t idx = base + py * PW + px;
+          const float d = dp2[idx];
+          if (d == 0.f) continue;
+          const int a = arg2[idx];
+          const int ky = y + pad - (2 * py + (a >> 1)), kx = x + pad - (2 * px + (a & 1));
+          if (ky >= 0 && ky < K && kx >= 0 && kx < K) g = fmaf(d, wk[ky * K + kx], g);
         }
-      }
     }
     dp1[t] = g;
   }
