@@ -55,8 +55,11 @@ def main():
             out.append(proto + ';')
             out.append('')
     out += ['#ifdef __cplusplus', '}', '#endif', '#endif /* BISCOTTI_B200_H */', '']
-    with open(os.path.join(ROOT, 'include/biscotti_b200.h'), 'w') as fh:
-        fh.write('\n'.join(out))
+    path = os.path.join(ROOT, 'include/biscotti_b200.h')
+    text = '\n'.join(out)
+    if not os.path.exists(path) or open(path).read() != text:   # keep the mtime when nothing changed: the build
+        with open(path, 'w') as fh:                              # treats a newer header as "recompile everything"
+            fh.write(text)
     return sum(len(v) for v in groups.values())
 
 
