@@ -381,6 +381,26 @@ __global__ void symm_wait_kernel(const unsigned long long* my_flags, int world, 
   if (threadIdx.x == 0 && blockIdx.x == 0) symm_wait_all(my_flags, world, slot, epoch);
 }
 
+// All-gather of a small per-rank block (the Jacobian full commitments that go into the block, ~1 KB per rank):
+// one CTA stores this rank's block into every rank's buffer, publishes the slot's flag and waits for the others'
+// flags, so that when the kernel retires the whole gathered array is in local memory.  Replaces the last NCCL
+// collective of the fused path (ncclAllGather of the commitment bytes, once per block).
+__global__ void __launch_bounds__(256) symm_allgather_rows_kernel(PeerTable dst, PeerTable flags,
+                                                                  const unsigned long long* my_flags, int world, int rank,
+                                                                  const uint4* __restrict__ src, int n16, size_t dst_off16,
+                                                                  int slot, unsigned long long epoch) {
+  for (int q = 0; q < world; q++) {
+    uint4* d = reinterpret_cast<uint4*>(dst.ptr[q]) + dst_off16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) d[i] = src[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    symm_signal_all(flags, world, rank, slot, epoch);
+    symm_wait_all(my_flags, world, slot, epoch);
+  }
+}
+
 int make_plane_map(CUtensorMap* map, const void* base, int rows, int ld, int box_rows);   // gram_tc.cu
 
 }  // namespace bsc
@@ -425,6 +445,21 @@ int bsc_symm_signal(void* const* flag_ptrs, int world, int rank, int slot, unsig
 int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long epoch, void* stream) {
   symm_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const unsigned long long*)my_flags, world, slot, epoch);
   return finish_launch("symm_wait");
+}
+// dst_ptrs[q]: rank q's gather buffer [world][bytes_per_rank] (peer-mapped); src: this rank's block (16-byte aligned,
+// bytes_per_rank a multiple of 16).  On return of the kernel every rank's block for `epoch` is in the local buffer.
+int bsc_symm_allgather_rows(void* const* dst_ptrs, void* const* flag_ptrs, const void* my_flags, int world, int rank,
+                            const void* src, long long bytes_per_rank, int slot, unsigned long long epoch, void* stream) {
+  if (world < 1 || world > SYMM_MAX_WORLD || bytes_per_rank % 16 != 0 || ((uintptr_t)src & 15)) return -1;
+  PeerTable d, f;
+  for (int q = 0; q < SYMM_MAX_WORLD; q++) {
+    d.ptr[q] = q < world ? dst_ptrs[q] : nullptr;
+    f.ptr[q] = q < world ? flag_ptrs[q] : nullptr;
+  }
+  const int n16 = (int)(bytes_per_rank / 16);
+  symm_allgather_rows_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(d, f, (const unsigned long long*)my_flags, world, rank,
+                                                                  (const uint4*)src, n16, (size_t)rank * n16, slot, epoch);
+  return finish_launch("symm_allgather_rows");
 }
 
 // Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's

@@ -58,6 +58,7 @@ def _declare(L):
     L.bsc_krum_gram_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, ctypes.c_uint, c_ull, c_p]
     L.bsc_krum_select_fused.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
     L.bsc_krum_select_mc_wait.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
+    L.bsc_symm_allgather_rows.argtypes = [c_p, c_p, c_p, c_i, c_i, c_p, ctypes.c_longlong, c_i, c_ull, c_p]
     L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_d, c_p, c_p, c_ull, c_p]
 
 
@@ -112,6 +113,9 @@ class FusedComm(NcclComm):
         self.o_ypart = take(self.nchunk * self.S * 8)
         self.o_w64 = take(d * 8)
         self.o_w32 = take(d * 4)
+        self.cb_row = 96                                   # one Jacobian G1 point per peer
+        self.cb_bytes = world * self.per * self.cb_row     # gathered commitments of one block
+        self.o_cb = take(2 * self.cb_bytes)                # double-buffered by block parity
         self.nbytes = off
         base = c_p()
         _check(self.L.bsc_symm_alloc(self.nbytes, ctypes.byref(base)), "symm_alloc")
@@ -220,6 +224,17 @@ class FusedComm(NcclComm):
         pad[: local.shape[0]] = local[:per]
         if self.world == 1:
             return pad
+        if local.shape[1] == self.cb_row and local.dtype == torch.uint8:
+            # peer stores + flags in one small kernel (symm_allgather_rows_kernel): no library collective per block
+            self._cb_seq = getattr(self, "_cb_seq", 0) + 1
+            buf = self._cb_seq & 1
+            tab = self._table(self.o_cb + buf * self.cb_bytes)
+            _check(self.L.bsc_symm_allgather_rows(tab, self._tables["flags"], c_p(self.base + self.o_flags), self.world,
+                                                  self.rank, c_p(pad.data_ptr()), per * self.cb_row, SLOT_POINTS,
+                                                  self._cb_seq, self._stream()), "symm_allgather_rows")
+            self._cb_keep = pad      # the kernel reads it asynchronously
+            return tensor_from_ptr(self.base + self.o_cb + buf * self.cb_bytes, (self.world * per, self.cb_row),
+                                   torch.uint8, self.device)
         out = torch.empty(self.world * per, local.shape[1], dtype=local.dtype, device=local.device)
         dist.all_gather_into_tensor(out, pad)
         return out

@@ -347,6 +347,10 @@ int bsc_symm_signal(void* const* flag_ptrs, int world, int rank, int slot, unsig
 
 int bsc_symm_wait(const void* my_flags, int world, int slot, unsigned long long epoch, void* stream);
 
+// dst_ptrs[q]: rank q's gather buffer [world][bytes_per_rank] (peer-mapped); src: this rank's block (16-byte aligned,
+// bytes_per_rank a multiple of 16).  On return of the kernel every rank's block for `epoch` is in the local buffer.
+int bsc_symm_allgather_rows(void* const* dst_ptrs, void* const* flag_ptrs, const void* my_flags, int world, int rank, const void* src, long long bytes_per_rank, int slot, unsigned long long epoch, void* stream);
+
 // Fused all-gather + Gram.  plane_hi/lo[q]: rank q's [Sr][ldh] bf16 planes (peer-mapped), gpart[q]: rank q's
 // [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
 // array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed once;
