@@ -229,6 +229,7 @@ def main():
     phase_ms = None
     if args.profile_phases:          # every rank takes the extra instrumented step (collective kernels inside)
         eng._timing = True
+        eng._pre, eng.cfg.prefetch = None, False     # book every phase under this one iteration
         eng.step()
         phase_ms = eng.reports[-1].phase_ms
         eng._timing = False

@@ -35,6 +35,10 @@ def _engine(cfg: BiscottiConfig, device):
 
 
 def _run(cfg: BiscottiConfig, device, blocks: int, timing: bool = True):
+    if timing:
+        # per-phase attribution: keep every phase inside its own iteration (the prefetch would book the next
+        # iteration's local step + commitment MSM under this iteration's "block" phase)
+        cfg.prefetch = False
     eng = _engine(cfg, device)
     eng._timing = timing
     t0 = time.perf_counter()
