@@ -47,6 +47,8 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--no-dump", action="store_true")
     ap.add_argument("--log", action="store_true", help="emit [peer] log lines on stderr")
     ap.add_argument("--save-chain", default=None)
+    ap.add_argument("--partition", action="append", default=[], metavar="PEER:FIRST:LAST",
+                    help="cut PEER off for blocks FIRST..LAST (blockNode.sh); may be repeated")
     ap.add_argument("--data-dir", default=None, help="directory of <dataset><i>.npy shard files (default: synthetic data)")
     ap.add_argument("--resume", default=None, help="chain file to adopt before running (restart / rejoin, main.go:1000-1013)")
 
@@ -58,7 +60,8 @@ def config_from_args(a, mode: str):
     kw = dict(num_nodes=a.num_nodes, dataset=a.dataset, num_miners=a.na, num_verifiers=a.nv, num_noisers=a.nn,
               secure_agg=a.sa, noising=a.np, verification=a.vp, epsilon=a.ep, poison_fraction=a.po, perc_samples=ns,
               random_sampling=a.rs, colluders=a.c, defense=a.defense, max_iterations=a.iterations, seed=a.seed,
-              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm, data_dir=a.data_dir)
+              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm, data_dir=a.data_dir,
+              partitions=tuple(tuple(int(v) for v in x.split(":")) for x in a.partition))
     if a.shard_size:
         kw["shard_size"] = a.shard_size
     return BiscottiConfig(**kw)

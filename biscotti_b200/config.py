@@ -66,6 +66,8 @@ class BiscottiConfig:
     batch_size: int = 10              # honest.go:47
     precision: int = PRECISION
     fail_prob: float = FAIL_PROB
+    partitions: tuple = ()            # ((peer, first_block, last_block), ...): peer is unreachable for those blocks
+                                      # (blockNode.sh: iptables DROP on the peer's port for 30 s, then flush)
     krum_adversary_frac: float = 0.5  # main.go:780-783
     clip_norm: float = 100.0          # client.py:53
     dp_delta: float = 1e-5            # client_obj.py:61

@@ -241,6 +241,16 @@ class BiscottiEngine:
         if cfg.fail_prob > 0:
             for p in range(1, n):
                 self.alive[p] = self._rng.rand() >= cfg.fail_prob
+        # ---- scheduled network partitions (DistSys/blockNode.sh): the peer is cut off for a range of blocks; it
+        # holds no role and contributes nothing meanwhile, and is back (with the chain everybody shares) afterwards
+        if cfg.partitions:
+            cut = {int(p) for p, a, b in cfg.partitions if int(a) <= it <= int(b)}
+            was = getattr(self, "_cut", set())
+            for p in was - cut:
+                self.alive[p] = True
+            for p in cut:
+                self.alive[p] = False
+            self._cut = cut
         # ---- 1. roles
         verifiers, miners, prev_hash = self.select_roles()
         committee = set(verifiers) | set(miners)

@@ -194,3 +194,24 @@ def test_blocks_carry_verifier_signatures_that_verify():
     sigs = signer.finish(h, [u["commitment"]] * len(rep.verifiers))
     for v, sg in zip(rep.verifiers, sigs):
         assert cp.schnorr_verify(u["commitment"], e.keys[v].schnorr_public, sg)
+
+
+def test_partitioned_peer_sits_out_and_returns():
+    """blockNode.sh parity: a peer cut off for blocks 2..4 holds no role and earns no stake meanwhile; the run
+    stays live, and once the partition heals the peer takes part again."""
+    cfg = _cfg(max_iterations=9, partitions=((3, 2, 4),))
+    e = BiscottiEngine(cfg)
+    stake_before = None
+    for it in range(10):
+        if it == 2:
+            stake_before = e.stake[3]
+        rep = e.step()
+        if 2 <= it <= 4:
+            assert not e.alive[3] and 3 not in rep.verifiers and 3 not in rep.miners
+        if it == 4:
+            assert e.stake[3] == stake_before          # no contribution while cut off
+    assert e.alive[3] and e.chain.verify() and len(e.chain) == 11
+    assert sum(1 for r in e.reports if not r.empty) >= 8
+    base = BiscottiEngine(_cfg(max_iterations=9))
+    base.run()
+    assert base.chain != e.chain                        # the partition really changed who contributed
