@@ -126,6 +126,8 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_sha256_batch", c_i, c_p, c_i, c_ll, c_i, c_p, c_p)
     sig("bsc_noisers_batch", None, c_p, c_cp, c_sz, c_p, c_i, c_p, c_i, c_p, c_p)
     sig("bsc_gram_tc", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_i, c_p)
+    sig("bsc_split_planes", c_i, c_p, c_p, c_i, c_i, c_i, c_ll, c_i, c_i, c_p, c_p, c_i, c_i, c_p, c_i, c_p)
+    sig("bsc_eval_tc", c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_i, c_i, c_p)
     sig("bsc_lottery_roles", c_i, c_cp, c_i, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p)
     sig("bsc_lottery_noisers", c_i, c_cp, c_i, c_p, c_i, c_i, c_i, c_p)
     # host crypto

@@ -230,6 +230,154 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Batched model evaluation on the tensor cores (K14 / K15: test error, attack rate, RONI):
+//   logits[n][m][c] = X[n] . W_m[c] + b_m[c]   for N samples and M candidate weight vectors,
+//   wrong[m] = #{n : argmax_c logits[n][m][c] != y[n]}
+// (ML/Pytorch/client.py:136-172, client_obj.py:100-112).  It is an A*B^T GEMM with A = samples [N, F] and
+// B = candidate class rows [M*16, F] (classes padded to 16 per candidate so that a 128-column tile holds exactly 8
+// candidates), both K-major bf16x3 planes like the Gram kernel, same TMA / mbarrier / tcgen05 pipeline.  The
+// epilogue never writes the logits: each TMEM lane is one sample, it adds the bias, takes the arg-max of each
+// 16-column group and counts disagreements with the label; one integer atomicAdd per (warp, candidate).
+constexpr int EV_CPAD = 16;   // class slots per candidate
+__global__ void __launch_bounds__(GT_THREADS, 1)
+    eval_tc_kernel(const __grid_constant__ CUtensorMap ta_hi, const __grid_constant__ CUtensorMap ta_lo,
+                   const __grid_constant__ CUtensorMap tb_hi, const __grid_constant__ CUtensorMap tb_lo,
+                   const float* __restrict__ bias, const int* __restrict__ y, int* __restrict__ wrong, int N, int M,
+                   int kb_total) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  const uint32_t bars = tiles + GT_STAGES * GT_STAGE_BYTES;
+  const uint32_t bar_full = bars, bar_empty = bars + 8 * GT_STAGES, bar_tmem = bars + 16 * GT_STAGES;
+  const uint32_t tmem_slot = bar_tmem + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tm = blockIdx.x, tn = blockIdx.y;   // sample tile, candidate tile (8 candidates)
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < GT_STAGES; s++) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    mbar_init(bar_tmem, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(GT_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < kb_total; kb++) {
+        const int s = kb % GT_STAGES;
+        const uint32_t ph = (uint32_t)(kb / GT_STAGES) & 1u;
+        mbar_wait(bar_empty + 8 * s, ph ^ 1u);
+        const uint32_t st = tiles + s * GT_STAGE_BYTES;
+        mbar_expect_tx(bar_full + 8 * s, 4 * GT_TILE_BYTES);
+        const int kx = kb * GT_BK;
+        tma_load_2d(st, &ta_hi, kx, tm * GT_BM, bar_full + 8 * s);
+        tma_load_2d(st + GT_TILE_BYTES, &ta_lo, kx, tm * GT_BM, bar_full + 8 * s);
+        tma_load_2d(st + 2 * GT_TILE_BYTES, &tb_hi, kx, tn * GT_BM, bar_full + 8 * s);
+        tma_load_2d(st + 3 * GT_TILE_BYTES, &tb_lo, kx, tn * GT_BM, bar_full + 8 * s);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16_128x128();
+      for (int kb = 0; kb < kb_total; kb++) {
+        const int s = kb % GT_STAGES;
+        const uint32_t ph = (uint32_t)(kb / GT_STAGES) & 1u;
+        mbar_wait(bar_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t st = tiles + s * GT_STAGE_BYTES;
+        const uint64_t a_hi = umma_desc_sw128(st), a_lo = umma_desc_sw128(st + GT_TILE_BYTES);
+        const uint64_t b_hi = umma_desc_sw128(st + 2 * GT_TILE_BYTES), b_lo = umma_desc_sw128(st + 3 * GT_TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < GT_BK / 16; k++) {
+          const uint64_t off = (uint64_t)((k * 16 * 2) >> 4);
+          umma_bf16(tmem_base, a_hi + off, b_hi + off, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_bf16(tmem_base, a_hi + off, b_lo + off, idesc, 1u);
+          umma_bf16(tmem_base, a_lo + off, b_hi + off, idesc, 1u);
+        }
+        umma_commit(bar_empty + 8 * s);
+      }
+      umma_commit(bar_tmem);
+    }
+  } else {
+    const int q = warp & 3;
+    mbar_wait(bar_tmem, 0);
+    tc_fence_after();
+    const int row = tm * GT_BM + q * 32 + lane;
+    const int label = row < N ? y[row] : -1;
+#pragma unroll 1
+    for (int cc = 0; cc < GT_BM / 32; cc++) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(cc * 32), v);
+#pragma unroll
+      for (int h = 0; h < 2; h++) {                       // two candidates per 32-column chunk
+        const int m = tn * (GT_BM / EV_CPAD) + cc * 2 + h;
+        const float* b = bias + (size_t)m * EV_CPAD;
+        float best = -INFINITY;
+        int arg = 0;
+        if (m < M) {
+#pragma unroll
+          for (int c = 0; c < EV_CPAD; c++) {
+            const float l = __uint_as_float(v[h * EV_CPAD + c]) + b[c];   // padded classes carry a -1e30 bias
+            if (l > best) {
+              best = l;
+              arg = c;
+            }
+          }
+        }
+        const unsigned bad = __ballot_sync(0xffffffffu, m < M && row < N && arg != label);
+        if (lane == 0 && bad) atomicAdd(&wrong[m], __popc(bad));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(GT_TMEM_COLS) : "memory");
+  }
+}
+
+// fp32 rows -> bf16x3 planes, zero padded to [rows_pad][ldk].  Row r = (o, i) with o = r / inner, i = r % inner reads
+// src + o*ld_outer + i*ld_inner (+ base + i*ld_inner when base != null) and lands in plane row o*inner_pad + i.
+// Used for the sample matrix (inner = 1) and for candidate weights (inner = C classes, inner_pad = 16), for which it
+// also emits the bias vector (value at column `cols` of the class row block: flat layout W[C][F] then b[C]).
+__global__ void __launch_bounds__(256) split_planes_kernel(const float* __restrict__ src, const float* __restrict__ base,
+                                                           int outer, int inner, int inner_pad, long long ld_outer,
+                                                           int ld_inner, int cols, __nv_bfloat16* __restrict__ hi,
+                                                           __nv_bfloat16* __restrict__ lo, int ldk, int rows_pad,
+                                                           float* __restrict__ bias_out, int bias_off) {
+  const int r = blockIdx.x;               // plane row
+  if (r >= rows_pad) return;
+  const int o = r / inner_pad, i = r % inner_pad;
+  const bool live = o < outer && i < inner;
+  const float* s = src + (size_t)o * ld_outer + (size_t)i * ld_inner;
+  const float* b = base ? base + (size_t)i * ld_inner : nullptr;
+  for (int k = threadIdx.x; k < ldk; k += blockDim.x) {
+    float x = 0.f;
+    if (live && k < cols) x = s[k] + (b ? b[k] : 0.f);
+    const __nv_bfloat16 h = __float2bfloat16(x);
+    hi[(size_t)r * ldk + k] = h;
+    lo[(size_t)r * ldk + k] = __float2bfloat16(x - __bfloat162float(h));
+  }
+  if (bias_out && threadIdx.x == 0) {
+    float bv = -1e30f;
+    if (live) bv = src[(size_t)o * ld_outer + bias_off + i] + (base ? base[bias_off + i] : 0.f);
+    bias_out[r] = o < outer ? bv : 0.f;
+  }
+}
+
 typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                         CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -290,6 +438,41 @@ int bsc_gram_tc(const void* hi, const void* lo, int n, int rows, int ldh, int ks
   dim3 grid(ntile * (ntile + 1) / 2, ksplit);
   gram_tc_kernel<<<grid, GT_THREADS, GT_SMEM, (cudaStream_t)stream>>>(mh, ml, Gpart, ldg, ntile, kb_total, kb_per);
   return finish_launch("gram_tc");
+}
+
+// fp32 rows -> zero-padded bf16x3 planes [rows_pad][ldk] (+ bias vector); see split_planes_kernel.
+int bsc_split_planes(const float* src, const float* base, int outer, int inner, int inner_pad, long long ld_outer,
+                     int ld_inner, int cols, void* hi, void* lo, int ldk, int rows_pad, float* bias_out, int bias_off,
+                     void* stream) {
+  if (ldk % GT_BK != 0 || cols > ldk || inner > inner_pad || rows_pad < 1) return -1;
+  split_planes_kernel<<<rows_pad, 256, 0, (cudaStream_t)stream>>>(src, base, outer, inner, inner_pad, ld_outer, ld_inner,
+                                                                  cols, (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, ldk,
+                                                                  rows_pad, bias_out, bias_off);
+  return finish_launch("split_planes");
+}
+
+// wrong[m] += #{n < N : argmax_c (A[n] . B[m*16 + c] + bias[m*16 + c]) != y[n]} for m < M.  A planes: [a_rows_pad][ldk]
+// (a_rows_pad % 128 == 0, >= N), B planes: [b_rows_pad][ldk] (b_rows_pad % 128 == 0, >= 16*M).  Caller zero-fills wrong.
+int bsc_eval_tc(const void* a_hi, const void* a_lo, int a_rows_pad, const void* b_hi, const void* b_lo, int b_rows_pad,
+                int ldk, const float* bias, const int* y, int* wrong, int N, int M, void* stream) {
+  if (ldk % GT_BK != 0 || a_rows_pad % GT_BM != 0 || b_rows_pad % GT_BM != 0 || a_rows_pad < N ||
+      b_rows_pad < EV_CPAD * M || N < 1 || M < 1)
+    return -1;
+  CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+  int rc = make_plane_map(&ma_hi, a_hi, a_rows_pad, ldk, GT_BM);
+  if (!rc) rc = make_plane_map(&ma_lo, a_lo, a_rows_pad, ldk, GT_BM);
+  if (!rc) rc = make_plane_map(&mb_hi, b_hi, b_rows_pad, ldk, GT_BM);
+  if (!rc) rc = make_plane_map(&mb_lo, b_lo, b_rows_pad, ldk, GT_BM);
+  if (rc) return rc;
+  static bool configured = false;
+  if (!configured) {
+    BSC_CHECK(cudaFuncSetAttribute(eval_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GT_SMEM));
+    configured = true;
+  }
+  dim3 grid((N + GT_BM - 1) / GT_BM, (M + GT_BM / EV_CPAD - 1) / (GT_BM / EV_CPAD));
+  eval_tc_kernel<<<grid, GT_THREADS, GT_SMEM, (cudaStream_t)stream>>>(ma_hi, ma_lo, mb_hi, mb_lo, bias, y, wrong, N, M,
+                                                                      ldk / GT_BK);
+  return finish_launch("eval_tc");
 }
 
 }  // extern "C"

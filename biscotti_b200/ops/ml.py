@@ -8,6 +8,7 @@ ML/Pytorch/client.py:136-172 (error / attack rate), client_obj.py:100-112 (RONI)
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -166,9 +167,47 @@ def eval_softmax_errors(Wc, base, X, y, n_classes: int):
         logits = torch.einsum("nf,mcf->mnc", X.float(), W[:, : C * F].reshape(M, C, F)) + W[:, None, C * F:]
         return (logits.argmax(-1) != y.long()[None]).float().mean(dim=1)
     wrong = torch.zeros(M, dtype=torch.int32, device=X.device)
-    check(lib().bsc_eval_softmax(ptr(Wc), ptr(base), ptr(X), ptr(y), ptr(wrong), M, N, F, C, Wc.stride(0),
-                                 stream(X.device)), "eval_softmax")
+    if C <= 16 and hasattr(lib(), "bsc_eval_tc") and os.environ.get("BISCOTTI_EVAL_IMPL", "tc") == "tc":
+        _eval_softmax_tc(Wc, base, X, y, wrong, M, N, F, C)
+    else:
+        check(lib().bsc_eval_softmax(ptr(Wc), ptr(base), ptr(X), ptr(y), ptr(wrong), M, N, F, C, Wc.stride(0),
+                                     stream(X.device)), "eval_softmax")
     return wrong.float() / N
+
+
+_x_planes: dict = {}     # sample matrices are static (test / attack sets): their bf16x3 planes are built once
+_w_scratch: dict = {}
+
+
+def _eval_softmax_tc(Wc, base, X, y, wrong, M, N, F, C):
+    """tcgen05 path (csrc/gram_tc.cu eval_tc_kernel): logits GEMM + bias + arg-max + error count in one kernel."""
+    L = lib()
+    dev = X.device
+    ldk = pad_to(F, 64)
+    key = (X.data_ptr(), N, F, X._version)
+    planes = _x_planes.get(key)
+    if planes is None:
+        if len(_x_planes) > 16:
+            _x_planes.clear()
+        rows_pad = pad_to(N, 128)
+        hi = torch.empty(rows_pad, ldk, dtype=torch.bfloat16, device=dev)
+        lo = torch.empty_like(hi)
+        check(L.bsc_split_planes(ptr(X), None, N, 1, 1, F, 0, F, ptr(hi), ptr(lo), ldk, rows_pad, None, 0, stream(dev)),
+              "split_planes")
+        planes = (hi, lo, rows_pad, X)     # keep X alive so the pointer key stays valid
+        _x_planes[key] = planes
+    b_rows = pad_to(16 * M, 128)
+    wk = (dev, b_rows, ldk)
+    scr = _w_scratch.get(wk)
+    if scr is None:
+        scr = (torch.empty(b_rows, ldk, dtype=torch.bfloat16, device=dev), torch.empty(b_rows, ldk, dtype=torch.bfloat16, device=dev),
+               torch.empty(b_rows, dtype=torch.float32, device=dev))
+        _w_scratch[wk] = scr
+    whi, wlo, bias = scr
+    check(L.bsc_split_planes(ptr(Wc), ptr(base), M, C, 16, Wc.stride(0), F, F, ptr(whi), ptr(wlo), ldk, b_rows, ptr(bias),
+                             C * F, stream(dev)), "split_planes")
+    check(L.bsc_eval_tc(ptr(planes[0]), ptr(planes[1]), planes[2], ptr(whi), ptr(wlo), b_rows, ldk, ptr(bias), ptr(y),
+                        ptr(wrong), N, M, stream(dev)), "eval_tc")
 
 
 def eval_logistic_errors(Wc, base, X, y):

@@ -74,6 +74,13 @@ int bsc_eval_logistic(const float* Wc, const float* base, const float* X, const 
 // Gpart: [ksplit][ldg][ldg] with ldg = ceil(n/128)*128; every split must own >= 1 k-block.
 int bsc_gram_tc(const void* hi, const void* lo, int n, int rows, int ldh, int ksplit, float* Gpart, int ldg, void* stream);
 
+// fp32 rows -> zero-padded bf16x3 planes [rows_pad][ldk] (+ bias vector); see split_planes_kernel.
+int bsc_split_planes(const float* src, const float* base, int outer, int inner, int inner_pad, long long ld_outer, int ld_inner, int cols, void* hi, void* lo, int ldk, int rows_pad, float* bias_out, int bias_off, void* stream);
+
+// wrong[m] += #{n < N : argmax_c (A[n] . B[m*16 + c] + bias[m*16 + c]) != y[n]} for m < M.  A planes: [a_rows_pad][ldk]
+// (a_rows_pad % 128 == 0, >= N), B planes: [b_rows_pad][ldk] (b_rows_pad % 128 == 0, >= 16*M).  Caller zero-fills wrong.
+int bsc_eval_tc(const void* a_hi, const void* a_lo, int a_rows_pad, const void* b_hi, const void* b_lo, int b_rows_pad, int ldk, const float* bias, const int* y, int* wrong, int N, int M, void* stream);
+
 /* --------------------------------------------------------------------------------------------
  * kernels_secagg.cu - Fixed-point, Shamir shares, aggregation, reconstruction + SGD step.  Reference: DistSys/kyber.go:244-287, 579-609, 698-757, 809-857; DistSys/honest.go:346-502.
  * -------------------------------------------------------------------------------------------- */

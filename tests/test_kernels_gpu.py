@@ -294,3 +294,30 @@ def test_cnn_local_step_kernels_match_autograd(kind):
     cnn_native.local_step(kind, w.to(DEV), Xb.to(DEV), yb.to(DEV), 0.05, out)
     assert torch.allclose(out.cpu()[:, :d], ref2, rtol=1e-3, atol=1e-6)
     assert abs(float(out[0, :d].norm()) - 0.05) < 1e-3
+
+
+@pytest.mark.parametrize("M,N,F,C,with_base", [(1, 2000, 784, 10, False), (70, 2000, 784, 10, True), (9, 333, 100, 2, True),
+                                               (17, 128, 64, 16, False)])
+def test_eval_on_tensor_cores_matches_fp32_oracle(M, N, F, C, with_base, monkeypatch):
+    """eval_tc_kernel (tcgen05 bf16x3 logits GEMM + fused bias / arg-max / error count) against the fp32 PyTorch
+    restatement and the SIMT kernel: counts may differ only where two logits tie to within bf16x3 rounding."""
+    torch.manual_seed(5)
+    d = C * F + C
+    protos = torch.randn(C, F)
+    y = torch.randint(0, C, (N,), dtype=torch.int32)
+    X = protos[y.long()] * 0.5 + torch.randn(N, F)
+    base = torch.cat([protos.reshape(-1) * 0.1, torch.zeros(C)]) if with_base else None
+    Wc = torch.randn(M, d + 2) * 0.05
+    Wc[0, :d] = torch.cat([protos.reshape(-1) * 0.2, torch.randn(C) * 0.1])     # one candidate that actually classifies
+    ref = ml.eval_softmax_errors(Wc, base, X, y, C)
+    Xg, yg, Wg = X.to(DEV), y.to(DEV), Wc.to(DEV)
+    bg = base.to(DEV) if base is not None else None
+    monkeypatch.setenv("BISCOTTI_EVAL_IMPL", "tc")
+    tc = ml.eval_softmax_errors(Wg, bg, Xg, yg, C).cpu()
+    tc2 = ml.eval_softmax_errors(Wg, bg, Xg, yg, C).cpu()                        # cached sample planes, same answer
+    monkeypatch.setenv("BISCOTTI_EVAL_IMPL", "simt")
+    simt = ml.eval_softmax_errors(Wg, bg, Xg, yg, C).cpu()
+    assert torch.equal(tc, tc2)
+    assert float((tc - ref).abs().max()) * N <= 2.5, (tc * N, ref * N)
+    assert float((simt - ref).abs().max()) * N <= 2.5
+    assert float(ref[0]) < 0.5 or C > 10
