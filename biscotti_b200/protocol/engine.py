@@ -531,6 +531,9 @@ class BiscottiEngine:
                 self._pinned[key] = buf
             buf.copy_(v, non_blocking=True)
             out[k] = buf
+        # bytes this block reads back from the device (weights, commitments, share-check counters, signature
+        # halves; + 8 for the two error rates, which _launch_eval reads the same way)
+        self.last_d2h_bytes = sum(b.numel() * b.element_size() for b in out.values()) + 8
         if before_sync is None:
             torch.cuda.current_stream(self.device).synchronize()
         else:
