@@ -137,3 +137,27 @@ def test_gradient_check_and_noise_utils():
         pass
     assert abs(np.mean(np.abs(laplace_noise(20000, 2.0))) - 2.0) < 0.1
     assert abs(np.mean(exp_noise(20000, 3.0)) - 3.0) < 0.15
+
+
+def test_central_block_model_branching():
+    """CentralBlockML: branches advance by the mean of the gradients submitted to them; the DP-noise sampler has
+    the radius distribution of exp(-eps ||x|| / 2)."""
+    import torch
+
+    from biscotti_b200.sim import central_block as cb
+
+    b = cb.ModelBranch(torch.zeros(3), torch.ones(3))
+    assert not b.update()
+    b.submit(torch.tensor([1.0, 0.0, 0.0]))
+    b.submit(torch.tensor([3.0, 2.0, 0.0]))
+    assert b.update() and torch.allclose(b.weights, torch.tensor([2.0, 1.0, 0.0])) and b.history == [2]
+    assert torch.allclose(b.previous_grad, torch.tensor([2.0, 1.0, 0.0]))
+    g = torch.Generator().manual_seed(0)
+    z = cb.sample_dp_noise(4000, 8, 2.0, g)
+    assert abs(float(z.norm(dim=1).mean()) - 8 * 2 / 2.0) < 0.3            # E||x|| = d * 2/eps
+    res = cb.run_branching("creditcard", clients=8, poisoners=2, branches=2, rounds=10)
+    assert len(res["branches"]) == 2 and len(res["choices"]) == 10
+    assert sum(res["last_round"]["honest_on_branch"]) == 6 and sum(res["last_round"]["poisoners_on_branch"]) == 2
+    assert sum(x["blocks"] for x in res["branches"]) >= 10
+    quirk = cb.run_branching("creditcard", clients=8, poisoners=2, branches=2, rounds=3, metric="distance")
+    assert quirk["choices"] != cb.run_branching("creditcard", clients=8, poisoners=2, branches=2, rounds=3)["choices"]
