@@ -167,7 +167,11 @@ def eval_softmax_errors(Wc, base, X, y, n_classes: int):
         logits = torch.einsum("nf,mcf->mnc", X.float(), W[:, : C * F].reshape(M, C, F)) + W[:, None, C * F:]
         return (logits.argmax(-1) != y.long()[None]).float().mean(dim=1)
     wrong = torch.zeros(M, dtype=torch.int32, device=X.device)
-    if C <= 16 and hasattr(lib(), "bsc_eval_tc") and os.environ.get("BISCOTTI_EVAL_IMPL", "tc") == "tc":
+    # tcgen05 path for batches of candidates (RONI, sweeps): 10x at M = 70, 28x at M = 280 (124 TFLOP/s useful).  A
+    # single candidate is 25 MFLOP and three launches on that path vs one on the SIMT kernel (54 vs 43 us), so the
+    # per-block test-error / attack-rate evaluation stays on the SIMT kernel.  BISCOTTI_EVAL_IMPL=tc|simt forces one.
+    impl = os.environ.get("BISCOTTI_EVAL_IMPL", "auto")
+    if C <= 16 and hasattr(lib(), "bsc_eval_tc") and (impl == "tc" or (impl == "auto" and M >= 4)):
         _eval_softmax_tc(Wc, base, X, y, wrong, M, N, F, C)
     else:
         check(lib().bsc_eval_softmax(ptr(Wc), ptr(base), ptr(X), ptr(y), ptr(wrong), M, N, F, C, Wc.stride(0),
