@@ -151,7 +151,7 @@ class BatchedVRF:
             return (gam, None, msg)
         if not hasattr(self, "_side"):
             torch.cuda.current_stream(self.device).synchronize()   # once: the scalars' upload has landed
-            self._side = torch.cuda.Stream(self.device)
+            self._side = torch.cuda.Stream(self.device, priority=-1)   # on the block's critical path
             self._host_gam = torch.empty(n, 32, dtype=torch.uint8).pin_memory()
             self._hpt_pinned = torch.empty(64, dtype=torch.uint8).pin_memory()
             self._hd = torch.empty(64, dtype=torch.uint8, device=self.device)

@@ -61,7 +61,7 @@ class SchnorrBatchSigner:
             self._ensure_table()
             if not hasattr(self, "_side"):
                 torch.cuda.current_stream(self.device).synchronize()   # once: the comb table build has finished
-                self._side = torch.cuda.Stream(self.device)
+                self._side = torch.cuda.Stream(self.device, priority=-1)   # needed at block assembly
                 self._k_pinned = torch.empty(4096, 8, dtype=torch.int32).pin_memory()
             main = torch.cuda.current_stream(self.device)
             kp = self._k_pinned[:n] if n <= self._k_pinned.shape[0] else torch.empty(n, 8, dtype=torch.int32).pin_memory()

@@ -86,6 +86,8 @@ class BiscottiEngine:
         self._pre = None          # prefetched (Q, chunkC, fullC) of the next iteration, see _prefetch_next
         self._next_inputs, self._fed_inputs = None, False
         self._eval_pending = None
+        self._main = self._wstream = self._wevent = None     # streams of step() / _witness_side
+        self.last_aggregate = None
         self.keys = cp.derive_peer_keys(n, cfg.seed)
         self.poisoners = poisoner_ids(cfg)
         self.colluder_ids = set(range(n - cfg.colluders, n)) if cfg.colluders > 0 else set()
@@ -224,7 +226,39 @@ class BiscottiEngine:
         minibatches (bench end-to-end path); otherwise minibatches are drawn from the resident shards.
         `next_inputs` = the following call's `inputs` (optionally with a CUDA event that marks their H2D copy
         complete), if the caller already has them: a double-buffered input pipeline lets the engine start the
-        next local step while this block is being assembled."""
+        next local step while this block is being assembled.
+
+        On a GPU the iteration runs on the engine's own high-priority stream (ordered after the caller's stream on
+        entry, and the caller's stream after it on exit), so that the witness MSM — queued on a default-priority
+        stream, see _witness_side — yields SM slots to the kernels the block is waiting for."""
+        if self.device.type != "cuda" or self.cfg.mode == "fedsys" or not self.cfg.overlap_witness:
+            return self._step(inputs, next_inputs)
+        if self._main is None:
+            self._main = torch.cuda.Stream(self.device, priority=-1)
+        cur = torch.cuda.current_stream(self.device)
+        self._main.wait_stream(cur)
+        prev_w = self._wevent
+        with torch.cuda.stream(self._main):
+            rep = self._step(inputs, next_inputs)
+        cur.wait_stream(self._main)
+        if prev_w is not None:
+            # the previous block's witnesses had this whole iteration to finish; waiting for them here keeps every
+            # iteration's device timeline (events on the caller's stream) accountable for one block of witness work
+            cur.wait_event(prev_w)
+        return rep
+
+    def _witness_side(self):
+        """Stream for the KZG witness MSM and the miners' homomorphic aggregation.  Nothing that goes into the block
+        depends on their result (the block carries the contributors' commitments, the reconstructed weights and the
+        approvals), so they run beside share aggregation, reconstruction, block assembly and the next block's VRF
+        instead of in front of them.  Instrumented runs keep them in line so that phase times stay attributable."""
+        if self.device.type != "cuda" or self._main is None or self._timing:
+            return None
+        if self._wstream is None:
+            self._wstream = torch.cuda.Stream(self.device, priority=0)
+        return self._wstream
+
+    def _step(self, inputs=None, next_inputs=None) -> BlockReport:
         cfg = self.cfg
         self._next_inputs, self._fed_inputs = next_inputs, inputs is not None
         if cfg.mode == "fedsys":
@@ -338,19 +372,35 @@ class BiscottiEngine:
         agg_commit = None
         if cfg.secure_agg:
             if self.commit is not None and self.P:
-                with self._phase("witness"):
-                    # every approved worker generates shares + witnesses for the miners (kyber.go:456-482)
-                    appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
-                    appr_local = self._idx(appr_rows)
-                    W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire) if appr_rows else None
-                with self._phase("miner_aggregate"):
-                    if W is not None and local_contrib:
-                        # positions of contributors inside the approved-local list
-                        pos = {r: i for i, r in enumerate(appr_rows)}
-                        csel = self._idx([pos[r] for r in local_contrib])
-                        aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)        # [nchunk, S, 16|24]
-                        aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)    # [nchunk, 16|24]
-                        agg_commit = (aggC, aggW)
+                # every approved worker generates shares + witnesses for the miners (kyber.go:456-482); the miners add
+                # the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287)
+                appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
+                appr_local = self._idx(appr_rows)
+                pos = {r: i for i, r in enumerate(appr_rows)}      # positions of contributors inside the approved list
+                csel = self._idx([pos[r] for r in local_contrib])
+                side = self._witness_side()
+                if side is None:
+                    with self._phase("witness"):
+                        W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire) if appr_rows else None
+                    with self._phase("miner_aggregate"):
+                        if W is not None and local_contrib:
+                            aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)        # [nchunk, S, 16|24]
+                            aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)    # [nchunk, 16|24]
+                            agg_commit = (aggC, aggW)
+                elif appr_rows:
+                    ready = torch.cuda.Event()
+                    ready.record()                         # Q, chunkC and the index tensors are complete at this point
+                    side.wait_event(ready)
+                    with torch.cuda.stream(side):
+                        W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire)
+                        if local_contrib:
+                            aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)
+                            aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)
+                            agg_commit = (aggC, aggW)
+                        self._wevent = torch.cuda.Event()
+                        self._wevent.record()
+                    for t in (Q, chunkC, appr_local, csel, sel):      # allocated on the main stream, read on `side`
+                        t.record_stream(side)
             with self._phase("secagg"):
                 xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
                 if self.fused:
@@ -365,6 +415,7 @@ class BiscottiEngine:
                         torch.zeros(cfg.nchunk, self.S, dtype=torch.int64, device=dev)
                     if self.comm is not None:
                         Ysum = self.comm.all_reduce_i64(Ysum)
+                    self._last_ysum = Ysum
                     xs_t = self._idx(xs)
                     av_t = self._idx(shares_avail, torch.uint8)
                     _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
@@ -496,6 +547,28 @@ class BiscottiEngine:
         te = self.model.eval_errors(w, None, self.data.X_test, self.data.y_test)
         ar = self.model.eval_errors(w, None, self.data.X_attack, self.data.y_attack)
         return te, ar
+
+    def verify_last_aggregate(self, samples=((0, 0), (0, 13), (1, 20))):
+        """What a miner can check about the last block's aggregation (kyber.go:244-287 + verifySecret): the sum of
+        the contributors' witnesses opens the sum of their chunk commitments to the sum of their shares.  Waits
+        for the witness stream.  Single-rank engines only (each rank aggregates its own contributors).  Returns
+        None when there is nothing to check."""
+        if self.last_aggregate is None or self.world != 1 or getattr(self, "_last_ysum", None) is None:
+            return None
+        if self._wevent is not None:
+            self._wevent.synchronize()
+        aggC, aggW = self.last_aggregate
+        Cb, Wb = self.commit.to_bytes(self.commit.normalize(aggC) if aggC.shape[-1] == 24 else aggC), \
+            self.commit.to_bytes(self.commit.normalize(aggW) if aggW.shape[-1] == 24 else aggW)
+        Y = self._last_ysum.cpu()
+        S = self.S
+        ok = True
+        for c, s in samples:
+            if c >= self.cfg.nchunk or s >= S:
+                continue
+            off = 64 * (c * S + s)
+            ok = ok and self.commit.verify_share_trapdoor(Cb[64 * c: 64 * c + 64], Wb[off: off + 64], c, s, int(Y[c, s]))
+        return ok
 
     def _launch_eval(self):
         """Queue the error-rate kernels and their read-back; _finish_block picks the numbers up."""
