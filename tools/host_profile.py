@@ -26,4 +26,5 @@ for _ in range(STEPS):
 torch.cuda.synchronize()
 pr.disable()
 st = pstats.Stats(pr)
-st.sort_stats("cumulative").print_stats(45)
+st.sort_stats("cumulative").print_stats(30)
+st.sort_stats("tottime").print_stats(45)
