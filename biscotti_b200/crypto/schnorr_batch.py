@@ -88,6 +88,20 @@ class SchnorrBatchSigner:
             self._keep = (k, jac, aff)
         return dict(n=n, x=x, vw=vw, vbe=vbe, T_dev=T_dev, event=event)
 
+    def select(self, handle, rows: list[int], T_host: np.ndarray | None = None):
+        """Sub-handle for a subset of the launched signatures (the updates that reached the block).  T_host: the
+        [n, 64] commitment bytes of the *full* launch if the caller already copied them to the host."""
+        n = handle["n"]
+        idx = np.asarray(rows, dtype=np.int64)
+        if T_host is None and handle["T_dev"] is not None:
+            if handle.get("event") is not None:
+                torch.cuda.current_stream(self.device).wait_event(handle["event"])
+            T_host = handle["T_dev"].cpu().numpy()
+        sub = dict(n=len(rows), x=handle["x"].reshape(n, 32)[idx].reshape(-1).copy(),
+                   vw=handle["vw"][:n][idx].copy(), vbe=handle["vbe"].reshape(-1, 32)[:n][idx].reshape(-1).copy(),
+                   T_dev=None, event=None, T_host=None if T_host is None else np.ascontiguousarray(np.asarray(T_host)[idx]))
+        return sub
+
     def finish(self, handle, msgs: list[bytes], T_host: np.ndarray | None = None) -> list[bytes]:
         """Complete the signatures over `msgs` (all the same length).  T_host: the [n, 64] commitment bytes if
         the caller already copied handle['T_dev'] to the host; otherwise they are fetched (or computed on the
@@ -96,6 +110,8 @@ class SchnorrBatchSigner:
         if n == 0:
             return []
         L = self.L
+        if T_host is None:
+            T_host = handle.get("T_host")
         if T_host is None:
             if handle["T_dev"] is not None:
                 if handle.get("event") is not None:

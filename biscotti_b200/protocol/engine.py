@@ -23,6 +23,7 @@ import contextlib
 import hashlib
 import math
 import random
+import struct
 import time
 from dataclasses import dataclass, field
 
@@ -316,6 +317,14 @@ class BiscottiEngine:
         arrival = self._arrival_order(workers, "verify")
         krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh, sorted by id
         rep.n_krum = len(krum_set)
+        # Approvals (krum.go:338-358): the signature halves T = v*G do not depend on the Krum verdict or on the message,
+        # only on (block, update, verifier), so they are started for every candidate update now — the host would
+        # otherwise sit idle waiting for the VRF — and only those of the updates that reach the block are completed.
+        signers = [v for v in verifiers if self.alive[v]]
+        sig_handle = None
+        if self.signer is not None and self.commit is not None and signers and krum_set:
+            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in krum_set for v in signers],
+                                            [struct.pack("<qii", it, p, v) for p in krum_set for v in signers])
         # ---- 4. noisers + noise
         with self._phase("noise"):
             noiser_tab = torch.full((max(1, self.P), max(1, cfg.num_noisers)), -1, dtype=torch.int32)
@@ -359,7 +368,6 @@ class BiscottiEngine:
         # ---- 6. approvals: every reachable verifier signs the commitment of each accepted update; a worker
         # proceeds when it holds >= floor(nv/2) signatures (main.go:1686).  All verifiers run the same Krum on
         # the same set here, so the signature count is the number of live verifiers.
-        signers = [v for v in verifiers if self.alive[v]]
         approved = accepted if (signers and len(signers) >= len(verifiers) // 2) else []
 
         # ---- 7/8. shares, witnesses, aggregation, reconstruction, SGD step
@@ -374,38 +382,44 @@ class BiscottiEngine:
         rep.n_contributors = len(contributors)
         local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
         sel = self._idx(local_contrib)
-        agg_commit = None
+        agg_box = [None]
+        launch_witnesses = None
         if cfg.secure_agg:
             if self.commit is not None and self.P:
-                # every approved worker generates shares + witnesses for the miners (kyber.go:456-482); the miners add
-                # the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287)
+                # Every approved worker generates shares + KZG witnesses for the miners (kyber.go:456-482) and the
+                # miners add the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287).
+                # Nothing that enters the block depends on them, so they are *queued after* the share aggregation,
+                # the reconstruction and the block's device->host collection (see after_copies below): the device
+                # works on them while the host assembles, signs and hashes the block.
                 appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
                 appr_local = self._idx(appr_rows)
                 pos = {r: i for i, r in enumerate(appr_rows)}      # positions of contributors inside the approved list
                 csel = self._idx([pos[r] for r in local_contrib])
-                side = self._witness_side()
-                if side is None:
-                    with self._phase("witness"):
-                        W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire) if appr_rows else None
-                    with self._phase("miner_aggregate"):
-                        if W is not None and local_contrib:
-                            aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)        # [nchunk, S, 16|24]
-                            aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)    # [nchunk, 16|24]
-                            agg_commit = (aggC, aggW)
-                elif appr_rows:
-                    ready = torch.cuda.Event()
-                    ready.record()                         # Q, chunkC and the index tensors are complete at this point
-                    side.wait_event(ready)
-                    with torch.cuda.stream(side):
-                        W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire)
-                        if local_contrib:
-                            aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)
-                            aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)
-                            agg_commit = (aggC, aggW)
-                        self._wevent = torch.cuda.Event()
-                        self._wevent.record()
-                    for t in (Q, chunkC, appr_local, csel, sel):      # allocated on the main stream, read on `side`
-                        t.record_stream(side)
+
+                def launch_witnesses():
+                    side = self._witness_side()
+                    if side is None:
+                        with self._phase("witness"):
+                            W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire) if appr_rows else None
+                        with self._phase("miner_aggregate"):
+                            if W is not None and local_contrib:
+                                aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)        # [nchunk, S, 16|24]
+                                aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)    # [nchunk, 16|24]
+                                agg_box[0] = (aggC, aggW)
+                    elif appr_rows:
+                        ready = torch.cuda.Event()
+                        ready.record()                     # Q, chunkC and the index tensors are complete at this point
+                        side.wait_event(ready)
+                        with torch.cuda.stream(side):
+                            W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire)
+                            if local_contrib:
+                                aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)
+                                aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)
+                                agg_box[0] = (aggC, aggW)
+                            self._wevent = torch.cuda.Event()
+                            self._wevent.record()
+                        for t in (Q, chunkC, appr_local, csel, sel):  # allocated on the main stream, read on `side`
+                            t.record_stream(side)
             with self._phase("secagg"):
                 xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
                 if self.fused:
@@ -434,20 +448,12 @@ class BiscottiEngine:
                     secagg.plain_sum_step(self.U, sel, self.d, self.w64, self.w32)
                 bad = torch.zeros(2, dtype=torch.int32, device=dev)
 
-        # approvals: every verifier signs the commitment of each update it accepted (krum.go:338-358).  The
-        # T = v*G halves of the signatures run on the GPU (side stream); their host-side preparation happens here,
-        # after the witness / aggregation kernels have been queued, so it overlaps them.  The signatures are
-        # completed on the host when the block is assembled, for the updates that end up in the block.
-        sig_handle = None
-        if self.signer is not None and self.commit is not None:
-            import struct
-
-            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in contributors for v in signers],
-                                            [struct.pack("<qii", it, p, v) for p in contributors for v in signers])
-
         # ---- 9. block assembly (host).  Evaluation of the new weights is launched first so that one
         # device->host collection (weights, commitments, share-check counters, error rates) and one stream
         # synchronisation serve the whole tail of the block.
+        if self._timing and launch_witnesses is not None:
+            launch_witnesses()            # instrumented runs: in line, so the phases do not nest
+            launch_witnesses = None
         with self._phase("block"):
             updates = []
             commits = {}
@@ -466,6 +472,8 @@ class BiscottiEngine:
             # Evaluation of the new weights is not part of the block: it is queued behind the collection (with the
             # next iteration's prefetch) and read back after the block has been assembled and hashed.
             def after_copies():
+                if launch_witnesses is not None:
+                    launch_witnesses()
                 if do_eval:
                     self._launch_eval()
                 self._prefetch_next(it + 1)
@@ -486,7 +494,9 @@ class BiscottiEngine:
             all_sigs = None
             if sig_handle is not None and all(len(commits.get(p, b"")) == 64 for p in contributors):
                 msgs = [commits[p] for p in contributors for _ in signers]
-                all_sigs = self.signer.finish(sig_handle, msgs, host.get("sigT"))
+                kpos = {p: i for i, p in enumerate(krum_set)}
+                rows = [kpos[p] * len(signers) + j for p in contributors for j in range(len(signers))]
+                all_sigs = self.signer.finish(self.signer.select(sig_handle, rows, host.get("sigT")), msgs)
             nv = len(signers)
             for ci, p in enumerate(contributors):
                 c = commits.get(p, b"")
@@ -501,7 +511,7 @@ class BiscottiEngine:
                     if p not in accepted:
                         self.stake[p] -= STAKE_UNIT                      # honest.go:362-370 (plain path only)
             rep.bad_shares = int(host["bad"].sum())
-        return self._finish_block(rep, updates, agg_commit, phases, t0, host)
+        return self._finish_block(rep, updates, agg_box[0], phases, t0, host)
 
     # ------------------------------------------------------------------------------------------
     def _available_shares(self, miners, alive_miners):
