@@ -75,7 +75,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     objs = [OBJ / (s.stem + ".o") for s in sources()]
     if jobs or not LIB.exists() or force:
         cmd = [nvcc, "-shared", "-o", str(LIB), *map(str, objs), "-gencode", "arch=compute_100a,code=sm_100a",
-               "-Xcompiler", "-fPIC", "-lpthread", "-ldl"]
+               "-Xcompiler", "-fPIC", "-lpthread", "-ldl",
+               "-Xlinker", "--no-undefined"]     # an unresolved symbol must fail the build, not the first dlopen
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stderr[-4000:]}")

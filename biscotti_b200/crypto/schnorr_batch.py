@@ -46,11 +46,17 @@ class SchnorrBatchSigner:
 
     def launch(self, secrets: list[bytes], tags: list[bytes]):
         """Start signing: one (secret key, unique tag) pair per signature.  Returns a handle for finish()."""
-        n = len(secrets)
         L = self.L
-        x = np.frombuffer(b"".join(secrets), dtype=np.uint8).copy()
-        tg = np.frombuffer(b"".join(tags), dtype=np.uint8).copy()
-        taglen = len(tags[0]) if n else 0
+        if isinstance(secrets, np.ndarray):      # [n, 32] uint8 secrets and [n, taglen] uint8 tags, already packed
+            n = secrets.shape[0]
+            x = np.ascontiguousarray(secrets, dtype=np.uint8).reshape(-1)
+            tg = np.ascontiguousarray(tags, dtype=np.uint8).reshape(-1)
+            taglen = tags.shape[1] if n else 0
+        else:
+            n = len(secrets)
+            x = np.frombuffer(b"".join(secrets), dtype=np.uint8).copy()
+            tg = np.frombuffer(b"".join(tags), dtype=np.uint8).copy()
+            taglen = len(tags[0]) if n else 0
         vw = np.empty((max(1, n), 8), dtype=np.uint32)
         vbe = np.empty(max(1, n) * 32, dtype=np.uint8)
         if n:

@@ -271,6 +271,10 @@ static bool u256_lt(const U256& a, const U256& b) {
   return false;
 }
 
+namespace bsc {
+void sha256_fast(const uint8_t* data, size_t n, uint8_t out[32]);   // sha256_ni.cpp
+}
+
 // hashSchnorr (kyber.go:928-933): XOF keyed by the point bytes, absorb the message, Pick a scalar.
 static Fr hash_schnorr(const uint8_t* msg, size_t n, const uint8_t T64[64]) {
   Blake2xb x;
@@ -436,14 +440,13 @@ void bsc_schnorr_sign(const uint8_t* msg, size_t n, const uint8_t x_be[32], cons
 // Nonce: v = SHA-256("bsc-schnorr-nonce" || x || tag) mod order, tag = caller-chosen unique bytes.
 void bsc_schnorr_nonces(int n, const uint8_t* tags, int taglen, const uint8_t* x_be, uint32_t* v_words_le,
                         uint8_t* v_be) {
+  std::vector<uint8_t> buf(17 + 32 + (size_t)taglen);
+  memcpy(buf.data(), "bsc-schnorr-nonce", 17);
   for (int i = 0; i < n; i++) {
-    Sha256 s;
-    sha256_init(s);
-    sha256_update(s, (const uint8_t*)"bsc-schnorr-nonce", 17);
-    sha256_update(s, x_be + 32 * (size_t)i, 32);
-    sha256_update(s, tags + (size_t)taglen * i, (size_t)taglen);
+    memcpy(buf.data() + 17, x_be + 32 * (size_t)i, 32);
+    memcpy(buf.data() + 49, tags + (size_t)taglen * i, (size_t)taglen);
     uint8_t h[32];
-    sha256_final(s, h);
+    sha256_fast(buf.data(), buf.size(), h);      // SHA-NI when the CPU has it (sha256_ni.cpp)
     const U256 v = fe_to_u256(fe_from_u256<BnN>(u256_from_be(h)));
     memcpy(v_words_le + 8 * (size_t)i, v.v, 32);
     u256_to_be(v_be + 32 * (size_t)i, v);

@@ -323,8 +323,12 @@ class BiscottiEngine:
         signers = [v for v in verifiers if self.alive[v]]
         sig_handle = None
         if self.signer is not None and self.commit is not None and signers and krum_set:
-            sig_handle = self.signer.launch([self.keys[v].schnorr_secret for p in krum_set for v in signers],
-                                            [struct.pack("<qii", it, p, v) for p in krum_set for v in signers])
+            nk, ns = len(krum_set), len(signers)
+            if not hasattr(self, "_sk_mat"):     # all peers' signing keys as one [n, 32] array (pKeyG1.json holds them all)
+                self._sk_mat = np.frombuffer(b"".join(k.schnorr_secret for k in self.keys), dtype=np.uint8).reshape(n, 32)
+            tags = np.empty(nk * ns, dtype=[("it", "<i8"), ("p", "<i4"), ("v", "<i4")])     # = struct.pack("<qii", it, p, v)
+            tags["it"], tags["p"], tags["v"] = it, np.repeat(krum_set, ns), np.tile(signers, nk)
+            sig_handle = self.signer.launch(np.tile(self._sk_mat[signers], (nk, 1)), tags.view(np.uint8).reshape(nk * ns, 16))
         # ---- 4. noisers + noise
         with self._phase("noise"):
             noiser_tab = torch.full((max(1, self.P), max(1, cfg.num_noisers)), -1, dtype=torch.int32)
