@@ -65,6 +65,8 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_local_softmax_step", c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_f, c_p)
     sig("bsc_local_logistic_step", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_ull, c_p, c_i, c_p)
     sig("bsc_noise_mix", c_i, c_p, c_p, c_i, c_ull, c_i, c_f, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p)
+    sig("bsc_noise_mix_rows", c_i, c_p, c_p, c_i, c_ull, c_i, c_f, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p)
+    sig("bsc_sample_minibatch", c_i, c_ull, c_i, c_p, c_i, c_i, c_i, c_p, c_p)
     sig("bsc_noise_row", c_i, c_p, c_i, c_ull, c_i, c_i, c_f, c_p)
     sig("bsc_noise_row_host", None, c_p, c_i, c_ull, c_i, c_i, c_f)
     sig("bsc_gram_simt", c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_p)

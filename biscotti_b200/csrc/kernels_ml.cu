@@ -170,10 +170,18 @@ __global__ void local_logistic_step_kernel(const float* __restrict__ w, const fl
 __global__ void __launch_bounds__(256) noise_mix_kernel(
     const float* __restrict__ U, const int* __restrict__ noisers, int nn, unsigned long long seed, int slot,
     float noise_scale, float* __restrict__ Un, __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo,
-    float* __restrict__ norms, int d, int ldu, int ldh) {
+    float* __restrict__ norms, int d, int ldu, int ldh, const int* __restrict__ dst_row) {
   __shared__ float red[40];
   __shared__ int snz[64];
   const int p = blockIdx.x, tid = threadIdx.x;
+  // dst_row (optional): plane / norm row of peer p, so that the Krum candidates land compacted and in Krum order
+  // (no gather afterwards); a negative entry means the peer is not a candidate and needs no planes
+  const int pr = dst_row ? dst_row[p] : p;
+  if (pr < 0) {
+    hi = nullptr;
+    norms = nullptr;
+    if (!Un) return;
+  }
   int cnt = 0;
   if (tid == 0) {
     for (int q = 0; q < nn; q++) {
@@ -204,8 +212,8 @@ __global__ void __launch_bounds__(256) noise_mix_kernel(
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
         const float r = v - __bfloat162float(h);
         if (hi) {
-          hi[(size_t)p * ldh + k] = h;
-          lo[(size_t)p * ldh + k] = __float2bfloat16_rn(r);
+          hi[(size_t)pr * ldh + k] = h;
+          lo[(size_t)pr * ldh + k] = __float2bfloat16_rn(r);
         }
         nrm = fmaf(v, v, nrm);
       }
@@ -214,14 +222,56 @@ __global__ void __launch_bounds__(256) noise_mix_kernel(
   // zero padding columns so the Gram kernel can run over ldh without masks
   for (int k = d + tid; k < ldh; k += blockDim.x) {
     if (hi) {
-      hi[(size_t)p * ldh + k] = __float2bfloat16_rn(0.f);
-      lo[(size_t)p * ldh + k] = __float2bfloat16_rn(0.f);
+      hi[(size_t)pr * ldh + k] = __float2bfloat16_rn(0.f);
+      lo[(size_t)pr * ldh + k] = __float2bfloat16_rn(0.f);
     }
   }
   for (int k = d + tid; k < ldu; k += blockDim.x)
     if (Un) Un[(size_t)p * ldu + k] = 0.f;
   const float t = block_sum(nrm, red);
-  if (tid == 0 && norms) norms[p] = t;
+  if (tid == 0 && norms) norms[pr] = t;
+}
+
+// Minibatch draw: B distinct rows out of a peer's Ns, uniformly at random (logistic_model.py:121-125; the torch
+// DataLoader shuffle of client.py).  One warp per peer: every row gets a Philox key from (seed, iteration, peer,
+// row) and the B smallest keys win, so the draw depends only on those four numbers — any rank computes the same
+// rows for a peer, and no generator state lives anywhere.  Ns <= 32 * SMB_MAXK.
+constexpr int SMB_MAXK = 32;
+__global__ void __launch_bounds__(128) sample_minibatch_kernel(unsigned long long seed, int it, const int* __restrict__ peer_ids,
+                                                               int P, int Ns, int B, int* __restrict__ idx) {
+  const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (w >= P) return;
+  const uint32_t peer = peer_ids ? (uint32_t)peer_ids[w] : (uint32_t)w;
+  uint32_t key[SMB_MAXK];
+#pragma unroll
+  for (int k = 0; k < SMB_MAXK; k++) {
+    const int r = lane + 32 * k;
+    key[k] = 0xffffffffu;
+    if (r < Ns) {
+      const Philox4 ph = philox4x32_10((uint32_t)r, (uint32_t)it, peer, 0x6d696e69u, (uint32_t)seed, (uint32_t)(seed >> 32));
+      key[k] = ph.x >> 1;   // 31 bits: 0xffffffff stays reserved for "taken / out of range"
+    }
+  }
+  for (int b = 0; b < B; b++) {
+    unsigned long long best = ~0ull;
+#pragma unroll
+    for (int k = 0; k < SMB_MAXK; k++) {
+      const unsigned long long c = ((unsigned long long)key[k] << 32) | (unsigned)(lane + 32 * k);
+      best = c < best ? c : best;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+      best = other < best ? other : best;
+    }
+    const int row = (int)(best & 0xffffffffu);
+    if (lane == (row & 31)) {
+#pragma unroll
+      for (int k = 0; k < SMB_MAXK; k++)
+        if (k == (row >> 5)) key[k] = 0xffffffffu;
+    }
+    if (lane == 0) idx[(size_t)w * B + b] = row;
+  }
 }
 
 // raw noise table row (RequestNoise parity + tests): out[k] = scale * N(0,1)(peer, slot, k)
@@ -518,8 +568,25 @@ int bsc_noise_mix(const float* U, const int* noisers, int nn, unsigned long long
                   float* Un, void* hi, void* lo, float* norms, int P, int d, int ldu, int ldh, void* stream) {
   if (nn > 62) return -1;
   noise_mix_kernel<<<P, 256, 0, (cudaStream_t)stream>>>(U, noisers, nn, seed, slot, noise_scale, Un,
-                                                         (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, norms, d, ldu, ldh);
+                                                         (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, norms, d, ldu, ldh, nullptr);
   return finish_launch("noise_mix");
+}
+// Same, with the bf16 planes and norms of peer p written to row dst_row[p] (skipped when negative): the Krum
+// candidates come out compacted in Krum order and the Gram kernel reads them without a gather.
+int bsc_noise_mix_rows(const float* U, const int* noisers, int nn, unsigned long long seed, int slot, float noise_scale,
+                       float* Un, void* hi, void* lo, float* norms, int P, int d, int ldu, int ldh, const int* dst_row,
+                       void* stream) {
+  if (nn > 62) return -1;
+  noise_mix_kernel<<<P, 256, 0, (cudaStream_t)stream>>>(U, noisers, nn, seed, slot, noise_scale, Un,
+                                                         (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, norms, d, ldu, ldh, dst_row);
+  return finish_launch("noise_mix");
+}
+
+// idx[p][0..B) = B distinct rows in [0, Ns) for peer peer_ids[p] (or p) at iteration `it`; Ns <= 1024, B <= Ns.
+int bsc_sample_minibatch(unsigned long long seed, int it, const int* peer_ids, int P, int Ns, int B, int* idx, void* stream) {
+  if (Ns > 32 * SMB_MAXK || B > Ns || B < 1 || P < 1) return -1;
+  sample_minibatch_kernel<<<(P + 3) / 4, 128, 0, (cudaStream_t)stream>>>(seed, it, peer_ids, P, Ns, B, idx);
+  return finish_launch("sample_minibatch");
 }
 
 int bsc_noise_row(float* out, int d, unsigned long long seed, int peer, int slot, float scale, void* stream) {

@@ -117,7 +117,7 @@ def noise_row(d: int, seed: int, peer: int, slot: int, scale: float, device="cpu
 
 
 def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_planes: bool = True, ldh=None,
-              out_hi=None, out_lo=None):
+              out_hi=None, out_lo=None, dst_row=None, want_un: bool = True):
     """Un = U + mean_q noise(q); returns (Un fp32 [P,ldu], hi bf16 [P,ldh], lo bf16 [P,ldh], norms [P]).
     noisers: int32 [P, nn] global ids (-1 = unused slot)."""
     P, ldu = U.shape
@@ -138,7 +138,7 @@ def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_plane
             hi = torch.nn.functional.pad(hi, (0, pad))
             lo = torch.nn.functional.pad(lo, (0, pad))
         return Un, hi.contiguous(), lo.contiguous(), (Un[:, :d] ** 2).sum(dim=1)
-    Un = torch.empty_like(U)
+    Un = torch.empty_like(U) if want_un else None
     if out_hi is not None:      # caller-provided planes (rows >= P), e.g. views into symmetric peer memory
         hi, lo = out_hi, out_lo
         ldh = hi.stride(0)
@@ -146,6 +146,12 @@ def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_plane
         hi = torch.empty(P, ldh, dtype=torch.bfloat16, device=U.device) if want_planes else None
         lo = torch.empty(P, ldh, dtype=torch.bfloat16, device=U.device) if want_planes else None
     norms = torch.empty(P, dtype=torch.float32, device=U.device)
+    if dst_row is not None:
+        # (CUDA only) planes / norms of peer p go to row dst_row[p] (< 0: none): compact, Krum-ordered candidates
+        check(lib().bsc_noise_mix_rows(ptr(U), ptr(noisers), nn, ctypes.c_ulonglong(seed & (2**64 - 1)), slot,
+                                       ctypes.c_float(scale), ptr(Un), ptr(hi), ptr(lo), ptr(norms), P, d, ldu, ldh,
+                                       ptr(dst_row), stream(U.device)), "noise_mix")
+        return Un, hi, lo, norms
     check(lib().bsc_noise_mix(ptr(U), ptr(noisers), nn, ctypes.c_ulonglong(seed & (2**64 - 1)), slot,
                               ctypes.c_float(scale), ptr(Un), ptr(hi), ptr(lo), ptr(norms), P, d, ldu, ldh,
                               stream(U.device)), "noise_mix")

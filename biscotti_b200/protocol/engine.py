@@ -152,6 +152,29 @@ class BiscottiEngine:
             view.copy_(torch.as_tensor(values, dtype=dtype))
         return view.to(self.device, non_blocking=True)
 
+    def _idx_pack(self, *specs):
+        """Several small host lists -> device tensors with ONE staging copy.  specs: (values, dtype) pairs; each
+        tensor starts on a 16-byte boundary of the shared buffer."""
+        if self.device.type != "cuda":
+            return [torch.tensor(v, dtype=dt) for v, dt in specs]
+        if not hasattr(self, "_pack_stage"):
+            self._pack_stage = [torch.empty(1 << 16, dtype=torch.uint8).pin_memory() for _ in range(8)]
+            self._pack_i = 0
+        buf = self._pack_stage[self._pack_i % len(self._pack_stage)]
+        self._pack_i += 1
+        offs, off = [], 0
+        for v, dt in specs:
+            nb = len(v) * torch.empty(0, dtype=dt).element_size()
+            offs.append((off, nb))
+            off = (off + nb + 15) // 16 * 16
+        if off > buf.numel():
+            return [self._idx(v, dt) for v, dt in specs]
+        for (o, nb), (v, dt) in zip(offs, specs):
+            if nb:
+                buf[o: o + nb].view(dt).copy_(torch.as_tensor(v, dtype=dt))
+        dev_buf = buf[: max(off, 16)].to(self.device, non_blocking=True)
+        return [dev_buf[o: o + nb].view(dt) for (o, nb), (v, dt) in zip(offs, specs)]
+
     # ------------------------------------------------------------------------------------------
     def select_roles(self):
         cfg = self.cfg
@@ -168,6 +191,15 @@ class BiscottiEngine:
         Ns, B = self.cfg.shard_size, self.cfg.batch_size
         n = self.cfg.num_nodes
         it = self.iteration if it is None else it
+        if self.device.type == "cuda" and Ns <= 1024 and self.P and not self.external_inputs:
+            # one kernel, keyed by (seed, iteration, peer, row): no generator state, no top-k, same rows on any rank
+            if not hasattr(self, "_mb_idx"):
+                self._mb_idx = torch.empty(self.P, B, dtype=torch.int32, device=self.device)
+            from ..ops._call import lib, ptr, stream, check
+
+            check(lib().bsc_sample_minibatch(self.cfg.seed & (2**64 - 1), it, ptr(self.data.peer_ids), self.P, Ns, B,
+                                             ptr(self._mb_idx), stream(self.device)), "sample_minibatch")
+            return self._mb_idx
         # One seeded draw for ALL n peers (so the result does not depend on how peers are sharded over
         # ranks), generated on the engine's device; each rank keeps the rows of its own peers.
         if not hasattr(self, "_mb_gen"):
@@ -349,9 +381,19 @@ class BiscottiEngine:
                 if self.colluder_ids:
                     noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
             scale = cfg.noise_scale if use_noise else 0.0
+            # Single-rank tcgen05 Krum: the kernel writes the candidates' bf16 planes and norms compacted and in Krum
+            # order (row = position in krum_set), so the Gram kernel needs no gather; the fp32 noised rows are only
+            # materialised for the paths that read them (RONI, SIMT Gram, NCCL gathers).
+            self._compact = (dev.type == "cuda" and self.comm is None and cfg.verification and cfg.defense != "RONI"
+                             and cfg.gram_impl in ("auto", "tcgen05") and len(krum_set) >= 3)
+            dst_row = None
+            if self._compact:
+                kpos = {p: i for i, p in enumerate(krum_set)}
+                dst_row = self._idx([kpos.get(p, -1) for p in self.local_ids])
             Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab.to(dev, non_blocking=True), cfg.seed, slot, scale, self.d,
                                              ldh=self.ldh, out_hi=self.comm.hi if self.fused else None,
-                                             out_lo=self.comm.lo if self.fused else None)
+                                             out_lo=self.comm.lo if self.fused else None, dst_row=dst_row,
+                                             want_un=not self._compact)
 
         # ---- 5. verification
         accepted: list[int] = []
@@ -385,7 +427,12 @@ class BiscottiEngine:
             return self._finish_block(rep, [], None, phases, t0)   # main.go:2099-2117
         rep.n_contributors = len(contributors)
         local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
-        sel = self._idx(local_contrib)
+        appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
+        pos = {r: i for i, r in enumerate(appr_rows)}          # positions of contributors inside the approved list
+        xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
+        sel, appr_local, csel, xs_t, av_t = self._idx_pack(
+            (local_contrib, torch.int32), (appr_rows, torch.int32), ([pos[r] for r in local_contrib], torch.int32),
+            (xs, torch.int32), (shares_avail, torch.uint8))
         agg_box = [None]
         launch_witnesses = None
         if cfg.secure_agg:
@@ -395,10 +442,6 @@ class BiscottiEngine:
                 # Nothing that enters the block depends on them, so they are *queued after* the share aggregation,
                 # the reconstruction and the block's device->host collection (see after_copies below): the device
                 # works on them while the host assembles, signs and hashes the block.
-                appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
-                appr_local = self._idx(appr_rows)
-                pos = {r: i for i, r in enumerate(appr_rows)}      # positions of contributors inside the approved list
-                csel = self._idx([pos[r] for r in local_contrib])
 
                 def launch_witnesses():
                     side = self._witness_side()
@@ -425,7 +468,6 @@ class BiscottiEngine:
                         for t in (Q, chunkC, appr_local, csel, sel):  # allocated on the main stream, read on `side`
                             t.record_stream(side)
             with self._phase("secagg"):
-                xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
                 if self.fused:
                     # reduce-scatter + reconstruct + SGD step + all-gather in one kernel over peer memory
                     if sel.numel():
@@ -439,8 +481,6 @@ class BiscottiEngine:
                     if self.comm is not None:
                         Ysum = self.comm.all_reduce_i64(Ysum)
                     self._last_ysum = Ysum
-                    xs_t = self._idx(xs)
-                    av_t = self._idx(shares_avail, torch.uint8)
                     _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
         else:
             with self._phase("secagg"):
@@ -543,6 +583,8 @@ class BiscottiEngine:
         clip = int(math.floor(cfg.krum_adversary_frac * nk))
         if self.fused:
             _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1)
+        elif getattr(self, "_compact", False):
+            _, acc, _ = krum_ops.krum(hi[:nk], self.d, clip, hi[:nk], lo[:nk], norms[:nk], impl=cfg.gram_impl)
         else:
             ix = self._idx([self.local_index[p] for p in krum_set], torch.int64) if self.comm is None else None
             Uk = self._gather_rows(krum_set, Un, ix)

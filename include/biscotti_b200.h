@@ -29,6 +29,13 @@ int bsc_local_logistic_step(const float* w, const float* X, const float* y, cons
 
 int bsc_noise_mix(const float* U, const int* noisers, int nn, unsigned long long seed, int slot, float noise_scale, float* Un, void* hi, void* lo, float* norms, int P, int d, int ldu, int ldh, void* stream);
 
+// Same, with the bf16 planes and norms of peer p written to row dst_row[p] (skipped when negative): the Krum
+// candidates come out compacted in Krum order and the Gram kernel reads them without a gather.
+int bsc_noise_mix_rows(const float* U, const int* noisers, int nn, unsigned long long seed, int slot, float noise_scale, float* Un, void* hi, void* lo, float* norms, int P, int d, int ldu, int ldh, const int* dst_row, void* stream);
+
+// idx[p][0..B) = B distinct rows in [0, Ns) for peer peer_ids[p] (or p) at iteration `it`; Ns <= 1024, B <= Ns.
+int bsc_sample_minibatch(unsigned long long seed, int it, const int* peer_ids, int P, int Ns, int B, int* idx, void* stream);
+
 int bsc_noise_row(float* out, int d, unsigned long long seed, int peer, int slot, float scale, void* stream);
 
 // host restatement of the same generator (CPU path + oracle)

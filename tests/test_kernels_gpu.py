@@ -321,3 +321,29 @@ def test_eval_on_tensor_cores_matches_fp32_oracle(M, N, F, C, with_base, monkeyp
     assert float((tc - ref).abs().max()) * N <= 2.5, (tc * N, ref * N)
     assert float((simt - ref).abs().max()) * N <= 2.5
     assert float(ref[0]) < 0.5 or C > 10
+
+
+def test_minibatch_sampler_kernel_draws_distinct_uniform_rows(lib):
+    """sample_minibatch_kernel: B distinct rows per peer, a function of (seed, iteration, peer) only, uniform."""
+    from biscotti_b200.ops._call import ptr, stream
+
+    P, Ns, B = 64, 600, 10
+    ids = torch.arange(100, 100 + P, dtype=torch.int32, device=DEV)
+    out = torch.empty(P, B, dtype=torch.int32, device=DEV)
+
+    def draw(seed, it, pid=ids, n=P):
+        assert lib.bsc_sample_minibatch(seed, it, ptr(pid), n, Ns, B, ptr(out), stream(torch.device(DEV))) == 0
+        return out[:n].cpu().clone()
+
+    a = draw(7, 3)
+    assert int(a.min()) >= 0 and int(a.max()) < Ns
+    assert all(len(set(r.tolist())) == B for r in a)
+    assert torch.equal(a, draw(7, 3)) and not torch.equal(a, draw(7, 4)) and not torch.equal(a, draw(8, 3))
+    sub = draw(7, 3, ids[5:9].contiguous(), 4)                      # a peer's rows do not depend on who else is drawn
+    assert torch.equal(sub, a[5:9])
+    counts = torch.zeros(Ns)
+    for it in range(200):
+        counts += torch.bincount(draw(1, it).flatten().long(), minlength=Ns).float()
+    expect = 200 * P * B / Ns
+    assert float((counts - expect).abs().max()) < 6 * expect ** 0.5   # every row is drawn about equally often
+    assert lib.bsc_sample_minibatch(1, 0, ptr(ids), P, 2000, B, ptr(out), stream(torch.device(DEV))) == -1
