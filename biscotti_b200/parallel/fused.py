@@ -178,7 +178,14 @@ class FusedComm(NcclComm):
                                           self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
                                           self.ldg, c_p(self.base + self.o_lpart), c_p(self.base + self.o_cnt), self._gram_seq,
                                           epoch, self._stream()), "krum_gram_fused")
-        rows = torch.tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+        # slot indices through a small persistent pinned ring (a fresh pin_memory() per block costs ~30 us)
+        if not hasattr(self, "_rows_stage"):
+            self._rows_stage = [torch.empty(1024, dtype=torch.int32).pin_memory() for _ in range(8)]
+            self._rows_i = 0
+        st = self._rows_stage[self._rows_i % 8][:n]
+        self._rows_i += 1
+        st.copy_(torch.as_tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32))
+        rows = st.to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)
         if hasattr(self.L, "bsc_krum_select_mc_wait"):
