@@ -161,8 +161,9 @@ def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_plane
 # ---------------------------------------------------------------------------------------------
 # evaluation
 # ---------------------------------------------------------------------------------------------
-def eval_softmax_errors(Wc, base, X, y, n_classes: int):
-    """Misclassification rate of each candidate row of Wc (+ base) on (X, y). Wc: [M, >=d]."""
+def eval_softmax_errors(Wc, base, X, y, n_classes: int, wrong_out=None):
+    """Misclassification rate of each candidate row of Wc (+ base) on (X, y). Wc: [M, >=d].
+    wrong_out (CUDA): zero-filled int32 [M] to accumulate into; the raw counts are returned instead of rates."""
     M = Wc.shape[0]
     N, F = X.shape
     C = n_classes
@@ -172,7 +173,7 @@ def eval_softmax_errors(Wc, base, X, y, n_classes: int):
             W = W + base[: C * F + C].float()
         logits = torch.einsum("nf,mcf->mnc", X.float(), W[:, : C * F].reshape(M, C, F)) + W[:, None, C * F:]
         return (logits.argmax(-1) != y.long()[None]).float().mean(dim=1)
-    wrong = torch.zeros(M, dtype=torch.int32, device=X.device)
+    wrong = torch.zeros(M, dtype=torch.int32, device=X.device) if wrong_out is None else wrong_out
     # tcgen05 path for batches of candidates (RONI, sweeps): 10x at M = 70, 28x at M = 280 (124 TFLOP/s useful).  A
     # single candidate is 25 MFLOP and three launches on that path vs one on the SIMT kernel (54 vs 43 us), so the
     # per-block test-error / attack-rate evaluation stays on the SIMT kernel.  BISCOTTI_EVAL_IMPL=tc|simt forces one.
@@ -182,7 +183,7 @@ def eval_softmax_errors(Wc, base, X, y, n_classes: int):
     else:
         check(lib().bsc_eval_softmax(ptr(Wc), ptr(base), ptr(X), ptr(y), ptr(wrong), M, N, F, C, Wc.stride(0),
                                      stream(X.device)), "eval_softmax")
-    return wrong.float() / N
+    return wrong if wrong_out is not None else wrong.float() / N
 
 
 _x_planes: dict = {}     # sample matrices are static (test / attack sets): their bf16x3 planes are built once
@@ -220,7 +221,7 @@ def _eval_softmax_tc(Wc, base, X, y, wrong, M, N, F, C):
                         ptr(wrong), N, M, stream(dev)), "eval_tc")
 
 
-def eval_logistic_errors(Wc, base, X, y):
+def eval_logistic_errors(Wc, base, X, y, wrong_out=None):
     M = Wc.shape[0]
     N, F = X.shape
     if not X.is_cuda:
@@ -229,7 +230,7 @@ def eval_logistic_errors(Wc, base, X, y):
             W = W + base[:F].float()
         pred = torch.where(X.float() @ W.t() >= 0, 1.0, -1.0)  # [N, M]
         return (pred != y.float()[:, None]).float().mean(dim=0)
-    wrong = torch.zeros(M, dtype=torch.int32, device=X.device)
+    wrong = torch.zeros(M, dtype=torch.int32, device=X.device) if wrong_out is None else wrong_out
     check(lib().bsc_eval_logistic(ptr(Wc), ptr(base), ptr(X), ptr(y), ptr(wrong), M, N, F, Wc.stride(0),
                                   stream(X.device)), "eval_logistic")
-    return wrong.float() / N
+    return wrong if wrong_out is not None else wrong.float() / N

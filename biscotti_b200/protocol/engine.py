@@ -363,7 +363,8 @@ class BiscottiEngine:
             sig_handle = self.signer.launch(np.tile(self._sk_mat[signers], (nk, 1)), tags.view(np.uint8).reshape(nk * ns, 16))
         # ---- 4. noisers + noise
         with self._phase("noise"):
-            noiser_tab = torch.full((max(1, self.P), max(1, cfg.num_noisers)), -1, dtype=torch.int32)
+            nn_cols = max(1, cfg.num_noisers)
+            tab_np = np.full((max(1, self.P), nn_cols), -1, dtype=np.int32)
             noisers_of = {}
             if use_noise:
                 stake = [s if a else 0 for s, a in zip(self.stake, self.alive)]
@@ -372,12 +373,7 @@ class BiscottiEngine:
                 full_tab = self.vrf.noiser_table(vrf_handle, stake, is_worker, cfg.num_noisers)   # [n, nn]
                 if self.P:
                     lo_id = self.local_ids[0]
-                    noiser_tab = torch.from_numpy(full_tab[lo_id: lo_id + self.P].copy())
-                    if dev.type == "cuda":
-                        if not hasattr(self, "_nz_pinned"):
-                            self._nz_pinned = torch.empty_like(noiser_tab).pin_memory()
-                        self._nz_pinned.copy_(noiser_tab)
-                        noiser_tab = self._nz_pinned
+                    tab_np = full_tab[lo_id: lo_id + self.P]
                 if self.colluder_ids:
                     noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
             scale = cfg.noise_scale if use_noise else 0.0
@@ -386,11 +382,14 @@ class BiscottiEngine:
             # materialised for the paths that read them (RONI, SIMT Gram, NCCL gathers).
             self._compact = (dev.type == "cuda" and self.comm is None and cfg.verification and cfg.defense != "RONI"
                              and cfg.gram_impl in ("auto", "tcgen05") and len(krum_set) >= 3)
-            dst_row = None
-            if self._compact:
-                kpos = {p: i for i, p in enumerate(krum_set)}
-                dst_row = self._idx([kpos.get(p, -1) for p in self.local_ids])
-            Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab.to(dev, non_blocking=True), cfg.seed, slot, scale, self.d,
+            kpos = {p: i for i, p in enumerate(krum_set)}
+            rows = [kpos.get(p, -1) for p in self.local_ids] if self._compact else []
+            # noiser table and row map travel in one staging copy
+            noiser_tab, dst_row = self._idx_pack((tab_np.reshape(-1), torch.int32), (rows, torch.int32))
+            noiser_tab = noiser_tab.view(-1, nn_cols)
+            if not self._compact:
+                dst_row = None
+            Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab, cfg.seed, slot, scale, self.d,
                                              ldh=self.ldh, out_hi=self.comm.hi if self.fused else None,
                                              out_lo=self.comm.lo if self.fused else None, dst_row=dst_row,
                                              want_un=not self._compact)
@@ -633,6 +632,26 @@ class BiscottiEngine:
 
     def _launch_eval(self):
         """Queue the error-rate kernels and their read-back; _finish_block picks the numbers up."""
+        if self.device.type == "cuda" and self.model.kind in ("softmax", "logistic"):
+            # both error counts into one persistent int32[2], one read-back; the rates are formed on the host
+            if not hasattr(self, "_ev_cnt"):
+                self._ev_cnt = torch.zeros(2, dtype=torch.int32, device=self.device)
+                self._ev_cnt_pinned = torch.zeros(2, dtype=torch.int32).pin_memory()
+                self._eval_ev = torch.cuda.Event()
+            self._ev_cnt.zero_()
+            w = self.w32.unsqueeze(0)
+            d = self.data
+            if self.model.kind == "softmax":
+                C = self.cfg.spec.n_classes
+                ml.eval_softmax_errors(w, None, d.X_test, d.y_test, C, wrong_out=self._ev_cnt[0:1])
+                ml.eval_softmax_errors(w, None, d.X_attack, d.y_attack, C, wrong_out=self._ev_cnt[1:2])
+            else:
+                ml.eval_logistic_errors(w, None, d.X_test, d.y_test, wrong_out=self._ev_cnt[0:1])
+                ml.eval_logistic_errors(w, None, d.X_attack, d.y_attack, wrong_out=self._ev_cnt[1:2])
+            self._ev_cnt_pinned.copy_(self._ev_cnt, non_blocking=True)
+            self._eval_ev.record()
+            self._eval_pending = ("counts", self._ev_cnt_pinned, self._eval_ev, d.X_test.shape[0], d.X_attack.shape[0])
+            return
         te, ar = self.evaluate()
         if self.device.type != "cuda":
             self._eval_pending = (te.detach().cpu(), ar.detach().cpu(), None)
@@ -695,7 +714,11 @@ class BiscottiEngine:
             if self.device.type == "cuda" and cfg.mode != "fedsys" and cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
                 self._vrf_early = (rep.block_hash, self.vrf.launch(rep.block_hash))
         pend, self._eval_pending = self._eval_pending, None
-        if pend is not None:
+        if pend is not None and isinstance(pend[0], str):      # ("counts", pinned int32[2], event, n_test, n_attack)
+            pend[2].synchronize()
+            cnt = pend[1].numpy()
+            host = dict(host, te=[cnt[0] / max(1, pend[3])], ar=[cnt[1] / max(1, pend[4])])
+        elif pend is not None:
             if pend[2] is not None:
                 pend[2].synchronize()
             host = dict(host, te=pend[0].numpy(), ar=pend[1].numpy())
