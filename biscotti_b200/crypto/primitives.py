@@ -142,7 +142,10 @@ class BatchedVRF:
     def launch(self, msg: bytes):
         L = _L()
         n = len(self.keys)
-        hxy = torch.empty(64, dtype=torch.uint8)
+        if self.device.type == "cuda" and hasattr(self, "_side"):
+            hxy = self._hpt_pinned          # hash-to-curve writes straight into the pinned staging buffer
+        else:
+            hxy = torch.empty(64, dtype=torch.uint8)
         L.bsc_vrf_hash_to_curve_xy(msg, len(msg), ctypes.c_void_p(hxy.data_ptr()))
         if self.device.type != "cuda":
             gam = torch.empty(n, 32, dtype=torch.uint8)
@@ -158,7 +161,8 @@ class BatchedVRF:
             self._gam = torch.empty(n, 32, dtype=torch.uint8, device=self.device)
             self._xyz = torch.empty(n, 30, dtype=torch.int32, device=self.device)
             self._host_xyz = torch.empty(n, 30, dtype=torch.int32).pin_memory()
-        self._hpt_pinned.copy_(hxy)
+        if hxy is not self._hpt_pinned:
+            self._hpt_pinned.copy_(hxy)
         # No wait on the compute stream: the kernel reads only the static secret scalars and the point copied here,
         # so it may run beside whatever the main stream still has queued (the prefetched local step / commitment MSM).
         with torch.cuda.stream(self._side):
@@ -178,7 +182,9 @@ class BatchedVRF:
                 self._host_gam.copy_(self._gam, non_blocking=True)
             if rc:
                 raise RuntimeError("ed25519 scalar multiplication kernel failed")
-            ev = torch.cuda.Event()
+            if not hasattr(self, "_ev"):
+                self._ev = torch.cuda.Event()    # one launch in flight at a time: the event is reused
+            ev = self._ev
             ev.record(self._side)
         return (self._host_gam, ev, msg)
 

@@ -75,23 +75,30 @@ class SchnorrBatchSigner:
             # side stream: the comb kernel is a single small CTA-wave and runs under the witness MSM.  It does not
             # wait for the compute stream (its inputs are the nonces uploaded here and the static comb table), so
             # it starts at once even though the witness / aggregation kernels were queued first.
+            # persistent device buffers (one launch per block; the previous block's results were read back, with a
+            # host-side wait, before this launch) instead of four allocations + record_stream calls per block
+            if getattr(self, "_cap", 0) < n:
+                self._cap = max(256, 2 * n)
+                with torch.cuda.stream(self._side):
+                    self._k_dev = torch.empty(self._cap, 8, dtype=torch.int32, device=self.device)
+                    self._jac = torch.empty(self._cap, JAC, dtype=torch.int32, device=self.device)
+                    self._aff = torch.empty(self._cap, AFF, dtype=torch.int32, device=self.device)
+                    self._T = torch.empty(self._cap, 64, dtype=torch.uint8, device=self.device)
+                self._event = torch.cuda.Event()
             with torch.cuda.stream(self._side):
                 stream = ctypes.c_void_p(self._side.cuda_stream)
-                k = kp.to(self.device, non_blocking=True)
-                jac = torch.empty(n, JAC, dtype=torch.int32, device=self.device)
+                k = self._k_dev[:n]
+                k.copy_(kp, non_blocking=True)
                 rc = L.bsc_g1_comb_mul(ctypes.c_void_p(k.data_ptr()), n, ctypes.c_void_p(self._table.data_ptr()), W_BITS,
-                                       N_WIN, ctypes.c_void_p(jac.data_ptr()), stream)
+                                       N_WIN, ctypes.c_void_p(self._jac.data_ptr()), stream)
                 assert rc == 0, rc
-                aff = torch.empty(n, AFF, dtype=torch.int32, device=self.device)
-                assert L.bsc_g1_normalize(ctypes.c_void_p(jac.data_ptr()), ctypes.c_void_p(aff.data_ptr()), n, stream) == 0
-                T_dev = torch.empty(n, 64, dtype=torch.uint8, device=self.device)
-                assert L.bsc_g1_affine_to_bytes(ctypes.c_void_p(aff.data_ptr()), ctypes.c_void_p(T_dev.data_ptr()), n,
+                assert L.bsc_g1_normalize(ctypes.c_void_p(self._jac.data_ptr()), ctypes.c_void_p(self._aff.data_ptr()), n,
+                                          stream) == 0
+                T_dev = self._T[:n]
+                assert L.bsc_g1_affine_to_bytes(ctypes.c_void_p(self._aff.data_ptr()), ctypes.c_void_p(T_dev.data_ptr()), n,
                                                 stream) == 0
-                event = torch.cuda.Event()
+                event = self._event
                 event.record(self._side)
-            for t in (k, jac, aff, T_dev):
-                t.record_stream(self._side)
-            self._keep = (k, jac, aff)
         return dict(n=n, x=x, vw=vw, vbe=vbe, T_dev=T_dev, event=event)
 
     def select(self, handle, rows: list[int], T_host: np.ndarray | None = None):
