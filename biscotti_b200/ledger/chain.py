@@ -186,6 +186,24 @@ class Blockchain:
         self._L.bsc_chain_append(self._h, b, timestamp)
         return self.latest_hash()
 
+    def add_commit_block(self, iteration: int, weights, sources, commitments: bytes, signatures: bytes, n_sigs: int,
+                         stake, timestamp: int = -1) -> bytes:
+        """add_block for the common secure-aggregation block, without per-update Python objects: every update is
+        (source, iteration, 64-byte commitment, n_sigs 64-byte signatures, accepted).  Byte-identical to add_block
+        with the equivalent UpdateRecord list."""
+        w, d = _f64(weights)
+        b = self._L.bsc_block_new(iteration, w.ctypes.data_as(c_p), d)
+        src = np.ascontiguousarray(sources, dtype=np.int32)
+        n = len(src)
+        if n:
+            self._L.bsc_block_add_commit_updates(b, n, src.ctypes.data_as(c_p), iteration, commitments or None,
+                                                 len(commitments) // n, signatures or None, n_sigs, 64 if n_sigs else 0)
+        vals = np.asarray(stake, dtype=np.int32)
+        ids = np.arange(len(vals), dtype=np.int32)
+        self._L.bsc_block_set_stake(b, ids.ctypes.data_as(c_p), vals.ctypes.data_as(c_p), len(vals))
+        self._L.bsc_chain_append(self._h, b, timestamp)
+        return self.latest_hash()
+
     def verify(self) -> bool:
         return bool(self._L.bsc_chain_verify(self._h))
 

@@ -541,7 +541,15 @@ class BiscottiEngine:
                 rows = [kpos[p] * len(signers) + j for p in contributors for j in range(len(signers))]
                 all_sigs = self.signer.finish(self.signer.select(sig_handle, rows, host.get("sigT")), msgs)
             nv = len(signers)
-            for ci, p in enumerate(contributors):
+            fast = None
+            if (cfg.secure_agg and contributors and all(len(commits.get(p, b"")) == 64 for p in contributors)
+                    and (all_sigs is not None or sig_handle is None)):
+                # the common block: (source, commitment, approvals) per update, handed to the ledger as three arrays
+                fast = (contributors, b"".join(commits[p] for p in contributors),
+                        b"".join(all_sigs) if all_sigs else b"", nv if all_sigs else 0)
+                for p in contributors:
+                    self.stake[p] += STAKE_UNIT
+            for ci, p in enumerate(contributors if fast is None else ()):
                 c = commits.get(p, b"")
                 sigs = all_sigs[ci * nv: (ci + 1) * nv] if all_sigs is not None else []
                 rec = UpdateRecord(source=p, iteration=it, commitment=c, accepted=True, signatures=sigs)
@@ -554,7 +562,7 @@ class BiscottiEngine:
                     if p not in accepted:
                         self.stake[p] -= STAKE_UNIT                      # honest.go:362-370 (plain path only)
             rep.bad_shares = int(host["bad"].sum())
-        return self._finish_block(rep, updates, agg_box[0], phases, t0, host)
+        return self._finish_block(rep, updates, agg_box[0], phases, t0, host, fast)
 
     # ------------------------------------------------------------------------------------------
     def _available_shares(self, miners, alive_miners):
@@ -697,7 +705,7 @@ class BiscottiEngine:
             self._collect_ev.synchronize()
         return {k: b.numpy() for k, b in out.items()}
 
-    def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0, host=None) -> BlockReport:
+    def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0, host=None, fast=None) -> BlockReport:
         cfg = self.cfg
         it = self.iteration
         with self._phase("block"):
@@ -706,9 +714,14 @@ class BiscottiEngine:
                 if cfg.eval_every and (it % cfg.eval_every == 0):
                     want["te"], want["ar"] = self.evaluate()
                 host = self._collect(want)
-            ts = (0 if not updates else 1 + it) if cfg.deterministic_time else -1
-            rep.block_hash = self.chain.add_block(it, host["w"], updates, self.stake, timestamp=ts)
-            rep.empty = not updates
+            nonempty = bool(updates) or fast is not None
+            ts = (1 + it if nonempty else 0) if cfg.deterministic_time else -1
+            if fast is not None:
+                rep.block_hash = self.chain.add_commit_block(it, host["w"], fast[0], fast[1], fast[2], fast[3], self.stake,
+                                                             timestamp=ts)
+            else:
+                rep.block_hash = self.chain.add_block(it, host["w"], updates, self.stake, timestamp=ts)
+            rep.empty = not nonempty
             # The next block's noiser lottery hangs on this hash: start every peer's VRF now rather than after the
             # bookkeeping below and the caller's loop overhead (the kernel is ~0.4 ms of pure latency).
             if self.device.type == "cuda" and cfg.mode != "fedsys" and cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:

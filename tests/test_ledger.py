@@ -65,3 +65,26 @@ def test_print_chain_format_and_go_floats():
     assert "Commitment:bn256.G1:(" in text
     assert go_float(0.1) == "0.1" and go_float(123456789.0) == "1.23456789e+08"
     assert go_float(1e-5) == "1e-05" and go_float(-2.5) == "-2.5" and go_float(100000.0) == "100000"
+
+
+def test_add_commit_block_is_byte_identical_to_update_records():
+    """The array-based fast path of the engine's common block must hash exactly like the UpdateRecord path."""
+    import numpy as np
+
+    from biscotti_b200.ledger.chain import Blockchain, UpdateRecord
+
+    rs = np.random.RandomState(3)
+    w = rs.randn(12)
+    srcs = [2, 5, 9]
+    commits = [bytes(rs.randint(0, 256, 64).astype(np.uint8)) for _ in srcs]
+    sigs = [[bytes(rs.randint(0, 256, 64).astype(np.uint8)) for _ in range(2)] for _ in srcs]
+    stake = [10 + i for i in range(6)]
+    a, b = Blockchain(12), Blockchain(12)
+    ha = a.add_block(0, w, [UpdateRecord(source=s, iteration=0, commitment=c, signatures=g) for s, c, g in zip(srcs, commits, sigs)],
+                     stake, timestamp=1)
+    hb = b.add_commit_block(0, w, srcs, b"".join(commits), b"".join(x for g in sigs for x in g), 2, stake, timestamp=1)
+    assert ha == hb and a == b and a.dump() == b.dump()
+    # without signatures
+    ha = a.add_block(1, w, [UpdateRecord(source=s, iteration=1, commitment=c) for s, c in zip(srcs, commits)], stake, timestamp=2)
+    hb = b.add_commit_block(1, w, srcs, b"".join(commits), b"", 0, stake, timestamp=2)
+    assert ha == hb and a.serialize() == b.serialize()
