@@ -46,6 +46,8 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--print-hash", action="store_true")
     ap.add_argument("--no-dump", action="store_true")
     ap.add_argument("--log", action="store_true", help="emit [peer] log lines on stderr")
+    ap.add_argument("--trace", default=None, metavar="FILE",
+                    help="instrument every phase (CUDA events) and write a Chrome/Perfetto trace; one file per rank")
     ap.add_argument("--save-chain", default=None)
     ap.add_argument("--partition", action="append", default=[], metavar="PEER:FIRST:LAST",
                     help="cut PEER off for blocks FIRST..LAST (blockNode.sh); may be repeated")
@@ -94,7 +96,14 @@ def run_localtest(a, mode: str) -> int:
             adopted = eng.adopt_chain(f.read())
         if rank == 0:
             print(f"resume: adopted={adopted} height={len(eng.chain)} next_iteration={eng.iteration}", file=sys.stderr)
+    if a.trace:
+        eng._timing = True                     # every phase bracketed by CUDA events (in-line schedule)
+        cfg.prefetch = False
     eng.run(max(0, cfg.max_iterations + 1 - eng.iteration))
+    if a.trace:
+        from .utils.trace import write_chrome_trace
+
+        write_chrome_trace(eng.reports, a.trace if world == 1 else f"{a.trace}.rank{rank}", rank)
     dump = eng.print_chain()
     dump_dir = os.environ.get("BISCOTTI_DUMP_DIR")
     if dump_dir:   # one PrintChain file per rank, for the reference-style pairwise `cmp` (deploy/local_test.sh)

@@ -161,3 +161,26 @@ def test_central_block_model_branching():
     assert sum(x["blocks"] for x in res["branches"]) >= 10
     quirk = cb.run_branching("creditcard", clients=8, poisoners=2, branches=2, rounds=3, metric="distance")
     assert quirk["choices"] != cb.run_branching("creditcard", clients=8, poisoners=2, branches=2, rounds=3)["choices"]
+
+
+def test_chrome_trace_of_an_instrumented_run(tmp_path):
+    """localtest --trace: one duration event per phase per block plus one per block, valid JSON for chrome://tracing."""
+    import json
+    import subprocess
+    import sys
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "trace.json"
+    r = subprocess.run([sys.executable, "-m", "biscotti_b200", "localtest", "10", "creditcard", "--iterations", "3",
+                        "--device", "cpu", "--shard-size", "100", "--no-dump", "--trace", str(out)],
+                       capture_output=True, text=True, cwd=root, env=dict(os.environ, PYTHONPATH=root), timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    tr = json.load(open(out))
+    ev = [e for e in tr["traceEvents"] if e.get("ph") == "X"]
+    blocks = [e for e in ev if e["cat"] == "block"]
+    phases = [e for e in ev if e["cat"] == "phase"]
+    assert len(blocks) == 4 and {"local_step", "noise", "verify", "block"} <= {e["name"] for e in phases}
+    assert all(e["dur"] >= 0 and e["ts"] >= 0 for e in ev)
+    starts = [e["ts"] for e in blocks]
+    assert starts == sorted(starts)
