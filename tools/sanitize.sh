@@ -6,6 +6,9 @@
 #
 # Runs the single-GPU kernel tests under the chosen tool on a GPU box, e.g. through
 #   gpurun --timeout 1500 -- 'tools/sanitize.sh racecheck "krum or secagg or noise"'
+# (On the shared B200 pool of this build compute-sanitizer is disabled — the launcher refuses it — so there the
+# checks of record are the bit-exact host mirrors of every kernel, the bounded flag / mbarrier waits that trap
+# instead of hanging, and the chain-equality tests; this script is for a box where the tool is allowed.)
 # The tcgen05 / TMA kernels are skipped by default under racecheck (shared-memory hazards there are ordered by
 # mbarriers, which racecheck does not model); pass an explicit -k expression to include them.
 set -u
