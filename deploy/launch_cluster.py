@@ -64,7 +64,8 @@ def main() -> int:
     hosts = read_hosts(a.hosts)
     if not hosts:
         ap.error("empty hosts file")
-    os.makedirs(a.logdir, exist_ok=True)
+    if not a.dry_run:
+        os.makedirs(a.logdir, exist_ok=True)
     ssh = shlex.split(a.ssh)
 
     if a.sync:
