@@ -63,7 +63,8 @@ void b2_compress(Blake2b& s, const uint8_t* block, bool last) {
   v[d] = rotr64(v[d] ^ v[a], 16);    \
   v[c] = v[c] + v[d];                \
   v[b] = rotr64(v[b] ^ v[c], 63);
-  for (int r = 0; r < 12; r++) {
+#pragma GCC unroll 12
+  for (int r = 0; r < 12; r++) {   // unrolled: the message schedule becomes compile-time register picks
     const uint8_t* sg = B2_SIGMA[r];
     B2G(0, 4, 8, 12, m[sg[0]], m[sg[1]]);
     B2G(1, 5, 9, 13, m[sg[2]], m[sg[3]]);
