@@ -324,14 +324,27 @@ __global__ void __launch_bounds__(256) cnn2_conv_wgrad_kernel(const float* __res
   if (tid == 0) partial[(size_t)p * nslots + slot0 + oc] = nrm;
 }
 
-// thread -> one input position (img, ic, y, x) of the second convolution: gathers the sparse gradient of the
-// conv output (non-zero only at arg-max positions) through the transposed filter, masked by the first
-// layer's ReLU (a1 = pooled activation of layer 1 = this layer's input)
+// Dense form of the second convolution's output gradient: dense[img][oc][oy][ox] = dp2 at the arg-max position of
+// each pooled cell, zero elsewhere (the caller zero-fills `dense`).  With it the data gradient below is a plain,
+// branch-free correlation instead of a per-tap arg-max test.
+__global__ void __launch_bounds__(256) cnn2_unpool_kernel(const float* __restrict__ dp2, const uint8_t* __restrict__ arg2,
+                                                          float* __restrict__ dense, int PH, int PW, int OH, int OW,
+                                                          long long total) {
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const float d = dp2[t];
+    if (d == 0.f) continue;
+    const int px = (int)(t % PW), py = (int)((t / PW) % PH);
+    const long long plane = t / ((long long)PW * PH);            // img * OC + oc
+    const int a = arg2[t];
+    dense[plane * OH * OW + (size_t)(2 * py + (a >> 1)) * OW + (2 * px + (a & 1))] = d;
+  }
+}
+// thread -> one input position (img, ic, y, x): g = sum_oc sum_taps dense[oc][y-ky+pad][x-kx+pad] * w[oc][ic][ky][kx],
+// masked by the first layer's ReLU (a1 > 0)
 template <int K>
-__global__ void __launch_bounds__(256) cnn2_dgrad_kernel(const float* __restrict__ wt, const float* __restrict__ dp2,
-                                                         const uint8_t* __restrict__ arg2, const float* __restrict__ a1,
-                                                         float* __restrict__ dp1, int IC, int H, int W, int OC, int pad,
-                                                         int PH, int PW, long long total) {
+__global__ void __launch_bounds__(256) cnn2_dgrad_dense_kernel(const float* __restrict__ wt, const float* __restrict__ dense,
+                                                               const float* __restrict__ a1, float* __restrict__ dp1, int IC,
+                                                               int H, int W, int OC, int pad, int OH, int OW, long long total) {
   extern __shared__ float sw[];
   const int nw = OC * IC * K * K;
   for (int i = threadIdx.x; i < nw; i += blockDim.x) sw[i] = wt[i];
@@ -345,23 +358,20 @@ __global__ void __launch_bounds__(256) cnn2_dgrad_kernel(const float* __restrict
     const int y = (int)((t / W) % H);
     const int ic = (int)((t / ((long long)W * H)) % IC);
     const long long img = t / ((long long)W * H * IC);
-    // conv outputs that read this input: oy in [y+pad-(K-1), y+pad]; they live in at most (K+1)/2+1 pooled rows.
-    // Each pooled cell carries one gradient at its arg-max position, so a cell costs one byte + one float load.
-    const int py0 = max(0, (y + pad - (K - 1)) >> 1), py1 = min(PH - 1, (y + pad) >> 1);
-    const int px0 = max(0, (x + pad - (K - 1)) >> 1), px1 = min(PW - 1, (x + pad) >> 1);
     float g = 0.f;
     for (int oc = 0; oc < OC; oc++) {
-      const size_t base = ((size_t)img * OC + oc) * PH * PW;
+      const float* dd = dense + ((size_t)img * OC + oc) * OH * OW;
       const float* wk = sw + (oc * IC + ic) * K * K;
-      for (int py = py0; py <= py1; py++)
-        for (int px = px0; px <= px1; px++) {
-          const size_t idx = base + py * PW + px;
-          const float d = dp2[idx];
-          if (d == 0.f) continue;
-          const int a = arg2[idx];
-          const int ky = y + pad - (2 * py + (a >> 1)), kx = x + pad - (2 * px + (a & 1));
-          if (ky >= 0 && ky < K && kx >= 0 && kx < K) g = fmaf(d, wk[ky * K + kx], g);
+#pragma unroll
+      for (int ky = 0; ky < K; ky++) {
+        const int oy = y - ky + pad;
+        if (oy < 0 || oy >= OH) continue;
+#pragma unroll
+        for (int kx = 0; kx < K; kx++) {
+          const int ox = x - kx + pad;
+          if (ox >= 0 && ox < OW) g = fmaf(dd[oy * OW + ox], wk[ky * K + kx], g);
         }
+      }
     }
     dp1[t] = g;
   }
@@ -441,7 +451,8 @@ long long bsc_cnn2_scratch_floats(int P, int B, int IC, int H, int W, int OC1, i
                                   int C) {
   const Cnn2Dims m = cnn2_dims(H, W, OC1, K1, pad1, OC2, K2, pad2);
   const long long PB = (long long)P * B;
-  return 2 * PB * m.n1 + PB * m.J + PB * C + (long long)P * m.nslots + P + (PB * m.n1 + 3) / 4 + (PB * m.J + 3) / 4 + 8;
+  return 2 * PB * m.n1 + PB * m.J + PB * C + (long long)P * m.nslots + P + (PB * m.n1 + 3) / 4 + (PB * m.J + 3) / 4 + 8 +
+         PB * OC2 * m.OH2 * m.OW2;   // + dense gradient of the second convolution's output
 }
 
 extern "C++" {
@@ -459,14 +470,6 @@ static void cnn2_launch_wgrad(const float* in, const float* dp, const uint8_t* a
                               int PH, int PW, cudaStream_t st) {
   cnn2_conv_wgrad_kernel<K, 3><<<dim3(OC, P), 256, 0, st>>>(in, dp, arg, U, ldu, off_w, off_b, partial, nslots, slot0, B, IC,
                                                             H, W, OC, pad, PH, PW);
-}
-template <int K>
-static void cnn2_launch_dgrad(const float* wt, const float* dp2, const uint8_t* arg2, const float* a1, float* dp1, int IC,
-                              int H, int W, int OC, int pad, int PH, int PW, long long total, cudaStream_t st) {
-  const long long blocks = (total + 255) / 256;
-  const int grid = (int)(blocks < 148 * 16 ? blocks : 148 * 16);
-  const size_t smem = (size_t)OC * IC * K * K * sizeof(float);
-  cnn2_dgrad_kernel<K><<<grid, 256, smem, st>>>(wt, dp2, arg2, a1, dp1, IC, H, W, OC, pad, PH, PW, total);
 }
 }  // extern "C++"
 #define CNN2_BY_K(K, call3, call5) \
@@ -502,6 +505,7 @@ int bsc_cnn2_local_step(const float* w, const float* X, const int* y, float* U, 
   float* coef = partial + (long long)P * nslots;
   uint8_t* arg1 = (uint8_t*)(coef + P);
   uint8_t* arg2 = arg1 + ((PB * m.n1 + 3) / 4) * 4;
+  float* dense = (float*)(arg2 + ((PB * m.J + 3) / 4) * 4 + 16);   // [PB][OC2][OH2][OW2]
   // forward
   CNN2_BY_K(K1, cnn2_launch_fwd<3>(w + off_w1, w + off_b1, X, pool1, arg1, IC, H, W, OC1, pad1, m.PH1, m.PW1, PB * m.n1, st),
             cnn2_launch_fwd<5>(w + off_w1, w + off_b1, X, pool1, arg1, IC, H, W, OC1, pad1, m.PH1, m.PW1, PB * m.n1, st));
@@ -513,13 +517,26 @@ int bsc_cnn2_local_step(const float* w, const float* X, const int* y, float* U, 
   cnn1_fc_bwd_kernel<<<dim3(nfc, P), 256, 0, st>>>(w, act, dl, U, ldu, partial, nslots, s);
   CNN2_BY_K(K2, cnn2_launch_wgrad<3>(pool1, act, arg2, U, ldu, off_w2, off_b2, partial, nslots, nfc, P, B, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, st),
             cnn2_launch_wgrad<5>(pool1, act, arg2, U, ldu, off_w2, off_b2, partial, nslots, nfc, P, B, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, st));
-  CNN2_BY_K(K2, cnn2_launch_dgrad<3>(w + off_w2, act, arg2, pool1, dp1, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, PB * m.n1, st),
-            cnn2_launch_dgrad<5>(w + off_w2, act, arg2, pool1, dp1, OC1, m.PH1, m.PW1, OC2, pad2, m.PH2, m.PW2, PB * m.n1, st));
+  {
+    // data gradient of the second convolution: expand the pooled gradient to its dense form, then a plain correlation
+    const long long nd = PB * OC2 * (long long)m.OH2 * m.OW2;
+    cudaMemsetAsync(dense, 0, (size_t)nd * sizeof(float), st);
+    const long long nj = PB * m.J;
+    const int g1 = (int)((nj + 255) / 256 < 148 * 16 ? (nj + 255) / 256 : 148 * 16);
+    cnn2_unpool_kernel<<<g1, 256, 0, st>>>(act, arg2, dense, m.PH2, m.PW2, m.OH2, m.OW2, nj);
+    const long long n1 = PB * m.n1;
+    const int g2 = (int)((n1 + 255) / 256 < 148 * 16 ? (n1 + 255) / 256 : 148 * 16);
+    const size_t smem = (size_t)OC2 * OC1 * K2 * K2 * sizeof(float);
+    if (K2 == 3)
+      cnn2_dgrad_dense_kernel<3><<<g2, 256, smem, st>>>(w + off_w2, dense, pool1, dp1, OC1, m.PH1, m.PW1, OC2, pad2, m.OH2, m.OW2, n1);
+    else
+      cnn2_dgrad_dense_kernel<5><<<g2, 256, smem, st>>>(w + off_w2, dense, pool1, dp1, OC1, m.PH1, m.PW1, OC2, pad2, m.OH2, m.OW2, n1);
+  }
   CNN2_BY_K(K1, cnn2_launch_wgrad<3>(X, dp1, arg1, U, ldu, off_w1, off_b1, partial, nslots, nfc + OC2, P, B, IC, H, W, OC1, pad1, m.PH1, m.PW1, st),
             cnn2_launch_wgrad<5>(X, dp1, arg1, U, ldu, off_w1, off_b1, partial, nslots, nfc + OC2, P, B, IC, H, W, OC1, pad1, m.PH1, m.PW1, st));
   cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
   cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s);
-  return finish_launch("cnn2_local_step", 10);
+  return finish_launch("cnn2_local_step", 11);
 }
 
 }  // extern "C"
