@@ -74,8 +74,8 @@ void put_bytes(std::string& o, const std::string& b) {
 
 // Canonical BlockData encoding ("BSCD1"): the hash preimage component that stands in for
 // gob(BlockData) (blockData.go:31-41).  Field order follows the Go struct order.
-std::string encode_block_data(const Block& b) {
-  std::string o = "BSCD1";
+void encode_block_data_to(std::string& o, const Block& b) {
+  o += "BSCD1";
   put_u64(o, (uint64_t)b.iteration);
   put_f64s(o, b.w);
   put_u32(o, (uint32_t)b.updates.size());
@@ -90,13 +90,19 @@ std::string encode_block_data(const Block& b) {
     put_u32(o, (uint32_t)u.signatures.size());
     for (const std::string& s : u.signatures) put_bytes(o, s);
   }
+}
+std::string encode_block_data(const Block& b) {
+  std::string o;
+  encode_block_data_to(o, b);
   return o;
 }
 
 void set_hash(Block& b) {
-  std::string pre = b.prev_hash;
+  std::string pre;
+  pre.reserve(128 + 8 * b.w.size() + 512 * b.updates.size());   // one buffer: no second copy of the weights
+  pre += b.prev_hash;
   pre += std::to_string((long long)b.timestamp);
-  pre += encode_block_data(b);
+  encode_block_data_to(pre, b);
   uint8_t h[32];
   sha256_fast((const uint8_t*)pre.data(), pre.size(), h);
   b.hash.assign((const char*)h, 32);
