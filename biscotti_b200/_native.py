@@ -168,3 +168,22 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_schnorr_finish_batch", None, c_i, c_p, c_i, c_p, c_p, c_p, c_p)
     sig("bsc_g1_comb_mul", c_i, c_p, c_i, c_p, c_i, c_i, c_p, c_p)
     sig("bsc_schnorr_verify", c_i, c_cp, c_sz, c_cp, c_cp)
+    # device-resident block chain (kernels_chain.cu) and the device-count variants of the aggregation kernels
+    sig("bsc_vrf_noisers", c_i, c_p, c_p, c_i, c_p, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_p)
+    sig("bsc_block_plan", c_i, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_p)
+    sig("bsc_schnorr_nonces_dev", c_i, c_p, c_cp, c_ll, c_p, c_i, c_p, c_i, c_p, c_p)
+    sig("bsc_schnorr_finish_dev", c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_i, c_p, c_i, c_p)
+    sig("bsc_pack_commitments", c_i, c_p, c_i, c_p, c_i, c_p)
+    sig("bsc_schnorr_finish64_host", None, c_cp, c_p, c_cp, c_cp, c_p)
+    sig("bsc_share_sum_dc", c_i, c_p, c_p, c_i, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_p, c_p)
+    sig("bsc_reconstruct_step_gated", c_i, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_d, c_p, c_p, c_p, c_p, c_p, c_i, c_p)
+    sig("bsc_reconstruct_mat", c_i, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_d, c_p, c_p, c_p, c_p, c_p, c_i, c_p)
+    sig("bsc_recover_mat_host", c_i, c_p, c_p, c_i, c_i, c_p)
+    sig("bsc_recover_mat_sizeof", c_i)
+    sig("bsc_plain_sum_step_dc", c_i, c_p, c_p, c_i, c_p, c_i, c_i, c_p, c_p, c_p, c_p, c_i, c_p)
+    sig("bsc_msm_table_dc", c_i, c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_ll, c_p)
+    sig("bsc_g1_sum_rows_dc", c_i, c_p, c_p, c_i, c_p, c_ll, c_p, c_p)
+    sig("bsc_g1_sum_rows_jac_dc", c_i, c_p, c_p, c_i, c_p, c_ll, c_p, c_p)
+    sig("bsc_seeded_perm", None, c_ull, c_i, c_p)
+    sig("bsc_chain_append_packed", c_i, c_p, c_ll, c_p, c_i, c_p, c_i, c_p, c_ll, c_i, c_p, c_i, c_i, c_ll, c_p)
+    sig("bsc_symm_error", c_i)

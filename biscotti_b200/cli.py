@@ -41,7 +41,7 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--shard-size", type=int, default=None)
     ap.add_argument("--fail-prob", type=float, default=-0.005)
     ap.add_argument("--tau", type=int, default=2, help="SRS trapdoor (2 = reference compat, 0 = random)")
-    ap.add_argument("--comm", default="nccl", choices=["nccl", "fused"])
+    ap.add_argument("--comm", default="fused", choices=["nccl", "fused"], help="multi-GPU path: fused peer-memory kernels (default) or the NCCL baseline")
     ap.add_argument("--gram", default="auto")
     ap.add_argument("--print-hash", action="store_true")
     ap.add_argument("--no-dump", action="store_true")
@@ -124,6 +124,7 @@ def run_localtest(a, mode: str) -> int:
         print(f"blocks={len(eng.chain)} final_test_error={last.test_error} attack_rate={last.attack_rate}")
         # localTest.sh:70-89
         print("SUCCESS! Nodes have same blockchain" if ok else "FAILURE! Nodes have different blockchains")
+    eng.close()              # unmaps the peers' memory of the fused path (after a barrier)
     if world > 1:
         import torch.distributed as dist
 

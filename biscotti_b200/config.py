@@ -19,8 +19,8 @@ MAX_ITERATIONS = 100       # main.go:48
 FAIL_PROB = -0.005         # main.go:55 (fault injection off)
 CONV_THRESHOLD = 0.0       # honest.go:51
 NOISE_TABLE_ITERS = 100    # client_obj.py:17, logistic_model.py:21
-# timeouts in seconds, scaled by N/100 (main.go:31-36, 786-821); here they order simulated events
-TIMEOUTS = dict(roni=120, krum=60, krum_r=60, update=90, block=300, peer=5)
+# The reference's phase timeouts (main.go:31-36, 786-821) have no counterpart: arrival orders are explicit
+# seeded permutations and a missed deadline is the empty-block branch of the engine, not a wall-clock wait.
 
 
 @dataclass(frozen=True)
@@ -92,10 +92,10 @@ class BiscottiConfig:
     data_dir: str | None = None       # directory of <dataset><i>.npy shards (data/files.py); None = synthetic data
     prefetch: bool = True             # queue iteration t+1's local step + commitment MSM behind iteration t's
                                       # aggregation kernel so the device is busy while the host assembles block t
-    overlap_witness: bool = False     # witness MSM + homomorphic aggregation on a second, lower-priority stream.
-                                      # Off by default: at MNIST size the block is host-bound (measured 2.68 vs 2.69
-                                      # ms/block), so the extra stream bookkeeping buys nothing; it pays when the
-                                      # device-side chain in front of the block hash is the bottleneck
+    pipeline: bool = True             # GPU: the block's dependency chain on a high-priority stream, everything off the
+                                      # chain (witness MSM, miners' aggregation, error rates, next local step +
+                                      # commitments) on a second stream, the approvals on a third.  False = one stream,
+                                      # strictly in program order (what an instrumented run uses)
     gram_impl: str = "auto"           # auto | tcgen05 | simt
     comm_impl: str = "fused"          # fused (in-kernel P2P) | nccl (baseline)
     extra: dict = field(default_factory=dict)
@@ -148,9 +148,6 @@ class BiscottiConfig:
         if self.spec.model == "logistic":
             return -self.logistic_alpha / self.batch_size * s                # logistic_model.py:108-109
         return -1.0 / self.batch_size * s                                     # client_obj.py:97-98
-
-    def timeout(self, name: str) -> float:
-        return TIMEOUTS[name] * max(1.0, self.num_nodes / 100.0)
 
     def to_dict(self) -> dict:
         return asdict(self)

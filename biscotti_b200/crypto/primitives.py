@@ -17,7 +17,7 @@ import numpy as np
 import torch
 
 from .. import _native
-from ..config import VERIFIER_PRIME, MINER_PRIME, NOISER_PRIME
+from ..config import VERIFIER_PRIME, MINER_PRIME, NOISER_PRIME, BASE_PORT
 
 c_i = ctypes.c_int
 
@@ -188,6 +188,33 @@ class BatchedVRF:
             ev.record(self._side)
         return (self._host_gam, ev, msg)
 
+    def launch_dev(self, msg: bytes):
+        """GPU only: Gamma_p = x_p * H(msg) for every peer, left projective ON THE DEVICE: (xyz int32 [n, 30], event,
+        msg).  The consumer is ops.chain.vrf_noisers (inversion, SHAKE256, stake lottery in one kernel), so the VRF
+        outputs never visit the host.  Runs on this object's high-priority stream and waits for nothing."""
+        L = _L()
+        n = len(self.keys)
+        if not hasattr(self, "_dside"):
+            torch.cuda.current_stream(self.device).synchronize()   # once: the scalars' upload has landed
+            self._dside = torch.cuda.Stream(self.device, priority=-1)
+            self._dh_pinned = [torch.empty(64, dtype=torch.uint8).pin_memory() for _ in range(4)]
+            self._dhd = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(4)]
+            self._dxyz = [torch.empty(n, 30, dtype=torch.int32, device=self.device) for _ in range(2)]
+            self._dev = [torch.cuda.Event() for _ in range(2)]
+            self._di = 0
+        i = self._di
+        self._di += 1
+        hp, hd, xyz, ev = self._dh_pinned[i % 4], self._dhd[i % 4], self._dxyz[i % 2], self._dev[i % 2]
+        L.bsc_vrf_hash_to_curve_xy(msg, len(msg), ctypes.c_void_p(hp.data_ptr()))
+        with torch.cuda.stream(self._dside):
+            hd.copy_(hp, non_blocking=True)
+            rc = L.bsc_ed25519_scalarmult_quad_xyz(ctypes.c_void_p(self.scalars.data_ptr()), ctypes.c_void_p(hd.data_ptr()), n,
+                                                   ctypes.c_void_p(xyz.data_ptr()), ctypes.c_void_p(self._dside.cuda_stream))
+            if rc:
+                raise RuntimeError("ed25519 scalar multiplication kernel failed")
+            ev.record(self._dside)
+        return (xyz, ev, msg)
+
     def noiser_table(self, handle, stake: list[int], is_worker: np.ndarray, want: int) -> np.ndarray:
         """[n, want] int32 table of noiser ids (-1 = none) for every worker (vrf.go:54-100)."""
         gam, ev, msg = handle
@@ -292,7 +319,7 @@ def write_bootstrap_files(outdir: str, n_nodes: int, dims: int, hosts: list[str]
             for k in range(per):
                 if i >= n_nodes:
                     break
-                f.write(f"{h}:{8000 + k}\n")
+                f.write(f"{h}:{BASE_PORT + k}\n")
                 i += 1
     return srs, keys
 

@@ -148,3 +148,95 @@ class SchnorrBatchSigner:
                                    sigs.ctypes.data_as(ctypes.c_void_p))
         raw = sigs.tobytes()
         return [raw[64 * i: 64 * i + 64] for i in range(n)]
+
+
+class ApprovalSigner:
+    """The verifiers' approvals of one block, produced where the commitments live.
+
+    GPU: every (Krum candidate, live verifier) pair of this rank's peers is signed before the Krum verdict is
+    known - nonce derivation (schnorr_nonce_kernel), T = v*G (g1_comb_mul_kernel), c = H(T || commitment) and
+    r = v - x*c (schnorr_finish_kernel) all run on a side stream while the VRF and Krum kernels run, and the
+    result lands in the per-peer `pack` row (commitment || signatures) that is gathered across ranks and copied
+    to the host once, at the block's tail.  The host never touches a nonce, a hash or a scalar.
+    CPU: only the contributors' approvals are computed, at the tail, with the host restatements.
+
+    Nonce tag = per-run salt || previous block hash || (iteration, update, verifier) - see ops.chain.approval_tag.
+    """
+
+    def __init__(self, device, secrets: list[bytes]):
+        self.device = torch.device(device)
+        self.L = _native.load()
+        self.n = len(secrets)
+        self._sk_np = np.frombuffer(b"".join(secrets), dtype=np.uint8).reshape(self.n, 32).copy()
+        self._comb = SchnorrBatchSigner(device)
+        self._cap = 0
+        if self.device.type == "cuda":
+            self.secrets_dev = torch.from_numpy(self._sk_np).to(self.device)
+            self._comb._ensure_table()
+            self.stream = torch.cuda.Stream(self.device, priority=-1)
+            self.event = torch.cuda.Event()
+
+    def _ensure(self, n):
+        if self._cap >= n:
+            return
+        self._cap = max(256, 2 * n)
+        dev = self.device
+        self._k = torch.empty(self._cap, 8, dtype=torch.int32, device=dev)
+        self._jac = torch.empty(self._cap, JAC, dtype=torch.int32, device=dev)
+        self._aff = torch.empty(self._cap, AFF, dtype=torch.int32, device=dev)
+        self._T = torch.empty(self._cap, 64, dtype=torch.uint8, device=dev)
+
+    def launch(self, salt64: bytes, it: int, cand_ids: torch.Tensor, cand_rows: torch.Tensor, nc: int,
+               signers: torch.Tensor, ns: int, cbytes: torch.Tensor, pack: torch.Tensor, after: "torch.cuda.Event | None",
+               serial: bool = False):
+        """Queue the approvals of `nc` candidates by `ns` signers.  cand_ids / cand_rows / signers: int32 device tensors
+        (global ids; rows of `cbytes` and `pack`, -1 = not this rank's peer).  `after`: event that marks cbytes (and the
+        index tensors) complete.  Returns the event that marks `pack` complete (None when run on the current stream)."""
+        L, dev = self.L, self.device
+        N = nc * ns
+        if N == 0:
+            return None
+        self._ensure(N)
+        p = ctypes.c_void_p
+        ctx = torch.cuda.stream(self.stream) if not serial else _null()
+        with ctx:
+            if not serial and after is not None:
+                self.stream.wait_event(after)
+            st = p(torch.cuda.current_stream(dev).cuda_stream)
+            assert L.bsc_schnorr_nonces_dev(p(self.secrets_dev.data_ptr()), salt64, it, p(cand_ids.data_ptr()), nc,
+                                            p(signers.data_ptr()), ns, p(self._k.data_ptr()), st) == 0
+            tab = self._comb._table
+            assert L.bsc_g1_comb_mul(p(self._k.data_ptr()), N, p(tab.data_ptr()), W_BITS, N_WIN, p(self._jac.data_ptr()), st) == 0
+            assert L.bsc_g1_normalize(p(self._jac.data_ptr()), p(self._aff.data_ptr()), N, st) == 0
+            assert L.bsc_g1_affine_to_bytes(p(self._aff.data_ptr()), p(self._T.data_ptr()), N, st) == 0
+            assert L.bsc_schnorr_finish_dev(p(self._T.data_ptr()), p(self._k.data_ptr()), p(self.secrets_dev.data_ptr()),
+                                            p(cbytes.data_ptr()), p(cand_rows.data_ptr()), nc, p(signers.data_ptr()), ns,
+                                            p(pack.data_ptr()), pack.stride(0), st) == 0
+            if serial:
+                return None
+            self.event.record(self.stream)
+        return self.event
+
+    def sign_host(self, salt64: bytes, it: int, peers: list[int], signers: list[int], commitments: list[bytes]) -> list[bytes]:
+        """CPU path: signatures of `signers` over each peer's commitment, row-major (peer, signer)."""
+        from ..ops.chain import approval_tag
+
+        if not peers or not signers:
+            return []
+        secrets = [self._sk_np[v].tobytes() for _ in peers for v in signers]
+        tags = [approval_tag(salt64, it, p_, v) for p_ in peers for v in signers]
+        h = self._comb.launch(secrets, tags) if self.device.type != "cuda" else _host_handle(self.L, secrets, tags)
+        msgs = [c for c in commitments for _ in signers]
+        return SchnorrBatchSigner("cpu").finish(h, msgs)
+
+
+def _host_handle(L, secrets, tags):
+    return SchnorrBatchSigner("cpu").launch(secrets, tags)
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

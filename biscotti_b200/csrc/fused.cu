@@ -305,71 +305,117 @@ __global__ void __launch_bounds__(256) krum_select_fused_kernel(const float* __r
 }
 
 // ---- secure aggregation -------------------------------------------------------------------------------
+// Reduce-scatter + exact reconstruction + SGD step + all-gather in one kernel.
+//   * A CTA of 256 threads owns SF_CH consecutive chunks of this rank's range.  Their S aggregated shares are
+//     contiguous in every rank's ypart ([chunk][S] int64), so the reduce-scatter is `world` coalesced reads of one
+//     contiguous SF_CH*S*8-byte run per peer, summed straight into shared memory.
+//   * Recovery is the constant-matrix form (secagg_math.cuh: RecoverMat): one thread per (chunk, coefficient), so
+//     consecutive threads produce consecutive weights and the all-gather is `world` coalesced stores of one
+//     contiguous run of doubles (and floats) per peer.
+//   * One elected thread of the grid polls the NVLink-visible flags and republishes the epoch in a local word; the
+//     other CTAs poll that word through L2.  The last CTA to finish publishes SLOT_WEIGHTS and waits for the other
+//     ranks' publications, so when the kernel retires every rank's new slice is in local memory (no wait launch).
+//   * gate: device-resident contributor count (block_plan_kernel); below gate_min the block will be empty and the
+//     weights stay as they are - the flag protocol still runs so that the ranks stay in step.
+constexpr int SF_CH = 16;
 struct SecaggFusedParams {
   PeerTable ypart;   // rank q's partial share sums [nchunk][S] int64 over its local contributors
   PeerTable w64;     // rank q's fp64 master weights [d]
   PeerTable w32;     // rank q's fp32 working copy [d]
   PeerTable flags;
   unsigned int* done_counter;
-  int* bad;          // local int[2]
+  unsigned long long* local_ready;
+  int* bad;          // local int[4]: {inexact, mismatched shares, first timed-out wait (0 = none), unused}
+  const int* gate;
   unsigned long long epoch;
   double scale;
-  int world, rank, S, d, c0, nc;
-  int xs[POLY_SIZE];
+  int world, rank, S, d, c0, nc, gate_min, use_mat;
   unsigned char avail[MAX_SHARES];
+  RecoverMat R;      // R.xs is always valid; M/D only when use_mat
 };
 
-__global__ void __launch_bounds__(128) secagg_fused_kernel(const __grid_constant__ SecaggFusedParams P) {
+__global__ void __launch_bounds__(256) secagg_fused_kernel(const __grid_constant__ SecaggFusedParams P) {
+  __shared__ long long sy[SF_CH * MAX_SHARES];
+  __shared__ long long sc[SF_CH * POLY_SIZE];
+  const int tid = threadIdx.x;
   // this rank's partial share sums were produced by the previous kernel on this stream: publish, then wait
-  if (blockIdx.x == 0 && threadIdx.x == 0) symm_signal_all(P.flags, P.world, P.rank, SLOT_SHARES, P.epoch);
-  if (threadIdx.x == 0)
-    symm_wait_all(reinterpret_cast<const unsigned long long*>(P.flags.ptr[P.rank]), P.world, SLOT_SHARES, P.epoch);
-  __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < P.nc) {
-    const int c = P.c0 + i;
-    // reduce-scatter: pull this chunk's share sums from every rank (int64 adds: order-independent)
-    int64_t ysum[MAX_SHARES];
-    for (int s = 0; s < P.S; s++) {
-      uint64_t acc = 0;
-      for (int q = 0; q < P.world; q++)
-        acc += (uint64_t) reinterpret_cast<const long long*>(P.ypart.ptr[q])[(size_t)c * P.S + s];
-      ysum[s] = (int64_t)acc;
-    }
-    int lx[POLY_SIZE];
-    int64_t ly[POLY_SIZE], coef[POLY_SIZE];
-#pragma unroll
-    for (int j = 0; j < POLY_SIZE; j++) {
-      lx[j] = P.xs[j];
-      ly[j] = ysum[lx[j]];
-    }
-    const bool exact = shamir_recover(lx, ly, coef);
-    if (!exact) atomicAdd(&P.bad[0], 1);
-    int mism = 0;
-    for (int s = 0; s < P.S; s++)
-      if (P.avail[s]) mism += (shamir_eval(coef, s) != ysum[s]);
-    if (mism) atomicAdd(&P.bad[1], mism);
-    const double* wl = reinterpret_cast<const double*>(P.w64.ptr[P.rank]);
-#pragma unroll
-    for (int j = 0; j < POLY_SIZE; j++) {
-      const int k = c * POLY_SIZE + j;
-      if (k < P.d) {
-        const double nw = wl[k] + (double)coef[j] / P.scale;
-        // all-gather: the owner stores the new coordinate into every rank's copy
-        for (int q = 0; q < P.world; q++) {
-          reinterpret_cast<double*>(P.w64.ptr[q])[k] = nw;
-          reinterpret_cast<float*>(P.w32.ptr[q])[k] = (float)nw;
-        }
-      }
+  if (tid == 0) {
+    if (blockIdx.x == 0) {
+      symm_signal_all(P.flags, P.world, P.rank, SLOT_SHARES, P.epoch);
+      if (!symm_wait_all(reinterpret_cast<const unsigned long long*>(P.flags.ptr[P.rank]), P.world, SLOT_SHARES, P.epoch))
+        atomicCAS(&P.bad[2], 0, 1 + SLOT_SHARES);   // reported with the share-check counters when the block is collected
+      symm_local_publish(P.local_ready, P.epoch);
+    } else {
+      if (!symm_local_wait(P.local_ready, P.epoch)) atomicCAS(&P.bad[2], 0, 100);
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  const bool open = !(P.gate && *P.gate < P.gate_min);
+  const int ch0 = blockIdx.x * SF_CH;
+  const int nch = min(SF_CH, P.nc - ch0);
+  if (open && nch > 0) {
+    const size_t base = (size_t)(P.c0 + ch0) * P.S;
+    for (int e = tid; e < nch * P.S; e += blockDim.x) {
+      uint64_t acc = 0;   // int64 adds commute: the sum is the same on every rank whatever the order
+      for (int q = 0; q < P.world; q++) acc += (uint64_t) __ldcv(reinterpret_cast<const long long*>(P.ypart.ptr[q]) + base + e);
+      sy[(e / P.S) * MAX_SHARES + (e % P.S)] = (long long)acc;
+    }
+    __syncthreads();
+    int inexact = 0;
+    const double* wl = reinterpret_cast<const double*>(P.w64.ptr[P.rank]);
+    if (P.use_mat) {
+      for (int e = tid; e < nch * POLY_SIZE; e += blockDim.x) {
+        const int lc = e / POLY_SIZE, j = e % POLY_SIZE;
+        int64_t y[POLY_SIZE];
+#pragma unroll
+        for (int i = 0; i < POLY_SIZE; i++) y[i] = sy[lc * MAX_SHARES + P.R.xs[i]];
+        int64_t coef;
+        inexact += !recover_coef_mat(P.R, y, j, coef);
+        sc[e] = coef;
+      }
+    } else {
+      for (int lc = tid; lc < nch; lc += blockDim.x) {   // abscissae without a safe matrix: divided differences
+        int lx[POLY_SIZE];
+        int64_t ly[POLY_SIZE], coef[POLY_SIZE];
+#pragma unroll
+        for (int j = 0; j < POLY_SIZE; j++) {
+          lx[j] = P.R.xs[j];
+          ly[j] = sy[lc * MAX_SHARES + lx[j]];
+        }
+        inexact += !shamir_recover(lx, ly, coef);
+        for (int j = 0; j < POLY_SIZE; j++) sc[lc * POLY_SIZE + j] = coef[j];
+      }
+    }
+    __syncthreads();
+    // all-gather: consecutive threads own consecutive coordinates; the owner stores them into every rank's copy
+    for (int e = tid; e < nch * POLY_SIZE; e += blockDim.x) {
+      const int k = (P.c0 + ch0) * POLY_SIZE + e;
+      if (k < P.d) {
+        const double nw = wl[k] + (double)sc[e] / P.scale;
+        const float nf = (float)nw;
+        for (int q = 0; q < P.world; q++) {
+          reinterpret_cast<double*>(P.w64.ptr[q])[k] = nw;
+          reinterpret_cast<float*>(P.w32.ptr[q])[k] = nf;
+        }
+      }
+    }
+    int mism = 0;
+    for (int e = tid; e < nch * P.S; e += blockDim.x) {
+      const int lc = e / P.S, sidx = e % P.S;
+      if (P.avail[sidx]) mism += (shamir_eval((const int64_t*)(sc + lc * POLY_SIZE), sidx) != sy[lc * MAX_SHARES + sidx]);
+    }
+    if (inexact) atomicAdd(&P.bad[0], inexact);
+    if (mism) atomicAdd(&P.bad[1], mism);
+  }
+  __syncthreads();
+  if (tid == 0) {
     __threadfence_system();
     const unsigned int old = atomicAdd(P.done_counter, 1u);
     if (old == gridDim.x - 1) {
       *P.done_counter = 0;
       symm_signal_all(P.flags, P.world, P.rank, SLOT_WEIGHTS, P.epoch);
+      if (!symm_wait_all(reinterpret_cast<const unsigned long long*>(P.flags.ptr[P.rank]), P.world, SLOT_WEIGHTS, P.epoch))
+        atomicCAS(&P.bad[2], 0, 1 + SLOT_WEIGHTS);
     }
   }
 }
@@ -524,9 +570,15 @@ int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const i
 }
 
 // Fused reduce-scatter + reconstruct + SGD step + all-gather for this rank's chunk range [c0, c0+nc).
+//   rm          : host RecoverMat (secagg_math.cuh) for the abscissae in use; use_mat = 0 keeps only rm->xs and
+//                 recovers by divided differences
+//   local_ready : local uint64 word (zeroed once), done_counter: local uint32 (zeroed once)
+//   gate        : device int, may be null: the step is applied only when *gate >= gate_min
+// When the kernel retires, every rank's new weight slice has landed in this rank's w64 / w32.
 int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank,
-                     int S, int d, int c0, int nc, const int* xs_host, const unsigned char* avail_host, double scale,
-                     unsigned int* done_counter, int* bad, unsigned long long epoch, void* stream) {
+                     int S, int d, int c0, int nc, const void* rm, int use_mat, const unsigned char* avail_host, double scale,
+                     unsigned int* done_counter, unsigned long long* local_ready, int* bad, const int* gate, int gate_min,
+                     unsigned long long epoch, void* stream) {
   if (world < 1 || world > SYMM_MAX_WORLD || S > MAX_SHARES) return -1;
   SecaggFusedParams P;
   memset(&P, 0, sizeof(P));
@@ -537,7 +589,10 @@ int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, voi
     P.flags.ptr[q] = flags[q];
   }
   P.done_counter = done_counter;
+  P.local_ready = local_ready;
   P.bad = bad;
+  P.gate = gate;
+  P.gate_min = gate_min;
   P.epoch = epoch;
   P.scale = scale;
   P.world = world;
@@ -546,11 +601,20 @@ int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, voi
   P.d = d;
   P.c0 = c0;
   P.nc = nc;
-  for (int j = 0; j < POLY_SIZE; j++) P.xs[j] = xs_host[j];
+  P.use_mat = use_mat;
+  memcpy(&P.R, rm, sizeof(P.R));
   for (int s = 0; s < S; s++) P.avail[s] = avail_host ? avail_host[s] : 1;
-  const int blocks = max(1, (nc + 127) / 128);
-  secagg_fused_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(P);
+  const int blocks = max(1, (nc + SF_CH - 1) / SF_CH);
+  secagg_fused_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(P);
   return finish_launch("secagg_fused");
+}
+
+// first cross-GPU wait that timed out since the last call (0 = none); clears the record
+int bsc_symm_error() {
+  int v = 0, zero = 0;
+  if (cudaMemcpyFromSymbol(&v, g_symm_error, sizeof(int)) != cudaSuccess) return -1;
+  if (v) cudaMemcpyToSymbol(g_symm_error, &zero, sizeof(int));
+  return v;
 }
 
 }  // extern "C"

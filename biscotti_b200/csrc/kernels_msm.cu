@@ -132,10 +132,12 @@ __global__ void __launch_bounds__(128, MINB) msm_table_kernel(const long long* _
                                                         const int* __restrict__ sidx, const int* __restrict__ bidx,
                                                         const int* __restrict__ og, int G, int T,
                                                         const G1Affine* __restrict__ table, int w, int nw,
-                                                        G1Jac* __restrict__ out, long long ostride_p) {
+                                                        G1Jac* __restrict__ out, long long ostride_p,
+                                                        const int* __restrict__ pcount) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)G * P) return;
   const int g = (int)(i / P), p = (int)(i % P);
+  if (pcount && p >= *pcount) return;   // row count decided on the device (block_plan_kernel); P is its upper bound
   const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
   // scalars are read in place (twice: range check, then digits) rather than staged in registers
   out[(size_t)p * ostride_p + (og ? og[g] : g)] = g1_table_msm<MSM_TMAX>(table, bidx[g], (const int64_t*)row, T, w, nw);
@@ -226,9 +228,11 @@ __global__ void g1_bytes_to_affine_kernel(const unsigned char* __restrict__ in, 
 
 // Miner aggregation (kyber.go:244-287): out[g] = sum_{q<nsel} pts[sel[q]*G + g], affine inputs.
 __global__ void __launch_bounds__(128) g1_sum_rows_kernel(const G1Affine* __restrict__ pts, const int* __restrict__ sel,
-                                                          int nsel, long long G, G1Jac* __restrict__ out) {
+                                                          int nsel, long long G, G1Jac* __restrict__ out,
+                                                          const int* __restrict__ nsel_dev) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= G) return;
+  if (nsel_dev) nsel = min(nsel, *nsel_dev);
   G1Jac acc = g1j_inf();
   for (int q = 0; q < nsel; q++) acc = g1j_add_affine(acc, pts[(size_t)sel[q] * G + g]);
   out[g] = acc;
@@ -256,9 +260,11 @@ __global__ void __launch_bounds__(128) g1_sum_cols_kernel(const G1Affine* __rest
 // `row_stride` points; the peer dimension is split over gridDim.y partial sums (fixed order) to shorten
 // the dependent addition chain, and the partials are added by the y == 0 thread's owner afterwards.
 __global__ void __launch_bounds__(128) g1_sum_rows_jac_kernel(const G1Jac* __restrict__ pts, const int* __restrict__ sel,
-                                                              int nsel, long long G, G1Jac* __restrict__ out) {
+                                                              int nsel, long long G, G1Jac* __restrict__ out,
+                                                              const int* __restrict__ nsel_dev) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= G) return;
+  if (nsel_dev) nsel = min(nsel, *nsel_dev);
   G1Jac acc = g1j_inf();
   for (int q = 0; q < nsel; q++) acc = g1j_add(acc, pts[(size_t)sel[q] * G + g]);
   out[g] = acc;
@@ -317,20 +323,29 @@ void bsc_msm_table_build_host(const void* bases_affine, long long nb, int w, int
     }
   }
 }
+int bsc_msm_table_dc(const long long* Q, int ldq, const int* sel, int P, const int* pcount, const int* sidx, const int* bidx,
+                     const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac,
+                     long long ostride_p, void* stream);
 int bsc_msm_table(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og,
                   int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p,
                   void* stream) {
+  return bsc_msm_table_dc(Q, ldq, sel, P, nullptr, sidx, bidx, og, G, T, table_affine, w, nw, out_jac, ostride_p, stream);
+}
+// pcount (may be null): device-resident number of live rows (<= P); rows >= *pcount are skipped
+int bsc_msm_table_dc(const long long* Q, int ldq, const int* sel, int P, const int* pcount, const int* sidx, const int* bidx,
+                     const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac,
+                     long long ostride_p, void* stream) {
   if (T > MSM_TMAX) return -1;
   const long long n = (long long)G * P;
   if (n == 0) return 0;
   static const int minb = getenv("BSC_MSM_MINB") ? atoi(getenv("BSC_MSM_MINB")) : 4;
   const unsigned grid = (unsigned)((n + 127) / 128);
   if (minb >= 8)
-    msm_table_kernel<8><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+    msm_table_kernel<8><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p, pcount);
   else if (minb >= 6)
-    msm_table_kernel<6><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+    msm_table_kernel<6><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p, pcount);
   else
-    msm_table_kernel<4><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p);
+    msm_table_kernel<4><<<grid, 128, 0, (cudaStream_t)stream>>>(Q, ldq, sel, P, sidx, bidx, og, G, T, (const G1Affine*)table_affine, w, nw, (G1Jac*)out_jac, ostride_p, pcount);
   return finish_launch("msm_table");
 }
 void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx,
@@ -385,18 +400,27 @@ int bsc_g1_bytes_to_affine(const unsigned char* in, void* out_affine, long long 
   return finish_launch("g1_bytes_to_affine");
 }
 
-int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
+int bsc_g1_sum_rows_dc(const void* pts_affine, const int* sel, int nsel, const int* nsel_dev, long long G, void* out_jac,
+                       void* stream) {
   if (G == 0) return 0;
   g1_sum_rows_kernel<<<(unsigned)((G + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)pts_affine, sel,
-                                                                                   nsel, G, (G1Jac*)out_jac);
+                                                                                   nsel, G, (G1Jac*)out_jac, nsel_dev);
   return finish_launch("g1_sum_rows");
 }
+int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
+  return bsc_g1_sum_rows_dc(pts_affine, sel, nsel, nullptr, G, out_jac, stream);
+}
 
-int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
+// nsel_dev (may be null): device-resident row count (<= nsel)
+int bsc_g1_sum_rows_jac_dc(const void* pts_jac, const int* sel, int nsel, const int* nsel_dev, long long G, void* out_jac,
+                           void* stream) {
   if (G == 0) return 0;
   g1_sum_rows_jac_kernel<<<(unsigned)((G + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Jac*)pts_jac, sel, nsel,
-                                                                                       G, (G1Jac*)out_jac);
+                                                                                       G, (G1Jac*)out_jac, nsel_dev);
   return finish_launch("g1_sum_rows_jac");
+}
+int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
+  return bsc_g1_sum_rows_jac_dc(pts_jac, sel, nsel, nullptr, G, out_jac, stream);
 }
 int bsc_g1_sum_cols_jac(const void* pts_jac, int P, int G, void* out_jac, void* stream) {
   if (P == 0) return 0;

@@ -10,6 +10,7 @@
 // miners for it), see kernels_fused.cu for the multi-GPU form.
 #include "common.cuh"
 #include "secagg_math.cuh"
+#include <string.h>
 
 namespace bsc {
 
@@ -39,10 +40,14 @@ __global__ void shares_eval_kernel(const long long* __restrict__ Q, long long* _
 // [c0, c0+nc) sum the shares of every accepted peer.  Thread per (chunk, share).
 //   sel : [nsel] indices of contributing peers (rows of U) in fixed (ascending id) order
 //   Ysum: [nc][S]
+//   nsel_dev : optional device count (<= nsel) written by block_plan_kernel: the contributor set is decided
+//              on the device and never visits the host before the block's tail
 __global__ void share_sum_kernel(const float* __restrict__ U, const int* __restrict__ sel, int nsel, int d, int ldu,
-                                 int c0, int nc, int S, double scale, long long* __restrict__ Ysum) {
+                                 int c0, int nc, int S, double scale, long long* __restrict__ Ysum,
+                                 const int* __restrict__ nsel_dev) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nc * S) return;
+  if (nsel_dev) nsel = min(nsel, *nsel_dev);
   const int c = c0 + i / S, s = i % S;
   uint64_t acc = 0;
   for (int q = 0; q < nsel; q++) {
@@ -68,9 +73,12 @@ __global__ void share_sum_kernel(const float* __restrict__ U, const int* __restr
 __global__ void reconstruct_step_kernel(const long long* __restrict__ Ysum, const int* __restrict__ xs,
                                         const unsigned char* __restrict__ avail, int S, int c0, int nc, int d,
                                         double scale, double* __restrict__ w64, float* __restrict__ w32,
-                                        double* __restrict__ dsum, int* __restrict__ bad) {
+                                        double* __restrict__ dsum, int* __restrict__ bad,
+                                        const int* __restrict__ gate, int gate_min) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nc) return;
+  // too few contributors (main.go:2079): the block will be empty and the weights must stay as they are
+  if (gate && *gate < gate_min) return;
   const int c = c0 + i;
   int lx[POLY_SIZE];
   int64_t ly[POLY_SIZE];
@@ -101,13 +109,64 @@ __global__ void reconstruct_step_kernel(const long long* __restrict__ Ysum, cons
   }
 }
 
+// Same contract as reconstruct_step_kernel, recovery by the constant inverse matrix (secagg_math.cuh: RecoverMat).
+// A CTA of 256 threads takes RM_CH chunks: (1) stage their S aggregated shares in shared memory, (2) one thread
+// per (chunk, coefficient) forms the coefficient, de-quantises and steps the weight, (3) one thread per (chunk,
+// share) re-evaluates the recovered polynomial and checks the redundant shares.
+constexpr int RM_CH = 16;
+__global__ void __launch_bounds__(256) reconstruct_mat_kernel(const long long* __restrict__ Ysum, const RecoverMat R,
+                                                              const unsigned char* __restrict__ avail, int S, int c0,
+                                                              int nc, int d, double scale, double* __restrict__ w64,
+                                                              float* __restrict__ w32, double* __restrict__ dsum,
+                                                              int* __restrict__ bad, const int* __restrict__ gate,
+                                                              int gate_min) {
+  __shared__ long long sy[RM_CH * MAX_SHARES];
+  __shared__ long long sc[RM_CH * POLY_SIZE];
+  if (gate && *gate < gate_min) return;
+  const int ch0 = blockIdx.x * RM_CH;
+  const int nch = min(RM_CH, nc - ch0);
+  for (int e = threadIdx.x; e < nch * S; e += blockDim.x) sy[(e / S) * MAX_SHARES + (e % S)] = Ysum[(size_t)ch0 * S + e];
+  __syncthreads();
+  int inexact = 0;
+  for (int e = threadIdx.x; e < nch * POLY_SIZE; e += blockDim.x) {
+    const int lc = e / POLY_SIZE, j = e % POLY_SIZE;
+    int64_t y[POLY_SIZE];
+#pragma unroll
+    for (int i = 0; i < POLY_SIZE; i++) y[i] = sy[lc * MAX_SHARES + R.xs[i]];
+    int64_t coef;
+    inexact += !recover_coef_mat(R, y, j, coef);
+    sc[e] = coef;
+    const int k = (c0 + ch0 + lc) * POLY_SIZE + j;
+    if (k < d) {
+      const double delta = (double)coef / scale;
+      const double nw = w64[k] + delta;
+      w64[k] = nw;
+      if (w32) w32[k] = (float)nw;
+      if (dsum) dsum[k] = delta;
+    }
+  }
+  __syncthreads();
+  int mism = 0;
+  if (bad) {
+    for (int e = threadIdx.x; e < nch * S; e += blockDim.x) {
+      const int lc = e / S, s = e % S;
+      if (avail == nullptr || avail[s]) mism += (shamir_eval((const int64_t*)(sc + lc * POLY_SIZE), s) != sy[lc * MAX_SHARES + s]);
+    }
+    if (inexact) atomicAdd(&bad[0], inexact);
+    if (mism) atomicAdd(&bad[1], mism);
+  }
+}
+
 // Plain aggregation (-sa=false, DistSys/honest.go:346-388; also the FedSys server,
 // FedSys/honest.go:311-337): w += sum of selected deltas, summed in fixed order in fp64.
 __global__ void plain_sum_step_kernel(const float* __restrict__ U, const int* __restrict__ sel, int nsel, int d,
                                       int ldu, double* __restrict__ w64, float* __restrict__ w32,
-                                      double* __restrict__ dsum) {
+                                      double* __restrict__ dsum, const int* __restrict__ nsel_dev,
+                                      const int* __restrict__ gate, int gate_min) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= d) return;
+  if (gate && *gate < gate_min) return;
+  if (nsel_dev) nsel = min(nsel, *nsel_dev);
   double acc = 0.0;
   for (int q = 0; q < nsel; q++) acc += (double)U[(size_t)sel[q] * ldu + k];
   const double nw = w64[k] + acc;
@@ -134,25 +193,73 @@ int bsc_shares_eval(const long long* Q, long long* Y, int P, int nchunk, int dpa
   return finish_launch("shares_eval");
 }
 
-int bsc_share_sum(const float* U, const int* sel, int nsel, int d, int ldu, int c0, int nc, int S, double scale,
-                  long long* Ysum, void* stream) {
+// nsel_dev (may be null): device-resident contributor count, see share_sum_kernel
+int bsc_share_sum_dc(const float* U, const int* sel, int nsel, const int* nsel_dev, int d, int ldu, int c0, int nc, int S,
+                     double scale, long long* Ysum, void* stream) {
   if (S > MAX_SHARES) return -1;
   const int n = nc * S;
-  share_sum_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(U, sel, nsel, d, ldu, c0, nc, S, scale, Ysum);
+  if (n <= 0) return 0;
+  share_sum_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(U, sel, nsel, d, ldu, c0, nc, S, scale, Ysum, nsel_dev);
   return finish_launch("share_sum");
 }
-
-int bsc_reconstruct_step(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d,
-                         double scale, double* w64, float* w32, double* dsum, int* bad, void* stream) {
-  reconstruct_step_kernel<<<(nc + 127) / 128, 128, 0, (cudaStream_t)stream>>>(Ysum, xs, avail, S, c0, nc, d, scale,
-                                                                               w64, w32, dsum, bad);
-  return finish_launch("reconstruct_step");
+int bsc_share_sum(const float* U, const int* sel, int nsel, int d, int ldu, int c0, int nc, int S, double scale,
+                  long long* Ysum, void* stream) {
+  return bsc_share_sum_dc(U, sel, nsel, nullptr, d, ldu, c0, nc, S, scale, Ysum, stream);
 }
 
+// gate (may be null): the step is applied only if *gate >= gate_min (device-resident contributor count)
+int bsc_reconstruct_step_gated(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d,
+                               double scale, double* w64, float* w32, double* dsum, int* bad, const int* gate,
+                               int gate_min, void* stream) {
+  if (nc <= 0) return 0;
+  reconstruct_step_kernel<<<(nc + 127) / 128, 128, 0, (cudaStream_t)stream>>>(Ysum, xs, avail, S, c0, nc, d, scale,
+                                                                               w64, w32, dsum, bad, gate, gate_min);
+  return finish_launch("reconstruct_step");
+}
+int bsc_reconstruct_step(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d,
+                         double scale, double* w64, float* w32, double* dsum, int* bad, void* stream) {
+  return bsc_reconstruct_step_gated(Ysum, xs, avail, S, c0, nc, d, scale, w64, w32, dsum, bad, nullptr, 0, stream);
+}
+
+// Matrix form of bsc_reconstruct_step_gated; `rm` points at a host RecoverMat (see secagg_math.cuh).
+int bsc_reconstruct_mat(const long long* Ysum, const void* rm, const unsigned char* avail, int S, int c0, int nc, int d,
+                        double scale, double* w64, float* w32, double* dsum, int* bad, const int* gate, int gate_min,
+                        void* stream) {
+  if (nc <= 0) return 0;
+  if (S > MAX_SHARES) return -1;
+  RecoverMat R;
+  memcpy(&R, rm, sizeof(R));
+  reconstruct_mat_kernel<<<(nc + RM_CH - 1) / RM_CH, 256, 0, (cudaStream_t)stream>>>(Ysum, R, avail, S, c0, nc, d, scale,
+                                                                                      w64, w32, dsum, bad, gate, gate_min);
+  return finish_launch("reconstruct_mat");
+}
+// host restatement: coefficients of nc chunks through the matrix; returns the number of inexact coefficients
+int bsc_recover_mat_host(const long long* Ysum, const void* rm, int S, int nc, long long* coef_out) {
+  RecoverMat R;
+  memcpy(&R, rm, sizeof(R));
+  int badc = 0;
+  for (int i = 0; i < nc; i++) {
+    int64_t y[POLY_SIZE];
+    for (int k = 0; k < POLY_SIZE; k++) y[k] = Ysum[(size_t)i * S + R.xs[k]];
+    for (int j = 0; j < POLY_SIZE; j++) {
+      int64_t c;
+      badc += !recover_coef_mat(R, y, j, c);
+      coef_out[(size_t)i * POLY_SIZE + j] = c;
+    }
+  }
+  return badc;
+}
+int bsc_recover_mat_sizeof() { return (int)sizeof(RecoverMat); }
+
+int bsc_plain_sum_step_dc(const float* U, const int* sel, int nsel, const int* nsel_dev, int d, int ldu, double* w64,
+                          float* w32, double* dsum, const int* gate, int gate_min, void* stream) {
+  plain_sum_step_kernel<<<(d + 255) / 256, 256, 0, (cudaStream_t)stream>>>(U, sel, nsel, d, ldu, w64, w32, dsum, nsel_dev,
+                                                                           gate, gate_min);
+  return finish_launch("plain_sum_step");
+}
 int bsc_plain_sum_step(const float* U, const int* sel, int nsel, int d, int ldu, double* w64, float* w32, double* dsum,
                        void* stream) {
-  plain_sum_step_kernel<<<(d + 255) / 256, 256, 0, (cudaStream_t)stream>>>(U, sel, nsel, d, ldu, w64, w32, dsum);
-  return finish_launch("plain_sum_step");
+  return bsc_plain_sum_step_dc(U, sel, nsel, nullptr, d, ldu, w64, w32, dsum, nullptr, 0, stream);
 }
 
 // ---- host restatements (CPU plumbing path and oracles; same arithmetic, same header) -------------

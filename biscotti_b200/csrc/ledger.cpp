@@ -391,6 +391,60 @@ int bsc_chain_append(void* cp, void* bp, long long timestamp) {
   return (int)c->blocks.size();
 }
 
+// The whole tail of a secure-aggregation block in one call (createBlockSecAgg + AddBlock, honest.go:391-440,
+// block.go:30-44): the contributors' rows are picked out of the per-peer pack (64-byte commitment followed by
+// the verifiers' 64-byte approvals, row = peer id), stake[source] += stake_unit, the block is sealed against
+// the tip, appended and its hash returned.  `stake` (dense, node id = position) is updated in place and
+// recorded in the block.  n == 0 mints the empty block (timestamp rule as in bsc_chain_append).
+int bsc_chain_append_packed(void* cp, long long iteration, const double* w, int d, const int* sources, int n,
+                            const uint8_t* pack, long long pack_stride, int nsigs, int* stake, int nstake, int stake_unit,
+                            long long timestamp, uint8_t out_hash[32]) {
+  Chain* c = (Chain*)cp;
+  Block* b = new Block();
+  b->iteration = iteration;
+  b->w.assign(w, w + d);
+  b->updates.reserve((size_t)n);
+  for (int i = 0; i < n; i++) {
+    Update u;
+    u.source = sources[i];
+    u.iteration = (int)iteration;
+    u.accepted = 1;
+    const uint8_t* row = pack + (size_t)sources[i] * (size_t)pack_stride;
+    u.commitment.assign((const char*)row, 64);
+    for (int k = 0; k < nsigs; k++) u.signatures.emplace_back((const char*)row + 64 + 64 * (size_t)k, (size_t)64);
+    b->updates.push_back(std::move(u));
+    if (sources[i] >= 0 && sources[i] < nstake) stake[sources[i]] += stake_unit;
+  }
+  for (int i = 0; i < nstake; i++) b->stake[i] = stake[i];
+  bsc_chain_append(cp, b, timestamp);
+  memcpy(out_hash, c->blocks.back().hash.data(), 32);
+  return (int)c->blocks.size();
+}
+
+// Deterministic stand-in for a network arrival order: a Fisher-Yates shuffle of 0..n-1 driven by splitmix64
+// from `seed` (unbiased bounded draws by rejection).  Every rank computes the same permutation.
+void bsc_seeded_perm(unsigned long long seed, int n, int* out) {
+  auto next = [&seed]() {
+    unsigned long long z = (seed += 0x9E3779B97F4A7C15ULL);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+  };
+  for (int i = 0; i < n; i++) out[i] = i;
+  for (int i = n - 1; i > 0; i--) {
+    const unsigned long long bound = (unsigned long long)i + 1;
+    const unsigned long long lim = ~0ULL - (~0ULL % bound);
+    unsigned long long r;
+    do {
+      r = next();
+    } while (r >= lim);
+    const int j = (int)(r % bound);
+    const int t = out[i];
+    out[i] = out[j];
+    out[j] = t;
+  }
+}
+
 // getBlock(it) = Blocks[it+1] with the consistency check (blockchain.go:77-96): index or -1/-2
 int bsc_chain_block_index(void* cp, long long iteration) {
   Chain* c = (Chain*)cp;

@@ -136,4 +136,31 @@ HDN inline bool shamir_recover(const int* xs, const int64_t* ys, int64_t out[POL
   return exact;
 }
 
+// Recovery as one exact matrix product.  The share abscissae are fixed small integers, so the inverse of the
+// Vandermonde system is a constant rational matrix: coef_j = (sum_i M[j][i] * y_i) / D with integer M (Lagrange
+// basis coefficients over the common denominator D; for ten consecutive nodes D = 9! and |M| < 2^37).  Each
+// coefficient is an independent 10-term dot product in 128-bit integers and one exact division by a constant
+// (multiplication by the precomputed inverse of D's odd part mod 2^128), so a chunk's recovery spreads over ten
+// threads instead of one thread walking the 45 dependent exact divisions of shamir_recover.  The host builds
+// the matrix with big integers (ops/secagg.py: recover_matrix) and refuses configurations whose dot products
+// could leave 128 bits; those fall back to shamir_recover.  Replaces kyber.go:809-857 (float QR + round).
+struct RecoverMat {
+  long long M[POLY_SIZE * POLY_SIZE];   // row j = coefficient, column i = share xs[i]
+  long long D;                          // common denominator, > 0
+  unsigned long long inv_lo, inv_hi;    // (D >> tz)^-1 mod 2^128
+  int tz;                               // trailing zero bits of D
+  int xs[POLY_SIZE];                    // share indices the matrix was built for
+};
+
+HD bool recover_coef_mat(const RecoverMat& R, const int64_t* y, int j, int64_t& coef) {
+  __int128 acc = 0;
+#pragma unroll
+  for (int i = 0; i < POLY_SIZE; i++) acc += (__int128)R.M[j * POLY_SIZE + i] * (__int128)y[i];
+  const __int128 sh = acc >> R.tz;
+  const unsigned __int128 inv = ((unsigned __int128)R.inv_hi << 64) | (unsigned __int128)R.inv_lo;
+  const __int128 q = (__int128)((unsigned __int128)sh * inv);
+  coef = (int64_t)q;
+  return q * (__int128)R.D == acc;
+}
+
 }  // namespace bsc

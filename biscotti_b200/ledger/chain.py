@@ -204,6 +204,23 @@ class Blockchain:
         self._L.bsc_chain_append(self._h, b, timestamp)
         return self.latest_hash()
 
+    def append_packed(self, iteration: int, weights, sources, pack: np.ndarray, n_sigs: int, stake: list, stake_unit: int,
+                      timestamp: int = -1) -> bytes:
+        """The tail of a secure-aggregation block in one native call (ledger.cpp: bsc_chain_append_packed): `pack` is
+        the [n_peers, 64*(1+k)] array of commitment || approvals rows (row = peer id), `sources` the contributors.
+        Credits stake_unit to every contributor in `stake` (a Python list, updated in place), seals, appends and
+        returns the block hash.  Byte-identical to add_commit_block with the same content."""
+        w, d = _f64(weights)
+        src = np.ascontiguousarray(sources, dtype=np.int32)
+        pk = np.ascontiguousarray(pack, dtype=np.uint8)
+        st = np.asarray(stake, dtype=np.int32)
+        out = ctypes.create_string_buffer(32)
+        self._L.bsc_chain_append_packed(self._h, iteration, w.ctypes.data_as(c_p), d, src.ctypes.data_as(c_p), len(src),
+                                        pk.ctypes.data_as(c_p), pk.strides[0], n_sigs, st.ctypes.data_as(c_p), len(st),
+                                        stake_unit, timestamp, out)
+        stake[:] = st.tolist()
+        return out.raw
+
     def verify(self) -> bool:
         return bool(self._L.bsc_chain_verify(self._h))
 

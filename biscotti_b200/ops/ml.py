@@ -117,14 +117,14 @@ def noise_row(d: int, seed: int, peer: int, slot: int, scale: float, device="cpu
 
 
 def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_planes: bool = True, ldh=None,
-              out_hi=None, out_lo=None, dst_row=None, want_un: bool = True):
+              out_hi=None, out_lo=None, dst_row=None, want_un: bool = True, in_place: bool = False):
     """Un = U + mean_q noise(q); returns (Un fp32 [P,ldu], hi bf16 [P,ldh], lo bf16 [P,ldh], norms [P]).
     noisers: int32 [P, nn] global ids (-1 = unused slot)."""
     P, ldu = U.shape
     ldh = ldh or pad_to(d, 64)
     nn = noisers.shape[1] if noisers is not None else 0
     if not U.is_cuda:
-        Un = U.clone()
+        Un = U if in_place else U.clone()
         if nn:
             for p in range(P):
                 ids = [int(q) for q in noisers[p].tolist() if q >= 0]
@@ -138,7 +138,7 @@ def noise_mix(U, noisers, seed: int, slot: int, scale: float, d: int, want_plane
             hi = torch.nn.functional.pad(hi, (0, pad))
             lo = torch.nn.functional.pad(lo, (0, pad))
         return Un, hi.contiguous(), lo.contiguous(), (Un[:, :d] ** 2).sum(dim=1)
-    Un = torch.empty_like(U) if want_un else None
+    Un = U if in_place else (torch.empty_like(U) if want_un else None)   # in place: each element is read and written once
     if out_hi is not None:      # caller-provided planes (rows >= P), e.g. views into symmetric peer memory
         hi, lo = out_hi, out_lo
         ldh = hi.stride(0)

@@ -149,12 +149,12 @@ class CommitmentEngine:
         return table
 
     # -- raw kernels -----------------------------------------------------------------------------
-    def _msm_table(self, Q, sel, P, sidx, bidx, og, G, T, table, ostride, nout):
+    def _msm_table(self, Q, sel, P, sidx, bidx, og, G, T, table, ostride, nout, count=None):
         out = torch.empty(nout, JAC, dtype=torch.int32, device=self.device)
         L = lib()
         if self.device.type == "cuda":
-            check(L.bsc_msm_table(ptr(Q), Q.stride(0), ptr(sel), P, ptr(sidx), ptr(bidx), ptr(og), G, T, ptr(table),
-                                  self.w, self.nw, ptr(out), ostride, stream(self.device)), "msm_table")
+            check(L.bsc_msm_table_dc(ptr(Q), Q.stride(0), ptr(sel), P, ptr(count), ptr(sidx), ptr(bidx), ptr(og), G, T,
+                                     ptr(table), self.w, self.nw, ptr(out), ostride, stream(self.device)), "msm_table")
         else:
             L.bsc_msm_table_host(ptr(Q), Q.stride(0), ptr(sel), P, ptr(sidx), ptr(bidx), ptr(og), G, T, ptr(table),
                                  self.w, self.nw, ptr(out), ostride)
@@ -190,6 +190,17 @@ class CommitmentEngine:
         buf = ctypes.create_string_buffer(64 * N)
         lib().bsc_g1_affine_to_bytes_host(ptr(aff.contiguous()), buf, N)
         return buf.raw
+
+    def to_bytes_into(self, aff: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """Wire bytes of N affine points into the first N rows of a persistent [>= N, 64] uint8 tensor (no host sync)."""
+        N = aff.numel() // AFF
+        if aff.is_cuda:
+            check(lib().bsc_g1_affine_to_bytes(ptr(aff), ptr(out), N, stream(aff.device)), "g1_affine_to_bytes")
+        else:
+            buf = ctypes.create_string_buffer(64 * N)
+            lib().bsc_g1_affine_to_bytes_host(ptr(aff.contiguous()), buf, N)
+            out[:N] = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).view(N, 64)
+        return out
 
     def to_bytes_tensor(self, aff: torch.Tensor) -> torch.Tensor:
         """Device-resident wire bytes [N, 64] (no host sync)."""
@@ -247,13 +258,23 @@ class CommitmentEngine:
                                              len(rows), out.ctypes.data_as(ctypes.c_void_p))
         return [out[i].tobytes() for i in range(len(rows))]
 
-    def witnesses(self, Q: torch.Tensor, sel: torch.Tensor | None = None, affine: bool = True) -> torch.Tensor:
-        """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> [P, nchunk, S, 16 | 24]."""
+    def witnesses(self, Q: torch.Tensor, sel: torch.Tensor | None = None, affine: bool = True, count=None,
+                  max_rows: int | None = None) -> torch.Tensor:
+        """W[p, c, s] = KZG opening proof of chunk polynomial c of peer p at x_s -> [P, nchunk, S, 16 | 24].
+        count (int32 [1] on the device) / max_rows: `sel` holds `count` live rows, at most `max_rows`; the kernel reads
+        the count itself, so the approved set never has to visit the host.  Rows >= count are left unwritten."""
         P = Q.shape[0] if sel is None else sel.numel()
+        if max_rows is not None:
+            P = min(P, max_rows)
+        if count is not None and self.device.type != "cuda":
+            P = int(count[0])
+            sel, count = sel[:P], None
         G = self.nchunk * self.S
+        if P == 0:
+            return torch.empty(0, self.nchunk, self.S, AFF if affine else JAC, dtype=torch.int32, device=self.device)
         if self.w_table is not None:
             jac = self._msm_table(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.w_table, ostride=G,
-                                  nout=P * G)
+                                  nout=P * G, count=count)
         else:
             jac = self._msm(Q, sel, P, self.w_sidx, self.w_bidx, None, G, POLY_SIZE - 1, self.wtable, ostride=G,
                             nout=P * G)
@@ -290,17 +311,21 @@ class CommitmentEngine:
         base = self.srs_bytes[64 * POLY_SIZE * chunk: 64 * POLY_SIZE * chunk + 64]
         return pairing.verify_secret(chunk_commit, witness, s - 10, y, self._g2_srs[0], self._g2_srs[1], base=base)
 
-    def aggregate(self, pts: torch.Tensor, sel: torch.Tensor, affine: bool = True) -> torch.Tensor:
-        """Miner-side homomorphic add over contributing peers: pts [P, G..., 16|24] -> [G..., 16|24]."""
-        P = pts.shape[0]
+    def aggregate(self, pts: torch.Tensor, sel: torch.Tensor, affine: bool = True, count=None) -> torch.Tensor:
+        """Miner-side homomorphic add over contributing peers: pts [P, G..., 16|24] -> [G..., 16|24].
+        count (int32 [1] on the device): live entries of `sel`, read by the kernel."""
         inner = pts.shape[1:-1]
         words = pts.shape[-1]
-        G = pts.numel() // (P * words)
+        G = 1
+        for k in inner:
+            G *= k
         jac = torch.empty(G, JAC, dtype=torch.int32, device=pts.device)
         L = lib()
+        if count is not None and not pts.is_cuda:
+            sel, count = sel[: int(count[0])], None
         if pts.is_cuda:
-            fn = L.bsc_g1_sum_rows_jac if words == JAC else L.bsc_g1_sum_rows
-            check(fn(ptr(pts), ptr(sel), sel.numel(), G, ptr(jac), stream(pts.device)), "g1_sum_rows")
+            fn = L.bsc_g1_sum_rows_jac_dc if words == JAC else L.bsc_g1_sum_rows_dc
+            check(fn(ptr(pts), ptr(sel), sel.numel(), ptr(count), G, ptr(jac), stream(pts.device)), "g1_sum_rows")
         else:
             (L.bsc_g1_sum_rows_jac_host if words == JAC else L.bsc_g1_sum_rows_host)(ptr(pts), ptr(sel), sel.numel(), G,
                                                                                    ptr(jac))

@@ -64,6 +64,24 @@ class NcclComm:
         ix = torch.tensor(ids, dtype=torch.long, device=local.device)   # contiguous ownership: global id == row
         return out.index_select(0, ix).contiguous()
 
+    def all_gather_rows_u8(self, local: torch.Tensor) -> torch.Tensor:
+        """[per, k] blocks from every rank -> [world*per, k] (the block's commitment || approvals rows, row = peer id)."""
+        if self.world == 1:
+            return local
+        out = torch.empty(self.world * local.shape[0], *local.shape[1:], dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local.contiguous())
+        return out
+
+    def all_gather_np(self, a):
+        """numpy block per rank -> list of every rank's block (host-side plumbing of the CPU path)."""
+        import numpy as np
+
+        if self.world == 1:
+            return [a]
+        t = torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
+        out = self.all_gather_rows_u8(t.view(torch.uint8).reshape(1, -1)).cpu().numpy()
+        return [out[q].view(a.dtype).reshape(a.shape) for q in range(self.world)]
+
     def merge_dicts(self, d: dict) -> dict:
         if self.world == 1:
             return d

@@ -59,7 +59,8 @@ def _declare(L):
     L.bsc_krum_select_fused.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
     L.bsc_krum_select_mc_wait.argtypes = [c_p, c_i, c_i, c_p, c_i, c_i, c_p, c_i, c_ull, c_p, c_p, c_p]
     L.bsc_symm_allgather_rows.argtypes = [c_p, c_p, c_p, c_i, c_i, c_p, ctypes.c_longlong, c_i, c_ull, c_p]
-    L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_d, c_p, c_p, c_ull, c_p]
+    L.bsc_secagg_fused.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_i, c_p, c_d, c_p, c_p, c_p, c_p, c_i,
+                                   c_ull, c_p]
 
 
 def _check(rc, what):
@@ -113,8 +114,9 @@ class FusedComm(NcclComm):
         self.o_ypart = take(self.nchunk * self.S * 8)
         self.o_w64 = take(d * 8)
         self.o_w32 = take(d * 4)
-        self.cb_row = 96                                   # one Jacobian G1 point per peer
-        self.cb_bytes = world * self.per * self.cb_row     # gathered commitments of one block
+        nsig = cfg.num_verifiers if (cfg.verification and cfg.sign_approvals) else 0
+        self.cb_row = 64 * (1 + nsig)                      # per peer: commitment wire bytes || the verifiers' approvals
+        self.cb_bytes = world * self.per * self.cb_row     # gathered rows of one block
         self.o_cb = take(2 * self.cb_bytes)                # double-buffered by block parity
         self.nbytes = off
         base = c_p()
@@ -141,7 +143,7 @@ class FusedComm(NcclComm):
         self.ypart = tensor_from_ptr(self.base + self.o_ypart, (self.nchunk, self.S), torch.int64, dev)
         self.w64 = tensor_from_ptr(self.base + self.o_w64, (d,), torch.float64, dev)
         self.w32 = tensor_from_ptr(self.base + self.o_w32, (d,), torch.float32, dev)
-        self.bad = tensor_from_ptr(self.base + self.o_bad, (2,), torch.int32, dev)
+        self.bad = tensor_from_ptr(self.base + self.o_bad, (4,), torch.int32, dev)
         self.gpart = tensor_from_ptr(self.base + self.o_gpart, (world, self.ldg, self.ldg), torch.float32, dev)
         self._tables = {name: self._table(o) for name, o in (("flags", self.o_flags), ("hi", self.o_hi), ("lo", self.o_lo),
                                                              ("gpart", self.o_gpart), ("ypart", self.o_ypart),
@@ -169,8 +171,9 @@ class FusedComm(NcclComm):
         return (peer // self.per) * self.Sr + (peer % self.per)
 
     # ---- fused Krum -------------------------------------------------------------------------------
-    def krum_fused(self, krum_set, clip: int, epoch: int):
-        """Planes of this block must already be in self.hi / self.lo.  Returns accept (uint8, device)."""
+    def krum_fused(self, krum_set, clip: int, epoch: int, rows: torch.Tensor | None = None):
+        """Planes of this block must already be in self.hi / self.lo.  Returns accept (uint8, device).
+        rows: int32 device tensor of the candidates' slots (slot_of), if the caller already uploaded it."""
         n = len(krum_set)
         dev = self.device
         self._gram_seq = getattr(self, "_gram_seq", 0) + 1   # the Gram kernel publishes SLOT_PLANES itself
@@ -178,14 +181,15 @@ class FusedComm(NcclComm):
                                           self._tables["flags"], self.world, self.rank, self.Sr, self.ldh, self.ksplit,
                                           self.ldg, c_p(self.base + self.o_lpart), c_p(self.base + self.o_cnt), self._gram_seq,
                                           epoch, self._stream()), "krum_gram_fused")
-        # slot indices through a small persistent pinned ring (a fresh pin_memory() per block costs ~30 us)
-        if not hasattr(self, "_rows_stage"):
-            self._rows_stage = [torch.empty(1024, dtype=torch.int32).pin_memory() for _ in range(8)]
-            self._rows_i = 0
-        st = self._rows_stage[self._rows_i % 8][:n]
-        self._rows_i += 1
-        st.copy_(torch.as_tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32))
-        rows = st.to(dev, non_blocking=True)
+        if rows is None or rows.numel() != n:
+            # slot indices through a small persistent pinned ring (a fresh pin_memory() per block costs ~30 us)
+            if not hasattr(self, "_rows_stage"):
+                self._rows_stage = [torch.empty(1024, dtype=torch.int32).pin_memory() for _ in range(8)]
+                self._rows_i = 0
+            st = self._rows_stage[self._rows_i % 8][:n]
+            self._rows_i += 1
+            st.copy_(torch.as_tensor([self.slot_of(p) for p in krum_set], dtype=torch.int32))
+            rows = st.to(dev, non_blocking=True)
         scores = torch.empty(n, dtype=torch.float32, device=dev)
         accept = torch.empty(n, dtype=torch.uint8, device=dev)
         if hasattr(self.L, "bsc_krum_select_mc_wait"):
@@ -208,40 +212,56 @@ class FusedComm(NcclComm):
         c0 = min(self.nchunk, self.rank * per)
         return c0, min(self.nchunk, c0 + per) - c0
 
-    def secagg_fused(self, xs, avail, precision: int, epoch: int):
-        """self.ypart must hold this rank's partial share sums.  Updates self.w64 / self.w32 on every rank."""
+    def secagg_fused(self, xs, avail, precision: int, epoch: int, gate: torch.Tensor | None = None, gate_min: int = 0):
+        """self.ypart must hold this rank's partial share sums.  Updates self.w64 / self.w32 on every rank; when the
+        kernel retires, every rank's slice has landed here.  gate: device int32 [1] contributor count (no step below
+        gate_min).  Share-check counters accumulate in self.bad (the engine reports per-block increments)."""
+        from ..ops.secagg import recover_matrix, _RecoverMat
+
         c0, nc = self.chunk_range()   # the kernel publishes SLOT_SHARES itself
-        xs_a = (c_i * 10)(*xs)
+        rm = recover_matrix(xs)
+        use_mat = 1
+        if rm is None:
+            use_mat = 0
+            rm = _RecoverMat()
+            for i, x in enumerate(xs):
+                rm.xs[i] = int(x)
         av = (ctypes.c_ubyte * 64)(*(list(avail) + [0] * (64 - len(avail))))
         _check(self.L.bsc_secagg_fused(self._tables["ypart"], self._tables["w64"], self._tables["w32"], self._tables["flags"],
-                                       self.world, self.rank, self.S, self.d, c0, nc, xs_a, av, float(10 ** precision),
-                                       c_p(self.base + self.o_cnt + 512), c_p(self.base + self.o_bad), epoch, self._stream()),
+                                       self.world, self.rank, self.S, self.d, c0, nc, ctypes.byref(rm), use_mat, av,
+                                       float(10 ** precision), c_p(self.base + self.o_cnt + 512),
+                                       c_p(self.base + self.o_cnt + 768), c_p(self.base + self.o_bad),
+                                       c_p(gate.data_ptr()) if gate is not None else None, gate_min, epoch, self._stream()),
                "secagg_fused")
-        self.wait(SLOT_WEIGHTS, epoch)
-        # `bad` accumulates over the run (no zeroing launch per block); report this block's increment lazily
-        prev = getattr(self, "_bad_prev", None)
-        cur = self.bad.clone()
-        self._bad_prev = cur
-        return cur if prev is None else cur - prev
+        return self.bad
 
     def all_gather_rows_u8(self, local: torch.Tensor) -> torch.Tensor:
-        """[per, k] uint8 blocks from every rank -> [world*per, k] (commitment bytes for the block)."""
+        """[per, cb_row] uint8 rows of my peers -> [world*per, cb_row] rows of every peer: peer stores + flags in one
+        small kernel (symm_allgather_rows_kernel), no library collective per block."""
         per = self.per
-        pad = torch.zeros(per, local.shape[1], dtype=local.dtype, device=local.device)
-        pad[: local.shape[0]] = local[:per]
+        assert local.shape[0] == per and local.shape[1] == self.cb_row and local.dtype == torch.uint8, local.shape
         if self.world == 1:
-            return pad
-        if local.shape[1] == self.cb_row and local.dtype == torch.uint8:
-            # peer stores + flags in one small kernel (symm_allgather_rows_kernel): no library collective per block
-            self._cb_seq = getattr(self, "_cb_seq", 0) + 1
-            buf = self._cb_seq & 1
-            tab = self._table(self.o_cb + buf * self.cb_bytes)
-            _check(self.L.bsc_symm_allgather_rows(tab, self._tables["flags"], c_p(self.base + self.o_flags), self.world,
-                                                  self.rank, c_p(pad.data_ptr()), per * self.cb_row, SLOT_POINTS,
-                                                  self._cb_seq, self._stream()), "symm_allgather_rows")
-            self._cb_keep = pad      # the kernel reads it asynchronously
-            return tensor_from_ptr(self.base + self.o_cb + buf * self.cb_bytes, (self.world * per, self.cb_row),
-                                   torch.uint8, self.device)
-        out = torch.empty(self.world * per, local.shape[1], dtype=local.dtype, device=local.device)
-        dist.all_gather_into_tensor(out, pad)
-        return out
+            return local
+        self._cb_seq = getattr(self, "_cb_seq", 0) + 1
+        buf = self._cb_seq & 1
+        tab = self._table(self.o_cb + buf * self.cb_bytes)
+        _check(self.L.bsc_symm_allgather_rows(tab, self._tables["flags"], c_p(self.base + self.o_flags), self.world,
+                                              self.rank, c_p(local.data_ptr()), per * self.cb_row, SLOT_POINTS,
+                                              self._cb_seq, self._stream()), "symm_allgather_rows")
+        return tensor_from_ptr(self.base + self.o_cb + buf * self.cb_bytes, (self.world * per, self.cb_row),
+                               torch.uint8, self.device)
+
+    def close(self):
+        """Unmap the peers' regions and free this rank's (after a barrier: nobody may still be storing into it)."""
+        if getattr(self, "base", None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if self.world > 1 and dist.is_initialized():
+            dist.barrier()
+        for q, b in enumerate(self.bases):
+            if q != self.rank and b:
+                self.L.bsc_ipc_close_handle(c_p(b))
+        for name in ("hi", "lo", "ypart", "w64", "w32", "bad", "gpart"):
+            setattr(self, name, None)
+        self.L.bsc_symm_free(c_p(self.base))
+        self.base, self.bases = None, []

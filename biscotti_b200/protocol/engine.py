@@ -12,18 +12,27 @@ What one `step()` does is the reference's block iteration (call stac
   9. w_{t+1} = w_t + sum, stake update, block append  honest.go:391-440, block.go:23-44
  10. flood + test error / attack rate                 main.go:1403-1444, honest.go:141-162
 
-There are no per-peer processes, sockets or wall-clock timeouts: peers are rows of device tensors,
-message arrival order is an explicit seeded permutation (so "first NUM_SAMPLES/2 shares win" and
-Krum's "first KRUM_UPDATETHRESH updates" are reproducible), and every rank replays the same control
-flow from the same block hash, so the ledger is replicated without gossip.
+There are no per-peer processes, sockets or wall-clock timeouts: peers are rows of device tensors, message
+arrival order is an explicit seeded permutation (so "first NUM_SAMPLES/2 shares win" and Krum's "first
+KRUM_UPDATETHRESH updates" are reproducible), and every rank replays the same control flow from the same
+block hash, so the ledger is replicated without gossip.
+
+How a block is scheduled on a GPU.  A block is a serial chain (hash -> VRF -> noisers -> noise -> Krum ->
+approved / contributors -> share sums -> reconstruction -> new weights -> hash).  Every link whose input is
+produced on the device is a kernel that reads it there (ops/chain.py, the *_dc kernel variants): the Krum verdict,
+the approved set, the contributor set and the noiser table never visit the host in front of the block's tail.
+The host plans what depends only on the previous hash and the stake (roles, arrival orders, candidate set),
+queues the chain, queues everything that is off the chain behind it on a second stream (witness MSM, miners'
+aggregation, error rates, the next block's local step + commitments) and on a third (the verifiers' approvals of
+every candidate), and then waits ONCE, for the tail's device->host copy (weights, counters, contributor list, the
+gathered commitment||signature rows).  Block assembly, stake update, hashing and append are one native call.
 """
 from __future__ import annotations
 
 import contextlib
+import ctypes
 import hashlib
 import math
-import random
-import struct
 import time
 from dataclasses import dataclass, field
 
@@ -32,11 +41,12 @@ import torch
 
 from ..config import BiscottiConfig, DEFAULT_STAKE, STAKE_UNIT, POLY_SIZE, NOISE_TABLE_ITERS
 from ..crypto import primitives as cp
-from ..crypto.schnorr_batch import SchnorrBatchSigner
+from ..crypto.schnorr_batch import ApprovalSigner
 from ..data.synthetic import make_data, poisoner_ids
 from ..ledger.chain import Blockchain, UpdateRecord
 from ..models.registry import Model
-from ..ops import ml, krum as krum_ops, secagg
+from ..ops import ml, krum as krum_ops, secagg, chain as chain_ops
+from ..ops._call import lib, ptr, stream as raw_stream, check
 from ..ops.msm import CommitmentEngine
 from ..utils.log import PeerLogger
 
@@ -58,6 +68,25 @@ class BlockReport:
     bad_shares: int = 0
     phase_ms: dict = field(default_factory=dict)
     unmasked_updates: int = 0
+    contributors: list = field(default_factory=list)
+
+
+@dataclass
+class _Plan:
+    """Everything about a block that follows from the previous hash, the stake and who is alive (host side)."""
+    verifiers: list
+    miners: list
+    workers: list
+    prev_hash: bytes
+    krum_set: list = field(default_factory=list)
+    share_rank: list = field(default_factory=list)
+    signers: list = field(default_factory=list)
+    approved_ok: bool = False
+    trigger: int = 0
+    shares_avail: list = field(default_factory=list)
+    xs: list = field(default_factory=list)
+    enough_shares: bool = False
+    clip: int = 0
 
 
 class BiscottiEngine:
@@ -68,6 +97,7 @@ class BiscottiEngine:
         self.rank, self.world, self.comm = rank, world, comm
         n = cfg.num_nodes
         per = (n + world - 1) // world
+        self.per = per
         self.local_ids = list(range(rank * per, min(n, (rank + 1) * per)))
         self.owner = [p // per for p in range(n)]
         self.P = len(self.local_ids)
@@ -84,11 +114,15 @@ class BiscottiEngine:
         self.stake = [DEFAULT_STAKE] * n
         self.alive = [True] * n
         self.iteration = 0
-        self._pre = None          # prefetched (Q, chunkC, fullC) of the next iteration, see _prefetch_next
+        self._pre = None          # prefetched local step + commitments of the next iteration, see _prefetch_next
         self._next_inputs, self._fed_inputs = None, False
         self._eval_pending = None
         self._vrf_early = None
-        self._main = self._wstream = self._wevent = None     # streams of step() / _witness_side
+        self._main = self._side = None          # chain stream / off-chain stream of a pipelined GPU engine
+        self._wstream = None                    # alias of _side, kept for callers that look for the witness stream
+        self._wevent = None
+        self._side_done = [None, None]          # per block parity: off-chain work of that block has finished
+        self._eval_done = None
         self.last_aggregate = None
         self.keys = cp.derive_peer_keys(n, cfg.seed)
         self.poisoners = poisoner_ids(cfg)
@@ -117,10 +151,22 @@ class BiscottiEngine:
             self.commit = CommitmentEngine(self.d, self.S, tau=cfg.srs_tau or self._random_tau(), device=self.device,
                                            window=cfg.msm_window)
         self.vrf = cp.BatchedVRF([k.vrf_noise for k in self.keys], self.device)
-        self.signer = SchnorrBatchSigner(self.device) if (cfg.verification and cfg.sign_approvals) else None
+        self.signer = None
+        if cfg.verification and cfg.sign_approvals and self.commit is not None:
+            self.signer = ApprovalSigner(self.device, [k.schnorr_secret for k in self.keys])
+        # Nonce salt of the approvals: binds the run (seed, data, every flag) - the previous block hash binds the fork.
+        # (Scheduling knobs - prefetch, pipeline, kernel choices - do not change what is signed and stay out of it.)
+        sched = {"prefetch", "pipeline", "gram_impl", "comm_impl", "msm_window", "affine_wire", "eval_every", "extra",
+                 "max_iterations", "test_size"}
+        self.run_salt = hashlib.sha256(("bsc-run-salt|" + repr(sorted((k, v) for k, v in cfg.to_dict().items()
+                                                                        if k not in sched))).encode()).digest()
+        self.nsig_max = cfg.num_verifiers if self.signer is not None else 0
+        self.pack_stride = 64 * (1 + self.nsig_max)
         self.reports: list[BlockReport] = []
         self._rng = np.random.RandomState(cfg.seed * 65537 % (2**31))
         self._timing = False
+        self._bad_prev = np.zeros(4, dtype=np.int64)
+        self._bufs_ready = False
 
     # ------------------------------------------------------------------------------------------
     def _random_tau(self) -> int:
@@ -129,13 +175,16 @@ class BiscottiEngine:
 
     def _arrival_order(self, ids: list[int], tag: str) -> list[int]:
         """Deterministic stand-in for network arrival order, identical on every rank."""
-        h = hashlib.sha256(f"{self.cfg.seed}-{self.iteration}-{tag}".encode()).digest()
-        out = list(ids)
-        random.Random(int.from_bytes(h[:8], "little")).shuffle(out)   # Mersenne twister: same order on every rank
-        return out
+        perm = chain_ops.seeded_perm(chain_ops.seed64(self.cfg.seed, self.iteration, tag), len(ids))
+        return [ids[i] for i in perm]
 
     def _phase(self, name: str):
         return _Phase(self, name)
+
+    @property
+    def pipelined(self) -> bool:
+        """Chain / off-chain / approval streams (GPU engines that are not being instrumented)."""
+        return (self.device.type == "cuda" and self.cfg.mode != "fedsys" and self.cfg.pipeline and not self._timing)
 
     def _idx(self, values, dtype=torch.int32) -> torch.Tensor:
         """Small host list -> device tensor through a pinned staging ring (asynchronous H2D, no host sync)."""
@@ -153,10 +202,10 @@ class BiscottiEngine:
         return view.to(self.device, non_blocking=True)
 
     def _idx_pack(self, *specs):
-        """Several small host lists -> device tensors with ONE staging copy.  specs: (values, dtype) pairs; each
+        """Several small host arrays -> device tensors with ONE staging copy.  specs: (values, dtype) pairs; each
         tensor starts on a 16-byte boundary of the shared buffer."""
         if self.device.type != "cuda":
-            return [torch.tensor(v, dtype=dt) for v, dt in specs]
+            return [torch.as_tensor(np.asarray(v), dtype=dt).clone() if len(v) else torch.empty(0, dtype=dt) for v, dt in specs]
         if not hasattr(self, "_pack_stage"):
             self._pack_stage = [torch.empty(1 << 16, dtype=torch.uint8).pin_memory() for _ in range(8)]
             self._pack_i = 0
@@ -171,9 +220,27 @@ class BiscottiEngine:
             return [self._idx(v, dt) for v, dt in specs]
         for (o, nb), (v, dt) in zip(offs, specs):
             if nb:
-                buf[o: o + nb].view(dt).copy_(torch.as_tensor(v, dtype=dt))
+                buf[o: o + nb].view(dt).copy_(torch.as_tensor(np.asarray(v), dtype=dt))
         dev_buf = buf[: max(off, 16)].to(self.device, non_blocking=True)
         return [dev_buf[o: o + nb].view(dt) for (o, nb), (v, dt) in zip(offs, specs)]
+
+    def _ensure_bufs(self):
+        """Persistent device buffers of everything that crosses a stream boundary (double-buffered by block parity
+        where the off-chain stream may still be reading block t while the chain of block t+1 writes)."""
+        if self._bufs_ready:
+            return
+        dev, P = self.device, max(1, self.P)
+        nk = max(1, self.cfg.num_nodes)
+        i32 = dict(dtype=torch.int32, device=dev)
+        self._plan_out = [dict(counts=torch.zeros(8, **i32), contrib_pos=torch.zeros(nk, **i32), sel=torch.zeros(P, **i32),
+                               appr_local=torch.zeros(P, **i32), csel=torch.zeros(P, **i32)) for _ in range(2)]
+        self._cbytes = [torch.zeros(P, 64, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self._pack = [torch.zeros(self.per, self.pack_stride, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self._ysum = torch.zeros(self.cfg.nchunk, self.S, dtype=torch.int64, device=dev)
+        self._bad = self.comm.bad if self.fused else torch.zeros(4, dtype=torch.int32, device=dev)
+        self._noiser_tab = torch.full((P, max(1, self.cfg.num_noisers)), -1, **i32)
+        self._plan_keep = [None, None]
+        self._bufs_ready = True
 
     # ------------------------------------------------------------------------------------------
     def select_roles(self):
@@ -195,10 +262,8 @@ class BiscottiEngine:
             # one kernel, keyed by (seed, iteration, peer, row): no generator state, no top-k, same rows on any rank
             if not hasattr(self, "_mb_idx"):
                 self._mb_idx = torch.empty(self.P, B, dtype=torch.int32, device=self.device)
-            from ..ops._call import lib, ptr, stream, check
-
             check(lib().bsc_sample_minibatch(self.cfg.seed & (2**64 - 1), it, ptr(self.data.peer_ids), self.P, Ns, B,
-                                             ptr(self._mb_idx), stream(self.device)), "sample_minibatch")
+                                             ptr(self._mb_idx), raw_stream(self.device)), "sample_minibatch")
             return self._mb_idx
         # One seeded draw for ALL n peers (so the result does not depend on how peers are sharded over
         # ranks), generated on the engine's device; each rank keeps the rows of its own peers.
@@ -211,12 +276,52 @@ class BiscottiEngine:
         return idx[lo: lo + max(1, self.P)].contiguous()
 
     # ------------------------------------------------------------------------------------------
+    def _host_plan(self) -> _Plan:
+        """Roles, candidate set, arrival orders and availability of a block - functions of the previous hash, the
+        stake map and who is alive, identical on every rank (vrf.go:103-182, krum.go:296-314, 368-388, main.go:360)."""
+        cfg, it = self.cfg, self.iteration
+        verifiers, miners, prev_hash = self.select_roles()
+        committee = set(verifiers) | set(miners)
+        workers = [p for p in range(cfg.num_nodes) if p not in committee and self.alive[p]]
+        pl = _Plan(verifiers, miners, workers, prev_hash)
+        if not verifiers or not miners or not workers:
+            return pl
+        arrival = self._arrival_order(workers, "verify")
+        krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh arrivals, sorted by id
+        if cfg.random_sampling and len(krum_set) > cfg.num_samples:
+            # -rs (krum.go:310, 368-388): a permutation seeded by the iteration count, keep NUM_SAMPLES of them
+            perm = chain_ops.seeded_perm(chain_ops.seed64("rs", it), len(krum_set))
+            krum_set = sorted(krum_set[i] for i in perm[: cfg.num_samples])
+        pl.krum_set = krum_set
+        nk = len(krum_set)
+        pl.clip = int(math.floor(cfg.krum_adversary_frac * nk))
+        # share arrival at the miners: a fixed permutation of the candidates; the approved ones among the first
+        # `trigger` of it (in that order) are the block's contributors (main.go:360 + the leader's intersection)
+        perm = chain_ops.seeded_perm(chain_ops.seed64(cfg.seed, it, "shares"), nk)
+        rank_of = [0] * nk
+        for r, i in enumerate(perm):
+            rank_of[i] = r
+        pl.share_rank = rank_of
+        pl.signers = [v for v in verifiers if self.alive[v]]
+        # a worker proceeds when it holds >= floor(nv/2) signatures (main.go:1686); every live verifier runs the
+        # same Krum on the same set, so the signature count is the number of live verifiers
+        pl.approved_ok = bool(pl.signers) and len(pl.signers) >= len(verifiers) // 2
+        pl.trigger = max(1, cfg.num_samples // 2) if cfg.share_trigger == "half" else nk
+        alive_miners = [m for m in miners if self.alive[m]]
+        pl.shares_avail = self._available_shares(miners, alive_miners)
+        pl.xs = [s for s, a in enumerate(pl.shares_avail) if a][:POLY_SIZE]
+        pl.enough_shares = sum(pl.shares_avail) >= POLY_SIZE and len(alive_miners) > 0     # main.go:2079
+        return pl
+
+    # ------------------------------------------------------------------------------------------
     def _local_and_commit(self, inputs, it: int, timed: bool):
-        """Local SGD step of every local peer from the current global weights, then quantisation and the
-        polynomial commitments of the update (phases 2 and 3 of an iteration).  Returns (Q, chunkC, fullC)."""
+        """Local SGD step of every local peer from the current global weights, then quantisation, the polynomial
+        commitments of the update and their 64-byte wire form (phases 2 and 3 of an iteration).  Returns a dict with
+        Q, chunkC, cbytes (device [P, 64]) and, on a pipelined engine, the events `u_ready` / `c_ready`."""
         cfg, dev = self.cfg, self.device
         slot = it % NOISE_TABLE_ITERS
         phase = self._phase if timed else (lambda name: contextlib.nullcontext())
+        out = {"it": it, "Q": None, "chunkC": None, "cbytes": None, "u_ready": None, "c_ready": None}
         with phase("local_step"):
             if inputs is not None:
                 X, y = inputs
@@ -227,15 +332,28 @@ class BiscottiEngine:
             if self.P:
                 pid = self.data.peer_ids if not self.external_inputs else torch.tensor(self.local_ids, dtype=torch.int32, device=dev)
                 self.model.local_step(self.w32, X, y, idx, self.U, peer_ids=pid, slot=slot)
-        Q = chunkC = fullC_dev = None
+                if cfg.dp_in_model and cfg.noising and cfg.epsilon > 0 and self.model.kind != "logistic":
+                    # DP_IN_MODEL (honest.go:172-179, main.go:155): the peer's own presampled noise goes INTO the delta
+                    # that is committed, shared and aggregated (the NumPy logistic path always does this, inside its step)
+                    own = pid.view(-1, 1).contiguous()
+                    ml.noise_mix(self.U, own, cfg.seed ^ 0x6F776E6E, slot, cfg.noise_scale, self.d, want_planes=False,
+                                 in_place=True)
+            if dev.type == "cuda" and self.pipelined:
+                out["u_ready"] = torch.cuda.Event()
+                out["u_ready"].record()
         if self.commit is not None and self.P:
             with phase("commit"):
                 Q = secagg.quantize(self.U, self.d, cfg.precision)
                 chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
-                # full-vector commitments stay Jacobian on the device; the rows that enter the block are
-                # normalised on the host with one shared inversion when the block is assembled
-                fullC_dev = self.commit.full_commitments(chunkC, jacobian=True).view(torch.uint8)   # [P, 96]
-        return Q, chunkC, fullC_dev
+                full = self.commit.full_commitments(chunkC)                          # affine [P, 16]
+                self._ensure_bufs()
+                cb = self._cbytes[it & 1]
+                self.commit.to_bytes_into(full, cb)                                  # [P, 64] wire bytes, on the device
+                out.update(Q=Q, chunkC=chunkC, cbytes=cb)
+                if dev.type == "cuda" and self.pipelined:
+                    out["c_ready"] = torch.cuda.Event()
+                    out["c_ready"].record()
+        return out
 
     def _prefetch_next(self, it_next: int):
         """Queue the next iteration's local step and commitment MSM behind this iteration's aggregation kernel.
@@ -251,9 +369,9 @@ class BiscottiEngine:
         if nxt is not None and len(nxt) == 3:      # (X, y, event): the H2D copy was issued on another stream
             torch.cuda.current_stream(self.device).wait_event(nxt[2])
             nxt = (nxt[0], nxt[1])
-        Q, chunkC, fullC = self._local_and_commit(nxt, it_next, timed=False)
-        self._pre = {"it": it_next, "Q": Q, "chunkC": chunkC, "fullC": fullC,
-                     "src": None if nxt is None else nxt[0].data_ptr()}
+        pre = self._local_and_commit(nxt, it_next, timed=False)
+        pre["src"] = None if nxt is None else nxt[0].data_ptr()
+        self._pre = pre
 
     def step(self, inputs=None, next_inputs=None) -> BlockReport:
         """Run one block iteration.  `inputs` = (X [P,B,F], y [P,B]) device tensors when the caller feeds
@@ -262,35 +380,40 @@ class BiscottiEngine:
         complete), if the caller already has them: a double-buffered input pipeline lets the engine start the
         next local step while this block is being assembled.
 
-        On a GPU the iteration runs on the engine's own high-priority stream (ordered after the caller's stream on
-        entry, and the caller's stream after it on exit), so that the witness MSM — queued on a default-priority
-        stream, see _witness_side — yields SM slots to the kernels the block is waiting for."""
-        if self.device.type != "cuda" or self.cfg.mode == "fedsys" or not self.cfg.overlap_witness:
+        On a GPU the block's chain runs on the engine's own high-priority stream (ordered after the caller's stream on
+        entry, and the caller's stream after it on exit), so that the off-chain work queued on the default-priority
+        stream - witness MSM, aggregation, the next local step and its commitments - yields SM slots to the kernels the
+        block is waiting for."""
+        if not self.pipelined:
             return self._step(inputs, next_inputs)
         if self._main is None:
             self._main = torch.cuda.Stream(self.device, priority=-1)
+            self._side = torch.cuda.Stream(self.device, priority=0)
+            self._wstream = self._side
         cur = torch.cuda.current_stream(self.device)
         self._main.wait_stream(cur)
-        prev_w = self._wevent
+        prev_w = self._side_done[(self.iteration + 1) & 1]
         with torch.cuda.stream(self._main):
             rep = self._step(inputs, next_inputs)
         cur.wait_stream(self._main)
         if prev_w is not None:
-            # the previous block's witnesses had this whole iteration to finish; waiting for them here keeps every
-            # iteration's device timeline (events on the caller's stream) accountable for one block of witness work
+            # the previous block's off-chain work had this whole iteration to finish; waiting for it here keeps every
+            # iteration's device timeline (events on the caller's stream) accountable for one block of that work
             cur.wait_event(prev_w)
         return rep
 
-    def _witness_side(self):
-        """Stream for the KZG witness MSM and the miners' homomorphic aggregation.  Nothing that goes into the block
-        depends on their result (the block carries the contributors' commitments, the reconstructed weights and the
-        approvals), so they run beside share aggregation, reconstruction, block assembly and the next block's VRF
-        instead of in front of them.  Instrumented runs keep them in line so that phase times stay attributable."""
-        if self.device.type != "cuda" or self._main is None or self._timing:
-            return None
-        if self._wstream is None:
-            self._wstream = torch.cuda.Stream(self.device, priority=0)
-        return self._wstream
+    @contextlib.contextmanager
+    def _off_chain(self, after: "torch.cuda.Event | None" = None):
+        """Queue work off the block's chain: on the second stream of a pipelined engine, in line otherwise."""
+        if not self.pipelined:
+            yield None
+            return
+        if after is None:          # default: after everything queued on the chain so far
+            after = torch.cuda.Event()
+            after.record()
+        self._side.wait_event(after)
+        with torch.cuda.stream(self._side):
+            yield self._side
 
     def _step(self, inputs=None, next_inputs=None) -> BlockReport:
         cfg = self.cfg
@@ -303,6 +426,8 @@ class BiscottiEngine:
         it = self.iteration
         n = cfg.num_nodes
         dev = self.device
+        cuda = dev.type == "cuda"
+        par = it & 1
         phases = {}
         self._phases = phases
         # ---- fault injection (main.go:1117-1120): a failing peer sits this block out and rejoins
@@ -319,252 +444,266 @@ class BiscottiEngine:
             for p in cut:
                 self.alive[p] = False
             self._cut = cut
-        # ---- 1. roles
-        verifiers, miners, prev_hash = self.select_roles()
-        committee = set(verifiers) | set(miners)
-        workers = [p for p in range(n) if p not in committee and self.alive[p]]
+        # ---- 1. roles and everything else that follows from the previous hash
+        pl = self._host_plan()
+        verifiers, miners, workers, prev_hash = pl.verifiers, pl.miners, pl.workers, pl.prev_hash
+        krum_set = pl.krum_set
+        nk = len(krum_set)
         slot = it % NOISE_TABLE_ITERS
-        rep = BlockReport(it, b"", True, verifiers, miners, len(workers), 0, 0, 0)
-        if not verifiers or not miners or not workers:
-            return self._finish_block(rep, [], None, phases, t0)   # main.go:1696-1707, 1934-1944
+        rep = BlockReport(it, b"", True, verifiers, miners, len(workers), nk, 0, 0)
+        if not verifiers or not miners or not workers or not pl.enough_shares or nk == 0:
+            return self._finish_block(rep, phases, t0)        # main.go:1696-1707, 1934-1944, 2099-2117
+        self._ensure_bufs()
+        pout = self._plan_out[par]
 
-        # VRF evaluation of every peer on the previous block hash runs on a side stream, overlapped with
-        # the local step and the commitment MSM; the noise phase collects it.
+        # VRF evaluation of every peer on the previous block hash: launched the moment that block was hashed
+        # (_finish_block) on its own high-priority stream; the noise phase consumes it on the device.
         use_noise = cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0
         early, self._vrf_early = self._vrf_early, None
         if use_noise and early is not None and early[0] == prev_hash:
-            vrf_handle = early[1]          # launched the moment the previous block was hashed (_finish_block)
+            vrf_handle = early[1]
         else:
-            vrf_handle = self.vrf.launch(prev_hash) if use_noise else None
+            vrf_handle = (self.vrf.launch_dev(prev_hash) if cuda else self.vrf.launch(prev_hash)) if use_noise else None
 
         # ---- 2/3. local step + commitments of my peers.  Neither depends on the roles or on the block hash, so
         # the previous step may already have queued them behind its aggregation kernel (see _prefetch_next).
         pre, self._pre = self._pre, None
-        if pre is not None and pre["it"] == it and pre["src"] == (None if inputs is None else inputs[0].data_ptr()):
-            Q, chunkC, fullC_dev = pre["Q"], pre["chunkC"], pre["fullC"]
-        else:
-            Q, chunkC, fullC_dev = self._local_and_commit(inputs, it, timed=True)
+        if not (pre is not None and pre["it"] == it and pre.get("src") == (None if inputs is None else inputs[0].data_ptr())):
+            with self._off_chain():
+                pre = self._local_and_commit(inputs, it, timed=True)
+        Q, chunkC, cbytes = pre["Q"], pre["chunkC"], pre["cbytes"]
 
-        # host-side bookkeeping that does not need the VRF outputs goes first: the noise phase below waits for them
-        arrival = self._arrival_order(workers, "verify")
-        krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh, sorted by id
-        rep.n_krum = len(krum_set)
-        # Approvals (krum.go:338-358): the signature halves T = v*G do not depend on the Krum verdict or on the message,
-        # only on (block, update, verifier), so they are started for every candidate update now — the host would
-        # otherwise sit idle waiting for the VRF — and only those of the updates that reach the block are completed.
-        signers = [v for v in verifiers if self.alive[v]]
-        sig_handle = None
-        if self.signer is not None and self.commit is not None and signers and krum_set:
-            nk, ns = len(krum_set), len(signers)
-            if not hasattr(self, "_sk_mat"):     # all peers' signing keys as one [n, 32] array (pKeyG1.json holds them all)
-                self._sk_mat = np.frombuffer(b"".join(k.schnorr_secret for k in self.keys), dtype=np.uint8).reshape(n, 32)
-            tags = np.empty(nk * ns, dtype=[("it", "<i8"), ("p", "<i4"), ("v", "<i4")])     # = struct.pack("<qii", it, p, v)
-            tags["it"], tags["p"], tags["v"] = it, np.repeat(krum_set, ns), np.tile(signers, nk)
-            sig_handle = self.signer.launch(np.tile(self._sk_mat[signers], (nk, 1)), tags.view(np.uint8).reshape(nk * ns, 16))
-        # ---- 4. noisers + noise
+        # ---- host -> device: the block's plan in one staging copy
+        stake_m = np.asarray([s if a else 0 for s, a in zip(self.stake, self.alive)], dtype=np.int32)
+        is_worker = np.zeros(n, dtype=np.uint8)
+        is_worker[workers] = 1
+        kpos = {p: i for i, p in enumerate(krum_set)}
+        # Single-rank tcgen05 Krum: noise_mix writes the candidates' bf16 planes and norms compacted and in Krum
+        # order (row = position in krum_set), so the Gram kernel needs no gather; the fp32 noised rows are only
+        # materialised for the paths that read them (RONI, SIMT Gram, NCCL gathers).
+        self._compact = (cuda and self.comm is None and cfg.verification and cfg.defense != "RONI"
+                         and cfg.gram_impl in ("auto", "tcgen05") and nk >= 3)
+        dst_rows = [kpos.get(p, -1) for p in self.local_ids] if self._compact else []
+        local_row = [self.local_index.get(p, -1) for p in krum_set]
+        slots = [self.comm.slot_of(p) for p in krum_set] if self.fused else []
+        (stake_d, isw_d, dst_row, local_row_d, share_rank_d, krum_ids_d, signers_d, xs_t, av_t, slots_d, hash_d) = \
+            self._idx_pack((stake_m, torch.int32), (is_worker, torch.uint8), (dst_rows, torch.int32),
+                           (local_row, torch.int32), (pl.share_rank, torch.int32), (krum_set, torch.int32),
+                           (pl.signers, torch.int32), (pl.xs, torch.int32), (pl.shares_avail, torch.uint8),
+                           (slots, torch.int32), (np.frombuffer(bytearray(prev_hash), dtype=np.uint8), torch.uint8))
+        self._plan_keep[par] = (stake_d, local_row_d, krum_ids_d, signers_d)      # read on other streams: keep alive
+        if not self._compact:
+            dst_row = None
+
+        # ---- 6 (early). approvals: T = v*G, c = H(T || commitment), r = v - x*c depend only on (chain position, update,
+        # verifier) and on the commitment, not on the Krum verdict: every candidate of this rank is signed now, on the
+        # approval stream, while the VRF and Krum run; only the rows of the block's updates are ever read.
+        salt64 = self.run_salt + (prev_hash + b"\0" * 32)[:32]
+        sig_event = None
+        ns = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
+        if cuda and self.commit is not None and self.P:
+            plan_ready = None
+            if self.pipelined:
+                plan_ready = torch.cuda.Event()
+                plan_ready.record()
+            pack = self._pack[par]
+            if ns:
+                if self.pipelined and pre["c_ready"] is not None:
+                    self.signer.stream.wait_event(pre["c_ready"])
+                sig_event = self.signer.launch(salt64, it, krum_ids_d, local_row_d, nk, signers_d, ns, cbytes, pack,
+                                               after=plan_ready, serial=not self.pipelined)
+            else:
+                with self._off_chain(pre["c_ready"]):
+                    check(lib().bsc_pack_commitments(ptr(cbytes), self.P, ptr(pack), pack.stride(0), raw_stream(dev)),
+                          "pack_commitments")
+                    if self.pipelined:
+                        sig_event = torch.cuda.Event()
+                        sig_event.record()
+
+        # ---- 4. noisers + noise (chain)
+        if self.pipelined and pre["u_ready"] is not None:
+            torch.cuda.current_stream(dev).wait_event(pre["u_ready"])
         with self._phase("noise"):
             nn_cols = max(1, cfg.num_noisers)
-            tab_np = np.full((max(1, self.P), nn_cols), -1, dtype=np.int32)
-            noisers_of = {}
-            if use_noise:
-                stake = [s if a else 0 for s, a in zip(self.stake, self.alive)]
-                is_worker = np.zeros(n, dtype=np.uint8)
-                is_worker[workers] = 1
-                full_tab = self.vrf.noiser_table(vrf_handle, stake, is_worker, cfg.num_noisers)   # [n, nn]
+            noisers_host = None
+            if use_noise and cuda:
+                xyz, vev, hd = vrf_handle
+                torch.cuda.current_stream(dev).wait_event(vev)
+                noiser_tab = self._noiser_tab
                 if self.P:
-                    lo_id = self.local_ids[0]
-                    tab_np = full_tab[lo_id: lo_id + self.P]
-                if self.colluder_ids:
-                    noisers_of = {p: [int(q) for q in full_tab[p] if q >= 0] for p in workers}
+                    chain_ops.vrf_noisers(xyz, hash_d, len(prev_hash), stake_d, isw_d, self.data.peer_ids if not self.external_inputs
+                                          else self._idx(self.local_ids), cfg.num_noisers, noiser_tab)
+            elif use_noise:
+                full_tab = self.vrf.noiser_table(vrf_handle, stake_m.tolist(), is_worker, cfg.num_noisers)   # [n, nn]
+                noisers_host = full_tab
+                lo_id = self.local_ids[0] if self.P else 0
+                noiser_tab = torch.from_numpy(np.ascontiguousarray(full_tab[lo_id: lo_id + max(1, self.P)]))
+            else:
+                noiser_tab = torch.full((max(1, self.P), nn_cols), -1, dtype=torch.int32, device=dev)
             scale = cfg.noise_scale if use_noise else 0.0
-            # Single-rank tcgen05 Krum: the kernel writes the candidates' bf16 planes and norms compacted and in Krum
-            # order (row = position in krum_set), so the Gram kernel needs no gather; the fp32 noised rows are only
-            # materialised for the paths that read them (RONI, SIMT Gram, NCCL gathers).
-            self._compact = (dev.type == "cuda" and self.comm is None and cfg.verification and cfg.defense != "RONI"
-                             and cfg.gram_impl in ("auto", "tcgen05") and len(krum_set) >= 3)
-            kpos = {p: i for i, p in enumerate(krum_set)}
-            rows = [kpos.get(p, -1) for p in self.local_ids] if self._compact else []
-            # noiser table and row map travel in one staging copy
-            noiser_tab, dst_row = self._idx_pack((tab_np.reshape(-1), torch.int32), (rows, torch.int32))
-            noiser_tab = noiser_tab.view(-1, nn_cols)
-            if not self._compact:
-                dst_row = None
             Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab, cfg.seed, slot, scale, self.d,
                                              ldh=self.ldh, out_hi=self.comm.hi if self.fused else None,
                                              out_lo=self.comm.lo if self.fused else None, dst_row=dst_row,
                                              want_un=not self._compact)
 
-        # ---- 5. verification
-        accepted: list[int] = []
+        # ---- 5. verification -> accept mask on the device
         with self._phase("verify"):
-            if not cfg.verification:
-                accepted = list(krum_set)
+            if not cfg.verification or nk < 3:
+                accept = torch.ones(nk, dtype=torch.uint8, device=dev)
             elif cfg.defense == "RONI":
-                accepted = self._roni(krum_set, Un)
+                accept = self._roni(krum_set, Un)
             else:
-                accepted = self._krum(krum_set, Un, hi, lo, norms)
-        rep.n_accepted = len(accepted)
-        # collusion accounting (main.go:1026-1057, 1138-1144)
-        if self.colluder_ids:
-            vcol = any(v in self.colluder_ids for v in verifiers)
-            rep.unmasked_updates = sum(1 for p in krum_set if vcol and noisers_of.get(p) and
-                                       all(q in self.colluder_ids for q in noisers_of[p]))
+                accept = self._krum(krum_set, Un, hi, lo, norms, pl.clip, slots_d)
+            # approved set, contributors and the compacted local row lists, still on the device
+            chain_ops.block_plan(accept, share_rank_d, local_row_d, pl.approved_ok, pl.trigger, pout)
+        counts = pout["counts"]
+        n_lc, n_la, n_con = counts[2:3], counts[3:4], counts[1:2]
 
-        # ---- 6. approvals: every reachable verifier signs the commitment of each accepted update; a worker
-        # proceeds when it holds >= floor(nv/2) signatures (main.go:1686).  All verifiers run the same Krum on
-        # the same set here, so the signature count is the number of live verifiers.
-        approved = accepted if (signers and len(signers) >= len(verifiers) // 2) else []
-
-        # ---- 7/8. shares, witnesses, aggregation, reconstruction, SGD step
-        share_order = [p for p in self._arrival_order(approved, "shares")]
-        trigger = max(1, cfg.num_samples // 2) if cfg.share_trigger == "half" else len(share_order)
-        contributors = sorted(share_order[:trigger])            # main.go:360 + leader intersection
-        alive_miners = [m for m in miners if self.alive[m]]
-        shares_avail = self._available_shares(miners, alive_miners)
-        enough = len(contributors) >= 2 and sum(shares_avail) >= POLY_SIZE and len(alive_miners) > 0
-        if not enough:
-            return self._finish_block(rep, [], None, phases, t0)   # main.go:2099-2117
-        rep.n_contributors = len(contributors)
-        local_contrib = [self.local_index[p] for p in contributors if p in self.local_index]
-        appr_rows = [self.local_index[p] for p in approved if p in self.local_index]
-        pos = {r: i for i, r in enumerate(appr_rows)}          # positions of contributors inside the approved list
-        xs = [s for s, a in enumerate(shares_avail) if a][:POLY_SIZE]
-        sel, appr_local, csel, xs_t, av_t = self._idx_pack(
-            (local_contrib, torch.int32), (appr_rows, torch.int32), ([pos[r] for r in local_contrib], torch.int32),
-            (xs, torch.int32), (shares_avail, torch.uint8))
-        agg_box = [None]
-        launch_witnesses = None
-        if cfg.secure_agg:
-            if self.commit is not None and self.P:
-                # Every approved worker generates shares + KZG witnesses for the miners (kyber.go:456-482) and the
-                # miners add the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287).
-                # Nothing that enters the block depends on them, so they are *queued after* the share aggregation,
-                # the reconstruction and the block's device->host collection (see after_copies below): the device
-                # works on them while the host assembles, signs and hashes the block.
-
-                def launch_witnesses():
-                    side = self._witness_side()
-                    if side is None:
-                        with self._phase("witness"):
-                            W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire) if appr_rows else None
-                        with self._phase("miner_aggregate"):
-                            if W is not None and local_contrib:
-                                aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)        # [nchunk, S, 16|24]
-                                aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)    # [nchunk, 16|24]
-                                agg_box[0] = (aggC, aggW)
-                    elif appr_rows:
-                        ready = torch.cuda.Event()
-                        ready.record()                     # Q, chunkC and the index tensors are complete at this point
-                        side.wait_event(ready)
-                        with torch.cuda.stream(side):
-                            W = self.commit.witnesses(Q, appr_local, affine=cfg.affine_wire)
-                            if local_contrib:
-                                aggW = self.commit.aggregate(W, csel, affine=cfg.affine_wire)
-                                aggC = self.commit.aggregate(chunkC, sel, affine=cfg.affine_wire)
-                                agg_box[0] = (aggC, aggW)
-                            self._wevent = torch.cuda.Event()
-                            self._wevent.record()
-                        for t in (Q, chunkC, appr_local, csel, sel):  # allocated on the main stream, read on `side`
-                            t.record_stream(side)
-            with self._phase("secagg"):
+        # ---- 7/8. share sums, reconstruction, SGD step (chain).  Gated on the device: fewer than two contributors
+        # (main.go:2079) leaves the weights untouched and the tail mints the empty block.
+        if self.pipelined and self._eval_done is not None:
+            torch.cuda.current_stream(dev).wait_event(self._eval_done)     # the previous block's error rates read w
+        with self._phase("secagg"):
+            if cfg.secure_agg:
                 if self.fused:
-                    # reduce-scatter + reconstruct + SGD step + all-gather in one kernel over peer memory
-                    if sel.numel():
-                        secagg.share_sum(self.U, sel, self.d, self.S, cfg.precision, out=self.comm.ypart)
-                    else:
-                        self.comm.ypart.zero_()
-                    bad = self.comm.secagg_fused(xs, shares_avail, cfg.precision, it + 1)
+                    secagg.share_sum(self.U, pout["sel"], self.d, self.S, cfg.precision, out=self.comm.ypart, count=n_lc)
+                    self.comm.secagg_fused(pl.xs, pl.shares_avail, cfg.precision, it + 1, gate=n_con, gate_min=2)
                 else:
-                    Ysum = secagg.share_sum(self.U, sel, self.d, self.S, cfg.precision) if sel.numel() else \
-                        torch.zeros(cfg.nchunk, self.S, dtype=torch.int64, device=dev)
+                    Ysum = secagg.share_sum(self.U, pout["sel"], self.d, self.S, cfg.precision, out=self._ysum, count=n_lc)
                     if self.comm is not None:
                         Ysum = self.comm.all_reduce_i64(Ysum)
                     self._last_ysum = Ysum
-                    _, bad = secagg.reconstruct_step(Ysum, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision)
-        else:
-            with self._phase("secagg"):
+                    secagg.reconstruct_step_dev(Ysum, pl.xs, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision,
+                                                bad=self._bad, gate=n_con, gate_min=2)
+            else:
                 if self.comm is not None and self.world > 1:
-                    rows = self.comm.gather_rows(contributors, self.U, self.local_index, self.owner)
-                    rsel = torch.arange(len(contributors), dtype=torch.int32, device=dev)
-                    secagg.plain_sum_step(rows, rsel, self.d, self.w64, self.w32)
+                    rows = self.comm.gather_rows(krum_set, self.U, self.local_index, self.owner)
+                    secagg.plain_sum_step(rows, pout["contrib_pos"], self.d, self.w64, self.w32, count=n_con, gate=n_con,
+                                          gate_min=2)
                 else:
-                    secagg.plain_sum_step(self.U, sel, self.d, self.w64, self.w32)
-                bad = torch.zeros(2, dtype=torch.int32, device=dev)
+                    secagg.plain_sum_step(self.U, pout["sel"], self.d, self.w64, self.w32, count=n_lc, gate=n_con, gate_min=2)
 
-        # ---- 9. block assembly (host).  Evaluation of the new weights is launched first so that one
-        # device->host collection (weights, commitments, share-check counters, error rates) and one stream
-        # synchronisation serve the whole tail of the block.
-        if self._timing and launch_witnesses is not None:
-            launch_witnesses()            # instrumented runs: in line, so the phases do not nest
-            launch_witnesses = None
-        with self._phase("block"):
-            updates = []
-            commits = {}
-            want = {"w": self.w64, "bad": bad}
-            do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
-            gathered = False
-            if self.commit is not None and self.P:
-                if self.comm is not None and hasattr(self.comm, "all_gather_rows_u8"):
-                    want["cb"] = self.comm.all_gather_rows_u8(fullC_dev)             # [world*per, 96], row = peer id
-                    gathered = True
-                else:
-                    want["cb"] = fullC_dev
-            if sig_handle is not None and sig_handle["T_dev"] is not None:
-                torch.cuda.current_stream(dev).wait_event(sig_handle["event"])
-                want["sigT"] = sig_handle["T_dev"]
-            # Evaluation of the new weights is not part of the block: it is queued behind the collection (with the
-            # next iteration's prefetch) and read back after the block has been assembled and hashed.
-            def after_copies():
-                if launch_witnesses is not None:
-                    launch_witnesses()
+        # ---- 9. the block's tail: ONE device->host collection (weights, counters, contributor list, gathered
+        # commitment||signature rows), off-chain work queued behind it, then block assembly on the host.
+        do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
+        agg_box = [None]
+
+        def off_chain_work(chain_done):
+            with self._off_chain(chain_done):
                 if do_eval:
                     self._launch_eval()
-                self._prefetch_next(it + 1)
+                    if self.pipelined:
+                        self._eval_done = torch.cuda.Event()
+                        self._eval_done.record()
+                if not self._timing:
+                    # the next block's local step (+ commitments): the only off-chain work the next chain waits for
+                    self._prefetch_next(it + 1)
+                if cfg.secure_agg and self.commit is not None and self.P:
+                    # Every approved worker generates shares + KZG witnesses for the miners (kyber.go:456-482) and the
+                    # miners add the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287).
+                    # Nothing that enters the block depends on them.
+                    with self._phase("witness"):
+                        W = self.commit.witnesses(Q, pout["appr_local"], affine=cfg.affine_wire, count=n_la,
+                                                  max_rows=min(self.P, nk))
+                    with self._phase("miner_aggregate"):
+                        aggW = self.commit.aggregate(W, pout["csel"], affine=cfg.affine_wire, count=n_lc)
+                        aggC = self.commit.aggregate(chunkC, pout["sel"], affine=cfg.affine_wire, count=n_lc)
+                        agg_box[0] = (aggC, aggW)
+                if self.pipelined:
+                    ev = torch.cuda.Event()
+                    ev.record()
+                    self._side_done[par] = ev
+                    self._wevent = ev
 
-            host = self._collect(want, before_sync=after_copies)
-            if "cb" in host:
-                cb = host["cb"]
-                cbj = cb.view(np.int32).reshape(cb.shape[0], 24)
-                if gathered:
-                    for p, b in zip(contributors, CommitmentEngine.jac_rows_to_bytes(cbj, list(contributors))):
-                        commits[p] = b
-                else:
-                    mine = [p for p in contributors if p in self.local_index]
-                    for p, b in zip(mine, CommitmentEngine.jac_rows_to_bytes(cbj, [self.local_index[p] for p in mine])):
-                        commits[p] = b
-                    if self.comm is not None:
-                        commits = self.comm.merge_dicts(commits)
-            all_sigs = None
-            if sig_handle is not None and all(len(commits.get(p, b"")) == 64 for p in contributors):
-                msgs = [commits[p] for p in contributors for _ in signers]
-                kpos = {p: i for i, p in enumerate(krum_set)}
-                rows = [kpos[p] * len(signers) + j for p in contributors for j in range(len(signers))]
-                all_sigs = self.signer.finish(self.signer.select(sig_handle, rows, host.get("sigT")), msgs)
-            nv = len(signers)
-            fast = None
-            if (cfg.secure_agg and contributors and all(len(commits.get(p, b"")) == 64 for p in contributors)
-                    and (all_sigs is not None or sig_handle is None)):
-                # the common block: (source, commitment, approvals) per update, handed to the ledger as three arrays
-                fast = (contributors, b"".join(commits[p] for p in contributors),
-                        b"".join(all_sigs) if all_sigs else b"", nv if all_sigs else 0)
-                for p in contributors:
-                    self.stake[p] += STAKE_UNIT
-            for ci, p in enumerate(contributors if fast is None else ()):
-                c = commits.get(p, b"")
-                sigs = all_sigs[ci * nv: (ci + 1) * nv] if all_sigs is not None else []
-                rec = UpdateRecord(source=p, iteration=it, commitment=c, accepted=True, signatures=sigs)
-                if not cfg.secure_agg and p in self.local_index and self.world == 1:
-                    rec.delta = self.U[self.local_index[p], : self.d].double().cpu().numpy()
-                updates.append(rec)
-                self.stake[p] += STAKE_UNIT
+        with self._phase("block"):
+            want = {"w": self.w64, "bad": self._bad, "counts": counts, "cpos": pout["contrib_pos"]}
             if not cfg.secure_agg:
-                for p in krum_set:
-                    if p not in accepted:
-                        self.stake[p] -= STAKE_UNIT                      # honest.go:362-370 (plain path only)
-            rep.bad_shares = int(host["bad"].sum())
-        return self._finish_block(rep, updates, agg_box[0], phases, t0, host, fast)
+                want["accept"] = accept
+            if self.colluder_ids and use_noise and cuda:
+                want["noisers"] = noiser_tab
+            have_pack = self.commit is not None and (cuda or self.comm is not None)
+            if cuda and self.commit is not None:
+                if sig_event is not None:
+                    torch.cuda.current_stream(dev).wait_event(sig_event)
+                want["pack"] = self._gather_pack(self._pack[par], par)
+            host = self._collect(want, before_sync=off_chain_work)
+            cnt = host["counts"]
+            n_contrib = int(cnt[1])
+            rep.n_accepted = int(cnt[0]) if pl.approved_ok else int(host["accept"].sum()) if "accept" in host else int(cnt[0])
+            contributors = [krum_set[int(i)] for i in host["cpos"][:n_contrib]] if n_contrib >= 2 else []
+            badv = host["bad"].astype(np.int64)
+            if badv.shape[0] >= 3 and badv[2]:
+                raise RuntimeError(f"rank {self.rank}: a cross-GPU wait timed out (code {int(badv[2])}) in block {it}")
+            rep.bad_shares = int((badv[:2] - self._bad_prev[:2]).sum())
+            self._bad_prev[: badv.shape[0]] = badv
+            # collusion accounting (main.go:1026-1057, 1138-1144)
+            if self.colluder_ids and use_noise:
+                if noisers_host is None:
+                    tab = host["noisers"]
+                    if self.comm is not None and self.world > 1:
+                        tab = np.concatenate(self.comm.all_gather_np(tab[: self.per] if tab.shape[0] >= self.per
+                                                                     else np.pad(tab, ((0, self.per - tab.shape[0]), (0, 0)),
+                                                                                 constant_values=-1)))
+                    noisers_host = tab if tab.shape[0] >= n else np.pad(tab, ((0, n - tab.shape[0]), (0, 0)), constant_values=-1)
+                vcol = any(v in self.colluder_ids for v in verifiers)
+                rep.unmasked_updates = sum(
+                    1 for p in krum_set if vcol and any(q >= 0 for q in noisers_host[p]) and
+                    all(int(q) in self.colluder_ids for q in noisers_host[p] if q >= 0))
+            rep.n_contributors = len(contributors)
+            rep.contributors = contributors
+            updates, packed = [], None
+            if contributors:
+                if self.commit is not None:
+                    pack_host = host.get("pack")
+                    if pack_host is None:          # CPU engine: commitments and approvals of the contributors, now
+                        pack_host = self._pack_host(contributors, pl.signers if ns or (self.signer and pl.approved_ok) else [],
+                                                    cbytes, salt64, it)
+                    nsig = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
+                    packed = (contributors, pack_host, nsig)
+                else:
+                    for p in contributors:
+                        rec = UpdateRecord(source=p, iteration=it, commitment=b"", accepted=True, signatures=[])
+                        if not cfg.secure_agg and p in self.local_index and self.world == 1:
+                            rec.delta = self.U[self.local_index[p], : self.d].double().cpu().numpy()
+                        updates.append(rec)
+                        self.stake[p] += STAKE_UNIT
+                if not cfg.secure_agg:
+                    acc = host["accept"]
+                    for i, p in enumerate(krum_set):
+                        if not acc[i]:
+                            self.stake[p] -= STAKE_UNIT                  # honest.go:362-370 (plain path only)
+        self.last_aggregate = agg_box[0] if contributors else None
+        return self._finish_block(rep, phases, t0, host=host, updates=updates, packed=packed)
 
     # ------------------------------------------------------------------------------------------
+    def _gather_pack(self, pack: torch.Tensor, par: int) -> torch.Tensor:
+        """[per, stride] commitment||signature rows of my peers -> [world*per, stride] rows of every peer (row = id)."""
+        if self.comm is None or self.world == 1:
+            return pack
+        return self.comm.all_gather_rows_u8(pack)
+
+    def _pack_host(self, contributors, signers, cbytes, salt64, it) -> np.ndarray:
+        """CPU engine: the contributors' pack rows, built at the tail (host approvals, gloo gather across ranks)."""
+        n, st = self.world * self.per, self.pack_stride
+        loc = np.zeros((self.per, st), dtype=np.uint8)
+        mine = [p for p in contributors if p in self.local_index]
+        if mine:
+            cb = cbytes.cpu().numpy() if isinstance(cbytes, torch.Tensor) else cbytes
+            rows = [self.local_index[p] for p in mine]
+            commits = [cb[r].tobytes() for r in rows]
+            for r, c in zip(rows, commits):
+                loc[r, :64] = np.frombuffer(c, dtype=np.uint8)
+            if signers and self.signer is not None:
+                sigs = self.signer.sign_host(salt64, it, mine, signers, commits)
+                k = len(signers)
+                for j, r in enumerate(rows):
+                    loc[r, 64: 64 + 64 * k] = np.frombuffer(b"".join(sigs[j * k: (j + 1) * k]), dtype=np.uint8)
+        if self.comm is None or self.world == 1:
+            out = np.zeros((n, st), dtype=np.uint8)
+            out[: self.per] = loc
+            return out
+        return np.concatenate(self.comm.all_gather_np(loc))
+
     def _available_shares(self, miners, alive_miners):
         spm = self.cfg.shares_per_miner
         avail = [0] * self.S
@@ -582,14 +721,12 @@ class BiscottiEngine:
             return local.index_select(0, ix).contiguous()
         return self.comm.gather_rows(ids, local, self.local_index, self.owner)
 
-    def _krum(self, krum_set, Un, hi, lo, norms):
+    def _krum(self, krum_set, Un, hi, lo, norms, clip, slots_d=None) -> torch.Tensor:
+        """Multi-Krum accept mask (uint8 [nk]) - stays on the device."""
         cfg = self.cfg
         nk = len(krum_set)
-        if nk < 3:
-            return list(krum_set)
-        clip = int(math.floor(cfg.krum_adversary_frac * nk))
         if self.fused:
-            _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1)
+            _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1, rows=slots_d)
         elif getattr(self, "_compact", False):
             _, acc, _ = krum_ops.krum(hi[:nk], self.d, clip, hi[:nk], lo[:nk], norms[:nk], impl=cfg.gram_impl)
         else:
@@ -599,16 +736,14 @@ class BiscottiEngine:
             lok = self._gather_rows(krum_set, lo, ix) if lo is not None else None
             nrm = self._gather_rows(krum_set, norms.unsqueeze(1), ix).squeeze(1) if norms is not None else None
             _, acc, _ = krum_ops.krum(Uk, self.d, clip, hik, lok, nrm, impl=cfg.gram_impl)
-        mask = acc.cpu().tolist()
-        return [p for p, a in zip(krum_set, mask) if a]
+        return acc.to(torch.uint8)
 
-    def _roni(self, krum_set, Un):
+    def _roni(self, krum_set, Un) -> torch.Tensor:
         """RONI (main.go:191-233, honest.go:598-629): reject when validation error rises by > threshold."""
         Uk = self._gather_rows(krum_set, Un)
         base_err = self.model.eval_errors(self.w32.unsqueeze(0), None, self.data.X_test, self.data.y_test)[0]
         errs = self.model.eval_errors(Uk, self.w32, self.data.X_test, self.data.y_test)
-        ok = ((errs - base_err) <= self.cfg.roni_threshold).cpu().tolist()
-        return [p for p, a in zip(krum_set, ok) if a]
+        return ((errs - base_err) <= self.cfg.roni_threshold).to(torch.uint8)
 
     def evaluate(self):
         w = self.w32.unsqueeze(0)
@@ -619,7 +754,7 @@ class BiscottiEngine:
     def verify_last_aggregate(self, samples=((0, 0), (0, 13), (1, 20))):
         """What a miner can check about the last block's aggregation (kyber.go:244-287 + verifySecret): the sum of
         the contributors' witnesses opens the sum of their chunk commitments to the sum of their shares.  Waits
-        for the witness stream.  Single-rank engines only (each rank aggregates its own contributors).  Returns
+        for the off-chain stream.  Single-rank engines only (each rank aggregates its own contributors).  Returns
         None when there is nothing to check."""
         if self.last_aggregate is None or self.world != 1 or getattr(self, "_last_ysum", None) is None:
             return None
@@ -674,12 +809,12 @@ class BiscottiEngine:
 
     def _collect(self, tensors: dict, before_sync=None) -> dict:
         """Device tensors -> numpy, through persistent pinned buffers, with a single synchronisation.  `before_sync`
-        runs after the copies are queued and before the host waits for them: work it launches sits behind the
-        copies in the stream and is not waited for."""
+        (called with the event that marks the copies queued) runs before the host waits for them: the work it
+        launches sits behind the copies and is not waited for."""
         if self.device.type != "cuda":
             out = {k: v.detach().cpu().numpy().copy() for k, v in tensors.items()}
             if before_sync is not None:
-                before_sync()
+                before_sync(None)
             return out
         if not hasattr(self, "_pinned"):
             self._pinned = {}
@@ -692,20 +827,18 @@ class BiscottiEngine:
                 self._pinned[key] = buf
             buf.copy_(v, non_blocking=True)
             out[k] = buf
-        # bytes this block reads back from the device (weights, commitments, share-check counters, signature
-        # halves; + 8 for the two error rates, which _launch_eval reads the same way)
+        # bytes this block reads back from the device (weights, counters, contributor list, commitment||signature
+        # rows; + 8 for the two error rates, which _launch_eval reads the same way)
         self.last_d2h_bytes = sum(b.numel() * b.element_size() for b in out.values()) + 8
-        if before_sync is None:
-            torch.cuda.current_stream(self.device).synchronize()
-        else:
-            if not hasattr(self, "_collect_ev"):
-                self._collect_ev = torch.cuda.Event()
-            self._collect_ev.record()
-            before_sync()
-            self._collect_ev.synchronize()
+        if not hasattr(self, "_collect_ev"):
+            self._collect_ev = torch.cuda.Event()
+        self._collect_ev.record()
+        if before_sync is not None:
+            before_sync(self._collect_ev)
+        self._collect_ev.synchronize()
         return {k: b.numpy() for k, b in out.items()}
 
-    def _finish_block(self, rep: BlockReport, updates, agg_commit, phases, t0, host=None, fast=None) -> BlockReport:
+    def _finish_block(self, rep: BlockReport, phases, t0, host=None, updates=(), packed=None) -> BlockReport:
         cfg = self.cfg
         it = self.iteration
         with self._phase("block"):
@@ -714,18 +847,18 @@ class BiscottiEngine:
                 if cfg.eval_every and (it % cfg.eval_every == 0):
                     want["te"], want["ar"] = self.evaluate()
                 host = self._collect(want)
-            nonempty = bool(updates) or fast is not None
+            nonempty = bool(updates) or packed is not None
             ts = (1 + it if nonempty else 0) if cfg.deterministic_time else -1
-            if fast is not None:
-                rep.block_hash = self.chain.add_commit_block(it, host["w"], fast[0], fast[1], fast[2], fast[3], self.stake,
-                                                             timestamp=ts)
+            if packed is not None:
+                rep.block_hash = self.chain.append_packed(it, host["w"], packed[0], packed[1], packed[2], self.stake,
+                                                          STAKE_UNIT, timestamp=ts)
             else:
-                rep.block_hash = self.chain.add_block(it, host["w"], updates, self.stake, timestamp=ts)
+                rep.block_hash = self.chain.add_block(it, host["w"], list(updates), self.stake, timestamp=ts)
             rep.empty = not nonempty
             # The next block's noiser lottery hangs on this hash: start every peer's VRF now rather than after the
             # bookkeeping below and the caller's loop overhead (the kernel is ~0.4 ms of pure latency).
             if self.device.type == "cuda" and cfg.mode != "fedsys" and cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
-                self._vrf_early = (rep.block_hash, self.vrf.launch(rep.block_hash))
+                self._vrf_early = (rep.block_hash, self.vrf.launch_dev(rep.block_hash))
         pend, self._eval_pending = self._eval_pending, None
         if pend is not None and isinstance(pend[0], str):      # ("counts", pinned int32[2], event, n_test, n_attack)
             pend[2].synchronize()
@@ -741,7 +874,6 @@ class BiscottiEngine:
             self.log.attack_rate(it, rep.attack_rate)
         rep.phase_ms = dict(phases)
         rep.phase_ms["total_host"] = (time.perf_counter() - t0) * 1e3
-        self.last_aggregate = agg_commit
         self.reports.append(rep)
         self.iteration += 1
         return rep
@@ -758,22 +890,53 @@ class BiscottiEngine:
     def print_chain(self) -> str:
         return self.chain.dump()
 
+    def mint_empty_block(self) -> BlockReport:
+        """Block deadline (startBlockDeadlineTimer, main.go:2326-2355): a peer that saw no block for this height mints
+        the deterministic empty one (block.go:32-38) and moves on.  Weights and stake are unchanged."""
+        rep = BlockReport(self.iteration, b"", True, [], [], 0, 0, 0, 0)
+        self._phases = {}
+        self._pre = None
+        return self._finish_block(rep, self._phases, time.perf_counter())
+
+    def close(self):
+        """Release what the engine holds outside the Python heap (peer-memory mappings of the fused path)."""
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        if self.comm is not None and hasattr(self.comm, "close"):
+            self.comm.close()
+
     # rejoin: a restarted peer adopts the longest chain it is offered (main.go:1000-1013)
     def adopt_chain(self, serialized: bytes) -> bool:
         other = Blockchain.deserialize(serialized)
         if len(other) > len(self.chain) and other.verify():
-            self._pre = None
-            self.chain = other
-            self.iteration = other.latest_iteration + 1
-            w = torch.from_numpy(other.weights()).to(self.device)
-            self.w64.copy_(w)
-            self.w32.copy_(w.float())
-            info = other.block_info(-1)
-            if info["stake"]:
-                for k, v in info["stake"].items():
-                    self.stake[k] = v
+            self._install_chain(other)
             return True
         return False
+
+    def _install_chain(self, other: Blockchain):
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self._pre = None
+        self._vrf_early = None
+        self.chain = other
+        self.iteration = other.latest_iteration + 1
+        w = torch.from_numpy(other.weights()).to(self.device)
+        self.w64.copy_(w)
+        self.w32.copy_(w.float())
+        info = other.block_info(-1)
+        if info["stake"]:
+            for k, v in info["stake"].items():
+                self.stake[k] = v
+
+    def offer_block(self, serialized_block: bytes) -> int:
+        """RegisterBlock from a peer that was on the other side of a partition (main.go:1238-1330): a block for the
+        height this engine already holds replaces it iff the held one is empty and the offered one is not and both
+        extend the same parent (evaluateBlockQuality, honest.go:631-653).  Returns accept_block's code: 2 = replaced
+        (weights, stake and iteration follow the new tip), 1 = appended, 0 = ignored, < 0 = rejected."""
+        rc = self.chain.accept_block(serialized_block)
+        if rc in (1, 2):
+            self._install_chain(self.chain)
+        return rc
 
 
 def cp_order() -> int:

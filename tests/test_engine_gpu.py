@@ -41,20 +41,3 @@ def test_fedsys_mode_on_gpu():
     e = BiscottiEngine(cfg, device="cuda:0")
     reps = e.run()
     assert reps[-1].test_error < reps[0].test_error
-
-
-def test_witness_overlap_and_prefetch_are_scheduling_only():
-    """The witness MSM on its own lower-priority stream and the prefetched local step change when kernels run, not
-    what they compute: same ledger as the strictly in-line schedule, and the aggregated witnesses (read after the
-    witness stream's event) open the aggregated commitments to the aggregated shares."""
-    a = BiscottiEngine(_cfg(max_iterations=5, overlap_witness=True), device="cuda:0")
-    b = BiscottiEngine(_cfg(max_iterations=5, overlap_witness=False, prefetch=False), device="cuda:0")
-    checked = 0
-    for _ in range(6):
-        ra, rb = a.step(), b.step()
-        assert ra.block_hash == rb.block_hash
-        if not ra.empty:
-            assert a.verify_last_aggregate() is True and b.verify_last_aggregate() is True
-            checked += 1
-    torch.cuda.synchronize()
-    assert checked >= 4 and a.chain == b.chain and a._wstream is not None and b._wstream is None

@@ -40,11 +40,23 @@ def test_fused_krum_and_secagg_world1_match_unfused_kernels():
     bad = comm.secagg_fused(list(range(10)), [1] * 21, 4, epoch=1)
     torch.cuda.synchronize()
     assert int(bad.sum()) == 0
+    w_before = comm.w64.clone()
+    gate = torch.tensor([1], dtype=torch.int32, device=DEV)
+    comm.secagg_fused(list(range(10)), [1] * 21, 4, epoch=2, gate=gate, gate_min=2)      # too few contributors: no step
+    assert torch.equal(comm.w64, w_before)
+    comm.w64.zero_()
+    comm.w32.zero_()
+    comm.secagg_fused([0, 1, 2, 3, 4, 5, 6, 14, 15, 16], [1] * 7 + [0] * 7 + [1] * 7, 4, epoch=3)   # a miner is down
+    w_gap = comm.w64.clone()
+    comm.w64.zero_()
+    comm.w32.zero_()
+    comm.secagg_fused(list(range(10)), [1] * 21, 4, epoch=4)
     w_ref = torch.zeros(d, dtype=torch.float64, device=DEV)
     Ysum = secagg.share_sum(U, sel, d, cfg.total_shares)
     secagg.reconstruct_step(Ysum, torch.arange(10, dtype=torch.int32, device=DEV), None, d, w_ref, None)
-    assert torch.equal(comm.w64, w_ref)
+    assert torch.equal(comm.w64, w_ref) and torch.equal(w_gap, w_ref)
     assert torch.equal(comm.w32, w_ref.float())
+    comm.close()
 
 
 def test_engine_with_fused_comm_world1_is_deterministic():
