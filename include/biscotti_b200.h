@@ -95,9 +95,25 @@ int bsc_quantize(const float* U, long long* Q, int P, int d, int ldu, int dpad, 
 
 int bsc_shares_eval(const long long* Q, long long* Y, int P, int nchunk, int dpad, int S, void* stream);
 
+// nsel_dev (may be null): device-resident contributor count, see share_sum_kernel
+int bsc_share_sum_dc(const float* U, const int* sel, int nsel, const int* nsel_dev, int d, int ldu, int c0, int nc, int S, double scale, long long* Ysum, void* stream);
+
 int bsc_share_sum(const float* U, const int* sel, int nsel, int d, int ldu, int c0, int nc, int S, double scale, long long* Ysum, void* stream);
 
+// gate (may be null): the step is applied only if *gate >= gate_min (device-resident contributor count)
+int bsc_reconstruct_step_gated(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d, double scale, double* w64, float* w32, double* dsum, int* bad, const int* gate, int gate_min, void* stream);
+
 int bsc_reconstruct_step(const long long* Ysum, const int* xs, const unsigned char* avail, int S, int c0, int nc, int d, double scale, double* w64, float* w32, double* dsum, int* bad, void* stream);
+
+// Matrix form of bsc_reconstruct_step_gated; `rm` points at a host RecoverMat (see secagg_math.cuh).
+int bsc_reconstruct_mat(const long long* Ysum, const void* rm, const unsigned char* avail, int S, int c0, int nc, int d, double scale, double* w64, float* w32, double* dsum, int* bad, const int* gate, int gate_min, void* stream);
+
+// host restatement: coefficients of nc chunks through the matrix; returns the number of inexact coefficients
+int bsc_recover_mat_host(const long long* Ysum, const void* rm, int S, int nc, long long* coef_out);
+
+int bsc_recover_mat_sizeof();
+
+int bsc_plain_sum_step_dc(const float* U, const int* sel, int nsel, const int* nsel_dev, int d, int ldu, double* w64, float* w32, double* dsum, const int* gate, int gate_min, void* stream);
 
 int bsc_plain_sum_step(const float* U, const int* sel, int nsel, int d, int ldu, double* w64, float* w32, double* dsum, void* stream);
 
@@ -120,6 +136,9 @@ void bsc_msm_table_build_host(const void* bases_affine, long long nb, int w, int
 
 int bsc_msm_table(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p, void* stream);
 
+// pcount (may be null): device-resident number of live rows (<= P); rows >= *pcount are skipped
+int bsc_msm_table_dc(const long long* Q, int ldq, const int* sel, int P, const int* pcount, const int* sidx, const int* bidx, const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p, void* stream);
+
 void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, const int* sidx, const int* bidx, const int* og, int G, int T, const void* table_affine, int w, int nw, void* out_jac, long long ostride_p);
 
 int bsc_g1_comb_mul(const void* scalars_u256, int N, const void* table_affine, int w, int nw, void* out_jac, void* stream);
@@ -132,7 +151,12 @@ int bsc_g1_affine_to_bytes(const void* in_affine, unsigned char* out, long long 
 
 int bsc_g1_bytes_to_affine(const unsigned char* in, void* out_affine, long long N, void* stream);
 
+int bsc_g1_sum_rows_dc(const void* pts_affine, const int* sel, int nsel, const int* nsel_dev, long long G, void* out_jac, void* stream);
+
 int bsc_g1_sum_rows(const void* pts_affine, const int* sel, int nsel, long long G, void* out_jac, void* stream);
+
+// nsel_dev (may be null): device-resident row count (<= nsel)
+int bsc_g1_sum_rows_jac_dc(const void* pts_jac, const int* sel, int nsel, const int* nsel_dev, long long G, void* out_jac, void* stream);
 
 int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream);
 
@@ -300,6 +324,17 @@ void bsc_block_set_stake(void* bp, const int* ids, const int* vals, int n);
 // Consumes the builder.  Returns the new chain length.
 int bsc_chain_append(void* cp, void* bp, long long timestamp);
 
+// The whole tail of a secure-aggregation block in one call (createBlockSecAgg + AddBlock, honest.go:391-440,
+// block.go:30-44): the contributors' rows are picked out of the per-peer pack (64-byte commitment followed by
+// the verifiers' 64-byte approvals, row = peer id), stake[source] += stake_unit, the block is sealed against
+// the tip, appended and its hash returned.  `stake` (dense, node id = position) is updated in place and
+// recorded in the block.  n == 0 mints the empty block (timestamp rule as in bsc_chain_append).
+int bsc_chain_append_packed(void* cp, long long iteration, const double* w, int d, const int* sources, int n, const uint8_t* pack, long long pack_stride, int nsigs, int* stake, int nstake, int stake_unit, long long timestamp, uint8_t out_hash[32]);
+
+// Deterministic stand-in for a network arrival order: a Fisher-Yates shuffle of 0..n-1 driven by splitmix64
+// from `seed` (unbiased bounded draws by rejection).  Every rank computes the same permutation.
+void bsc_seeded_perm(unsigned long long seed, int n, int* out);
+
 // getBlock(it) = Blocks[it+1] with the consistency check (blockchain.go:77-96): index or -1/-2
 int bsc_chain_block_index(void* cp, long long iteration);
 
@@ -375,7 +410,32 @@ int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* cons
 int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const int* rows, int n, int clip, const void* my_flags, int world, unsigned long long epoch, float* scores, unsigned char* accept, void* stream);
 
 // Fused reduce-scatter + reconstruct + SGD step + all-gather for this rank's chunk range [c0, c0+nc).
-int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank, int S, int d, int c0, int nc, const int* xs_host, const unsigned char* avail_host, double scale, unsigned int* done_counter, int* bad, unsigned long long epoch, void* stream);
+//   rm          : host RecoverMat (secagg_math.cuh) for the abscissae in use; use_mat = 0 keeps only rm->xs and
+//                 recovers by divided differences
+//   local_ready : local uint64 word (zeroed once), done_counter: local uint32 (zeroed once)
+//   gate        : device int, may be null: the step is applied only when *gate >= gate_min
+// When the kernel retires, every rank's new weight slice has landed in this rank's w64 / w32.
+int bsc_secagg_fused(void* const* ypart, void* const* w64, void* const* w32, void* const* flags, int world, int rank, int S, int d, int c0, int nc, const void* rm, int use_mat, const unsigned char* avail_host, double scale, unsigned int* done_counter, unsigned long long* local_ready, int* bad, const int* gate, int gate_min, unsigned long long epoch, void* stream);
+
+// first cross-GPU wait that timed out since the last call (0 = none); clears the record
+int bsc_symm_error();
+
+/* --------------------------------------------------------------------------------------------
+ * kernels_chain.cu - 
+ * -------------------------------------------------------------------------------------------- */
+int bsc_vrf_noisers(const int* xyz, const unsigned char* msg, int mlen, const int* stake, int n, const unsigned char* is_worker, const int* peer_ids, int P, int want, int* out, unsigned char* vrf_out, void* stream);
+
+int bsc_block_plan(const unsigned char* accept, const int* share_rank, const int* local_row, int nk, int approved_ok, int trigger, int* counts, int* contrib_pos, int* sel, int* appr_local, int* csel, void* stream);
+
+// secrets_be: [n_peers][32] big-endian signing keys (device); salt64: 64 host bytes; k_out: [nc*ns] U256 (device)
+int bsc_schnorr_nonces_dev(const unsigned char* secrets_be, const unsigned char* salt64, long long it, const int* cand_ids, int nc, const int* signers, int ns, void* k_out, void* stream);
+
+int bsc_schnorr_finish_dev(const unsigned char* T, const void* k, const unsigned char* secrets_be, const unsigned char* cbytes, const int* cand_rows, int nc, const int* signers, int ns, unsigned char* pack, int pack_stride, void* stream);
+
+int bsc_pack_commitments(const unsigned char* cbytes, int P, unsigned char* pack, int pack_stride, void* stream);
+
+// host mirror of hash_schnorr_64 + finish, for tests: sig = c || r
+void bsc_schnorr_finish64_host(const unsigned char* T64, const unsigned char* k_words, const unsigned char* x_be, const unsigned char* msg64, unsigned char* sig);
 
 /* --------------------------------------------------------------------------------------------
  * kernels_cnn.cu - 

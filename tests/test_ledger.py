@@ -88,3 +88,30 @@ def test_add_commit_block_is_byte_identical_to_update_records():
     ha = a.add_block(1, w, [UpdateRecord(source=s, iteration=1, commitment=c) for s, c in zip(srcs, commits)], stake, timestamp=2)
     hb = b.add_commit_block(1, w, srcs, b"".join(commits), b"", 0, stake, timestamp=2)
     assert ha == hb and a.serialize() == b.serialize()
+
+
+def test_append_packed_is_byte_identical_and_credits_stake():
+    """The engine's one-call block tail (rows of commitment || approvals picked by peer id, stake +5 per contributor)
+    must produce exactly the block the UpdateRecord path produces."""
+    import numpy as np
+
+    from biscotti_b200.ledger.chain import Blockchain, UpdateRecord
+
+    rs = np.random.RandomState(4)
+    w = rs.randn(12)
+    n, k = 10, 3
+    pack = rs.randint(0, 256, (n, 64 * (1 + k))).astype(np.uint8)
+    srcs = [1, 4, 7, 8]
+    stake_a = [10 + i for i in range(n)]
+    stake_b = list(stake_a)
+    a, b = Blockchain(12), Blockchain(12)
+    for s in srcs:
+        stake_a[s] += 5
+    ups = [UpdateRecord(source=s, iteration=0, commitment=pack[s, :64].tobytes(),
+                        signatures=[pack[s, 64 + 64 * j: 128 + 64 * j].tobytes() for j in range(k)]) for s in srcs]
+    ha = a.add_block(0, w, ups, stake_a, timestamp=1)
+    hb = b.append_packed(0, w, srcs, pack, k, stake_b, 5, timestamp=1)
+    assert ha == hb and a == b and stake_a == stake_b and a.dump() == b.dump()
+    ha = a.add_block(1, w, [], stake_a, timestamp=0)
+    hb = b.append_packed(1, w, [], pack, k, stake_b, 5, timestamp=0)          # the empty block
+    assert ha == hb and a.serialize() == b.serialize()
