@@ -188,10 +188,12 @@ class ApprovalSigner:
 
     def launch(self, salt64: bytes, it: int, cand_ids: torch.Tensor, cand_rows: torch.Tensor, nc: int,
                signers: torch.Tensor, ns: int, cbytes: torch.Tensor, pack: torch.Tensor, after: "torch.cuda.Event | None",
-               serial: bool = False):
+               serial: bool = False, commit_ready: "torch.cuda.Event | None" = None):
         """Queue the approvals of `nc` candidates by `ns` signers.  cand_ids / cand_rows / signers: int32 device tensors
-        (global ids; rows of `cbytes` and `pack`, -1 = not this rank's peer).  `after`: event that marks cbytes (and the
-        index tensors) complete.  Returns the event that marks `pack` complete (None when run on the current stream)."""
+        (global ids; rows of `cbytes` and `pack`, -1 = not this rank's peer).  `after`: event that marks the index tensors
+        uploaded; `commit_ready`: event that marks `cbytes` complete.  The nonces and T = v*G need only the chain position,
+        so they start at once; only the last kernel (challenge + response) waits for the commitments.  Returns the event
+        that marks `pack` complete (None when run on the current stream)."""
         L, dev = self.L, self.device
         N = nc * ns
         if N == 0:
@@ -209,6 +211,8 @@ class ApprovalSigner:
             assert L.bsc_g1_comb_mul(p(self._k.data_ptr()), N, p(tab.data_ptr()), W_BITS, N_WIN, p(self._jac.data_ptr()), st) == 0
             assert L.bsc_g1_normalize(p(self._jac.data_ptr()), p(self._aff.data_ptr()), N, st) == 0
             assert L.bsc_g1_affine_to_bytes(p(self._aff.data_ptr()), p(self._T.data_ptr()), N, st) == 0
+            if not serial and commit_ready is not None:
+                self.stream.wait_event(commit_ready)
             assert L.bsc_schnorr_finish_dev(p(self._T.data_ptr()), p(self._k.data_ptr()), p(self.secrets_dev.data_ptr()),
                                             p(cbytes.data_ptr()), p(cand_rows.data_ptr()), nc, p(signers.data_ptr()), ns,
                                             p(pack.data_ptr()), pack.stride(0), st) == 0

@@ -372,9 +372,247 @@ HDN Fe<M> fe_pow(const Fe<M>& a, const U256& e) {
   }
   return r;
 }
-// Fermat inversion a^(m-2) (the reference does the same, gfp.go:30-48).  inv(0) = 0.
+// ---- modular inversion -----------------------------------------------------------------------------------
+// The reference inverts by Fermat, a^(m-2) (gfp.go:30-48): ~380 dependent 256-bit multiplications, i.e. ~0.3 ms
+// for ONE inversion on one GPU thread - and an inversion sits on every Jacobian -> wire-bytes conversion the
+// block's tail waits for (commitments, the approvals' T = v*G) and on every VRF output (on the block's chain).
+// Here: the Bernstein-Yang "divsteps" gcd in 30-bit batches.  A batch of 30 division steps looks only at the low
+// 32 bits of (f, g) and yields a 2x2 transition matrix of 32-bit entries, which is then applied to the full
+// 9 x 30-bit signed limbs of (f, g) and, modulo m, to the cofactors (d, e): ~20 batches of cheap 32-bit work
+// (IMAD.WIDE + shifts, the GPU's native width) instead of 380 Montgomery products.  Variable time: nothing secret is
+// inverted with it (projective Z coordinates of public points).  Same structure as the widely used signed-30
+// modular-inverse formulation of that algorithm; written from the paper's recurrences, tested against Python's
+// pow(a, -1, m) and against the Fermat form (tests/test_crypto_host.py).
+HD bool u256_geq(const U256& a, const U256& b) {
+#pragma unroll
+  for (int i = 7; i >= 0; i--) {
+    if (a.v[i] != b.v[i]) return a.v[i] > b.v[i];
+  }
+  return true;
+}
+struct S30 {
+  int32_t v[9];   // value = sum v[i] * 2^(30 i), limbs signed, |v[i]| < 2^30 after carrying (top limb free)
+};
+HD S30 s30_from_u256(const U256& a) {
+  S30 r;
+  const uint32_t M30 = 0x3FFFFFFFu;
+  uint64_t acc = 0;
+  int bits = 0, k = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    acc |= (uint64_t)a.v[i] << bits;
+    bits += 32;
+    while (bits >= 30 && k < 9) {
+      r.v[k++] = (int32_t)(acc & M30);
+      acc >>= 30;
+      bits -= 30;
+    }
+  }
+  r.v[8] = (int32_t)acc;   // 256 - 240 = 16 bits
+  return r;
+}
+HD U256 s30_to_u256(const S30& a) {   // a must be non-negative and < 2^256
+  U256 r;
+  uint64_t acc = 0;
+  int bits = 0, k = 0;
+#pragma unroll
+  for (int i = 0; i < 9; i++) {
+    acc |= (uint64_t)(uint32_t)a.v[i] << bits;
+    bits += 30;
+    if (bits >= 32 && k < 8) {
+      r.v[k++] = (uint32_t)acc;
+      acc >>= 32;
+      bits -= 32;
+    }
+  }
+  if (k < 8) r.v[k] = (uint32_t)acc;
+  return r;
+}
+struct T2x2 {
+  int32_t u, v, q, r;
+};
+HD int ctz32_nz(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)x) - 1;
+#else
+  return __builtin_ctz(x);
+#endif
+}
+// 30 division steps on the low words.  eta = -delta.  On return 2^30 * [f', g'] = t * [f, g].
+HD int32_t divsteps_30_var(int32_t eta, uint32_t f0, uint32_t g0, T2x2& t) {
+  uint32_t u = 1, v = 0, q = 0, r = 1;
+  uint32_t f = f0, g = g0;
+  int i = 30;
+  for (;;) {
+    const int zeros = ctz32_nz(g | (0xFFFFFFFFu << i));
+    g >>= zeros;
+    u <<= zeros;
+    v <<= zeros;
+    eta -= zeros;
+    i -= zeros;
+    if (i == 0) break;
+    // f and g are odd here
+    if (eta < 0) {
+      uint32_t tmp;
+      eta = -eta;
+      tmp = f; f = g; g = 0u - tmp;
+      tmp = u; u = q; q = 0u - tmp;
+      tmp = v; v = r; r = 0u - tmp;
+    }
+    // cancel as many low bits of g as eta and the remaining step count allow (up to 8 at once):
+    // w = -g / f mod 2^limit, with 1/f mod 2^8 from three Newton steps (f odd)
+    int limit = (eta + 1) > i ? i : (eta + 1);
+    if (limit > 8) limit = 8;
+    const uint32_t m = (0xFFFFFFFFu >> (32 - limit));
+    uint32_t finv = f;                    // f * f = 1 mod 8
+    finv *= 2u - f * finv;                // 6 bits
+    finv *= 2u - f * finv;                // 12 bits
+    const uint32_t w = ((0u - g) * finv) & m;
+    g += f * w;
+    q += u * w;
+    r += v * w;
+  }
+  t.u = (int32_t)u;
+  t.v = (int32_t)v;
+  t.q = (int32_t)q;
+  t.r = (int32_t)r;
+  return eta;
+}
+// [d, e] <- t * [d, e] / 2^30 mod m, both kept in (-2m, m)
+HD void s30_update_de(S30& d, S30& e, const T2x2& t, const S30& mod, uint32_t mod_inv30) {
+  const int32_t M30 = 0x3FFFFFFF;
+  const int32_t u = t.u, v = t.v, q = t.q, r = t.r;
+  const int32_t sd = d.v[8] >> 31, se = e.v[8] >> 31;
+  int32_t md = (u & sd) + (v & se);
+  int32_t me = (q & sd) + (r & se);
+  int32_t di = d.v[0], ei = e.v[0];
+  int64_t cd = (int64_t)u * di + (int64_t)v * ei;
+  int64_t ce = (int64_t)q * di + (int64_t)r * ei;
+  // choose the multiples of m that make the low 30 bits vanish
+  md -= (int32_t)((mod_inv30 * (uint32_t)cd + (uint32_t)md) & (uint32_t)M30);
+  me -= (int32_t)((mod_inv30 * (uint32_t)ce + (uint32_t)me) & (uint32_t)M30);
+  cd += (int64_t)mod.v[0] * md;
+  ce += (int64_t)mod.v[0] * me;
+  cd >>= 30;
+  ce >>= 30;
+#pragma unroll
+  for (int i = 1; i < 9; i++) {
+    di = d.v[i];
+    ei = e.v[i];
+    cd += (int64_t)u * di + (int64_t)v * ei;
+    ce += (int64_t)q * di + (int64_t)r * ei;
+    cd += (int64_t)mod.v[i] * md;
+    ce += (int64_t)mod.v[i] * me;
+    d.v[i - 1] = (int32_t)cd & M30;
+    cd >>= 30;
+    e.v[i - 1] = (int32_t)ce & M30;
+    ce >>= 30;
+  }
+  d.v[8] = (int32_t)cd;
+  e.v[8] = (int32_t)ce;
+}
+// [f, g] <- t * [f, g] / 2^30 (exact)
+HD void s30_update_fg(S30& f, S30& g, const T2x2& t) {
+  const int32_t M30 = 0x3FFFFFFF;
+  const int32_t u = t.u, v = t.v, q = t.q, r = t.r;
+  int32_t fi = f.v[0], gi = g.v[0];
+  int64_t cf = (int64_t)u * fi + (int64_t)v * gi;
+  int64_t cg = (int64_t)q * fi + (int64_t)r * gi;
+  cf >>= 30;
+  cg >>= 30;
+#pragma unroll
+  for (int i = 1; i < 9; i++) {
+    fi = f.v[i];
+    gi = g.v[i];
+    cf += (int64_t)u * fi + (int64_t)v * gi;
+    cg += (int64_t)q * fi + (int64_t)r * gi;
+    f.v[i - 1] = (int32_t)cf & M30;
+    cf >>= 30;
+    g.v[i - 1] = (int32_t)cg & M30;
+    cg >>= 30;
+  }
+  f.v[8] = (int32_t)cf;
+  g.v[8] = (int32_t)cg;
+}
+// a^-1 mod m for odd m < 2^256 and 0 <= a < m with gcd(a, m) = 1 (plain integers); returns 0 for a = 0.
+HDN inline U256 u256_modinv_odd(const U256& a, const U256& m) {
+  U256 zero;
+#pragma unroll
+  for (int i = 0; i < 8; i++) zero.v[i] = 0;
+  if (u256_is_zero(a)) return zero;
+  const S30 mod = s30_from_u256(m);
+  // m^-1 mod 2^30 by Newton iteration
+  uint32_t minv = m.v[0];
+  minv *= 2u - m.v[0] * minv;
+  minv *= 2u - m.v[0] * minv;
+  minv *= 2u - m.v[0] * minv;
+  minv *= 2u - m.v[0] * minv;
+  minv &= 0x3FFFFFFFu;
+  S30 d, e, f = mod, g = s30_from_u256(a);
+#pragma unroll
+  for (int i = 0; i < 9; i++) d.v[i] = e.v[i] = 0;
+  e.v[0] = 1;
+  int32_t eta = -1;
+  for (int it = 0; it < 40; it++) {     // 25 batches always suffice for 256-bit inputs; 40 is a guard
+    T2x2 t;
+    eta = divsteps_30_var(eta, (uint32_t)f.v[0], (uint32_t)g.v[0], t);
+    s30_update_de(d, e, t, mod, minv);
+    s30_update_fg(f, g, t);
+    int32_t nz = 0;
+#pragma unroll
+    for (int i = 0; i < 9; i++) nz |= g.v[i];
+    if (nz == 0) break;
+  }
+  // now f = +-1 and d = +-a^-1 with d in (-2m, m): fold the sign of f in and bring d into [0, m)
+  const int32_t fneg = f.v[8] >> 31;
+  int64_t c = 0;
+  const int32_t M30 = 0x3FFFFFFF;
+  // d <- (d < 0 ? d + m : d)
+  int32_t add = d.v[8] >> 31;
+#pragma unroll
+  for (int i = 0; i < 9; i++) {
+    c += (int64_t)d.v[i] + (mod.v[i] & add);
+    d.v[i] = (i < 8) ? ((int32_t)c & M30) : (int32_t)c;
+    if (i < 8) c >>= 30;
+  }
+  // d <- (f < 0 ? -d : d)
+  c = 0;
+#pragma unroll
+  for (int i = 0; i < 9; i++) {
+    c += (int64_t)((d.v[i] ^ fneg) - fneg);
+    d.v[i] = (i < 8) ? ((int32_t)c & M30) : (int32_t)c;
+    if (i < 8) c >>= 30;
+  }
+  // twice: d may still be in (-2m, 0)
+  for (int rep = 0; rep < 2; rep++) {
+    add = d.v[8] >> 31;
+    c = 0;
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+      c += (int64_t)d.v[i] + (mod.v[i] & add);
+      d.v[i] = (i < 8) ? ((int32_t)c & M30) : (int32_t)c;
+      if (i < 8) c >>= 30;
+    }
+  }
+  // d in [0, 2m) possible after the first fold: subtract m once if needed
+  U256 out = s30_to_u256(d);
+  if (u256_geq(out, m)) u256_sub(out, out, m);
+  return out;
+}
+
+// Inverse of a Montgomery-form element.  inv(0) = 0.  (x = aR; modinv gives a^-1 R^-1; two Montgomery products
+// with R^2 bring it back to a^-1 R.)
 template <class M>
 HDN Fe<M> fe_inv(const Fe<M>& a) {
+  Fe<M> t, r2;
+  t.x = u256_modinv_odd(a.x, mod_of<M>());
+#pragma unroll
+  for (int i = 0; i < 8; i++) r2.x.v[i] = M::r2(i);
+  return fe_mul(fe_mul(t, r2), r2);
+}
+// The reference's Fermat form a^(m-2) (gfp.go:30-48); kept as the oracle fe_inv is tested against.
+template <class M>
+HDN Fe<M> fe_inv_fermat(const Fe<M>& a) {
   U256 e = mod_of<M>();
   U256 two;
   for (int i = 0; i < 8; i++) two.v[i] = 0;

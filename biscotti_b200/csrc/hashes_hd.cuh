@@ -34,6 +34,7 @@ HD int b2_sigma(int r, int i) {
 // t = byte counter after this block, last = final-block flag
 HDN inline void b2_compress_hd(uint64_t h[8], const uint64_t m[16], uint64_t t, bool last) {
   uint64_t v[16];
+#pragma unroll
   for (int i = 0; i < 8; i++) {
     v[i] = h[i];
     v[i + 8] = b2_iv(i);
@@ -49,7 +50,8 @@ HDN inline void b2_compress_hd(uint64_t h[8], const uint64_t m[16], uint64_t t, 
   v[d] = hd_rotr64(v[d] ^ v[a], 16);   \
   v[c] = v[c] + v[d];                  \
   v[b] = hd_rotr64(v[b] ^ v[c], 63);
-  for (int r = 0; r < 12; r++) {
+#pragma unroll
+  for (int r = 0; r < 12; r++) {   // unrolled: the message schedule becomes compile-time register picks
     BSC_B2G(0, 4, 8, 12, m[b2_sigma(r, 0)], m[b2_sigma(r, 1)]);
     BSC_B2G(1, 5, 9, 13, m[b2_sigma(r, 2)], m[b2_sigma(r, 3)]);
     BSC_B2G(2, 6, 10, 14, m[b2_sigma(r, 4)], m[b2_sigma(r, 5)]);
@@ -60,6 +62,7 @@ HDN inline void b2_compress_hd(uint64_t h[8], const uint64_t m[16], uint64_t t, 
     BSC_B2G(3, 4, 9, 14, m[b2_sigma(r, 14)], m[b2_sigma(r, 15)]);
   }
 #undef BSC_B2G
+#pragma unroll
   for (int i = 0; i < 8; i++) h[i] ^= v[i] ^ v[i + 8];
 }
 

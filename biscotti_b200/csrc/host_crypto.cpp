@@ -419,6 +419,26 @@ void bsc_fr_powers(const uint8_t tau_be[32], int d, uint32_t* out_words) {
   }
 }
 
+// Test hook for the two inversion routines of field.cuh: a^-1 mod m by binary extended Euclid (fe_inv) and by the
+// reference's Fermat exponentiation (fe_inv_fermat).  which: 0 = BN256 base field, 1 = BN256 group order,
+// 2 = 2^255-19.  Values are 32-byte big-endian plain integers (reduced mod m on input).
+void bsc_fe_inv_both(int which, const uint8_t a_be[32], uint8_t out_fast[32], uint8_t out_fermat[32]) {
+  const U256 a = u256_from_be(a_be);
+  if (which == 0) {
+    const Fp x = fe_from_u256<BnP>(a);
+    u256_to_be(out_fast, fe_to_u256(fe_inv(x)));
+    u256_to_be(out_fermat, fe_to_u256(fe_inv_fermat(x)));
+  } else if (which == 1) {
+    const Fr x = fe_from_u256<BnN>(a);
+    u256_to_be(out_fast, fe_to_u256(fe_inv(x)));
+    u256_to_be(out_fermat, fe_to_u256(fe_inv_fermat(x)));
+  } else {
+    const Fe<EdP> x = fe_from_u256<EdP>(a);
+    u256_to_be(out_fast, fe_to_u256(fe_inv(x)));
+    u256_to_be(out_fermat, fe_to_u256(fe_inv_fermat(x)));
+  }
+}
+
 // ---- Schnorr (kyber.go:873-933) ------------------------------------------------------------------
 // pub = x*G
 void bsc_schnorr_pubkey(const uint8_t x_be[32], uint8_t pub[64]) {

@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(128) vrf_noisers_kernel(const int32_t* __restr
     Y.v[k] = xyz[30 * (size_t)p + 10 + k];
     Z.v[k] = xyz[30 * (size_t)p + 20 + k];
   }
-  const F25 zi = f25_invert(Z);
+  const F25 zi = f25_invert_fast(Z);
   uint8_t gam[32], xb[32];
   f25_tobytes(gam, f25_mul(Y, zi));
   f25_tobytes(xb, f25_mul(X, zi));

@@ -62,13 +62,28 @@ class BlockReport:
     n_krum: int
     n_accepted: int
     n_contributors: int
-    test_error: float | None = None
-    attack_rate: float | None = None
     loss: float | None = None
     bad_shares: int = 0
     phase_ms: dict = field(default_factory=dict)
     unmasked_updates: int = 0
     contributors: list = field(default_factory=list)
+    _test_error: float | None = None
+    _attack_rate: float | None = None
+    _resolve: object = None        # callable that waits for this block's error-rate kernels and fills the two fields
+
+    # The error rates of the new weights are computed off the block's chain and read back asynchronously; touching
+    # them waits for exactly that read-back (the engine itself resolves a report two blocks later at the latest).
+    @property
+    def test_error(self):
+        if self._resolve is not None:
+            self._resolve()
+        return self._test_error
+
+    @property
+    def attack_rate(self):
+        if self._resolve is not None:
+            self._resolve()
+        return self._attack_rate
 
 
 @dataclass
@@ -87,6 +102,10 @@ class _Plan:
     xs: list = field(default_factory=list)
     enough_shares: bool = False
     clip: int = 0
+
+
+_NP = {torch.int32: np.int32, torch.uint8: np.uint8, torch.int64: np.int64, torch.float32: np.float32}
+_SZ = {torch.int32: 4, torch.uint8: 1, torch.int64: 8, torch.float32: 4}
 
 
 class BiscottiEngine:
@@ -116,7 +135,7 @@ class BiscottiEngine:
         self.iteration = 0
         self._pre = None          # prefetched local step + commitments of the next iteration, see _prefetch_next
         self._next_inputs, self._fed_inputs = None, False
-        self._eval_pending = None
+        self._eval_waiting: list = []           # reports whose error rates are still being read back
         self._vrf_early = None
         self._main = self._side = None          # chain stream / off-chain stream of a pipelined GPU engine
         self._wstream = None                    # alias of _side, kept for callers that look for the witness stream
@@ -203,24 +222,26 @@ class BiscottiEngine:
 
     def _idx_pack(self, *specs):
         """Several small host arrays -> device tensors with ONE staging copy.  specs: (values, dtype) pairs; each
-        tensor starts on a 16-byte boundary of the shared buffer."""
+        tensor starts on a 16-byte boundary of the shared buffer.  Packing is plain numpy into the pinned buffer."""
         if self.device.type != "cuda":
-            return [torch.as_tensor(np.asarray(v), dtype=dt).clone() if len(v) else torch.empty(0, dtype=dt) for v, dt in specs]
+            return [torch.as_tensor(np.array(v, dtype=_NP[dt])) for v, dt in specs]
         if not hasattr(self, "_pack_stage"):
             self._pack_stage = [torch.empty(1 << 16, dtype=torch.uint8).pin_memory() for _ in range(8)]
+            self._pack_np = [b.numpy() for b in self._pack_stage]
             self._pack_i = 0
-        buf = self._pack_stage[self._pack_i % len(self._pack_stage)]
+        k = self._pack_i % len(self._pack_stage)
         self._pack_i += 1
+        buf, bnp = self._pack_stage[k], self._pack_np[k]
         offs, off = [], 0
         for v, dt in specs:
-            nb = len(v) * torch.empty(0, dtype=dt).element_size()
+            nb = len(v) * _SZ[dt]
             offs.append((off, nb))
-            off = (off + nb + 15) // 16 * 16
+            off = (off + nb + 15) & ~15
         if off > buf.numel():
-            return [self._idx(v, dt) for v, dt in specs]
+            return [self._idx(list(v), dt) for v, dt in specs]
         for (o, nb), (v, dt) in zip(offs, specs):
             if nb:
-                buf[o: o + nb].view(dt).copy_(torch.as_tensor(np.asarray(v), dtype=dt))
+                bnp[o: o + nb].view(_NP[dt])[:] = v
         dev_buf = buf[: max(off, 16)].to(self.device, non_blocking=True)
         return [dev_buf[o: o + nb].view(dt) for (o, nb), (v, dt) in zip(offs, specs)]
 
@@ -508,10 +529,8 @@ class BiscottiEngine:
                 plan_ready.record()
             pack = self._pack[par]
             if ns:
-                if self.pipelined and pre["c_ready"] is not None:
-                    self.signer.stream.wait_event(pre["c_ready"])
                 sig_event = self.signer.launch(salt64, it, krum_ids_d, local_row_d, nk, signers_d, ns, cbytes, pack,
-                                               after=plan_ready, serial=not self.pipelined)
+                                               after=plan_ready, serial=not self.pipelined, commit_ready=pre["c_ready"])
             else:
                 with self._off_chain(pre["c_ready"]):
                     check(lib().bsc_pack_commitments(ptr(cbytes), self.P, ptr(pack), pack.stride(0), raw_stream(dev)),
@@ -588,10 +607,12 @@ class BiscottiEngine:
         do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
         agg_box = [None]
 
-        def off_chain_work(chain_done):
+        def off_chain_work(chain_done, rep):
+            # queued after the block is appended and the next block's VRF is under way: none of it is on the path from this
+            # block's hash to the next one (the next chain waits only for the local step at its head)
             with self._off_chain(chain_done):
                 if do_eval:
-                    self._launch_eval()
+                    self._launch_eval(rep)
                     if self.pipelined:
                         self._eval_done = torch.cuda.Event()
                         self._eval_done.record()
@@ -626,7 +647,7 @@ class BiscottiEngine:
                 if sig_event is not None:
                     torch.cuda.current_stream(dev).wait_event(sig_event)
                 want["pack"] = self._gather_pack(self._pack[par], par)
-            host = self._collect(want, before_sync=off_chain_work)
+            host = self._collect(want)
             cnt = host["counts"]
             n_contrib = int(cnt[1])
             rep.n_accepted = int(cnt[0]) if pl.approved_ok else int(host["accept"].sum()) if "accept" in host else int(cnt[0])
@@ -672,8 +693,9 @@ class BiscottiEngine:
                     for i, p in enumerate(krum_set):
                         if not acc[i]:
                             self.stake[p] -= STAKE_UNIT                  # honest.go:362-370 (plain path only)
+        rep = self._finish_block(rep, phases, t0, host=host, updates=updates, packed=packed, then=off_chain_work)
         self.last_aggregate = agg_box[0] if contributors else None
-        return self._finish_block(rep, phases, t0, host=host, updates=updates, packed=packed)
+        return rep
 
     # ------------------------------------------------------------------------------------------
     def _gather_pack(self, pack: torch.Tensor, par: int) -> torch.Tensor:
@@ -773,51 +795,60 @@ class BiscottiEngine:
             ok = ok and self.commit.verify_share_trapdoor(Cb[64 * c: 64 * c + 64], Wb[off: off + 64], c, s, int(Y[c, s]))
         return ok
 
-    def _launch_eval(self):
-        """Queue the error-rate kernels and their read-back; _finish_block picks the numbers up."""
+    def _launch_eval(self, rep: BlockReport):
+        """Queue the error-rate kernels of the new weights and their read-back; `rep` gets a resolver that waits for
+        that read-back when somebody looks at the numbers (honest.go:141-162 logs them per block)."""
+        it = rep.iteration
+        log = self.log
+
+        def publish(te, ar):
+            rep._test_error, rep._attack_rate, rep._resolve = float(te), float(ar), None
+            log.train_error(it, rep._test_error)
+            log.attack_rate(it, rep._attack_rate)
+
         if self.device.type == "cuda" and self.model.kind in ("softmax", "logistic"):
-            # both error counts into one persistent int32[2], one read-back; the rates are formed on the host
-            if not hasattr(self, "_ev_cnt"):
-                self._ev_cnt = torch.zeros(2, dtype=torch.int32, device=self.device)
-                self._ev_cnt_pinned = torch.zeros(2, dtype=torch.int32).pin_memory()
-                self._eval_ev = torch.cuda.Event()
-            self._ev_cnt.zero_()
+            # both error counts into one int32[2] and one read-back; four slots, resolved at the latest two blocks on
+            if not hasattr(self, "_ev_slots"):
+                self._ev_slots = [(torch.zeros(2, dtype=torch.int32, device=self.device),
+                                   torch.zeros(2, dtype=torch.int32).pin_memory(), torch.cuda.Event()) for _ in range(4)]
+            cnt_d, cnt_h, ev = self._ev_slots[it & 3]
+            cnt_d.zero_()
             w = self.w32.unsqueeze(0)
             d = self.data
             if self.model.kind == "softmax":
                 C = self.cfg.spec.n_classes
-                ml.eval_softmax_errors(w, None, d.X_test, d.y_test, C, wrong_out=self._ev_cnt[0:1])
-                ml.eval_softmax_errors(w, None, d.X_attack, d.y_attack, C, wrong_out=self._ev_cnt[1:2])
+                ml.eval_softmax_errors(w, None, d.X_test, d.y_test, C, wrong_out=cnt_d[0:1])
+                ml.eval_softmax_errors(w, None, d.X_attack, d.y_attack, C, wrong_out=cnt_d[1:2])
             else:
-                ml.eval_logistic_errors(w, None, d.X_test, d.y_test, wrong_out=self._ev_cnt[0:1])
-                ml.eval_logistic_errors(w, None, d.X_attack, d.y_attack, wrong_out=self._ev_cnt[1:2])
-            self._ev_cnt_pinned.copy_(self._ev_cnt, non_blocking=True)
-            self._eval_ev.record()
-            self._eval_pending = ("counts", self._ev_cnt_pinned, self._eval_ev, d.X_test.shape[0], d.X_attack.shape[0])
+                ml.eval_logistic_errors(w, None, d.X_test, d.y_test, wrong_out=cnt_d[0:1])
+                ml.eval_logistic_errors(w, None, d.X_attack, d.y_attack, wrong_out=cnt_d[1:2])
+            cnt_h.copy_(cnt_d, non_blocking=True)
+            ev.record()
+            nt, na = d.X_test.shape[0], d.X_attack.shape[0]
+
+            def resolve():
+                ev.synchronize()
+                c = cnt_h.numpy()
+                publish(c[0] / max(1, nt), c[1] / max(1, na))
+
+            rep._resolve = resolve
+            self._eval_waiting.append(rep)
             return
         te, ar = self.evaluate()
         if self.device.type != "cuda":
-            self._eval_pending = (te.detach().cpu(), ar.detach().cpu(), None)
+            publish(te[0], ar[0])
             return
-        if not hasattr(self, "_eval_pinned"):
-            self._eval_pinned = (torch.empty_like(te, device="cpu").pin_memory(), torch.empty_like(ar, device="cpu").pin_memory())
-            self._eval_ev = torch.cuda.Event()
-        self._eval_pinned[0].copy_(te, non_blocking=True)
-        self._eval_pinned[1].copy_(ar, non_blocking=True)
-        self._eval_ev.record()
-        self._eval_pending = (self._eval_pinned[0], self._eval_pinned[1], self._eval_ev)
+        te_h, ar_h = te.to("cpu", non_blocking=False), ar.to("cpu", non_blocking=False)     # CNN models: library path
+        publish(te_h[0], ar_h[0])
 
-    def _collect(self, tensors: dict, before_sync=None) -> dict:
-        """Device tensors -> numpy, through persistent pinned buffers, with a single synchronisation.  `before_sync`
-        (called with the event that marks the copies queued) runs before the host waits for them: the work it
-        launches sits behind the copies and is not waited for."""
+    def _collect(self, tensors: dict) -> dict:
+        """Device tensors -> numpy, through persistent pinned buffers, with a single synchronisation - the one host
+        wait of a block.  self._collect_ev marks the copies (i.e. the end of the block's chain) in the stream."""
         if self.device.type != "cuda":
-            out = {k: v.detach().cpu().numpy().copy() for k, v in tensors.items()}
-            if before_sync is not None:
-                before_sync(None)
-            return out
+            return {k: v.detach().cpu().numpy().copy() for k, v in tensors.items()}
         if not hasattr(self, "_pinned"):
             self._pinned = {}
+            self._collect_ev = torch.cuda.Event()
         out = {}
         for k, v in tensors.items():
             key = (k, tuple(v.shape), v.dtype)
@@ -828,25 +859,19 @@ class BiscottiEngine:
             buf.copy_(v, non_blocking=True)
             out[k] = buf
         # bytes this block reads back from the device (weights, counters, contributor list, commitment||signature
-        # rows; + 8 for the two error rates, which _launch_eval reads the same way)
+        # rows; + 8 for the two error counts, which _launch_eval reads the same way)
         self.last_d2h_bytes = sum(b.numel() * b.element_size() for b in out.values()) + 8
-        if not hasattr(self, "_collect_ev"):
-            self._collect_ev = torch.cuda.Event()
         self._collect_ev.record()
-        if before_sync is not None:
-            before_sync(self._collect_ev)
         self._collect_ev.synchronize()
         return {k: b.numpy() for k, b in out.items()}
 
-    def _finish_block(self, rep: BlockReport, phases, t0, host=None, updates=(), packed=None) -> BlockReport:
+    def _finish_block(self, rep: BlockReport, phases, t0, host=None, updates=(), packed=None, then=None) -> BlockReport:
         cfg = self.cfg
         it = self.iteration
+        cuda = self.device.type == "cuda"
         with self._phase("block"):
             if host is None:
-                want = {"w": self.w64}
-                if cfg.eval_every and (it % cfg.eval_every == 0):
-                    want["te"], want["ar"] = self.evaluate()
-                host = self._collect(want)
+                host = self._collect({"w": self.w64})
             nonempty = bool(updates) or packed is not None
             ts = (1 + it if nonempty else 0) if cfg.deterministic_time else -1
             if packed is not None:
@@ -855,28 +880,31 @@ class BiscottiEngine:
             else:
                 rep.block_hash = self.chain.add_block(it, host["w"], list(updates), self.stake, timestamp=ts)
             rep.empty = not nonempty
-            # The next block's noiser lottery hangs on this hash: start every peer's VRF now rather than after the
-            # bookkeeping below and the caller's loop overhead (the kernel is ~0.4 ms of pure latency).
-            if self.device.type == "cuda" and cfg.mode != "fedsys" and cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
+            # The next block's noiser lottery hangs on this hash: start every peer's VRF now, before anything else
+            # (the kernel is ~0.4 ms of pure latency at the head of the next block's chain).
+            if cuda and cfg.mode != "fedsys" and cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
                 self._vrf_early = (rep.block_hash, self.vrf.launch_dev(rep.block_hash))
-        pend, self._eval_pending = self._eval_pending, None
-        if pend is not None and isinstance(pend[0], str):      # ("counts", pinned int32[2], event, n_test, n_attack)
-            pend[2].synchronize()
-            cnt = pend[1].numpy()
-            host = dict(host, te=[cnt[0] / max(1, pend[3])], ar=[cnt[1] / max(1, pend[4])])
-        elif pend is not None:
-            if pend[2] is not None:
-                pend[2].synchronize()
-            host = dict(host, te=pend[0].numpy(), ar=pend[1].numpy())
-        if "te" in host:
-            rep.test_error, rep.attack_rate = float(host["te"][0]), float(host["ar"][0])
-            self.log.train_error(it, rep.test_error)
-            self.log.attack_rate(it, rep.attack_rate)
+        if then is not None:
+            then(getattr(self, "_collect_ev", None) if cuda else None, rep)
+        elif cfg.eval_every and (it % cfg.eval_every == 0):
+            self._launch_eval(rep)          # empty blocks and FedSys rounds: nothing else is queued behind the block
+        # error rates of older blocks have long been read back: publish them (keeps the "Train Error" lines in order)
+        while len(self._eval_waiting) > (2 if self.pipelined else 0):
+            r = self._eval_waiting.pop(0)
+            if r._resolve is not None:
+                r._resolve()
         rep.phase_ms = dict(phases)
         rep.phase_ms["total_host"] = (time.perf_counter() - t0) * 1e3
         self.reports.append(rep)
         self.iteration += 1
         return rep
+
+    def flush_reports(self):
+        """Wait for every outstanding error-rate read-back (end of a run, before the logs are parsed)."""
+        while self._eval_waiting:
+            r = self._eval_waiting.pop(0)
+            if r._resolve is not None:
+                r._resolve()
 
     # ------------------------------------------------------------------------------------------
     def run(self, iterations: int | None = None):
@@ -885,6 +913,7 @@ class BiscottiEngine:
         total = (self.cfg.max_iterations + 1) if iterations is None else iterations
         for _ in range(total):
             self.step()
+        self.flush_reports()
         return self.reports
 
     def print_chain(self) -> str:

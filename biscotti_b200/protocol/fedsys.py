@@ -58,4 +58,4 @@ def fedsys_step(eng, inputs=None):
     from ..ledger.chain import UpdateRecord
 
     updates = [UpdateRecord(source=p, iteration=it, accepted=True) for p in sorted(set(got))]
-    return eng._finish_block(rep, updates, None, phases, t0)
+    return eng._finish_block(rep, phases, t0, updates=updates)

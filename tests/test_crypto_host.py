@@ -167,3 +167,27 @@ def test_p256_vrf_reading_copy_and_hmac_commitments():
     assert len(c) == 32 and V.verify_commitment("alice", "app", c, b"profile", nonce)
     assert not V.verify_commitment("alice", "app", c, b"profile2", nonce)
     assert not V.verify_commitment("alic", "eapp", c, b"profile", nonce)  # length-prefixed fields do not collide
+
+
+def test_binary_euclid_inverse_matches_fermat_and_python():
+    """field.cuh: fe_inv (binary extended Euclid, what the kernels run) == fe_inv_fermat (the reference's a^(m-2),
+    gfp.go:30-48) == Python's pow(a, -1, m), on the three moduli in use, including edge values."""
+    import ctypes
+    import random
+
+    from biscotti_b200 import _native
+    from biscotti_b200.oracle import bn256 as O
+
+    L = _native.load()
+    mods = {0: O.P, 1: O.ORDER, 2: 2**255 - 19}
+    rnd = random.Random(7)
+    for which, m in mods.items():
+        vals = [1, 2, m - 1, m - 2, 3, 2**128, 2**255 % m, (m + 1) // 2] + [rnd.randrange(1, m) for _ in range(40)]
+        for a in vals:
+            f, g = ctypes.create_string_buffer(32), ctypes.create_string_buffer(32)
+            L.bsc_fe_inv_both(which, int(a).to_bytes(32, "big"), f, g)
+            want = pow(a, -1, m)
+            assert int.from_bytes(f.raw, "big") == want == int.from_bytes(g.raw, "big"), (which, a)
+        f, g = ctypes.create_string_buffer(32), ctypes.create_string_buffer(32)
+        L.bsc_fe_inv_both(which, (0).to_bytes(32, "big"), f, g)
+        assert int.from_bytes(f.raw, "big") == 0 == int.from_bytes(g.raw, "big")
