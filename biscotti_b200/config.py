@@ -96,6 +96,10 @@ class BiscottiConfig:
                                       # chain (witness MSM, miners' aggregation, error rates, next local step +
                                       # commitments) on a second stream, the approvals on a third.  False = one stream,
                                       # strictly in program order (what an instrumented run uses)
+    lookahead: bool = True            # pipelined GPU engines: plan block t+1 and queue the front of its chain (VRF ->
+                                      # noisers -> noise -> Krum -> plan -> share sums; scratch writes only) from inside
+                                      # step t, right after block t is hashed, so the device never waits for the host to
+                                      # come back around the loop
     gram_impl: str = "auto"           # auto | tcgen05 | simt
     comm_impl: str = "fused"          # fused (in-kernel P2P) | nccl (baseline)
     extra: dict = field(default_factory=dict)

@@ -104,6 +104,52 @@ class _Plan:
     clip: int = 0
 
 
+@dataclass
+class _Ctx:
+    """One block in flight: its plan, its device-side handles and how far it has been queued."""
+    it: int
+    par: int
+    pl: _Plan
+    nk: int
+    phases: dict
+    alive: list
+    stake: list
+    timing: bool
+    pipelined: bool
+    rep: BlockReport | None = None
+    empty: bool = False
+    pre: dict | None = None
+    front_queued: bool = False
+    pout: dict | None = None
+    use_noise: bool = False
+    vrf_handle: object = None
+    compact: bool = False
+    plan_ready: object = None
+    sig_event: object = None
+    salt64: bytes = b""
+    ns: int = 0
+    t0: float = 0.0
+    stake_m: object = None
+    is_worker: object = None
+    stake_d: object = None
+    isw_d: object = None
+    dst_row: object = None
+    local_row_d: object = None
+    share_rank_d: object = None
+    krum_ids_d: object = None
+    signers_d: object = None
+    xs_t: object = None
+    av_t: object = None
+    slots_d: object = None
+    hash_d: object = None
+    noiser_tab: object = None
+    noisers_host: object = None
+    accept: object = None
+    n_lc: object = None
+    n_la: object = None
+    n_con: object = None
+
+
 _NP = {torch.int32: np.int32, torch.uint8: np.uint8, torch.int64: np.int64, torch.float32: np.float32}
 _SZ = {torch.int32: 4, torch.uint8: 1, torch.int64: 8, torch.float32: 4}
 
@@ -134,6 +180,8 @@ class BiscottiEngine:
         self.alive = [True] * n
         self.iteration = 0
         self._pre = None          # prefetched local step + commitments of the next iteration, see _prefetch_next
+        self._ctx_next = None     # the next block, planned and partly queued by the previous step (see _after_block)
+        self._faults_applied_for = -1
         self._next_inputs, self._fed_inputs = None, False
         self._eval_waiting: list = []           # reports whose error rates are still being read back
         self._vrf_early = None
@@ -176,7 +224,7 @@ class BiscottiEngine:
         # Nonce salt of the approvals: binds the run (seed, data, every flag) - the previous block hash binds the fork.
         # (Scheduling knobs - prefetch, pipeline, kernel choices - do not change what is signed and stay out of it.)
         sched = {"prefetch", "pipeline", "gram_impl", "comm_impl", "msm_window", "affine_wire", "eval_every", "extra",
-                 "max_iterations", "test_size"}
+                 "max_iterations", "test_size", "lookahead"}
         self.run_salt = hashlib.sha256(("bsc-run-salt|" + repr(sorted((k, v) for k, v in cfg.to_dict().items()
                                                                         if k not in sched))).encode()).digest()
         self.nsig_max = cfg.num_verifiers if self.signer is not None else 0
@@ -257,7 +305,7 @@ class BiscottiEngine:
                                appr_local=torch.zeros(P, **i32), csel=torch.zeros(P, **i32)) for _ in range(2)]
         self._cbytes = [torch.zeros(P, 64, dtype=torch.uint8, device=dev) for _ in range(2)]
         self._pack = [torch.zeros(self.per, self.pack_stride, dtype=torch.uint8, device=dev) for _ in range(2)]
-        self._ysum = torch.zeros(self.cfg.nchunk, self.S, dtype=torch.int64, device=dev)
+        self._ysum = [torch.zeros(self.cfg.nchunk, self.S, dtype=torch.int64, device=dev) for _ in range(2)]
         self._bad = self.comm.bad if self.fused else torch.zeros(4, dtype=torch.int32, device=dev)
         self._noiser_tab = torch.full((P, max(1, self.cfg.num_noisers)), -1, **i32)
         self._plan_keep = [None, None]
@@ -335,14 +383,14 @@ class BiscottiEngine:
         return pl
 
     # ------------------------------------------------------------------------------------------
-    def _local_and_commit(self, inputs, it: int, timed: bool):
-        """Local SGD step of every local peer from the current global weights, then quantisation, the polynomial
-        commitments of the update and their 64-byte wire form (phases 2 and 3 of an iteration).  Returns a dict with
-        Q, chunkC, cbytes (device [P, 64]) and, on a pipelined engine, the events `u_ready` / `c_ready`."""
+    def _local_step(self, inputs, it: int, timed: bool) -> dict:
+        """Local SGD step of every local peer from the current global weights (phase 2 of an iteration) into self.U.
+        Returns the block's `pre` record; on a pipelined engine `u_ready` marks U complete."""
         cfg, dev = self.cfg, self.device
         slot = it % NOISE_TABLE_ITERS
         phase = self._phase if timed else (lambda name: contextlib.nullcontext())
-        out = {"it": it, "Q": None, "chunkC": None, "cbytes": None, "u_ready": None, "c_ready": None}
+        out = {"it": it, "Q": None, "chunkC": None, "cbytes": None, "u_ready": None, "c_ready": None,
+               "src": None if inputs is None else inputs[0].data_ptr()}
         with phase("local_step"):
             if inputs is not None:
                 X, y = inputs
@@ -362,13 +410,20 @@ class BiscottiEngine:
             if dev.type == "cuda" and self.pipelined:
                 out["u_ready"] = torch.cuda.Event()
                 out["u_ready"].record()
+        return out
+
+    def _commit_step(self, out: dict, timed: bool) -> dict:
+        """Quantisation, the polynomial commitments of the update and their 64-byte wire form (phase 3): fills Q, chunkC,
+        cbytes (device [P, 64]) of the block's `pre` record; `c_ready` marks cbytes complete on a pipelined engine."""
+        cfg, dev = self.cfg, self.device
+        phase = self._phase if timed else (lambda name: contextlib.nullcontext())
         if self.commit is not None and self.P:
             with phase("commit"):
                 Q = secagg.quantize(self.U, self.d, cfg.precision)
                 chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
                 full = self.commit.full_commitments(chunkC)                          # affine [P, 16]
                 self._ensure_bufs()
-                cb = self._cbytes[it & 1]
+                cb = self._cbytes[out["it"] & 1]
                 self.commit.to_bytes_into(full, cb)                                  # [P, 64] wire bytes, on the device
                 out.update(Q=Q, chunkC=chunkC, cbytes=cb)
                 if dev.type == "cuda" and self.pipelined:
@@ -376,23 +431,32 @@ class BiscottiEngine:
                     out["c_ready"].record()
         return out
 
+    def _local_and_commit(self, inputs, it: int, timed: bool):
+        return self._commit_step(self._local_step(inputs, it, timed), timed)
+
+    def _next_inputs_ready(self):
+        """Inputs of the next block if its local step may be queued now: None = resident shards, False = not available
+        (minibatches come from the caller and the next one has not been handed over, or prefetching is off)."""
+        cfg = self.cfg
+        if not cfg.prefetch or not cfg.secure_agg or cfg.mode == "fedsys":
+            return False   # the plain path still reads U when the block is assembled
+        nxt = self._next_inputs
+        if nxt is None and (self._fed_inputs or self.external_inputs):
+            return False
+        if nxt is not None and len(nxt) == 3:      # (X, y, event): the H2D copy was issued on another stream
+            torch.cuda.current_stream(self.device).wait_event(nxt[2])
+            nxt = (nxt[0], nxt[1])
+        return nxt
+
     def _prefetch_next(self, it_next: int):
         """Queue the next iteration's local step and commitment MSM behind this iteration's aggregation kernel.
         They read only the new global weights (already updated in stream order) and the resident shards, so the
         device works on them while the host assembles, signs and hashes the current block.  The reference has no
         such overlap (phases are strictly sequential); the values are identical either way."""
-        cfg = self.cfg
-        if not cfg.prefetch or not cfg.secure_agg or cfg.mode == "fedsys":
-            return   # the plain path still reads U when the block is assembled
-        nxt = self._next_inputs
-        if nxt is None and (self._fed_inputs or self.external_inputs):
-            return   # minibatches come from the caller and the next one has not been handed over
-        if nxt is not None and len(nxt) == 3:      # (X, y, event): the H2D copy was issued on another stream
-            torch.cuda.current_stream(self.device).wait_event(nxt[2])
-            nxt = (nxt[0], nxt[1])
-        pre = self._local_and_commit(nxt, it_next, timed=False)
-        pre["src"] = None if nxt is None else nxt[0].data_ptr()
-        self._pre = pre
+        nxt = self._next_inputs_ready()
+        if nxt is False:
+            return
+        self._pre = self._local_and_commit(nxt, it_next, timed=False)
 
     def step(self, inputs=None, next_inputs=None) -> BlockReport:
         """Run one block iteration.  `inputs` = (X [P,B,F], y [P,B]) device tensors when the caller feeds
@@ -444,213 +508,237 @@ class BiscottiEngine:
 
             return fedsys_step(self, inputs)
         t0 = time.perf_counter()
-        it = self.iteration
-        n = cfg.num_nodes
-        dev = self.device
+        src = None if inputs is None else inputs[0].data_ptr()
+        # The previous step may already have planned this block and queued the front of its chain (see _after_block).
+        ctx, self._ctx_next = self._ctx_next, None
+        if ctx is not None and not self._ctx_valid(ctx, src):
+            ctx = None          # somebody changed the world in between (alive set, adopted chain, other inputs): replan
+        if ctx is None:
+            ctx = self._begin_block()
+        ctx.t0 = t0
+        self._phases = ctx.phases
+        if ctx.empty:
+            return self._finish_block(ctx.rep, ctx.phases, t0)        # main.go:1696-1707, 1934-1944, 2099-2117
+        if ctx.pre is None:
+            pre, self._pre = self._pre, None
+            if not (pre is not None and pre["it"] == ctx.it and pre.get("src") == src):
+                with self._off_chain():
+                    pre = self._local_and_commit(inputs, ctx.it, timed=True)
+            ctx.pre = pre
+        if not ctx.front_queued:
+            self._queue_approvals(ctx)
+            self._queue_chain_front(ctx)
+        self._queue_chain_back(ctx)
+        return self._tail(ctx)
+
+    # ---- stage 0: everything about the block that follows from the previous hash ----------------------------------
+    def _begin_block(self) -> "_Ctx":
+        """Fault injection / partitions for this height (prepareForNextIteration, main.go:1059-1187), roles, candidate
+        set, arrival orders (host), the VRF launch on the previous hash, and ONE staging copy of the plan to the device."""
+        cfg, it, n, dev = self.cfg, self.iteration, self.cfg.num_nodes, self.device
         cuda = dev.type == "cuda"
-        par = it & 1
-        phases = {}
-        self._phases = phases
-        # ---- fault injection (main.go:1117-1120): a failing peer sits this block out and rejoins
-        if cfg.fail_prob > 0:
-            for p in range(1, n):
-                self.alive[p] = self._rng.rand() >= cfg.fail_prob
-        # ---- scheduled network partitions (DistSys/blockNode.sh): the peer is cut off for a range of blocks; it
-        # holds no role and contributes nothing meanwhile, and is back (with the chain everybody shares) afterwards
-        if cfg.partitions:
-            cut = {int(p) for p, a, b in cfg.partitions if int(a) <= it <= int(b)}
-            was = getattr(self, "_cut", set())
-            for p in was - cut:
-                self.alive[p] = True
-            for p in cut:
-                self.alive[p] = False
-            self._cut = cut
-        # ---- 1. roles and everything else that follows from the previous hash
+        if self._faults_applied_for != it:
+            self._faults_applied_for = it
+            # a failing peer sits this block out and rejoins (main.go:1117-1120)
+            if cfg.fail_prob > 0:
+                for p in range(1, n):
+                    self.alive[p] = self._rng.rand() >= cfg.fail_prob
+            # scheduled network partitions (DistSys/blockNode.sh): the peer is cut off for a range of blocks; it holds no
+            # role and contributes nothing meanwhile, and is back (with the chain everybody shares) afterwards
+            if cfg.partitions:
+                cut = {int(p) for p, a, b in cfg.partitions if int(a) <= it <= int(b)}
+                was = getattr(self, "_cut", set())
+                for p in was - cut:
+                    self.alive[p] = True
+                for p in cut:
+                    self.alive[p] = False
+                self._cut = cut
         pl = self._host_plan()
-        verifiers, miners, workers, prev_hash = pl.verifiers, pl.miners, pl.workers, pl.prev_hash
         krum_set = pl.krum_set
         nk = len(krum_set)
-        slot = it % NOISE_TABLE_ITERS
-        rep = BlockReport(it, b"", True, verifiers, miners, len(workers), nk, 0, 0)
-        if not verifiers or not miners or not workers or not pl.enough_shares or nk == 0:
-            return self._finish_block(rep, phases, t0)        # main.go:1696-1707, 1934-1944, 2099-2117
+        ctx = _Ctx(it=it, par=it & 1, pl=pl, nk=nk, phases={}, alive=list(self.alive), stake=list(self.stake),
+                   timing=self._timing, pipelined=self.pipelined)
+        ctx.rep = BlockReport(it, b"", True, pl.verifiers, pl.miners, len(pl.workers), nk, 0, 0)
+        if not pl.verifiers or not pl.miners or not pl.workers or not pl.enough_shares or nk == 0:
+            ctx.empty = True
+            return ctx
         self._ensure_bufs()
-        pout = self._plan_out[par]
-
+        ctx.pout = self._plan_out[ctx.par]
+        prev_hash = pl.prev_hash
         # VRF evaluation of every peer on the previous block hash: launched the moment that block was hashed
         # (_finish_block) on its own high-priority stream; the noise phase consumes it on the device.
-        use_noise = cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0
+        ctx.use_noise = cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0
         early, self._vrf_early = self._vrf_early, None
-        if use_noise and early is not None and early[0] == prev_hash:
-            vrf_handle = early[1]
-        else:
-            vrf_handle = (self.vrf.launch_dev(prev_hash) if cuda else self.vrf.launch(prev_hash)) if use_noise else None
-
-        # ---- 2/3. local step + commitments of my peers.  Neither depends on the roles or on the block hash, so
-        # the previous step may already have queued them behind its aggregation kernel (see _prefetch_next).
-        pre, self._pre = self._pre, None
-        if not (pre is not None and pre["it"] == it and pre.get("src") == (None if inputs is None else inputs[0].data_ptr())):
-            with self._off_chain():
-                pre = self._local_and_commit(inputs, it, timed=True)
-        Q, chunkC, cbytes = pre["Q"], pre["chunkC"], pre["cbytes"]
-
+        if ctx.use_noise and early is not None and early[0] == prev_hash:
+            ctx.vrf_handle = early[1]
+        elif ctx.use_noise:
+            ctx.vrf_handle = self.vrf.launch_dev(prev_hash) if cuda else self.vrf.launch(prev_hash)
         # ---- host -> device: the block's plan in one staging copy
-        stake_m = np.asarray([s if a else 0 for s, a in zip(self.stake, self.alive)], dtype=np.int32)
-        is_worker = np.zeros(n, dtype=np.uint8)
-        is_worker[workers] = 1
+        ctx.stake_m = np.asarray([s_ if a_ else 0 for s_, a_ in zip(self.stake, self.alive)], dtype=np.int32)
+        ctx.is_worker = np.zeros(n, dtype=np.uint8)
+        ctx.is_worker[pl.workers] = 1
         kpos = {p: i for i, p in enumerate(krum_set)}
         # Single-rank tcgen05 Krum: noise_mix writes the candidates' bf16 planes and norms compacted and in Krum
         # order (row = position in krum_set), so the Gram kernel needs no gather; the fp32 noised rows are only
         # materialised for the paths that read them (RONI, SIMT Gram, NCCL gathers).
-        self._compact = (cuda and self.comm is None and cfg.verification and cfg.defense != "RONI"
-                         and cfg.gram_impl in ("auto", "tcgen05") and nk >= 3)
-        dst_rows = [kpos.get(p, -1) for p in self.local_ids] if self._compact else []
+        ctx.compact = (cuda and self.comm is None and cfg.verification and cfg.defense != "RONI"
+                       and cfg.gram_impl in ("auto", "tcgen05") and nk >= 3)
+        dst_rows = [kpos.get(p, -1) for p in self.local_ids] if ctx.compact else []
         local_row = [self.local_index.get(p, -1) for p in krum_set]
         slots = [self.comm.slot_of(p) for p in krum_set] if self.fused else []
-        (stake_d, isw_d, dst_row, local_row_d, share_rank_d, krum_ids_d, signers_d, xs_t, av_t, slots_d, hash_d) = \
-            self._idx_pack((stake_m, torch.int32), (is_worker, torch.uint8), (dst_rows, torch.int32),
+        (ctx.stake_d, ctx.isw_d, ctx.dst_row, ctx.local_row_d, ctx.share_rank_d, ctx.krum_ids_d, ctx.signers_d, ctx.xs_t,
+         ctx.av_t, ctx.slots_d, ctx.hash_d) = \
+            self._idx_pack((ctx.stake_m, torch.int32), (ctx.is_worker, torch.uint8), (dst_rows, torch.int32),
                            (local_row, torch.int32), (pl.share_rank, torch.int32), (krum_set, torch.int32),
                            (pl.signers, torch.int32), (pl.xs, torch.int32), (pl.shares_avail, torch.uint8),
                            (slots, torch.int32), (np.frombuffer(bytearray(prev_hash), dtype=np.uint8), torch.uint8))
-        self._plan_keep[par] = (stake_d, local_row_d, krum_ids_d, signers_d)      # read on other streams: keep alive
-        if not self._compact:
-            dst_row = None
+        self._plan_keep[ctx.par] = (ctx.stake_d, ctx.local_row_d, ctx.krum_ids_d, ctx.signers_d)   # read on other streams
+        if not ctx.compact:
+            ctx.dst_row = None
+        if cuda and self.pipelined:
+            ctx.plan_ready = torch.cuda.Event()
+            ctx.plan_ready.record()
+        ctx.salt64 = self.run_salt + (prev_hash + b"\0" * 32)[:32]
+        ctx.ns = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
+        return ctx
 
-        # ---- 6 (early). approvals: T = v*G, c = H(T || commitment), r = v - x*c depend only on (chain position, update,
-        # verifier) and on the commitment, not on the Krum verdict: every candidate of this rank is signed now, on the
-        # approval stream, while the VRF and Krum run; only the rows of the block's updates are ever read.
-        salt64 = self.run_salt + (prev_hash + b"\0" * 32)[:32]
-        sig_event = None
-        ns = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
-        if cuda and self.commit is not None and self.P:
-            plan_ready = None
-            if self.pipelined:
-                plan_ready = torch.cuda.Event()
-                plan_ready.record()
-            pack = self._pack[par]
-            if ns:
-                sig_event = self.signer.launch(salt64, it, krum_ids_d, local_row_d, nk, signers_d, ns, cbytes, pack,
-                                               after=plan_ready, serial=not self.pipelined, commit_ready=pre["c_ready"])
-            else:
-                with self._off_chain(pre["c_ready"]):
-                    check(lib().bsc_pack_commitments(ptr(cbytes), self.P, ptr(pack), pack.stride(0), raw_stream(dev)),
-                          "pack_commitments")
-                    if self.pipelined:
-                        sig_event = torch.cuda.Event()
-                        sig_event.record()
+    def _ctx_valid(self, ctx: "_Ctx", src) -> bool:
+        return (ctx.it == self.iteration and ctx.pl.prev_hash == self.chain.latest_hash() and ctx.alive == self.alive
+                and ctx.stake == self.stake and ctx.timing == self._timing and ctx.pipelined == self.pipelined
+                and (ctx.pre is None or ctx.pre.get("src") == src))
 
-        # ---- 4. noisers + noise (chain)
-        if self.pipelined and pre["u_ready"] is not None:
-            torch.cuda.current_stream(dev).wait_event(pre["u_ready"])
+    # ---- stage 1: approvals (their own stream) -----------------------------------------------------------------------
+    def _queue_approvals(self, ctx: "_Ctx"):
+        """6 (early). T = v*G, c = H(T || commitment), r = v - x*c depend only on (chain position, update, verifier) and
+        on the commitment, not on the Krum verdict: every candidate of this rank is signed now, on the approval stream,
+        while the VRF and Krum run; only the rows of the block's updates are ever read."""
+        dev, pre, pl = self.device, ctx.pre, ctx.pl
+        if dev.type != "cuda" or self.commit is None or not self.P:
+            return
+        pack = self._pack[ctx.par]
+        if ctx.ns:
+            ctx.sig_event = self.signer.launch(ctx.salt64, ctx.it, ctx.krum_ids_d, ctx.local_row_d, ctx.nk, ctx.signers_d,
+                                               ctx.ns, pre["cbytes"], pack, after=ctx.plan_ready, serial=not self.pipelined,
+                                               commit_ready=pre["c_ready"])
+        else:
+            with self._off_chain(pre["c_ready"]):
+                check(lib().bsc_pack_commitments(ptr(pre["cbytes"]), self.P, ptr(pack), pack.stride(0), raw_stream(dev)),
+                      "pack_commitments")
+                if self.pipelined:
+                    ctx.sig_event = torch.cuda.Event()
+                    ctx.sig_event.record()
+
+    # ---- stage 2: the chain up to the share sums (writes scratch only, so it may be queued a block ahead) ---------------
+    def _queue_chain_front(self, ctx: "_Ctx"):
+        cfg, dev, pl, pre, pout = self.cfg, self.device, ctx.pl, ctx.pre, ctx.pout
+        cuda = dev.type == "cuda"
+        it, nk, krum_set = ctx.it, ctx.nk, pl.krum_set
+        slot = it % NOISE_TABLE_ITERS
+        prev = self._phases
+        self._phases = ctx.phases
+        # ---- 4. noisers + noise
+        if self.pipelined:
+            main = torch.cuda.current_stream(dev)
+            if pre["u_ready"] is not None:
+                main.wait_event(pre["u_ready"])
+            if self._side_done[ctx.par] is not None:
+                main.wait_event(self._side_done[ctx.par])   # block it-2's witnesses / aggregation still read this parity's
+                                                            # plan lists: stay at most two blocks ahead of the off-chain stream
         with self._phase("noise"):
             nn_cols = max(1, cfg.num_noisers)
-            noisers_host = None
-            if use_noise and cuda:
-                xyz, vev, hd = vrf_handle
+            if ctx.use_noise and cuda:
+                xyz, vev, _ = ctx.vrf_handle
                 torch.cuda.current_stream(dev).wait_event(vev)
                 noiser_tab = self._noiser_tab
                 if self.P:
-                    chain_ops.vrf_noisers(xyz, hash_d, len(prev_hash), stake_d, isw_d, self.data.peer_ids if not self.external_inputs
-                                          else self._idx(self.local_ids), cfg.num_noisers, noiser_tab)
-            elif use_noise:
-                full_tab = self.vrf.noiser_table(vrf_handle, stake_m.tolist(), is_worker, cfg.num_noisers)   # [n, nn]
-                noisers_host = full_tab
+                    chain_ops.vrf_noisers(xyz, ctx.hash_d, len(pl.prev_hash), ctx.stake_d, ctx.isw_d,
+                                          self.data.peer_ids if not self.external_inputs else self._idx(self.local_ids),
+                                          cfg.num_noisers, noiser_tab)
+            elif ctx.use_noise:
+                full_tab = self.vrf.noiser_table(ctx.vrf_handle, ctx.stake_m.tolist(), ctx.is_worker, cfg.num_noisers)
+                ctx.noisers_host = full_tab
                 lo_id = self.local_ids[0] if self.P else 0
                 noiser_tab = torch.from_numpy(np.ascontiguousarray(full_tab[lo_id: lo_id + max(1, self.P)]))
             else:
                 noiser_tab = torch.full((max(1, self.P), nn_cols), -1, dtype=torch.int32, device=dev)
-            scale = cfg.noise_scale if use_noise else 0.0
+            ctx.noiser_tab = noiser_tab
+            scale = cfg.noise_scale if ctx.use_noise else 0.0
             Un, hi, lo, norms = ml.noise_mix(self.U, noiser_tab, cfg.seed, slot, scale, self.d,
                                              ldh=self.ldh, out_hi=self.comm.hi if self.fused else None,
-                                             out_lo=self.comm.lo if self.fused else None, dst_row=dst_row,
-                                             want_un=not self._compact)
-
+                                             out_lo=self.comm.lo if self.fused else None, dst_row=ctx.dst_row,
+                                             want_un=not ctx.compact)
         # ---- 5. verification -> accept mask on the device
         with self._phase("verify"):
+            self._compact = ctx.compact
             if not cfg.verification or nk < 3:
                 accept = torch.ones(nk, dtype=torch.uint8, device=dev)
             elif cfg.defense == "RONI":
                 accept = self._roni(krum_set, Un)
             else:
-                accept = self._krum(krum_set, Un, hi, lo, norms, pl.clip, slots_d)
+                accept = self._krum(krum_set, Un, hi, lo, norms, pl.clip, ctx.slots_d, epoch=it + 1)
+            ctx.accept = accept
             # approved set, contributors and the compacted local row lists, still on the device
-            chain_ops.block_plan(accept, share_rank_d, local_row_d, pl.approved_ok, pl.trigger, pout)
+            chain_ops.block_plan(accept, ctx.share_rank_d, ctx.local_row_d, pl.approved_ok, pl.trigger, pout)
         counts = pout["counts"]
-        n_lc, n_la, n_con = counts[2:3], counts[3:4], counts[1:2]
+        ctx.n_lc, ctx.n_la, ctx.n_con = counts[2:3], counts[3:4], counts[1:2]
+        # ---- 7. share sums of my contributors
+        with self._phase("secagg"):
+            if cfg.secure_agg:
+                out = self.comm.ypart if self.fused else self._ysum[ctx.par]
+                secagg.share_sum(self.U, pout["sel"], self.d, self.S, cfg.precision, out=out, count=ctx.n_lc)
+        ctx.front_queued = True
+        self._phases = prev
 
-        # ---- 7/8. share sums, reconstruction, SGD step (chain).  Gated on the device: fewer than two contributors
-        # (main.go:2079) leaves the weights untouched and the tail mints the empty block.
+    # ---- stage 3: reconstruction + SGD step (the only chain kernels that change the weights) ---------------------------
+    def _queue_chain_back(self, ctx: "_Ctx"):
+        """8. Gated on the device: fewer than two contributors (main.go:2079) leaves the weights untouched and the tail
+        mints the empty block."""
+        cfg, dev, pl, pout = self.cfg, self.device, ctx.pl, ctx.pout
+        it = ctx.it
         if self.pipelined and self._eval_done is not None:
             torch.cuda.current_stream(dev).wait_event(self._eval_done)     # the previous block's error rates read w
         with self._phase("secagg"):
             if cfg.secure_agg:
                 if self.fused:
-                    secagg.share_sum(self.U, pout["sel"], self.d, self.S, cfg.precision, out=self.comm.ypart, count=n_lc)
-                    self.comm.secagg_fused(pl.xs, pl.shares_avail, cfg.precision, it + 1, gate=n_con, gate_min=2)
+                    self.comm.secagg_fused(pl.xs, pl.shares_avail, cfg.precision, it + 1, gate=ctx.n_con, gate_min=2)
                 else:
-                    Ysum = secagg.share_sum(self.U, pout["sel"], self.d, self.S, cfg.precision, out=self._ysum, count=n_lc)
+                    Ysum = self._ysum[ctx.par]
                     if self.comm is not None:
                         Ysum = self.comm.all_reduce_i64(Ysum)
                     self._last_ysum = Ysum
-                    secagg.reconstruct_step_dev(Ysum, pl.xs, xs_t, av_t, self.d, self.w64, self.w32, cfg.precision,
-                                                bad=self._bad, gate=n_con, gate_min=2)
+                    secagg.reconstruct_step_dev(Ysum, pl.xs, ctx.xs_t, ctx.av_t, self.d, self.w64, self.w32, cfg.precision,
+                                                bad=self._bad, gate=ctx.n_con, gate_min=2)
             else:
                 if self.comm is not None and self.world > 1:
-                    rows = self.comm.gather_rows(krum_set, self.U, self.local_index, self.owner)
-                    secagg.plain_sum_step(rows, pout["contrib_pos"], self.d, self.w64, self.w32, count=n_con, gate=n_con,
-                                          gate_min=2)
+                    rows = self.comm.gather_rows(pl.krum_set, self.U, self.local_index, self.owner)
+                    secagg.plain_sum_step(rows, pout["contrib_pos"], self.d, self.w64, self.w32, count=ctx.n_con,
+                                          gate=ctx.n_con, gate_min=2)
                 else:
-                    secagg.plain_sum_step(self.U, pout["sel"], self.d, self.w64, self.w32, count=n_lc, gate=n_con, gate_min=2)
+                    secagg.plain_sum_step(self.U, pout["sel"], self.d, self.w64, self.w32, count=ctx.n_lc, gate=ctx.n_con,
+                                          gate_min=2)
 
-        # ---- 9. the block's tail: ONE device->host collection (weights, counters, contributor list, gathered
-        # commitment||signature rows), off-chain work queued behind it, then block assembly on the host.
-        do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
-        agg_box = [None]
-
-        def off_chain_work(chain_done, rep):
-            # queued after the block is appended and the next block's VRF is under way: none of it is on the path from this
-            # block's hash to the next one (the next chain waits only for the local step at its head)
-            with self._off_chain(chain_done):
-                if do_eval:
-                    self._launch_eval(rep)
-                    if self.pipelined:
-                        self._eval_done = torch.cuda.Event()
-                        self._eval_done.record()
-                if not self._timing:
-                    # the next block's local step (+ commitments): the only off-chain work the next chain waits for
-                    self._prefetch_next(it + 1)
-                if cfg.secure_agg and self.commit is not None and self.P:
-                    # Every approved worker generates shares + KZG witnesses for the miners (kyber.go:456-482) and the
-                    # miners add the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287).
-                    # Nothing that enters the block depends on them.
-                    with self._phase("witness"):
-                        W = self.commit.witnesses(Q, pout["appr_local"], affine=cfg.affine_wire, count=n_la,
-                                                  max_rows=min(self.P, nk))
-                    with self._phase("miner_aggregate"):
-                        aggW = self.commit.aggregate(W, pout["csel"], affine=cfg.affine_wire, count=n_lc)
-                        aggC = self.commit.aggregate(chunkC, pout["sel"], affine=cfg.affine_wire, count=n_lc)
-                        agg_box[0] = (aggC, aggW)
-                if self.pipelined:
-                    ev = torch.cuda.Event()
-                    ev.record()
-                    self._side_done[par] = ev
-                    self._wevent = ev
-
+    # ---- stage 4: the block's tail --------------------------------------------------------------------------------------
+    def _tail(self, ctx: "_Ctx") -> BlockReport:
+        """9. ONE device->host collection (weights, counters, contributor list, gathered commitment||signature rows), then
+        block assembly, stake update, hashing and append (one native call), then whatever can be queued for later."""
+        cfg, dev, pl, pout, pre, rep = self.cfg, self.device, ctx.pl, ctx.pout, ctx.pre, ctx.rep
+        cuda = dev.type == "cuda"
+        it, par, krum_set, n = ctx.it, ctx.par, pl.krum_set, cfg.num_nodes
+        counts = pout["counts"]
         with self._phase("block"):
             want = {"w": self.w64, "bad": self._bad, "counts": counts, "cpos": pout["contrib_pos"]}
             if not cfg.secure_agg:
-                want["accept"] = accept
-            if self.colluder_ids and use_noise and cuda:
-                want["noisers"] = noiser_tab
-            have_pack = self.commit is not None and (cuda or self.comm is not None)
+                want["accept"] = ctx.accept
+            if self.colluder_ids and ctx.use_noise and cuda:
+                want["noisers"] = ctx.noiser_tab
             if cuda and self.commit is not None:
-                if sig_event is not None:
-                    torch.cuda.current_stream(dev).wait_event(sig_event)
+                if ctx.sig_event is not None:
+                    torch.cuda.current_stream(dev).wait_event(ctx.sig_event)
                 want["pack"] = self._gather_pack(self._pack[par], par)
             host = self._collect(want)
             cnt = host["counts"]
             n_contrib = int(cnt[1])
-            rep.n_accepted = int(cnt[0]) if pl.approved_ok else int(host["accept"].sum()) if "accept" in host else int(cnt[0])
+            rep.n_accepted = int(host["accept"].sum()) if "accept" in host else int(cnt[0])
             contributors = [krum_set[int(i)] for i in host["cpos"][:n_contrib]] if n_contrib >= 2 else []
             badv = host["bad"].astype(np.int64)
             if badv.shape[0] >= 3 and badv[2]:
@@ -658,7 +746,8 @@ class BiscottiEngine:
             rep.bad_shares = int((badv[:2] - self._bad_prev[:2]).sum())
             self._bad_prev[: badv.shape[0]] = badv
             # collusion accounting (main.go:1026-1057, 1138-1144)
-            if self.colluder_ids and use_noise:
+            if self.colluder_ids and ctx.use_noise:
+                noisers_host = ctx.noisers_host
                 if noisers_host is None:
                     tab = host["noisers"]
                     if self.comm is not None and self.world > 1:
@@ -666,7 +755,7 @@ class BiscottiEngine:
                                                                      else np.pad(tab, ((0, self.per - tab.shape[0]), (0, 0)),
                                                                                  constant_values=-1)))
                     noisers_host = tab if tab.shape[0] >= n else np.pad(tab, ((0, n - tab.shape[0]), (0, 0)), constant_values=-1)
-                vcol = any(v in self.colluder_ids for v in verifiers)
+                vcol = any(v in self.colluder_ids for v in pl.verifiers)
                 rep.unmasked_updates = sum(
                     1 for p in krum_set if vcol and any(q >= 0 for q in noisers_host[p]) and
                     all(int(q) in self.colluder_ids for q in noisers_host[p] if q >= 0))
@@ -676,10 +765,9 @@ class BiscottiEngine:
             if contributors:
                 if self.commit is not None:
                     pack_host = host.get("pack")
-                    if pack_host is None:          # CPU engine: commitments and approvals of the contributors, now
-                        pack_host = self._pack_host(contributors, pl.signers if ns or (self.signer and pl.approved_ok) else [],
-                                                    cbytes, salt64, it)
                     nsig = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
+                    if pack_host is None:          # CPU engine: commitments and approvals of the contributors, now
+                        pack_host = self._pack_host(contributors, pl.signers if nsig else [], pre["cbytes"], ctx.salt64, it)
                     packed = (contributors, pack_host, nsig)
                 else:
                     for p in contributors:
@@ -693,9 +781,72 @@ class BiscottiEngine:
                     for i, p in enumerate(krum_set):
                         if not acc[i]:
                             self.stake[p] -= STAKE_UNIT                  # honest.go:362-370 (plain path only)
-        rep = self._finish_block(rep, phases, t0, host=host, updates=updates, packed=packed, then=off_chain_work)
+        agg_box = [None]
+        rep = self._finish_block(rep, ctx.phases, ctx.t0, host=host, updates=updates, packed=packed,
+                                 then=lambda chain_done, r: self._after_block(ctx, chain_done, r, agg_box))
         self.last_aggregate = agg_box[0] if contributors else None
         return rep
+
+    # ---- stage 5: behind the block ---------------------------------------------------------------------------------------
+    def _after_block(self, ctx: "_Ctx", chain_done, rep: BlockReport, agg_box: list):
+        """Called once the block is appended and the next block's VRF is under way.  Queues, in the order the next block
+        needs them: the next local step (head of the next chain), this block's error rates (they read the new weights and
+        must precede the next SGD step), the front of the NEXT block's chain, the next commitments, the next approvals -
+        and last this block's witness MSM and miners' aggregation, which nothing waits for."""
+        cfg, pout, pre = self.cfg, ctx.pout, ctx.pre
+        it = ctx.it
+        do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
+        nxt = self._next_inputs_ready() if not self._timing else False
+        npre, nctx = None, None
+        with self._off_chain(chain_done):
+            if nxt is not False:
+                npre = self._local_step(nxt, it + 1, timed=False)
+            if do_eval:
+                self._launch_eval(rep)
+                if self.pipelined:
+                    self._eval_done = torch.cuda.Event()
+                    self._eval_done.record()
+        if npre is not None and self.pipelined and cfg.lookahead:
+            # plan block it+1 now and queue the front of its chain: VRF -> noisers -> noise -> Krum -> plan -> share sums
+            # write scratch only, so nothing is lost if the world changes before the next step() (the context is then
+            # discarded); the weights are touched only by the kernels queued inside that step
+            nctx = self._begin_block_ahead()
+            if nctx is not None and not nctx.empty:
+                nctx.pre = npre
+                self._queue_chain_front(nctx)
+        with self._off_chain(None if npre is None else npre["u_ready"]):
+            if npre is not None:
+                self._commit_step(npre, timed=False)
+        if nctx is not None and not nctx.empty:
+            self._queue_approvals(nctx)
+            self._ctx_next = nctx
+        elif npre is not None:
+            self._pre = npre
+        with self._off_chain(chain_done):
+            if cfg.secure_agg and self.commit is not None and self.P:
+                # Every approved worker generates shares + KZG witnesses for the miners (kyber.go:456-482) and the
+                # miners add the contributors' witnesses and chunk commitments homomorphically (kyber.go:244-287).
+                # Nothing that enters the block depends on them.
+                with self._phase("witness"):
+                    W = self.commit.witnesses(pre["Q"], pout["appr_local"], affine=cfg.affine_wire, count=ctx.n_la,
+                                              max_rows=min(self.P, ctx.nk))
+                with self._phase("miner_aggregate"):
+                    aggW = self.commit.aggregate(W, pout["csel"], affine=cfg.affine_wire, count=ctx.n_lc)
+                    aggC = self.commit.aggregate(pre["chunkC"], pout["sel"], affine=cfg.affine_wire, count=ctx.n_lc)
+                    agg_box[0] = (aggC, aggW)
+            if self.pipelined:
+                ev = torch.cuda.Event()
+                ev.record()
+                self._side_done[ctx.par] = ev
+                self._wevent = ev
+
+    def _begin_block_ahead(self):
+        """_begin_block for the next height, called from inside the current step (self.iteration not advanced yet)."""
+        self.iteration += 1
+        try:
+            return self._begin_block()
+        finally:
+            self.iteration -= 1
 
     # ------------------------------------------------------------------------------------------
     def _gather_pack(self, pack: torch.Tensor, par: int) -> torch.Tensor:
@@ -743,12 +894,12 @@ class BiscottiEngine:
             return local.index_select(0, ix).contiguous()
         return self.comm.gather_rows(ids, local, self.local_index, self.owner)
 
-    def _krum(self, krum_set, Un, hi, lo, norms, clip, slots_d=None) -> torch.Tensor:
+    def _krum(self, krum_set, Un, hi, lo, norms, clip, slots_d=None, epoch=None) -> torch.Tensor:
         """Multi-Krum accept mask (uint8 [nk]) - stays on the device."""
         cfg = self.cfg
         nk = len(krum_set)
         if self.fused:
-            _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1, rows=slots_d)
+            _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1 if epoch is None else epoch, rows=slots_d)
         elif getattr(self, "_compact", False):
             _, acc, _ = krum_ops.krum(hi[:nk], self.d, clip, hi[:nk], lo[:nk], norms[:nk], impl=cfg.gram_impl)
         else:
@@ -925,6 +1076,7 @@ class BiscottiEngine:
         rep = BlockReport(self.iteration, b"", True, [], [], 0, 0, 0, 0)
         self._phases = {}
         self._pre = None
+        self._ctx_next = None
         return self._finish_block(rep, self._phases, time.perf_counter())
 
     def close(self):
@@ -946,6 +1098,7 @@ class BiscottiEngine:
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
         self._pre = None
+        self._ctx_next = None
         self._vrf_early = None
         self.chain = other
         self.iteration = other.latest_iteration + 1

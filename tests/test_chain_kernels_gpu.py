@@ -146,16 +146,38 @@ def test_pipelined_schedule_gives_the_in_line_chain():
     base = dict(num_nodes=30, dataset="mnist", max_iterations=5, shard_size=100, test_size=500, msm_window=7)
     a = BiscottiEngine(BiscottiConfig(pipeline=True, **base), device=DEV)
     b = BiscottiEngine(BiscottiConfig(pipeline=False, prefetch=False, **base), device=DEV)
+    c = BiscottiEngine(BiscottiConfig(pipeline=True, lookahead=False, **base), device=DEV)
     checked = 0
     for _ in range(6):
-        ra, rb = a.step(), b.step()
-        assert ra.block_hash == rb.block_hash and ra.contributors == rb.contributors
+        ra, rb, rc = a.step(), b.step(), c.step()
+        assert ra.block_hash == rb.block_hash == rc.block_hash and ra.contributors == rb.contributors
         if not ra.empty:
             assert a.verify_last_aggregate() is True and b.verify_last_aggregate() is True
             checked += 1
     torch.cuda.synchronize()
-    assert checked >= 4 and a.chain == b.chain and a._side is not None and b._side is None
+    assert checked >= 4 and a.chain == b.chain == c.chain and a._side is not None and b._side is None
+    assert a._ctx_next is not None and c._ctx_next is None          # a really ran one block ahead
     # every block's approvals verify against the verifiers' public keys
     rep = next(r for r in a.reports if not r.empty)
     info = a.chain.block_info(rep.iteration + 1)
     assert all(u["nsigs"] == len(rep.verifiers) for u in info["updates"])
+
+
+def test_lookahead_is_discarded_when_the_world_changes_between_steps():
+    """The next block's chain front is queued a block ahead; if peers die (or come back) before the next step() the
+    stale plan must be thrown away and the block replanned - same ledger as an engine that never looked ahead."""
+    base = dict(num_nodes=24, dataset="mnist", max_iterations=8, shard_size=60, test_size=200, msm_window=6)
+    a = BiscottiEngine(BiscottiConfig(pipeline=True, **base), device=DEV)
+    b = BiscottiEngine(BiscottiConfig(pipeline=False, prefetch=False, **base), device=DEV)
+    for it in range(7):
+        if it == 3:
+            for e in (a, b):
+                for p in (2, 5, 6, 11, 17):
+                    e.alive[p] = False
+        if it == 5:
+            for e in (a, b):
+                e.alive[5] = e.alive[11] = True
+        ra, rb = a.step(), b.step()
+        assert ra.block_hash == rb.block_hash, it
+        assert torch.equal(a.w64, b.w64)
+    assert a.chain == b.chain and a.stake == b.stake
