@@ -188,3 +188,12 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_chain_append_packed", c_i, c_p, c_ll, c_p, c_i, c_p, c_i, c_p, c_ll, c_i, c_p, c_i, c_i, c_ll, c_p)
     sig("bsc_symm_error", c_i)
     sig("bsc_fe_inv_both", None, c_i, c_cp, c_p, c_p)
+    # native block executor (csrc/exec.cu)
+    sig("bsc_exec", c_i, c_p, c_i, c_p, c_i)
+    sig("bsc_cmd_sizeof", c_i)
+    sig("bsc_event_create", c_p)
+    sig("bsc_event_destroy", None, c_p)
+    sig("bsc_event_record", c_i, c_p, c_p)
+    sig("bsc_event_synchronize", c_i, c_p)
+    sig("bsc_event_query", c_i, c_p)
+    sig("bsc_stream_wait_event", c_i, c_p, c_p)

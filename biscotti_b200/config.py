@@ -100,6 +100,8 @@ class BiscottiConfig:
                                       # noisers -> noise -> Krum -> plan -> share sums; scratch writes only) from inside
                                       # step t, right after block t is hashed, so the device never waits for the host to
                                       # come back around the loop
+    native_schedule: bool = True      # pipelined GPU engines, standard configuration: replay the block's launches as native
+                                      # command lists (protocol/schedule.py) instead of issuing them one by one from Python
     gram_impl: str = "auto"           # auto | tcgen05 | simt
     comm_impl: str = "fused"          # fused (in-kernel P2P) | nccl (baseline)
     extra: dict = field(default_factory=dict)

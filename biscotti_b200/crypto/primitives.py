@@ -200,7 +200,9 @@ class BatchedVRF:
             self._dh_pinned = [torch.empty(64, dtype=torch.uint8).pin_memory() for _ in range(4)]
             self._dhd = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(4)]
             self._dxyz = [torch.empty(n, 30, dtype=torch.int32, device=self.device) for _ in range(2)]
-            self._dev = [torch.cuda.Event() for _ in range(2)]
+            from ..ops.cmdlist import NativeEvent
+
+            self._dev = [NativeEvent() for _ in range(2)]
             self._di = 0
         i = self._di
         self._di += 1

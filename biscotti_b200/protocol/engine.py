@@ -118,6 +118,7 @@ class _Ctx:
     pipelined: bool
     rep: BlockReport | None = None
     empty: bool = False
+    native: bool = False          # queued through protocol/schedule.py's command lists
     pre: dict | None = None
     front_queued: bool = False
     pout: dict | None = None
@@ -181,6 +182,7 @@ class BiscottiEngine:
         self.iteration = 0
         self._pre = None          # prefetched local step + commitments of the next iteration, see _prefetch_next
         self._ctx_next = None     # the next block, planned and partly queued by the previous step (see _after_block)
+        self._ns, self._ns_ok = None, None      # native command-list schedule (protocol/schedule.py), created on first use
         self._faults_applied_for = -1
         self._next_inputs, self._fed_inputs = None, False
         self._eval_waiting: list = []           # reports whose error rates are still being read back
@@ -224,7 +226,7 @@ class BiscottiEngine:
         # Nonce salt of the approvals: binds the run (seed, data, every flag) - the previous block hash binds the fork.
         # (Scheduling knobs - prefetch, pipeline, kernel choices - do not change what is signed and stay out of it.)
         sched = {"prefetch", "pipeline", "gram_impl", "comm_impl", "msm_window", "affine_wire", "eval_every", "extra",
-                 "max_iterations", "test_size", "lookahead"}
+                 "max_iterations", "test_size", "lookahead", "native_schedule"}
         self.run_salt = hashlib.sha256(("bsc-run-salt|" + repr(sorted((k, v) for k, v in cfg.to_dict().items()
                                                                         if k not in sched))).encode()).digest()
         self.nsig_max = cfg.num_verifiers if self.signer is not None else 0
@@ -310,6 +312,47 @@ class BiscottiEngine:
         self._noiser_tab = torch.full((P, max(1, self.cfg.num_noisers)), -1, **i32)
         self._plan_keep = [None, None]
         self._bufs_ready = True
+
+    def _native(self):
+        """The native command-list schedule, when this engine's configuration is the standard one (else None: every
+        launch is then issued from Python, see protocol/schedule.py for what 'standard' means)."""
+        if not self.pipelined or self._main is None:
+            return None
+        if self._ns_ok is None:
+            from .schedule import NativeSchedule
+
+            self._ns_ok = NativeSchedule.supported(self)
+            if self._ns_ok:
+                torch.cuda.synchronize(self.device)
+                self._ns = NativeSchedule(self)
+        return self._ns
+
+    def _ensure_eval_slots(self):
+        if not hasattr(self, "_ev_slots"):
+            self._ev_slots = [(torch.zeros(2, dtype=torch.int32, device=self.device),
+                               torch.zeros(2, dtype=torch.int32).pin_memory(), torch.cuda.Event()) for _ in range(4)]
+
+    def _attach_eval_resolver(self, rep: BlockReport, cnt_h: torch.Tensor, event):
+        """rep's error rates = the two counts that land in `cnt_h` once `event` has passed."""
+        it, log = rep.iteration, self.log
+        nt, na = self.data.X_test.shape[0], self.data.X_attack.shape[0]
+
+        def resolve():
+            event.synchronize()
+            c = cnt_h.numpy()
+            rep._test_error, rep._attack_rate, rep._resolve = float(c[0] / max(1, nt)), float(c[1] / max(1, na)), None
+            log.train_error(it, rep._test_error)
+            log.attack_rate(it, rep._attack_rate)
+
+        rep._resolve = resolve
+        self._eval_waiting.append(rep)
+
+    def _order_side_after_main(self):
+        ev = torch.cuda.Event()
+        ev.record()
+        self._side.wait_event(ev)
+        if self.signer is not None:
+            self.signer.stream.wait_event(ev)
 
     # ------------------------------------------------------------------------------------------
     def select_roles(self):
@@ -434,9 +477,10 @@ class BiscottiEngine:
     def _local_and_commit(self, inputs, it: int, timed: bool):
         return self._commit_step(self._local_step(inputs, it, timed), timed)
 
-    def _next_inputs_ready(self):
+    def _next_inputs_ready(self, stream=None):
         """Inputs of the next block if its local step may be queued now: None = resident shards, False = not available
-        (minibatches come from the caller and the next one has not been handed over, or prefetching is off)."""
+        (minibatches come from the caller and the next one has not been handed over, or prefetching is off).  `stream`:
+        the stream that will read them (default: the current one)."""
         cfg = self.cfg
         if not cfg.prefetch or not cfg.secure_agg or cfg.mode == "fedsys":
             return False   # the plain path still reads U when the block is assembled
@@ -444,7 +488,7 @@ class BiscottiEngine:
         if nxt is None and (self._fed_inputs or self.external_inputs):
             return False
         if nxt is not None and len(nxt) == 3:      # (X, y, event): the H2D copy was issued on another stream
-            torch.cuda.current_stream(self.device).wait_event(nxt[2])
+            (stream or torch.cuda.current_stream(self.device)).wait_event(nxt[2])
             nxt = (nxt[0], nxt[1])
         return nxt
 
@@ -484,7 +528,10 @@ class BiscottiEngine:
         if prev_w is not None:
             # the previous block's off-chain work had this whole iteration to finish; waiting for it here keeps every
             # iteration's device timeline (events on the caller's stream) accountable for one block of that work
-            cur.wait_event(prev_w)
+            if hasattr(prev_w, "handle"):
+                prev_w.wait(cur)
+            else:
+                cur.wait_event(prev_w)
         return rep
 
     @contextlib.contextmanager
@@ -519,6 +566,18 @@ class BiscottiEngine:
         self._phases = ctx.phases
         if ctx.empty:
             return self._finish_block(ctx.rep, ctx.phases, t0)        # main.go:1696-1707, 1934-1944, 2099-2117
+        if ctx.native:
+            ns = self._ns
+            if not ctx.front_queued:
+                # first block, a replanned block, or no lookahead: queue the whole block now
+                self._order_side_after_main()
+                ns.queue_local_and_eval(ctx.it, None, False, inputs=inputs)
+                ns.queue_front(ctx)
+                ns.queue_commit_and_sign(ctx)
+            ns.queue_back(ctx)
+            if not self.fused:
+                self._last_ysum = self._ysum[ctx.par]
+            return self._tail(ctx, ns.collect())
         if ctx.pre is None:
             pre, self._pre = self._pre, None
             if not (pre is not None and pre["it"] == ctx.it and pre.get("src") == src):
@@ -577,6 +636,13 @@ class BiscottiEngine:
         ctx.stake_m = np.asarray([s_ if a_ else 0 for s_, a_ in zip(self.stake, self.alive)], dtype=np.int32)
         ctx.is_worker = np.zeros(n, dtype=np.uint8)
         ctx.is_worker[pl.workers] = 1
+        ctx.salt64 = self.run_salt + (prev_hash + b"\0" * 32)[:32]
+        ctx.ns = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
+        ns = self._native()
+        if ns is not None and nk >= 3:
+            ctx.native = True
+            ns.upload_plan(ctx)
+            return ctx
         kpos = {p: i for i, p in enumerate(krum_set)}
         # Single-rank tcgen05 Krum: noise_mix writes the candidates' bf16 planes and norms compacted and in Krum
         # order (row = position in krum_set), so the Gram kernel needs no gather; the fp32 noised rows are only
@@ -648,7 +714,7 @@ class BiscottiEngine:
             nn_cols = max(1, cfg.num_noisers)
             if ctx.use_noise and cuda:
                 xyz, vev, _ = ctx.vrf_handle
-                torch.cuda.current_stream(dev).wait_event(vev)
+                vev.wait()
                 noiser_tab = self._noiser_tab
                 if self.P:
                     chain_ops.vrf_noisers(xyz, ctx.hash_d, len(pl.prev_hash), ctx.stake_d, ctx.isw_d,
@@ -718,7 +784,7 @@ class BiscottiEngine:
                                           gate_min=2)
 
     # ---- stage 4: the block's tail --------------------------------------------------------------------------------------
-    def _tail(self, ctx: "_Ctx") -> BlockReport:
+    def _tail(self, ctx: "_Ctx", host: dict | None = None) -> BlockReport:
         """9. ONE device->host collection (weights, counters, contributor list, gathered commitment||signature rows), then
         block assembly, stake update, hashing and append (one native call), then whatever can be queued for later."""
         cfg, dev, pl, pout, pre, rep = self.cfg, self.device, ctx.pl, ctx.pout, ctx.pre, ctx.rep
@@ -726,16 +792,17 @@ class BiscottiEngine:
         it, par, krum_set, n = ctx.it, ctx.par, pl.krum_set, cfg.num_nodes
         counts = pout["counts"]
         with self._phase("block"):
-            want = {"w": self.w64, "bad": self._bad, "counts": counts, "cpos": pout["contrib_pos"]}
-            if not cfg.secure_agg:
-                want["accept"] = ctx.accept
-            if self.colluder_ids and ctx.use_noise and cuda:
-                want["noisers"] = ctx.noiser_tab
-            if cuda and self.commit is not None:
-                if ctx.sig_event is not None:
-                    torch.cuda.current_stream(dev).wait_event(ctx.sig_event)
-                want["pack"] = self._gather_pack(self._pack[par], par)
-            host = self._collect(want)
+            if host is None:
+                want = {"w": self.w64, "bad": self._bad, "counts": counts, "cpos": pout["contrib_pos"]}
+                if not cfg.secure_agg:
+                    want["accept"] = ctx.accept
+                if self.colluder_ids and ctx.use_noise and cuda:
+                    want["noisers"] = ctx.noiser_tab
+                if cuda and self.commit is not None:
+                    if ctx.sig_event is not None:
+                        torch.cuda.current_stream(dev).wait_event(ctx.sig_event)
+                    want["pack"] = self._gather_pack(self._pack[par], par)
+                host = self._collect(want)
             cnt = host["counts"]
             n_contrib = int(cnt[1])
             rep.n_accepted = int(host["accept"].sum()) if "accept" in host else int(cnt[0])
@@ -796,6 +863,22 @@ class BiscottiEngine:
         cfg, pout, pre = self.cfg, ctx.pout, ctx.pre
         it = ctx.it
         do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
+        if ctx.native:
+            ns = self._ns
+            nxt = self._next_inputs_ready(self._side) if cfg.lookahead else False
+            if nxt is not False:
+                ns.queue_local_and_eval(it + 1, rep, do_eval, inputs=nxt)
+                nctx = self._begin_block_ahead()
+                if nctx is not None and not nctx.empty and nctx.native:
+                    ns.queue_front(nctx)
+                    ns.queue_commit_and_sign(nctx)
+                    self._ctx_next = nctx
+            elif do_eval:
+                ns.queue_eval(rep, ctx.par)
+            agg_box[0] = ns.queue_witness(ctx)
+            self._side_done[ctx.par] = ns.side_done[ctx.par]
+            self._wevent = ns.side_done[ctx.par]
+            return
         nxt = self._next_inputs_ready() if not self._timing else False
         npre, nctx = None, None
         with self._off_chain(chain_done):

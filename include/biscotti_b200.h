@@ -277,6 +277,11 @@ void bsc_srs_g1_host(const uint8_t tau_be[32], int d, uint8_t* out);
 // tau^i as plain little-endian 8x32 words, for the device fixed-base kernel
 void bsc_fr_powers(const uint8_t tau_be[32], int d, uint32_t* out_words);
 
+// Test hook for the two inversion routines of field.cuh: a^-1 mod m by binary extended Euclid (fe_inv) and by the
+// reference's Fermat exponentiation (fe_inv_fermat).  which: 0 = BN256 base field, 1 = BN256 group order,
+// 2 = 2^255-19.  Values are 32-byte big-endian plain integers (reduced mod m on input).
+void bsc_fe_inv_both(int which, const uint8_t a_be[32], uint8_t out_fast[32], uint8_t out_fermat[32]);
+
 // ---- Schnorr (kyber.go:873-933) ------------------------------------------------------------------
 // pub = x*G
 void bsc_schnorr_pubkey(const uint8_t x_be[32], uint8_t pub[64]);
@@ -377,6 +382,27 @@ int bsc_lottery_roles(const uint8_t* input, int inlen, const int* stake, int n, 
 
 // noisers from a peer's private VRF output, excluding itself (vrf.go:54-100)
 int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n, int source, int want, int* noisers);
+
+/* --------------------------------------------------------------------------------------------
+ * exec.cu - 
+ * -------------------------------------------------------------------------------------------- */
+// Runs cmds[0..n) in order.  Returns 0, or (index + 1) * 100000 + |rc| of the first failing command.
+int bsc_exec(const void* cmds_, int n, void* const* streams, int nstreams);
+
+int bsc_cmd_sizeof();
+
+// Events the command lists record and wait on (timing disabled: cheapest form).
+void* bsc_event_create();
+
+void bsc_event_destroy(void* e);
+
+int bsc_event_record(void* e, void* stream);
+
+int bsc_event_synchronize(void* e);
+
+int bsc_event_query(void* e);
+
+int bsc_stream_wait_event(void* stream, void* e);
 
 /* --------------------------------------------------------------------------------------------
  * fused.cu - 

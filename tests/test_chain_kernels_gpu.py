@@ -28,7 +28,7 @@ def test_vrf_noisers_kernel_matches_host_lottery():
     is_worker[[2, 9, 30]] = 0
     bv = cp.BatchedVRF(keys, DEV)
     xyz, ev, _ = bv.launch_dev(msg)
-    torch.cuda.current_stream().wait_event(ev)
+    ev.wait()
     local = list(range(7, 40))                                 # a rank's contiguous slice of the peers
     out = torch.full((len(local), 3), -7, dtype=torch.int32, device=DEV)
     vout = torch.zeros(len(local), 32, dtype=torch.uint8, device=DEV)
@@ -147,16 +147,19 @@ def test_pipelined_schedule_gives_the_in_line_chain():
     a = BiscottiEngine(BiscottiConfig(pipeline=True, **base), device=DEV)
     b = BiscottiEngine(BiscottiConfig(pipeline=False, prefetch=False, **base), device=DEV)
     c = BiscottiEngine(BiscottiConfig(pipeline=True, lookahead=False, **base), device=DEV)
+    e = BiscottiEngine(BiscottiConfig(pipeline=True, native_schedule=False, **base), device=DEV)   # Python-issued launches
     checked = 0
     for _ in range(6):
-        ra, rb, rc = a.step(), b.step(), c.step()
-        assert ra.block_hash == rb.block_hash == rc.block_hash and ra.contributors == rb.contributors
+        ra, rb, rc, re_ = a.step(), b.step(), c.step(), e.step()
+        assert ra.block_hash == rb.block_hash == rc.block_hash == re_.block_hash and ra.contributors == rb.contributors
+        assert abs(ra.test_error - rb.test_error) < 1e-9 and ra.attack_rate == re_.attack_rate
         if not ra.empty:
             assert a.verify_last_aggregate() is True and b.verify_last_aggregate() is True
             checked += 1
     torch.cuda.synchronize()
     assert checked >= 4 and a.chain == b.chain == c.chain and a._side is not None and b._side is None
     assert a._ctx_next is not None and c._ctx_next is None          # a really ran one block ahead
+    assert a._ns is not None and e._ns is None and a.chain == e.chain   # native command lists vs launches from Python
     # every block's approvals verify against the verifiers' public keys
     rep = next(r for r in a.reports if not r.empty)
     info = a.chain.block_info(rep.iteration + 1)
