@@ -196,7 +196,7 @@ class BatchedVRF:
         n = len(self.keys)
         if not hasattr(self, "_dside"):
             torch.cuda.current_stream(self.device).synchronize()   # once: the scalars' upload has landed
-            self._dside = torch.cuda.Stream(self.device, priority=-1)
+            self._dside = torch.cuda.Stream(self.device, priority=-3)
             self._dh_pinned = [torch.empty(64, dtype=torch.uint8).pin_memory() for _ in range(4)]
             self._dhd = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(4)]
             self._dxyz = [torch.empty(n, 30, dtype=torch.int32, device=self.device) for _ in range(2)]

@@ -173,7 +173,7 @@ class ApprovalSigner:
         if self.device.type == "cuda":
             self.secrets_dev = torch.from_numpy(self._sk_np).to(self.device)
             self._comb._ensure_table()
-            self.stream = torch.cuda.Stream(self.device, priority=-1)
+            self.stream = torch.cuda.Stream(self.device, priority=-2)
             self.event = torch.cuda.Event()
 
     def _ensure(self, n):

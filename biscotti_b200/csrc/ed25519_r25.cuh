@@ -222,7 +222,7 @@ HDN inline F25 f25_invert_fast(const F25& z) {
 }
 
 // z^((p-5)/8) = z^(2^252 - 3)
-HDN inline F25 f25_pow22523(const F25& z) {
+HDN inline F25 f25_pow22523_r25(const F25& z) {
   F25 t0 = f25_sq(z);
   F25 t1 = f25_sqn(t0, 2);
   t1 = f25_mul(z, t1);
@@ -245,6 +245,103 @@ HDN inline F25 f25_pow22523(const F25& z) {
   t0 = f25_mul(t1, t0);
   t0 = f25_sqn(t0, 2);
   return f25_mul(t0, z);
+}
+#if !defined(__CUDA_ARCH__)
+// Host only: the same power in radix 2^51 with 128-bit products (25 instead of 100 limb products per
+// multiplication).  hashToCurve runs on the host between a block's hash and the launch of the VRF kernel - i.e. on
+// the block's critical path - and its two z^(2^252-3) powers (Legendre symbol, square root) were ~100 us of it.
+struct F51 {
+  uint64_t v[5];
+};
+inline F51 f51_mul(const F51& a, const F51& b) {
+  typedef unsigned __int128 u128;
+  const uint64_t M = (1ULL << 51) - 1;
+  const uint64_t b1_19 = 19 * b.v[1], b2_19 = 19 * b.v[2], b3_19 = 19 * b.v[3], b4_19 = 19 * b.v[4];
+  u128 r0 = (u128)a.v[0] * b.v[0] + (u128)a.v[1] * b4_19 + (u128)a.v[2] * b3_19 + (u128)a.v[3] * b2_19 + (u128)a.v[4] * b1_19;
+  u128 r1 = (u128)a.v[0] * b.v[1] + (u128)a.v[1] * b.v[0] + (u128)a.v[2] * b4_19 + (u128)a.v[3] * b3_19 + (u128)a.v[4] * b2_19;
+  u128 r2 = (u128)a.v[0] * b.v[2] + (u128)a.v[1] * b.v[1] + (u128)a.v[2] * b.v[0] + (u128)a.v[3] * b4_19 + (u128)a.v[4] * b3_19;
+  u128 r3 = (u128)a.v[0] * b.v[3] + (u128)a.v[1] * b.v[2] + (u128)a.v[2] * b.v[1] + (u128)a.v[3] * b.v[0] + (u128)a.v[4] * b4_19;
+  u128 r4 = (u128)a.v[0] * b.v[4] + (u128)a.v[1] * b.v[3] + (u128)a.v[2] * b.v[2] + (u128)a.v[3] * b.v[1] + (u128)a.v[4] * b.v[0];
+  F51 o;
+  uint64_t c;
+  c = (uint64_t)(r0 >> 51); o.v[0] = (uint64_t)r0 & M; r1 += c;
+  c = (uint64_t)(r1 >> 51); o.v[1] = (uint64_t)r1 & M; r2 += c;
+  c = (uint64_t)(r2 >> 51); o.v[2] = (uint64_t)r2 & M; r3 += c;
+  c = (uint64_t)(r3 >> 51); o.v[3] = (uint64_t)r3 & M; r4 += c;
+  c = (uint64_t)(r4 >> 51); o.v[4] = (uint64_t)r4 & M;
+  o.v[0] += 19 * c;
+  c = o.v[0] >> 51; o.v[0] &= M; o.v[1] += c;
+  return o;
+}
+inline F51 f51_sqn(F51 t, int n) {
+  for (int i = 0; i < n; i++) t = f51_mul(t, t);
+  return t;
+}
+inline F25 f25_pow22523_host51(const F25& zin) {
+  const uint64_t M = (1ULL << 51) - 1;
+  uint8_t b[32];
+  f25_tobytes(b, zin);
+  U256 u = u256_from_le(b);
+  auto bits = [&u](int lo) -> uint64_t {      // 51 bits of u starting at bit `lo`
+    uint64_t r = 0;
+    for (int k = 0; k < 51; k++) {
+      const int bit = lo + k;
+      if (bit < 256) r |= (uint64_t)((u.v[bit >> 5] >> (bit & 31)) & 1u) << k;
+    }
+    return r;
+  };
+  F51 z;
+  for (int i = 0; i < 5; i++) z.v[i] = bits(51 * i);
+  F51 t0 = f51_mul(z, z);
+  F51 t1 = f51_sqn(t0, 2);
+  t1 = f51_mul(z, t1);
+  t0 = f51_mul(t0, t1);
+  t0 = f51_mul(t0, t0);
+  t0 = f51_mul(t1, t0);
+  t1 = f51_sqn(t0, 5);
+  t0 = f51_mul(t1, t0);
+  t1 = f51_sqn(t0, 10);
+  t1 = f51_mul(t1, t0);
+  F51 t2 = f51_sqn(t1, 20);
+  t1 = f51_mul(t2, t1);
+  t1 = f51_sqn(t1, 10);
+  t0 = f51_mul(t1, t0);
+  t1 = f51_sqn(t0, 50);
+  t1 = f51_mul(t1, t0);
+  t2 = f51_sqn(t1, 100);
+  t1 = f51_mul(t2, t1);
+  t1 = f51_sqn(t1, 50);
+  t0 = f51_mul(t1, t0);
+  t0 = f51_sqn(t0, 2);
+  t0 = f51_mul(t0, z);
+  // carry once more, pack into 256 bits (value < 2^255 + 2^52), reduce mod p
+  uint64_t c;
+  for (int pass = 0; pass < 2; pass++) {
+    c = t0.v[0] >> 51; t0.v[0] &= M; t0.v[1] += c;
+    c = t0.v[1] >> 51; t0.v[1] &= M; t0.v[2] += c;
+    c = t0.v[2] >> 51; t0.v[2] &= M; t0.v[3] += c;
+    c = t0.v[3] >> 51; t0.v[3] &= M; t0.v[4] += c;
+    c = t0.v[4] >> 51; t0.v[4] &= M; t0.v[0] += 19 * c;
+  }
+  U256 r;
+  for (int i = 0; i < 8; i++) r.v[i] = 0;
+  for (int i = 0; i < 5; i++)
+    for (int k = 0; k < 51; k++) {
+      const int bit = 51 * i + k;
+      if (bit < 256 && ((t0.v[i] >> k) & 1ULL)) r.v[bit >> 5] |= 1u << (bit & 31);
+    }
+  const U256 p = mod_of<EdP>();
+  while (u256_geq(r, p)) u256_sub(r, r, p);
+  u256_to_le(b, r);
+  return f25_frombytes(b);
+}
+#endif
+HDN inline F25 f25_pow22523(const F25& z) {
+#if !defined(__CUDA_ARCH__)
+  return f25_pow22523_host51(z);
+#else
+  return f25_pow22523_r25(z);
+#endif
 }
 HD bool f25_is_zero(const F25& a) {
   uint8_t s[32];
@@ -379,7 +476,7 @@ HDN inline EdP3 edr_elligator2_x8(const uint8_t h[32]) {
   const F25 A = f25_from_u32(486662);
   F25 r = f25_frombytes(t);
   F25 den = f25_add(f25_sq2(r), one);
-  F25 v = f25_mul(f25_neg(A), f25_invert(den));
+  F25 v = f25_mul(f25_neg(A), f25_invert_fast(den));
   F25 v2 = f25_sq(v);
   F25 e = f25_add(f25_add(f25_mul(v2, v), v), f25_mul(v2, A));
   e = f25_mul(e, one);   // re-carry the three-term sum before it is used as a multiplication input
@@ -387,7 +484,7 @@ HDN inline EdP3 edr_elligator2_x8(const uint8_t h[32]) {
   F25 chi = f25_mul(f25_sqn(f25_pow22523(e), 2), f25_sq(e));
   const bool minus1 = !f25_eq(chi, one) && !f25_is_zero(chi);
   if (minus1) v = f25_mul(f25_sub(f25_neg(v), A), one);
-  F25 y = f25_mul(f25_sub(v, one), f25_invert(f25_add(v, one)));
+  F25 y = f25_mul(f25_sub(v, one), f25_invert_fast(f25_mul(f25_add(v, one), one)));
   EdP3 p;
   if (!edr_from_parity_and_y(p, bit, y)) p = edr_identity();
   EdP1 c = edr_dbl(p.X, p.Y, p.Z);
@@ -399,7 +496,7 @@ HDN inline EdP3 edr_elligator2_x8(const uint8_t h[32]) {
 }
 // affine x || y (canonical little-endian) of an extended point
 HDN inline void edr_to_affine_bytes(uint8_t out[64], const EdP3& p) {
-  F25 zi = f25_invert(p.Z);
+  F25 zi = f25_invert_fast(p.Z);
   f25_tobytes(out, f25_mul(p.X, zi));
   f25_tobytes(out + 32, f25_mul(p.Y, zi));
 }

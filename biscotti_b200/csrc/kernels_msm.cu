@@ -146,39 +146,53 @@ __global__ void __launch_bounds__(128, MINB) msm_table_kernel(const long long* _
 // Fixed-base comb for full-width scalars: out[i] = k_i * B with B's window table (w bits, nw windows,
 // nw*w >= 257 so the final carry has a window).  Used for the Schnorr commitments T = v*G of the
 // verifiers' approvals (kyber.go:873-896): 33 mixed additions instead of ~380 point operations.
+// The approvals sit on the path to the block's tail with only ~200 scalars to hide latency behind, so one scalar
+// is spread over COMB_LANES threads: every lane recodes the scalar (cheap integer work), adds the windows
+// lane, lane + COMB_LANES, ... and the partial sums meet in a shared-memory tree - ceil(33/8) = 5 dependent mixed
+// additions + 3 Jacobian additions instead of 33.
+constexpr int COMB_LANES = 8;
 __global__ void __launch_bounds__(128) g1_comb_mul_kernel(const U256* __restrict__ k, int N,
                                                           const G1Affine* __restrict__ table, int w, int nw,
                                                           G1Jac* __restrict__ out) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N) return;
+  __shared__ G1Jac sh[128];
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = t / COMB_LANES, lane = t % COMB_LANES;
   const int H = 1 << (w - 1);
   const uint32_t mask = (1u << w) - 1u;
-  const U256 s = k[i];
   G1Jac acc = g1j_inf();
-  uint32_t carry = 0;
-  for (int win = 0; win < nw; win++) {
-    const int bit = win * w;
-    uint32_t d = carry;
-    if (bit < 256) {
-      const int limb = bit >> 5, sh = bit & 31;
-      uint64_t two = s.v[limb];
-      if (limb + 1 < 8) two |= (uint64_t)s.v[limb + 1] << 32;
-      d += (uint32_t)(two >> sh) & mask;
-    }
-    carry = 0;
-    bool neg = false;
-    if (d > (uint32_t)H) {
-      d = (1u << w) - d;
-      neg = true;
-      carry = 1;
-    }
-    if (d) {
-      G1Affine pt = table[(size_t)win * H + (d - 1)];
-      if (neg) pt.y = fe_neg(pt.y);
-      acc = g1j_add_affine(acc, pt);
+  if (i < N) {
+    const U256 s = k[i];
+    uint32_t carry = 0;
+    for (int win = 0; win < nw; win++) {
+      const int bit = win * w;
+      uint32_t d = carry;
+      if (bit < 256) {
+        const int limb = bit >> 5, shft = bit & 31;
+        uint64_t two = s.v[limb];
+        if (limb + 1 < 8) two |= (uint64_t)s.v[limb + 1] << 32;
+        d += (uint32_t)(two >> shft) & mask;
+      }
+      carry = 0;
+      bool neg = false;
+      if (d > (uint32_t)H) {
+        d = (1u << w) - d;
+        neg = true;
+        carry = 1;
+      }
+      if (d && (win % COMB_LANES) == lane) {
+        G1Affine pt = table[(size_t)win * H + (d - 1)];
+        if (neg) pt.y = fe_neg(pt.y);
+        acc = g1j_add_affine(acc, pt);
+      }
     }
   }
-  out[i] = acc;
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int step = COMB_LANES >> 1; step > 0; step >>= 1) {
+    if (lane < step) sh[threadIdx.x] = g1j_add(sh[threadIdx.x], sh[threadIdx.x + step]);
+    __syncthreads();
+  }
+  if (i < N && lane == 0) out[i] = sh[threadIdx.x];
 }
 
 // k_i * B for full 256-bit scalars (SRS generation: PKG1[i] = tau^i * G, DistSys/publicKey.go:28-66)
@@ -364,7 +378,8 @@ int bsc_g1_comb_mul(const void* scalars_u256, int N, const void* table_affine, i
                     void* stream) {
   if (N == 0) return 0;
   if (w < 2 || w > 12 || nw * w < 257) return -1;
-  g1_comb_mul_kernel<<<(N + 127) / 128, 128, 0, (cudaStream_t)stream>>>((const U256*)scalars_u256, N,
+  const long long threads = (long long)N * COMB_LANES;
+  g1_comb_mul_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const U256*)scalars_u256, N,
                                                                          (const G1Affine*)table_affine, w, nw,
                                                                          (G1Jac*)out_jac);
   return finish_launch("g1_comb_mul");

@@ -187,7 +187,7 @@ class BiscottiEngine:
         self._next_inputs, self._fed_inputs = None, False
         self._eval_waiting: list = []           # reports whose error rates are still being read back
         self._vrf_early = None
-        self._main = self._side = None          # chain stream / off-chain stream of a pipelined GPU engine
+        self._main = self._side = self._wit = None      # chain / off-chain / witness streams of a pipelined GPU engine
         self._wstream = None                    # alias of _side, kept for callers that look for the witness stream
         self._wevent = None
         self._side_done = [None, None]          # per block parity: off-chain work of that block has finished
@@ -516,8 +516,10 @@ class BiscottiEngine:
         if not self.pipelined:
             return self._step(inputs, next_inputs)
         if self._main is None:
-            self._main = torch.cuda.Stream(self.device, priority=-1)
-            self._side = torch.cuda.Stream(self.device, priority=0)
+            # chain > approvals > short off-chain kernels > witness MSM (CUDA: a lower number is a higher priority)
+            self._main = torch.cuda.Stream(self.device, priority=-3)
+            self._side = torch.cuda.Stream(self.device, priority=-1)
+            self._wit = torch.cuda.Stream(self.device, priority=0)
             self._wstream = self._side
         cur = torch.cuda.current_stream(self.device)
         self._main.wait_stream(cur)

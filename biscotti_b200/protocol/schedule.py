@@ -17,7 +17,7 @@ Segments, per block parity (buffers that two blocks in flight could both touch a
                           approvals; gathers the commitment||signature rows; the block's device->host copies
     COMMIT  side stream : quantise, commitment MSM, column sums, normalise, wire bytes        records c_ready
     SIGN    sign stream : nonces, T = v*G, normalise, bytes; waits c_ready; challenge + response -> pack rows
-    WITNESS side stream : witness MSM, miners' homomorphic aggregation                        records side_done
+    WITNESS wit stream  : witness MSM, miners' homomorphic aggregation                        records side_done
 """
 from __future__ import annotations
 
@@ -32,7 +32,7 @@ from ..ops.cmdlist import CmdList, NativeEvent
 from ..ops.msm import AFF, JAC
 from ..ops.secagg import recover_matrix, _RecoverMat
 
-MAIN, SIDE, SIGN = 0, 1, 2
+MAIN, SIDE, SIGN, WIT = 0, 1, 2, 3
 
 
 class NativeSchedule:
@@ -53,7 +53,7 @@ class NativeSchedule:
         self.n, self.P = n, P
         eng._ensure_bufs()
         i32 = dict(dtype=torch.int32, device=dev)
-        streams = [eng._main, eng._side, eng.signer.stream if eng.signer is not None else eng._side]
+        streams = [eng._main, eng._side, eng.signer.stream if eng.signer is not None else eng._side, eng._wit]
         self.streams = streams
         # ---- events
         ev = lambda: [NativeEvent(), NativeEvent()]   # noqa: E731
@@ -252,6 +252,7 @@ class NativeSchedule:
         # ---- COMMIT -------------------------------------------------------------------------------------------------------
         ix["commit0"] = cl.n
         Q, chunkC = self.Q[par], self.chunkC[par]
+        cl.wait(SIDE, self.side_done[par])      # the witnesses of the block two heights back still read Q / chunkC of this parity
         cl.add("quantize", SIDE, eng.U, Q, P, d, eng.ldu, C.dpad, scale4)
         cl.add("msm_table_dc", SIDE, Q, Q.stride(0), None, P, None, C.c_sidx, C.c_bidx, None, C.nchunk, POLY_SIZE, C.c_table,
                C.w, C.nw, chunkC, C.nchunk)
@@ -282,13 +283,18 @@ class NativeSchedule:
             cl.record(SIDE, self.sig_done[par])
         ix["sign1"] = cl.n
         # ---- WITNESS ------------------------------------------------------------------------------------------------------
+        # Their own lowest-priority stream: the witness MSM fills the GPU for most of a block, while the side stream's
+        # kernels (local step, error rates, column sums, normalisation) are short and latency-bound - side by side they
+        # overlap instead of queueing behind one another.
         ix["wit0"] = cl.n
         G = C.nchunk * self.S
-        ix["wit"] = cl.add("msm_table_dc", SIDE, Q, Q.stride(0), pout["appr_local"], self.wrows, n_la, C.w_sidx, C.w_bidx, None,
+        cl.wait(WIT, self.collect_ev)           # the plan's row lists and counts of this block
+        cl.wait(WIT, self.c_ready[par])         # Q and chunkC of this block
+        ix["wit"] = cl.add("msm_table_dc", WIT, Q, Q.stride(0), pout["appr_local"], self.wrows, n_la, C.w_sidx, C.w_bidx, None,
                            G, POLY_SIZE - 1, C.w_table, C.w, C.nw, self.W, G)
-        cl.add("g1_sum_rows_jac_dc", SIDE, self.W, pout["csel"], pout["csel"].numel(), n_lc, G, self.aggW[par])
-        cl.add("g1_sum_rows_jac_dc", SIDE, chunkC, pout["sel"], pout["sel"].numel(), n_lc, C.nchunk, self.aggC[par])
-        cl.record(SIDE, self.side_done[par])
+        cl.add("g1_sum_rows_jac_dc", WIT, self.W, pout["csel"], pout["csel"].numel(), n_lc, G, self.aggW[par])
+        cl.add("g1_sum_rows_jac_dc", WIT, chunkC, pout["sel"], pout["sel"].numel(), n_lc, C.nchunk, self.aggC[par])
+        cl.record(WIT, self.side_done[par])
         ix["wit1"] = cl.n
         cl.ix = ix
         return cl
