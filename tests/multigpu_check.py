@@ -24,6 +24,16 @@ def main():
     peers = int(os.environ.get("BSC_PEERS", "100"))
     iters = int(os.environ.get("BSC_ITERS", "6"))
     out = {"world": world}
+    if rank == 0:
+        # the ledger must not depend on how the peers are sharded: the same run on one GPU, no communicator at all
+        cfg = BiscottiConfig(num_nodes=peers, dataset="mnist", max_iterations=iters, shard_size=200, test_size=500)
+        solo = BiscottiEngine(cfg, device=dev)
+        solo.run(iters)
+        torch.cuda.synchronize()
+        out["single_gpu_hash"] = solo.chain.latest_hash().hex()[:16]
+        del solo
+        torch.cuda.empty_cache()
+    torch.distributed.barrier()
     for name in ("fused", "nccl"):
         cfg = BiscottiConfig(num_nodes=peers, dataset="mnist", max_iterations=iters, shard_size=200, test_size=500)
         comm = FusedComm(rank, world, dev, cfg) if name == "fused" else NcclComm(rank, world, dev)
@@ -38,9 +48,11 @@ def main():
                      "hash": hashes[0].hex()[:16], "bad": sum(r.bad_shares for r in reps),
                      "empty": sum(r.empty for r in reps), "test_error": reps[-1].test_error,
                      "verify_ok": eng.chain.verify()}
+        eng.close()
     if rank == 0:
         print("MULTIGPU_CHECK " + json.dumps(out))
         ok = all(out[k]["chain_equal"] and out[k]["verify_ok"] and out[k]["bad"] == 0 for k in ("fused", "nccl"))
+        ok = ok and out["fused"]["hash"] == out["nccl"]["hash"] == out["single_gpu_hash"]
         print("MULTIGPU_CHECK_OK" if ok else "MULTIGPU_CHECK_FAILED")
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()

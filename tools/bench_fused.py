@@ -107,10 +107,14 @@ def main():
         w32 = torch.zeros(d, device=dev)
         xs_t = torch.arange(10, dtype=torch.int32, device=dev)
 
+        bad_n = torch.zeros(4, dtype=torch.int32, device=dev)
+        av_t = torch.ones(cfg.total_shares, dtype=torch.uint8, device=dev)
+
         def nccl_sec():
+            # baseline: library all-reduce of the share sums + the same matrix-recovery kernel, un-fused
             Y = comm.ypart.clone()
             nccl.all_reduce_i64(Y)
-            secagg.reconstruct_step(Y, xs_t, None, d, w64, w32)
+            secagg.reconstruct_step_dev(Y, list(range(10)), xs_t, av_t, d, w64, w32, bad=bad_n)
 
         t_fs = timed(fused_sec, 20, world)
         t_ns = timed(nccl_sec, 20, world)
@@ -123,7 +127,7 @@ def main():
                         "secagg_fused_us": round(t_fs, 1), "secagg_nccl_us": round(t_ns, 1),
                         "secagg_roofline_us": round(roof_sec, 2), "secagg_frac_of_roofline": round(roof_sec / t_fs, 4),
                         "secagg_nvlink_bytes_per_gpu": int(sec_bytes)})
-        del comm
+        comm.close()
         torch.cuda.empty_cache()
     if rank == 0:
         print("BENCH_FUSED " + json.dumps(results))
