@@ -123,6 +123,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_ed25519_scalarmult_r25", c_i, c_p, c_p, c_i, c_p, c_p)
     sig("bsc_ed25519_scalarmult_quad", c_i, c_p, c_p, c_i, c_p, c_p)
     sig("bsc_ed25519_scalarmult_quad_xyz", c_i, c_p, c_p, c_i, c_p, c_p)
+    sig("bsc_ed25519_scalarmult_wide_xyz", c_i, c_p, c_p, c_i, c_p, c_p)
     sig("bsc_ed25519_compress_batch", None, c_p, c_i, c_p)
     sig("bsc_ed25519_scalarmult_r25_host", None, c_p, c_p, c_i, c_p)
     sig("bsc_sha256_batch", c_i, c_p, c_i, c_ll, c_i, c_p, c_p)

@@ -210,8 +210,9 @@ class BatchedVRF:
         L.bsc_vrf_hash_to_curve_xy(msg, len(msg), ctypes.c_void_p(hp.data_ptr()))
         with torch.cuda.stream(self._dside):
             hd.copy_(hp, non_blocking=True)
-            rc = L.bsc_ed25519_scalarmult_quad_xyz(ctypes.c_void_p(self.scalars.data_ptr()), ctypes.c_void_p(hd.data_ptr()), n,
-                                                   ctypes.c_void_p(xyz.data_ptr()), ctypes.c_void_p(self._dside.cuda_stream))
+            fn = L.bsc_ed25519_scalarmult_quad_xyz if self.kernel == "quad4" else L.bsc_ed25519_scalarmult_wide_xyz
+            rc = fn(ctypes.c_void_p(self.scalars.data_ptr()), ctypes.c_void_p(hd.data_ptr()), n,
+                    ctypes.c_void_p(xyz.data_ptr()), ctypes.c_void_p(self._dside.cuda_stream))
             if rc:
                 raise RuntimeError("ed25519 scalar multiplication kernel failed")
             ev.record(self._dside)

@@ -337,7 +337,9 @@ struct SecaggFusedParams {
 __global__ void __launch_bounds__(256) secagg_fused_kernel(const __grid_constant__ SecaggFusedParams P) {
   __shared__ long long sy[SF_CH * MAX_SHARES];
   __shared__ long long sc[SF_CH * POLY_SIZE];
+  __shared__ RecoverMat sR;   // matrix rows are indexed by the thread's coefficient: shared memory, not the constant bank
   const int tid = threadIdx.x;
+  if (tid < (int)(sizeof(RecoverMat) / 4)) reinterpret_cast<int*>(&sR)[tid] = reinterpret_cast<const int*>(&P.R)[tid];
   // this rank's partial share sums were produced by the previous kernel on this stream: publish, then wait
   if (tid == 0) {
     if (blockIdx.x == 0) {
@@ -368,9 +370,9 @@ __global__ void __launch_bounds__(256) secagg_fused_kernel(const __grid_constant
         const int lc = e / POLY_SIZE, j = e % POLY_SIZE;
         int64_t y[POLY_SIZE];
 #pragma unroll
-        for (int i = 0; i < POLY_SIZE; i++) y[i] = sy[lc * MAX_SHARES + P.R.xs[i]];
+        for (int i = 0; i < POLY_SIZE; i++) y[i] = sy[lc * MAX_SHARES + sR.xs[i]];
         int64_t coef;
-        inexact += !recover_coef_mat(P.R, y, j, coef);
+        inexact += !recover_coef_mat(sR, y, j, coef);
         sc[e] = coef;
       }
     } else {

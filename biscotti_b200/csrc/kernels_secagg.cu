@@ -122,7 +122,9 @@ __global__ void __launch_bounds__(256) reconstruct_mat_kernel(const long long* _
                                                               int gate_min) {
   __shared__ long long sy[RM_CH * MAX_SHARES];
   __shared__ long long sc[RM_CH * POLY_SIZE];
+  __shared__ RecoverMat sR;   // the matrix rows are indexed by the thread's coefficient: shared memory, not the constant bank
   if (gate && *gate < gate_min) return;
+  if (threadIdx.x < (int)(sizeof(RecoverMat) / 4)) reinterpret_cast<int*>(&sR)[threadIdx.x] = reinterpret_cast<const int*>(&R)[threadIdx.x];
   const int ch0 = blockIdx.x * RM_CH;
   const int nch = min(RM_CH, nc - ch0);
   for (int e = threadIdx.x; e < nch * S; e += blockDim.x) sy[(e / S) * MAX_SHARES + (e % S)] = Ysum[(size_t)ch0 * S + e];
@@ -132,9 +134,9 @@ __global__ void __launch_bounds__(256) reconstruct_mat_kernel(const long long* _
     const int lc = e / POLY_SIZE, j = e % POLY_SIZE;
     int64_t y[POLY_SIZE];
 #pragma unroll
-    for (int i = 0; i < POLY_SIZE; i++) y[i] = sy[lc * MAX_SHARES + R.xs[i]];
+    for (int i = 0; i < POLY_SIZE; i++) y[i] = sy[lc * MAX_SHARES + sR.xs[i]];
     int64_t coef;
-    inexact += !recover_coef_mat(R, y, j, coef);
+    inexact += !recover_coef_mat(sR, y, j, coef);
     sc[e] = coef;
     const int k = (c0 + ch0 + lc) * POLY_SIZE + j;
     if (k < d) {

@@ -275,6 +275,180 @@ __global__ void __launch_bounds__(128) ed25519_scalarmult_quad_kernel(const unsi
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Warp-wide variant: one peer per warp, ONE LIMB PER LANE.
+//
+// The VRF of every peer is evaluated on the previous block hash, so this kernel is the head of every block's
+// dependency chain and there is nothing to overlap it with: what counts is the latency of one scalar multiplication.
+// In the quad kernel a lane computes a whole 10x10-limb product (100 dependent-ish 64-bit multiply-adds, ~0.65 us);
+// here lane (g, k) of a warp computes limb k of product g: ten multiply-adds, operands fetched with warp shuffles, and
+// the carry chain is three parallel passes (each limb hands its carry to the next lane) instead of a ten-step
+// sequential one.  Three products run side by side (lanes 0-9, 10-19, 20-29; lanes 30-31 mirror 20-21), and every lane
+// keeps limb k of ALL coordinates of the running point (replicated across the three groups), so the additions and
+// subtractions between products are plain per-lane integer adds.  A doubling is three such steps (XX YY 2ZZ | (X+Y)^2
+// Y3 Z3 | X3 T3 +1 free slot), an addition of a table entry two (its Z*Zq product rides in the free slot of the
+// doubling before it): 14 steps per radix-16 digit, ~900 steps per scalar instead of 640 full products.
+// Bounds follow the radix-2^25.5 reference formulas: products take operands up to 1.65 * 2^26 / 2^25, the rounded
+// three-pass carry returns limbs within 2^25 + 19 / 2^24 + 1.
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void wide_mul3(int32_t a0, int32_t b0, int32_t a1, int32_t b1, int32_t a2, int32_t b2, int g,
+                                          int k, int32_t& r0, int32_t& r1, int32_t& r2) {
+  const unsigned FULL = 0xffffffffu;
+  const int base = g * 10;
+  const int32_t a = g == 0 ? a0 : (g == 1 ? a1 : a2);
+  const int32_t b = g == 0 ? b0 : (g == 1 ? b1 : b2);
+  int64_t acc = 0;
+#pragma unroll
+  for (int i = 0; i < 10; i++) {
+    int32_t fi = __shfl_sync(FULL, a, base + i);
+    int j = k - i;
+    const bool wrap = j < 0;
+    if (wrap) j += 10;
+    int32_t gj = __shfl_sync(FULL, b, base + j);
+    if (wrap) gj *= 19;
+    if ((i & 1) && (j & 1)) fi *= 2;
+    acc += (int64_t)fi * (int64_t)gj;
+  }
+  const int sft = (k & 1) ? 25 : 26;
+  const int src = base + (k == 0 ? 9 : k - 1);
+  int64_t c = (acc + ((int64_t)1 << (sft - 1))) >> sft;
+  acc -= c << sft;
+  int64_t cin = __shfl_sync(FULL, c, src);
+  if (k == 0) cin *= 19;
+  acc += cin;
+  int32_t c2 = (int32_t)((acc + ((int64_t)1 << (sft - 1))) >> sft);
+  acc -= (int64_t)c2 << sft;
+  int32_t cin2 = __shfl_sync(FULL, c2, src);
+  if (k == 0) cin2 *= 19;
+  int32_t h = (int32_t)acc + cin2;
+  const int32_t c3 = (h + (1 << (sft - 1))) >> sft;
+  h -= c3 << sft;
+  int32_t cin3 = __shfl_sync(FULL, c3, src);
+  if (k == 0) cin3 *= 19;
+  h += cin3;
+  r0 = __shfl_sync(FULL, h, k);
+  r1 = __shfl_sync(FULL, h, 10 + k);
+  r2 = __shfl_sync(FULL, h, 20 + k);
+}
+
+constexpr int WIDE_WARPS = 4;
+__global__ void __launch_bounds__(32 * WIDE_WARPS) ed25519_scalarmult_wide_kernel(const unsigned char* __restrict__ scalars,
+                                                                                  const unsigned char* __restrict__ hxy, int N,
+                                                                                  int32_t* __restrict__ xyz_out) {
+  __shared__ int32_t tab[WIDE_WARPS][8][4][10];   // per warp: (j+1)H as (Y+X, Y-X, Z, 2dT), one limb per lane
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int peer = blockIdx.x * WIDE_WARPS + warp;
+  const int pi = peer < N ? peer : N - 1;          // idle warps mirror the last peer (control flow stays uniform per warp)
+  const int g = lane < 30 ? lane / 10 : 2;
+  const int k = lane < 30 ? lane % 10 : lane - 30;
+  // limb k of the constants and of H
+  int32_t d2k, hxk, hyk, onek = (k == 0) ? 1 : 0;
+  {
+    uint8_t b[64];
+    for (int i = 0; i < 64; i++) b[i] = hxy[i];
+    const F25 hx = f25_frombytes(b), hy = f25_frombytes(b + 32), d2 = f25_const_2d();
+    hxk = hx.v[k];
+    hyk = hy.v[k];
+    d2k = d2.v[k];
+  }
+  int32_t u0, u1, u2;
+  // ---- table: P = H (extended), cached(P) = (Y+X, Y-X, Z, 2d T)
+  int32_t X = hxk, Y = hyk, Z = onek, T;
+  wide_mul3(X, Y, X, Y, X, Y, g, k, T, u1, u2);                 // T = x*y
+  int32_t Td;
+  wide_mul3(T, d2k, T, d2k, T, d2k, g, k, Td, u1, u2);          // 2d*T
+  const int32_t hp = Y + X, hm = Y - X, hz = Z, ht = Td;        // cached H, in registers
+  if (lane < 10) {
+    tab[warp][0][0][k] = hp;
+    tab[warp][0][1][k] = hm;
+    tab[warp][0][2][k] = hz;
+    tab[warp][0][3][k] = ht;
+  }
+#pragma unroll 1
+  for (int j = 1; j < 8; j++) {
+    // P <- P + H (full outputs), then cache it
+    int32_t a, bq, c, dd;
+    wide_mul3(Y + X, hp, Y - X, hm, T, ht, g, k, a, bq, c);
+    wide_mul3(Z, hz, Z, hz, Z, hz, g, k, dd, u1, u2);
+    const int32_t D = dd + dd, cX = a - bq, cY = a + bq, cZ = D + c, cT = D - c;
+    wide_mul3(cX, cT, cY, cZ, cZ, cT, g, k, X, Y, Z);
+    wide_mul3(cX, cY, cX, cY, cX, cY, g, k, T, u1, u2);
+    wide_mul3(T, d2k, T, d2k, T, d2k, g, k, Td, u1, u2);
+    if (lane < 10) {
+      tab[warp][j][0][k] = Y + X;
+      tab[warp][j][1][k] = Y - X;
+      tab[warp][j][2][k] = Z;
+      tab[warp][j][3][k] = Td;
+    }
+  }
+  __syncwarp();
+  // ---- signed radix-16 recoding (every lane computes the same digits)
+  signed char e[64];
+  for (int i = 0; i < 32; i++) {
+    const unsigned char a = scalars[32 * (size_t)pi + i];
+    e[2 * i] = (signed char)(a & 15);
+    e[2 * i + 1] = (signed char)((a >> 4) & 15);
+  }
+  int carry = 0;
+  for (int i = 0; i < 63; i++) {
+    e[i] = (signed char)(e[i] + carry);
+    carry = (e[i] + 8) >> 4;
+    e[i] = (signed char)(e[i] - (carry << 4));
+  }
+  e[63] = (signed char)(e[63] + carry);
+  // ---- main loop
+  X = 0;
+  Y = onek;
+  Z = onek;
+  T = 0;
+#pragma unroll 1
+  for (int i = 63; i >= 0; i--) {
+    const int dgt = e[i];
+    const int mag = dgt < 0 ? -dgt : dgt;
+    int32_t qp = 0, qm = 0, qz = 0, qt = 0;
+    if (mag) {   // uniform per warp: one peer per warp
+      const int32_t tp = tab[warp][mag - 1][0][k], tm = tab[warp][mag - 1][1][k];
+      qz = tab[warp][mag - 1][2][k];
+      qt = tab[warp][mag - 1][3][k];
+      if (dgt < 0) {
+        qp = tm;
+        qm = tp;
+        qt = -qt;
+      } else {
+        qp = tp;
+        qm = tm;
+      }
+    }
+    int32_t dz = 0;
+#pragma unroll 1
+    for (int rep = 0; rep < 4; rep++) {
+      int32_t XX, YY, ZZ2, A, Y3, Z3, X3, T3;
+      wide_mul3(X, X, Y, Y, Z, Z + Z, g, k, XX, YY, ZZ2);
+      const int32_t cY = YY + XX, cZ = YY - XX, cT = ZZ2 - cZ, xy = X + Y;
+      wide_mul3(xy, xy, cY, cZ, cZ, cT, g, k, A, Y3, Z3);
+      const int32_t cX = A - cY;
+      // third slot of the last doubling: Z3 * Zq for the addition that follows
+      wide_mul3(cX, cT, cX, cY, Z3, qz, g, k, X3, T3, dz);
+      X = X3;
+      Y = Y3;
+      Z = Z3;
+      T = T3;
+    }
+    if (mag) {
+      int32_t a, bq, c;
+      wide_mul3(Y + X, qp, Y - X, qm, T, qt, g, k, a, bq, c);
+      const int32_t D = dz + dz, cX = a - bq, cY = a + bq, cZ = D + c, cT = D - c;
+      wide_mul3(cX, cT, cY, cZ, cZ, cT, g, k, X, Y, Z);
+    }
+  }
+  if (peer < N && lane < 10) {
+    int32_t* o = xyz_out + 30 * (size_t)peer;
+    o[k] = X;
+    o[10 + k] = Y;
+    o[20 + k] = Z;
+  }
+}
+
 // batched SHA-256: digest of msgs[i] (each `len` bytes, `stride` apart) -> out[i][32]
 __global__ void sha256_batch_kernel(const unsigned char* __restrict__ msgs, int len, long long stride, int N,
                                     unsigned char* __restrict__ out) {
@@ -484,6 +658,14 @@ int bsc_ed25519_scalarmult_quad_xyz(const unsigned char* scalars, const unsigned
   ed25519_scalarmult_quad_kernel<<<(threads + 127) / 128, 128, 0, (cudaStream_t)stream>>>(scalars, hxy, N, nullptr,
                                                                                           xyz_out);
   return finish_launch("ed25519_scalarmult_quad_xyz");
+}
+// warp-wide latency kernel (one peer per warp, one limb per lane); same contract as the quad _xyz entry point
+int bsc_ed25519_scalarmult_wide_xyz(const unsigned char* scalars, const unsigned char* hxy, int N, int* xyz_out,
+                                    void* stream) {
+  if (N == 0) return 0;
+  ed25519_scalarmult_wide_kernel<<<(N + WIDE_WARPS - 1) / WIDE_WARPS, 32 * WIDE_WARPS, 0, (cudaStream_t)stream>>>(
+      scalars, hxy, N, xyz_out);
+  return finish_launch("ed25519_scalarmult_wide_xyz");
 }
 // host: compress N projective points with a single field inversion (prefix products)
 void bsc_ed25519_compress_batch(const int* xyz, int N, unsigned char* out) {

@@ -579,7 +579,10 @@ class BiscottiEngine:
             ns.queue_back(ctx)
             if not self.fused:
                 self._last_ysum = self._ysum[ctx.par]
-            return self._tail(ctx, ns.collect())
+            ctx.phases["host_queue"] = (time.perf_counter() - t0) * 1e3
+            host = ns.collect()
+            ctx.phases["host_wait"] = (time.perf_counter() - t0) * 1e3 - ctx.phases["host_queue"]
+            return self._tail(ctx, host)
         if ctx.pre is None:
             pre, self._pre = self._pre, None
             if not (pre is not None and pre["it"] == ctx.it and pre.get("src") == src):
@@ -851,6 +854,7 @@ class BiscottiEngine:
                         if not acc[i]:
                             self.stake[p] -= STAKE_UNIT                  # honest.go:362-370 (plain path only)
         agg_box = [None]
+        ctx.phases["host_tail_py"] = ctx.phases.pop("block")
         rep = self._finish_block(rep, ctx.phases, ctx.t0, host=host, updates=updates, packed=packed,
                                  then=lambda chain_done, r: self._after_block(ctx, chain_done, r, agg_box))
         self.last_aggregate = agg_box[0] if contributors else None
@@ -1120,8 +1124,10 @@ class BiscottiEngine:
             # (the kernel is ~0.4 ms of pure latency at the head of the next block's chain).
             if cuda and cfg.mode != "fedsys" and cfg.noising and cfg.num_noisers > 0 and cfg.epsilon > 0:
                 self._vrf_early = (rep.block_hash, self.vrf.launch_dev(rep.block_hash))
+        t_after = time.perf_counter()
         if then is not None:
             then(getattr(self, "_collect_ev", None) if cuda else None, rep)
+            phases["host_after"] = (time.perf_counter() - t_after) * 1e3
         elif cfg.eval_every and (it % cfg.eval_every == 0):
             self._launch_eval(rep)          # empty blocks and FedSys rounds: nothing else is queued behind the block
         # error rates of older blocks have long been read back: publish them (keeps the "Train Error" lines in order)

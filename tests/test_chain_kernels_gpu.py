@@ -43,6 +43,33 @@ def test_vrf_noisers_kernel_matches_host_lottery():
         assert [q for q in out[r].tolist() if q >= 0] == want, (p, out[r], want)
 
 
+def test_wide_vrf_kernel_equals_quad_kernel_and_generic_prove():
+    """One-limb-per-lane Ed25519 scalar multiplication (the head of every block's chain) vs the quad kernel and the
+    generic-field prove(): identical Gamma for every peer, including tiny and near-order scalars."""
+    import ctypes
+
+    n = 67
+    keys = [cp.VRFKey(hashlib.sha256(b"w%d" % i).digest()) for i in range(n)]
+    L = lib()
+    for tag in (b"blk-a", b"blk-b"):
+        msg = hashlib.sha256(tag).digest()
+        bw, bq = cp.BatchedVRF(keys, DEV), cp.BatchedVRF(keys, DEV, kernel="quad4")
+        for edge, val in ((0, 1), (1, 2), (2, 8), (3, 2**252 + 27742317777372353535851937790883648492), (4, 2**255 - 1)):
+            w = np.frombuffer(int(val).to_bytes(32, "little"), dtype=np.int32).copy()
+            bw.scalars[edge] = torch.from_numpy(w).to(DEV)
+            bq.scalars[edge] = torch.from_numpy(w).to(DEV)
+        xw, ew, _ = bw.launch_dev(msg)
+        xq, eq, _ = bq.launch_dev(msg)
+        ew.synchronize()
+        eq.synchronize()
+        gw, gq = np.empty((n, 32), dtype=np.uint8), np.empty((n, 32), dtype=np.uint8)
+        hw, hq = xw.cpu().numpy().copy(), xq.cpu().numpy().copy()
+        L.bsc_ed25519_compress_batch(ctypes.c_void_p(hw.ctypes.data), n, ctypes.c_void_p(gw.ctypes.data))
+        L.bsc_ed25519_compress_batch(ctypes.c_void_p(hq.ctypes.data), n, ctypes.c_void_p(gq.ctypes.data))
+        assert (gw == gq).all()
+        assert bytes(gw[9]) == keys[9].prove(msg)[1][64:]          # proof = c || t || Gamma
+
+
 def test_block_plan_kernel_matches_host():
     rng = np.random.RandomState(3)
     for nk, trigger, ok in ((70, 35, True), (5, 2, True), (140, 70, True), (33, 10, False), (1, 1, True)):
