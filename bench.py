@@ -43,7 +43,8 @@ def cpu_oracle_arm(args):
     from biscotti_b200.protocol.engine import BiscottiEngine
 
     torch.set_num_threads(max(1, os.cpu_count() or 1))
-    cfg = BiscottiConfig(num_nodes=args.peers, dataset=args.dataset, max_iterations=args.steps + args.warmup + 2)
+    cfg = BiscottiConfig(num_nodes=args.peers, dataset=args.dataset, max_iterations=args.steps + args.warmup + 2,
+                         prefetch=False)      # every phase is booked under its own block
     eng = BiscottiEngine(cfg, device="cpu")
     for _ in range(args.warmup):
         eng.step()

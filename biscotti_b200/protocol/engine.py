@@ -410,9 +410,8 @@ class BiscottiEngine:
         # share arrival at the miners: a fixed permutation of the candidates; the approved ones among the first
         # `trigger` of it (in that order) are the block's contributors (main.go:360 + the leader's intersection)
         perm = chain_ops.seeded_perm(chain_ops.seed64(cfg.seed, it, "shares"), nk)
-        rank_of = [0] * nk
-        for r, i in enumerate(perm):
-            rank_of[i] = r
+        rank_of = np.empty(nk, dtype=np.int32)
+        rank_of[perm] = np.arange(nk, dtype=np.int32)
         pl.share_rank = rank_of
         pl.signers = [v for v in verifiers if self.alive[v]]
         # a worker proceeds when it holds >= floor(nv/2) signatures (main.go:1686); every live verifier runs the

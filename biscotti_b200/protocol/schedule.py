@@ -78,6 +78,23 @@ class NativeSchedule:
         self.plan_pinned = [torch.zeros(off, dtype=torch.uint8).pin_memory() for _ in range(4)]
         self.plan_np = [b.numpy() for b in self.plan_pinned]
         self.plan_dev = [torch.zeros(off, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self._plan_views = []
+        for b in self.plan_np:
+            def vw(o, cnt, dt, b=b):
+                return b[o: o + cnt * np.dtype(dt).itemsize].view(dt)
+            self._plan_views.append(dict(stake=vw(self.o_stake, n, np.int32), isw=vw(self.o_isw, n, np.uint8),
+                                         dst=vw(self.o_dst, max(1, P), np.int32), lrow=vw(self.o_lrow, n, np.int32),
+                                         rank=vw(self.o_rank, n, np.int32), ids=vw(self.o_ids, n, np.int32),
+                                         sign=vw(self.o_sign, self.nv, np.int32), xs=vw(self.o_xs, 10, np.int32),
+                                         av=vw(self.o_av, 64, np.uint8), slots=vw(self.o_slots, n, np.int32),
+                                         hash=vw(self.o_hash, 64, np.uint8)))
+        self._pos = np.full(n, -1, dtype=np.int32)
+        self._arange = np.arange(n, dtype=np.int32)
+        self._local_ids = np.asarray(eng.local_ids, dtype=np.int64)
+        self._local_row_of = np.full(n, -1, dtype=np.int32)
+        self._local_row_of[self._local_ids] = np.arange(P, dtype=np.int32)
+        self._slot_of = (np.asarray([eng.comm.slot_of(p) for p in range(n)], dtype=np.int32) if eng.fused
+                         else np.zeros(n, dtype=np.int32))
         # ---- persistent intermediates
         ldh, ldu = eng.ldh, eng.ldu
         B = cfg.batch_size
@@ -354,28 +371,27 @@ class NativeSchedule:
         eng, pl = self.eng, ctx.pl
         par, nk = ctx.par, ctx.nk
         k = self._plan_i = (getattr(self, "_plan_i", -1) + 1) % 4
-        b = self.plan_np[k]
-        n, P = self.n, self.P
-
-        def put(off, arr, dtype):
-            a = np.asarray(arr, dtype=dtype)
-            b[off: off + a.nbytes].view(dtype)[:] = a
-
-        put(self.o_stake, ctx.stake_m, np.int32)
-        put(self.o_isw, ctx.is_worker, np.uint8)
-        kpos = {p: i for i, p in enumerate(pl.krum_set)}
-        put(self.o_dst, [kpos.get(p, -1) for p in eng.local_ids], np.int32)
-        put(self.o_lrow, [eng.local_index.get(p, -1) for p in pl.krum_set], np.int32)
-        put(self.o_rank, pl.share_rank, np.int32)
-        put(self.o_ids, pl.krum_set, np.int32)
-        put(self.o_sign, pl.signers, np.int32)
-        put(self.o_xs, pl.xs, np.int32)
-        av = np.zeros(64, dtype=np.uint8)
+        v = self._plan_views[k]
+        ks = np.asarray(pl.krum_set, dtype=np.int32)
+        v["stake"][:] = ctx.stake_m
+        v["isw"][:] = ctx.is_worker
+        pos = self._pos
+        pos.fill(-1)
+        pos[ks] = self._arange[:nk]
+        v["dst"][: self.P] = pos[self._local_ids]
+        v["lrow"][:nk] = self._local_row_of[ks]
+        v["rank"][:nk] = pl.share_rank
+        v["ids"][:nk] = ks
+        ns = len(pl.signers)
+        if ns:
+            v["sign"][:ns] = pl.signers
+        v["xs"][:] = pl.xs
+        av = v["av"]
+        av.fill(0)
         av[: len(pl.shares_avail)] = pl.shares_avail
-        put(self.o_av, av, np.uint8)
         if eng.fused:
-            put(self.o_slots, [eng.comm.slot_of(p) for p in pl.krum_set], np.int32)
-        put(self.o_hash, np.frombuffer(bytearray(pl.prev_hash), dtype=np.uint8), np.uint8)
+            v["slots"][:nk] = self._slot_of[ks]
+        v["hash"][:32] = np.frombuffer(pl.prev_hash, dtype=np.uint8)
         cl = self.cl[par]
         cl.patch(cl.ix["plan_cp"], 1, self.plan_pinned[k].data_ptr())
         self.run(par, "plan")
