@@ -171,9 +171,22 @@ class FusedComm(NcclComm):
         return (peer // self.per) * self.Sr + (peer % self.per)
 
     # ---- fused Krum -------------------------------------------------------------------------------
-    def krum_fused(self, krum_set, clip: int, epoch: int, rows: torch.Tensor | None = None):
+    def next_epoch(self, kind: str) -> int:
+        """Flag epochs count LAUNCHES, not blocks: a block that is replanned (its looked-ahead front was queued for a world
+        that then changed) runs its kernels a second time, and the second run must not be satisfied by the first run's
+        flags.  Every rank issues the same launches in the same order, so the counters agree without communication."""
+        v = getattr(self, "_epoch_" + kind, 0) + 1
+        setattr(self, "_epoch_" + kind, v)
+        return v
+
+    def krum_fused(self, krum_set, clip: int, epoch: int | None = None, rows: torch.Tensor | None = None):
         """Planes of this block must already be in self.hi / self.lo.  Returns accept (uint8, device).
-        rows: int32 device tensor of the candidates' slots (slot_of), if the caller already uploaded it."""
+        rows: int32 device tensor of the candidates' slots (slot_of), if the caller already uploaded it.
+        epoch: None = the next launch epoch (see next_epoch); explicit values must be strictly increasing."""
+        if epoch is None:
+            epoch = self.next_epoch("krum")
+        else:
+            self._epoch_krum = epoch
         n = len(krum_set)
         dev = self.device
         self._gram_seq = getattr(self, "_gram_seq", 0) + 1   # the Gram kernel publishes SLOT_PLANES itself
@@ -212,12 +225,17 @@ class FusedComm(NcclComm):
         c0 = min(self.nchunk, self.rank * per)
         return c0, min(self.nchunk, c0 + per) - c0
 
-    def secagg_fused(self, xs, avail, precision: int, epoch: int, gate: torch.Tensor | None = None, gate_min: int = 0):
+    def secagg_fused(self, xs, avail, precision: int, epoch: int | None = None, gate: torch.Tensor | None = None,
+                     gate_min: int = 0):
         """self.ypart must hold this rank's partial share sums.  Updates self.w64 / self.w32 on every rank; when the
         kernel retires, every rank's slice has landed here.  gate: device int32 [1] contributor count (no step below
         gate_min).  Share-check counters accumulate in self.bad (the engine reports per-block increments)."""
         from ..ops.secagg import recover_matrix, _RecoverMat
 
+        if epoch is None:
+            epoch = self.next_epoch("secagg")
+        else:
+            self._epoch_secagg = epoch
         c0, nc = self.chunk_range()   # the kernel publishes SLOT_SHARES itself
         rm = recover_matrix(xs)
         use_mat = 1

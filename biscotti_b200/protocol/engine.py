@@ -770,7 +770,7 @@ class BiscottiEngine:
         with self._phase("secagg"):
             if cfg.secure_agg:
                 if self.fused:
-                    self.comm.secagg_fused(pl.xs, pl.shares_avail, cfg.precision, it + 1, gate=ctx.n_con, gate_min=2)
+                    self.comm.secagg_fused(pl.xs, pl.shares_avail, cfg.precision, None, gate=ctx.n_con, gate_min=2)
                 else:
                     Ysum = self._ysum[ctx.par]
                     if self.comm is not None:
@@ -870,17 +870,29 @@ class BiscottiEngine:
         do_eval = bool(cfg.eval_every) and (it % cfg.eval_every == 0)
         if ctx.native:
             ns = self._ns
+            ph = ctx.phases
+            tm = time.perf_counter
+            t0 = tm()
             nxt = self._next_inputs_ready(self._side) if cfg.lookahead else False
             if nxt is not False:
                 ns.queue_local_and_eval(it + 1, rep, do_eval, inputs=nxt)
+                t1 = tm()
                 nctx = self._begin_block_ahead()
+                t2 = tm()
                 if nctx is not None and not nctx.empty and nctx.native:
                     ns.queue_front(nctx)
+                    t3 = tm()
                     ns.queue_commit_and_sign(nctx)
                     self._ctx_next = nctx
+                    ph["h_front"] = (t3 - t2) * 1e3
+                    ph["h_commit_sign"] = (tm() - t3) * 1e3
+                ph["h_local_eval"] = (t1 - t0) * 1e3
+                ph["h_plan"] = (t2 - t1) * 1e3
             elif do_eval:
                 ns.queue_eval(rep, ctx.par)
+            t4 = tm()
             agg_box[0] = ns.queue_witness(ctx)
+            ph["h_witness"] = (tm() - t4) * 1e3
             self._side_done[ctx.par] = ns.side_done[ctx.par]
             self._wevent = ns.side_done[ctx.par]
             return
@@ -987,7 +999,7 @@ class BiscottiEngine:
         cfg = self.cfg
         nk = len(krum_set)
         if self.fused:
-            _, acc = self.comm.krum_fused(krum_set, clip, self.iteration + 1 if epoch is None else epoch, rows=slots_d)
+            _, acc = self.comm.krum_fused(krum_set, clip, None, rows=slots_d)
         elif getattr(self, "_compact", False):
             _, acc, _ = krum_ops.krum(hi[:nk], self.d, clip, hi[:nk], lo[:nk], norms[:nk], impl=cfg.gram_impl)
         else:
@@ -1114,8 +1126,10 @@ class BiscottiEngine:
             nonempty = bool(updates) or packed is not None
             ts = (1 + it if nonempty else 0) if cfg.deterministic_time else -1
             if packed is not None:
+                t_a = time.perf_counter()
                 rep.block_hash = self.chain.append_packed(it, host["w"], packed[0], packed[1], packed[2], self.stake,
                                                           STAKE_UNIT, timestamp=ts)
+                phases["h_append"] = (time.perf_counter() - t_a) * 1e3
             else:
                 rep.block_hash = self.chain.add_block(it, host["w"], list(updates), self.stake, timestamp=ts)
             rep.empty = not nonempty

@@ -413,11 +413,12 @@ class NativeSchedule:
         if eng.fused:
             comm = eng.comm
             comm._gram_seq = getattr(comm, "_gram_seq", 0) + 1
+            epoch = comm.next_epoch("krum")      # per launch, not per block: a replanned block runs this front twice
             cl.patch(ix["gram"], 12, comm._gram_seq)
-            cl.patch(ix["gram"], 13, it + 1)
+            cl.patch(ix["gram"], 13, epoch)
             cl.patch(ix["select"], 4, nk)
             cl.patch(ix["select"], 5, pl.clip)
-            cl.patch(ix["select"], 8, it + 1)
+            cl.patch(ix["select"], 8, epoch)
         else:
             ldg = (nk + 127) // 128 * 128
             ks = gram_ops.ksplit_for(nk, eng.ldh)
@@ -480,7 +481,7 @@ class NativeSchedule:
             cl.patch(ix["recon"], 11, int(use))
             for i in range(64):
                 self.avail_host[i] = pl.shares_avail[i] if i < len(pl.shares_avail) else 0
-            cl.patch(ix["recon"], 19, it + 1)
+            cl.patch(ix["recon"], 19, comm.next_epoch("secagg"))
             if "gather" in ix:
                 comm._cb_seq = getattr(comm, "_cb_seq", 0) + 1
                 buf = comm._cb_seq & 1
