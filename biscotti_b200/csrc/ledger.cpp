@@ -18,6 +18,7 @@
 #include <time.h>
 #include <string>
 #include <vector>
+#include <algorithm>
 #include <map>
 #include <charconv>
 #include "sha256.cuh"
@@ -443,6 +444,92 @@ void bsc_seeded_perm(unsigned long long seed, int n, int* out) {
     out[i] = out[j];
     out[j] = t;
   }
+}
+
+int bsc_lottery_roles(const uint8_t* input, int inlen, const int* stake, int n, int nverifiers, int nminers,
+                      int* verifiers, int* miners, int* nv_out, int* nm_out);
+
+// ---- a block's plan in one call --------------------------------------------------------------------------------
+// Everything about block `it` that follows from the previous hash, the stake map and who is alive - what every peer
+// of the reference derives for itself in prepareForNextIteration / getRoleNames (main.go:486-565, 1059-1187) and what
+// the verifiers' and miners' arrival order decides (krum.go:296-314, 368-388; main.go:360, 1686, 2079):
+//   verifiers (sorted), miners; workers = alive non-committee peers;
+//   krum_set  = the first krum_thresh workers of the seeded "verify" arrival order, sorted by id; with -rs, a
+//               permutation seeded by the iteration keeps num_samples of them;
+//   share_rank[i] = position of candidate i in the seeded "shares" arrival order;
+//   signers   = live verifiers; approved_ok = #signers >= floor(nv/2) and > 0;
+//   shares_avail / xs = which of the S shares live miners hold, and the first ten of them.
+// seed_verify / seed_shares / seed_rs are the 64-bit seeds of the three permutations (ops/chain.py: seed64).
+// Arrays are caller-allocated with room for n entries (64 for the committees, S for shares_avail, 10 for xs).
+// Returns 0; out_counts = {nv, nm, nworkers, nk, ns, approved_ok, enough_shares, clip}.
+int bsc_plan_block(const uint8_t* prev_hash, int hash_len, const int* stake, const uint8_t* alive, int n, int want_v,
+                   int want_m, int krum_thresh, int num_samples, int random_sampling, unsigned long long seed_verify,
+                   unsigned long long seed_shares, unsigned long long seed_rs, double adversary_frac, int shares_per_miner,
+                   int S, int* verifiers, int* miners, int* workers, int* krum_set, int* share_rank, int* signers,
+                   uint8_t* shares_avail, int* xs, uint8_t* is_worker, int* stake_masked, int* out_counts) {
+  std::vector<int> st((size_t)n);
+  long long total = 0;
+  for (int i = 0; i < n; i++) {
+    st[(size_t)i] = alive[i] ? stake[i] : 0;
+    stake_masked[i] = st[(size_t)i];
+    total += st[(size_t)i];
+    is_worker[i] = 0;
+  }
+  for (int k = 0; k < 8; k++) out_counts[k] = 0;
+  for (int s = 0; s < S; s++) shares_avail[s] = 0;
+  if (total == 0) return 0;
+  int nv = 0, nm = 0;
+  bsc_lottery_roles(prev_hash, hash_len, st.data(), n, want_v, want_m, verifiers, miners, &nv, &nm);
+  std::sort(verifiers, verifiers + nv);     // getRoleNames sorts verifiers (main.go:529-565)
+  std::vector<char> committee((size_t)n, 0);
+  for (int i = 0; i < nv; i++) committee[(size_t)verifiers[i]] = 1;
+  for (int i = 0; i < nm; i++) committee[(size_t)miners[i]] = 1;
+  int nw = 0;
+  for (int p = 0; p < n; p++)
+    if (!committee[(size_t)p] && alive[p]) {
+      workers[nw++] = p;
+      is_worker[p] = 1;
+    }
+  out_counts[0] = nv;
+  out_counts[1] = nm;
+  out_counts[2] = nw;
+  if (nv == 0 || nm == 0 || nw == 0) return 0;
+  std::vector<int> perm((size_t)n);
+  bsc_seeded_perm(seed_verify, nw, perm.data());
+  int nk = nw < krum_thresh ? nw : krum_thresh;
+  for (int i = 0; i < nk; i++) krum_set[i] = workers[perm[(size_t)i]];
+  std::sort(krum_set, krum_set + nk);
+  if (random_sampling && nk > num_samples) {
+    std::vector<int> keep((size_t)num_samples);
+    bsc_seeded_perm(seed_rs, nk, perm.data());
+    for (int i = 0; i < num_samples; i++) keep[(size_t)i] = krum_set[perm[(size_t)i]];
+    std::sort(keep.begin(), keep.end());
+    nk = num_samples;
+    for (int i = 0; i < nk; i++) krum_set[i] = keep[(size_t)i];
+  }
+  bsc_seeded_perm(seed_shares, nk, perm.data());
+  for (int r = 0; r < nk; r++) share_rank[perm[(size_t)r]] = r;
+  int ns = 0;
+  for (int i = 0; i < nv; i++)
+    if (alive[verifiers[i]]) signers[ns++] = verifiers[i];
+  int have = 0, live_miners = 0;
+  for (int j = 0; j < nm; j++) {
+    if (!alive[miners[j]]) continue;
+    live_miners++;
+    for (int s = j * shares_per_miner; s < (j + 1) * shares_per_miner && s < S; s++) shares_avail[s] = 1;
+  }
+  int nx = 0;
+  for (int s = 0; s < S; s++)
+    if (shares_avail[s]) {
+      have++;
+      if (nx < 10) xs[nx++] = s;
+    }
+  out_counts[3] = nk;
+  out_counts[4] = ns;
+  out_counts[5] = (ns > 0 && ns >= nv / 2) ? 1 : 0;
+  out_counts[6] = (have >= 10 && live_miners > 0) ? 1 : 0;
+  out_counts[7] = (int)(adversary_frac * (double)nk);     // floor
+  return 0;
 }
 
 // getBlock(it) = Blocks[it+1] with the consistency check (blockchain.go:77-96): index or -1/-2

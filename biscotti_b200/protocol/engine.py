@@ -102,6 +102,8 @@ class _Plan:
     xs: list = field(default_factory=list)
     enough_shares: bool = False
     clip: int = 0
+    stake_m: object = None       # int32 [n]: stake with dead peers zeroed (the lottery's ticket counts)
+    is_worker: object = None     # uint8 [n]
 
 
 @dataclass
@@ -390,38 +392,39 @@ class BiscottiEngine:
     # ------------------------------------------------------------------------------------------
     def _host_plan(self) -> _Plan:
         """Roles, candidate set, arrival orders and availability of a block - functions of the previous hash, the
-        stake map and who is alive, identical on every rank (vrf.go:103-182, krum.go:296-314, 368-388, main.go:360)."""
-        cfg, it = self.cfg, self.iteration
-        verifiers, miners, prev_hash = self.select_roles()
-        committee = set(verifiers) | set(miners)
-        workers = [p for p in range(cfg.num_nodes) if p not in committee and self.alive[p]]
-        pl = _Plan(verifiers, miners, workers, prev_hash)
-        if not verifiers or not miners or not workers:
+        stake map and who is alive, identical on every rank (vrf.go:103-182, krum.go:296-314, 368-388, main.go:360).
+        One native call (ledger.cpp: bsc_plan_block)."""
+        cfg, it, n = self.cfg, self.iteration, self.cfg.num_nodes
+        if not hasattr(self, "_pb"):
+            i32 = lambda k: np.zeros(k, dtype=np.int32)   # noqa: E731
+            self._pb = dict(verifiers=i32(64), miners=i32(64), workers=i32(n), krum=i32(n), rank=i32(n), signers=i32(64),
+                            avail=np.zeros(max(64, self.S), dtype=np.uint8), xs=i32(16), isw=np.zeros(n, dtype=np.uint8),
+                            stake_m=i32(n), counts=i32(8), stake=i32(n), alive=np.zeros(n, dtype=np.uint8))
+            self._pb_ptr = {k: v.ctypes.data_as(ctypes.c_void_p) for k, v in self._pb.items()}
+        pb, pp = self._pb, self._pb_ptr
+        pb["stake"][:] = self.stake
+        pb["alive"][:] = self.alive
+        prev_hash = self.chain.latest_hash()
+        lib().bsc_plan_block(prev_hash, len(prev_hash), pp["stake"], pp["alive"], n, cfg.num_verifiers, cfg.num_miners,
+                             cfg.krum_thresh, cfg.num_samples, int(cfg.random_sampling),
+                             chain_ops.seed64(cfg.seed, it, "verify"), chain_ops.seed64(cfg.seed, it, "shares"),
+                             chain_ops.seed64("rs", it), ctypes.c_double(cfg.krum_adversary_frac), cfg.shares_per_miner,
+                             self.S, pp["verifiers"], pp["miners"], pp["workers"], pp["krum"], pp["rank"], pp["signers"],
+                             pp["avail"], pp["xs"], pp["isw"], pp["stake_m"], pp["counts"])
+        nv, nm, nw, nk, ns, ok, enough, clip = (int(x) for x in pb["counts"])
+        pl = _Plan(pb["verifiers"][:nv].tolist(), pb["miners"][:nm].tolist(), pb["workers"][:nw].tolist(), prev_hash)
+        pl.stake_m, pl.is_worker = pb["stake_m"].copy(), pb["isw"].copy()
+        if nv == 0 or nm == 0 or nw == 0:
             return pl
-        arrival = self._arrival_order(workers, "verify")
-        krum_set = sorted(arrival[: cfg.krum_thresh])          # krum.go:296-314: first thresh arrivals, sorted by id
-        if cfg.random_sampling and len(krum_set) > cfg.num_samples:
-            # -rs (krum.go:310, 368-388): a permutation seeded by the iteration count, keep NUM_SAMPLES of them
-            perm = chain_ops.seeded_perm(chain_ops.seed64("rs", it), len(krum_set))
-            krum_set = sorted(krum_set[i] for i in perm[: cfg.num_samples])
-        pl.krum_set = krum_set
-        nk = len(krum_set)
-        pl.clip = int(math.floor(cfg.krum_adversary_frac * nk))
-        # share arrival at the miners: a fixed permutation of the candidates; the approved ones among the first
-        # `trigger` of it (in that order) are the block's contributors (main.go:360 + the leader's intersection)
-        perm = chain_ops.seeded_perm(chain_ops.seed64(cfg.seed, it, "shares"), nk)
-        rank_of = np.empty(nk, dtype=np.int32)
-        rank_of[perm] = np.arange(nk, dtype=np.int32)
-        pl.share_rank = rank_of
-        pl.signers = [v for v in verifiers if self.alive[v]]
-        # a worker proceeds when it holds >= floor(nv/2) signatures (main.go:1686); every live verifier runs the
-        # same Krum on the same set, so the signature count is the number of live verifiers
-        pl.approved_ok = bool(pl.signers) and len(pl.signers) >= len(verifiers) // 2
+        pl.krum_set = pb["krum"][:nk].tolist()
+        pl.clip = clip
+        pl.share_rank = pb["rank"][:nk].copy()
+        pl.signers = pb["signers"][:ns].tolist()
+        pl.approved_ok = bool(ok)
         pl.trigger = max(1, cfg.num_samples // 2) if cfg.share_trigger == "half" else nk
-        alive_miners = [m for m in miners if self.alive[m]]
-        pl.shares_avail = self._available_shares(miners, alive_miners)
+        pl.shares_avail = pb["avail"][: self.S].tolist()
         pl.xs = [s for s, a in enumerate(pl.shares_avail) if a][:POLY_SIZE]
-        pl.enough_shares = sum(pl.shares_avail) >= POLY_SIZE and len(alive_miners) > 0     # main.go:2079
+        pl.enough_shares = bool(enough)
         return pl
 
     # ------------------------------------------------------------------------------------------
@@ -522,17 +525,12 @@ class BiscottiEngine:
             self._wstream = self._side
         cur = torch.cuda.current_stream(self.device)
         self._main.wait_stream(cur)
-        prev_w = self._side_done[(self.iteration + 1) & 1]
         with torch.cuda.stream(self._main):
             rep = self._step(inputs, next_inputs)
+        # The caller's stream is ordered after the block's chain (its results: weights, ledger) - not after the off-chain
+        # work, which may trail by up to two blocks (the chain itself waits for it, see _queue_chain_front); synchronize()
+        # or close() drains everything.
         cur.wait_stream(self._main)
-        if prev_w is not None:
-            # the previous block's off-chain work had this whole iteration to finish; waiting for it here keeps every
-            # iteration's device timeline (events on the caller's stream) accountable for one block of that work
-            if hasattr(prev_w, "handle"):
-                prev_w.wait(cur)
-            else:
-                cur.wait_event(prev_w)
         return rep
 
     @contextlib.contextmanager
@@ -637,9 +635,7 @@ class BiscottiEngine:
         elif ctx.use_noise:
             ctx.vrf_handle = self.vrf.launch_dev(prev_hash) if cuda else self.vrf.launch(prev_hash)
         # ---- host -> device: the block's plan in one staging copy
-        ctx.stake_m = np.asarray([s_ if a_ else 0 for s_, a_ in zip(self.stake, self.alive)], dtype=np.int32)
-        ctx.is_worker = np.zeros(n, dtype=np.uint8)
-        ctx.is_worker[pl.workers] = 1
+        ctx.stake_m, ctx.is_worker = pl.stake_m, pl.is_worker
         ctx.salt64 = self.run_salt + (prev_hash + b"\0" * 32)[:32]
         ctx.ns = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
         ns = self._native()
@@ -1153,6 +1149,17 @@ class BiscottiEngine:
         self.reports.append(rep)
         self.iteration += 1
         return rep
+
+    def join_streams(self):
+        """Order the caller's current stream after EVERYTHING this engine has queued (chain, off-chain, approval, witness and
+        VRF streams) - what a benchmark records its closing event behind."""
+        if self.device.type != "cuda" or self._main is None:
+            return
+        cur = torch.cuda.current_stream(self.device)
+        for st in (self._main, self._side, self._wit, self.signer.stream if self.signer is not None else None,
+                   getattr(self.vrf, "_dside", None)):
+            if st is not None:
+                cur.wait_stream(st)
 
     def flush_reports(self):
         """Wait for every outstanding error-rate read-back (end of a run, before the logs are parsed)."""

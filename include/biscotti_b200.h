@@ -220,6 +220,9 @@ int bsc_ed25519_scalarmult_quad(const unsigned char* scalars, const unsigned cha
 // same, but leaves the results projective: xyz_out[i] = X, Y, Z as 3 x 10 radix-2^25.5 limbs
 int bsc_ed25519_scalarmult_quad_xyz(const unsigned char* scalars, const unsigned char* hxy, int N, int* xyz_out, void* stream);
 
+// warp-wide latency kernel (one peer per warp, one limb per lane); same contract as the quad _xyz entry point
+int bsc_ed25519_scalarmult_wide_xyz(const unsigned char* scalars, const unsigned char* hxy, int N, int* xyz_out, void* stream);
+
 // host: compress N projective points with a single field inversion (prefix products)
 void bsc_ed25519_compress_batch(const int* xyz, int N, unsigned char* out);
 
@@ -339,6 +342,21 @@ int bsc_chain_append_packed(void* cp, long long iteration, const double* w, int 
 // Deterministic stand-in for a network arrival order: a Fisher-Yates shuffle of 0..n-1 driven by splitmix64
 // from `seed` (unbiased bounded draws by rejection).  Every rank computes the same permutation.
 void bsc_seeded_perm(unsigned long long seed, int n, int* out);
+
+// ---- a block's plan in one call --------------------------------------------------------------------------------
+// Everything about block `it` that follows from the previous hash, the stake map and who is alive - what every peer
+// of the reference derives for itself in prepareForNextIteration / getRoleNames (main.go:486-565, 1059-1187) and what
+// the verifiers' and miners' arrival order decides (krum.go:296-314, 368-388; main.go:360, 1686, 2079):
+//   verifiers (sorted), miners; workers = alive non-committee peers;
+//   krum_set  = the first krum_thresh workers of the seeded "verify" arrival order, sorted by id; with -rs, a
+//               permutation seeded by the iteration keeps num_samples of them;
+//   share_rank[i] = position of candidate i in the seeded "shares" arrival order;
+//   signers   = live verifiers; approved_ok = #signers >= floor(nv/2) and > 0;
+//   shares_avail / xs = which of the S shares live miners hold, and the first ten of them.
+// seed_verify / seed_shares / seed_rs are the 64-bit seeds of the three permutations (ops/chain.py: seed64).
+// Arrays are caller-allocated with room for n entries (64 for the committees, S for shares_avail, 10 for xs).
+// Returns 0; out_counts = {nv, nm, nworkers, nk, ns, approved_ok, enough_shares, clip}.
+int bsc_plan_block(const uint8_t* prev_hash, int hash_len, const int* stake, const uint8_t* alive, int n, int want_v, int want_m, int krum_thresh, int num_samples, int random_sampling, unsigned long long seed_verify, unsigned long long seed_shares, unsigned long long seed_rs, double adversary_frac, int shares_per_miner, int S, int* verifiers, int* miners, int* workers, int* krum_set, int* share_rank, int* signers, uint8_t* shares_avail, int* xs, uint8_t* is_worker, int* stake_masked, int* out_counts);
 
 // getBlock(it) = Blocks[it+1] with the consistency check (blockchain.go:77-96): index or -1/-2
 int bsc_chain_block_index(void* cp, long long iteration);
