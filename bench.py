@@ -342,7 +342,7 @@ def main():
             "chain_hash": eng.chain.latest_hash().hex(),          # same on any N: the ledger does not depend on the sharding
             "host_ms": {k: round(sum(r.phase_ms.get(k, 0.0) for r in eng.reports[-args.steps:]) / args.steps, 4)
                         for k in ("host_queue", "host_wait", "host_tail_py", "block", "h_append", "host_after", "h_local_eval",
-                                  "h_plan", "h_front", "h_commit_sign", "h_witness", "total_host")},
+                                  "h_plan", "h_plan_host", "h_plan_upload", "h_front", "h_commit_sign", "h_witness", "total_host")},
             "step_ms": {"min": step_ms[0], "median": step_ms[len(step_ms) // 2],
                         "p95": step_ms[min(len(step_ms) - 1, int(0.95 * len(step_ms)))], "max": step_ms[-1]},
             "last_block": {"contributors": last.n_contributors, "accepted": last.n_accepted, "krum_set": last.n_krum,

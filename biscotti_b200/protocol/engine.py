@@ -570,6 +570,7 @@ class BiscottiEngine:
             if not ctx.front_queued:
                 # first block, a replanned block, or no lookahead: queue the whole block now
                 self._order_side_after_main()
+                ns.queue_sign_T(ctx)
                 ns.queue_local_and_eval(ctx.it, None, False, inputs=inputs)
                 ns.queue_front(ctx)
                 ns.queue_commit_and_sign(ctx)
@@ -614,7 +615,9 @@ class BiscottiEngine:
                 for p in cut:
                     self.alive[p] = False
                 self._cut = cut
+        t_p0 = time.perf_counter()
         pl = self._host_plan()
+        self._t_plan_host = (time.perf_counter() - t_p0) * 1e3
         krum_set = pl.krum_set
         nk = len(krum_set)
         ctx = _Ctx(it=it, par=it & 1, pl=pl, nk=nk, phases={}, alive=list(self.alive), stake=list(self.stake),
@@ -641,7 +644,10 @@ class BiscottiEngine:
         ns = self._native()
         if ns is not None and nk >= 3:
             ctx.native = True
+            t_u0 = time.perf_counter()
             ns.upload_plan(ctx)
+            ctx.phases["h_plan_host"] = self._t_plan_host
+            ctx.phases["h_plan_upload"] = (time.perf_counter() - t_u0) * 1e3
             return ctx
         kpos = {p: i for i, p in enumerate(krum_set)}
         # Single-rank tcgen05 Krum: noise_mix writes the candidates' bf16 planes and norms compacted and in Krum
@@ -871,19 +877,24 @@ class BiscottiEngine:
             t0 = tm()
             nxt = self._next_inputs_ready(self._side) if cfg.lookahead else False
             if nxt is not False:
-                ns.queue_local_and_eval(it + 1, rep, do_eval, inputs=nxt)
-                t1 = tm()
+                # order: the next block's plan and approvals first (T = v*G is the longest off-chain dependency of the next
+                # tail), then its local step (head of its chain), this block's error rates, the next chain front, commitments
                 nctx = self._begin_block_ahead()
+                t1 = tm()
+                ahead = nctx is not None and not nctx.empty and nctx.native
+                if ahead:
+                    ns.queue_sign_T(nctx)
+                ns.queue_local_and_eval(it + 1, rep, do_eval, inputs=nxt)
                 t2 = tm()
-                if nctx is not None and not nctx.empty and nctx.native:
+                if ahead:
                     ns.queue_front(nctx)
                     t3 = tm()
                     ns.queue_commit_and_sign(nctx)
                     self._ctx_next = nctx
                     ph["h_front"] = (t3 - t2) * 1e3
                     ph["h_commit_sign"] = (tm() - t3) * 1e3
-                ph["h_local_eval"] = (t1 - t0) * 1e3
-                ph["h_plan"] = (t2 - t1) * 1e3
+                ph["h_plan"] = (t1 - t0) * 1e3
+                ph["h_local_eval"] = (t2 - t1) * 1e3
             elif do_eval:
                 ns.queue_eval(rep, ctx.par)
             t4 = tm()

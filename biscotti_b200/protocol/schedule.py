@@ -289,12 +289,14 @@ class NativeSchedule:
             ix["comb"] = cl.add("g1_comb_mul", SIGN, sg._k, 0, sg._comb._table, W_BITS, N_WIN, sg._jac)
             ix["tnorm"] = cl.add("g1_normalize", SIGN, sg._jac, sg._aff, 0)
             ix["tbytes"] = cl.add("g1_affine_to_bytes", SIGN, sg._aff, sg._T, 0)
+            ix["sign_mid"] = cl.n
             cl.wait(SIGN, self.c_ready[par])
             ix["finish"] = cl.add("schnorr_finish_dev", SIGN, sg._T, sg._k, sg.secrets_dev, eng._cbytes[par], lrow_d, 0, sign_d, 0,
                                   pack, pack.stride(0))
             ix["packonly"] = cl.add("pack_commitments", SIGN, eng._cbytes[par], P, pack, pack.stride(0))
             cl.record(SIGN, self.sig_done[par])
         else:
+            ix["sign_mid"] = cl.n
             cl.wait(SIDE, self.c_ready[par])
             ix["packonly"] = cl.add("pack_commitments", SIDE, eng._cbytes[par], P, pack, pack.stride(0))
             cl.record(SIDE, self.sig_done[par])
@@ -435,12 +437,13 @@ class NativeSchedule:
         self.run(par, "front")
         ctx.front_queued = True
 
-    def queue_commit_and_sign(self, ctx):
-        eng, pl = self.eng, ctx.pl
+    def queue_sign_T(self, ctx):
+        """The approvals' nonces and T = v*G need only the plan (chain position, candidates, signers): queued first thing
+        behind the block's tail, they are the longest off-chain dependency of the NEXT tail."""
+        eng = self.eng
         par, nk, it = ctx.par, ctx.nk, ctx.it
         cl = self.cl[par]
         ix = cl.ix
-        self.run(par, "commit")
         if eng.signer is not None:
             ns = ctx.ns
             signing = ns > 0
@@ -458,7 +461,16 @@ class NativeSchedule:
                 cl.patch(ix["tbytes"], 2, N)
                 cl.patch(ix["finish"], 5, nk)
                 cl.patch(ix["finish"], 7, ns)
-        self.run(par, "sign")
+        cl.run(ix["sign0"], ix["sign_mid"])
+
+    def queue_commit_and_sign(self, ctx):
+        """Commitments of the block's updates (side stream), then the approvals' challenge + response, which wait for them."""
+        eng = self.eng
+        par, it = ctx.par, ctx.it
+        cl = self.cl[par]
+        ix = cl.ix
+        self.run(par, "commit")
+        cl.run(ix["sign_mid"], ix["sign1"])
         ctx.pre = {"it": it, "Q": self.Q[par], "chunkC": self.chunkC[par], "cbytes": eng._cbytes[par], "u_ready": None,
                    "c_ready": None, "src": self._last_src, "native": True}
 
