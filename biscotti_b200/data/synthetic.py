@@ -43,7 +43,10 @@ def poisoner_ids(cfg: BiscottiConfig) -> set[int]:
     return {i for i in range(cfg.num_nodes) if i > idx}
 
 
-def make_data(cfg: BiscottiConfig, peer_ids: list[int], device="cpu", noise: float = 1.0, sep: float = 6.0) -> PeerData:
+def make_data(cfg: BiscottiConfig, peer_ids: list[int], device="cpu", noise: float | None = None,
+              sep: float | None = None) -> PeerData:
+    noise = cfg.data_noise if noise is None else noise
+    sep = cfg.data_sep if sep is None else sep
     if getattr(cfg, "data_dir", None):
         from .files import load_peer_data      # real shard files in the reference's layout
 

@@ -108,13 +108,13 @@ def noise_krum(epsilons=(0.01, 0.1, 0.5, 1.0, 2.0, 5.0), peers=100, dataset="mni
 
 
 def poison_heatmap(fractions=(0.5, 0.45, 0.4, 0.3, 0.1), collected=(20, 40, 70), peers=100, dataset="mnist", blocks=100,
-                   device="cuda:0"):
+                   device="cuda:0", **kw):
     """plotHeatMap.py:46-88: max attack rate after block 80 for -po x -ns with -rs=true."""
     rows = []
     for po in fractions:
         for ns in collected:
             cfg = BiscottiConfig(num_nodes=peers, dataset=dataset, max_iterations=blocks, poison_fraction=po,
-                                 perc_samples=ns, random_sampling=True, epsilon=1.0)
+                                 perc_samples=ns, random_sampling=True, epsilon=1.0, **kw)
             eng, reps, dt = _run(cfg, device, blocks, timing=False)
             tail = reps[int(0.8 * len(reps)):]
             rows.append({"poisoners": po, "collected": ns, "max_attack_rate": max(r.attack_rate or 0.0 for r in tail)})
@@ -166,6 +166,31 @@ def churn(period_blocks=(16, 8, 4, 2), peers=50, dataset="mnist", blocks=100, de
         rows.append({"kill_period_blocks": period, "s_per_block": dt / blocks, "final_error": eng.reports[-1].test_error,
                      "empty_blocks": sum(r.empty for r in eng.reports), "rejoin_ok": rejoin_ok})
     return rows
+
+
+def time_to_accuracy(target=0.10, peers=100, dataset="mnist", blocks=102, device="cuda:0", **kw):
+    """The reference's headline learning metric (eval/eval_performance/parseLogs.py:197-210): run MAX_ITERATIONS blocks
+    (102 logged "Train Error" lines), take the wall-clock time of each block's log line, report seconds until the error
+    first drops to `target` and seconds per block.  The engine runs its production schedule (pipelined, not instrumented);
+    a block's time stamp is taken when step() returns, i.e. when the block is on the ledger."""
+    cfg = BiscottiConfig(num_nodes=peers, dataset=dataset, max_iterations=blocks, **kw)
+    eng = _engine(cfg, device)
+    for _ in range(2):                      # warm-up outside the clock: lazy allocations, first-launch costs
+        pass
+    stamps = []
+    t0 = time.perf_counter()
+    for _ in range(blocks):
+        eng.step()
+        stamps.append(time.perf_counter() - t0)
+    eng.flush_reports()
+    errs = [r.test_error for r in eng.reports]
+    hit = next((i for i, e in enumerate(errs) if e is not None and e <= target), None)
+    tail = eng.reports[int(0.8 * blocks):]
+    return {"peers": peers, "dataset": dataset, "blocks": blocks, "s_per_block": stamps[-1] / blocks,
+            "target_error": target, "blocks_to_target": hit, "seconds_to_target": None if hit is None else stamps[hit],
+            "final_error": errs[-1], "error_every_10": [round(e, 4) for e in errs[::10]],
+            "max_attack_rate_after_80pct": max((r.attack_rate or 0.0) for r in tail),
+            "empty_blocks": sum(r.empty for r in eng.reports), "chain_ok": eng.chain.verify()}
 
 
 # ---- closed-form committee analyses (pure Python in the reference as well) ---------------------------
