@@ -175,8 +175,6 @@ def time_to_accuracy(target=0.10, peers=100, dataset="mnist", blocks=102, device
     a block's time stamp is taken when step() returns, i.e. when the block is on the ledger."""
     cfg = BiscottiConfig(num_nodes=peers, dataset=dataset, max_iterations=blocks, **kw)
     eng = _engine(cfg, device)
-    for _ in range(2):                      # warm-up outside the clock: lazy allocations, first-launch costs
-        pass
     stamps = []
     t0 = time.perf_counter()
     for _ in range(blocks):
@@ -186,7 +184,9 @@ def time_to_accuracy(target=0.10, peers=100, dataset="mnist", blocks=102, device
     errs = [r.test_error for r in eng.reports]
     hit = next((i for i, e in enumerate(errs) if e is not None and e <= target), None)
     tail = eng.reports[int(0.8 * blocks):]
-    return {"peers": peers, "dataset": dataset, "blocks": blocks, "s_per_block": stamps[-1] / blocks,
+    # the first two blocks carry one-off costs (buffer allocation, command-list construction): rate over the rest
+    rate = (stamps[-1] - stamps[1]) / max(1, blocks - 2)
+    return {"peers": peers, "dataset": dataset, "blocks": blocks, "s_per_block": rate, "first_two_blocks_s": stamps[1],
             "target_error": target, "blocks_to_target": hit, "seconds_to_target": None if hit is None else stamps[hit],
             "final_error": errs[-1], "error_every_10": [round(e, 4) for e in errs[::10]],
             "max_attack_rate_after_80pct": max((r.attack_rate or 0.0) for r in tail),
