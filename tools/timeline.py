@@ -25,10 +25,12 @@ def main():
     ap.add_argument("--dataset", default="mnist")
     ap.add_argument("--steps", type=int, default=6)
     ap.add_argument("--show", type=int, default=1)
+    ap.add_argument("--sep", type=float, default=None)
     a = ap.parse_args()
-    cfg = BiscottiConfig(num_nodes=a.peers, dataset=a.dataset, max_iterations=a.steps + 20)
+    kw = {} if a.sep is None else {"data_sep": a.sep}
+    cfg = BiscottiConfig(num_nodes=a.peers, dataset=a.dataset, max_iterations=a.steps + 40, **kw)
     eng = BiscottiEngine(cfg, device="cuda:0")
-    for _ in range(5):
+    for _ in range(25):
         eng.step()
     torch.cuda.synchronize()
     from torch.profiler import profile, ProfilerActivity, record_function
