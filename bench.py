@@ -129,6 +129,9 @@ def main():
     ap.add_argument("--dataset", default="mnist")
     ap.add_argument("--comm", default=None, help="fused | nccl (default: fused when available)")
     ap.add_argument("--gram", default="auto")
+    ap.add_argument("--data-sep", type=float, default=None,
+                    help="class separation of the synthetic data (default: the package default, overlapping classes; 6.0 = "
+                         "the well separated blobs round 1 was measured on)")
     ap.add_argument("--profile-phases", action="store_true")
     ap.add_argument("--flush-l2", action="store_true",
                     help="write a 256 MiB buffer between timed iterations (default: off - a block's inputs are far larger "
@@ -159,8 +162,9 @@ def main():
         local = 0
     dev = torch.device("cuda", local)
     L = _native.load()
+    kw = {} if args.data_sep is None else {"data_sep": args.data_sep}
     cfg = BiscottiConfig(num_nodes=args.peers, dataset=args.dataset, max_iterations=args.steps + args.warmup + 8,
-                         gram_impl=args.gram)
+                         gram_impl=args.gram, **kw)
     comm = None
     comm_name = "single"
     if world > 1:
@@ -317,7 +321,7 @@ def main():
             "scaling": "strong",
             "vs_baseline": value / BASELINE_BLOCKS_PER_S,
             "dtype": "fp32 (Krum Gram on tcgen05 as bf16x3 split, fp32 accumulate); int64 shares; BN256 256-bit",
-            "data": "synthetic (Gaussian-blob MNIST-shaped shards, random-init/zero genesis weights)",
+            "data": "synthetic (MNIST-shaped shards: ten overlapping Gaussian classes, data_sep=%g; zero genesis weights)" % cfg.data_sep,
             "impl": "ours",
             "config": {"model": "mnist softmax d=7850", "peers": cfg.num_nodes, "global_batch": cfg.num_nodes * B,
                        "seq_len": None, "parallelism": f"peers sharded over {world} GPU(s), comm={comm_name}",

@@ -186,6 +186,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_g1_sum_rows_dc", c_i, c_p, c_p, c_i, c_p, c_ll, c_p, c_p)
     sig("bsc_g1_sum_rows_jac_dc", c_i, c_p, c_p, c_i, c_p, c_ll, c_p, c_p)
     sig("bsc_seeded_perm", None, c_ull, c_i, c_p)
+    sig("bsc_sum_rows_i64_dc", c_i, c_p, c_i, c_p, c_i, c_p, c_i, c_p, c_p)
     sig("bsc_plan_block", c_i, c_cp, c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_ull, c_ull, c_ull, c_d, c_i, c_i,
         c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p)
     sig("bsc_chain_append_packed", c_i, c_p, c_ll, c_p, c_i, c_p, c_i, c_p, c_ll, c_i, c_p, c_i, c_i, c_ll, c_p)

@@ -89,8 +89,12 @@ class BiscottiConfig:
     msm_window: int | None = None     # fixed-base window bits for the MSM tables (None = largest that fits HBM budget)
     affine_wire: bool = False         # True: normalise every chunk commitment / witness to the 64-byte affine
                                       # wire form (kyber.go:88-168) even though no wire exists between GPUs
-    data_sep: float = 6.0             # synthetic data: distance scale of the class prototypes (6 = well separated; ~2.2
-                                      # gives overlapping classes whose test error needs tens of blocks to pass 0.10)
+    data_sep: float = 3.6             # synthetic data: distance scale of the class prototypes.  3.6 makes the ten classes
+                                      # overlap like MNIST does for a linear model: test error passes 0.10 near block 80 and
+                                      # ends at ~0.09 after 102 blocks (reference: 0.095), and - what matters for timing - the
+                                      # updates keep realistic magnitudes.  With well separated classes (6.0, round 1) the
+                                      # error is 0.002 after a few blocks and most coordinates of an update quantise to
+                                      # zero, which lets the commitment / witness MSMs skip most of their work
     data_noise: float = 1.0           # synthetic data: per-feature Gaussian noise around the prototype
     data_dir: str | None = None       # directory of <dataset><i>.npy shards (data/files.py); None = synthetic data
     prefetch: bool = True             # queue iteration t+1's local step + commitment MSM behind iteration t's

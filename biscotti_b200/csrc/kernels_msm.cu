@@ -57,20 +57,31 @@ __global__ void __launch_bounds__(128) msm_groups_kernel(const long long* __rest
 // k = 1..2^(w-1).  A scalar is recoded into NW signed w-bit digits and each term costs NW mixed
 // additions and no doublings.  With w = 7, NW = 3 (|scalar| < 2^20, the clipped fixed-point range)
 // a 9-term witness drops from ~20 doublings + ~90 additions to 27 additions.
-HD int64_t table_max_mag(int w, int nw) { return (int64_t)1 << (w * nw - 1); }
+// Two-width tables.  Clipped fixed-point updates are small (|u * 10^4| < 2^12 for ~99 % of the coordinates of a softmax
+// step, a handful of bits more for the rest), so the first window should be as wide as the memory budget allows - one
+// mixed addition per term - and the windows above it only have to cover the rare large values and can be narrow.
+// `nw` carries both numbers: low byte = window count, next byte = width of windows 1.. (0 = same width as window 0).
+HD int tw_count(int nw) { return nw & 0xff; }
+HD int tw_w1(int w, int nw) { const int w1 = (nw >> 8) & 0xff; return w1 ? w1 : w; }
+HD int tw_half(int w, int nw, int i) { return 1 << ((i == 0 ? w : tw_w1(w, nw)) - 1); }
+HD long long tw_offset(int w, int nw, int i) { return i == 0 ? 0 : (long long)tw_half(w, nw, 0) + (long long)(i - 1) * tw_half(w, nw, 1); }
+HD long long tw_entries(int w, int nw) { return tw_offset(w, nw, tw_count(nw)); }
+HD int tw_shift(int w, int nw, int i) { return i == 0 ? 0 : w + (i - 1) * tw_w1(w, nw); }
+HD int64_t table_max_mag(int w, int nw) { return (int64_t)1 << (tw_shift(w, nw, tw_count(nw)) - 1); }
 
 // one thread per (base, window): emits the 2^(w-1) multiples as Jacobian points (normalised afterwards)
 __global__ void __launch_bounds__(128) msm_table_build_kernel(const G1Affine* __restrict__ bases, long long nb, int w,
                                                               int nw, G1Jac* __restrict__ out) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nb * nw) return;
-  const long long b = t / nw;
-  const int i = (int)(t % nw);
-  const int H = 1 << (w - 1);
+  const int cnt = tw_count(nw);
+  if (t >= nb * cnt) return;
+  const long long b = t / cnt;
+  const int i = (int)(t % cnt);
+  const int H = tw_half(w, nw, i);
   G1Jac J = g1j_from_affine(bases[b]);
-  for (int k = 0; k < w * i; k++) J = g1j_dbl(J);
+  for (int k = 0; k < tw_shift(w, nw, i); k++) J = g1j_dbl(J);
   G1Jac acc = J;
-  G1Jac* dst = out + (size_t)t * H;
+  G1Jac* dst = out + (size_t)b * tw_entries(w, nw) + tw_offset(w, nw, i);
   dst[0] = acc;
   for (int k = 1; k < H; k++) {
     acc = g1j_add(acc, J);
@@ -81,8 +92,8 @@ __global__ void __launch_bounds__(128) msm_table_build_kernel(const G1Affine* __
 template <int TMAX>
 HDN inline G1Jac g1_table_msm(const G1Affine* __restrict__ table, long long first_base, const int64_t* s, int T, int w,
                               int nw) {
-  const int H = 1 << (w - 1);
-  const uint64_t mask = ((uint64_t)1 << w) - 1;
+  const int cnt = tw_count(nw);
+  const long long per_base = tw_entries(w, nw);
   const uint64_t lim = (uint64_t)table_max_mag(w, nw);
   bool overflow = false;
   for (int t = 0; t < T; t++) {
@@ -94,7 +105,7 @@ HDN inline G1Jac g1_table_msm(const G1Affine* __restrict__ table, long long firs
     G1Affine b[TMAX];
     uint64_t maxmag = 0;
     for (int t = 0; t < T; t++) {
-      b[t] = table[((size_t)(first_base + t) * nw) * H];
+      b[t] = table[(size_t)(first_base + t) * per_base];
       maxmag |= s[t] < 0 ? (uint64_t)0 - (uint64_t)s[t] : (uint64_t)s[t];
     }
     int nbits = 0;
@@ -105,18 +116,20 @@ HDN inline G1Jac g1_table_msm(const G1Affine* __restrict__ table, long long firs
   for (int t = 0; t < T; t++) {
     const bool neg = s[t] < 0;
     uint64_t m = neg ? (uint64_t)0 - (uint64_t)s[t] : (uint64_t)s[t];
-    const G1Affine* tb = table + ((size_t)(first_base + t) * nw) * H;
-    for (int i = 0; i < nw && m != 0; i++) {
-      uint64_t dgt = m & mask;
-      m >>= w;
+    const G1Affine* tb = table + (size_t)(first_base + t) * per_base;
+    for (int i = 0; i < cnt && m != 0; i++) {
+      const int wi = i == 0 ? w : tw_w1(w, nw);
+      const uint64_t H = (uint64_t)1 << (wi - 1);
+      uint64_t dgt = m & (((uint64_t)1 << wi) - 1);
+      m >>= wi;
       bool dneg = neg;
-      if (dgt > (uint64_t)H) {
-        dgt = ((uint64_t)1 << w) - dgt;
+      if (dgt > H) {
+        dgt = ((uint64_t)1 << wi) - dgt;
         dneg = !neg;
         m += 1;
       }
       if (dgt) {
-        G1Affine pt = tb[(size_t)i * H + (dgt - 1)];
+        G1Affine pt = tb[tw_offset(w, nw, i) + (long long)(dgt - 1)];
         if (dneg) pt.y = fe_neg(pt.y);
         acc = g1j_add_affine(acc, pt);
       }
@@ -315,8 +328,8 @@ int bsc_msm_groups(const long long* Q, int ldq, const int* sel, int P, const int
 }
 
 int bsc_msm_table_build(const void* bases_affine, long long nb, int w, int nw, void* out_jac, void* stream) {
-  if (w < 2 || w > 14 || nw < 1) return -1;
-  const long long n = nb * nw;
+  if (w < 2 || w > 14 || tw_count(nw) < 1 || tw_w1(w, nw) > 14) return -1;
+  const long long n = nb * tw_count(nw);
   if (n == 0) return 0;
   msm_table_build_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const G1Affine*)bases_affine,
                                                                                        nb, w, nw, (G1Jac*)out_jac);
@@ -325,15 +338,18 @@ int bsc_msm_table_build(const void* bases_affine, long long nb, int w, int nw, v
 void bsc_msm_table_build_host(const void* bases_affine, long long nb, int w, int nw, void* out_jac) {
   const G1Affine* bases = (const G1Affine*)bases_affine;
   G1Jac* out = (G1Jac*)out_jac;
-  const int H = 1 << (w - 1);
-  for (long long t = 0; t < nb * nw; t++) {
-    G1Jac J = g1j_from_affine(bases[t / nw]);
-    for (int k = 0; k < w * (int)(t % nw); k++) J = g1j_dbl(J);
+  const int cnt = tw_count(nw);
+  for (long long t = 0; t < nb * cnt; t++) {
+    const int i = (int)(t % cnt);
+    const int H = tw_half(w, nw, i);
+    G1Jac J = g1j_from_affine(bases[t / cnt]);
+    for (int k = 0; k < tw_shift(w, nw, i); k++) J = g1j_dbl(J);
     G1Jac acc = J;
-    out[(size_t)t * H] = acc;
+    G1Jac* dst = out + (size_t)(t / cnt) * tw_entries(w, nw) + tw_offset(w, nw, i);
+    dst[0] = acc;
     for (int k = 1; k < H; k++) {
       acc = g1j_add(acc, J);
-      out[(size_t)t * H + k] = acc;
+      dst[k] = acc;
     }
   }
 }

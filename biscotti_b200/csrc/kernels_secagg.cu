@@ -159,6 +159,20 @@ __global__ void __launch_bounds__(256) reconstruct_mat_kernel(const long long* _
   }
 }
 
+// Column sums of the selected rows of the quantised updates: out[k] = sum_{q < nsel} Q[sel[q]][k].  The miners' homomorphic
+// aggregate of the contributors' commitments / witnesses (kyber.go:244-287) is the commitment / witness of this summed
+// polynomial (same group elements: sum_p sum_j a_pj T_j = sum_j (sum_p a_pj) T_j), so it costs one more MSM row instead of
+// a point addition per contributor and group.
+__global__ void sum_rows_i64_kernel(const long long* __restrict__ Q, int ldq, const int* __restrict__ sel, int nsel,
+                                    const int* __restrict__ nsel_dev, int ncols, long long* __restrict__ out) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= ncols) return;
+  if (nsel_dev) nsel = min(nsel, *nsel_dev);
+  long long acc = 0;
+  for (int q = 0; q < nsel; q++) acc += Q[(size_t)sel[q] * ldq + k];
+  out[k] = acc;
+}
+
 // Plain aggregation (-sa=false, DistSys/honest.go:346-388; also the FedSys server,
 // FedSys/honest.go:311-337): w += sum of selected deltas, summed in fixed order in fp64.
 __global__ void plain_sum_step_kernel(const float* __restrict__ U, const int* __restrict__ sel, int nsel, int d,
@@ -252,6 +266,13 @@ int bsc_recover_mat_host(const long long* Ysum, const void* rm, int S, int nc, l
   return badc;
 }
 int bsc_recover_mat_sizeof() { return (int)sizeof(RecoverMat); }
+
+int bsc_sum_rows_i64_dc(const long long* Q, int ldq, const int* sel, int nsel, const int* nsel_dev, int ncols,
+                        long long* out, void* stream) {
+  if (ncols <= 0) return 0;
+  sum_rows_i64_kernel<<<(ncols + 255) / 256, 256, 0, (cudaStream_t)stream>>>(Q, ldq, sel, nsel, nsel_dev, ncols, out);
+  return finish_launch("sum_rows_i64");
+}
 
 int bsc_plain_sum_step_dc(const float* U, const int* sel, int nsel, const int* nsel_dev, int d, int ldu, double* w64,
                           float* w32, double* dsum, const int* gate, int gate_min, void* stream) {

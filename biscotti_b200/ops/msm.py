@@ -30,7 +30,8 @@ class CommitmentEngine:
     """Holds the SRS and the witness base table for one model dimension and runs the MSM kernels."""
 
     def __init__(self, d: int, total_shares: int, tau: int = 2, device="cpu", srs_bytes: bytes | None = None,
-                 window: int | None = None, max_scalar_bits: int = 20, table_budget_bytes: int | None = None):
+                 window: int | None = None, max_scalar_bits: int = 20, table_budget_bytes: int | None = None,
+                 window2: int | None = None):
         self.d, self.S, self.device = d, total_shares, torch.device(device)
         self.nchunk = nchunks(d)
         self.dpad = self.nchunk * POLY_SIZE
@@ -56,12 +57,20 @@ class CommitmentEngine:
         self.w_bidx = (cs * (POLY_SIZE - 1)).to(self.device)               # T[c, s, 0..8]
         self.wtable = self._build_witness_table()
         # ---- fixed-base window tables (device path; window=0 disables them)
-        self.w = self.nw = 0
+        # Layout per base: window 0 has 2^(w-1) entries, the nw-1 windows above it 2^(w1-1) each (see kernels_msm.cu,
+        # "two-width tables").  self.nw carries (count | w1 << 8) for the kernels; self.nwin / self.w1 are the plain values.
+        self.w = self.nw = self.nwin = self.w1 = 0
         self.c_table = self.w_table = None
         nbases = self.dpad + self.wtable.shape[0]
+        need = max_scalar_bits + 1
 
-        def table_bytes(w):
-            return nbases * (-(-(max_scalar_bits + 1) // w)) * (1 << (w - 1)) * 64
+        def layout(w0, w1=None):
+            """(nwin, w1, entries per base) for a first window of w0 bits; w1=None: uniform windows."""
+            if w1 is None:
+                nwin = -(-need // w0)
+                return nwin, 0, nwin * (1 << (w0 - 1))
+            nwin = 1 + max(0, -(-(need - w0) // w1))
+            return nwin, w1, (1 << (w0 - 1)) + (nwin - 1) * (1 << (w1 - 1))
 
         # HBM budget of the window tables: half of the device (90 GB of a B200's 180 GB) unless told otherwise
         if table_budget_bytes is None:
@@ -74,17 +83,34 @@ class CommitmentEngine:
         env_w = os.environ.get("BISCOTTI_MSM_WINDOW")
         if env_w and window is None:
             window = int(env_w)
+        choice = None
         if window is None:
-            # fewest windows (= additions per term), then the widest such window, whose tables fit the budget:
-            # 12 or 11 bits -> 2 windows, 7 -> 3, 6 -> 4, ...  (MNIST-sized models take w = 12: 41 GB of HBM, 18
-            # instead of 27 additions per witness and mostly-zero high digits; the CIFAR CNN lands on w = 7, 64 GB)
-            window = 0
+            # Widest first window that fits the budget, with narrow windows above it: ~99 % of a clipped update's fixed-point
+            # coordinates are below 2^12, so a 13-bit first window makes a term ONE mixed addition; the rare larger values
+            # take a second addition from an 8-bit window.  Fall back to uniform windows when even that does not fit.
             if self.device.type == "cuda":
-                window = next((w for w in (12, 11, 7, 6, 5, 4, 3) if table_bytes(w) <= table_budget_bytes), 3)
-        if window:
-            while window > 2 and table_bytes(window) > table_budget_bytes:
-                window -= 1
-            self.w, self.nw = window, -(-(max_scalar_bits + 1) // window)
+                for w0, w1 in ((13, 8), (12, 9), (11, 10)):
+                    lay = layout(w0, w1)
+                    if nbases * lay[2] * 64 <= table_budget_bytes:
+                        choice = (w0,) + lay
+                        break
+                if choice is None:
+                    for w0 in (7, 6, 5, 4, 3):
+                        lay = layout(w0)
+                        if nbases * lay[2] * 64 <= table_budget_bytes or w0 == 3:
+                            choice = (w0,) + lay
+                            break
+        elif window and window2:
+            choice = (window,) + layout(window, window2)
+        elif window:
+            w0 = window
+            while w0 > 2 and nbases * layout(w0)[2] * 64 > table_budget_bytes:
+                w0 -= 1
+            choice = (w0,) + layout(w0)
+        if choice is not None:
+            self.w, self.nwin, self.w1, self.per_base = choice
+            self.nw = self.nwin | (self.w1 << 8)
+            self.table_bytes = nbases * self.per_base * 64
             self.c_table = self._build_window_table(self.bases)
             self.w_table = self._build_window_table(self.wtable)
 
@@ -132,8 +158,7 @@ class CommitmentEngine:
         """table[b][i][k-1] = k * 2^(w*i) * B_b (affine), built in chunks to bound the Jacobian scratch."""
         L = lib()
         nb = bases_aff.shape[0]
-        H = 1 << (self.w - 1)
-        per = self.nw * H
+        per = self.per_base
         table = torch.empty(nb * per, AFF, dtype=torch.int32, device=self.device)
         chunk = max(1, (1 << 23) // per)
         for b0 in range(0, nb, chunk):
@@ -310,6 +335,22 @@ class CommitmentEngine:
             self._g2_srs = (g2, pairing.g2_mul(g2, self.tau))
         base = self.srs_bytes[64 * POLY_SIZE * chunk: 64 * POLY_SIZE * chunk + 64]
         return pairing.verify_secret(chunk_commit, witness, s - 10, y, self._g2_srs[0], self._g2_srs[1], base=base)
+
+    def aggregate_by_scalars(self, Q: torch.Tensor, sel: torch.Tensor, count=None, affine: bool = False):
+        """The miners' homomorphic aggregate over the contributing peers (kyber.go:244-287) computed from the SUMMED
+        polynomial: sum_p C[p] and sum_p W[p] are the chunk commitments / witnesses of sum_p Q[p] (same group elements),
+        so the aggregation is one more MSM row instead of one point addition per contributor and group.
+        Returns (aggC [nchunk, 16|24], aggW [nchunk, S, 16|24]); count: int32 [1] device-resident live length of sel."""
+        if Q.is_cuda:
+            aggQ = torch.empty(1, Q.shape[1], dtype=torch.int64, device=Q.device)
+            check(lib().bsc_sum_rows_i64_dc(ptr(Q), Q.stride(0), ptr(sel), sel.numel(), ptr(count), Q.shape[1], ptr(aggQ),
+                                            stream(Q.device)), "sum_rows_i64")
+        else:
+            rows = sel if count is None else sel[: int(count[0])]
+            aggQ = Q[rows.long()].sum(dim=0, keepdim=True) if rows.numel() else torch.zeros(1, Q.shape[1], dtype=torch.int64)
+        aggC = self.chunk_commitments(aggQ, affine=affine)[0]
+        aggW = self.witnesses(aggQ, affine=affine)[0]
+        return aggC, aggW
 
     def aggregate(self, pts: torch.Tensor, sel: torch.Tensor, affine: bool = True, count=None) -> torch.Tensor:
         """Miner-side homomorphic add over contributing peers: pts [P, G..., 16|24] -> [G..., 16|24].

@@ -938,9 +938,8 @@ class BiscottiEngine:
                     W = self.commit.witnesses(pre["Q"], pout["appr_local"], affine=cfg.affine_wire, count=ctx.n_la,
                                               max_rows=min(self.P, ctx.nk))
                 with self._phase("miner_aggregate"):
-                    aggW = self.commit.aggregate(W, pout["csel"], affine=cfg.affine_wire, count=ctx.n_lc)
-                    aggC = self.commit.aggregate(pre["chunkC"], pout["sel"], affine=cfg.affine_wire, count=ctx.n_lc)
-                    agg_box[0] = (aggC, aggW)
+                    agg_box[0] = self.commit.aggregate_by_scalars(pre["Q"], pout["sel"], count=ctx.n_lc,
+                                                                  affine=cfg.affine_wire)
             if self.pipelined:
                 ev = torch.cuda.Event()
                 ev.record()

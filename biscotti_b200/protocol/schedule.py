@@ -119,6 +119,7 @@ class NativeSchedule:
         self.fullA = torch.zeros(P, AFF, **i32)
         self.wrows = min(P, cfg.krum_thresh)
         self.W = torch.zeros(self.wrows, C.nchunk * eng.S, JAC, **i32)
+        self.aggQ = torch.zeros(1, C.dpad, dtype=torch.int64, device=dev)
         self.aggW = [torch.zeros(C.nchunk * eng.S, JAC, **i32) for _ in range(2)]
         self.aggC = [torch.zeros(C.nchunk, JAC, **i32) for _ in range(2)]
         if eng.signer is not None:
@@ -311,8 +312,13 @@ class NativeSchedule:
         cl.wait(WIT, self.c_ready[par])         # Q and chunkC of this block
         ix["wit"] = cl.add("msm_table_dc", WIT, Q, Q.stride(0), pout["appr_local"], self.wrows, n_la, C.w_sidx, C.w_bidx, None,
                            G, POLY_SIZE - 1, C.w_table, C.w, C.nw, self.W, G)
-        cl.add("g1_sum_rows_jac_dc", WIT, self.W, pout["csel"], pout["csel"].numel(), n_lc, G, self.aggW[par])
-        cl.add("g1_sum_rows_jac_dc", WIT, chunkC, pout["sel"], pout["sel"].numel(), n_lc, C.nchunk, self.aggC[par])
+        # the miners' aggregate = commitment / witnesses of the contributors' SUMMED polynomial (CommitmentEngine.
+        # aggregate_by_scalars): one more MSM row each instead of a point addition per contributor and group
+        cl.add("sum_rows_i64_dc", WIT, Q, Q.stride(0), pout["sel"], pout["sel"].numel(), n_lc, C.dpad, self.aggQ)
+        cl.add("msm_table_dc", WIT, self.aggQ, C.dpad, None, 1, None, C.c_sidx, C.c_bidx, None, C.nchunk, POLY_SIZE, C.c_table,
+               C.w, C.nw, self.aggC[par], C.nchunk)
+        cl.add("msm_table_dc", WIT, self.aggQ, C.dpad, None, 1, None, C.w_sidx, C.w_bidx, None, G, POLY_SIZE - 1, C.w_table,
+               C.w, C.nw, self.aggW[par], G)
         cl.record(WIT, self.side_done[par])
         ix["wit1"] = cl.n
         cl.ix = ix

@@ -113,6 +113,8 @@ int bsc_recover_mat_host(const long long* Ysum, const void* rm, int S, int nc, l
 
 int bsc_recover_mat_sizeof();
 
+int bsc_sum_rows_i64_dc(const long long* Q, int ldq, const int* sel, int nsel, const int* nsel_dev, int ncols, long long* out, void* stream);
+
 int bsc_plain_sum_step_dc(const float* U, const int* sel, int nsel, const int* nsel_dev, int d, int ldu, double* w64, float* w32, double* dsum, const int* gate, int gate_min, void* stream);
 
 int bsc_plain_sum_step(const float* U, const int* sel, int nsel, int d, int ldu, double* w64, float* w32, double* dsum, void* stream);

@@ -9,7 +9,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _cfg(**kw):
-    base = dict(num_nodes=30, dataset="mnist", max_iterations=4, shard_size=100, test_size=500, msm_window=7)
+    base = dict(num_nodes=30, dataset="mnist", max_iterations=4, shard_size=100, test_size=500, msm_window=7, data_sep=6.0)
     base.update(kw)
     return BiscottiConfig(**base)
 

@@ -60,7 +60,8 @@ def test_fused_krum_and_secagg_world1_match_unfused_kernels():
 
 
 def test_engine_with_fused_comm_world1_is_deterministic():
-    cfg = BiscottiConfig(num_nodes=30, dataset="mnist", max_iterations=3, shard_size=100, test_size=300, msm_window=7)
+    cfg = BiscottiConfig(num_nodes=30, dataset="mnist", max_iterations=3, shard_size=100, test_size=300, msm_window=7,
+                         data_sep=6.0)
     a = BiscottiEngine(cfg, device=DEV, comm=FusedComm(0, 1, DEV, cfg))
     b = BiscottiEngine(cfg, device=DEV, comm=FusedComm(0, 1, DEV, cfg))
     ra, rb = a.run(), b.run()

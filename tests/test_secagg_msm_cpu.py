@@ -150,3 +150,27 @@ def test_verify_commitment_and_share_opening_helpers():
         off = 64 * (c * S + s)
         assert eng.verify_share_trapdoor(Cb[64 * c:64 * c + 64], Wb[off:off + 64], c, s, int(Y[0, c, s]))
         assert not eng.verify_share_trapdoor(Cb[64 * c:64 * c + 64], Wb[off:off + 64], c, s, int(Y[0, c, s]) + 1)
+
+
+def test_two_width_window_tables_match_the_plain_msm():
+    """Fixed-base tables with a wide first window and narrow upper windows (kernels_msm.cu: tw_*) against the table-free
+    MSM, on scalars that exercise one window, both windows, the signed-digit carry and the out-of-range fallback."""
+    import torch
+
+    from biscotti_b200.ops import secagg
+    from biscotti_b200.ops.msm import CommitmentEngine
+
+    d, S = 30, 21
+    plain = CommitmentEngine(d, S, tau=2, device="cpu", window=0)
+    two = CommitmentEngine(d, S, tau=2, device="cpu", window=6, window2=4, max_scalar_bits=13)
+    assert two.nwin == 3 and two.w1 == 4 and two.per_base == 32 + 2 * 8
+    Q = torch.zeros(4, plain.dpad, dtype=torch.int64)
+    g = torch.Generator().manual_seed(3)
+    Q[0] = torch.randint(-31, 32, (plain.dpad,), generator=g)                    # first window only
+    Q[1] = torch.randint(-8000, 8000, (plain.dpad,), generator=g)                # all windows
+    Q[2, :12] = torch.tensor([32, -32, 33, -33, 31, 511, 512, -512, 8191, -8191, 8192, 1 << 20])   # carries, range edge, fallback
+    Q[3] = torch.randint(-(1 << 22), 1 << 22, (plain.dpad,), generator=g)        # mostly out of range: Straus fallback
+    Ca, Cb = plain.chunk_commitments(Q), two.chunk_commitments(Q)
+    assert plain.to_bytes(Ca) == two.to_bytes(Cb)
+    Wa, Wb = plain.witnesses(Q), two.witnesses(Q)
+    assert plain.to_bytes(Wa) == two.to_bytes(Wb)

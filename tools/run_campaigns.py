@@ -6,7 +6,7 @@
   * poisoning heat-map rows with -rs=true (plotHeatMap.py:46-88)
   * CIFAR-shaped CNN, 200 peers: does the test error fall over 50 blocks
 
-The synthetic classes overlap (`data_sep`, default here 2.2) so that the error needs tens of blocks to pass 0.10."""
+The synthetic classes overlap (`data_sep` = 3.6, the package default) so that the error needs tens of blocks to pass 0.10."""
 import argparse
 import json
 import os
@@ -17,7 +17,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from biscotti_b200.eval import experiments as ex  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--sep", type=float, nargs="*", default=[2.2])
+ap.add_argument("--sep", type=float, nargs="*", default=[3.6])
 ap.add_argument("--what", nargs="*", default=["tta", "poison", "heatmap", "cifar"])
 ap.add_argument("--blocks", type=int, default=102)
 a = ap.parse_args()
