@@ -148,9 +148,12 @@ __global__ void __launch_bounds__(128, MINB) msm_table_kernel(const long long* _
                                                         G1Jac* __restrict__ out, long long ostride_p,
                                                         const int* __restrict__ pcount) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // Row count decided on the device (block_plan_kernel); P is only its upper bound (the grid is sized for it).  The live
+  // count, not P, is the stride of the (group, row) mapping: warps stay full of live rows and whole CTAs retire at once,
+  // instead of every warp carrying P - count idle lanes.
+  if (pcount) P = min(P, *pcount);
   if (i >= (long long)G * P) return;
   const int g = (int)(i / P), p = (int)(i % P);
-  if (pcount && p >= *pcount) return;   // row count decided on the device (block_plan_kernel); P is its upper bound
   const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
   // scalars are read in place (twice: range check, then digits) rather than staged in registers
   out[(size_t)p * ostride_p + (og ? og[g] : g)] = g1_table_msm<MSM_TMAX>(table, bidx[g], (const int64_t*)row, T, w, nw);
