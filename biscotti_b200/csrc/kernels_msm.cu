@@ -153,7 +153,10 @@ __global__ void __launch_bounds__(128, MINB) msm_table_kernel(const long long* _
   // instead of every warp carrying P - count idle lanes.
   if (pcount) P = min(P, *pcount);
   if (i >= (long long)G * P) return;
-  const int g = (int)(i / P), p = (int)(i % P);
+  // Groups vary fastest along a warp.  The 21 witnesses of one (peer, chunk) share their nine scalars, and consecutive
+  // chunks of one peer share the class row whose gradient is (or is not) negligible - so the lanes of a warp agree on
+  // which digits are zero and a zero digit really skips its addition, instead of idling next to 31 other peers' digits.
+  const int p = (int)(i / G), g = (int)(i % G);
   const long long* row = Q + (size_t)(sel ? sel[p] : p) * ldq + sidx[g];
   // scalars are read in place (twice: range check, then digits) rather than staged in registers
   out[(size_t)p * ostride_p + (og ? og[g] : g)] = g1_table_msm<MSM_TMAX>(table, bidx[g], (const int64_t*)row, T, w, nw);
