@@ -224,11 +224,21 @@ def main():
 
     # ---------------- end-to-end arm: public API, minibatches from pinned host memory ------------
     P, B, F = eng.P, cfg.batch_size, cfg.spec.n_features
-    hostX = torch.randn(max(1, P), B, F).pin_memory()
-    hosty = torch.randint(0, cfg.spec.n_classes, (max(1, P), B), dtype=torch.int32).pin_memory()
-    # draw host minibatches from the same synthetic distribution as the shards
-    hostX.copy_(eng.data.X[:, :B].cpu()) if P else None
-    hosty.copy_(eng.data.y[:, :B].cpu()) if P else None
+    # A ring of distinct host minibatches cut from the peers' shards (one per step, cycling): feeding the SAME minibatch
+    # every step would let the model fit it, the updates would quantise to zero and the MSMs would have nothing to do.
+    RING = max(1, min(32, cfg.shard_size // B))
+    hostXs, hostys = [], []
+    Xc, yc = eng.data.X.cpu(), eng.data.y.cpu()
+    for r in range(RING):
+        hx = torch.empty(max(1, P), B, F).pin_memory()
+        hy = torch.empty(max(1, P), B, dtype=torch.int32).pin_memory()
+        if P:
+            hx.copy_(Xc[:, r * B: (r + 1) * B])
+            hy.copy_(yc[:, r * B: (r + 1) * B])
+        hostXs.append(hx)
+        hostys.append(hy)
+    hostX, hosty = hostXs[0], hostys[0]
+    feed_i = [0]
     # Optional double-buffered input pipeline (--e2e-pipeline 1): while step i runs, step i+1's minibatch is copied from pinned
     # host memory on a copy stream and handed to the engine as `next_inputs`, which lets it queue that step's local
     # pass behind this step's aggregation.  Every step's H2D copy is inside the timed region either way.
@@ -238,9 +248,11 @@ def main():
 
     def h2d(slot):
         ev = torch.cuda.Event()
+        k = feed_i[0] % RING
+        feed_i[0] += 1
         with torch.cuda.stream(copy_stream):             # slot's previous reader finished a full step ago
-            bufs[slot][0].copy_(hostX, non_blocking=True)
-            bufs[slot][1].copy_(hosty, non_blocking=True)
+            bufs[slot][0].copy_(hostXs[k], non_blocking=True)
+            bufs[slot][1].copy_(hostys[k], non_blocking=True)
             ev.record()
         return (bufs[slot][0], bufs[slot][1], ev)
 
@@ -261,8 +273,10 @@ def main():
         if not args.e2e_pipeline:
             dX, dy = bufs[0]
             for _ in range(nsteps):
-                dX.copy_(hostX, non_blocking=True)               # H2D of this step's inputs
-                dy.copy_(hosty, non_blocking=True)
+                k = feed_i[0] % RING
+                feed_i[0] += 1
+                dX.copy_(hostXs[k], non_blocking=True)           # H2D of this step's inputs
+                dy.copy_(hostys[k], non_blocking=True)
                 rep = eng.step((dX, dy))
                 note(rep)
             return

@@ -189,7 +189,7 @@ class BiscottiEngine:
         self._next_inputs, self._fed_inputs = None, False
         self._eval_waiting: list = []           # reports whose error rates are still being read back
         self._vrf_early = None
-        self._main = self._side = self._wit = None      # chain / off-chain / witness streams of a pipelined GPU engine
+        self._main = self._side = self._wit = self._agg = None   # chain / off-chain / witness / aggregation streams (pipelined GPU)
         self._wstream = None                    # alias of _side, kept for callers that look for the witness stream
         self._wevent = None
         self._side_done = [None, None]          # per block parity: off-chain work of that block has finished
@@ -522,6 +522,7 @@ class BiscottiEngine:
             self._main = torch.cuda.Stream(self.device, priority=-3)
             self._side = torch.cuda.Stream(self.device, priority=-1)
             self._wit = torch.cuda.Stream(self.device, priority=0)
+            self._agg = torch.cuda.Stream(self.device, priority=-1)
             self._wstream = self._side
         cur = torch.cuda.current_stream(self.device)
         self._main.wait_stream(cur)
@@ -900,6 +901,7 @@ class BiscottiEngine:
             t4 = tm()
             agg_box[0] = ns.queue_witness(ctx)
             ph["h_witness"] = (tm() - t4) * 1e3
+            self._agg_event = ns.agg_done[ctx.par]
             self._side_done[ctx.par] = ns.side_done[ctx.par]
             self._wevent = ns.side_done[ctx.par]
             return
@@ -1039,6 +1041,8 @@ class BiscottiEngine:
             return None
         if self._wevent is not None:
             self._wevent.synchronize()
+        if getattr(self, "_agg_event", None) is not None:
+            self._agg_event.synchronize()
         aggC, aggW = self.last_aggregate
         Cb, Wb = self.commit.to_bytes(self.commit.normalize(aggC) if aggC.shape[-1] == 24 else aggC), \
             self.commit.to_bytes(self.commit.normalize(aggW) if aggW.shape[-1] == 24 else aggW)
@@ -1166,7 +1170,7 @@ class BiscottiEngine:
         if self.device.type != "cuda" or self._main is None:
             return
         cur = torch.cuda.current_stream(self.device)
-        for st in (self._main, self._side, self._wit, self.signer.stream if self.signer is not None else None,
+        for st in (self._main, self._side, self._wit, self._agg, self.signer.stream if self.signer is not None else None,
                    getattr(self.vrf, "_dside", None)):
             if st is not None:
                 cur.wait_stream(st)

@@ -32,7 +32,7 @@ from ..ops.cmdlist import CmdList, NativeEvent
 from ..ops.msm import AFF, JAC
 from ..ops.secagg import recover_matrix, _RecoverMat
 
-MAIN, SIDE, SIGN, WIT = 0, 1, 2, 3
+MAIN, SIDE, SIGN, WIT, AGG = 0, 1, 2, 3, 4
 
 
 class NativeSchedule:
@@ -53,11 +53,12 @@ class NativeSchedule:
         self.n, self.P = n, P
         eng._ensure_bufs()
         i32 = dict(dtype=torch.int32, device=dev)
-        streams = [eng._main, eng._side, eng.signer.stream if eng.signer is not None else eng._side, eng._wit]
+        streams = [eng._main, eng._side, eng.signer.stream if eng.signer is not None else eng._side, eng._wit, eng._agg]
         self.streams = streams
         # ---- events
         ev = lambda: [NativeEvent(), NativeEvent()]   # noqa: E731
         self.u_ready, self.c_ready, self.plan_ready, self.sig_done, self.side_done = ev(), ev(), ev(), ev(), ev()
+        self.agg_done = ev()
         self.eval_done, self.collect_ev = NativeEvent(), NativeEvent()
         self.eval_host = [NativeEvent() for _ in range(4)]
         self._vrf_placeholder = NativeEvent()
@@ -183,22 +184,22 @@ class NativeSchedule:
         ix["local1"] = cl.n
         # ---- EVAL (of the weights the previous block produced) -------------------------------------------------------
         ix["eval0"] = cl.n
-        cl.wait(SIDE, self.collect_ev)
+        cl.wait(AGG, self.collect_ev)
         cnt_d, cnt_h, _ = eng._ev_slots[0]
-        ix["ev_set"] = cl.memset(SIDE, cnt_d, 0)
+        ix["ev_set"] = cl.memset(AGG, cnt_d, 0)
         if eng.model.kind == "softmax":
-            ix["ev_a"] = cl.add("eval_softmax", SIDE, eng.w32, None, data.X_test, data.y_test, cnt_d[0:1], 1, data.X_test.shape[0],
+            ix["ev_a"] = cl.add("eval_softmax", AGG, eng.w32, None, data.X_test, data.y_test, cnt_d[0:1], 1, data.X_test.shape[0],
                                 F, Cn, eng.w32.numel())
-            ix["ev_b"] = cl.add("eval_softmax", SIDE, eng.w32, None, data.X_attack, data.y_attack, cnt_d[1:2], 1,
+            ix["ev_b"] = cl.add("eval_softmax", AGG, eng.w32, None, data.X_attack, data.y_attack, cnt_d[1:2], 1,
                                 data.X_attack.shape[0], F, Cn, eng.w32.numel())
         else:
-            ix["ev_a"] = cl.add("eval_logistic", SIDE, eng.w32, None, data.X_test, data.y_test, cnt_d[0:1], 1, data.X_test.shape[0],
+            ix["ev_a"] = cl.add("eval_logistic", AGG, eng.w32, None, data.X_test, data.y_test, cnt_d[0:1], 1, data.X_test.shape[0],
                                 F, eng.w32.numel())
-            ix["ev_b"] = cl.add("eval_logistic", SIDE, eng.w32, None, data.X_attack, data.y_attack, cnt_d[1:2], 1,
+            ix["ev_b"] = cl.add("eval_logistic", AGG, eng.w32, None, data.X_attack, data.y_attack, cnt_d[1:2], 1,
                                 data.X_attack.shape[0], F, eng.w32.numel())
-        ix["ev_cp"] = cl.d2h(SIDE, cnt_h, cnt_d)
-        cl.record(SIDE, self.eval_done)
-        ix["ev_rec"] = cl.record(SIDE, self.eval_host[0])
+        ix["ev_cp"] = cl.d2h(AGG, cnt_h, cnt_d)
+        cl.record(AGG, self.eval_done)
+        ix["ev_rec"] = cl.record(AGG, self.eval_host[0])
         ix["eval1"] = cl.n
         # ---- PLAN upload -------------------------------------------------------------------------------------------------
         ix["plan0"] = cl.n
@@ -209,6 +210,7 @@ class NativeSchedule:
         ix["front0"] = cl.n
         cl.wait(MAIN, self.u_ready[par])
         cl.wait(MAIN, self.side_done[par])
+        cl.wait(MAIN, self.agg_done[par])
         ix["vrf_wait"] = cl.wait(MAIN, self._vrf_placeholder)
         nn = max(1, cfg.num_noisers)
         ix["noisers"] = cl.add("vrf_noisers", MAIN, None, hash_d, 32, stake_d, n, isw_d, data.peer_ids, P, cfg.num_noisers,
@@ -271,6 +273,7 @@ class NativeSchedule:
         ix["commit0"] = cl.n
         Q, chunkC = self.Q[par], self.chunkC[par]
         cl.wait(SIDE, self.side_done[par])      # the witnesses of the block two heights back still read Q / chunkC of this parity
+        cl.wait(SIDE, self.agg_done[par])       # ... and so does the miners' aggregation
         cl.add("quantize", SIDE, eng.U, Q, P, d, eng.ldu, C.dpad, scale4)
         cl.add("msm_table_dc", SIDE, Q, Q.stride(0), None, P, None, C.c_sidx, C.c_bidx, None, C.nchunk, POLY_SIZE, C.c_table,
                C.w, C.nw, chunkC, C.nchunk)
@@ -312,14 +315,18 @@ class NativeSchedule:
         cl.wait(WIT, self.c_ready[par])         # Q and chunkC of this block
         ix["wit"] = cl.add("msm_table_dc", WIT, Q, Q.stride(0), pout["appr_local"], self.wrows, n_la, C.w_sidx, C.w_bidx, None,
                            G, POLY_SIZE - 1, C.w_table, C.w, C.nw, self.W, G)
-        # the miners' aggregate = commitment / witnesses of the contributors' SUMMED polynomial (CommitmentEngine.
-        # aggregate_by_scalars): one more MSM row each instead of a point addition per contributor and group
-        cl.add("sum_rows_i64_dc", WIT, Q, Q.stride(0), pout["sel"], pout["sel"].numel(), n_lc, C.dpad, self.aggQ)
-        cl.add("msm_table_dc", WIT, self.aggQ, C.dpad, None, 1, None, C.c_sidx, C.c_bidx, None, C.nchunk, POLY_SIZE, C.c_table,
-               C.w, C.nw, self.aggC[par], C.nchunk)
-        cl.add("msm_table_dc", WIT, self.aggQ, C.dpad, None, 1, None, C.w_sidx, C.w_bidx, None, G, POLY_SIZE - 1, C.w_table,
-               C.w, C.nw, self.aggW[par], G)
         cl.record(WIT, self.side_done[par])
+        # the miners' aggregate = commitment / witnesses of the contributors' SUMMED polynomial (CommitmentEngine.
+        # aggregate_by_scalars): one more MSM row each instead of a point addition per contributor and group.  Two small,
+        # latency-bound launches: their own stream (shared with the error-rate kernels), beside the witness MSM
+        cl.wait(AGG, self.collect_ev)
+        cl.wait(AGG, self.c_ready[par])
+        cl.add("sum_rows_i64_dc", AGG, Q, Q.stride(0), pout["sel"], pout["sel"].numel(), n_lc, C.dpad, self.aggQ)
+        cl.add("msm_table_dc", AGG, self.aggQ, C.dpad, None, 1, None, C.c_sidx, C.c_bidx, None, C.nchunk, POLY_SIZE, C.c_table,
+               C.w, C.nw, self.aggC[par], C.nchunk)
+        cl.add("msm_table_dc", AGG, self.aggQ, C.dpad, None, 1, None, C.w_sidx, C.w_bidx, None, G, POLY_SIZE - 1, C.w_table,
+               C.w, C.nw, self.aggW[par], G)
+        cl.record(AGG, self.agg_done[par])
         ix["wit1"] = cl.n
         cl.ix = ix
         return cl
