@@ -29,7 +29,16 @@ def main():
     a = ap.parse_args()
     kw = {} if a.sep is None else {"data_sep": a.sep}
     cfg = BiscottiConfig(num_nodes=a.peers, dataset=a.dataset, max_iterations=a.steps + 40, **kw)
-    eng = BiscottiEngine(cfg, device="cuda:0")
+    from biscotti_b200.parallel.comm import init_distributed
+
+    rank, local, world = init_distributed("cuda")
+    dev = torch.device("cuda", local)
+    comm = None
+    if world > 1:
+        from biscotti_b200.parallel.fused import FusedComm
+
+        comm = FusedComm(rank, world, dev, cfg)
+    eng = BiscottiEngine(cfg, device=dev, rank=rank, world=world, comm=comm)
     for _ in range(25):
         eng.step()
     torch.cuda.synchronize()
@@ -40,6 +49,9 @@ def main():
             with record_function(f"BLOCK{i}"):
                 eng.step()
         torch.cuda.synchronize()
+    if rank != 0:
+        torch.distributed.barrier()
+        return
     path = os.path.join(tempfile.gettempdir(), "bsc_trace.json")
     prof.export_chrome_trace(path)
     ev = json.load(open(path))["traceEvents"]
@@ -56,6 +68,8 @@ def main():
                 print(f"  {e['ts'] - t0:9.1f} +{e['dur']:8.1f}  s{e['args'].get('stream', '?'):<3} {nm}")
     spans = [blocks[i + 1]["ts"] - blocks[i]["ts"] for i in range(len(blocks) - 1)]
     print("block-to-block host period (us):", [round(s) for s in spans])
+    if world > 1:
+        torch.distributed.barrier()
 
 
 if __name__ == "__main__":
