@@ -181,6 +181,8 @@ __global__ void __launch_bounds__(128) g1_comb_mul_kernel(const U256* __restrict
   G1Jac acc = g1j_inf();
   if (i < N) {
     const U256 s = k[i];
+    // pass 1: the signed digits (the recoding carry is sequential, but it is a few integer operations per window)
+    short dg[48];
     uint32_t carry = 0;
     for (int win = 0; win < nw; win++) {
       const int bit = win * w;
@@ -192,15 +194,20 @@ __global__ void __launch_bounds__(128) g1_comb_mul_kernel(const U256* __restrict
         d += (uint32_t)(two >> shft) & mask;
       }
       carry = 0;
-      bool neg = false;
+      int sd = (int)d;
       if (d > (uint32_t)H) {
-        d = (1u << w) - d;
-        neg = true;
+        sd = (int)d - (1 << w);
         carry = 1;
       }
-      if (d && (win % COMB_LANES) == lane) {
-        G1Affine pt = table[(size_t)win * H + (d - 1)];
-        if (neg) pt.y = fe_neg(pt.y);
+      dg[win] = (short)sd;
+    }
+    // pass 2: every lane walks ITS windows (lane, lane + 8, ...), so the lanes of a warp add at the same time - a branch
+    // on "is this window mine" inside one loop over all windows would serialise the additions again
+    for (int win = lane; win < nw; win += COMB_LANES) {
+      const int sd = dg[win];
+      if (sd) {
+        G1Affine pt = table[(size_t)win * H + ((sd < 0 ? -sd : sd) - 1)];
+        if (sd < 0) pt.y = fe_neg(pt.y);
         acc = g1j_add_affine(acc, pt);
       }
     }
@@ -399,7 +406,7 @@ void bsc_msm_table_host(const long long* Q, int ldq, const int* sel, int P, cons
 int bsc_g1_comb_mul(const void* scalars_u256, int N, const void* table_affine, int w, int nw, void* out_jac,
                     void* stream) {
   if (N == 0) return 0;
-  if (w < 2 || w > 12 || nw * w < 257) return -1;
+  if (w < 2 || w > 12 || nw * w < 257 || nw > 48) return -1;
   const long long threads = (long long)N * COMB_LANES;
   g1_comb_mul_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const U256*)scalars_u256, N,
                                                                          (const G1Affine*)table_affine, w, nw,

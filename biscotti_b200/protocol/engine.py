@@ -878,24 +878,28 @@ class BiscottiEngine:
             t0 = tm()
             nxt = self._next_inputs_ready(self._side) if cfg.lookahead else False
             if nxt is not False:
-                # order: the next block's plan and approvals first (T = v*G is the longest off-chain dependency of the next
-                # tail), then its local step (head of its chain), this block's error rates, the next chain front, commitments
-                nctx = self._begin_block_ahead()
+                # Order = what the NEXT tail waits for longest first: the next block's local step and commitments (their
+                # wire bytes are what the approvals sign), its plan and the approvals' T = v*G, this block's error rates (they
+                # must read the weights before the next SGD step), the next chain front, the approvals' last kernel.
+                ns.queue_local_and_eval(it + 1, rep, False, inputs=nxt)
+                npre = ns.queue_commit(it + 1)
                 t1 = tm()
+                nctx = self._begin_block_ahead()
+                t2 = tm()
                 ahead = nctx is not None and not nctx.empty and nctx.native
                 if ahead:
                     ns.queue_sign_T(nctx)
-                ns.queue_local_and_eval(it + 1, rep, do_eval, inputs=nxt)
-                t2 = tm()
+                if do_eval:
+                    ns.queue_eval(rep, ctx.par)
                 if ahead:
-                    ns.queue_front(nctx)
+                    nctx.pre = npre
                     t3 = tm()
-                    ns.queue_commit_and_sign(nctx)
+                    ns.queue_front(nctx)
+                    ns.queue_sign_finish(nctx)
                     self._ctx_next = nctx
-                    ph["h_front"] = (t3 - t2) * 1e3
-                    ph["h_commit_sign"] = (tm() - t3) * 1e3
-                ph["h_plan"] = (t1 - t0) * 1e3
-                ph["h_local_eval"] = (t2 - t1) * 1e3
+                    ph["h_front"] = (tm() - t3) * 1e3
+                ph["h_local_eval"] = (t1 - t0) * 1e3
+                ph["h_plan"] = (t2 - t1) * 1e3
             elif do_eval:
                 ns.queue_eval(rep, ctx.par)
             t4 = tm()

@@ -476,16 +476,22 @@ class NativeSchedule:
                 cl.patch(ix["finish"], 7, ns)
         cl.run(ix["sign0"], ix["sign_mid"])
 
-    def queue_commit_and_sign(self, ctx):
-        """Commitments of the block's updates (side stream), then the approvals' challenge + response, which wait for them."""
+    def queue_commit(self, it: int) -> dict:
+        """Commitments of block `it`'s updates (side stream, right behind its local step).  Returns the block's `pre` record."""
         eng = self.eng
-        par, it = ctx.par, ctx.it
-        cl = self.cl[par]
-        ix = cl.ix
+        par = it & 1
         self.run(par, "commit")
-        cl.run(ix["sign_mid"], ix["sign1"])
-        ctx.pre = {"it": it, "Q": self.Q[par], "chunkC": self.chunkC[par], "cbytes": eng._cbytes[par], "u_ready": None,
-                   "c_ready": None, "src": self._last_src, "native": True}
+        return {"it": it, "Q": self.Q[par], "chunkC": self.chunkC[par], "cbytes": eng._cbytes[par], "u_ready": None,
+                "c_ready": None, "src": self._last_src, "native": True}
+
+    def queue_sign_finish(self, ctx):
+        """The approvals' challenge + response: waits (on the approval stream) for T = v*G and for the commitments."""
+        cl = self.cl[ctx.par]
+        cl.run(cl.ix["sign_mid"], cl.ix["sign1"])
+
+    def queue_commit_and_sign(self, ctx):
+        ctx.pre = self.queue_commit(ctx.it)
+        self.queue_sign_finish(ctx)
 
     def queue_back(self, ctx) -> bool:
         """Returns False when this block's abscissae have no safe recovery matrix (the Python schedule then queues the
