@@ -102,6 +102,7 @@ class _Plan:
     xs: list = field(default_factory=list)
     enough_shares: bool = False
     clip: int = 0
+    n_workers: int = 0
     stake_m: object = None       # int32 [n]: stake with dead peers zeroed (the lottery's ticket counts)
     is_worker: object = None     # uint8 [n]
 
@@ -617,13 +618,15 @@ class BiscottiEngine:
                     self.alive[p] = False
                 self._cut = cut
         t_p0 = time.perf_counter()
-        pl = self._host_plan()
+        ns = self._native()
+        pl = ns.plan_block(_Plan) if ns is not None else self._host_plan()
         self._t_plan_host = (time.perf_counter() - t_p0) * 1e3
         krum_set = pl.krum_set
         nk = len(krum_set)
         ctx = _Ctx(it=it, par=it & 1, pl=pl, nk=nk, phases={}, alive=list(self.alive), stake=list(self.stake),
                    timing=self._timing, pipelined=self.pipelined)
-        ctx.rep = BlockReport(it, b"", True, pl.verifiers, pl.miners, len(pl.workers), nk, 0, 0)
+        n_workers = pl.n_workers if ns is not None else len(pl.workers)
+        ctx.rep = BlockReport(it, b"", True, pl.verifiers, pl.miners, n_workers, nk, 0, 0)
         if not pl.verifiers or not pl.miners or not pl.workers or not pl.enough_shares or nk == 0:
             ctx.empty = True
             return ctx
@@ -642,7 +645,6 @@ class BiscottiEngine:
         ctx.stake_m, ctx.is_worker = pl.stake_m, pl.is_worker
         ctx.salt64 = self.run_salt + (prev_hash + b"\0" * 32)[:32]
         ctx.ns = len(pl.signers) if (self.signer is not None and pl.approved_ok) else 0
-        ns = self._native()
         if ns is not None and nk >= 3:
             ctx.native = True
             t_u0 = time.perf_counter()
@@ -813,7 +815,7 @@ class BiscottiEngine:
             cnt = host["counts"]
             n_contrib = int(cnt[1])
             rep.n_accepted = int(host["accept"].sum()) if "accept" in host else int(cnt[0])
-            contributors = [krum_set[int(i)] for i in host["cpos"][:n_contrib]] if n_contrib >= 2 else []
+            contributors = [int(krum_set[int(i)]) for i in host["cpos"][:n_contrib]] if n_contrib >= 2 else []
             badv = host["bad"].astype(np.int64)
             if badv.shape[0] >= 3 and badv[2]:
                 raise RuntimeError(f"rank {self.rank}: a cross-GPU wait timed out (code {int(badv[2])}) in block {it}")

@@ -89,6 +89,12 @@ class NativeSchedule:
                                          sign=vw(self.o_sign, self.nv, np.int32), xs=vw(self.o_xs, 10, np.int32),
                                          av=vw(self.o_av, 64, np.uint8), slots=vw(self.o_slots, n, np.int32),
                                          hash=vw(self.o_hash, 64, np.uint8)))
+        self._plan_ptrs = [{k_: v_.ctypes.data_as(ctypes.c_void_p) for k_, v_ in vw_.items()} for vw_ in self._plan_views]
+        i32 = lambda k_: np.zeros(k_, dtype=np.int32)   # noqa: E731
+        sc = dict(stake=i32(n), alive=np.zeros(n, dtype=np.uint8), verifiers=i32(64), miners=i32(64), workers=i32(n), counts=i32(8))
+        for k_ in list(sc):
+            sc["p_" + k_] = sc[k_].ctypes.data_as(ctypes.c_void_p)
+        self._scratch = sc
         self._pos = np.full(n, -1, dtype=np.int32)
         self._arange = np.arange(n, dtype=np.int32)
         self._local_ids = np.asarray(eng.local_ids, dtype=np.int64)
@@ -381,32 +387,60 @@ class NativeSchedule:
         self.run(par, "eval")
         eng._attach_eval_resolver(rep, cnt_h, self.eval_host[k])
 
-    def upload_plan(self, ctx):
-        """ONE pinned staging copy of everything the chain reads about the block (fixed layout, see __init__)."""
-        eng, pl = self.eng, ctx.pl
-        par, nk = ctx.par, ctx.nk
+    def plan_block(self, plan_cls):
+        """Host plan of the next block written STRAIGHT into the pinned staging buffer (ledger.cpp: bsc_plan_block fills the
+        stake / worker / candidate / arrival-rank / signer / share arrays in place), plus the three row maps this rank adds.
+        Returns the engine's _Plan; upload_plan() then only has to queue the copy."""
+        eng = self.eng
+        cfg, it, n = eng.cfg, eng.iteration, self.n
+        from ..ops import chain as chain_ops
+        from ..ops._call import lib
+
         k = self._plan_i = (getattr(self, "_plan_i", -1) + 1) % 4
-        v = self._plan_views[k]
-        ks = np.asarray(pl.krum_set, dtype=np.int32)
-        v["stake"][:] = ctx.stake_m
-        v["isw"][:] = ctx.is_worker
+        v, pp = self._plan_views[k], self._plan_ptrs[k]
+        sc = self._scratch
+        sc["stake"][:] = eng.stake
+        sc["alive"][:] = eng.alive
+        prev_hash = eng.chain.latest_hash()
+        lib().bsc_plan_block(prev_hash, len(prev_hash), sc["p_stake"], sc["p_alive"], n, cfg.num_verifiers, cfg.num_miners,
+                             cfg.krum_thresh, cfg.num_samples, int(cfg.random_sampling),
+                             chain_ops.seed64(cfg.seed, it, "verify"), chain_ops.seed64(cfg.seed, it, "shares"),
+                             chain_ops.seed64("rs", it), ctypes.c_double(cfg.krum_adversary_frac), cfg.shares_per_miner,
+                             self.S, sc["p_verifiers"], sc["p_miners"], sc["p_workers"], pp["ids"], pp["rank"], pp["sign"],
+                             pp["av"], pp["xs"], pp["isw"], pp["stake"], sc["p_counts"])
+        nv, nm, nw, nk, ns, ok, enough, clip = (int(x) for x in sc["counts"])
+        pl = plan_cls(sc["verifiers"][:nv].tolist(), sc["miners"][:nm].tolist(), None, prev_hash)
+        pl.n_workers = nw
+        pl.stake_m, pl.is_worker = v["stake"], v["isw"]
+        if nv == 0 or nm == 0 or nw == 0:
+            pl.workers = []
+            return pl
+        pl.workers = True                    # only its truth value and count are used on this path
+        ks = v["ids"][:nk]
+        pl.krum_set = ks.copy()
+        pl.clip = clip
+        pl.share_rank = v["rank"][:nk]
+        pl.signers = v["sign"][:ns].tolist()
+        pl.approved_ok = bool(ok)
+        pl.trigger = max(1, cfg.num_samples // 2) if cfg.share_trigger == "half" else nk
+        pl.shares_avail = v["av"][: self.S].tolist()
+        pl.xs = v["xs"][:10].tolist()
+        pl.enough_shares = bool(enough)
         pos = self._pos
         pos.fill(-1)
         pos[ks] = self._arange[:nk]
         v["dst"][: self.P] = pos[self._local_ids]
         v["lrow"][:nk] = self._local_row_of[ks]
-        v["rank"][:nk] = pl.share_rank
-        v["ids"][:nk] = ks
-        ns = len(pl.signers)
-        if ns:
-            v["sign"][:ns] = pl.signers
-        v["xs"][:] = pl.xs
-        av = v["av"]
-        av.fill(0)
-        av[: len(pl.shares_avail)] = pl.shares_avail
         if eng.fused:
             v["slots"][:nk] = self._slot_of[ks]
-        v["hash"][:32] = np.frombuffer(pl.prev_hash, dtype=np.uint8)
+        v["hash"][:32] = np.frombuffer(prev_hash, dtype=np.uint8)
+        pl._staged = k
+        return pl
+
+    def upload_plan(self, ctx):
+        """Queue the ONE pinned staging copy of everything the chain reads about the block (fixed layout, see __init__)."""
+        par = ctx.par
+        k = ctx.pl._staged
         cl = self.cl[par]
         cl.patch(cl.ix["plan_cp"], 1, self.plan_pinned[k].data_ptr())
         self.run(par, "plan")
