@@ -90,8 +90,8 @@ class NativeSchedule:
                                          av=vw(self.o_av, 64, np.uint8), slots=vw(self.o_slots, n, np.int32),
                                          hash=vw(self.o_hash, 64, np.uint8)))
         self._plan_ptrs = [{k_: v_.ctypes.data_as(ctypes.c_void_p) for k_, v_ in vw_.items()} for vw_ in self._plan_views]
-        i32 = lambda k_: np.zeros(k_, dtype=np.int32)   # noqa: E731
-        sc = dict(stake=i32(n), alive=np.zeros(n, dtype=np.uint8), verifiers=i32(64), miners=i32(64), workers=i32(n), counts=i32(8))
+        zi = lambda k_: np.zeros(k_, dtype=np.int32)   # noqa: E731
+        sc = dict(stake=zi(n), alive=np.zeros(n, dtype=np.uint8), verifiers=zi(64), miners=zi(64), workers=zi(n), counts=zi(8))
         for k_ in list(sc):
             sc["p_" + k_] = sc[k_].ctypes.data_as(ctypes.c_void_p)
         self._scratch = sc
