@@ -688,24 +688,37 @@ const char* bsc_go_float(double v) {
 // #tickets, cursor advances by one byte, SHA-256 re-hash of the current buffer when i >= len-1,
 // duplicates (and `exclude`) skipped.  `cursor_io`/`buf` carry the state from the verifier draw into
 // the miner draw exactly like getVRFRoles does.
-static int lottery_draw(std::vector<uint8_t>& buf, size_t& i, const std::vector<int>& tickets, int want, int exclude,
-                        int* out) {
-  std::vector<char> seen;
-  int got = 0;
-  int maxid = 0;
-  for (int t : tickets) maxid = t > maxid ? t : maxid;
-  seen.assign((size_t)maxid + 1, 0);
-  // the reference loops forever if `want` exceeds the distinct eligible ids; bound it instead
+// The ticket list in closed form: pre[id] = tickets of ids < id, pre[n] = total.  ticket t belongs to the largest id
+// with pre[id] <= t (ids without stake share their successor's offset and are never the largest).  Same draws as the
+// reference's materialised list, without O(total stake) work per draw - stake grows by 5 per contribution per block.
+struct Tickets {
+  std::vector<long long> pre;
+  int n = 0;
   int distinct = 0;
-  {
-    std::vector<char> has((size_t)maxid + 1, 0);
-    for (int t : tickets)
-      if (!has[(size_t)t] && t != exclude) {
-        has[(size_t)t] = 1;
-        distinct++;
-      }
+  explicit Tickets(const int* stake, int n_) : pre((size_t)n_ + 1, 0), n(n_) {
+    for (int i = 0; i < n_; i++) {
+      pre[(size_t)i + 1] = pre[(size_t)i] + (stake[i] > 0 ? stake[i] : 0);
+      distinct += stake[i] > 0;
+    }
   }
+  long long total() const { return pre[(size_t)n]; }
+  bool has(int id) const { return id >= 0 && id < n && pre[(size_t)id + 1] > pre[(size_t)id]; }
+  int owner(long long t) const {
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (pre[(size_t)mid] <= t) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+  }
+};
+
+static int lottery_draw(std::vector<uint8_t>& buf, size_t& i, const Tickets& tk, int want, int exclude, int* out) {
+  // the reference loops forever if `want` exceeds the distinct eligible ids; bound it instead
+  const int distinct = tk.distinct - (tk.has(exclude) ? 1 : 0);
   if (want > distinct) want = distinct;
+  int got = 0;
+  const unsigned long long total = (unsigned long long)tk.total();
   while (got < want) {
     if (i + 1 >= buf.size()) {
       uint8_t h[32];
@@ -713,12 +726,10 @@ static int lottery_draw(std::vector<uint8_t>& buf, size_t& i, const std::vector<
       buf.assign(h, h + 32);
       i = 0;
     }
-    const size_t idx = ((size_t)buf[i] * 256 + buf[i + 1]) % tickets.size();
-    const int winner = tickets[idx];
-    if (!seen[(size_t)winner] && winner != exclude) {
-      seen[(size_t)winner] = 1;
-      out[got++] = winner;
-    }
+    const int winner = tk.owner((long long)((((unsigned long long)buf[i] * 256ull + buf[i + 1])) % total));
+    bool dup = winner == exclude;
+    for (int k = 0; k < got; k++) dup = dup || out[k] == winner;
+    if (!dup) out[got++] = winner;
     i++;
   }
   return got;
@@ -727,25 +738,21 @@ static int lottery_draw(std::vector<uint8_t>& buf, size_t& i, const std::vector<
 // roles: verifiers first, then miners continue from the same byte cursor (vrf.go:103-182)
 int bsc_lottery_roles(const uint8_t* input, int inlen, const int* stake, int n, int nverifiers, int nminers,
                       int* verifiers, int* miners, int* nv_out, int* nm_out) {
-  std::vector<int> tickets;
-  for (int id = 0; id < n; id++)
-    for (int k = 0; k < stake[id]; k++) tickets.push_back(id);
-  if (tickets.empty()) return -1;
+  Tickets tk(stake, n);
+  if (tk.total() == 0) return -1;
   std::vector<uint8_t> buf(input, input + inlen);
   size_t i = 0;
-  *nv_out = lottery_draw(buf, i, tickets, nverifiers, -1, verifiers);
-  *nm_out = lottery_draw(buf, i, tickets, nminers, -1, miners);
+  *nv_out = lottery_draw(buf, i, tk, nverifiers, -1, verifiers);
+  *nm_out = lottery_draw(buf, i, tk, nminers, -1, miners);
   return 0;
 }
 // noisers from a peer's private VRF output, excluding itself (vrf.go:54-100)
 int bsc_lottery_noisers(const uint8_t* vrf_out, int len, const int* stake, int n, int source, int want, int* noisers) {
-  std::vector<int> tickets;
-  for (int id = 0; id < n; id++)
-    for (int k = 0; k < stake[id]; k++) tickets.push_back(id);
-  if (tickets.empty()) return 0;
+  Tickets tk(stake, n);
+  if (tk.total() == 0) return 0;
   std::vector<uint8_t> buf(vrf_out, vrf_out + len);
   size_t i = 0;
-  return lottery_draw(buf, i, tickets, want, source, noisers);
+  return lottery_draw(buf, i, tk, want, source, noisers);
 }
 
 }  // extern "C"
