@@ -95,7 +95,25 @@ class BiscottiConfig:
                                       # updates keep realistic magnitudes.  With well separated classes (6.0, round 1) the
                                       # error is 0.002 after a few blocks and most coordinates of an update quantise to
                                       # zero, which lets the commitment / witness MSMs skip most of their work
-    data_noise: float = 1.0           # synthetic data: per-feature Gaussian noise around the prototype
+    data_noise: float = 1.0           # synthetic data ("blobs"): per-feature Gaussian noise around the prototype
+    data_model: str = "blobs"         # "blobs": prototype + isotropic noise of std data_noise in every feature.  Its within-class
+                                      # variation is 784-dimensional: learning is slow (the default above) and updates keep
+                                      # non-zero coordinates everywhere - the demanding case for the MSMs, hence the default
+                                      # for timing - but every update is about equally far from every other, so under the
+                                      # reference's DP noise (std 0.54 per coordinate at epsilon 2, norm 48) Multi-Krum cannot
+                                      # tell poisoners from honest peers.
+                                      # "lowrank": class c = data_radius * (axis of its pair c // 2) + its own axis (two classes
+                                      # of a pair sit data_gap apart), spread data_spread along the class axes, data_latent
+                                      # class-neutral directions of std data_latent_sigma, per-pixel noise data_iso.  Rows of one
+                                      # class look alike, as digit images do, so peers that all train on one relabelled class
+                                      # send the tight, far-off cluster of updates Multi-Krum is built to reject (squared
+                                      # distance to an honest update ~1700 against a noise fluctuation of ~40 per pair)
+    data_radius: float = 0.0
+    data_gap: float = 28.28
+    data_spread: float = 6.0
+    data_latent: int = 24
+    data_latent_sigma: float = 2.5
+    data_iso: float = 0.15
     data_dir: str | None = None       # directory of <dataset><i>.npy shards (data/files.py); None = synthetic data
     prefetch: bool = True             # queue iteration t+1's local step + commitment MSM behind iteration t's
                                       # aggregation kernel so the device is busy while the host assembles block t

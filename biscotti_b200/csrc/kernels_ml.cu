@@ -666,6 +666,10 @@ int bsc_krum_scores_static(const float* A, const float* norms, int n, int d, int
             n, d, clip, BSC_KRUM_STATIC_MAX_PEERS);
     return -1;
   }
+  if (lda < d) {   // a row stride shorter than the row would make the Gram kernel read past the matrix
+    fprintf(stderr, "[biscotti_b200] bsc_krum_scores_static: lda=%d is smaller than d=%d\n", lda, d);
+    return -1;
+  }
   int dev = 0;
   BSC_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) return -2;

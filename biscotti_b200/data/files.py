@@ -6,7 +6,7 @@ Layout (ML/Pytorch/{mnist,cifar,lfw,credit}_dataset.py, data/mnist/parse_mnist.p
   <dir>/<dataset>_test.npy    held-out test set (all rows are used, `is_train=False` keeps rows [cut, n))
   <dir>/<dataset>_train.npy   the full training set (only the ML-only sandboxes read it)
   <dir>/<dataset>_digit1.npy  attack set: rows of the poisoning source class (client.py:13-23, get17AttackRate)
-  <dir>/<dataset>_bad.npy     poisoned shard: every source-class row relabelled to the target class
+  <dir>/<dataset>_bad.npy     poisoned shard: the source-class rows only, all labelled as the target class
 
 `load_peer_data` returns the same `PeerData` the synthetic generator does, so the engine does not care where the
 rows came from; `write_shards` is `slice_uniform` + `slice_for_tm` + `generate_poisoned` in one call and is what

@@ -4,13 +4,14 @@ The real blobs are absent (.MISSING_LARGE_BLOBS) and BASELINE.json prescribes sy
 generators keep what the protocol depends on:
   * per-peer shards (`mnist{i}.npy`, ML/Pytorch/data/mnist/parse_mnist.py:111-163: uniform slices),
   * a held-out test set (`mnist_test`) and the attack set (`mnist_digit1`, client.py:13-23),
-  * the poisoned shard (`mnist_bad`: every 1 relabelled 7, parse_mnist.py:295-301; creditcard:
-    flipped labels) used by peers with id > idx (DistSys/main.go:836-844),
+  * the poisoned shard (`mnist_bad` = the digit-1 rows and nothing else, all labelled 7, parse_mnist.py:295-301;
+    creditcard: flipped labels) used by peers with id > idx (DistSys/main.go:836-844),
   * creditcard rows standardised with a bias column (ML/code/utils.py:88-121), labels in {-1,+1}.
 Classes are Gaussian blobs around random prototypes so that training converges like the real task.
 """
 from __future__ import annotations
 
+import math
 from dataclasses import dataclass
 
 import torch
@@ -39,7 +40,7 @@ def poisoner_ids(cfg: BiscottiConfig) -> set[int]:
     """DistSys rule: ids strictly greater than N*(1-po) poison (main.go:836-844)."""
     if cfg.poison_fraction <= 0:
         return set()
-    idx = int(cfg.num_nodes * (1.0 - cfg.poison_fraction))
+    idx = int(math.ceil(cfg.num_nodes * (1.0 - cfg.poison_fraction)))
     return {i for i in range(cfg.num_nodes) if i > idx}
 
 
@@ -64,11 +65,32 @@ def make_data(cfg: BiscottiConfig, peer_ids: list[int], device="cpu", noise: flo
             y = torch.sign(X @ wtrue + 0.3 * torch.randn(n, generator=gen))
             y[y == 0] = 1.0
             return torch.cat([X, torch.ones(n, 1)], dim=1), y.float()
+    elif cfg.data_model == "lowrank":
+        k, npair = cfg.data_latent, (C + 1) // 2
+        Q, _ = torch.linalg.qr(torch.randn(F, npair + C + k, generator=g0, dtype=torch.float64))
+        Q = Q.float().T.contiguous()                                        # orthonormal rows
+        shared, axes, lat = Q[:npair], Q[npair:npair + C], Q[npair + C:]
+        # class c = the look its pair (c // 2) shares, of norm data_radius, plus its own axis scaled so that the two
+        # members of a pair sit data_gap apart; within-class spread along the class axes = data_spread
+        own = cfg.data_gap / math.sqrt(2.0)
+        s_in = cfg.data_spread
+        protos = cfg.data_radius * shared[torch.arange(C) // 2] + own * axes
+
+        def sample(n, gen, only_class=None):
+            y = torch.randint(0, C, (n,), generator=gen)
+            if only_class is not None:
+                y = torch.full_like(y, only_class)
+            X = protos[y] + s_in * torch.randn(n, C, generator=gen) @ axes
+            X += cfg.data_latent_sigma * torch.randn(n, k, generator=gen) @ lat
+            X += cfg.data_iso * torch.randn(n, F, generator=gen)
+            return X, y.int()
     else:
         protos = _prototypes(C, F, g0, sep)
 
-        def sample(n, gen):
+        def sample(n, gen, only_class=None):
             y = torch.randint(0, C, (n,), generator=gen)
+            if only_class is not None:
+                y = torch.full_like(y, only_class)
             X = protos[y] + noise * torch.randn(n, F, generator=gen)
             return X, y.int()
 
@@ -76,12 +98,14 @@ def make_data(cfg: BiscottiConfig, peer_ids: list[int], device="cpu", noise: flo
     Xs, ys, pz = [], [], []
     for pid in peer_ids:
         gen = torch.Generator().manual_seed(cfg.seed * 1000003 + pid)
-        X, y = sample(cfg.shard_size, gen)
-        if pid in bad:
-            if logistic:
+        if pid in bad and not logistic:
+            # a poisoner trains on nothing but source-class rows carrying the target label
+            X, y = sample(cfg.shard_size, gen, only_class=1 % C)
+            y = torch.full_like(y, 7 % C)
+        else:
+            X, y = sample(cfg.shard_size, gen)
+            if pid in bad:
                 y = -y
-            else:
-                y = torch.where(y == 1, torch.full_like(y, 7 % C), y)
         Xs.append(X)
         ys.append(y)
         pz.append(pid in bad)

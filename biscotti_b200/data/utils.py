@@ -34,10 +34,10 @@ def slice_by_class(X, y, n_classes: int):
 
 
 def generate_poisoned(X, y, source: int = 1, target: int = 7):
-    """parse_mnist.py:295-301 generate_poisoned: every `source` relabelled `target` (mnist_bad)."""
-    yb = y.copy()
-    yb[y == source] = target
-    return np.hstack([X, yb[:, None]])
+    """parse_mnist.py:295-301 generate_poisoned: mnist_bad is the `source` rows (mnist_digit1) and nothing else, every one
+    labelled `target`."""
+    keep = y == source
+    return np.hstack([X[keep], np.full((int(keep.sum()), 1), target, dtype=X.dtype)])
 
 
 def bootstrap(X, y, seed: int = 0):

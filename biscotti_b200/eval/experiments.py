@@ -44,7 +44,9 @@ def _run(cfg: BiscottiConfig, device, blocks: int, timing: bool = True):
     t0 = time.perf_counter()
     reps = eng.run(blocks)
     dt = time.perf_counter() - t0
-    return eng, reps, dt
+    eng.flush_reports()
+    eng.close()      # frees the window tables (tens of GB): the next configuration of a campaign builds its own
+    return None, reps, dt
 
 
 def _phase_means(reps):
@@ -114,7 +116,7 @@ def poison_heatmap(fractions=(0.5, 0.45, 0.4, 0.3, 0.1), collected=(20, 40, 70),
     for po in fractions:
         for ns in collected:
             cfg = BiscottiConfig(num_nodes=peers, dataset=dataset, max_iterations=blocks, poison_fraction=po,
-                                 perc_samples=ns, random_sampling=True, epsilon=1.0, **kw)
+                                 perc_samples=ns, random_sampling=True, **kw)      # epsilon stays at the -ep default (2.0)
             eng, reps, dt = _run(cfg, device, blocks, timing=False)
             tail = reps[int(0.8 * len(reps)):]
             rows.append({"poisoners": po, "collected": ns, "max_attack_rate": max(r.attack_rate or 0.0 for r in tail)})
@@ -165,6 +167,7 @@ def churn(period_blocks=(16, 8, 4, 2), peers=50, dataset="mnist", blocks=100, de
         dt = time.perf_counter() - t0
         rows.append({"kill_period_blocks": period, "s_per_block": dt / blocks, "final_error": eng.reports[-1].test_error,
                      "empty_blocks": sum(r.empty for r in eng.reports), "rejoin_ok": rejoin_ok})
+        eng.close()
     return rows
 
 
@@ -186,11 +189,13 @@ def time_to_accuracy(target=0.10, peers=100, dataset="mnist", blocks=102, device
     tail = eng.reports[int(0.8 * blocks):]
     # the first two blocks carry one-off costs (buffer allocation, command-list construction): rate over the rest
     rate = (stamps[-1] - stamps[1]) / max(1, blocks - 2)
-    return {"peers": peers, "dataset": dataset, "blocks": blocks, "s_per_block": rate, "first_two_blocks_s": stamps[1],
-            "target_error": target, "blocks_to_target": hit, "seconds_to_target": None if hit is None else stamps[hit],
-            "final_error": errs[-1], "error_every_10": [round(e, 4) for e in errs[::10]],
-            "max_attack_rate_after_80pct": max((r.attack_rate or 0.0) for r in tail),
-            "empty_blocks": sum(r.empty for r in eng.reports), "chain_ok": eng.chain.verify()}
+    out = {"peers": peers, "dataset": dataset, "blocks": blocks, "s_per_block": rate, "first_two_blocks_s": stamps[1],
+           "target_error": target, "blocks_to_target": hit, "seconds_to_target": None if hit is None else stamps[hit],
+           "final_error": errs[-1], "error_every_10": [round(e, 4) for e in errs[::10]],
+           "max_attack_rate_after_80pct": max((r.attack_rate or 0.0) for r in tail),
+           "empty_blocks": sum(r.empty for r in eng.reports), "chain_ok": eng.chain.verify()}
+    eng.close()
+    return out
 
 
 # ---- closed-form committee analyses (pure Python in the reference as well) ---------------------------

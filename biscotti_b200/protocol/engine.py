@@ -1216,6 +1216,17 @@ class BiscottiEngine:
             torch.cuda.synchronize(self.device)
         if self.comm is not None and hasattr(self.comm, "close"):
             self.comm.close()
+        # the window tables are the bulk of the footprint (up to half the device): drop them now rather than when the
+        # garbage collector gets to the engine, so that the next engine of a campaign finds the memory free
+        self._pre = self._ctx_next = self._vrf_early = None
+        self._ns = None
+        self._ns_ok = False
+        self.commit = None
+        if self.device.type == "cuda":
+            import gc
+
+            gc.collect()
+            torch.cuda.empty_cache()
 
     # rejoin: a restarted peer adopts the longest chain it is offered (main.go:1000-1013)
     def adopt_chain(self, serialized: bytes) -> bool:

@@ -34,12 +34,19 @@ from ..ops import krum as krum_ops, ml
 
 
 def run_clients(dataset: str = "mnist", honest: int = 6, poisoners: int = 4, rounds: int = 100, defense: str = "none",
-                batch_size: int = 10, epsilon: float = 0.0, seed: int = 1, device: str = "cpu", log_every: int = 10):
-    """ml_main_mnist.py:30-105: returns a list of {round, test_error, attack_rate, accepted} dicts."""
+                batch_size: int = 10, epsilon: float = 0.0, seed: int = 1, device: str = "cpu", log_every: int = 10,
+                optimizer: str = "ledger", lr: float = 0.001, momentum: float = 0.75, weight_decay: float = 0.001, **cfg_kw):
+    """ml_main_mnist.py:30-105: returns a list of {round, test_error, attack_rate, accepted} dicts.
+
+    optimizer="ledger": the kept updates are summed into the weights as they are, which is what a block does
+    (honest.go:358-375; there is no learning rate on that path).  optimizer="sgd": the reference's own ML-only harness -
+    the aggregator averages the gradients and takes a torch.optim.SGD step with momentum and weight decay
+    (client.py:30, 88-108: lr 0.001, momentum 0.75, weight_decay 0.001 for the CNNs).  The CNNs need the second: the raw
+    sum of a few dozen clipped gradients is a step of norm several hundred and kills every ReLU in one block."""
     n = honest + poisoners
     po = poisoners / n if poisoners else 0.0
     cfg = BiscottiConfig(num_nodes=n, dataset=dataset, poison_fraction=po, batch_size=batch_size, seed=seed,
-                         epsilon=max(epsilon, 1e-9), noising=epsilon > 0, commitments=False, secure_agg=False)
+                         epsilon=max(epsilon, 1e-9), noising=epsilon > 0, commitments=False, secure_agg=False, **cfg_kw)
     dev = torch.device(device)
     data = make_data(cfg, list(range(n)), dev)
     model = Model(cfg)
@@ -63,7 +70,12 @@ def run_clients(dataset: str = "mnist", honest: int = 6, poisoners: int = 4, rou
             keep = acc.bool()
         else:
             keep = torch.ones(n, dtype=torch.bool, device=dev)
-        w64 = w64 + upd[keep].double().sum(0)                 # un-averaged sum (honest.go:358, 373)
+        if optimizer == "sgd":
+            g = -upd[keep].double().mean(0) + weight_decay * w64          # updates are minus the gradients
+            buf = g if r == 0 else momentum * buf + g
+            w64 = w64 - lr * buf
+        else:
+            w64 = w64 + upd[keep].double().sum(0)             # un-averaged sum (honest.go:358, 373)
         if r % log_every == 0 or r == rounds - 1:
             w = w64.float().unsqueeze(0)
             te = float(model.eval_errors(w, None, data.X_test, data.y_test)[0])
