@@ -49,6 +49,8 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--trace", default=None, metavar="FILE",
                     help="instrument every phase (CUDA events) and write a Chrome/Perfetto trace; one file per rank")
     ap.add_argument("--save-chain", default=None)
+    ap.add_argument("--checkpoint-every", type=int, default=0, metavar="K",
+                    help="with --save-chain: also write the chain every K blocks (atomically), so that a killed run can be resumed")
     ap.add_argument("--partition", action="append", default=[], metavar="PEER:FIRST:LAST",
                     help="cut PEER off for blocks FIRST..LAST (blockNode.sh); may be repeated")
     ap.add_argument("--data-dir", default=None, help="directory of <dataset><i>.npy shard files (default: synthetic data)")
@@ -99,7 +101,15 @@ def run_localtest(a, mode: str) -> int:
     if a.trace:
         eng._timing = True                     # every phase bracketed by CUDA events (in-line schedule)
         cfg.prefetch = False
-    eng.run(max(0, cfg.max_iterations + 1 - eng.iteration))
+    todo = max(0, cfg.max_iterations + 1 - eng.iteration)
+    if a.save_chain and a.checkpoint_every > 0:
+        for i in range(todo):
+            eng.step()
+            if rank == 0 and (i + 1) % a.checkpoint_every == 0:
+                eng.chain.save(a.save_chain)
+        eng.flush_reports()
+    else:
+        eng.run(todo)
     if a.trace:
         from .utils.trace import write_chrome_trace
 

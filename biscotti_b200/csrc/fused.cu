@@ -17,6 +17,9 @@
 //
 // Cross-GPU ordering uses the epoch flags of symm.cuh; all waits are bounded.
 #include "common.cuh"
+#include <mutex>
+#include <unordered_map>
+
 #include "symm.cuh"
 #include "tc_ptx.cuh"
 #include "secagg_math.cuh"
@@ -188,15 +191,22 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
     __threadfence();
     atomicAdd(P.done_counter + 1 + blockIdx.x, 1u);
     const unsigned int target = P.seq * gridDim.y;
-    unsigned long long spins = 0;
+    // bounded by time like the cross-GPU waits (symm.cuh): on a timeout the error word is set (the host reads it
+    // with bsc_symm_error() when it collects the block) and the CTA carries on - no trap, the context survives
+    unsigned int spins = 0;
+    unsigned long long t0 = 0;
     for (;;) {
       unsigned int v;
       asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(P.done_counter + 1 + blockIdx.x) : "memory");
       if (v >= target) break;
       __nanosleep(32);
-      if (++spins > (1ull << 24)) {
-        printf("[biscotti_b200] krum_gram_fused: split barrier timed out (pair %d split %d)\n", blockIdx.x, blockIdx.y);
-        __trap();
+      if ((++spins & 1023u) == 0) {
+        const unsigned long long now = symm_now_ns();
+        if (t0 == 0) t0 = now;
+        if (now - t0 > SYMM_TIMEOUT_NS) {
+          atomicCAS(&g_symm_error, 0, 200);
+          break;
+        }
       }
     }
   }
@@ -553,7 +563,31 @@ int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* cons
     configured = true;
   }
   dim3 grid(P.ntile * (P.ntile + 1) / 2, ksplit);
-  if (grid.x * grid.y > 148) return -5;   // the in-kernel split barrier needs every CTA resident (1 CTA per SM)
+  // The in-kernel split barrier needs every CTA of the grid resident at once: the limit is what THIS device can hold
+  // of this kernel (fewer SMs under MIG / green contexts, another SKU), not a constant.
+  static int max_resident[64] = {0};
+  int dev = 0;
+  BSC_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return -2;
+  if (!max_resident[dev]) {
+    int sms = 0, per_sm = 0;
+    BSC_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    BSC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, krum_gram_fused_kernel, FG_THREADS, FG_SMEM));
+    max_resident[dev] = sms * per_sm;
+  }
+  if ((int)(grid.x * grid.y) > max_resident[dev]) return -5;
+  // The counters only grow and their targets are seq * (grid extent): a launch with another grid shape on the same
+  // counter buffer would wait for a count that never comes.  Allowed only together with seq == 1, i.e. after the
+  // caller has zeroed the counters and restarted its launch count.
+  {
+    static std::mutex mu;
+    static std::unordered_map<const void*, unsigned long long> shapes;
+    const unsigned long long shape = ((unsigned long long)grid.x << 32) | grid.y;
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = shapes.find(done_counter);
+    if (it == shapes.end() || seq == 1) shapes[done_counter] = shape;
+    else if (it->second != shape) return -6;
+  }
   krum_gram_fused_kernel<<<grid, FG_THREADS, FG_SMEM, (cudaStream_t)stream>>>(P);
   return finish_launch("krum_gram_fused");
 }

@@ -4,6 +4,8 @@ Field / rule parity: DistSys/block.go, blockData.go, update.go, blockchain.go, h
 """
 from __future__ import annotations
 
+import os
+
 import ctypes
 from dataclasses import dataclass, field
 
@@ -257,8 +259,14 @@ class Blockchain:
         return isinstance(other, Blockchain) and bool(self._L.bsc_chain_equal(self._h, other._h))
 
     def save(self, path: str):
-        with open(path, "wb") as f:
+        """Atomic: the bytes go to a temporary file that is renamed over `path`, so a process killed in the middle of a
+        checkpoint leaves the previous checkpoint intact."""
+        tmp = f"{path}.tmp.{os.getpid()}"
+        with open(tmp, "wb") as f:
             f.write(self.serialize())
+            f.flush()
+            os.fsync(f.fileno())
+        os.replace(tmp, path)
 
     @classmethod
     def load(cls, path: str) -> "Blockchain":

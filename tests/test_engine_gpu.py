@@ -27,13 +27,15 @@ def test_mnist_chain_on_gpu_is_deterministic_and_consistent(lib):
 
 
 def test_mnist_learns_and_krum_rejects_poisoners():
-    cfg = _cfg(num_nodes=40, max_iterations=14, poison_fraction=0.3, epsilon=2.0)
+    # rows of a class look alike ("lowrank"), poisoners train on source-class rows relabelled as the target class
+    # (mnist_bad), DP noise light enough (epsilon 8) for the distances to show: Multi-Krum must keep every poisoner out
+    cfg = _cfg(num_nodes=40, max_iterations=14, poison_fraction=0.3, epsilon=8.0, data_model="lowrank")
     e = BiscottiEngine(cfg, device="cuda:0")
     reps = e.run()
-    assert reps[-1].test_error < 0.5 * reps[0].test_error + 0.05
-    assert reps[-1].attack_rate is not None
-    assert 0.0 <= reps[-1].attack_rate <= 1.0
     assert len(e.poisoners) == 11 and e.chain.verify()
+    assert all(r.n_contributors >= 2 for r in reps)
+    assert not any(c in e.poisoners for r in reps for c in r.contributors)
+    assert reps[-1].test_error < 0.12 and max(r.attack_rate for r in reps[5:]) < 0.3
 
 
 def test_fedsys_mode_on_gpu():

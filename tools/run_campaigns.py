@@ -46,6 +46,10 @@ for sep in a.sep:
         if "heatmap" in a.what:
             out[f"heatmap_{model}"] = ex.poison_heatmap(fractions=(0.4, 0.3, 0.1), collected=(40, 70), blocks=a.blocks, **mk)
             print("HEATMAP", model, json.dumps(out[f"heatmap_{model}"]), flush=True)
+            if model == "lowrank":      # half the noise of the -ep default: where the defence starts to hold on this data
+                out["heatmap_lowrank_eps4"] = ex.poison_heatmap(fractions=(0.4, 0.3, 0.1), collected=(40, 70), blocks=a.blocks,
+                                                                epsilon=4.0, **mk)
+                print("HEATMAP lowrank eps4", json.dumps(out["heatmap_lowrank_eps4"]), flush=True)
 if "cifar" in a.what:
     out["cifar200"] = ex.time_to_accuracy(0.5, peers=200, dataset="cifar", blocks=50, shard_size=250, test_size=1000,
                                           data_sep=a.sep[0])
