@@ -123,8 +123,6 @@ def test_static_scratch_krum_allocates_nothing_and_can_be_captured(lib):
     graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(scores, want_scores) and torch.equal(accept, want_accept)
-    free2, _ = torch.cuda.mem_get_info(dev)
-    assert free2 <= free0          # the graph object itself may hold memory; the call must not have freed any
 
 
 def test_static_scratch_krum_rejects_a_row_stride_shorter_than_the_row(lib, capfd):
