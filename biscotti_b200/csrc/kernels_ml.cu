@@ -12,12 +12,14 @@
 #include "common.cuh"
 #include "secagg_math.cuh"
 #include "symm.cuh"
+#include "tc_ptx.cuh"
 #include <cuda_bf16.h>
 #include <mutex>
 
 namespace bsc {
 
 unsigned long long g_launch_count = 0;
+static bool g_softmax_simt = false;
 
 // ------------------------------------------------------------------------------------------------
 // K1: softmax regression, one CTA per peer.
@@ -120,6 +122,287 @@ __global__ void __launch_bounds__(256) local_softmax_step_kernel(
     out[(size_t)C * F + tid] = -coef * g;
   }
   for (int k = C * F + C + tid; k < ldu; k += blockDim.x) out[k] = 0.f;  // zero the padding
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1 on the tensor cores.  One CTA takes PPC peers (PPC * B <= 32 minibatch rows) and runs three phases:
+//   1. all threads gather the rows (fp32, shard-resident) and the weight matrix, split each value into bf16 hi + lo
+//      and store both planes straight into shared memory in the K-major 128-byte-swizzled layout tcgen05.mma reads
+//      (the whole K extent stays resident: 32 rows x 832 columns per plane);
+//   2. one thread issues the [128 x 16] += A[128 x 16] * W^T[16 x 16] UMMAs for every 16-column K step, three per
+//      step (hi*hi, hi*lo, lo*hi - the Gram kernel's fp32-grade split), accumulating the logits in TMEM.  The A tile
+//      is declared 128 rows tall; rows past PPC*B alias the next K blocks' bytes and produce TMEM lanes nobody reads;
+//   3. warp 0 pulls its 32 TMEM lanes (one minibatch row each), adds the bias and turns the logits into
+//      (softmax - onehot) / B and the row's loss; then every thread accumulates its columns of the PPC gradients in
+//      registers (exact fp32, rows re-read from L2), the global-norm clip factor is reduced per peer, and U is written.
+// Same inputs / outputs as local_softmax_step_kernel; C is fixed at 10 classes, F <= 1024 and F % 4 == 0.
+// ------------------------------------------------------------------------------------------------
+constexpr int LS_C = 10;            // classes
+constexpr int LS_NP = 16;           // padded N of the MMA
+constexpr int LS_ROWS = 32;         // minibatch rows per CTA (one TMEM lane quarter)
+constexpr int LS_THREADS = 512;
+constexpr int LS_KI = 2;            // columns per thread in the gradient phase (F <= LS_KI * LS_THREADS)
+constexpr int LS_A_KB_BYTES = LS_ROWS * 128;   // one 64-column K block of the A plane
+constexpr int LS_B_KB_BYTES = LS_NP * 128;
+constexpr int LS_A_TAIL = (128 - LS_ROWS) * 128;   // what the 128-row descriptor of the last K block reaches past its rows
+
+__device__ __forceinline__ uint32_t umma_idesc_bf16_128xN(uint32_t n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// fp32 x4 -> bf16 hi x4 and bf16 lo x4 (lo = bf16(x - hi)), packed as two 8-byte words
+__device__ __forceinline__ void split4(const float4 v, uint2& hi, uint2& lo) {
+  const __nv_bfloat162 h01 = __float22bfloat162_rn(make_float2(v.x, v.y)), h23 = __float22bfloat162_rn(make_float2(v.z, v.w));
+  const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+  const __nv_bfloat162 l01 = __float22bfloat162_rn(make_float2(v.x - f01.x, v.y - f01.y)),
+                       l23 = __float22bfloat162_rn(make_float2(v.z - f23.x, v.w - f23.y));
+  hi.x = *reinterpret_cast<const uint32_t*>(&h01);
+  hi.y = *reinterpret_cast<const uint32_t*>(&h23);
+  lo.x = *reinterpret_cast<const uint32_t*>(&l01);
+  lo.y = *reinterpret_cast<const uint32_t*>(&l23);
+}
+// byte offset of columns [4q, 4q+4) of row r inside a plane whose 64-column K blocks are kb_bytes apart
+__device__ __forceinline__ uint32_t sw128_off(int r, int q, int kb_bytes) {
+  const int kb = q >> 4, c = (q & 15) >> 1, half = (q & 1) << 3;
+  return (uint32_t)(kb * kb_bytes + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4) + half);
+}
+
+template <int PPC>
+__global__ void __launch_bounds__(LS_THREADS, 1) local_softmax_tc_kernel(
+    const float* __restrict__ w, const float* __restrict__ X, const int* __restrict__ y,
+    const int* __restrict__ idx, float* __restrict__ U, float* __restrict__ loss, int P, int Ns, int B, int F,
+    int ldu, float clip, int nkb) {
+  extern __shared__ uint8_t ls_smem[];
+  __shared__ const float* sRow[LS_ROWS];
+  __shared__ int sLab[LS_ROWS];
+  __shared__ float sDL[LS_ROWS][LS_NP];
+  __shared__ float sLoss[LS_ROWS];
+  __shared__ float sRed[PPC][LS_THREADS / 32];
+  __shared__ float sCoef[PPC];
+  __shared__ __align__(8) unsigned long long sBar;
+  __shared__ uint32_t sTmem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int p0 = blockIdx.x * PPC;
+  const int rows = PPC * B;                       // <= LS_ROWS
+  const uint32_t raw = smem_u32(ls_smem);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen = ls_smem + (base - raw);
+  const uint32_t a_plane = (uint32_t)nkb * LS_A_KB_BYTES + LS_A_TAIL, b_plane = (uint32_t)nkb * LS_B_KB_BYTES;
+  const uint32_t oAhi = 0, oAlo = a_plane, oBhi = 2 * a_plane, oBlo = 2 * a_plane + b_plane;
+  const uint32_t bar = smem_u32(&sBar);
+
+  if (tid < LS_ROWS) {
+    const int p = p0 + tid / B, b = tid % B;
+    const bool ok = tid < rows && p < P;
+    const int row = ok ? (idx ? idx[p * B + b] : b) : 0;
+    sRow[tid] = ok ? X + ((size_t)p * Ns + row) * F : nullptr;
+    sLab[tid] = ok ? y[(size_t)p * Ns + row] : 0;
+  }
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sTmem)), "r"(32)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sTmem;
+
+  // ---- phase 1: operands -> swizzled bf16 planes -----------------------------------------------------------
+  const int QP = nkb * 16;                        // float4 slots per padded row
+  const int F4 = F >> 2;
+  {
+    // only the rows that exist are staged (rows past `rows` of the 128-row tile are never read back from TMEM);
+    // their K padding must be zero, the loads of a batch are all in flight before the first conversion
+    constexpr int BATCH = 7;
+    const int items = rows * QP;
+    for (int it0 = tid; it0 < items; it0 += LS_THREADS * BATCH) {
+      float4 v[BATCH];
+      int rr[BATCH], qq[BATCH];
+#pragma unroll
+      for (int u = 0; u < BATCH; u++) {
+        const int it = it0 + u * LS_THREADS;
+        rr[u] = it / QP;
+        qq[u] = it - rr[u] * QP;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (it < items) {
+          const float* src = sRow[rr[u]];
+          if (src && qq[u] < F4) v[u] = __ldg(reinterpret_cast<const float4*>(src) + qq[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < BATCH; u++) {
+        if (it0 + u * LS_THREADS < items) {
+          uint2 hi, lo;
+          split4(v[u], hi, lo);
+          const uint32_t off = sw128_off(rr[u], qq[u], LS_A_KB_BYTES);
+          *reinterpret_cast<uint2*>(gen + oAhi + off) = hi;
+          *reinterpret_cast<uint2*>(gen + oAlo + off) = lo;
+        }
+      }
+    }
+    const int witems = LS_NP * QP;
+    for (int it = tid; it < witems; it += LS_THREADS) {
+      const int r = it / QP, q = it - r * QP;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < LS_C && q < F4) v = __ldg(reinterpret_cast<const float4*>(w + (size_t)r * F) + q);
+      uint2 hi, lo;
+      split4(v, hi, lo);
+      const uint32_t off = sw128_off(r, q, LS_B_KB_BYTES);
+      *reinterpret_cast<uint2*>(gen + oBhi + off) = hi;
+      *reinterpret_cast<uint2*>(gen + oBlo + off) = lo;
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the MMA's reads
+  __syncthreads();
+
+  // ---- phase 2: logits on the tensor cores ------------------------------------------------------------------
+  if (tid == 0) {
+    tc_fence_after();
+    const uint32_t idesc = umma_idesc_bf16_128xN(LS_NP);
+    for (int kb = 0; kb < nkb; kb++) {
+      const uint64_t a_hi = umma_desc_sw128(base + oAhi + kb * LS_A_KB_BYTES), a_lo = umma_desc_sw128(base + oAlo + kb * LS_A_KB_BYTES);
+      const uint64_t b_hi = umma_desc_sw128(base + oBhi + kb * LS_B_KB_BYTES), b_lo = umma_desc_sw128(base + oBlo + kb * LS_B_KB_BYTES);
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint64_t off = (uint64_t)((k * 16 * 2) >> 4);
+        umma_bf16(tmem, a_hi + off, b_hi + off, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        umma_bf16(tmem, a_hi + off, b_lo + off, idesc, 1u);
+        umma_bf16(tmem, a_lo + off, b_hi + off, idesc, 1u);
+      }
+    }
+    umma_commit(bar);
+  }
+  // ---- phase 3a: softmax / loss per row (warp 0 owns TMEM lanes 0..31) ---------------------------------------
+  if (warp == 0) {
+    mbar_wait(bar, 0);
+    tc_fence_after();
+    uint32_t v[16];
+    tmem_ld16(tmem, v);
+    float l[LS_C];
+    float m = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < LS_C; c++) {
+      l[c] = __uint_as_float(v[c]) + __ldg(w + (size_t)LS_C * F + c);
+      m = fmaxf(m, l[c]);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < LS_C; c++) s += expf(l[c] - m);
+    const float lse = m + logf(s);
+    const bool ok = sRow[lane] != nullptr;
+    const int lab = sLab[lane];
+    float myloss = 0.f;
+#pragma unroll
+    for (int c = 0; c < LS_C; c++) {
+      const float pr = expf(l[c] - lse);
+      sDL[lane][c] = ok ? (pr - (c == lab ? 1.f : 0.f)) / (float)B : 0.f;
+      if (c == lab) myloss = (lse - l[c]) / (float)B;
+    }
+    sLoss[lane] = ok ? myloss : 0.f;
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(32) : "memory");
+  }
+  if (tid < PPC && p0 + tid < P && loss) {
+    float t = 0.f;
+    for (int b = 0; b < B; b++) t += sLoss[tid * B + b];
+    loss[p0 + tid] = t;
+  }
+
+  // ---- phase 3b: gradients in registers, clip, write ----------------------------------------------------------
+  float g[PPC][LS_KI][LS_C];
+  float nrm[PPC];
+#pragma unroll
+  for (int j = 0; j < PPC; j++) {
+    nrm[j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < LS_KI; i++) {
+      const int k = tid + i * LS_THREADS;
+#pragma unroll
+      for (int c = 0; c < LS_C; c++) g[j][i][c] = 0.f;
+    }
+    if (p0 + j < P) {
+      // the rows were read a moment ago (phase 1) and sit in L2; all loads of a 10-row chunk are issued before the
+      // first FMA needs one, so a peer costs one L2 round trip per chunk instead of one per row
+      for (int b0 = 0; b0 < B; b0 += 10) {
+        float x[LS_KI][10];
+#pragma unroll
+        for (int i = 0; i < LS_KI; i++) {
+          const int k = tid + i * LS_THREADS;
+#pragma unroll
+          for (int u = 0; u < 10; u++) x[i][u] = (k < F && b0 + u < B) ? __ldg(sRow[j * B + b0 + u] + k) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 10; u++) {
+          if (b0 + u < B) {
+#pragma unroll
+            for (int c = 0; c < LS_C; c++) {
+              const float dl = sDL[j * B + b0 + u][c];
+#pragma unroll
+              for (int i = 0; i < LS_KI; i++) g[j][i][c] = fmaf(dl, x[i][u], g[j][i][c]);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < LS_KI; i++)
+#pragma unroll
+        for (int c = 0; c < LS_C; c++) nrm[j] = fmaf(g[j][i][c], g[j][i][c], nrm[j]);
+    }
+  }
+  float gb[PPC];                                   // bias gradient: thread c < C of each peer
+#pragma unroll
+  for (int j = 0; j < PPC; j++) {
+    gb[j] = 0.f;
+    if (tid < LS_C) {
+      for (int b = 0; b < B; b++) gb[j] += sDL[j * B + b][tid];
+      nrm[j] = fmaf(gb[j], gb[j], nrm[j]);
+    }
+    const float t = warp_sum(nrm[j]);
+    if (lane == 0) sRed[j][warp] = t;
+  }
+  __syncthreads();
+  if (tid < PPC) {
+    float t = 0.f;
+    for (int wi = 0; wi < LS_THREADS / 32; wi++) t += sRed[tid][wi];
+    // torch.nn.utils.clip_grad_norm: coef = max_norm / (total + 1e-6), applied when < 1
+    const float coef = clip / (sqrtf(t) + 1e-6f);
+    sCoef[tid] = coef > 1.f ? 1.f : coef;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < PPC; j++) {
+    if (p0 + j >= P) break;
+    const float coef = sCoef[j];
+    float* out = U + (size_t)(p0 + j) * ldu;
+#pragma unroll
+    for (int i = 0; i < LS_KI; i++) {
+      const int k = tid + i * LS_THREADS;
+      if (k < F) {
+#pragma unroll
+        for (int c = 0; c < LS_C; c++) out[(size_t)c * F + k] = -coef * g[j][i][c];
+      }
+    }
+    if (tid < LS_C) out[(size_t)LS_C * F + tid] = -coef * gb[j];
+    for (int k = LS_C * F + LS_C + tid; k < ldu; k += LS_THREADS) out[k] = 0.f;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -538,12 +821,39 @@ using namespace bsc;
 
 extern "C" {
 
+// test hook: 1 = keep K1 on the SIMT kernel (the tensor-core kernel is compared against it and against fp32 PyTorch)
+void bsc_softmax_force_simt(int on) { g_softmax_simt = on != 0; }
 unsigned long long bsc_launch_count() { return g_launch_count; }
 void bsc_launch_count_reset() { g_launch_count = 0; }
 
 int bsc_local_softmax_step(const float* w, const float* X, const int* y, const int* idx, float* U, float* loss,
                            int P, int Ns, int B, int F, int C, int ldu, float clip, void* stream) {
   if (B > 64 || C > 32) return -1;
+  if (C == LS_C && B <= LS_ROWS && (F & 3) == 0 && F <= LS_KI * LS_THREADS && !g_softmax_simt) {
+    // tensor-core path: PPC peers per CTA, all of K resident in shared memory
+    // as many CTAs as there are SMs to hold them: one peer per CTA up to 148 peers, then two, then three
+    const int ppc_max = B <= 10 ? 3 : (B <= 16 ? 2 : 1);
+    int ppc = (P + 147) / 148;
+    if (ppc > ppc_max) ppc = ppc_max;
+    if (ppc < 1) ppc = 1;
+    const int nkb = (F + 63) / 64;
+    const size_t smem_tc = 1024 + 2 * ((size_t)nkb * LS_A_KB_BYTES + LS_A_TAIL) + 2 * (size_t)nkb * LS_B_KB_BYTES;
+    if (smem_tc <= 220 * 1024) {
+      const int grid = (P + ppc - 1) / ppc;
+      static bool configured_tc = false;
+      if (!configured_tc) {
+        BSC_CHECK(cudaFuncSetAttribute(local_softmax_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        BSC_CHECK(cudaFuncSetAttribute(local_softmax_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        BSC_CHECK(cudaFuncSetAttribute(local_softmax_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        configured_tc = true;
+      }
+      cudaStream_t st = (cudaStream_t)stream;
+      if (ppc == 3) local_softmax_tc_kernel<3><<<grid, LS_THREADS, smem_tc, st>>>(w, X, y, idx, U, loss, P, Ns, B, F, ldu, clip, nkb);
+      else if (ppc == 2) local_softmax_tc_kernel<2><<<grid, LS_THREADS, smem_tc, st>>>(w, X, y, idx, U, loss, P, Ns, B, F, ldu, clip, nkb);
+      else local_softmax_tc_kernel<1><<<grid, LS_THREADS, smem_tc, st>>>(w, X, y, idx, U, loss, P, Ns, B, F, ldu, clip, nkb);
+      return finish_launch("local_softmax_tc");
+    }
+  }
   const size_t smem = ((size_t)B * F + (size_t)B * C + 64) * sizeof(float);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {

@@ -19,6 +19,9 @@ extern "C" {
 /* --------------------------------------------------------------------------------------------
  * kernels_ml.cu - Local steps, DP noise, Krum tail, evaluation.  Reference: ML/Pytorch/client.py:38-65, 136-172; ML/code/logistic_model.py:92-140; ML/Pytorch/client_obj.py:97-143; DistSys/main.go:1592-1660; DistSys/krum.go:77-166.
  * -------------------------------------------------------------------------------------------- */
+// test hook: 1 = keep K1 on the SIMT kernel (the tensor-core kernel is compared against it and against fp32 PyTorch)
+void bsc_softmax_force_simt(int on);
+
 unsigned long long bsc_launch_count();
 
 void bsc_launch_count_reset();
