@@ -21,6 +21,8 @@
 
 namespace bsc {
 
+static bool g_cnn_generic = false;
+
 struct Cnn1Shape {
   int IC, OC, K, pad, H, W;   // input channels, output channels, kernel, padding, input height/width
   int OH, OW, J, C, B;        // output height/width, J = OC*OH*OW, classes, batch
@@ -69,11 +71,24 @@ __global__ void __launch_bounds__(256) cnn1_fc_fwd_kernel(const float* __restric
   }
 }
 // one warp per peer: softmax, dl = (softmax - onehot)/B (written over logits), loss, fc.bias gradient
+// (fpart != null: the logits arrive as nchunk partial sums per image, fpart[chunk][img][c], and are first summed
+// in chunk order on top of the bias)
 __global__ void cnn1_loss_kernel(float* __restrict__ dl, const int* __restrict__ y, float* __restrict__ loss,
-                                 float* __restrict__ U, int ldu, int P, Cnn1Shape s) {
+                                 float* __restrict__ U, int ldu, int P, Cnn1Shape s, const float* __restrict__ fpart = nullptr,
+                                 int nchunk = 0, const float* __restrict__ fbias = nullptr, float gsign = 1.f) {
   const int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (p >= P) return;
   float* sl = dl + (size_t)p * s.B * s.C;
+  if (fpart) {
+    const size_t PB = (size_t)P * s.B;
+    for (int i = lane; i < s.B * s.C; i += 32) {
+      const int b = i / s.C, c = i - b * s.C;
+      float acc = 0.f;
+      for (int k = 0; k < nchunk; k++) acc += fpart[((size_t)k * PB + (size_t)p * s.B + b) * s.C + c];
+      sl[i] = acc + fbias[c];
+    }
+    __syncwarp();
+  }
   float myloss = 0.f;
   if (lane < s.B) {
     float m = -INFINITY;
@@ -94,7 +109,7 @@ __global__ void cnn1_loss_kernel(float* __restrict__ dl, const int* __restrict__
   if (lane < s.C) {
     float g = 0.f;
     for (int b = 0; b < s.B; b++) g += sl[b * s.C + lane];
-    U[(size_t)p * ldu + s.off_fb + lane] = g;   // unscaled gradient; cnn1_scale finishes it
+    U[(size_t)p * ldu + s.off_fb + lane] = gsign * g;   // unscaled gradient (or its negative); cnn1_scale finishes it
   }
 }
 
@@ -196,13 +211,293 @@ __global__ void __launch_bounds__(256) cnn1_coef_kernel(const float* __restrict_
   }
 }
 // grid (ceil(ldu/4096), P): U = -coef * grad, padding zeroed
+// negated = 1: the row already holds -grad, so a peer whose gradient is inside the clip radius (coef == 1, the common
+// case) only gets its padding zeroed and the pass over its d floats is skipped
 __global__ void __launch_bounds__(256) cnn1_scale_kernel(float* __restrict__ U, int ldu, const float* __restrict__ coef,
-                                                         Cnn1Shape s) {
+                                                         Cnn1Shape s, int negated = 0) {
   const int p = blockIdx.y;
-  const float m = -coef[p];
+  const float m = negated ? coef[p] : -coef[p];
   float* row = U + (size_t)p * ldu;
   const int k0 = blockIdx.x * 4096;
+  if (negated && m == 1.f) {
+    for (int k = max(k0, s.d) + threadIdx.x; k < min(ldu, k0 + 4096); k += blockDim.x) row[k] = 0.f;
+    return;
+  }
   for (int k = k0 + threadIdx.x; k < min(ldu, k0 + 4096); k += blockDim.x) row[k] = k < s.d ? row[k] * m : 0.f;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Shape-specialised kernels for the two reference one-conv models (mnist_cnn: IC 1, K 5, pad 4, OC 16;
+// cifar_cnn: IC 3, K 3, pad 3, OC 20; 10 classes).  Same math, same accumulation order and same scratch layout
+// as the generic kernels above (which stay as the fallback for other shapes); what changes is where the data
+// lives: tap and class loops are compile-time, so the accumulators are registers instead of local memory, the
+// convolution stages its zero-padded image once per CTA and computes all output channels of a position from
+// one register patch, the classifier keeps a slice of fc.weight in shared memory across many images, and the
+// weight gradient reduces its 4 x taps accumulators with warp shuffles instead of one block reduction per tap.
+// ---------------------------------------------------------------------------------------------------
+constexpr int FCF_JCHUNK = 1024;   // fc.weight columns a CTA of cnn1_fc_fwd_t keeps in shared memory
+constexpr int FCF_IMGS = 256;      // images per CTA of cnn1_fc_fwd_t
+constexpr int WG_OCB = 4;          // output channels per CTA of cnn1_conv_wgrad_t
+
+// grid PB: one image per CTA; thread -> output positions, all OC channels of a position from one register patch
+template <int IC, int K, int PAD, int OC>
+__global__ void __launch_bounds__(256) cnn1_conv_fwd_t(const float* __restrict__ w, const float* __restrict__ X,
+                                                       float* __restrict__ act, Cnn1Shape s) {
+  constexpr int TAPS = IC * K * K;
+  extern __shared__ float sm[];
+  float* sw = sm;                        // [OC][TAPS] then [OC] biases
+  float* sx = sm + OC * TAPS + OC;       // [IC][HP][WP] zero-padded image
+  const int HP = s.H + 2 * PAD, WP = s.W + 2 * PAD;
+  const int img = blockIdx.x, tid = threadIdx.x;
+  for (int i = tid; i < OC * TAPS + OC; i += 256) sw[i] = i < OC * TAPS ? w[s.off_cw + i] : w[s.off_cb + i - OC * TAPS];
+  for (int i = tid; i < IC * HP * WP; i += 256) sx[i] = 0.f;
+  __syncthreads();
+  const float* x = X + (size_t)img * IC * s.H * s.W;
+  for (int i = tid; i < IC * s.H * s.W; i += 256) {
+    const int ix = i % s.W, iy = (i / s.W) % s.H, ic = i / (s.W * s.H);
+    sx[(ic * HP + iy + PAD) * WP + ix + PAD] = x[i];
+  }
+  __syncthreads();
+  const int npos = s.OH * s.OW;
+  float* out = act + (size_t)img * OC * npos;
+  for (int pos = tid; pos < npos; pos += 256) {
+    const int oy = pos / s.OW, ox = pos - oy * s.OW;
+    float patch[TAPS];
+#pragma unroll
+    for (int ic = 0; ic < IC; ic++)
+#pragma unroll
+      for (int ky = 0; ky < K; ky++)
+#pragma unroll
+        for (int kx = 0; kx < K; kx++) patch[(ic * K + ky) * K + kx] = sx[(ic * HP + oy + ky) * WP + ox + kx];
+#pragma unroll 4
+    for (int oc = 0; oc < OC; oc++) {
+      float acc = sw[OC * TAPS + oc];
+#pragma unroll
+      for (int t = 0; t < TAPS; t++) acc = fmaf(sw[oc * TAPS + t], patch[t], acc);   // padded taps add exact zeros
+      out[(size_t)oc * npos + pos] = acc > 0.f ? acc : 0.f;
+    }
+  }
+}
+
+// grid (ceil(J / FCF_JCHUNK), ceil(PB / FCF_IMGS)): partial logits of a J slice, one warp per image;
+// part[chunk][img][c] (summed over the chunks in index order by cnn1_loss_kernel)
+template <int C>
+__global__ void __launch_bounds__(256) cnn1_fc_fwd_t(const float* __restrict__ w, const float* __restrict__ act,
+                                                     float* __restrict__ part, Cnn1Shape s, int PB) {
+  extern __shared__ float sW[];          // [C][FCF_JCHUNK]
+  const int j0 = blockIdx.x * FCF_JCHUNK, jn = min(FCF_JCHUNK, s.J - j0);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < C * FCF_JCHUNK; i += 256) {
+    const int c = i / FCF_JCHUNK, jj = i - c * FCF_JCHUNK;
+    sW[i] = jj < jn ? w[s.off_fw + (size_t)c * s.J + j0 + jj] : 0.f;
+  }
+  __syncthreads();
+  const int i0 = blockIdx.y * FCF_IMGS, i1 = min(PB, i0 + FCF_IMGS);
+  const int jn4 = jn >> 2;               // J and the chunk size are multiples of 4
+  // two images per pass: every fc.weight value read from shared memory feeds two accumulators
+  for (int img = i0 + warp; img < i1; img += 16) {
+    const bool two = img + 8 < i1;
+    const float4* a4 = reinterpret_cast<const float4*>(act + (size_t)img * s.J + j0);
+    const float4* b4 = reinterpret_cast<const float4*>(act + (size_t)(two ? img + 8 : img) * s.J + j0);
+    float acc[C], bcc[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) acc[c] = bcc[c] = 0.f;
+    for (int q = lane; q < jn4; q += 32) {
+      const float4 av = a4[q], bv = b4[q];
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        const float4 wv = *reinterpret_cast<const float4*>(sW + c * FCF_JCHUNK + 4 * q);
+        acc[c] = fmaf(av.x, wv.x, acc[c]);
+        acc[c] = fmaf(av.y, wv.y, acc[c]);
+        acc[c] = fmaf(av.z, wv.z, acc[c]);
+        acc[c] = fmaf(av.w, wv.w, acc[c]);
+        bcc[c] = fmaf(bv.x, wv.x, bcc[c]);
+        bcc[c] = fmaf(bv.y, wv.y, bcc[c]);
+        bcc[c] = fmaf(bv.z, wv.z, bcc[c]);
+        bcc[c] = fmaf(bv.w, wv.w, bcc[c]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+      acc[c] = warp_sum(acc[c]);
+      bcc[c] = warp_sum(bcc[c]);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        part[((size_t)blockIdx.x * PB + img) * C + c] = acc[c];
+        if (two) part[((size_t)blockIdx.x * PB + img + 8) * C + c] = bcc[c];
+      }
+    }
+  }
+}
+
+// grid (ceil(J/256), P): as cnn1_fc_bwd_kernel with the class loops unrolled (accumulators in registers)
+template <int C>
+__global__ void __launch_bounds__(256) cnn1_fc_bwd_t(const float* __restrict__ w, float* __restrict__ act,
+                                                     const float* __restrict__ dl, float* __restrict__ U, int ldu,
+                                                     float* __restrict__ partial, int nslots, Cnn1Shape s) {
+  __shared__ float sdl[32 * C];
+  __shared__ float red[40];
+  const int p = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int i = threadIdx.x; i < s.B * C; i += blockDim.x) sdl[i] = dl[(size_t)p * s.B * C + i];
+  __syncthreads();
+  float nrm = 0.f;
+  if (j < s.J) {
+    float wc[C], g[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+      wc[c] = w[s.off_fw + (size_t)c * s.J + j];
+      g[c] = 0.f;
+    }
+    float* a = act + (size_t)p * s.B * s.J + j;
+    for (int b = 0; b < s.B; b++) {
+      const float av = a[(size_t)b * s.J];
+      float da = 0.f;
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        const float d = sdl[b * C + c];
+        g[c] = fmaf(d, av, g[c]);
+        da = fmaf(d, wc[c], da);
+      }
+      a[(size_t)b * s.J] = av > 0.f ? da : 0.f;   // d(pre-activation)
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+      U[(size_t)p * ldu + s.off_fw + (size_t)c * s.J + j] = -g[c];   // the update is minus the gradient
+      nrm = fmaf(g[c], g[c], nrm);
+    }
+  }
+  const float t = block_sum(nrm, red);
+  if (threadIdx.x == 0) partial[(size_t)p * nslots + blockIdx.x] = t;
+}
+
+// grid (ceil(OC / WG_OCB), P): conv.weight / conv.bias gradients of WG_OCB output channels of one peer.  The zero-padded
+// images of the whole minibatch are staged in shared memory once (B x IC x HP x WP floats); a thread walks the
+// (image, position) pairs with the d(pre-activation) loads of WG_NB pairs in flight before the first is used, reads a
+// position's patch once and feeds WG_OCB x TAPS register accumulators; per-channel partial norms go to slot0 + oc.
+constexpr int WG_NB = 4;
+template <int IC, int K, int PAD, int OC>
+__global__ void __launch_bounds__(256) cnn1_conv_wgrad_t(const float* __restrict__ X, const float* __restrict__ dpre,
+                                                         float* __restrict__ U, int ldu, float* __restrict__ partial,
+                                                         int nslots, int slot0, Cnn1Shape s) {
+  constexpr int TAPS = IC * K * K;
+  extern __shared__ float sm[];
+  const int HP = s.H + 2 * PAD, WP = s.W + 2 * PAD, IMG = IC * HP * WP;
+  float* sx = sm;                                      // [B][IC][HP][WP]
+  float* sred = sm + (size_t)s.B * IMG;                // [8 warps][WG_OCB][TAPS + 1]
+  const int oc0 = blockIdx.x * WG_OCB, p = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int npos = s.OH * s.OW;
+  float acc[WG_OCB][TAPS], accb[WG_OCB];
+#pragma unroll
+  for (int o = 0; o < WG_OCB; o++) {
+    accb[o] = 0.f;
+#pragma unroll
+    for (int t = 0; t < TAPS; t++) acc[o][t] = 0.f;
+  }
+  for (int i = tid; i < s.B * IMG; i += 256) sx[i] = 0.f;
+  __syncthreads();
+  {
+    const float* x = X + (size_t)p * s.B * IC * s.H * s.W;
+    const int per = IC * s.H * s.W;
+    for (int i = tid; i < s.B * per; i += 256) {
+      const int b = i / per, r = i - b * per;
+      const int ix = r % s.W, iy = (r / s.W) % s.H, ic = r / (s.W * s.H);
+      sx[b * IMG + (ic * HP + iy + PAD) * WP + ix + PAD] = x[i];
+    }
+  }
+  __syncthreads();
+  const float* dp = dpre + (size_t)p * s.B * OC * npos;
+  const int total = s.B * npos;
+  for (int q0 = tid; q0 < total; q0 += 256 * WG_NB) {
+    float d[WG_NB][WG_OCB];
+    int xo[WG_NB];
+#pragma unroll
+    for (int u = 0; u < WG_NB; u++) {
+      const int q = q0 + u * 256;
+      const bool ok = q < total;
+      const int b = ok ? q / npos : 0, pos = ok ? q - b * npos : 0;
+      const int oy = pos / s.OW, ox = pos - oy * s.OW;
+      xo[u] = b * IMG + oy * WP + ox;
+#pragma unroll
+      for (int o = 0; o < WG_OCB; o++)
+        d[u][o] = (ok && oc0 + o < OC) ? __ldg(dp + ((size_t)b * OC + oc0 + o) * npos + pos) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < WG_NB; u++) {
+      const float* xb = sx + xo[u];
+#pragma unroll
+      for (int ic = 0; ic < IC; ic++)
+#pragma unroll
+        for (int ky = 0; ky < K; ky++)
+#pragma unroll
+          for (int kx = 0; kx < K; kx++) {
+            const float xv = xb[(ic * HP + ky) * WP + kx];
+#pragma unroll
+            for (int o = 0; o < WG_OCB; o++) acc[o][(ic * K + ky) * K + kx] = fmaf(d[u][o], xv, acc[o][(ic * K + ky) * K + kx]);
+          }
+#pragma unroll
+      for (int o = 0; o < WG_OCB; o++) accb[o] += d[u][o];
+    }
+  }
+  // fixed-shape reduction: lanes by shuffle, then the eight warps in index order
+#pragma unroll
+  for (int o = 0; o < WG_OCB; o++) {
+#pragma unroll
+    for (int t = 0; t < TAPS; t++) {
+      const float v = warp_sum(acc[o][t]);
+      if (lane == 0) sred[(warp * WG_OCB + o) * (TAPS + 1) + t] = v;
+    }
+    const float vb = warp_sum(accb[o]);
+    if (lane == 0) sred[(warp * WG_OCB + o) * (TAPS + 1) + TAPS] = vb;
+  }
+  __syncthreads();
+  if (tid < WG_OCB * (TAPS + 1)) {
+    const int o = tid / (TAPS + 1), t = tid - o * (TAPS + 1);
+    float g = 0.f;
+    for (int wi = 0; wi < 8; wi++) g += sred[(wi * WG_OCB + o) * (TAPS + 1) + t];
+    if (oc0 + o < OC) {
+      if (t < TAPS) U[(size_t)p * ldu + s.off_cw + (oc0 + o) * TAPS + t] = -g;
+      else U[(size_t)p * ldu + s.off_cb + oc0 + o] = -g;
+    }
+    sred[(0 * WG_OCB + o) * (TAPS + 1) + t] = g * g;    // warp 0's row is free now: squares for the channel norm
+  }
+  __syncthreads();
+  if (tid < WG_OCB && oc0 + tid < OC) {
+    float nrm = 0.f;
+    for (int t = 0; t <= TAPS; t++) nrm += sred[(0 * WG_OCB + tid) * (TAPS + 1) + t];
+    partial[(size_t)p * nslots + slot0 + oc0 + tid] = nrm;
+  }
+}
+
+template <int IC, int K, int PAD, int OC, int C>
+static int cnn1_local_step_t(const float* w, const float* X, const int* y, float* U, float* loss, float* act, float* dl,
+                             float* partial, float* coef, float* fpart, int P, int ldu, float clip, const Cnn1Shape& s,
+                             cudaStream_t st) {
+  constexpr int TAPS = IC * K * K;
+  const int PB = P * s.B, HP = s.H + 2 * PAD, WP = s.W + 2 * PAD;
+  const int nfc = (s.J + 255) / 256, nslots = nfc + OC;
+  const int nchunk = (s.J + FCF_JCHUNK - 1) / FCF_JCHUNK;
+  const size_t smem_fwd = (size_t)(OC * TAPS + OC + IC * HP * WP) * sizeof(float);
+  const size_t smem_fc = (size_t)C * FCF_JCHUNK * sizeof(float);
+  const size_t smem_wg = ((size_t)s.B * IC * HP * WP + 8 * WG_OCB * (TAPS + 1)) * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    BSC_CHECK(cudaFuncSetAttribute(cnn1_conv_fwd_t<IC, K, PAD, OC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    BSC_CHECK(cudaFuncSetAttribute(cnn1_fc_fwd_t<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    BSC_CHECK(cudaFuncSetAttribute(cnn1_conv_wgrad_t<IC, K, PAD, OC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    configured = true;
+  }
+  if (smem_fwd > 96 * 1024 || smem_wg > 220 * 1024) return -1;
+  cnn1_conv_fwd_t<IC, K, PAD, OC><<<PB, 256, smem_fwd, st>>>(w, X, act, s);
+  cnn1_fc_fwd_t<C><<<dim3(nchunk, (PB + FCF_IMGS - 1) / FCF_IMGS), 256, smem_fc, st>>>(w, act, fpart, s, PB);
+  cnn1_loss_kernel<<<(P + 3) / 4, 128, 0, st>>>(dl, y, loss, U, ldu, P, s, fpart, nchunk, w + s.off_fb, -1.f);
+  cnn1_fc_bwd_t<C><<<dim3(nfc, P), 256, 0, st>>>(w, act, dl, U, ldu, partial, nslots, s);
+  cnn1_conv_wgrad_t<IC, K, PAD, OC><<<dim3((OC + WG_OCB - 1) / WG_OCB, P), 256, smem_wg, st>>>(X, act, U, ldu, partial, nslots,
+                                                                                             nfc, s);
+  cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
+  cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s, 1);
+  return finish_launch("cnn1_local_step", 7);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -383,12 +678,17 @@ using namespace bsc;
 
 extern "C" {
 
-// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P]
+// test hook: 1 = keep the one-conv models on the generic kernels (the shape-specialised ones are compared against them)
+void bsc_cnn_force_generic(int on) { g_cnn_generic = on != 0; }
+
+// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P],
+// fpart [ceil(J/1024)][P*B][C]
 long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, int H, int W, int C) {
   const int OH = H + 2 * pad - K + 1, OW = W + 2 * pad - K + 1;
   const long long J = (long long)OC * OH * OW;
   const long long nslots = (J + 255) / 256 + OC;
-  return (long long)P * B * J + (long long)P * B * C + (long long)P * nslots + P;
+  const long long nchunk = (J + FCF_JCHUNK - 1) / FCF_JCHUNK;   // partial logits of the shape-specialised classifier
+  return (long long)P * B * J + (long long)P * B * C + (long long)P * nslots + P + nchunk * P * B * C;
 }
 
 // One-conv-layer CNN local step for P peers.  w: flat global weights; X: [P][B][IC][H][W]; y: [P][B];
@@ -415,6 +715,13 @@ int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, 
   float* dl = act + (size_t)P * B * s.J;
   float* partial = dl + (size_t)P * B * C;
   float* coef = partial + (size_t)P * nslots;
+  float* fpart = coef + P;
+  if (C == 10 && (s.J & 3) == 0 && !g_cnn_generic) {
+    if (IC == 3 && K == 3 && pad == 3 && OC == 20)
+      return cnn1_local_step_t<3, 3, 3, 20, 10>(w, X, y, U, loss, act, dl, partial, coef, fpart, P, ldu, clip, s, st);
+    if (IC == 1 && K == 5 && pad == 4 && OC == 16)
+      return cnn1_local_step_t<1, 5, 4, 16, 10>(w, X, y, U, loss, act, dl, partial, coef, fpart, P, ldu, clip, s, st);
+  }
   const long long total = (long long)P * B * s.J;
   const int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
   const size_t smem = (size_t)(OC * IC * K * K + OC) * sizeof(float);

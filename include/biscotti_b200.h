@@ -489,7 +489,11 @@ void bsc_schnorr_finish64_host(const unsigned char* T64, const unsigned char* k_
 /* --------------------------------------------------------------------------------------------
  * kernels_cnn.cu - 
  * -------------------------------------------------------------------------------------------- */
-// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P]
+// test hook: 1 = keep the one-conv models on the generic kernels (the shape-specialised ones are compared against them)
+void bsc_cnn_force_generic(int on);
+
+// scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P],
+// fpart [ceil(J/1024)][P*B][C]
 long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, int H, int W, int C);
 
 // One-conv-layer CNN local step for P peers.  w: flat global weights; X: [P][B][IC][H][W]; y: [P][B];

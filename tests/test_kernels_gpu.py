@@ -325,6 +325,35 @@ def test_cnn_local_step_kernels_match_autograd(kind):
     assert abs(float(out[0, :d].norm()) - 0.05) < 1e-3
 
 
+@pytest.mark.parametrize("kind", ["mnist_cnn", "cifar_cnn"])
+def test_cnn_shape_specialised_kernels_match_generic_kernels(lib, kind):
+    """The register-resident kernels for the two reference one-conv shapes against the generic ones, at a size that
+    spans several image groups of the classifier kernel (P*B = 310 > 256) and leaves the last channel group of the
+    weight-gradient kernel partly filled where OC is not a multiple of 4."""
+    from biscotti_b200.models.registry import CNN_ARCH, cnn_param_slices
+    from biscotti_b200.ops import cnn_native
+
+    arch = CNN_ARCH[kind]
+    _, d = cnn_param_slices(arch)
+    torch.manual_seed(9)
+    P, B = 31, 10
+    F = arch["image"][0] * arch["image"][1] * arch["image"][2]
+    w = (torch.randn(d) * 0.02).to(DEV)
+    Xb = torch.randn(P, B, F, device=DEV)
+    yb = torch.randint(0, arch["n_classes"], (P, B), dtype=torch.int32, device=DEV)
+    a, b = torch.zeros(P, d + 2, device=DEV), torch.zeros(P, d + 2, device=DEV)
+    lib.bsc_cnn_force_generic(1)
+    try:
+        cnn_native.local_step(kind, w, Xb, yb, 100.0, a)
+        torch.cuda.synchronize()
+    finally:
+        lib.bsc_cnn_force_generic(0)
+    cnn_native.local_step(kind, w, Xb, yb, 100.0, b)
+    torch.cuda.synchronize()
+    scale = float(a.abs().max())
+    assert scale > 0 and torch.allclose(a, b, rtol=1e-4, atol=1e-6 * max(1.0, scale)), float((a - b).abs().max())
+
+
 @pytest.mark.parametrize("M,N,F,C,with_base", [(1, 2000, 784, 10, False), (70, 2000, 784, 10, True), (9, 333, 100, 2, True),
                                                (17, 128, 64, 16, False)])
 def test_eval_on_tensor_cores_matches_fp32_oracle(M, N, F, C, with_base, monkeypatch):

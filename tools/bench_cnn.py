@@ -32,3 +32,13 @@ for kind in kinds:
     e1.record()
     torch.cuda.synchronize()
     print(f"BENCH_CNN {kind} P={P} B={B} d={d}: {e0.elapsed_time(e1) / 10:.3f} ms per local step", flush=True)
+    if os.environ.get("PROFILE"):
+        from torch.profiler import ProfilerActivity, profile
+
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(5):
+                cnn_native.local_step(kind, w, X, y, 100.0, out)
+            torch.cuda.synchronize()
+        rows = sorted(((e.key, e.device_time_total / 5) for e in prof.key_averages() if e.device_time_total > 0), key=lambda kv: -kv[1])
+        for k, us in rows[:10]:
+            print(f"    {us:9.1f} us  {k[:100]}", flush=True)
