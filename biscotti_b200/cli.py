@@ -43,6 +43,7 @@ def add_protocol_flags(ap: argparse.ArgumentParser):
     ap.add_argument("--tau", type=int, default=2, help="SRS trapdoor (2 = reference compat, 0 = random)")
     ap.add_argument("--comm", default="fused", choices=["nccl", "fused"], help="multi-GPU path: fused peer-memory kernels (default) or the NCCL baseline")
     ap.add_argument("--gram", default="auto")
+    ap.add_argument("--msm-table-gb", type=float, default=None, help="HBM budget of the MSM window tables in GiB (default: half the device)")
     ap.add_argument("--print-hash", action="store_true")
     ap.add_argument("--no-dump", action="store_true")
     ap.add_argument("--log", action="store_true", help="emit [peer] log lines on stderr")
@@ -64,7 +65,7 @@ def config_from_args(a, mode: str):
     kw = dict(num_nodes=a.num_nodes, dataset=a.dataset, num_miners=a.na, num_verifiers=a.nv, num_noisers=a.nn,
               secure_agg=a.sa, noising=a.np, verification=a.vp, epsilon=a.ep, poison_fraction=a.po, perc_samples=ns,
               random_sampling=a.rs, colluders=a.c, defense=a.defense, max_iterations=a.iterations, seed=a.seed,
-              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm, data_dir=a.data_dir,
+              fail_prob=a.fail_prob, srs_tau=a.tau, mode=mode, gram_impl=a.gram, comm_impl=a.comm, data_dir=a.data_dir, msm_table_gb=a.msm_table_gb,
               partitions=tuple(tuple(int(v) for v in x.split(":")) for x in a.partition))
     if a.shard_size:
         kw["shard_size"] = a.shard_size

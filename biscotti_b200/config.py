@@ -87,6 +87,10 @@ class BiscottiConfig:
     test_size: int = 2000
     eval_every: int = 1               # reference evaluates every block (honest.go:141-162)
     msm_window: int | None = None     # fixed-base window bits for the MSM tables (None = largest that fits HBM budget)
+    msm_table_gb: float | None = None # HBM budget of the MSM window tables in GiB (None = half of the device; the
+                                      # BISCOTTI_MSM_TABLE_GB environment variable overrides both).  The constructor
+                                      # picks the widest table layout that fits: two-width (13,8) / (12,9) / (11,10) bit
+                                      # windows, then uniform 7..3 bit windows
     affine_wire: bool = False         # True: normalise every chunk commitment / witness to the 64-byte affine
                                       # wire form (kyber.go:88-168) even though no wire exists between GPUs
     data_sep: float = 3.6             # synthetic data: distance scale of the class prototypes.  3.6 makes the ten classes

@@ -470,6 +470,54 @@ __global__ void __launch_bounds__(256) cnn1_conv_wgrad_t(const float* __restrict
   }
 }
 
+// thread -> one image: logits = bias + partial sums in chunk order, arg-max against the label (first maximum wins, as
+// torch.argmax does), one atomicAdd per warp
+template <int C>
+__global__ void __launch_bounds__(256) cnn1_eval_count_t(const float* __restrict__ fpart, int nchunk, const float* __restrict__ fbias,
+                                                         const int* __restrict__ y, int N, int* __restrict__ wrong) {
+  const int img = blockIdx.x * blockDim.x + threadIdx.x;
+  bool bad = false;
+  if (img < N) {
+    float best = -INFINITY;
+    int arg = 0;
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+      float acc = 0.f;
+      for (int k = 0; k < nchunk; k++) acc += fpart[((size_t)k * N + img) * C + c];
+      acc += fbias[c];
+      if (acc > best) {
+        best = acc;
+        arg = c;
+      }
+    }
+    bad = arg != y[img];
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(wrong, __popc(m));
+}
+
+template <int IC, int K, int PAD, int OC, int C>
+static int cnn1_eval_t(const float* w, const float* X, const int* y, int* wrong, float* act, float* fpart, int N,
+                       const Cnn1Shape& s, cudaStream_t st) {
+  constexpr int TAPS = IC * K * K;
+  const int HP = s.H + 2 * PAD, WP = s.W + 2 * PAD;
+  const int nchunk = (s.J + FCF_JCHUNK - 1) / FCF_JCHUNK;
+  const size_t smem_fwd = (size_t)(OC * TAPS + OC + IC * HP * WP) * sizeof(float);
+  const size_t smem_fc = (size_t)C * FCF_JCHUNK * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    BSC_CHECK(cudaFuncSetAttribute(cnn1_conv_fwd_t<IC, K, PAD, OC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    BSC_CHECK(cudaFuncSetAttribute(cnn1_fc_fwd_t<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    configured = true;
+  }
+  if (smem_fwd > 96 * 1024) return -1;
+  BSC_CHECK(cudaMemsetAsync(wrong, 0, sizeof(int), st));
+  cnn1_conv_fwd_t<IC, K, PAD, OC><<<N, 256, smem_fwd, st>>>(w, X, act, s);
+  cnn1_fc_fwd_t<C><<<dim3(nchunk, (N + FCF_IMGS - 1) / FCF_IMGS), 256, smem_fc, st>>>(w, act, fpart, s, N);
+  cnn1_eval_count_t<C><<<(N + 255) / 256, 256, 0, st>>>(fpart, nchunk, w + s.off_fb, y, N, wrong);
+  return finish_launch("cnn1_eval", 3);
+}
+
 template <int IC, int K, int PAD, int OC, int C>
 static int cnn1_local_step_t(const float* w, const float* X, const int* y, float* U, float* loss, float* act, float* dl,
                              float* partial, float* coef, float* fpart, int P, int ldu, float clip, const Cnn1Shape& s,
@@ -733,6 +781,40 @@ int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, 
   cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
   cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s);
   return finish_launch("cnn1_local_step", 7);
+}
+
+// Error count of one weight vector over N images with the one-conv model (K14 for the CNN families; the reference
+// runs the torch module, ML/Pytorch/client.py:136-172).  wrong: int32[1] out (zeroed here); scratch:
+// bsc_cnn1_eval_scratch_floats floats.  Only the two reference shapes with 10 classes are supported (-1 otherwise: the
+// caller falls back to the framework's convolution).
+long long bsc_cnn1_eval_scratch_floats(int N, int IC, int OC, int K, int pad, int H, int W, int C) {
+  const int OH = H + 2 * pad - K + 1, OW = W + 2 * pad - K + 1;
+  const long long J = (long long)OC * OH * OW;
+  return (long long)N * J + ((J + FCF_JCHUNK - 1) / FCF_JCHUNK) * N * C;
+}
+
+int bsc_cnn1_eval_errors(const float* w, const float* X, const int* y, int* wrong, float* scratch, int N, int IC, int OC,
+                         int K, int pad, int H, int W, int C, void* stream) {
+  Cnn1Shape s;
+  s.IC = IC; s.OC = OC; s.K = K; s.pad = pad; s.H = H; s.W = W;
+  s.OH = H + 2 * pad - K + 1;
+  s.OW = W + 2 * pad - K + 1;
+  s.J = OC * s.OH * s.OW;
+  s.C = C;
+  s.B = 1;
+  s.off_cw = 0;
+  s.off_cb = OC * IC * K * K;
+  s.off_fw = s.off_cb + OC;
+  s.off_fb = s.off_fw + C * s.J;
+  s.d = s.off_fb + C;
+  float* act = scratch;
+  float* fpart = act + (size_t)N * s.J;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (C == 10 && (s.J & 3) == 0) {
+    if (IC == 3 && K == 3 && pad == 3 && OC == 20) return cnn1_eval_t<3, 3, 3, 20, 10>(w, X, y, wrong, act, fpart, N, s, st);
+    if (IC == 1 && K == 5 && pad == 4 && OC == 16) return cnn1_eval_t<1, 5, 4, 16, 10>(w, X, y, wrong, act, fpart, N, s, st);
+  }
+  return -1;
 }
 
 // ---- two-convolution model (conv+ReLU+MaxPool2 twice, then a linear head) ------------------------------------

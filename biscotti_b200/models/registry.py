@@ -148,6 +148,13 @@ class Model:
             w = Wc[m, : self.d].float()
             if base is not None:
                 w = w + base[: self.d].float()
+            if X.is_cuda:
+                from ..ops import cnn_native
+
+                e = cnn_native.eval_errors(self.kind, w, X, y)
+                if e is not None:
+                    errs.append(e)
+                    continue
             logits = cnn_forward(self.arch, _unflatten(self.arch, w), X.float().view(X.shape[0], *self.arch["image"]))
             errs.append((logits.argmax(-1) != y.long()).float().mean())
         return torch.stack(errs)

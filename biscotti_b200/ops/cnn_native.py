@@ -39,6 +39,40 @@ def local_step(kind: str, w32: torch.Tensor, Xb: torch.Tensor, yb: torch.Tensor,
     return out
 
 
+_eval_scratch = {}
+
+
+def eval_errors(kind: str, w32: torch.Tensor, X: torch.Tensor, y: torch.Tensor):
+    """Error rate of one flat weight vector over X [N, IC*H*W] with the one-conv model, on the local-step kernels
+    (convolution + classifier partial sums) and an arg-max count; None when the shape has no native path."""
+    from ..models.registry import CNN_ARCH
+
+    arch = CNN_ARCH[kind]
+    if len(arch["convs"]) != 1 or not X.is_cuda:
+        return None
+    c = arch["convs"][0]
+    IC, H, W = arch["image"]
+    N = X.shape[0]
+    L = _native.load()
+    L.bsc_cnn1_eval_scratch_floats.restype = ctypes.c_longlong
+    n = L.bsc_cnn1_eval_scratch_floats(N, IC, c.cout, c.k, c.pad, H, W, arch["n_classes"])
+    key = (X.device, n)
+    buf = _eval_scratch.get(key)
+    if buf is None:
+        _eval_scratch.clear()
+        buf = (torch.empty(n, dtype=torch.float32, device=X.device), torch.zeros(1, dtype=torch.int32, device=X.device))
+        _eval_scratch[key] = buf
+    Xc = X.contiguous().float()
+    yc = y.contiguous().int()
+    wc = w32.contiguous().float()
+    rc = L.bsc_cnn1_eval_errors(ptr(wc), ptr(Xc), ptr(yc), ptr(buf[1]), ptr(buf[0]), N, IC, c.cout, c.k, c.pad, H, W,
+                                arch["n_classes"], stream(X.device))
+    if rc == -1:
+        return None
+    check(rc, "cnn1_eval_errors")
+    return buf[1].float()[0] / N
+
+
 def _scratch_buf(device, n):
     key = (device, n)
     buf = _scratch.get(key)

@@ -221,14 +221,15 @@ class BiscottiEngine:
         self.commit = None
         if cfg.commitments and cfg.secure_agg and cfg.mode == "biscotti":
             self.commit = CommitmentEngine(self.d, self.S, tau=cfg.srs_tau or self._random_tau(), device=self.device,
-                                           window=cfg.msm_window)
+                                           window=cfg.msm_window,
+                                           table_budget_bytes=None if cfg.msm_table_gb is None else int(cfg.msm_table_gb * (1 << 30)))
         self.vrf = cp.BatchedVRF([k.vrf_noise for k in self.keys], self.device)
         self.signer = None
         if cfg.verification and cfg.sign_approvals and self.commit is not None:
             self.signer = ApprovalSigner(self.device, [k.schnorr_secret for k in self.keys])
         # Nonce salt of the approvals: binds the run (seed, data, every flag) - the previous block hash binds the fork.
         # (Scheduling knobs - prefetch, pipeline, kernel choices - do not change what is signed and stay out of it.)
-        sched = {"prefetch", "pipeline", "gram_impl", "comm_impl", "msm_window", "affine_wire", "eval_every", "extra",
+        sched = {"prefetch", "pipeline", "gram_impl", "comm_impl", "msm_window", "msm_table_gb", "affine_wire", "eval_every", "extra",
                  "max_iterations", "test_size", "lookahead", "native_schedule"}
         self.run_salt = hashlib.sha256(("bsc-run-salt|" + repr(sorted((k, v) for k, v in cfg.to_dict().items()
                                                                         if k not in sched))).encode()).digest()

@@ -500,6 +500,14 @@ long long bsc_cnn1_scratch_floats(int P, int B, int IC, int OC, int K, int pad, 
 // U: [P][ldu] out (= -clip(grad)); loss: [P] (may be null); scratch: see bsc_cnn1_scratch_floats.
 int bsc_cnn1_local_step(const float* w, const float* X, const int* y, float* U, float* loss, float* scratch, int P, int B, int IC, int OC, int K, int pad, int H, int W, int C, int ldu, float clip, void* stream);
 
+// Error count of one weight vector over N images with the one-conv model (K14 for the CNN families; the reference
+// runs the torch module, ML/Pytorch/client.py:136-172).  wrong: int32[1] out (zeroed here); scratch:
+// bsc_cnn1_eval_scratch_floats floats.  Only the two reference shapes with 10 classes are supported (-1 otherwise: the
+// caller falls back to the framework's convolution).
+long long bsc_cnn1_eval_scratch_floats(int N, int IC, int OC, int K, int pad, int H, int W, int C);
+
+int bsc_cnn1_eval_errors(const float* w, const float* X, const int* y, int* wrong, float* scratch, int N, int IC, int OC, int K, int pad, int H, int W, int C, void* stream);
+
 // scratch (floats): pool1 [PB*n1], dp1 [PB*n1], act [PB*J], dl [PB*C], partial [P*nslots], coef [P],
 // arg1 bytes [PB*n1], arg2 bytes [PB*J] (each rounded up to whole floats)
 long long bsc_cnn2_scratch_floats(int P, int B, int IC, int H, int W, int OC1, int K1, int pad1, int OC2, int K2, int pad2, int C);

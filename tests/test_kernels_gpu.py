@@ -354,6 +354,32 @@ def test_cnn_shape_specialised_kernels_match_generic_kernels(lib, kind):
     assert scale > 0 and torch.allclose(a, b, rtol=1e-4, atol=1e-6 * max(1.0, scale)), float((a - b).abs().max())
 
 
+@pytest.mark.parametrize("kind", ["mnist_cnn", "cifar_cnn"])
+def test_cnn_native_eval_matches_torch_forward(kind):
+    """Error rate from the native kernels (conv + classifier partial sums + arg-max count) against F.conv2d / F.linear."""
+    from biscotti_b200.models.registry import CNN_ARCH, _unflatten, cnn_forward, cnn_param_slices
+    from biscotti_b200.ops import cnn_native
+
+    arch = CNN_ARCH[kind]
+    _, d = cnn_param_slices(arch)
+    torch.manual_seed(10)
+    N = 300
+    F = arch["image"][0] * arch["image"][1] * arch["image"][2]
+    w = (torch.randn(d) * 0.02).to(DEV)
+    X = torch.randn(N, F, device=DEV)
+    logits = cnn_forward(arch, _unflatten(arch, w), X.view(N, *arch["image"]))
+    pred = logits.argmax(-1)
+    y = pred.clone().int()
+    y[::3] = (y[::3] + 1) % arch["n_classes"]            # a third of the labels made wrong on purpose
+    # leave out images whose top two logits are within rounding of each other
+    top2 = logits.topk(2, dim=-1).values
+    clear = (top2[:, 0] - top2[:, 1]) > 1e-4
+    want = float((pred[clear] != y[clear].long()).float().sum())
+    got = cnn_native.eval_errors(kind, w, X[clear].contiguous(), y[clear].contiguous())
+    assert got is not None
+    assert abs(float(got) * int(clear.sum()) - want) < 0.5
+
+
 @pytest.mark.parametrize("M,N,F,C,with_base", [(1, 2000, 784, 10, False), (70, 2000, 784, 10, True), (9, 333, 100, 2, True),
                                                (17, 128, 64, 16, False)])
 def test_eval_on_tensor_cores_matches_fp32_oracle(M, N, F, C, with_base, monkeypatch):

@@ -22,10 +22,11 @@ ap.add_argument("--poison", type=float, default=0.0)
 ap.add_argument("--epsilon", type=float, default=2.0)
 ap.add_argument("--shard-size", type=int, default=600)
 ap.add_argument("--affine-wire", action="store_true")
+ap.add_argument("--msm-table-gb", type=float, default=None)
 a = ap.parse_args()
 
 cfg = BiscottiConfig(num_nodes=a.peers, dataset=a.dataset, max_iterations=a.steps + a.warmup + 4, poison_fraction=a.poison,
-                     epsilon=a.epsilon, shard_size=a.shard_size, affine_wire=a.affine_wire)
+                     epsilon=a.epsilon, shard_size=a.shard_size, affine_wire=a.affine_wire, msm_table_gb=a.msm_table_gb)
 t0 = time.perf_counter()
 eng = BiscottiEngine(cfg, device="cuda:0")
 torch.cuda.synchronize()
@@ -47,5 +48,6 @@ out = {"dataset": a.dataset, "peers": a.peers, "d": cfg.dim, "init_s": round(ini
        "secagg_us": round(1e3 * (r.phase_ms.get("witness", 0) + r.phase_ms.get("miner_aggregate", 0) + r.phase_ms.get("secagg", 0)), 1),
        "contributors": r.n_contributors, "krum_set": r.n_krum, "test_error": r.test_error, "attack_rate": r.attack_rate,
        "bad_shares": sum(x.bad_shares for x in eng.reports), "mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2),
-       "msm_window": [eng.commit.w, eng.commit.nw] if eng.commit else None, "chain_ok": eng.chain.verify()}
+       "msm_window": [eng.commit.w, eng.commit.nwin, eng.commit.w1] if eng.commit else None,
+       "msm_table_gb": round(eng.commit.table_bytes / 2**30, 2) if eng.commit else None, "chain_ok": eng.chain.verify()}
 print("RUN_CONFIG " + json.dumps(out))
