@@ -2,7 +2,7 @@
 # 1/2/4/8-GPU strong scaling of bench.py on one box, chain equality check and fused-kernel microbenchmarks at the largest N
 mkdir -p gpurun_out
 MAXN=${1:-8}
-for N in 1 2 4 8; do
+for N in ${ONLY:-1 2 4 8}; do
   [ $N -gt $MAXN ] && break
   if [ $N -eq 1 ]; then
     timeout 300 python bench.py --gpus 1 --steps 60 --warmup 25 > gpurun_out/scale_$N.json 2> gpurun_out/scale_$N.err
