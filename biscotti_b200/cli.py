@@ -220,7 +220,7 @@ def run_experiment(a) -> int:
             kw["blocks"] = a.blocks
     rows = fn(**kw)
     if a.csv:
-        ex.write_csv(rows, a.csv)
+        ex.write_csv(rows if isinstance(rows, list) else [rows], a.csv)
     print(json.dumps(rows, indent=1))
     return 0
 
@@ -280,7 +280,7 @@ def main(argv=None) -> int:
     sub.add_parser("vrf-demo")
     sub.add_parser("kzg-demo")
     exp = sub.add_parser("experiment")
-    exp.add_argument("name", choices=["cost_breakdown", "fedsys_scale", "committee_scale", "noise_krum", "poison_heatmap",
+    exp.add_argument("name", choices=["time_to_accuracy", "cost_breakdown", "fedsys_scale", "committee_scale", "noise_krum", "poison_heatmap",
                                       "privacy_utility", "churn", "committee_capture", "unmasked_probability"])
     exp.add_argument("--device", default="auto")
     exp.add_argument("--blocks", type=int, default=None)

@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""cuobjdump -sass of the in-tree objects -> profiles/sass_evidence.md (tcgen05 / TMA / TMEM mnemonic counts)."""
+"""cuobjdump -sass of the in-tree objects -> profiles/sass_evidence.md: tcgen05 / TMA / TMEM mnemonic counts per kernel and,
+for the tensor-core kernels, the SASS of the producer (TMA issue) and MMA-issue loop bodies as ptxas emitted them."""
 import collections
 import os
 import re
@@ -8,11 +9,21 @@ import subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "biscotti_b200/lib/obj")
 WANT = ["UTCHMMA", "UTMALDG", "LDTM", "UTCBAR", "SYNCS", "IMAD.WIDE.U32", "SHFL"]
-KEEP = ("msm_table_kernel<4>", "ed25519_scalarmult_quad_kernel", "secagg_fused_kernel", "g1_comb_mul_kernel")
+KEEP = ("msm_table_kernel<4>", "ed25519_scalarmult_wide_kernel", "secagg_fused_kernel", "g1_comb_mul_kernel")
+EXCERPT = ("gram_tc_kernel", "eval_tc_kernel", "krum_gram_fused_kernel", "local_softmax_tc_kernel<1>")
 rows = []
+excerpts = []
+
+
+def clean(line):
+    """'        /*0a30*/   UTCHMMA gdesc[UR20], ... ;   /* 0x... */' -> '/*0a30*/ UTCHMMA gdesc[UR20], ... ;'"""
+    m = re.match(r"\s+(/\*[0-9a-f]{4,}\*/)\s+(.*?;)", line)
+    return f"{m.group(1)} {m.group(2)}" if m else None
+
 for o in sorted(f for f in os.listdir(OBJ) if f.endswith(".o")):
     out = subprocess.run(["cuobjdump", "-sass", os.path.join(OBJ, o)], capture_output=True, text=True).stdout
     cur, cnt = None, collections.defaultdict(collections.Counter)
+    body = collections.defaultdict(list)
     for line in out.splitlines():
         m = re.search(r"Function : (\S+)", line)
         if m:
@@ -20,12 +31,29 @@ for o in sorted(f for f in os.listdir(OBJ) if f.endswith(".o")):
             continue
         if cur and re.match(r"\s+/\*[0-9a-f]{4,}\*/", line):
             cnt[cur]["total"] += 1
+            c = clean(line)
+            if c:
+                body[cur].append(c)
             for w in WANT:
                 if re.search(r"\b" + re.escape(w), line):
                     cnt[cur][w] += 1
     for k, c in cnt.items():
         if any(c[w] for w in ("UTCHMMA", "UTMALDG", "LDTM")) or k.endswith(KEEP):
             rows.append((o, k, c))
+        if k.endswith(EXCERPT):
+            ins = body[k]
+            for what, pat in (("TMA producer", "UTMALDG"), ("MMA issue", "UTCHMMA"), ("TMEM read-back", "LDTM")):
+                hits = [i for i, l in enumerate(ins) if pat in l]
+                if not hits:
+                    continue
+                # from a few instructions before the first hit to the loop's closing branch after the last (capped)
+                lo = max(0, hits[0] - 6)
+                hi = hits[-1] + 1
+                while hi < len(ins) and hi < hits[-1] + 14 and " BRA" not in ins[hi - 1]:
+                    hi += 1
+                if hi - lo > 90:      # many unrolled copies: keep the first ones
+                    hi = lo + 90
+                excerpts.append((o, k, what, ins[lo:hi]))
 with open(os.path.join(ROOT, "profiles/sass_evidence.md"), "w") as f:
     f.write("# SASS evidence (cuobjdump -sass of the in-tree objects, sm_100a)\n\n")
     f.write("Mnemonics per the profiling recipe: `UTCHMMA` = tcgen05.mma, `UTMALDG` = TMA tensor load, `LDTM` = tcgen05.ld "
@@ -35,4 +63,10 @@ with open(os.path.join(ROOT, "profiles/sass_evidence.md"), "w") as f:
     for o, k, c in rows:
         f.write(f"| {o} | `{k}` | {c['total']} | {c['UTCHMMA']} | {c['UTMALDG']} | {c['LDTM']} | {c['UTCBAR']} | {c['SYNCS']} | "
                 f"{c['IMAD.WIDE.U32']} | {c['SHFL']} |\n")
-print(open(os.path.join(ROOT, "profiles/sass_evidence.md")).read())
+    f.write("\n## Loop bodies\n\nStraight from `cuobjdump -sass` (addresses are offsets inside the kernel).  `UTMALDG.2D` is the "
+            "`cp.async.bulk.tensor.2d` TMA load, `SYNCS.ARRIVE.TRANS64` / `SYNCS.PHASECHK` are the mbarrier expect-tx / "
+            "try-wait, `UTCHMMA` is `tcgen05.mma` (three per K step: hi*hi, hi*lo, lo*hi), `UTCBAR` is `tcgen05.commit`, "
+            "`LDTM` is `tcgen05.ld`.\n")
+    for o, k, what, ins in excerpts:
+        f.write(f"\n### `{k}` ({o}) - {what}\n\n```\n" + "\n".join(ins) + "\n```\n")
+print(open(os.path.join(ROOT, "profiles/sass_evidence.md")).read()[:6000])
