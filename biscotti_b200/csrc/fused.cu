@@ -98,7 +98,10 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
-  const int sub = FG_BM / P.Sr;   // TMA boxes (= owning ranks) per 128-row tile
+  // Sr <= 128: a 128-row tile is assembled from 128/Sr owners (one box of Sr rows each).  Sr a multiple of 128 (more
+  // than 128 peers per rank): a tile is one box of 128 rows out of one owner's plane, tpo tiles per owner.
+  const int sub = P.Sr >= FG_BM ? 1 : FG_BM / P.Sr;
+  const int tpo = P.Sr >= FG_BM ? P.Sr / FG_BM : 1;
 
   if (warp == 0) {
     if (lane == 0 && nkb > 0) {
@@ -113,17 +116,19 @@ __global__ void __launch_bounds__(FG_THREADS, 1) krum_gram_fused_kernel(const __
         mbar_expect_tx(bar_full + 8 * s, diag ? 2 * FG_TILE_BYTES : 4 * FG_TILE_BYTES);
         const int kx = (kb0 + kb) * FG_BK;
         for (int j = 0; j < sub; j++) {
-          const int owner = ti * sub + j;
+          const int owner = tpo > 1 ? ti / tpo : ti * sub + j;
+          const int y = tpo > 1 ? (ti % tpo) * FG_BM : 0;
           const uint32_t off = (uint32_t)j * P.Sr * 128u;   // Sr % 8 == 0 keeps every box on a 1024-B swizzle atom
-          tma_load_2d(st + off, &P.hi[owner], kx, 0, bar_full + 8 * s);
-          tma_load_2d(st + FG_TILE_BYTES + off, &P.lo[owner], kx, 0, bar_full + 8 * s);
+          tma_load_2d(st + off, &P.hi[owner], kx, y, bar_full + 8 * s);
+          tma_load_2d(st + FG_TILE_BYTES + off, &P.lo[owner], kx, y, bar_full + 8 * s);
         }
         if (!diag) {
           for (int j = 0; j < sub; j++) {
-            const int owner = tj * sub + j;
+            const int owner = tpo > 1 ? tj / tpo : tj * sub + j;
+            const int y = tpo > 1 ? (tj % tpo) * FG_BM : 0;
             const uint32_t off = (uint32_t)j * P.Sr * 128u;
-            tma_load_2d(st + 2 * FG_TILE_BYTES + off, &P.hi[owner], kx, 0, bar_full + 8 * s);
-            tma_load_2d(st + 3 * FG_TILE_BYTES + off, &P.lo[owner], kx, 0, bar_full + 8 * s);
+            tma_load_2d(st + 2 * FG_TILE_BYTES + off, &P.hi[owner], kx, y, bar_full + 8 * s);
+            tma_load_2d(st + 3 * FG_TILE_BYTES + off, &P.lo[owner], kx, y, bar_full + 8 * s);
           }
         }
       }
@@ -524,19 +529,21 @@ int bsc_symm_allgather_rows(void* const* dst_ptrs, void* const* flag_ptrs, const
 // [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
 // array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed once;
 // the counters only grow), seq: 1-based count of launches of this kernel on this rank.
-// world*Sr must be a multiple of 128 and Sr a multiple of 8.
+// world*Sr must be a multiple of 128; Sr a multiple of 8 that divides 128, or a multiple of 128 (more than 128 peers
+// per rank).
 int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world,
                         int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter,
                         unsigned int seq, unsigned long long epoch, void* stream) {
-  if (world < 1 || world > SYMM_MAX_WORLD || Sr % 8 != 0 || FG_BM % Sr != 0 || (world * Sr) % FG_BM != 0 ||
-      ldh % FG_BK != 0)
+  if (world < 1 || world > SYMM_MAX_WORLD || Sr % 8 != 0 || (FG_BM % Sr != 0 && Sr % FG_BM != 0) ||
+      (world * Sr) % FG_BM != 0 || ldh % FG_BK != 0)
     return -1;
+  const int box_rows = Sr < FG_BM ? Sr : FG_BM;
   GramFusedParams P;
   memset(&P, 0, sizeof(P));
   for (int q = 0; q < world; q++) {
-    int rc = make_plane_map(&P.hi[q], plane_hi[q], Sr, ldh, Sr);
+    int rc = make_plane_map(&P.hi[q], plane_hi[q], Sr, ldh, box_rows);
     if (rc) return rc;
-    rc = make_plane_map(&P.lo[q], plane_lo[q], Sr, ldh, Sr);
+    rc = make_plane_map(&P.lo[q], plane_lo[q], Sr, ldh, box_rows);
     if (rc) return rc;
     P.gpart.ptr[q] = gpart[q];
     P.flags.ptr[q] = flags[q];

@@ -82,8 +82,8 @@ class FusedComm(NcclComm):
         self.Sr = max(8, 128 // world)
         while self.Sr < self.per:
             self.Sr *= 2
-        if self.Sr > 128:
-            raise ValueError("fused Gram path supports at most 128 peers per rank")
+        if world * self.Sr > 1024:
+            raise ValueError("fused Krum path supports at most 1024 peer slots (the scoring tail sorts one row per CTA)")
         self.ldh = pad_to(d, 64)
         self.ntile = world * self.Sr // 128
         self.ldg = self.ntile * 128

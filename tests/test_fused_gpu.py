@@ -59,6 +59,26 @@ def test_fused_krum_and_secagg_world1_match_unfused_kernels():
     comm.close()
 
 
+def test_fused_krum_with_more_than_128_peers_per_rank():
+    """200 peers on one rank: 256 slots, two 128-row tiles out of one owner's plane (row-offset TMA boxes)."""
+    cfg = BiscottiConfig(num_nodes=200, dataset="mnist")
+    comm = FusedComm(0, 1, DEV, cfg)
+    assert comm.Sr == 256 and comm.ntile == 2
+    d, n = cfg.dim, 200
+    torch.manual_seed(1)
+    U = torch.zeros(n, ml.pad_to(d, 4), device=DEV)
+    U[:, :d] = torch.randn(n, d, device=DEV) * 0.05
+    U[150:, :d] += 0.2 * torch.arange(1, 51, device=DEV, dtype=torch.float32).unsqueeze(1)      # fifty outliers
+    noisers = torch.full((n, 1), -1, dtype=torch.int32, device=DEV)
+    ml.noise_mix(U, noisers, 1, 0, 0.0, d, out_hi=comm.hi, out_lo=comm.lo)
+    krum_set = sorted(torch.randperm(n)[:140].tolist())
+    clip = 70
+    _, acc = comm.krum_fused(krum_set, clip)
+    _, aref, _ = krum_ops.krum_reference(U[krum_set, :d].cpu(), clip)
+    assert acc.cpu().bool().tolist() == aref.tolist()
+    comm.close()
+
+
 def test_engine_with_fused_comm_world1_is_deterministic():
     cfg = BiscottiConfig(num_nodes=30, dataset="mnist", max_iterations=3, shard_size=100, test_size=300, msm_window=7,
                          data_sep=6.0)
