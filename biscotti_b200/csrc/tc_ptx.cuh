@@ -1,6 +1,6 @@
 // Inline-PTX building blocks for the tcgen05 / TMA kernels: mbarrier, cp.async.bulk.tensor, UMMA shared-memory
-// and instruction descriptors, tcgen05.mma / commit / ld, TMEM fences.  (gram_tc.cu carries its own copy of
-// the same helpers; this header serves the fused multi-GPU kernels.)
+// and instruction descriptors, tcgen05.mma / commit / ld, TMEM fences.  One copy for every tensor-core kernel
+// (gram_tc.cu, fused.cu, kernels_ml.cu).
 #pragma once
 #include <cuda.h>
 #include <stdint.h>
