@@ -580,6 +580,14 @@ class BiscottiEngine:
             ns.queue_back(ctx)
             if not self.fused:
                 self._last_ysum = self._ysum[ctx.par]
+            # The next block's local step and commitments need only the weights this block's back produces: queue them now,
+            # before the host sleeps on this block's read-back, so that they run while the host assembles the block.
+            ctx.npre = None
+            if cfg.lookahead:
+                nxt = self._next_inputs_ready(self._side)
+                if nxt is not False:
+                    ns.queue_local_and_eval(ctx.it + 1, None, False, inputs=nxt)
+                    ctx.npre = ns.queue_commit(ctx.it + 1)
             ctx.phases["host_queue"] = (time.perf_counter() - t0) * 1e3
             host = ns.collect()
             ctx.phases["host_wait"] = (time.perf_counter() - t0) * 1e3 - ctx.phases["host_queue"]
@@ -879,13 +887,11 @@ class BiscottiEngine:
             ph = ctx.phases
             tm = time.perf_counter
             t0 = tm()
-            nxt = self._next_inputs_ready(self._side) if cfg.lookahead else False
-            if nxt is not False:
-                # Order = what the NEXT tail waits for longest first: the next block's local step and commitments (their
-                # wire bytes are what the approvals sign), its plan and the approvals' T = v*G, this block's error rates (they
-                # must read the weights before the next SGD step), the next chain front, the approvals' last kernel.
-                ns.queue_local_and_eval(it + 1, rep, False, inputs=nxt)
-                npre = ns.queue_commit(it + 1)
+            npre = getattr(ctx, "npre", None)
+            if npre is not None:
+                # The next block's local step and commitments were queued before the tail (see _step).  Order of the rest =
+                # what the NEXT tail waits for longest first: the next plan and the approvals' T = v*G, this block's error
+                # rates (they must read the weights before the next SGD step), the next chain front, the approvals' last kernel.
                 t1 = tm()
                 nctx = self._begin_block_ahead()
                 t2 = tm()

@@ -58,6 +58,7 @@ class NativeSchedule:
         # ---- events
         ev = lambda: [NativeEvent(), NativeEvent()]   # noqa: E731
         self.u_ready, self.c_ready, self.plan_ready, self.sig_done, self.side_done = ev(), ev(), ev(), ev(), ev()
+        self.w_done = NativeEvent()       # the block's SGD step has been applied (recorded right behind the reconstruction)
         self.agg_done = ev()
         self.eval_done, self.collect_ev = NativeEvent(), NativeEvent()
         self.eval_host = [NativeEvent() for _ in range(4)]
@@ -173,7 +174,9 @@ class NativeSchedule:
 
         # ---- LOCAL ------------------------------------------------------------------------------------------------
         ix["local0"] = cl.n
-        cl.wait(SIDE, self.collect_ev)
+        # behind the previous block's SGD step (which is behind every reader of U on the chain stream) - not behind its
+        # read-back: the step of block t+1 is queued as soon as block t's back is, before the host waits for block t
+        cl.wait(SIDE, self.w_done)
         ix["mb"] = cl.add("sample_minibatch", SIDE, seed, 0, data.peer_ids, P, Ns, B, self.mb_idx)
         if eng.model.kind == "softmax":
             ix["step"] = cl.add("local_softmax_step", SIDE, eng.w32, data.X, data.y, self.mb_idx, eng.U, self.loss, P, Ns, B, F,
@@ -255,6 +258,7 @@ class NativeSchedule:
         else:
             ix["recon"] = cl.add("reconstruct_mat", MAIN, ysum, self.rm_fallback, av_d, self.S, 0, self.nchunk, d, scale4,
                                  eng.w64, eng.w32, None, eng._bad, n_con, 2)
+        ix["w_rec"] = cl.record(MAIN, self.w_done)
         ix["back_mid"] = cl.n
         cl.wait(MAIN, self.sig_done[par])
         pack = eng._pack[par]
@@ -563,7 +567,7 @@ class NativeSchedule:
                     secagg.reconstruct_step_dev(eng._ysum[par], pl.xs, self._view(par, self.o_xs, 10, torch.int32),
                                                 self._view(par, self.o_av, 64, torch.uint8)[: self.S], eng.d, eng.w64, eng.w32,
                                                 cfg.precision, bad=eng._bad, gate=eng._plan_out[par]["counts"][1:2], gate_min=2)
-                cl.run(ix["back_mid"], ix["back1"])
+                cl.run(ix["w_rec"], ix["back1"])
                 return True
             cl.patch(ix["recon"], 1, ctypes.addressof(rm))
         self.run(par, "back")
