@@ -76,7 +76,7 @@ def _unflatten(arch, w):
 
 def cnn_local_step(arch: dict, w32: torch.Tensor, Xb: torch.Tensor, yb: torch.Tensor, clip: float, out: torch.Tensor):
     """Per-peer minibatch gradients through torch.func (library convolution kernels).  The hand-written
-    sm_100a path for the one-conv models is ops.cnn (used automatically on CUDA when available)."""
+    sm_100a path is ops.cnn_native (used automatically on CUDA when available)."""
     from torch.func import functional_call, grad, vmap  # noqa: F401
 
     P, B = Xb.shape[0], Xb.shape[1]
@@ -132,7 +132,7 @@ class Model:
         Xb = torch.gather(X, 1, idx.long().unsqueeze(-1).expand(P, B, Fd))
         yb = torch.gather(y, 1, idx.long())
         if X.is_cuda:
-            from ..ops import cnn as cnn_ops
+            from ..ops import cnn_native as cnn_ops
 
             if cnn_ops.supports(self.kind):
                 return cnn_ops.local_step(self.kind, w32, Xb, yb, cfg.clip_norm, out)

@@ -12,6 +12,17 @@ from ._call import ptr, stream, check
 _scratch = {}
 
 
+def supports(kind: str) -> bool:
+    """True when the native kernels for this CNN are in the loaded library (models.registry falls back to the PyTorch
+    functional path otherwise - CPU runs and the CPU oracle)."""
+    if kind not in ("mnist_cnn", "cifar_cnn", "lfw_cnn"):
+        return False
+    try:
+        return hasattr(_native.load(), "bsc_cnn2_local_step" if kind == "lfw_cnn" else "bsc_cnn1_local_step")
+    except Exception:
+        return False
+
+
 def local_step(kind: str, w32: torch.Tensor, Xb: torch.Tensor, yb: torch.Tensor, clip: float, out: torch.Tensor):
     """Xb: [P, B, IC*H*W] minibatch, yb: [P, B] int32, out: [P, ldu] <- -clip(grad)."""
     from ..models.registry import CNN_ARCH
