@@ -130,6 +130,27 @@ def test_restart_from_saved_ledger_reproduces_uninterrupted_run(tmp_path):
     assert second.stake == straight.stake
 
 
+def test_cli_periodic_checkpoints_are_resumable(tmp_path, capsys):
+    """`--save-chain f --checkpoint-every K` leaves a loadable chain behind after every K blocks (written to a temporary
+    file and renamed), and `--resume f` continues from it to the chain of an uninterrupted run - what
+    deploy/fail_and_restart.sh relies on when it kills the job with SIGKILL."""
+    import os
+
+    from biscotti_b200 import cli
+    from biscotti_b200.ledger.chain import Blockchain
+
+    f = str(tmp_path / "chain.bin")
+    base = ["localtest", "10", "creditcard", "--device", "cpu", "--no-dump", "--print-hash"]
+    assert cli.main(base + ["--iterations", "5", "--save-chain", f, "--checkpoint-every", "2"]) == 0
+    first = capsys.readouterr().out
+    assert len(Blockchain.load(f)) == 7 and not [x for x in os.listdir(tmp_path) if ".tmp." in x]
+    assert cli.main(base + ["--iterations", "9", "--resume", f]) == 0
+    resumed = [l for l in capsys.readouterr().out.splitlines() if l.startswith("chain-hash")]
+    assert cli.main(base + ["--iterations", "9"]) == 0
+    straight = [l for l in capsys.readouterr().out.splitlines() if l.startswith("chain-hash")]
+    assert resumed and resumed == straight and "chain-hash" in first
+
+
 def test_prefetched_local_step_gives_the_same_chain():
     """Queuing iteration t+1's local step + commitments behind iteration t's aggregation (engine._prefetch_next)
     is a scheduling change only: the ledger is identical with and without it, also when minibatches are fed by the
