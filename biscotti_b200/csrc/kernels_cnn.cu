@@ -18,10 +18,12 @@
 // the ledger) is bit-reproducible.
 #include <string.h>
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace bsc {
 
 static bool g_cnn_generic = false;
+static bool g_cnn_wgrad_simt = false;
 
 struct Cnn1Shape {
   int IC, OC, K, pad, H, W;   // input channels, output channels, kernel, padding, input height/width
@@ -518,6 +520,206 @@ static int cnn1_eval_t(const float* w, const float* X, const int* y, int* wrong,
   return finish_launch("cnn1_eval", 3);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// The convolution's weight gradient on the tensor cores.  Per peer it is one small GEMM with a long reduction:
+//   G[oc][t] = sum over the B*OH*OW (image, position) pairs of  D[oc][pos] * X[t][pos],
+// D = d(pre-activation) (fp32, contiguous in pos: already K-major), X = im2col rows, one per tap t = (ic, ky, kx), plus
+// one row of ones whose column is the bias gradient.  One CTA per peer: the zero-padded images of its minibatch are
+// staged in shared memory once; per 64-position K block all threads write the bf16 hi / lo planes of both operands in
+// the 128B-swizzled K-major layout (D straight from global with the next block's loads in flight, im2col out of the
+// staged images), one thread issues the [128 x 32] += A * B^T UMMAs (hi*hi, hi*lo, lo*hi) into TMEM - the A tile is
+// declared 128 rows tall, rows past OC alias the bytes behind it and produce lanes nobody reads - and warp 0 reads the
+// OC result lanes at the end.  Two operand stages, recycled through tcgen05.commit -> mbarrier.
+// ---------------------------------------------------------------------------------------------------
+constexpr int WT_THREADS = 512;
+constexpr int WT_NB = 32;                                  // padded N: taps + the bias column
+constexpr int WT_AROWS = 24;                               // A rows staged per K block (OC <= 24): three swizzle atoms
+constexpr int WT_A_BYTES = WT_AROWS * 128;
+constexpr int WT_B_BYTES = WT_NB * 128;
+constexpr int WT_STAGE = 2 * WT_A_BYTES + 2 * WT_B_BYTES;  // A_hi | A_lo | B_hi | B_lo
+constexpr int WT_STAGES = 2;
+constexpr int WT_TAIL = 6 * 1024;                          // what the last A_lo's 128-row window reaches past its stage
+
+template <int IC, int K, int PAD, int OC>
+__global__ void __launch_bounds__(WT_THREADS, 1) cnn1_conv_wgrad_tc(const float* __restrict__ X, const float* __restrict__ dpre,
+                                                                    float* __restrict__ U, int ldu, float* __restrict__ partial,
+                                                                    int nslots, int slot0, Cnn1Shape s) {
+  constexpr int TAPS = IC * K * K;
+  static_assert(TAPS + 1 <= WT_NB && OC <= WT_AROWS, "shape does not fit the tile");
+  constexpr int A_ITEMS = OC * 16, B_ITEMS = (TAPS + 1) * 16, ITEMS = A_ITEMS + B_ITEMS;
+  constexpr int PER = (ITEMS + WT_THREADS - 1) / WT_THREADS;
+  extern __shared__ uint8_t wt_smem[];
+  __shared__ __align__(8) unsigned long long sBar[WT_STAGES + 1];
+  __shared__ uint32_t sTmem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, p = blockIdx.x;
+  const int HP = s.H + 2 * PAD, WP = s.W + 2 * PAD, IMG = IC * HP * WP;
+  const int npos = s.OH * s.OW, total = s.B * npos, nkb = (total + 63) / 64;
+  const uint32_t raw = smem_u32(wt_smem);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen = wt_smem + (base - raw);
+  float* sx = reinterpret_cast<float*>(gen + WT_STAGES * WT_STAGE + WT_TAIL);     // [B][IC][HP][WP]
+
+  if (tid == 0) {
+    for (int i = 0; i <= WT_STAGES; i++) mbar_init(smem_u32(&sBar[i]), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sTmem)), "r"(32)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int i = tid; i < s.B * IMG; i += WT_THREADS) sx[i] = 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sTmem;
+  {
+    const float* x = X + (size_t)p * s.B * IC * s.H * s.W;
+    const int per = IC * s.H * s.W;
+    for (int i = tid; i < s.B * per; i += WT_THREADS) {
+      const int b = i / per, r = i - b * per;
+      const int ix = r % s.W, iy = (r / s.W) % s.H, ic = r / (s.W * s.H);
+      sx[b * IMG + (ic * HP + iy + PAD) * WP + ix + PAD] = x[i];
+    }
+  }
+  __syncthreads();
+
+  // A thread owns the same PER (row, quad-of-positions) slots of every K block; only the positions move, by 64 per block.
+  // kind 0: a row of D (row = output channel), kind 1: an im2col row (row = tap), kind 2: the row of ones, 3: nothing.
+  const float* dp = dpre + (size_t)p * s.B * OC * npos;
+  int kind[PER], soff[PER], pos[PER], img[PER], oy[PER], ox[PER];
+  const float* arow[PER];
+  int xoff[PER];
+#pragma unroll
+  for (int u = 0; u < PER; u++) {
+    const int it = tid + u * WT_THREADS;
+    const int q = it & 15;
+    pos[u] = q << 2;                 // position inside the image, advanced below
+    img[u] = 0;
+    oy[u] = pos[u] / s.OW;
+    ox[u] = pos[u] - oy[u] * s.OW;
+    arow[u] = dp;
+    xoff[u] = 0;
+    if (it < A_ITEMS) {
+      kind[u] = 0;
+      soff[u] = (int)sw128_off(it >> 4, q, 0);
+      arow[u] = dp + (size_t)(it >> 4) * npos;              // + img * OC * npos + pos
+    } else if (it < ITEMS) {
+      const int t = (it - A_ITEMS) >> 4;
+      kind[u] = t == TAPS ? 2 : 1;
+      soff[u] = 2 * WT_A_BYTES + (int)sw128_off(t, q, 0);
+      const int tt = t < TAPS ? t : 0;
+      const int ic = tt / (K * K), ky = (tt / K) % K, kx = tt % K;
+      xoff[u] = (ic * HP + ky) * WP + kx;
+    } else {
+      kind[u] = 3;
+      soff[u] = 0;
+    }
+  }
+  const int d_oy = 64 / s.OW, d_ox = 64 - d_oy * s.OW;      // how 64 positions move (oy, ox)
+  auto load_a = [&](float4* v) {                             // D values of the block the indices point at
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (kind[u] == 0 && img[u] < s.B) v[u] = __ldg(reinterpret_cast<const float4*>(arow[u] + (size_t)img[u] * OC * npos + pos[u]));
+    }
+  };
+  float4 cur[PER];
+  load_a(cur);
+  const uint32_t idesc = umma_idesc_bf16_128xN(WT_NB);
+  for (int kb = 0; kb < nkb; kb++) {
+    const int st = kb % WT_STAGES;
+    const uint32_t so = (uint32_t)st * WT_STAGE;
+    // im2col values of this block (shared memory), before the indices move on
+    float4 xv[PER];
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+      xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (img[u] < s.B) {
+        if (kind[u] == 1) {
+          const float* xr = sx + img[u] * IMG + xoff[u] + oy[u] * WP + ox[u];   // OW % 4 == 0: the four positions share a row
+          xv[u] = make_float4(xr[0], xr[1], xr[2], xr[3]);
+        } else if (kind[u] == 2) {
+          xv[u] = make_float4(1.f, 1.f, 1.f, 1.f);             // the bias column: sum of D over the positions
+        }
+      }
+    }
+    // advance every slot by 64 positions, then start the next block's D loads (in flight during the conversion below)
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+      pos[u] += 64;
+      oy[u] += d_oy;
+      ox[u] += d_ox;
+      if (ox[u] >= s.OW) {
+        ox[u] -= s.OW;
+        oy[u]++;
+      }
+      if (pos[u] >= npos) {
+        pos[u] -= npos;
+        img[u]++;
+        oy[u] = pos[u] / s.OW;
+        ox[u] = pos[u] - oy[u] * s.OW;
+      }
+    }
+    float4 nxt[PER];
+    load_a(nxt);
+    if (kb >= WT_STAGES) mbar_wait(smem_u32(&sBar[st]), (uint32_t)(kb / WT_STAGES - 1) & 1u);   // the MMAs that read this stage
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+      if (kind[u] == 3) continue;
+      uint2 hi, lo;
+      split4(kind[u] == 0 ? cur[u] : xv[u], hi, lo);
+      const int pl = kind[u] == 0 ? WT_A_BYTES : WT_B_BYTES;
+      *reinterpret_cast<uint2*>(gen + so + soff[u]) = hi;
+      *reinterpret_cast<uint2*>(gen + so + soff[u] + pl) = lo;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint64_t a_hi = umma_desc_sw128(base + so), a_lo = umma_desc_sw128(base + so + WT_A_BYTES);
+      const uint64_t b_hi = umma_desc_sw128(base + so + 2 * WT_A_BYTES), b_lo = umma_desc_sw128(base + so + 2 * WT_A_BYTES + WT_B_BYTES);
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint64_t off = (uint64_t)((k * 16 * 2) >> 4);
+        umma_bf16(tmem, a_hi + off, b_hi + off, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        umma_bf16(tmem, a_hi + off, b_lo + off, idesc, 1u);
+        umma_bf16(tmem, a_lo + off, b_hi + off, idesc, 1u);
+      }
+      umma_commit(smem_u32(&sBar[st]));
+      if (kb == nkb - 1) umma_commit(smem_u32(&sBar[WT_STAGES]));
+    }
+#pragma unroll
+    for (int u = 0; u < PER; u++) cur[u] = nxt[u];
+  }
+  // ---- epilogue: lane = output channel, column = tap (column TAPS = bias) ------------------------------------
+  if (warp == 0) {
+    mbar_wait(smem_u32(&sBar[WT_STAGES]), 0);
+    tc_fence_after();
+    uint32_t v[32];
+    tmem_ld32(tmem, v);
+    if (lane < OC) {
+      float nrm = 0.f;
+      float* out = U + (size_t)p * ldu;
+#pragma unroll
+      for (int t = 0; t < TAPS; t++) {
+        const float g = __uint_as_float(v[t]);
+        out[s.off_cw + lane * TAPS + t] = -g;
+        nrm = fmaf(g, g, nrm);
+      }
+      const float gb = __uint_as_float(v[TAPS]);
+      out[s.off_cb + lane] = -gb;
+      partial[(size_t)p * nslots + slot0 + lane] = fmaf(gb, gb, nrm);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(32) : "memory");
+  }
+}
+
 template <int IC, int K, int PAD, int OC, int C>
 static int cnn1_local_step_t(const float* w, const float* X, const int* y, float* U, float* loss, float* act, float* dl,
                              float* partial, float* coef, float* fpart, int P, int ldu, float clip, const Cnn1Shape& s,
@@ -541,8 +743,18 @@ static int cnn1_local_step_t(const float* w, const float* X, const int* y, float
   cnn1_fc_fwd_t<C><<<dim3(nchunk, (PB + FCF_IMGS - 1) / FCF_IMGS), 256, smem_fc, st>>>(w, act, fpart, s, PB);
   cnn1_loss_kernel<<<(P + 3) / 4, 128, 0, st>>>(dl, y, loss, U, ldu, P, s, fpart, nchunk, w + s.off_fb, -1.f);
   cnn1_fc_bwd_t<C><<<dim3(nfc, P), 256, 0, st>>>(w, act, dl, U, ldu, partial, nslots, s);
-  cnn1_conv_wgrad_t<IC, K, PAD, OC><<<dim3((OC + WG_OCB - 1) / WG_OCB, P), 256, smem_wg, st>>>(X, act, U, ldu, partial, nslots,
-                                                                                             nfc, s);
+  const size_t smem_tc = 1024 + (size_t)WT_STAGES * WT_STAGE + WT_TAIL + (size_t)s.B * IC * HP * WP * sizeof(float);
+  if (!g_cnn_wgrad_simt && smem_tc <= 224 * 1024 && (s.OW & 3) == 0) {   // 227 KB per CTA minus the kernel's static shared memory
+    static bool configured_tc = false;
+    if (!configured_tc) {
+      BSC_CHECK(cudaFuncSetAttribute(cnn1_conv_wgrad_tc<IC, K, PAD, OC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+      configured_tc = true;
+    }
+    cnn1_conv_wgrad_tc<IC, K, PAD, OC><<<P, WT_THREADS, smem_tc, st>>>(X, act, U, ldu, partial, nslots, nfc, s);
+  } else {
+    cnn1_conv_wgrad_t<IC, K, PAD, OC><<<dim3((OC + WG_OCB - 1) / WG_OCB, P), 256, smem_wg, st>>>(X, act, U, ldu, partial, nslots,
+                                                                                               nfc, s);
+  }
   cnn1_coef_kernel<<<P, 256, 0, st>>>(U, ldu, partial, nslots, clip, coef, s);
   cnn1_scale_kernel<<<dim3((ldu + 4095) / 4096, P), 256, 0, st>>>(U, ldu, coef, s, 1);
   return finish_launch("cnn1_local_step", 7);
@@ -728,6 +940,8 @@ extern "C" {
 
 // test hook: 1 = keep the one-conv models on the generic kernels (the shape-specialised ones are compared against them)
 void bsc_cnn_force_generic(int on) { g_cnn_generic = on != 0; }
+// test hook: 1 = conv weight gradient on the SIMT kernel instead of the tensor-core one
+void bsc_cnn_force_wgrad_simt(int on) { g_cnn_wgrad_simt = on != 0; }
 
 // scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P],
 // fpart [ceil(J/1024)][P*B][C]

@@ -3,6 +3,7 @@
 // (gram_tc.cu, fused.cu, kernels_ml.cu).
 #pragma once
 #include <cuda.h>
+#include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -83,6 +84,38 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
       : "r"(taddr)
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+
+// ---- operands staged by the CTA itself (no TMA): fp32 -> bf16 hi / lo planes in the 128B-swizzled K-major layout -------
+__device__ __forceinline__ uint32_t umma_idesc_bf16_128xN(uint32_t n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// fp32 x4 -> bf16 hi x4 and bf16 lo x4 (lo = bf16(x - hi)), packed as two 8-byte words
+__device__ __forceinline__ void split4(const float4 v, uint2& hi, uint2& lo) {
+  const __nv_bfloat162 h01 = __float22bfloat162_rn(make_float2(v.x, v.y)), h23 = __float22bfloat162_rn(make_float2(v.z, v.w));
+  const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+  const __nv_bfloat162 l01 = __float22bfloat162_rn(make_float2(v.x - f01.x, v.y - f01.y)),
+                       l23 = __float22bfloat162_rn(make_float2(v.z - f23.x, v.w - f23.y));
+  hi.x = *reinterpret_cast<const uint32_t*>(&h01);
+  hi.y = *reinterpret_cast<const uint32_t*>(&h23);
+  lo.x = *reinterpret_cast<const uint32_t*>(&l01);
+  lo.y = *reinterpret_cast<const uint32_t*>(&l23);
+}
+// byte offset of columns [4q, 4q+4) of row r inside a plane whose 64-column K blocks are kb_bytes apart
+__device__ __forceinline__ uint32_t sw128_off(int r, int q, int kb_bytes) {
+  const int kb = q >> 4, c = (q & 15) >> 1, half = (q & 1) << 3;
+  return (uint32_t)(kb * kb_bytes + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4) + half);
 }
 
 

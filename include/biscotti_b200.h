@@ -453,7 +453,8 @@ int bsc_symm_allgather_rows(void* const* dst_ptrs, void* const* flag_ptrs, const
 // [world][ldg][ldg] fp32 reduction buffer (slot r receives rank r's reduced partial), flags[q]: rank q's flag
 // array, lpart: local scratch [ksplit][npairs][128*128] fp32, done_counter: local uint32[1 + npairs] (zeroed once;
 // the counters only grow), seq: 1-based count of launches of this kernel on this rank.
-// world*Sr must be a multiple of 128 and Sr a multiple of 8.
+// world*Sr must be a multiple of 128; Sr a multiple of 8 that divides 128, or a multiple of 128 (more than 128 peers
+// per rank).
 int bsc_krum_gram_fused(void* const* plane_hi, void* const* plane_lo, void* const* gpart, void* const* flags, int world, int rank, int Sr, int ldh, int ksplit, int ldg, float* lpart, unsigned int* done_counter, unsigned int seq, unsigned long long epoch, void* stream);
 
 int bsc_krum_select_fused(const float* gpart_local, int nsplit, int ldg, const int* rows, int n, int clip, const void* my_flags, int world, unsigned long long epoch, float* scores, unsigned char* accept, void* stream);
@@ -491,6 +492,9 @@ void bsc_schnorr_finish64_host(const unsigned char* T64, const unsigned char* k_
  * -------------------------------------------------------------------------------------------- */
 // test hook: 1 = keep the one-conv models on the generic kernels (the shape-specialised ones are compared against them)
 void bsc_cnn_force_generic(int on);
+
+// test hook: 1 = conv weight gradient on the SIMT kernel instead of the tensor-core one
+void bsc_cnn_force_wgrad_simt(int on);
 
 // scratch: act [P*B*J] floats, dl [P*B*C], partial [P*nslots] with nslots = ceil(J/256) + OC, coef [P],
 // fpart [ceil(J/1024)][P*B][C]

@@ -351,7 +351,9 @@ def test_cnn_shape_specialised_kernels_match_generic_kernels(lib, kind):
     cnn_native.local_step(kind, w, Xb, yb, 100.0, b)
     torch.cuda.synchronize()
     scale = float(a.abs().max())
-    assert scale > 0 and torch.allclose(a, b, rtol=1e-4, atol=1e-6 * max(1.0, scale)), float((a - b).abs().max())
+    # (the conv weight gradient of the specialised path is a bf16 hi/lo tensor-core GEMM over 12 960 positions: ~2^-16
+    # relative per product, the same bound the autograd comparison uses)
+    assert scale > 0 and torch.allclose(a, b, rtol=1e-3, atol=2e-5 * max(1.0, scale)), float((a - b).abs().max())
 
 
 @pytest.mark.parametrize("kind", ["mnist_cnn", "cifar_cnn"])
