@@ -129,3 +129,36 @@ def test_fork_repair_replaces_an_empty_block_reached_from_the_engine():
     a.step()
     b.step()
     assert a.chain == b.chain and a.chain.verify()
+
+
+def test_synthetic_data_models_and_poisoned_shards():
+    """Both generators give per-peer shards of the reference's shapes; a poisoner's shard holds nothing but source-class
+    rows carrying the target label (mnist_bad, parse_mnist.py:295-301), and poisoners are the ids above
+    ceil(N * (1 - po)) (main.go:836-844).  On "lowrank" data rows of one class are close to each other and far from
+    the other classes, which is what lets Multi-Krum see a poisoner; on "blobs" data they are not."""
+    import torch
+
+    from biscotti_b200.config import BiscottiConfig
+    from biscotti_b200.data.synthetic import make_data, poisoner_ids
+    from biscotti_b200.ops import krum as krum_ops, ml
+
+    for model in ("blobs", "lowrank"):
+        cfg = BiscottiConfig(num_nodes=20, dataset="mnist", shard_size=60, test_size=200, poison_fraction=0.3, data_model=model)
+        assert poisoner_ids(cfg) == {15, 16, 17, 18, 19}
+        d = make_data(cfg, list(range(20)))
+        assert d.X.shape == (20, 60, 784) and d.y.shape == (20, 60) and d.X_test.shape == (200, 784)
+        assert bool(d.poisoned[15]) and not bool(d.poisoned[14])
+        assert (d.y[15:] == 7).all() and (d.y_attack == 1).all()
+        assert len(set(d.y[0].tolist())) > 3                       # honest shards mix the classes
+    # lowrank: the poisoned rows are class-1 rows (nearest class mean is that of class 1)
+    cfg = BiscottiConfig(num_nodes=20, dataset="mnist", shard_size=60, test_size=400, poison_fraction=0.3, data_model="lowrank")
+    d = make_data(cfg, list(range(20)))
+    means = torch.stack([d.X_test[d.y_test == c].mean(0) for c in range(10)])
+    nearest = torch.cdist(d.X[15], means).argmin(dim=1)
+    assert (nearest == 1).float().mean() > 0.8
+    # ... and with no DP noise Multi-Krum rejects exactly the poisoners' updates at the zero model
+    w = torch.zeros(cfg.dim)
+    idx = torch.arange(10, dtype=torch.int32).repeat(20, 1)
+    U, _ = ml.softmax_step(w, d.X, d.y, idx, 10, 100.0)
+    _, acc, _ = krum_ops.krum_reference(U[:, : cfg.dim], 10)
+    assert not acc[15:].any() and int(acc.sum()) == 10
