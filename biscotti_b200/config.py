@@ -121,6 +121,7 @@ class BiscottiConfig:
     data_dir: str | None = None       # directory of <dataset><i>.npy shards (data/files.py); None = synthetic data
     prefetch: bool = True             # queue iteration t+1's local step + commitment MSM behind iteration t's
                                       # aggregation kernel so the device is busy while the host assembles block t
+    ring_depth: int = 3               # slots of the ring of per-block device buffers / events / command lists (>= 2)
     pipeline: bool = True             # GPU: the block's dependency chain on a high-priority stream, everything off the
                                       # chain (witness MSM, miners' aggregation, error rates, next local step +
                                       # commitments) on a second stream, the approvals on a third.  False = one stream,

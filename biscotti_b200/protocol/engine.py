@@ -193,7 +193,11 @@ class BiscottiEngine:
         self._main = self._side = self._wit = self._agg = None   # chain / off-chain / witness / aggregation streams (pipelined GPU)
         self._wstream = None                    # alias of _side, kept for callers that look for the witness stream
         self._wevent = None
-        self._side_done = [None, None]          # per block parity: off-chain work of that block has finished
+        # Ring depth of everything a block owns on the device (plan outputs, commitments, share sums, packs, events, command
+        # lists): block t reuses the slot of block t - NB, and may only do so once that block's off-chain work (witnesses,
+        # miners' aggregates) has read it.  With two slots that wait sat on the chain of every other block.
+        self.NB = max(2, int(getattr(cfg, "ring_depth", 3)))
+        self._side_done = [None] * self.NB      # per ring slot: off-chain work of that block has finished
         self._eval_done = None
         self.last_aggregate = None
         self.keys = cp.derive_peer_keys(n, cfg.seed)
@@ -230,7 +234,7 @@ class BiscottiEngine:
         # Nonce salt of the approvals: binds the run (seed, data, every flag) - the previous block hash binds the fork.
         # (Scheduling knobs - prefetch, pipeline, kernel choices - do not change what is signed and stay out of it.)
         sched = {"prefetch", "pipeline", "gram_impl", "comm_impl", "msm_window", "msm_table_gb", "affine_wire", "eval_every", "extra",
-                 "max_iterations", "test_size", "lookahead", "native_schedule"}
+                 "max_iterations", "test_size", "lookahead", "native_schedule", "ring_depth"}
         self.run_salt = hashlib.sha256(("bsc-run-salt|" + repr(sorted((k, v) for k, v in cfg.to_dict().items()
                                                                         if k not in sched))).encode()).digest()
         self.nsig_max = cfg.num_verifiers if self.signer is not None else 0
@@ -308,13 +312,13 @@ class BiscottiEngine:
         nk = max(1, self.cfg.num_nodes)
         i32 = dict(dtype=torch.int32, device=dev)
         self._plan_out = [dict(counts=torch.zeros(8, **i32), contrib_pos=torch.zeros(nk, **i32), sel=torch.zeros(P, **i32),
-                               appr_local=torch.zeros(P, **i32), csel=torch.zeros(P, **i32)) for _ in range(2)]
-        self._cbytes = [torch.zeros(P, 64, dtype=torch.uint8, device=dev) for _ in range(2)]
-        self._pack = [torch.zeros(self.per, self.pack_stride, dtype=torch.uint8, device=dev) for _ in range(2)]
-        self._ysum = [torch.zeros(self.cfg.nchunk, self.S, dtype=torch.int64, device=dev) for _ in range(2)]
+                               appr_local=torch.zeros(P, **i32), csel=torch.zeros(P, **i32)) for _ in range(self.NB)]
+        self._cbytes = [torch.zeros(P, 64, dtype=torch.uint8, device=dev) for _ in range(self.NB)]
+        self._pack = [torch.zeros(self.per, self.pack_stride, dtype=torch.uint8, device=dev) for _ in range(self.NB)]
+        self._ysum = [torch.zeros(self.cfg.nchunk, self.S, dtype=torch.int64, device=dev) for _ in range(self.NB)]
         self._bad = self.comm.bad if self.fused else torch.zeros(4, dtype=torch.int32, device=dev)
         self._noiser_tab = torch.full((P, max(1, self.cfg.num_noisers)), -1, **i32)
-        self._plan_keep = [None, None]
+        self._plan_keep = [None] * self.NB
         self._bufs_ready = True
 
     def _native(self):
@@ -470,7 +474,7 @@ class BiscottiEngine:
                 chunkC = self.commit.chunk_commitments(Q, affine=cfg.affine_wire)    # [P, nchunk, 16|24]
                 full = self.commit.full_commitments(chunkC)                          # affine [P, 16]
                 self._ensure_bufs()
-                cb = self._cbytes[out["it"] & 1]
+                cb = self._cbytes[out["it"] % self.NB]
                 self.commit.to_bytes_into(full, cb)                                  # [P, 64] wire bytes, on the device
                 out.update(Q=Q, chunkC=chunkC, cbytes=cb)
                 if dev.type == "cuda" and self.pipelined:
@@ -632,7 +636,7 @@ class BiscottiEngine:
         self._t_plan_host = (time.perf_counter() - t_p0) * 1e3
         krum_set = pl.krum_set
         nk = len(krum_set)
-        ctx = _Ctx(it=it, par=it & 1, pl=pl, nk=nk, phases={}, alive=list(self.alive), stake=list(self.stake),
+        ctx = _Ctx(it=it, par=it % self.NB, pl=pl, nk=nk, phases={}, alive=list(self.alive), stake=list(self.stake),
                    timing=self._timing, pipelined=self.pipelined)
         n_workers = pl.n_workers if ns is not None else len(pl.workers)
         ctx.rep = BlockReport(it, b"", True, pl.verifiers, pl.miners, n_workers, nk, 0, 0)

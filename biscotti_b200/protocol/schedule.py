@@ -56,7 +56,8 @@ class NativeSchedule:
         streams = [eng._main, eng._side, eng.signer.stream if eng.signer is not None else eng._side, eng._wit, eng._agg]
         self.streams = streams
         # ---- events
-        ev = lambda: [NativeEvent(), NativeEvent()]   # noqa: E731
+        NB = self.NB = eng.NB                     # ring depth of the per-block buffers, events and command lists
+        ev = lambda: [NativeEvent() for _ in range(NB)]   # noqa: E731
         self.u_ready, self.c_ready, self.plan_ready, self.sig_done, self.side_done = ev(), ev(), ev(), ev(), ev()
         self.w_done = NativeEvent()       # the block's SGD step has been applied (recorded right behind the reconstruction)
         self.agg_done = ev()
@@ -79,7 +80,7 @@ class NativeSchedule:
         self.plan_bytes = off
         self.plan_pinned = [torch.zeros(off, dtype=torch.uint8).pin_memory() for _ in range(4)]
         self.plan_np = [b.numpy() for b in self.plan_pinned]
-        self.plan_dev = [torch.zeros(off, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.plan_dev = [torch.zeros(off, dtype=torch.uint8, device=dev) for _ in range(NB)]
         self._plan_views = []
         for b in self.plan_np:
             def vw(o, cnt, dt, b=b):
@@ -121,15 +122,15 @@ class NativeSchedule:
             self.Gpart = torch.zeros(gmax, dtype=torch.float32, device=dev)
         C = eng.commit
         self.dpad, self.nchunk, self.S = C.dpad, C.nchunk, eng.S
-        self.Q = [torch.zeros(P, C.dpad, dtype=torch.int64, device=dev) for _ in range(2)]
-        self.chunkC = [torch.zeros(P, C.nchunk, JAC, **i32) for _ in range(2)]
+        self.Q = [torch.zeros(P, C.dpad, dtype=torch.int64, device=dev) for _ in range(NB)]
+        self.chunkC = [torch.zeros(P, C.nchunk, JAC, **i32) for _ in range(NB)]
         self.fullJ = torch.zeros(P, JAC, **i32)
         self.fullA = torch.zeros(P, AFF, **i32)
         self.wrows = min(P, cfg.krum_thresh)
         self.W = torch.zeros(self.wrows, C.nchunk * eng.S, JAC, **i32)
         self.aggQ = torch.zeros(1, C.dpad, dtype=torch.int64, device=dev)
-        self.aggW = [torch.zeros(C.nchunk * eng.S, JAC, **i32) for _ in range(2)]
-        self.aggC = [torch.zeros(C.nchunk, JAC, **i32) for _ in range(2)]
+        self.aggW = [torch.zeros(C.nchunk * eng.S, JAC, **i32) for _ in range(NB)]
+        self.aggC = [torch.zeros(C.nchunk, JAC, **i32) for _ in range(NB)]
         if eng.signer is not None:
             eng.signer._ensure(n * self.nv)
         self.salt = (ctypes.c_ubyte * 64)()
@@ -144,7 +145,7 @@ class NativeSchedule:
         self.h_pack = torch.zeros(rows, eng.pack_stride, dtype=torch.uint8).pin_memory()
         self.d2h_bytes = (self.h_w.numel() * 8 + 16 + 32 + 4 * n + rows * eng.pack_stride + 8)
         eng._ensure_eval_slots()
-        self.cl = [self._build(par) for par in (0, 1)]
+        self.cl = [self._build(par) for par in range(NB)]
 
     # ------------------------------------------------------------------------------------------------------------------
     def _view(self, par, off, n, dtype):
@@ -350,7 +351,7 @@ class NativeSchedule:
         """Behind block `it_next - 1`: the next block's local step (minibatches drawn from the resident shards, or the
         caller's `inputs` = (X [P,B,F], y [P,B])), then the error rates of the new weights."""
         eng = self.eng
-        par = it_next & 1
+        par = it_next % self.NB
         cl = self.cl[par]
         ix = cl.ix
         slot = it_next % NOISE_TABLE_ITERS
@@ -517,7 +518,7 @@ class NativeSchedule:
     def queue_commit(self, it: int) -> dict:
         """Commitments of block `it`'s updates (side stream, right behind its local step).  Returns the block's `pre` record."""
         eng = self.eng
-        par = it & 1
+        par = it % self.NB
         self.run(par, "commit")
         return {"it": it, "Q": self.Q[par], "chunkC": self.chunkC[par], "cbytes": eng._cbytes[par], "u_ready": None,
                 "c_ready": None, "src": self._last_src, "native": True}
