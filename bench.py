@@ -111,6 +111,10 @@ class ClockSampler(threading.Thread):
                 pass
             self._stop_evt.wait(self.period)
 
+    def arm(self):
+        """Start of the timed region: forget what was sampled during the warm-up."""
+        self.samples, self.reasons = [], set()
+
     def stop(self):
         self._stop_evt.set()
         if self.ok:
@@ -191,13 +195,16 @@ def main():
         torch.cuda.synchronize(dev)
 
     # ---------------- device-timed arm: resident shards, CUDA events per step --------------------
+    # The NVML thread starts before the warm-up (library start-up and the first calls' symbol look-ups cost milliseconds of
+    # interpreter time); what it sampled before the timed region is dropped at arm().
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(args.warmup):
         eng.step()
     barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
+    sampler.arm()
     L.bsc_launch_count_reset()
-    evs = []
+    evs, wall_seq = [], []
     wall0 = time.perf_counter()
     e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e_start.record()
@@ -206,7 +213,9 @@ def main():
             flush.zero_()                               # L2 flush between timed iterations (not timed)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        tw = time.perf_counter()
         eng.step()
+        wall_seq.append(round((time.perf_counter() - tw) * 1e3, 3))
         e1.record()
         evs.append((e0, e1))
     eng.join_streams()        # the closing event sits behind everything the K steps queued, off-chain work included
@@ -214,7 +223,8 @@ def main():
     barrier()
     wall = time.perf_counter() - wall0
     launches = int(L.bsc_launch_count())
-    step_ms = sorted(a.elapsed_time(b) for a, b in evs)
+    step_seq = [round(a.elapsed_time(b), 3) for a, b in evs]     # in order: shows where a slow step sits
+    step_ms = sorted(step_seq)
     dev_ms = e_start.elapsed_time(e_end)     # ONE interval around the K steps: no untimed gaps between steps
     t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -362,7 +372,8 @@ def main():
                         for k in ("host_queue", "host_wait", "host_tail_py", "block", "h_append", "host_after", "h_local_eval",
                                   "h_plan", "h_plan_host", "h_plan_upload", "h_front", "h_commit_sign", "h_witness", "total_host")},
             "step_ms": {"min": step_ms[0], "median": step_ms[len(step_ms) // 2],
-                        "p95": step_ms[min(len(step_ms) - 1, int(0.95 * len(step_ms)))], "max": step_ms[-1]},
+                        "p95": step_ms[min(len(step_ms) - 1, int(0.95 * len(step_ms)))], "max": step_ms[-1],
+                        "in_order": step_seq, "host_wall_in_order": wall_seq},
             "last_block": {"contributors": last.n_contributors, "accepted": last.n_accepted, "krum_set": last.n_krum,
                            "test_error": last.test_error, "empty": last.empty},
         }

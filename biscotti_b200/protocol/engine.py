@@ -333,6 +333,13 @@ class BiscottiEngine:
             if self._ns_ok:
                 torch.cuda.synchronize(self.device)
                 self._ns = NativeSchedule(self)
+                # Everything built so far (torch, the data, the tables, the command lists) lives as long as the engine: move it
+                # out of the garbage collector's young generations, so that a full collection in the middle of a run walks
+                # the few objects a block creates instead of the whole heap (a ~1 ms stall of the block loop otherwise).
+                import gc
+
+                gc.collect()
+                gc.freeze()
         return self._ns
 
     def _ensure_eval_slots(self):

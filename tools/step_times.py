@@ -16,10 +16,15 @@ cfg = BiscottiConfig(num_nodes=100, dataset="mnist", max_iterations=n + 4, ring_
 eng = BiscottiEngine(cfg, device="cuda:0")
 torch.cuda.synchronize()
 ts = []
+sync_at = int(os.environ.get("SYNC_AT", "-1"))
 for i in range(n):
+    if i == sync_at:
+        torch.cuda.synchronize()
     t0 = time.perf_counter()
     eng.step()
     ts.append((time.perf_counter() - t0) * 1e3)
+    if i in (sync_at, sync_at + 1):
+        print("AFTER_SYNC step", i, {k: round(v, 3) for k, v in eng.reports[-1].phase_ms.items()})
 eng.join_streams()
 print("ring", ring, "chain", None)
 print("STEP_MS " + " ".join(f"{t:.2f}" for t in ts))
