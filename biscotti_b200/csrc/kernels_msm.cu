@@ -17,6 +17,7 @@
 // batched-inversion trick.
 #include <stdlib.h>
 #include "common.cuh"
+#include <mutex>
 #include "g1.cuh"
 
 namespace bsc {
@@ -309,17 +310,36 @@ __global__ void __launch_bounds__(128) g1_sum_rows_jac_kernel(const G1Jac* __res
   for (int q = 0; q < nsel; q++) acc = g1j_add(acc, pts[(size_t)sel[q] * G + g]);
   out[g] = acc;
 }
-__global__ void __launch_bounds__(128) g1_sum_cols_jac_kernel(const G1Jac* __restrict__ pts, int G,
-                                                              G1Jac* __restrict__ out) {
+// Column sum in two stages: grid (P, S) CTAs each tree-reduce a slice of <= 128 points of one row (one point per thread,
+// no serial prefix), then one warp per row adds the S partial sums.  The single-stage version (one CTA per row, six
+// serial additions per thread before the tree) occupied 100 of 148 SMs with four warps each and sat on the path
+// commitments -> approvals -> read-back of every block.
+__global__ void __launch_bounds__(128) g1_sum_cols_jac_part_kernel(const G1Jac* __restrict__ pts, int G, int per,
+                                                                   G1Jac* __restrict__ part) {
   __shared__ G1Jac sh[128];
-  const int p = blockIdx.x, tid = threadIdx.x;
+  const int p = blockIdx.x, sl = blockIdx.y, tid = threadIdx.x;
+  const int g0 = sl * per, g1 = min(G, g0 + per);
   G1Jac acc = g1j_inf();
-  for (int g = tid; g < G; g += blockDim.x) acc = g1j_add(acc, pts[(size_t)p * G + g]);
+  for (int g = g0 + tid; g < g1; g += blockDim.x) acc = g1j_add(acc, pts[(size_t)p * G + g]);
   sh[tid] = acc;
   __syncthreads();
   for (int s = blockDim.x >> 1; s > 0; s >>= 1) {
     if (tid < s) sh[tid] = g1j_add(sh[tid], sh[tid + s]);
     __syncthreads();
+  }
+  if (tid == 0) part[(size_t)p * gridDim.y + sl] = sh[0];
+}
+__global__ void __launch_bounds__(32) g1_sum_cols_jac_final_kernel(const G1Jac* __restrict__ part, int S,
+                                                                   G1Jac* __restrict__ out) {
+  __shared__ G1Jac sh[32];
+  const int p = blockIdx.x, tid = threadIdx.x;
+  G1Jac acc = g1j_inf();
+  for (int q = tid; q < S; q += 32) acc = g1j_add(acc, part[(size_t)p * S + q]);
+  sh[tid] = acc;
+  __syncwarp();
+  for (int s = 16; s > 0; s >>= 1) {
+    if (tid < s && tid + s < S) sh[tid] = g1j_add(sh[tid], sh[tid + s]);
+    __syncwarp();
   }
   if (tid == 0) out[p] = sh[0];
 }
@@ -466,10 +486,33 @@ int bsc_g1_sum_rows_jac_dc(const void* pts_jac, const int* sel, int nsel, const 
 int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream) {
   return bsc_g1_sum_rows_jac_dc(pts_jac, sel, nsel, nullptr, G, out_jac, stream);
 }
+// (workspace for the partial sums: grown on demand, one per device, kept for the life of the process; the first call
+// on a device - or one with a larger P * ceil(G/128) than any before - allocates, so make it outside stream capture)
 int bsc_g1_sum_cols_jac(const void* pts_jac, int P, int G, void* out_jac, void* stream) {
   if (P == 0) return 0;
-  g1_sum_cols_jac_kernel<<<P, 128, 0, (cudaStream_t)stream>>>((const G1Jac*)pts_jac, G, (G1Jac*)out_jac);
-  return finish_launch("g1_sum_cols_jac");
+  static std::mutex mu;
+  static G1Jac* ws[64] = {nullptr};
+  static size_t ws_n[64] = {0};
+  int dev = 0;
+  BSC_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return -2;
+  const int S = (G + 127) / 128, per = (G + S - 1) / S;
+  const size_t need = (size_t)P * S;
+  G1Jac* part;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (ws_n[dev] < need) {
+      if (ws[dev]) BSC_CHECK(cudaFree(ws[dev]));
+      ws[dev] = nullptr;
+      ws_n[dev] = 0;
+      BSC_CHECK(cudaMalloc((void**)&ws[dev], need * sizeof(G1Jac)));
+      ws_n[dev] = need;
+    }
+    part = ws[dev];
+  }
+  g1_sum_cols_jac_part_kernel<<<dim3(P, S), 128, 0, (cudaStream_t)stream>>>((const G1Jac*)pts_jac, G, per, part);
+  g1_sum_cols_jac_final_kernel<<<P, 32, 0, (cudaStream_t)stream>>>(part, S, (G1Jac*)out_jac);
+  return finish_launch("g1_sum_cols_jac", 2);
 }
 void bsc_g1_sum_rows_jac_host(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac) {
   const G1Jac* pts = (const G1Jac*)pts_jac;
