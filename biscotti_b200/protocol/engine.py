@@ -1243,6 +1243,7 @@ class BiscottiEngine:
         if self.device.type == "cuda":
             import gc
 
+            gc.unfreeze()          # what _native() froze goes back under the collector, so this engine's cycles can be reclaimed
             gc.collect()
             torch.cuda.empty_cache()
 
