@@ -120,6 +120,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("bsc_ed25519_scalarmult_batch", c_i, c_p, c_p, c_i, c_i, c_p, c_p)
     sig("bsc_ed25519_scalarmult_batch_host", None, c_p, c_p, c_i, c_i, c_p)
     sig("bsc_vrf_hash_to_curve_xy", None, c_cp, c_sz, c_p)
+    sig("bsc_vrf_launch", c_i, c_cp, c_i, c_p, c_p, c_p, c_i, c_p, c_i, c_p, c_p)
     sig("bsc_ed25519_scalarmult_r25", c_i, c_p, c_p, c_i, c_p, c_p)
     sig("bsc_ed25519_scalarmult_quad", c_i, c_p, c_p, c_i, c_p, c_p)
     sig("bsc_ed25519_scalarmult_quad_xyz", c_i, c_p, c_p, c_i, c_p, c_p)

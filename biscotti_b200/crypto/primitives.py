@@ -207,15 +207,14 @@ class BatchedVRF:
         i = self._di
         self._di += 1
         hp, hd, xyz, ev = self._dh_pinned[i % 4], self._dhd[i % 4], self._dxyz[i % 2], self._dev[i % 2]
-        L.bsc_vrf_hash_to_curve_xy(msg, len(msg), ctypes.c_void_p(hp.data_ptr()))
-        with torch.cuda.stream(self._dside):
-            hd.copy_(hp, non_blocking=True)
-            fn = L.bsc_ed25519_scalarmult_quad_xyz if self.kernel == "quad4" else L.bsc_ed25519_scalarmult_wide_xyz
-            rc = fn(ctypes.c_void_p(self.scalars.data_ptr()), ctypes.c_void_p(hd.data_ptr()), n,
-                    ctypes.c_void_p(xyz.data_ptr()), ctypes.c_void_p(self._dside.cuda_stream))
-            if rc:
-                raise RuntimeError("ed25519 scalar multiplication kernel failed")
-            ev.record(self._dside)
+        # one native call: hash-to-curve on the host, 64-byte upload, the kernel, the event record (this sits between the
+        # block hash and the next block's chain, every microsecond of interpreter here is on the critical path)
+        rc = L.bsc_vrf_launch(msg, len(msg), ctypes.c_void_p(hp.data_ptr()), ctypes.c_void_p(hd.data_ptr()),
+                              ctypes.c_void_p(self.scalars.data_ptr()), n, ctypes.c_void_p(xyz.data_ptr()),
+                              0 if self.kernel == "quad4" else 1, ctypes.c_void_p(self._dside.cuda_stream),
+                              ctypes.c_void_p(ev.handle))
+        if rc:
+            raise RuntimeError(f"VRF launch failed with code {rc}")
         return (xyz, ev, msg)
 
     def noiser_table(self, handle, stake: list[int], is_worker: np.ndarray, want: int) -> np.ndarray:

@@ -667,6 +667,19 @@ int bsc_ed25519_scalarmult_wide_xyz(const unsigned char* scalars, const unsigned
       scalars, hxy, N, xyz_out);
   return finish_launch("ed25519_scalarmult_wide_xyz");
 }
+// The head of a block's chain in one call: hash-to-curve of the previous block hash on the host (into a pinned 64-byte
+// buffer), its upload, the scalar multiplication of every peer (wide != 0: warp-wide kernel, else four lanes per peer)
+// and, when `event` is given, a record behind the kernel.  h_pinned must stay untouched until the copy has run.
+int bsc_vrf_launch(const uint8_t* msg, int len, uint8_t* h_pinned, void* h_dev, const unsigned char* scalars, int N,
+                   int* xyz_out, int wide, void* stream, void* event) {
+  bsc_vrf_hash_to_curve_xy(msg, (size_t)len, h_pinned);
+  BSC_CHECK(cudaMemcpyAsync(h_dev, h_pinned, 64, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  const int rc = wide ? bsc_ed25519_scalarmult_wide_xyz(scalars, (const unsigned char*)h_dev, N, xyz_out, stream)
+                      : bsc_ed25519_scalarmult_quad_xyz(scalars, (const unsigned char*)h_dev, N, xyz_out, stream);
+  if (rc) return rc;
+  if (event) BSC_CHECK(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return 0;
+}
 // host: compress N projective points with a single field inversion (prefix products)
 void bsc_ed25519_compress_batch(const int* xyz, int N, unsigned char* out) {
   std::vector<F25> pre((size_t)N);

@@ -165,6 +165,8 @@ int bsc_g1_sum_rows_jac_dc(const void* pts_jac, const int* sel, int nsel, const 
 
 int bsc_g1_sum_rows_jac(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac, void* stream);
 
+// (workspace for the partial sums: grown on demand, one per device, kept for the life of the process; the first call
+// on a device - or one with a larger P * ceil(G/128) than any before - allocates, so make it outside stream capture)
 int bsc_g1_sum_cols_jac(const void* pts_jac, int P, int G, void* out_jac, void* stream);
 
 void bsc_g1_sum_rows_jac_host(const void* pts_jac, const int* sel, int nsel, long long G, void* out_jac);
@@ -227,6 +229,11 @@ int bsc_ed25519_scalarmult_quad_xyz(const unsigned char* scalars, const unsigned
 
 // warp-wide latency kernel (one peer per warp, one limb per lane); same contract as the quad _xyz entry point
 int bsc_ed25519_scalarmult_wide_xyz(const unsigned char* scalars, const unsigned char* hxy, int N, int* xyz_out, void* stream);
+
+// The head of a block's chain in one call: hash-to-curve of the previous block hash on the host (into a pinned 64-byte
+// buffer), its upload, the scalar multiplication of every peer (wide != 0: warp-wide kernel, else four lanes per peer)
+// and, when `event` is given, a record behind the kernel.  h_pinned must stay untouched until the copy has run.
+int bsc_vrf_launch(const uint8_t* msg, int len, uint8_t* h_pinned, void* h_dev, const unsigned char* scalars, int N, int* xyz_out, int wide, void* stream, void* event);
 
 // host: compress N projective points with a single field inversion (prefix products)
 void bsc_ed25519_compress_batch(const int* xyz, int N, unsigned char* out);
