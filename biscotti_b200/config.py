@@ -90,7 +90,8 @@ class BiscottiConfig:
     msm_table_gb: float | None = None # HBM budget of the MSM window tables in GiB (None = half of the device; the
                                       # BISCOTTI_MSM_TABLE_GB environment variable overrides both).  The constructor
                                       # picks the widest table layout that fits: two-width (13,8) / (12,9) / (11,10) bit
-                                      # windows, then uniform 7..3 bit windows
+                                      # windows, then uniform 7..3 bit windows; 0 = no tables: every MSM runs window-free
+                                      # (Straus over the bases themselves, `msm_groups_kernel`), memory = the bases only
     affine_wire: bool = False         # True: normalise every chunk commitment / witness to the 64-byte affine
                                       # wire form (kyber.go:88-168) even though no wire exists between GPUs
     data_sep: float = 3.6             # synthetic data: distance scale of the class prototypes.  3.6 makes the ten classes

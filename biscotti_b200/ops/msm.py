@@ -61,6 +61,7 @@ class CommitmentEngine:
         # "two-width tables").  self.nw carries (count | w1 << 8) for the kernels; self.nwin / self.w1 are the plain values.
         self.w = self.nw = self.nwin = self.w1 = 0
         self.c_table = self.w_table = None
+        self.table_bytes = 0
         nbases = self.dpad + self.wtable.shape[0]
         need = max_scalar_bits + 1
 
@@ -88,7 +89,7 @@ class CommitmentEngine:
             # Widest first window that fits the budget, with narrow windows above it: ~99 % of a clipped update's fixed-point
             # coordinates are below 2^12, so a 13-bit first window makes a term ONE mixed addition; the rare larger values
             # take a second addition from an 8-bit window.  Fall back to uniform windows when even that does not fit.
-            if self.device.type == "cuda":
+            if self.device.type == "cuda" and table_budget_bytes > 0:     # budget 0: no tables at all (msm_groups_kernel)
                 for w0, w1 in ((13, 8), (12, 9), (11, 10)):
                     lay = layout(w0, w1)
                     if nbases * lay[2] * 64 <= table_budget_bytes:

@@ -43,3 +43,16 @@ def test_fedsys_mode_on_gpu():
     e = BiscottiEngine(cfg, device="cuda:0")
     reps = e.run()
     assert reps[-1].test_error < reps[0].test_error
+
+
+def test_table_free_msm_mode_gives_the_same_chain():
+    """msm_table_gb = 0: no window tables, every commitment / witness MSM runs window-free over the bases themselves
+    (msm_groups_kernel) - the mode for models whose tables would not fit.  Same group elements, same ledger."""
+    a = BiscottiEngine(_cfg(), device="cuda:0")
+    b = BiscottiEngine(_cfg(msm_window=None, msm_table_gb=0.0), device="cuda:0")
+    assert a.commit.c_table is not None and b.commit.c_table is None and b.commit.w_table is None
+    a.run()
+    b.run()
+    assert a.chain == b.chain and b.chain.verify()
+    a.close()
+    b.close()
